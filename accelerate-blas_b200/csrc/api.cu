@@ -1,0 +1,359 @@
+// api.cu -- extern "C" surface of libaccblas_b200.so (include/accblas_b200.h):
+// argument validation, shape derivation, kernel-family dispatch, host-buffer entry points.
+// There is NO CPU fallback anywhere in this file: every path ends in a kernel launch on
+// the caller's stream or in an error status.
+#include "common.cuh"
+#include <cstdio>
+#include <cstring>
+#include <algorithm>
+
+namespace accblas {
+
+thread_local uint64_t g_launches = 0;
+thread_local char g_cuda_err[256] = {0};
+thread_local int g_gemm_path = 0;
+
+int cuda_fail(cudaError_t e, const char *where)
+{
+    snprintf(g_cuda_err, sizeof(g_cuda_err), "%s: %s (%s)", where, cudaGetErrorName(e), cudaGetErrorString(e));
+    return ACCBLAS_ERR_CUDA;
+}
+
+namespace {
+struct DevInfo { int sms = 0; int cc_major = 0; };
+DevInfo &dev_info()
+{
+    static thread_local DevInfo cache[64];
+    static thread_local DevInfo none;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return none;
+    DevInfo &d = cache[dev];
+    if (d.sms == 0) {
+        cudaDeviceGetAttribute(&d.sms, cudaDevAttrMultiProcessorCount, dev);
+        cudaDeviceGetAttribute(&d.cc_major, cudaDevAttrComputeCapabilityMajor, dev);
+    }
+    return d;
+}
+}  // namespace
+
+int sm_count() { int s = dev_info().sms; return s > 0 ? s : 148; }
+int device_check() { return dev_info().cc_major == 10 ? ACCBLAS_OK : ACCBLAS_ERR_ARCH; }
+
+namespace {
+
+bool bad_dtype(int d) { return d < ACCBLAS_F32 || d > ACCBLAS_C64; }
+bool bad_op(int o) { return o < ACCBLAS_OP_N || o > ACCBLAS_OP_H; }
+
+bool overlaps(const void *a, size_t na, const void *b, size_t nb)
+{
+    if (!a || !b || na == 0 || nb == 0) return false;
+    const uintptr_t a0 = (uintptr_t)a, b0 = (uintptr_t)b;
+    return a0 < b0 + nb && b0 < a0 + na;
+}
+
+// shape derivation shared by the device and host entry points (LLVM/PTX/Level3.hs:54-65)
+int derive_gemm(GemmArgs &g)
+{
+    if (bad_dtype(g.dtype)) return ACCBLAS_ERR_DTYPE;
+    if (bad_op(g.opA) || bad_op(g.opB)) return ACCBLAS_ERR_OP;
+    if (g.rowsA < 0 || g.colsA < 0 || g.rowsB < 0 || g.colsB < 0) return ACCBLAS_ERR_SHAPE;
+    g.m = g.opA == ACCBLAS_OP_N ? g.rowsA : g.colsA;
+    g.k = g.opA == ACCBLAS_OP_N ? g.colsA : g.rowsA;
+    g.n = g.opB == ACCBLAS_OP_N ? g.colsB : g.rowsB;
+    const int64_t kb = g.opB == ACCBLAS_OP_N ? g.rowsB : g.colsB;
+    if (g.k != kb) return ACCBLAS_ERR_SHAPE;     // the reference never checks this
+    if (!is_complex(g.dtype)) {                  // H on a real type is T (BLAS/Level3.hs:100,110)
+        if (g.opA == ACCBLAS_OP_H) g.opA = ACCBLAS_OP_T;
+        if (g.opB == ACCBLAS_OP_H) g.opB = ACCBLAS_OP_T;
+    }
+    return ACCBLAS_OK;
+}
+
+enum Family { FAM_NONE, FAM_GENERIC, FAM_DMMA, FAM_TC };
+
+Family pick_family(const GemmArgs &g)
+{
+    if (g.m == 0 || g.n == 0) return FAM_NONE;
+    if (g_gemm_path == 1) return FAM_GENERIC;
+    if ((g.dtype == ACCBLAS_F64 || g.dtype == ACCBLAS_C64) && dgemm_dmma_eligible(g)) return FAM_DMMA;
+    if ((g.dtype == ACCBLAS_F32 || g.dtype == ACCBLAS_C32) && sgemm_tc_eligible(g)) return FAM_TC;
+    return FAM_GENERIC;
+}
+
+int gemm_device(GemmArgs &g)
+{
+    ACC_TRY(derive_gemm(g));
+    if (g.m == 0 || g.n == 0) return ACCBLAS_OK;                       // nothing to write
+    if (!g.C || !g.alpha) return ACCBLAS_ERR_NULL;
+    const size_t es = elem_size(g.dtype);
+    if (g.k == 0) {                                                    // alpha * (empty sum) = 0
+        ACC_CUDA(cudaMemsetAsync(g.C, 0, es * (size_t)g.m * (size_t)g.n, g.stream));
+        return ACCBLAS_OK;
+    }
+    if (!g.A || !g.B) return ACCBLAS_ERR_NULL;
+    const size_t bytesC = es * (size_t)g.m * (size_t)g.n;
+    if (overlaps(g.C, bytesC, g.A, es * (size_t)g.rowsA * (size_t)g.colsA) ||
+        overlaps(g.C, bytesC, g.B, es * (size_t)g.rowsB * (size_t)g.colsB))
+        return ACCBLAS_ERR_ALIAS;
+    ACC_TRY(device_check());
+    const Family f = pick_family(g);
+    if (g_gemm_path == 2 && f == FAM_GENERIC) return ACCBLAS_ERR_SHAPE;
+    switch (f) {
+    case FAM_DMMA: return dgemm_dmma(g);
+    case FAM_TC:   return sgemm_tc(g);
+    default:       return gemm_generic(g);
+    }
+}
+
+// RAII for stream-ordered scratch used by the host-buffer entry points
+struct Scratch {
+    void *p = nullptr;
+    cudaStream_t s;
+    explicit Scratch(cudaStream_t st) : s(st) {}
+    cudaError_t alloc(size_t bytes) { return cudaMallocAsync(&p, bytes ? bytes : 1, s); }
+    ~Scratch() { if (p) cudaFreeAsync(p, s); }
+};
+
+}  // namespace
+}  // namespace accblas
+
+using namespace accblas;
+
+extern "C" {
+
+int accblas_version(void) { return ACCBLAS_B200_VERSION; }
+
+const char *accblas_status_string(int s)
+{
+    switch (s) {
+    case ACCBLAS_OK: return "ok";
+    case ACCBLAS_ERR_DTYPE: return "unknown dtype";
+    case ACCBLAS_ERR_OP: return "unknown transpose op";
+    case ACCBLAS_ERR_SHAPE: return "shape mismatch";
+    case ACCBLAS_ERR_NULL: return "null pointer with non-empty extent";
+    case ACCBLAS_ERR_CUDA: return "CUDA error";
+    case ACCBLAS_ERR_ARCH: return "device is not sm_100 (B200)";
+    case ACCBLAS_ERR_WORKSPACE: return "workspace too small or misaligned";
+    case ACCBLAS_ERR_ALIAS: return "output aliases an input";
+    default: return "unknown status";
+    }
+}
+
+const char *accblas_last_cuda_error(void) { return g_cuda_err; }
+uint64_t accblas_launch_count(void) { return g_launches; }
+void accblas_set_gemm_path(int path) { g_gemm_path = (path >= 0 && path <= 2) ? path : 0; }
+
+int accblas_gemm(accblas_stream_t stream, int dtype, int opA, int opB, int64_t rowsA, int64_t colsA,
+                 int64_t rowsB, int64_t colsB, const void *alpha_host, const void *A, const void *B, void *C)
+{
+    GemmArgs g{};
+    g.dtype = dtype; g.opA = opA; g.opB = opB;
+    g.rowsA = rowsA; g.colsA = colsA; g.rowsB = rowsB; g.colsB = colsB;
+    g.alpha = alpha_host; g.A = A; g.B = B; g.C = C;
+    g.stream = static_cast<cudaStream_t>(stream);
+    return gemm_device(g);
+}
+
+const char *accblas_gemm_kernel_name(int dtype, int opA, int opB, int64_t rowsA, int64_t colsA,
+                                     int64_t rowsB, int64_t colsB)
+{
+    GemmArgs g{};
+    g.dtype = dtype; g.opA = opA; g.opB = opB;
+    g.rowsA = rowsA; g.colsA = colsA; g.rowsB = rowsB; g.colsB = colsB;
+    if (derive_gemm(g) != ACCBLAS_OK) return "invalid";
+    switch (pick_family(g)) {
+    case FAM_NONE: return "none";
+    case FAM_DMMA: return g.dtype == ACCBLAS_F64 ? "dgemm_dmma_tma" : "zgemm_dmma_tma";
+    case FAM_TC:   return g.dtype == ACCBLAS_F32 ? "sgemm_tf32x3_tcgen05" : "cgemm_tf32x3_tcgen05";
+    default:       return "gemm_simt_generic";
+    }
+}
+
+size_t accblas_gemm_workspace_bytes(int dtype, int opA, int opB, int64_t rowsA, int64_t colsA,
+                                    int64_t rowsB, int64_t colsB)
+{
+    GemmArgs g{};
+    g.dtype = dtype; g.opA = opA; g.opB = opB;
+    g.rowsA = rowsA; g.colsA = colsA; g.rowsB = rowsB; g.colsB = colsB;
+    if (derive_gemm(g) != ACCBLAS_OK) return 0;
+    return pick_family(g) == FAM_TC ? sgemm_tc_workspace(g) : 0;
+}
+
+int accblas_gemv(accblas_stream_t stream, int dtype, int opA, int64_t rowsA, int64_t colsA,
+                 const void *alpha_host, const void *A, const void *x, int64_t lenx, void *y)
+{
+    if (bad_dtype(dtype)) return ACCBLAS_ERR_DTYPE;
+    if (bad_op(opA)) return ACCBLAS_ERR_OP;
+    if (rowsA < 0 || colsA < 0 || lenx < 0) return ACCBLAS_ERR_SHAPE;
+    const int64_t need = opA == ACCBLAS_OP_N ? colsA : rowsA;
+    const int64_t leny = opA == ACCBLAS_OP_N ? rowsA : colsA;   // LLVM/PTX/Level2.hs:80-82
+    if (lenx != need) return ACCBLAS_ERR_SHAPE;
+    if (leny == 0) return ACCBLAS_OK;
+    if (!y || !alpha_host) return ACCBLAS_ERR_NULL;
+    if (need > 0 && (!A || !x)) return ACCBLAS_ERR_NULL;
+    const size_t es = elem_size(dtype);
+    if (overlaps(y, es * (size_t)leny, A, es * (size_t)rowsA * (size_t)colsA) ||
+        overlaps(y, es * (size_t)leny, x, es * (size_t)lenx))
+        return ACCBLAS_ERR_ALIAS;
+    ACC_TRY(device_check());
+    if (!is_complex(dtype) && opA == ACCBLAS_OP_H) opA = ACCBLAS_OP_T;
+    return gemv_dispatch(static_cast<cudaStream_t>(stream), dtype, opA, rowsA, colsA, alpha_host, A, x, y);
+}
+
+int accblas_dot(accblas_stream_t stream, int dtype, int conj_x, int64_t n, const void *x, const void *y,
+                void *out_dev)
+{
+    if (bad_dtype(dtype)) return ACCBLAS_ERR_DTYPE;
+    if (n < 0) return ACCBLAS_ERR_SHAPE;
+    if (!out_dev) return ACCBLAS_ERR_NULL;
+    if (n > 0 && (!x || !y)) return ACCBLAS_ERR_NULL;
+    ACC_TRY(device_check());
+    return dot_dispatch(static_cast<cudaStream_t>(stream), dtype, conj_x, n, x, y, out_dev);
+}
+
+// -------------------------------------------------------------------------------------
+// host-buffer entry points (upload -> kernels -> download, all on `stream`)
+// -------------------------------------------------------------------------------------
+int accblas_gemm_host(accblas_stream_t stream, int dtype, int opA, int opB, int64_t rowsA, int64_t colsA,
+                      int64_t rowsB, int64_t colsB, const void *alpha_host, const void *A_host,
+                      const void *B_host, void *C_host)
+{
+    GemmArgs g{};
+    g.dtype = dtype; g.opA = opA; g.opB = opB;
+    g.rowsA = rowsA; g.colsA = colsA; g.rowsB = rowsB; g.colsB = colsB;
+    g.alpha = alpha_host;
+    g.stream = static_cast<cudaStream_t>(stream);
+    ACC_TRY(derive_gemm(g));
+    if (g.m == 0 || g.n == 0) return ACCBLAS_OK;
+    if (!C_host || !alpha_host) return ACCBLAS_ERR_NULL;
+    if (g.k > 0 && (!A_host || !B_host)) return ACCBLAS_ERR_NULL;
+    const size_t es = elem_size(dtype);
+    const size_t bytesA = es * (size_t)rowsA * (size_t)colsA, bytesB = es * (size_t)rowsB * (size_t)colsB;
+    const size_t bytesC = es * (size_t)g.m * (size_t)g.n;
+    cudaStream_t s = g.stream;
+    Scratch dA(s), dB(s), dC(s);
+    ACC_CUDA(dA.alloc(bytesA));
+    ACC_CUDA(dB.alloc(bytesB));
+    ACC_CUDA(dC.alloc(bytesC));
+
+    // Row-panel pipeline when op(A) = A: panel p of A uploads on a side stream while panel
+    // p-1 multiplies, and finished panels of C download behind the next multiply.
+    const int64_t panels = (g.opA == ACCBLAS_OP_N && g.k > 0 && g.m >= 2048) ? std::min<int64_t>(8, g.m / 1024) : 1;
+    if (panels <= 1) {
+        if (bytesA) ACC_CUDA(cudaMemcpyAsync(dA.p, A_host, bytesA, cudaMemcpyHostToDevice, s));
+        if (bytesB) ACC_CUDA(cudaMemcpyAsync(dB.p, B_host, bytesB, cudaMemcpyHostToDevice, s));
+        g.A = dA.p; g.B = dB.p; g.C = dC.p;
+        g.opA = opA; g.opB = opB;
+        ACC_TRY(gemm_device(g));
+        ACC_CUDA(cudaMemcpyAsync(C_host, dC.p, bytesC, cudaMemcpyDeviceToHost, s));
+        ACC_CUDA(cudaStreamSynchronize(s));
+        return ACCBLAS_OK;
+    }
+
+    cudaStream_t up = nullptr, down = nullptr;
+    ACC_CUDA(cudaStreamCreateWithFlags(&up, cudaStreamNonBlocking));
+    ACC_CUDA(cudaStreamCreateWithFlags(&down, cudaStreamNonBlocking));
+    cudaEvent_t ev_start, ev_b, ev_up[8], ev_mm[8], ev_done;
+    cudaEventCreateWithFlags(&ev_start, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&ev_b, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&ev_done, cudaEventDisableTiming);
+    for (int i = 0; i < 8; ++i) {
+        cudaEventCreateWithFlags(&ev_up[i], cudaEventDisableTiming);
+        cudaEventCreateWithFlags(&ev_mm[i], cudaEventDisableTiming);
+    }
+    int status = ACCBLAS_OK;
+    cudaEventRecord(ev_start, s);                 // allocations are ordered on s
+    cudaStreamWaitEvent(up, ev_start, 0);
+    cudaStreamWaitEvent(down, ev_start, 0);
+    cudaMemcpyAsync(dB.p, B_host, bytesB, cudaMemcpyHostToDevice, up);
+    cudaEventRecord(ev_b, up);
+    const int64_t rows_per = ((g.m + panels - 1) / panels + 127) / 128 * 128;
+    int np = 0;
+    for (int64_t r0 = 0; r0 < g.m; r0 += rows_per, ++np) {
+        const int64_t rows = std::min<int64_t>(rows_per, g.m - r0);
+        const char *ah = static_cast<const char *>(A_host) + es * (size_t)r0 * (size_t)colsA;
+        char *ad = static_cast<char *>(dA.p) + es * (size_t)r0 * (size_t)colsA;
+        cudaMemcpyAsync(ad, ah, es * (size_t)rows * (size_t)colsA, cudaMemcpyHostToDevice, up);
+        cudaEventRecord(ev_up[np], up);
+    }
+    np = 0;
+    cudaStreamWaitEvent(s, ev_b, 0);
+    for (int64_t r0 = 0; r0 < g.m && status == ACCBLAS_OK; r0 += rows_per, ++np) {
+        const int64_t rows = std::min<int64_t>(rows_per, g.m - r0);
+        cudaStreamWaitEvent(s, ev_up[np], 0);
+        GemmArgs p = g;
+        p.opA = opA; p.opB = opB;
+        p.rowsA = rows;
+        p.A = static_cast<char *>(dA.p) + es * (size_t)r0 * (size_t)colsA;
+        p.B = dB.p;
+        p.C = static_cast<char *>(dC.p) + es * (size_t)r0 * (size_t)g.n;
+        status = gemm_device(p);
+        cudaEventRecord(ev_mm[np], s);
+        cudaStreamWaitEvent(down, ev_mm[np], 0);
+        cudaMemcpyAsync(static_cast<char *>(C_host) + es * (size_t)r0 * (size_t)g.n, p.C,
+                        es * (size_t)rows * (size_t)g.n, cudaMemcpyDeviceToHost, down);
+    }
+    cudaEventRecord(ev_done, down);
+    cudaStreamWaitEvent(s, ev_done, 0);
+    cudaError_t e = cudaStreamSynchronize(s);
+    cudaError_t e2 = cudaStreamSynchronize(up);
+    cudaEventDestroy(ev_start); cudaEventDestroy(ev_b); cudaEventDestroy(ev_done);
+    for (int i = 0; i < 8; ++i) { cudaEventDestroy(ev_up[i]); cudaEventDestroy(ev_mm[i]); }
+    cudaStreamDestroy(up); cudaStreamDestroy(down);
+    if (status != ACCBLAS_OK) return status;
+    if (e != cudaSuccess) return cuda_fail(e, "accblas_gemm_host sync");
+    if (e2 != cudaSuccess) return cuda_fail(e2, "accblas_gemm_host sync(up)");
+    return ACCBLAS_OK;
+}
+
+int accblas_gemv_host(accblas_stream_t stream, int dtype, int opA, int64_t rowsA, int64_t colsA,
+                      const void *alpha_host, const void *A_host, const void *x_host, int64_t lenx,
+                      void *y_host)
+{
+    if (bad_dtype(dtype)) return ACCBLAS_ERR_DTYPE;
+    if (bad_op(opA)) return ACCBLAS_ERR_OP;
+    if (rowsA < 0 || colsA < 0 || lenx < 0) return ACCBLAS_ERR_SHAPE;
+    const int64_t need = opA == ACCBLAS_OP_N ? colsA : rowsA;
+    const int64_t leny = opA == ACCBLAS_OP_N ? rowsA : colsA;
+    if (lenx != need) return ACCBLAS_ERR_SHAPE;
+    if (leny == 0) return ACCBLAS_OK;
+    if (!y_host || !alpha_host || (need > 0 && (!A_host || !x_host))) return ACCBLAS_ERR_NULL;
+    const size_t es = elem_size(dtype);
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    Scratch dA(s), dx(s), dy(s);
+    ACC_CUDA(dA.alloc(es * (size_t)rowsA * (size_t)colsA));
+    ACC_CUDA(dx.alloc(es * (size_t)lenx));
+    ACC_CUDA(dy.alloc(es * (size_t)leny));
+    if (need > 0) {
+        ACC_CUDA(cudaMemcpyAsync(dA.p, A_host, es * (size_t)rowsA * (size_t)colsA, cudaMemcpyHostToDevice, s));
+        ACC_CUDA(cudaMemcpyAsync(dx.p, x_host, es * (size_t)lenx, cudaMemcpyHostToDevice, s));
+    }
+    ACC_TRY(accblas_gemv(stream, dtype, opA, rowsA, colsA, alpha_host, dA.p, dx.p, lenx, dy.p));
+    ACC_CUDA(cudaMemcpyAsync(y_host, dy.p, es * (size_t)leny, cudaMemcpyDeviceToHost, s));
+    ACC_CUDA(cudaStreamSynchronize(s));
+    return ACCBLAS_OK;
+}
+
+int accblas_dot_host(accblas_stream_t stream, int dtype, int conj_x, int64_t n, const void *x_host,
+                     const void *y_host, void *out_host)
+{
+    if (bad_dtype(dtype)) return ACCBLAS_ERR_DTYPE;
+    if (n < 0) return ACCBLAS_ERR_SHAPE;
+    if (!out_host || (n > 0 && (!x_host || !y_host))) return ACCBLAS_ERR_NULL;
+    const size_t es = elem_size(dtype);
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    Scratch dx(s), dy(s), dout(s);
+    ACC_CUDA(dx.alloc(es * (size_t)n));
+    ACC_CUDA(dy.alloc(es * (size_t)n));
+    ACC_CUDA(dout.alloc(es));
+    if (n > 0) {
+        ACC_CUDA(cudaMemcpyAsync(dx.p, x_host, es * (size_t)n, cudaMemcpyHostToDevice, s));
+        ACC_CUDA(cudaMemcpyAsync(dy.p, y_host, es * (size_t)n, cudaMemcpyHostToDevice, s));
+    }
+    ACC_TRY(accblas_dot(stream, dtype, conj_x, n, dx.p, dy.p, dout.p));
+    ACC_CUDA(cudaMemcpyAsync(out_host, dout.p, es, cudaMemcpyDeviceToHost, s));
+    ACC_CUDA(cudaStreamSynchronize(s));
+    return ACCBLAS_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,143 @@
+// common.cuh -- shared device/host helpers for libaccblas_b200.so (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+#include "../../include/accblas_b200.h"
+
+namespace accblas {
+
+// ----------------------------------------------------------------------------------
+// per-thread bookkeeping (the library itself is stateless: these are diagnostics)
+// ----------------------------------------------------------------------------------
+extern thread_local uint64_t g_launches;      // kernels enqueued by this thread
+extern thread_local char g_cuda_err[256];     // text of the last CUDA failure
+extern thread_local int g_gemm_path;          // accblas_set_gemm_path
+
+int cuda_fail(cudaError_t e, const char *where);   // records text, returns ACCBLAS_ERR_CUDA
+inline int check_launch(const char *where) {
+    ++g_launches;
+    cudaError_t e = cudaPeekAtLastError();
+    return e == cudaSuccess ? ACCBLAS_OK : cuda_fail(cudaGetLastError(), where);
+}
+#define ACC_CUDA(call)                                                     \
+    do {                                                                   \
+        cudaError_t _e = (call);                                           \
+        if (_e != cudaSuccess) return ::accblas::cuda_fail(_e, #call);     \
+    } while (0)
+#define ACC_TRY(call)                                                      \
+    do {                                                                   \
+        int _s = (call);                                                   \
+        if (_s != ACCBLAS_OK) return _s;                                   \
+    } while (0)
+
+int sm_count();                                  // SMs of the current device (cached per device)
+int device_check();                              // ACCBLAS_OK iff current device is CC 10.x
+
+inline size_t elem_size(int dtype) {
+    return dtype == ACCBLAS_F32 ? 4 : dtype == ACCBLAS_C64 ? 16 : 8;
+}
+inline bool is_complex(int dtype) { return dtype == ACCBLAS_C32 || dtype == ACCBLAS_C64; }
+
+// ----------------------------------------------------------------------------------
+// scalar algebra over the four element types: float, double, float2, double2
+// ----------------------------------------------------------------------------------
+template <typename T> struct Scalar;
+template <> struct Scalar<float> {
+    using real = float; static constexpr bool cplx = false;
+    __host__ __device__ static inline float zero() { return 0.f; }
+};
+template <> struct Scalar<double> {
+    using real = double; static constexpr bool cplx = false;
+    __host__ __device__ static inline double zero() { return 0.0; }
+};
+template <> struct Scalar<float2> {
+    using real = float; static constexpr bool cplx = true;
+    __host__ __device__ static inline float2 zero() { return make_float2(0.f, 0.f); }
+};
+template <> struct Scalar<double2> {
+    using real = double; static constexpr bool cplx = true;
+    __host__ __device__ static inline double2 zero() { return make_double2(0.0, 0.0); }
+};
+
+__device__ __forceinline__ float  fma_acc(float a, float b, float c) { return fmaf(a, b, c); }
+__device__ __forceinline__ double fma_acc(double a, double b, double c) { return fma(a, b, c); }
+__device__ __forceinline__ float2 fma_acc(float2 a, float2 b, float2 c) {
+    c.x = fmaf(a.x, b.x, c.x); c.x = fmaf(-a.y, b.y, c.x);
+    c.y = fmaf(a.x, b.y, c.y); c.y = fmaf(a.y, b.x, c.y);
+    return c;
+}
+__device__ __forceinline__ double2 fma_acc(double2 a, double2 b, double2 c) {
+    c.x = fma(a.x, b.x, c.x); c.x = fma(-a.y, b.y, c.x);
+    c.y = fma(a.x, b.y, c.y); c.y = fma(a.y, b.x, c.y);
+    return c;
+}
+__device__ __forceinline__ float  mul_s(float a, float b) { return a * b; }
+__device__ __forceinline__ double mul_s(double a, double b) { return a * b; }
+__device__ __forceinline__ float2 mul_s(float2 a, float2 b) {
+    return make_float2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x);
+}
+__device__ __forceinline__ double2 mul_s(double2 a, double2 b) {
+    return make_double2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x);
+}
+__device__ __forceinline__ float  add_s(float a, float b) { return a + b; }
+__device__ __forceinline__ double add_s(double a, double b) { return a + b; }
+__device__ __forceinline__ float2 add_s(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
+__device__ __forceinline__ double2 add_s(double2 a, double2 b) { return make_double2(a.x + b.x, a.y + b.y); }
+__device__ __forceinline__ float  conj_s(float a) { return a; }
+__device__ __forceinline__ double conj_s(double a) { return a; }
+__device__ __forceinline__ float2 conj_s(float2 a) { return make_float2(a.x, -a.y); }
+__device__ __forceinline__ double2 conj_s(double2 a) { return make_double2(a.x, -a.y); }
+
+__device__ __forceinline__ float  shfl_xor_s(float v, int m) { return __shfl_xor_sync(0xffffffffu, v, m); }
+__device__ __forceinline__ double shfl_xor_s(double v, int m) { return __shfl_xor_sync(0xffffffffu, v, m); }
+__device__ __forceinline__ float2 shfl_xor_s(float2 v, int m) {
+    return make_float2(__shfl_xor_sync(0xffffffffu, v.x, m), __shfl_xor_sync(0xffffffffu, v.y, m));
+}
+__device__ __forceinline__ double2 shfl_xor_s(double2 v, int m) {
+    return make_double2(__shfl_xor_sync(0xffffffffu, v.x, m), __shfl_xor_sync(0xffffffffu, v.y, m));
+}
+template <typename T> __device__ __forceinline__ T warp_sum(T v) {
+#pragma unroll
+    for (int m = 16; m > 0; m >>= 1) v = add_s(v, shfl_xor_s(v, m));
+    return v;
+}
+
+// 128-bit streaming load (read once: do not allocate in L1)
+__device__ __forceinline__ int4 ldg_stream(const void *p) {
+    int4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.s32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    return r;
+}
+// 128-bit cached load (re-used operand such as the gemv vector)
+__device__ __forceinline__ int4 ldg_cached(const void *p) {
+    return __ldg(reinterpret_cast<const int4 *>(p));
+}
+
+// ----------------------------------------------------------------------------------
+// kernel-family entry points (one translation unit each)
+// ----------------------------------------------------------------------------------
+struct GemmArgs {
+    int dtype, opA, opB;
+    int64_t rowsA, colsA, rowsB, colsB;   // stored (pre-op) shapes
+    int64_t m, n, k;                      // derived: C is m x n, inner extent k
+    const void *alpha;                    // host pointer, one element
+    const void *A, *B;
+    void *C;
+    cudaStream_t stream;
+};
+
+int gemm_generic(const GemmArgs &g);                  // gemm_generic.cu : any shape
+bool dgemm_dmma_eligible(const GemmArgs &g);          // gemm_dmma.cu    : f64 / c64 on DMMA
+int  dgemm_dmma(const GemmArgs &g);
+bool sgemm_tc_eligible(const GemmArgs &g);            // gemm_tf32x3.cu  : f32 / c32 on tcgen05
+int  sgemm_tc(const GemmArgs &g);
+size_t sgemm_tc_workspace(const GemmArgs &g);
+
+int gemv_dispatch(cudaStream_t s, int dtype, int opA, int64_t rowsA, int64_t colsA,
+                  const void *alpha, const void *A, const void *x, void *y);          // gemv.cu
+int dot_dispatch(cudaStream_t s, int dtype, int conj_x, int64_t n,
+                 const void *x, const void *y, void *out);                            // dot.cu
+
+}  // namespace accblas

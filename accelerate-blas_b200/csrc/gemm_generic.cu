@@ -1,0 +1,125 @@
+// gemm_generic.cu -- shape-agnostic SIMT gemm: C = alpha * op(A) * op(B) for the four
+// element types, any extents (odd, unaligned, tiny), N/T/H on either operand.
+//
+// This is the path for problems the tensor-core kernels do not take (row pitch not a
+// multiple of 16 bytes, very small extents -- e.g. the 1..64 shapes of the reference's
+// property tests, test/Test/BLAS/Level3.hs:68, or the k = 1 outer product `><`,
+// LinearAlgebra.hs:73-78).  Replaces BLAS.?gemm at LLVM/PTX/Level3.hs:88-106 for those.
+//
+// Tiling: 64x64 output tile per 256-thread CTA, BK = 16, 4x4 register micro-tile,
+// operands staged k-major in shared memory; global reads are coalesced along the
+// stored row whichever op is requested.
+#include "common.cuh"
+
+namespace accblas {
+namespace {
+
+constexpr int BM = 64, BN = 64, BK = 16, TM = 4, TN = 4, NT = 256;
+
+// Read element (r, c) of a stored rows x cols row-major matrix, 0 outside.
+template <typename T>
+__device__ __forceinline__ T ld_guard(const T *__restrict__ p, int64_t rows, int64_t cols, int64_t r, int64_t c) {
+    return (r < rows && c < cols) ? p[r * cols + c] : Scalar<T>::zero();
+}
+
+template <typename T, bool TA, bool TB>
+__global__ void __launch_bounds__(NT)
+gemm_generic_kernel(int64_t m, int64_t n, int64_t k, int64_t rowsA, int64_t colsA, int64_t rowsB,
+                    int64_t colsB, bool conjA, bool conjB, T alpha, const T *__restrict__ A,
+                    const T *__restrict__ B, T *__restrict__ C)
+{
+    __shared__ T As[BK][BM + 1];
+    __shared__ T Bs[BK][BN + 1];
+    const int tid = threadIdx.x;
+    const int tx = tid % 16, ty = tid / 16;
+    const int64_t m0 = (int64_t)blockIdx.y * BM, n0 = (int64_t)blockIdx.x * BN;
+
+    T acc[TM][TN];
+#pragma unroll
+    for (int i = 0; i < TM; ++i)
+#pragma unroll
+        for (int j = 0; j < TN; ++j) acc[i][j] = Scalar<T>::zero();
+
+    for (int64_t k0 = 0; k0 < k; k0 += BK) {
+        // ---- stage op(A)[m0.., k0..] as As[kk][mm] ----
+#pragma unroll
+        for (int e = tid; e < BM * BK; e += NT) {
+            int mm, kk;
+            T v;
+            if (!TA) { kk = e % BK; mm = e / BK; v = ld_guard(A, rowsA, colsA, m0 + mm, k0 + kk); }
+            else     { mm = e % BM; kk = e / BM; v = ld_guard(A, rowsA, colsA, k0 + kk, m0 + mm); }
+            if (conjA) v = conj_s(v);
+            As[kk][mm] = v;
+        }
+        // ---- stage op(B)[k0.., n0..] as Bs[kk][nn] ----
+#pragma unroll
+        for (int e = tid; e < BN * BK; e += NT) {
+            int nn, kk;
+            T v;
+            if (!TB) { nn = e % BN; kk = e / BN; v = ld_guard(B, rowsB, colsB, k0 + kk, n0 + nn); }
+            else     { kk = e % BK; nn = e / BK; v = ld_guard(B, rowsB, colsB, n0 + nn, k0 + kk); }
+            if (conjB) v = conj_s(v);
+            Bs[kk][nn] = v;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int kk = 0; kk < BK; ++kk) {
+            T a[TM], b[TN];
+#pragma unroll
+            for (int i = 0; i < TM; ++i) a[i] = As[kk][ty + 16 * i];
+#pragma unroll
+            for (int j = 0; j < TN; ++j) b[j] = Bs[kk][tx + 16 * j];
+#pragma unroll
+            for (int i = 0; i < TM; ++i)
+#pragma unroll
+                for (int j = 0; j < TN; ++j) acc[i][j] = fma_acc(a[i], b[j], acc[i][j]);
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int i = 0; i < TM; ++i) {
+        const int64_t r = m0 + ty + 16 * i;
+        if (r >= m) continue;
+#pragma unroll
+        for (int j = 0; j < TN; ++j) {
+            const int64_t c = n0 + tx + 16 * j;
+            if (c < n) C[r * n + c] = mul_s(alpha, acc[i][j]);   // beta = 0: C is never read
+        }
+    }
+}
+
+template <typename T>
+int launch_typed(const GemmArgs &g)
+{
+    const bool ta = g.opA != ACCBLAS_OP_N, tb = g.opB != ACCBLAS_OP_N;
+    const bool ca = Scalar<T>::cplx && g.opA == ACCBLAS_OP_H;
+    const bool cb = Scalar<T>::cplx && g.opB == ACCBLAS_OP_H;
+    const T alpha = *static_cast<const T *>(g.alpha);
+    dim3 grid((unsigned)((g.n + BN - 1) / BN), (unsigned)((g.m + BM - 1) / BM));
+    if (grid.y > 65535u) return ACCBLAS_ERR_SHAPE;
+    const T *A = static_cast<const T *>(g.A), *B = static_cast<const T *>(g.B);
+    T *C = static_cast<T *>(g.C);
+#define GO(TA_, TB_)                                                                             \
+    gemm_generic_kernel<T, TA_, TB_><<<grid, NT, 0, g.stream>>>(g.m, g.n, g.k, g.rowsA, g.colsA,   \
+                                                                g.rowsB, g.colsB, ca, cb, alpha, A, B, C)
+    if (!ta && !tb) GO(false, false);
+    else if (!ta && tb) GO(false, true);
+    else if (ta && !tb) GO(true, false);
+    else GO(true, true);
+#undef GO
+    return check_launch("gemm_generic_kernel");
+}
+
+}  // namespace
+
+int gemm_generic(const GemmArgs &g)
+{
+    switch (g.dtype) {
+    case ACCBLAS_F32: return launch_typed<float>(g);
+    case ACCBLAS_F64: return launch_typed<double>(g);
+    case ACCBLAS_C32: return launch_typed<float2>(g);
+    default:          return launch_typed<double2>(g);
+    }
+}
+
+}  // namespace accblas

@@ -1,0 +1,258 @@
+// gemv.cu -- y = alpha * op(A) * x on row-major A (HBM-bound: the matrix is read once).
+//
+// Replaces BLAS.{s,d,c,z}gemv in as_gemv (LLVM/PTX/Level2.hs:105-124) AND the gemm detour
+// the reference takes for complex `H` (LLVM/PTX/Level2.hs:52-53,57-69): working on the
+// row-major data directly, conj-transpose is just another column-sum kernel.
+//
+//  op = N  (y_i = sum_j A[i][j] x_j; `#>`, LinearAlgebra.hs:99-101)
+//      A persistent grid (CTAs resident = occupancy x SM count) walks units of ROWS rows.  All
+//      threads of the CTA stride along the row in 16-byte vectors: ROWS streaming 128-bit
+//      loads of A plus one cached 128-bit load of x in flight per thread, x re-used from
+//      registers across the ROWS rows; warp-shuffle + shared-memory row reduction.
+//  op = T / H  (y_j = sum_i op(A[i][j]) x_i; `<#`, LinearAlgebra.hs:119-121)
+//      Column-owner threads: each thread owns one 16-byte column vector and marches down
+//      the rows with 8 independent streaming loads in flight; x is staged in shared memory.
+//      Rows are split over gridDim.y so that the whole grid is ONE resident wave; the
+//      per-split partial rows are summed in split order by a second tiny kernel
+//      (deterministic, no atomics).
+#include "common.cuh"
+
+namespace accblas {
+namespace {
+
+template <typename T> union Vec16 {
+    int4 raw;
+    T e[16 / sizeof(T)];
+};
+
+// ------------------------------------------------------------------ op = N ------------
+template <typename T> struct GnRows { static constexpr int value = sizeof(T) == 16 ? 4 : 8; };
+constexpr int GN_MAX_ROWS = 8;
+constexpr int GN_MAX_WARPS = 16;
+
+template <typename T, bool ALIGNED>
+__global__ void __launch_bounds__(512, 2)
+gemv_n_kernel(int64_t m, int64_t n, T alpha, const T *__restrict__ A, const T *__restrict__ x,
+              T *__restrict__ y)
+{
+    constexpr int VEC = ALIGNED ? 16 / sizeof(T) : 1;
+    constexpr int GN_ROWS = GnRows<T>::value;
+    __shared__ T red[GN_ROWS][GN_MAX_WARPS];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+    const int64_t nunits = (m + GN_ROWS - 1) / GN_ROWS;
+    const int64_t nv = n / VEC;
+
+    for (int64_t u = blockIdx.x; u < nunits; u += gridDim.x) {
+        const int64_t r0 = u * GN_ROWS;
+        // rows past the end re-read row m-1 (discarded at the store): offsets stay in bounds
+        const T *row0 = A + r0 * n;
+        int64_t roff[GN_ROWS];
+#pragma unroll
+        for (int r = 0; r < GN_ROWS; ++r) roff[r] = ((r0 + r < m) ? r : (m - 1 - r0)) * n;
+        T acc[GN_ROWS];
+#pragma unroll
+        for (int r = 0; r < GN_ROWS; ++r) acc[r] = Scalar<T>::zero();
+
+        if (ALIGNED) {
+            for (int64_t v = threadIdx.x; v < nv; v += blockDim.x) {
+                Vec16<T> xv, av[GN_ROWS];
+#pragma unroll
+                for (int r = 0; r < GN_ROWS; ++r)
+                    av[r].raw = ldg_stream(reinterpret_cast<const int4 *>(row0 + roff[r]) + v);
+                xv.raw = ldg_cached(reinterpret_cast<const int4 *>(x) + v);
+#pragma unroll
+                for (int r = 0; r < GN_ROWS; ++r)
+#pragma unroll
+                    for (int e = 0; e < VEC; ++e) acc[r] = fma_acc(av[r].e[e], xv.e[e], acc[r]);
+            }
+        } else {
+            for (int64_t j = threadIdx.x; j < n; j += blockDim.x) {
+                const T xj = x[j];
+#pragma unroll
+                for (int r = 0; r < GN_ROWS; ++r) acc[r] = fma_acc(row0[roff[r] + j], xj, acc[r]);
+            }
+        }
+#pragma unroll
+        for (int r = 0; r < GN_ROWS; ++r) {
+            acc[r] = warp_sum(acc[r]);
+            if (lane == 0) red[r][warp] = acc[r];
+        }
+        __syncthreads();
+        if (threadIdx.x < GN_ROWS && r0 + threadIdx.x < m) {
+            T s = Scalar<T>::zero();
+            for (int w = 0; w < nwarps; ++w) s = add_s(s, red[threadIdx.x][w]);
+            y[r0 + threadIdx.x] = mul_s(alpha, s);
+        }
+        __syncthreads();
+    }
+}
+
+// ------------------------------------------------------------------ op = T / H --------
+constexpr int GT_THREADS = 256;
+constexpr int GT_UNROLL = 8;
+constexpr int GT_XCHUNK = 1024;     // rows of x staged per shared-memory refill
+
+template <typename T, bool CONJ, bool ALIGNED>
+__global__ void __launch_bounds__(GT_THREADS, 3)
+gemv_t_kernel(int64_t m, int64_t n, int64_t rows_per_split, T alpha, const T *__restrict__ A,
+              const T *__restrict__ x, T *__restrict__ out /* y, or partial[split][n] */, bool direct)
+{
+    constexpr int VEC = ALIGNED ? 16 / sizeof(T) : 1;
+    __shared__ T xs[GT_XCHUNK];
+    const int64_t nv = (n + VEC - 1) / VEC;    // ALIGNED guarantees n % VEC == 0
+    const int64_t v = (int64_t)blockIdx.x * GT_THREADS + threadIdx.x;
+    const bool active = v < nv;
+    const int64_t r_begin = (int64_t)blockIdx.y * rows_per_split;
+    int64_t r_end = r_begin + rows_per_split;
+    if (r_end > m) r_end = m;
+
+    T acc[VEC];
+#pragma unroll
+    for (int e = 0; e < VEC; ++e) acc[e] = Scalar<T>::zero();
+    const char *colp = reinterpret_cast<const char *>(A) + (active ? v : 0) * (int64_t)(VEC * sizeof(T));
+    const int64_t pitch = n * (int64_t)sizeof(T);
+
+    for (int64_t rc = r_begin; rc < r_end; rc += GT_XCHUNK) {
+        const int cnt = (int)((r_end - rc) < GT_XCHUNK ? (r_end - rc) : GT_XCHUNK);
+        __syncthreads();
+        for (int i = threadIdx.x; i < cnt; i += GT_THREADS) xs[i] = x[rc + i];
+        __syncthreads();
+        if (!active) continue;
+        const char *p = colp + rc * pitch;
+        int i = 0;
+        for (; i + GT_UNROLL <= cnt; i += GT_UNROLL) {
+            Vec16<T> av[GT_UNROLL];
+#pragma unroll
+            for (int u = 0; u < GT_UNROLL; ++u) {
+                if (ALIGNED) av[u].raw = ldg_stream(p + (int64_t)(i + u) * pitch);
+                else av[u].e[0] = *reinterpret_cast<const T *>(p + (int64_t)(i + u) * pitch);
+            }
+#pragma unroll
+            for (int u = 0; u < GT_UNROLL; ++u) {
+                const T xi = xs[i + u];
+#pragma unroll
+                for (int e = 0; e < VEC; ++e) acc[e] = fma_acc(CONJ ? conj_s(av[u].e[e]) : av[u].e[e], xi, acc[e]);
+            }
+        }
+        for (; i < cnt; ++i) {
+            Vec16<T> av;
+            if (ALIGNED) av.raw = ldg_stream(p + (int64_t)i * pitch);
+            else av.e[0] = *reinterpret_cast<const T *>(p + (int64_t)i * pitch);
+            const T xi = xs[i];
+#pragma unroll
+            for (int e = 0; e < VEC; ++e) acc[e] = fma_acc(CONJ ? conj_s(av.e[e]) : av.e[e], xi, acc[e]);
+        }
+    }
+    if (!active) return;
+    T *dst = direct ? out : out + (int64_t)blockIdx.y * n;
+#pragma unroll
+    for (int e = 0; e < VEC; ++e) {
+        const int64_t j = v * VEC + e;
+        if (j < n) dst[j] = direct ? mul_s(alpha, acc[e]) : acc[e];
+    }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+gemv_t_reduce_kernel(int64_t n, int splits, T alpha, const T *__restrict__ partial, T *__restrict__ y)
+{
+    const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    T s = Scalar<T>::zero();
+    for (int sp = 0; sp < splits; ++sp) s = add_s(s, partial[(int64_t)sp * n + j]);
+    y[j] = mul_s(alpha, s);
+}
+
+template <typename T> __global__ void fill_zero_kernel(int64_t n, T *__restrict__ y)
+{
+    const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j < n) y[j] = Scalar<T>::zero();
+}
+
+template <typename K> int occupancy(K kernel, int threads)
+{
+    int nb = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kernel, threads, 0) != cudaSuccess || nb < 1) nb = 1;
+    return nb;
+}
+
+template <typename T>
+int gemv_typed(cudaStream_t st, int opA, int64_t rowsA, int64_t colsA, const void *alpha_p,
+               const void *A_, const void *x_, void *y_)
+{
+    const T alpha = *static_cast<const T *>(alpha_p);
+    const T *A = static_cast<const T *>(A_), *x = static_cast<const T *>(x_);
+    T *y = static_cast<T *>(y_);
+    const int64_t leny = opA == ACCBLAS_OP_N ? rowsA : colsA;
+    const int64_t lenx = opA == ACCBLAS_OP_N ? colsA : rowsA;
+    if (leny == 0) return ACCBLAS_OK;
+    if (lenx == 0) {   // empty sum: y = 0
+        fill_zero_kernel<T><<<(unsigned)((leny + 255) / 256), 256, 0, st>>>(leny, y);
+        return check_launch("fill_zero_kernel");
+    }
+    constexpr int VEC = 16 / sizeof(T);
+    const bool aligned = (reinterpret_cast<uintptr_t>(A) & 15u) == 0 && (colsA % VEC) == 0;
+
+    if (opA == ACCBLAS_OP_N) {
+        const bool al = aligned && (reinterpret_cast<uintptr_t>(x) & 15u) == 0;
+        const int64_t nv = al ? colsA / VEC : colsA;
+        int threads = nv >= 512 ? 512 : nv >= 256 ? 256 : nv >= 128 ? 128 : 64;
+        const int64_t units = (rowsA + GnRows<T>::value - 1) / GnRows<T>::value;
+        static thread_local int occ_a = 0, occ_u = 0;
+        if (!occ_a) { occ_a = occupancy(gemv_n_kernel<T, true>, 512); occ_u = occupancy(gemv_n_kernel<T, false>, 512); }
+        int64_t grid = (int64_t)sm_count() * (al ? occ_a : occ_u) * (512 / threads);
+        if (grid > units) grid = units;
+        if (al) gemv_n_kernel<T, true><<<(unsigned)grid, threads, 0, st>>>(rowsA, colsA, alpha, A, x, y);
+        else    gemv_n_kernel<T, false><<<(unsigned)grid, threads, 0, st>>>(rowsA, colsA, alpha, A, x, y);
+        return check_launch("gemv_n_kernel");
+    }
+
+    const bool conj = Scalar<T>::cplx && opA == ACCBLAS_OP_H;
+    const int64_t nv = aligned ? colsA / VEC : colsA;
+    const int64_t gx = (nv + GT_THREADS - 1) / GT_THREADS;
+    static thread_local int occ_t = 0;
+    if (!occ_t) occ_t = occupancy(gemv_t_kernel<T, false, true>, GT_THREADS);
+    const int64_t slots = (int64_t)sm_count() * occ_t;      // one resident wave
+    int64_t splits = slots / gx;
+    const int64_t max_splits = (rowsA + 63) / 64;            // at least 64 rows per split
+    if (splits > max_splits) splits = max_splits;
+    if (splits < 1) splits = 1;
+    if (splits > 65535) splits = 65535;
+    int64_t rps = (rowsA + splits - 1) / splits;
+    rps = (rps + GT_UNROLL - 1) / GT_UNROLL * GT_UNROLL;
+    splits = (rowsA + rps - 1) / rps;
+    const bool direct = splits == 1;
+    T *partial = nullptr;
+    if (!direct) ACC_CUDA(cudaMallocAsync(reinterpret_cast<void **>(&partial), sizeof(T) * (size_t)splits * (size_t)colsA, st));
+    dim3 grid((unsigned)gx, (unsigned)splits);
+    T *out = direct ? y : partial;
+#define GO(CJ, AL) gemv_t_kernel<T, CJ, AL><<<grid, GT_THREADS, 0, st>>>(rowsA, colsA, rps, alpha, A, x, out, direct)
+    if (aligned) { if (conj) GO(true, true); else GO(false, true); }
+    else         { if (conj) GO(true, false); else GO(false, false); }
+#undef GO
+    int s = check_launch("gemv_t_kernel");
+    if (!direct) {
+        if (s == ACCBLAS_OK) {
+            gemv_t_reduce_kernel<T><<<(unsigned)((colsA + 255) / 256), 256, 0, st>>>(colsA, (int)splits, alpha, partial, y);
+            s = check_launch("gemv_t_reduce_kernel");
+        }
+        cudaError_t e = cudaFreeAsync(partial, st);
+        if (s == ACCBLAS_OK && e != cudaSuccess) return cuda_fail(e, "cudaFreeAsync");
+    }
+    return s;
+}
+
+}  // namespace
+
+int gemv_dispatch(cudaStream_t s, int dtype, int opA, int64_t rowsA, int64_t colsA, const void *alpha,
+                  const void *A, const void *x, void *y)
+{
+    switch (dtype) {
+    case ACCBLAS_F32: return gemv_typed<float>(s, opA, rowsA, colsA, alpha, A, x, y);
+    case ACCBLAS_F64: return gemv_typed<double>(s, opA, rowsA, colsA, alpha, A, x, y);
+    case ACCBLAS_C32: return gemv_typed<float2>(s, opA, rowsA, colsA, alpha, A, x, y);
+    default:          return gemv_typed<double2>(s, opA, rowsA, colsA, alpha, A, x, y);
+    }
+}
+
+}  // namespace accblas

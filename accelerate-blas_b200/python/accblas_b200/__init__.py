@@ -1,0 +1,261 @@
+"""accblas_b200 -- host-side mirror of Data.Array.Accelerate.Numeric.LinearAlgebra for the
+B200-native library libaccblas_b200.so.
+
+The reference's public surface for the hot path (same names, argument order and meaning):
+
+    gemm alpha opA A opB B        BLAS/Level3.hs:57-64        ->  gemm(alpha, opA, A, opB, B)
+    gemv alpha opA A x            BLAS/Level2.hs:57-63        ->  gemv(alpha, opA, A, x)
+    dotu xs ys / dotc xs ys       BLAS/Level1.hs:73-74,85-92  ->  dotu(x, y) / dotc(x, y)
+    (<>) (#>) (<#) (<.>) (><)     LinearAlgebra.hs:58-155     ->  mXm, mXv, vXm, dot, outer
+    Transpose = N | T | H         Type.hs:78-90               ->  N, T, H
+    Numeric e => Float, Double, Complex Float, Complex Double (Type.hs:32-51)
+                                  ->  float32, float64, complex64, complex128
+
+Arrays are row-major and dense like Accelerate's.  Two kinds of operand are accepted:
+
+  * ``torch.Tensor`` on a CUDA device: the device-pointer ABI (accblas_gemm / gemv / dot) is
+    called on torch's current stream -- the analogue of the ForeignAcc hook receiving the
+    backend's device pointers and stream (LLVM/PTX/Level3.hs:78-85).  Results are new device
+    tensors; ``dotu`` returns a 0-d device tensor (the reference's ``Acc (Scalar e)``).
+  * ``numpy.ndarray``: the host-buffer ABI (accblas_*_host) -- what ``run`` does end to end:
+    upload, hook, download (test/Test/BLAS/Level3.hs:52-54).
+
+PyTorch is only the provider of device memory and streams.  No arithmetic happens in
+Python, torch or numpy, and there is no CPU fallback: without the CUDA library every call
+raises.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Union
+
+import numpy as np
+
+from . import _ffi
+from ._ffi import AccblasError, lib  # noqa: F401
+
+__all__ = ["N", "T", "H", "gemm", "gemv", "dotu", "dotc", "mXm", "mXv", "vXm", "dot", "outer",
+           "AccblasError", "kernel_name", "launch_count", "set_gemm_path", "version"]
+
+# Transpose -- Type.hs:78-90
+N, T, H = 0, 1, 2
+_OPS = {"N": N, "T": T, "H": H, N: N, T: T, H: H}
+
+# NumericR -- Type.hs:32-36
+F32, F64, C32, C64 = 0, 1, 2, 3
+_NP_CODE = {np.dtype(np.float32): F32, np.dtype(np.float64): F64,
+            np.dtype(np.complex64): C32, np.dtype(np.complex128): C64}
+_NP_OF = {v: k for k, v in _NP_CODE.items()}
+
+
+def _torch():
+    import torch
+    return torch
+
+
+def _is_torch(a) -> bool:
+    return type(a).__module__.startswith("torch")
+
+
+def _code(a) -> int:
+    if _is_torch(a):
+        torch = _torch()
+        table = {torch.float32: F32, torch.float64: F64, torch.complex64: C32, torch.complex128: C64}
+        if a.dtype not in table:
+            raise TypeError(f"accblas_b200: no Numeric instance for {a.dtype} (Type.hs:38-51)")
+        return table[a.dtype]
+    dt = np.dtype(a.dtype)
+    if dt not in _NP_CODE:
+        raise TypeError(f"accblas_b200: no Numeric instance for {dt} (Type.hs:38-51)")
+    return _NP_CODE[dt]
+
+
+def _op(op) -> int:
+    try:
+        return _OPS[op]
+    except (KeyError, TypeError):
+        raise ValueError(f"accblas_b200: Transpose must be N, T or H, got {op!r}") from None
+
+
+def _alpha_buf(alpha, code: int):
+    buf = np.array([alpha], dtype=_NP_OF[code])
+    return buf, buf.ctypes.data_as(ctypes.c_void_p)
+
+
+def _dev_operand(a, code: int, ndim: int, name: str):
+    if not _is_torch(a) or not a.is_cuda:
+        raise TypeError(f"{name}: expected a CUDA tensor when the first operand is one")
+    if _code(a) != code:
+        raise TypeError(f"{name}: element type differs from the first operand's")
+    if a.dim() != ndim:
+        raise ValueError(f"{name}: expected rank {ndim}, got {a.dim()}")
+    return a if a.is_contiguous() else a.contiguous()
+
+
+def _host_operand(a, code: int, ndim: int, name: str) -> np.ndarray:
+    a = np.asarray(a)
+    if _code(a) != code:
+        raise TypeError(f"{name}: element type differs from the first operand's")
+    if a.ndim != ndim:
+        raise ValueError(f"{name}: expected rank {ndim}, got {a.ndim}")
+    return np.ascontiguousarray(a)
+
+
+def _stream(t) -> ctypes.c_void_p:
+    torch = _torch()
+    return ctypes.c_void_p(torch.cuda.current_stream(t.device).cuda_stream)
+
+
+def _ptr(t) -> ctypes.c_void_p:
+    return ctypes.c_void_p(t.data_ptr() if _is_torch(t) else t.ctypes.data)
+
+
+# ------------------------------------------------------------------------------------
+# Level 3
+# ------------------------------------------------------------------------------------
+def gemm(alpha, opA, A, opB, B):
+    """``C = alpha * op(A) * op(B)`` -- gemm, BLAS/Level3.hs:57-64.
+
+    shape op(A) = (m, k), shape op(B) = (k, n), shape C = (m, n); stored shapes are pre-op.
+    """
+    oa, ob = _op(opA), _op(opB)
+    code = _code(A)
+    al_keep, al = _alpha_buf(alpha, code)
+    L = lib()
+    if _is_torch(A):
+        torch = _torch()
+        A = _dev_operand(A, code, 2, "gemm: A")
+        B = _dev_operand(B, code, 2, "gemm: B")
+        m = A.shape[0] if oa == N else A.shape[1]          # LLVM/PTX/Level3.hs:57-62
+        n = B.shape[1] if ob == N else B.shape[0]
+        with torch.cuda.device(A.device):
+            C = torch.empty((m, n), dtype=A.dtype, device=A.device)   # allocateRemote: uninitialised
+            st = L.accblas_gemm(_stream(A), code, oa, ob, A.shape[0], A.shape[1], B.shape[0], B.shape[1],
+                                al, _ptr(A), _ptr(B), _ptr(C))
+        _ffi.check(st, "accblas_gemm")
+        return C
+    A = _host_operand(A, code, 2, "gemm: A")
+    B = _host_operand(B, code, 2, "gemm: B")
+    m = A.shape[0] if oa == N else A.shape[1]
+    n = B.shape[1] if ob == N else B.shape[0]
+    C = np.empty((m, n), dtype=A.dtype)
+    st = L.accblas_gemm_host(None, code, oa, ob, A.shape[0], A.shape[1], B.shape[0], B.shape[1],
+                             al, _ptr(A), _ptr(B), _ptr(C))
+    _ffi.check(st, "accblas_gemm_host")
+    return C
+
+
+# ------------------------------------------------------------------------------------
+# Level 2
+# ------------------------------------------------------------------------------------
+def gemv(alpha, opA, A, x):
+    """``y = alpha * op(A) * x`` -- gemv, BLAS/Level2.hs:57-63."""
+    oa = _op(opA)
+    code = _code(A)
+    al_keep, al = _alpha_buf(alpha, code)
+    L = lib()
+    if _is_torch(A):
+        torch = _torch()
+        A = _dev_operand(A, code, 2, "gemv: A")
+        x = _dev_operand(x, code, 1, "gemv: x")
+        leny = A.shape[0] if oa == N else A.shape[1]       # LLVM/PTX/Level2.hs:80-82
+        with torch.cuda.device(A.device):
+            y = torch.empty((leny,), dtype=A.dtype, device=A.device)
+            st = L.accblas_gemv(_stream(A), code, oa, A.shape[0], A.shape[1], al, _ptr(A), _ptr(x),
+                                x.shape[0], _ptr(y))
+        _ffi.check(st, "accblas_gemv")
+        return y
+    A = _host_operand(A, code, 2, "gemv: A")
+    x = _host_operand(x, code, 1, "gemv: x")
+    leny = A.shape[0] if oa == N else A.shape[1]
+    y = np.empty((leny,), dtype=A.dtype)
+    st = L.accblas_gemv_host(None, code, oa, A.shape[0], A.shape[1], al, _ptr(A), _ptr(x), x.shape[0], _ptr(y))
+    _ffi.check(st, "accblas_gemv_host")
+    return y
+
+
+# ------------------------------------------------------------------------------------
+# Level 1
+# ------------------------------------------------------------------------------------
+def _dot(x, y, conj: bool):
+    code = _code(x)
+    L = lib()
+    if _is_torch(x):
+        torch = _torch()
+        x = _dev_operand(x, code, 1, "dot: x")
+        y = _dev_operand(y, code, 1, "dot: y")
+        n = min(x.shape[0], y.shape[0])                    # zipWith intersects extents
+        with torch.cuda.device(x.device):
+            out = torch.empty((), dtype=x.dtype, device=x.device)
+            st = L.accblas_dot(_stream(x), code, int(conj), n, _ptr(x), _ptr(y), _ptr(out))
+        _ffi.check(st, "accblas_dot")
+        return out
+    x = _host_operand(x, code, 1, "dot: x")
+    y = _host_operand(y, code, 1, "dot: y")
+    n = min(x.shape[0], y.shape[0])
+    out = np.zeros((1,), dtype=x.dtype)
+    st = L.accblas_dot_host(None, code, int(conj), n, _ptr(x), _ptr(y), _ptr(out))
+    _ffi.check(st, "accblas_dot_host")
+    return out[0]
+
+
+def dotu(x, y):
+    """``sum_i x_i * y_i`` -- dotu, BLAS/Level1.hs:73-74."""
+    return _dot(x, y, False)
+
+
+def dotc(x, y):
+    """``sum_i conj(x_i) * y_i`` -- dotc, BLAS/Level1.hs:85-92 (complex element types only)."""
+    if _code(x) not in (C32, C64):
+        raise TypeError("dotc: Numeric (Complex e) required (BLAS/Level1.hs:85)")
+    return _dot(x, y, True)
+
+
+# ------------------------------------------------------------------------------------
+# operators -- LinearAlgebra.hs
+# ------------------------------------------------------------------------------------
+def dot(x, y):
+    """``x <.> y = dotu x y`` -- LinearAlgebra.hs:58-60."""
+    return dotu(x, y)
+
+
+def outer(x, y):
+    """``x >< y`` : (len x, 1) <> (1, len y) -- LinearAlgebra.hs:73-78."""
+    return mXm(x.reshape(-1, 1), y.reshape(1, -1))
+
+
+def mXv(m, x):
+    """``m #> x = gemv 1 N m x`` -- LinearAlgebra.hs:99-101."""
+    return gemv(1, N, m, x)
+
+
+def vXm(x, m):
+    """``x <# m = gemv 1 T m x`` -- LinearAlgebra.hs:119-121."""
+    return gemv(1, T, m, x)
+
+
+def mXm(a, b):
+    """``a <> b = gemm 1 N a N b`` -- LinearAlgebra.hs:153-155."""
+    return gemm(1, N, a, N, b)
+
+
+# ------------------------------------------------------------------------------------
+# introspection
+# ------------------------------------------------------------------------------------
+def kernel_name(dtype_code: int, opA, opB, shapeA, shapeB) -> str:
+    return lib().accblas_gemm_kernel_name(dtype_code, _op(opA), _op(opB), shapeA[0], shapeA[1],
+                                          shapeB[0], shapeB[1]).decode()
+
+
+def launch_count() -> int:
+    return int(lib().accblas_launch_count())
+
+
+def set_gemm_path(path: Union[int, str]) -> None:
+    """0/'auto', 1/'generic' (SIMT), 2/'tensor' (error if the problem does not qualify)."""
+    table = {"auto": 0, "generic": 1, "tensor": 2}
+    lib().accblas_set_gemm_path(table.get(path, path))
+
+
+def version() -> int:
+    return int(lib().accblas_version())

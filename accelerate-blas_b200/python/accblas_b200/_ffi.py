@@ -1,0 +1,75 @@
+"""ctypes binding of libaccblas_b200.so (include/accblas_b200.h).
+
+The shared object is the product; this module only declares its symbols.  There is no
+fallback: if the library is missing or a call fails, an exception is raised.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+PKG_ROOT = os.path.dirname(os.path.dirname(_HERE))               # accelerate-blas_b200/
+LIB_PATH = os.environ.get("ACCBLAS_B200_LIB", os.path.join(PKG_ROOT, "lib", "libaccblas_b200.so"))
+
+# every symbol include/accblas_b200.h declares (tests/test_abi.py checks this list against the header)
+SYMBOLS = (
+    "accblas_gemm", "accblas_gemm_workspace_bytes", "accblas_gemv", "accblas_dot",
+    "accblas_gemm_host", "accblas_gemv_host", "accblas_dot_host",
+    "accblas_version", "accblas_status_string", "accblas_last_cuda_error",
+    "accblas_gemm_kernel_name", "accblas_launch_count", "accblas_set_gemm_path",
+)
+
+
+class AccblasError(RuntimeError):
+    def __init__(self, status: int, where: str, detail: str = ""):
+        self.status = status
+        msg = f"{where}: status {status}"
+        if detail:
+            msg += f" ({detail})"
+        super().__init__(msg)
+
+
+_lib = None
+
+
+def lib() -> ctypes.CDLL:
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise OSError(
+            f"{LIB_PATH} not found: build it with `make -C '{PKG_ROOT}'` (or __graft_entry__.build()). "
+            "accblas_b200 has no CPU fallback.")
+    L = ctypes.CDLL(LIB_PATH)
+    i64, vp, ci, sz = ctypes.c_int64, ctypes.c_void_p, ctypes.c_int, ctypes.c_size_t
+    L.accblas_gemm.argtypes = [vp, ci, ci, ci, i64, i64, i64, i64, vp, vp, vp, vp]
+    L.accblas_gemm_host.argtypes = L.accblas_gemm.argtypes
+    L.accblas_gemv.argtypes = [vp, ci, ci, i64, i64, vp, vp, vp, i64, vp]
+    L.accblas_gemv_host.argtypes = L.accblas_gemv.argtypes
+    L.accblas_dot.argtypes = [vp, ci, ci, i64, vp, vp, vp]
+    L.accblas_dot_host.argtypes = L.accblas_dot.argtypes
+    for f in (L.accblas_gemm, L.accblas_gemm_host, L.accblas_gemv, L.accblas_gemv_host, L.accblas_dot,
+              L.accblas_dot_host, L.accblas_version):
+        f.restype = ci
+    L.accblas_gemm_workspace_bytes.argtypes = [ci, ci, ci, i64, i64, i64, i64]
+    L.accblas_gemm_workspace_bytes.restype = sz
+    L.accblas_gemm_kernel_name.argtypes = [ci, ci, ci, i64, i64, i64, i64]
+    L.accblas_gemm_kernel_name.restype = ctypes.c_char_p
+    L.accblas_status_string.argtypes = [ci]
+    L.accblas_status_string.restype = ctypes.c_char_p
+    L.accblas_last_cuda_error.restype = ctypes.c_char_p
+    L.accblas_launch_count.restype = ctypes.c_uint64
+    L.accblas_set_gemm_path.argtypes = [ci]
+    L.accblas_set_gemm_path.restype = None
+    _lib = L
+    return L
+
+
+def check(status: int, where: str) -> None:
+    if status != 0:
+        L = lib()
+        detail = L.accblas_status_string(status).decode()
+        if status == 5:
+            detail += ": " + L.accblas_last_cuda_error().decode()
+        raise AccblasError(status, where, detail)

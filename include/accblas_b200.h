@@ -1,0 +1,156 @@
+/*
+ * accblas_b200.h -- C ABI of libaccblas_b200.so
+ *
+ * Hand-written sm_100a (B200) kernels for the dense-product hot path of
+ * tmcdonell/accelerate-blas: gemm, gemv, dotu/dotc over Float, Double,
+ * Complex Float, Complex Double with the N / T / H operand flags.
+ *
+ * The library is the callee of the reference's llvm-ptx ForeignAcc hooks.  Every entry
+ * point below names the reference interface it replaces (paths relative to the
+ * reference tree, src/Data/Array/Accelerate/Numeric/LinearAlgebra/...).
+ *
+ * Contract:
+ *   - stateless and re-entrant: no handle (the reference's withBLAS / cuBLAS handle
+ *     cache, LLVM/PTX/Context.hs:45-75, disappears); safe on concurrent streams/devices;
+ *     the CUDA device current on the calling thread is the one used;
+ *   - stream ordered: ALL device work, including internal workspace allocation
+ *     (cudaMallocAsync / cudaFreeAsync), is enqueued on the caller's stream, because the
+ *     reference tracks buffer lifetimes with an event recorded on that stream right after
+ *     the call (LLVM/PTX/Base.hs:94-98);
+ *   - row-major, dense, tight leading dimensions (lda = colsA, ldb = colsB, ldc = n:
+ *     LLVM/PTX/Level3.hs:64-65,91), stored shape is PRE-op, complex = interleaved (re,im)
+ *     (Type.hs:35-36);
+ *   - beta = 0 and the output is never read: the reference hands over an UNINITIALISED
+ *     buffer (LLVM/PTX/Level3.hs:80,90; LLVM/PTX/Level2.hs:98,108);
+ *   - `H` on a real dtype behaves exactly as `T` (BLAS/Level3.hs:97-100);
+ *   - alpha is read from HOST memory at call time (the reference fetches it with
+ *     indexRemote and passes a host pointer, LLVM/PTX/Level3.hs:81,89);
+ *   - every function returns an accblas_status_t; nothing throws, nothing falls back to
+ *     the CPU.  A zero extent launches nothing (k == 0 zero-fills the output).
+ */
+#ifndef ACCBLAS_B200_H
+#define ACCBLAS_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ACCBLAS_B200_VERSION 100 /* 0.1.0 */
+
+/* NumericR -- Type.hs:32-36 */
+typedef enum {
+    ACCBLAS_F32 = 0, /* NumericRfloat32   : Float                      4 B/element  */
+    ACCBLAS_F64 = 1, /* NumericRfloat64   : Double                     8 B/element  */
+    ACCBLAS_C32 = 2, /* NumericRcomplex32 : Vec2 Float  (re,im)        8 B/element  */
+    ACCBLAS_C64 = 3  /* NumericRcomplex64 : Vec2 Double (re,im)       16 B/element  */
+} accblas_dtype_t;
+
+/* Transpose -- Type.hs:78-90 (encodeTranspose, LLVM/PTX/Base.hs:44-47) */
+typedef enum {
+    ACCBLAS_OP_N = 0, /* as stored                        */
+    ACCBLAS_OP_T = 1, /* implicitly transposed            */
+    ACCBLAS_OP_H = 2  /* conjugated and transposed        */
+} accblas_op_t;
+
+typedef enum {
+    ACCBLAS_OK = 0,
+    ACCBLAS_ERR_DTYPE = 1,     /* dtype not in accblas_dtype_t                          */
+    ACCBLAS_ERR_OP = 2,        /* op not in accblas_op_t                                */
+    ACCBLAS_ERR_SHAPE = 3,     /* negative extent, inner extents differ, or |x| wrong   */
+    ACCBLAS_ERR_NULL = 4,      /* null pointer with a non-empty extent                  */
+    ACCBLAS_ERR_CUDA = 5,      /* a CUDA runtime / driver call failed (cudaGetLastError)*/
+    ACCBLAS_ERR_ARCH = 6,      /* device is not compute capability 10.x                 */
+    ACCBLAS_ERR_WORKSPACE = 7, /* caller-supplied workspace too small / misaligned      */
+    ACCBLAS_ERR_ALIAS = 8      /* output overlaps an input                              */
+} accblas_status_t;
+
+/* stream: a cudaStream_t passed as an opaque pointer (NULL = the legacy default stream). */
+typedef void *accblas_stream_t;
+
+/* ------------------------------------------------------------------------------------
+ * Level 3.   C (m x n) = alpha * op(A) * op(B)
+ *
+ * Replaces the four BLAS.{s,d,c,z}gemm calls of gemm'  LLVM/PTX/Level3.hs:88-106
+ * (and, for the complex-H gemv route, as_gemm         LLVM/PTX/Level2.hs:57-69).
+ *   (m,k) = opA == N ? (rowsA,colsA) : (colsA,rowsA)   LLVM/PTX/Level3.hs:57-59
+ *   n     = opB == N ? colsB : rowsB                   LLVM/PTX/Level3.hs:60-62
+ * Unlike the reference, the inner extents ARE compared (ACCBLAS_ERR_SHAPE).
+ * alpha_host points at one element of `dtype` in host memory.
+ * ---------------------------------------------------------------------------------- */
+int accblas_gemm(accblas_stream_t stream, int dtype, int opA, int opB,
+                 int64_t rowsA, int64_t colsA, int64_t rowsB, int64_t colsB,
+                 const void *alpha_host, const void *A, const void *B, void *C);
+
+/* Bytes of stream-ordered scratch accblas_gemm will take from the device's default
+ * memory pool for this problem (0 for the direct kernels).  Informational. */
+size_t accblas_gemm_workspace_bytes(int dtype, int opA, int opB,
+                                    int64_t rowsA, int64_t colsA, int64_t rowsB, int64_t colsB);
+
+/* ------------------------------------------------------------------------------------
+ * Level 2.   y = alpha * op(A) * x,   |y| = opA == N ? rowsA : colsA
+ *
+ * Replaces the four BLAS.{s,d,c,z}gemv calls of as_gemv  LLVM/PTX/Level2.hs:105-124 and
+ * the gemm detour for complex H (gemv' dispatch, LLVM/PTX/Level2.hs:48-54): all three
+ * ops of all four dtypes are served by native row-major gemv kernels.
+ * lenx must equal (opA == N ? colsA : rowsA).
+ * ---------------------------------------------------------------------------------- */
+int accblas_gemv(accblas_stream_t stream, int dtype, int opA,
+                 int64_t rowsA, int64_t colsA,
+                 const void *alpha_host, const void *A, const void *x, int64_t lenx, void *y);
+
+/* ------------------------------------------------------------------------------------
+ * Level 1.   out = sum_i x_i * y_i            (conj_x == 0: dotu, BLAS/Level1.hs:73-74)
+ *            out = sum_i conj(x_i) * y_i      (conj_x != 0: dotc, BLAS/Level1.hs:85-92)
+ *
+ * NEW hook: the reference has no foreign dot (it is `fold (+) 0 (zipWith (*) xs ys)`);
+ * INTEGRATION.md shows the foreignAcc alternative to add at BLAS/Level1.hs:74,91-92.
+ * n = min(|x|,|y|) (zipWith intersects extents).  The result (one element of `dtype`)
+ * is written to DEVICE memory at out_dev, like the reference's Acc (Scalar e), with a
+ * fixed summation order (bit-reproducible run to run).  n == 0 writes 0.
+ * conj_x is ignored for real dtypes.
+ * ---------------------------------------------------------------------------------- */
+int accblas_dot(accblas_stream_t stream, int dtype, int conj_x, int64_t n,
+                const void *x, const void *y, void *out_dev);
+
+/* ------------------------------------------------------------------------------------
+ * Host-buffer entry points: what `run (A <> B)` does end to end in the reference --
+ * `use` uploads the host arrays, the hook runs, the result is copied back
+ * (test/Test/BLAS/Level3.hs:52-54; bench/Bench/Accelerate.hs:111-114).  A, B, x, y, C,
+ * out are HOST pointers (pinned memory gives full PCIe rate, pageable works);
+ * uploads are pipelined against the kernels in row panels.  Synchronous: returns when
+ * the result is in host memory.  `stream` orders the work like above.
+ * ---------------------------------------------------------------------------------- */
+int accblas_gemm_host(accblas_stream_t stream, int dtype, int opA, int opB,
+                      int64_t rowsA, int64_t colsA, int64_t rowsB, int64_t colsB,
+                      const void *alpha_host, const void *A_host, const void *B_host, void *C_host);
+int accblas_gemv_host(accblas_stream_t stream, int dtype, int opA, int64_t rowsA, int64_t colsA,
+                      const void *alpha_host, const void *A_host, const void *x_host, int64_t lenx,
+                      void *y_host);
+int accblas_dot_host(accblas_stream_t stream, int dtype, int conj_x, int64_t n,
+                     const void *x_host, const void *y_host, void *out_host);
+
+/* ------------------------------------------------------------------------------------
+ * Introspection / tuning.  None of these change results beyond the stated tolerance.
+ * ---------------------------------------------------------------------------------- */
+int accblas_version(void);                     /* ACCBLAS_B200_VERSION */
+const char *accblas_status_string(int status); /* static string        */
+/* cudaGetLastError text captured by the last ACCBLAS_ERR_CUDA on this thread ("" if none) */
+const char *accblas_last_cuda_error(void);
+/* Name of the kernel family the dispatcher picks for this gemm problem, e.g.
+ * "dgemm_dmma_tma", "sgemm_tf32x3_tcgen05", "gemm_simt_generic".  Static string. */
+const char *accblas_gemm_kernel_name(int dtype, int opA, int opB,
+                                     int64_t rowsA, int64_t colsA, int64_t rowsB, int64_t colsB);
+/* Number of kernel launches this thread has enqueued through the library (bench.py's
+ * gpu_launches). */
+uint64_t accblas_launch_count(void);
+/* Force a kernel family for gemm on this thread: 0 = auto, 1 = generic SIMT,
+ * 2 = tensor path only (error ACCBLAS_ERR_SHAPE if the problem does not qualify). */
+void accblas_set_gemm_path(int path);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ACCBLAS_B200_H */

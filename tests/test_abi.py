@@ -1,0 +1,87 @@
+"""CPU: the C-ABI shared object loads without a GPU and exports every symbol the header declares;
+host-side argument handling of the python mirror.  No compute calls."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HEADER = os.path.join(ROOT, "include", "accblas_b200.h")
+
+
+def header_symbols():
+    src = open(HEADER).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(accblas_[a-z_0-9]+)\s*\(", src)))
+
+
+def test_library_exports_every_declared_symbol():
+    from accblas_b200 import _ffi
+    L = _ffi.lib()
+    syms = header_symbols()
+    assert len(syms) >= 13
+    for s in syms:
+        assert hasattr(L, s), f"{s} declared in include/accblas_b200.h but not exported"
+    assert sorted(_ffi.SYMBOLS) == syms
+
+
+def test_version_and_strings():
+    import accblas_b200 as ab
+    assert ab.version() == 100
+    L = ab.lib()
+    assert L.accblas_status_string(0) == b"ok"
+    assert L.accblas_status_string(3) == b"shape mismatch"
+
+
+def test_argument_validation_needs_no_gpu():
+    """Status codes for bad arguments are produced before any CUDA call."""
+    import accblas_b200 as ab
+    L = ab.lib()
+    one = np.array([1.0])
+    p = one.ctypes.data_as(ctypes.c_void_p)
+    assert L.accblas_gemm(None, 9, 0, 0, 1, 1, 1, 1, p, p, p, p) == 1          # dtype
+    assert L.accblas_gemm(None, 1, 7, 0, 1, 1, 1, 1, p, p, p, p) == 2          # op
+    assert L.accblas_gemm(None, 1, 0, 0, 2, 3, 4, 2, p, p, p, p) == 3          # inner extents differ
+    assert L.accblas_gemm(None, 1, 0, 0, 0, 3, 3, 2, p, p, p, None) == 0       # m == 0: nothing to do
+    assert L.accblas_gemm(None, 1, 0, 0, 2, 3, 3, 2, p, p, p, None) == 4       # null C
+    assert L.accblas_gemv(None, 1, 0, 2, 3, p, p, p, 2, p) == 3                # |x| wrong
+    assert L.accblas_gemv(None, 1, 1, 2, 3, p, p, p, 3, p) == 3
+    assert L.accblas_dot(None, 1, 0, -1, p, p, p) == 3
+    assert L.accblas_dot(None, 1, 0, 4, p, p, None) == 4
+
+
+def test_kernel_selection_names():
+    import accblas_b200 as ab
+    assert ab.kernel_name(1, "N", "N", (3, 5), (5, 2)) == "gemm_simt_generic"
+    assert ab.kernel_name(1, "N", "N", (3, 5), (4, 2)) == "invalid"
+    assert ab.kernel_name(1, "N", "N", (0, 5), (5, 2)) == "none"
+
+
+def test_python_mirror_rejects_bad_inputs():
+    import accblas_b200 as ab
+    with pytest.raises(ValueError):
+        ab.gemm(1, "X", np.zeros((2, 2)), "N", np.zeros((2, 2)))
+    with pytest.raises(TypeError):
+        ab.gemm(1, "N", np.zeros((2, 2), dtype=np.int32), "N", np.zeros((2, 2), dtype=np.int32))
+    with pytest.raises(TypeError):
+        ab.dotc(np.zeros(3), np.zeros(3))
+    with pytest.raises(TypeError):
+        ab.gemm(1, "N", np.zeros((2, 2)), "N", np.zeros((2, 2), dtype=np.float32))
+
+
+def test_no_cpu_fallback_in_product():
+    """The product tree must not reference the oracle or a CPU BLAS."""
+    bad = re.compile(r"\boracle\b|openblas|scipy|numpy\.dot|np\.matmul|torch\.matmul|torch\.mm\b|cublas", re.I)
+    prod = os.path.join(ROOT, "accelerate-blas_b200")
+    for d, _, files in os.walk(prod):
+        if os.sep + "build" in d or os.sep + "haskell" in d:
+            continue
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h")):
+                for i, line in enumerate(open(os.path.join(d, f), errors="ignore")):
+                    code = line.split("//")[0].split("#")[0] if not f.endswith(".py") else line.split("#")[0]
+                    if f.endswith(".py") and ('"""' in line or line.strip().startswith(("*", '"'))):
+                        continue
+                    assert not bad.search(code), f"{f}:{i + 1}: {line.strip()}"

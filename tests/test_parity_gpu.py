@@ -1,0 +1,298 @@
+"""GPU: parity of the CUDA path (through the C ABI, via the python mirror) with the oracle.
+
+Mirrors the reference's property tests (test/Test/BLAS/Level3.hs:31-72: gemm, dims 1..64, all nine
+opA x opB, four dtypes, alpha and elements in [-1,1]; test/Test/BLAS/Level2.hs:31-68: gemv, dims
+1..128) and adds what the reference omits: dot, zero extents, k = 1, n = 1,
+unaligned / large shapes, the haddock golden vectors, the committed OpenBLAS fixtures.
+
+Tolerances (floating point; stated here and in DESIGN.md):
+  normwise  ||C - C_oracle||_F <= TOL * (k+2) * eps * |alpha| * ||A||_F * ||B||_F
+  TOL = 1 (f32, f64), 2 (c32, c64: four real products per complex one), 4 on the 3xTF32 tensor path;
+  plus the reference suite's own, much looser, elementwise `~~~` (abs 5e-5 or rel 5e-3).
+"""
+import numpy as np
+import pytest
+
+from oracle import oracle as O
+from _util import (DT, OPN, TOL_UNITS, TOL_UNITS_TF32X3, as_np, gemm_inputs, gemv_inputs, haddock_cases,
+                   openblas_cases)
+
+pytestmark = pytest.mark.gpu
+DTYPES = [O.F32, O.F64, O.C32, O.C64]
+ids = lambda d: O.NAMES[d]  # noqa: E731
+
+
+def dev(a, cuda):
+    import torch
+    return torch.from_numpy(np.ascontiguousarray(a)).to(cuda)
+
+
+def host(t):
+    return t.cpu().numpy()
+
+
+def tol_for(ab, dt, oa, ob, A, B):
+    name = ab.kernel_name(dt, oa, ob, A.shape, B.shape)
+    return TOL_UNITS_TF32X3 if "tf32x3" in name else TOL_UNITS[dt]
+
+
+def check_gemm(ab, cuda, dt, oa, ob, al, A, B, path="auto"):
+    ab.set_gemm_path(path)
+    try:
+        C = host(ab.gemm(al, oa, dev(A, cuda), ob, dev(B, cuda)))
+        tol = tol_for(ab, dt, oa, ob, A, B)
+    finally:
+        ab.set_gemm_path("auto")
+    k = A.shape[1] if oa == "N" else A.shape[0]
+    ref = O.gemm(al, oa, A, ob, B, wide=True)
+    assert C.shape == ref.shape and C.dtype == ref.dtype
+    err = O.gemm_error_units(C, ref, A, B, k, al)
+    assert err <= tol, (O.NAMES[dt], oa, ob, A.shape, B.shape, err)
+    assert O.similar(C, O.gemm(al, oa, A, ob, B, wide=False))      # the reference's own criterion
+    return err
+
+
+# --------------------------------------------------------------------------- golden vectors
+@pytest.mark.parametrize("case", haddock_cases(), ids=lambda c: c["name"])
+def test_haddock_known_answers(case, cuda):
+    import accblas_b200 as ab
+    for name in ("f32", "f64", "c32", "c64"):
+        dt = DT[name]
+        if case["dtype"] == "c64" and dt in (O.F32, O.F64):
+            continue
+        conv = (lambda v: as_np(v, DT[case["dtype"]]).astype(O.NP_DTYPE[dt]))
+        exp = conv(case["expect"])
+        if case["op"] == "dotu":
+            got = host(ab.dot(dev(conv(case["x"]), cuda), dev(conv(case["y"]), cuda)))
+        elif case["op"] == "outer":
+            got = host(ab.outer(dev(conv(case["x"]), cuda), dev(conv(case["y"]), cuda)))
+        elif case["op"] == "mXv":
+            got = host(ab.mXv(dev(conv(case["m"]), cuda), dev(conv(case["x"]), cuda)))
+        elif case["op"] == "vXm":
+            got = host(ab.vXm(dev(conv(case["x"]), cuda), dev(conv(case["m"]), cuda)))
+        else:
+            got = host(ab.mXm(dev(conv(case["a"]), cuda), dev(conv(case["b"]), cuda)))
+        assert np.array_equal(got, exp), (case["name"], name, got, exp)   # small integers: exact
+
+
+def test_openblas_fixtures(cuda):
+    import accblas_b200 as ab
+    z = openblas_cases()
+    for i in range(int(z["n_gemm"][0])):
+        dt, oa, ob = (int(v) for v in z[f"gemm{i}_meta"])
+        A, B, al = z[f"gemm{i}_A"], z[f"gemm{i}_B"], z[f"gemm{i}_alpha"][0]
+        C = host(ab.gemm(al, oa, dev(A, cuda), ob, dev(B, cuda)))
+        k = A.shape[1] if oa == 0 else A.shape[0]
+        assert O.gemm_error_units(C, z[f"gemm{i}_C"], A, B, k, al) <= 2 * TOL_UNITS[dt], (i, dt, oa, ob)
+    for i in range(int(z["n_gemv"][0])):
+        dt, oa = (int(v) for v in z[f"gemv{i}_meta"])
+        A, x, al = z[f"gemv{i}_A"], z[f"gemv{i}_x"], z[f"gemv{i}_alpha"][0]
+        y = host(ab.gemv(al, oa, dev(A, cuda), dev(x, cuda)))
+        assert O.gemm_error_units(y, z[f"gemv{i}_y"], A, x, x.shape[0], al) <= 2 * TOL_UNITS[dt], (i, dt, oa)
+
+
+# --------------------------------------------------------------------------- gemm
+@pytest.mark.parametrize("dt", DTYPES, ids=ids)
+def test_gemm_property_small(dt, cuda):
+    """The reference's generator: m, n, k in [1, 64], random op pair (Level3.hs:37-50, 68)."""
+    import accblas_b200 as ab
+    rng = np.random.default_rng(1000 + dt)
+    for it in range(60):
+        oa, ob = OPN[rng.integers(3)], OPN[rng.integers(3)]
+        m, n, k = (int(v) for v in rng.integers(1, 65, size=3))
+        al, A, B = gemm_inputs(rng, dt, oa, ob, m, n, k)
+        check_gemm(ab, cuda, dt, oa, ob, al, A, B)
+
+
+@pytest.mark.parametrize("dt", DTYPES, ids=ids)
+@pytest.mark.parametrize("oa", list(OPN))
+@pytest.mark.parametrize("ob", list(OPN))
+def test_gemm_all_ops_medium(dt, oa, ob, cuda):
+    """Every op pair at tensor-path-eligible and at awkward extents."""
+    import accblas_b200 as ab
+    rng = np.random.default_rng(2000 + 16 * dt + 4 * OPN.index(oa) + OPN.index(ob))
+    for (m, n, k) in [(256, 384, 320), (200, 136, 72), (129, 65, 33), (130, 258, 514)]:
+        al, A, B = gemm_inputs(rng, dt, oa, ob, m, n, k)
+        check_gemm(ab, cuda, dt, oa, ob, al, A, B)
+
+
+@pytest.mark.parametrize("dt", DTYPES, ids=ids)
+def test_gemm_generic_path_matches(dt, cuda):
+    import accblas_b200 as ab
+    rng = np.random.default_rng(2500 + dt)
+    for oa in OPN:
+        for ob in OPN:
+            al, A, B = gemm_inputs(rng, dt, oa, ob, 96, 80, 112)
+            check_gemm(ab, cuda, dt, oa, ob, al, A, B, path="generic")
+
+
+@pytest.mark.parametrize("dt", DTYPES, ids=ids)
+def test_gemm_degenerate(dt, cuda):
+    """k = 1 (`><`, LinearAlgebra.hs:73-78), n = 1 (complex-H gemv route, PTX/Level2.hs:57-69),
+    m = 1, zero extents (k = 0 must zero-fill an uninitialised C)."""
+    import torch
+    import accblas_b200 as ab
+    rng = np.random.default_rng(3000 + dt)
+    for (m, n, k) in [(37, 41, 1), (64, 1, 50), (1, 70, 33), (1, 1, 1), (512, 512, 1), (1024, 1, 1024)]:
+        for oa, ob in [("N", "N"), ("H", "N"), ("T", "H")]:
+            al, A, B = gemm_inputs(rng, dt, oa, ob, m, n, k)
+            check_gemm(ab, cuda, dt, oa, ob, al, A, B)
+    tdt = torch.from_numpy(np.zeros(1, dtype=O.NP_DTYPE[dt])).dtype
+    C = ab.gemm(1, "N", torch.zeros((5, 0), dtype=tdt, device=cuda), "N", torch.zeros((0, 7), dtype=tdt, device=cuda))
+    assert C.shape == (5, 7) and torch.count_nonzero(C).item() == 0
+    assert ab.gemm(1, "N", torch.zeros((0, 4), dtype=tdt, device=cuda), "N", torch.zeros((4, 3), dtype=tdt, device=cuda)).shape == (0, 3)
+    with pytest.raises(ab.AccblasError):
+        ab.gemm(1, "N", torch.zeros((2, 3), dtype=tdt, device=cuda), "N", torch.zeros((4, 2), dtype=tdt, device=cuda))
+
+
+@pytest.mark.parametrize("dt", DTYPES, ids=ids)
+def test_gemm_large_sampled(dt, cuda):
+    """BASELINE-scale shapes: the oracle checks a sample of rows (it is O(mnk) scalar code); the
+    full result is checked through linearity: (A1 + A2) B == A1 B + A2 B within tolerance."""
+    import accblas_b200 as ab
+    rng = np.random.default_rng(4000 + dt)
+    n = 2048 if dt in (O.F32, O.F64) else 1024
+    for oa, ob in [("N", "N"), ("N", "T"), ("T", "N"), ("H", "H")]:
+        al, A, B = gemm_inputs(rng, dt, oa, ob, n, n, n)
+        dA, dB = dev(A, cuda), dev(B, cuda)
+        C = host(ab.gemm(al, oa, dA, ob, dB))
+        tol = tol_for(ab, dt, oa, ob, A, B)
+        rows = rng.choice(n, size=8, replace=False)
+        Asub = A[rows] if oa == "N" else np.ascontiguousarray(A[:, rows])
+        ref = O.gemm(al, oa, Asub, ob, B, wide=True)
+        err = O.gemm_error_units(C[rows], ref, Asub, B, n, al)
+        assert err <= tol, (O.NAMES[dt], oa, ob, err)
+        A2 = O.uniform(rng, A.shape, dt)
+        C2 = host(ab.gemm(al, oa, dev(A2, cuda), ob, dB))
+        C12 = host(ab.gemm(al, oa, dev(A + A2, cuda), ob, dB))
+        lin = O.gemm_error_units(C12, C + C2, A + A2, B, n, al)
+        assert lin <= 3 * tol, (O.NAMES[dt], oa, ob, lin)
+
+
+# --------------------------------------------------------------------------- gemv
+@pytest.mark.parametrize("dt", DTYPES, ids=ids)
+def test_gemv_property(dt, cuda):
+    """The reference's generator: m, n in [1, 128], op in N/T/H (Level2.hs:37-46, 64) + larger."""
+    import accblas_b200 as ab
+    rng = np.random.default_rng(5000 + dt)
+    shapes = [tuple(int(v) for v in rng.integers(1, 129, size=2)) for _ in range(40)]
+    shapes += [(1, 1), (1, 300), (300, 1), (1000, 2000), (2000, 3000), (513, 1027), (4096, 64), (64, 4096),
+               (3001, 2048), (2048, 3001)]
+    for (m, n) in shapes:
+        for oa in OPN:
+            al, A, x = gemv_inputs(rng, dt, oa, m, n)
+            y = host(ab.gemv(al, oa, dev(A, cuda), dev(x, cuda)))
+            ref = O.gemv(al, oa, A, x, wide=True)
+            assert y.shape == ref.shape
+            err = O.gemm_error_units(y, ref, A, x, x.shape[0], al)
+            assert err <= TOL_UNITS[dt], (O.NAMES[dt], oa, m, n, err)
+            assert O.similar(y, O.gemv(al, oa, A, x, wide=False))
+
+
+@pytest.mark.parametrize("dt", DTYPES, ids=ids)
+def test_gemv_edges(dt, cuda):
+    import torch
+    import accblas_b200 as ab
+    tdt = torch.from_numpy(np.zeros(1, dtype=O.NP_DTYPE[dt])).dtype
+    y = ab.gemv(1, "N", torch.zeros((6, 0), dtype=tdt, device=cuda), torch.zeros((0,), dtype=tdt, device=cuda))
+    assert y.shape == (6,) and torch.count_nonzero(y).item() == 0
+    y = ab.gemv(1, "T", torch.zeros((0, 6), dtype=tdt, device=cuda), torch.zeros((0,), dtype=tdt, device=cuda))
+    assert y.shape == (6,) and torch.count_nonzero(y).item() == 0
+    assert ab.gemv(1, "N", torch.zeros((0, 6), dtype=tdt, device=cuda), torch.zeros((6,), dtype=tdt, device=cuda)).shape == (0,)
+    with pytest.raises(ab.AccblasError):
+        ab.gemv(1, "N", torch.zeros((3, 6), dtype=tdt, device=cuda), torch.zeros((3,), dtype=tdt, device=cuda))
+    # unaligned base pointer (a view one element into a buffer)
+    rng = np.random.default_rng(5500 + dt)
+    al, A, x = gemv_inputs(rng, dt, "N", 67, 130)
+    buf = torch.zeros(A.size + 1, dtype=tdt, device=cuda)
+    buf[1:] = dev(A.reshape(-1), cuda)
+    for oa in OPN:
+        xx = x if oa == "N" else O.uniform(rng, (67,), dt)
+        y = host(ab.gemv(al, oa, buf[1:].view(67, 130), dev(xx, cuda)))
+        assert O.gemm_error_units(y, O.gemv(al, oa, A, xx), A, xx, xx.shape[0], al) <= TOL_UNITS[dt]
+
+
+def test_gemv_large_roundtrip(cuda):
+    """BASELINE-size-independent property at a large shape: A (x1 + x2) == A x1 + A x2, and
+    e_i^T A == row i, A e_j == column j (exact)."""
+    import torch
+    import accblas_b200 as ab
+    m = n = 8192
+    g = torch.Generator(device=cuda).manual_seed(7)
+    A = torch.rand((m, n), dtype=torch.float64, device=cuda, generator=g) * 2 - 1
+    e = torch.zeros(n, dtype=torch.float64, device=cuda)
+    e[1234] = 1.0
+    assert torch.equal(ab.mXv(A, e), A[:, 1234])
+    assert torch.equal(ab.vXm(e, A), A[1234, :])
+    x1 = torch.rand(n, dtype=torch.float64, device=cuda, generator=g) * 2 - 1
+    x2 = torch.rand(n, dtype=torch.float64, device=cuda, generator=g) * 2 - 1
+    for f in (lambda v: ab.mXv(A, v), lambda v: ab.vXm(v, A)):
+        d = (f(x1 + x2) - (f(x1) + f(x2))).abs().max().item()
+        assert d <= 3 * n * 2.0 ** -53 * 1.0 * (n ** 0.5), d
+
+
+# --------------------------------------------------------------------------- dot
+@pytest.mark.parametrize("dt", DTYPES, ids=ids)
+def test_dot(dt, cuda):
+    import accblas_b200 as ab
+    rng = np.random.default_rng(6000 + dt)
+    for n in [0, 1, 2, 3, 31, 32, 33, 1000, 2047, 2048, 2049, 65537, 1 << 20, (1 << 20) + 3, 5_000_001]:
+        x, y = O.uniform(rng, (n,), dt), O.uniform(rng, (n,), dt)
+        for conj in ([False, True] if dt in (O.C32, O.C64) else [False]):
+            got = host((ab.dotc if conj else ab.dotu)(dev(x, cuda), dev(y, cuda)))
+            ref = O.dot(x, y, conj=conj, wide=True)
+            bound = (n + 2) * O.EPS[dt] * max(np.linalg.norm(x) * np.linalg.norm(y), 1e-300) * TOL_UNITS[dt]
+            assert abs(complex(got) - complex(ref)) <= bound, (O.NAMES[dt], n, conj, got, ref)
+    # ragged extents: min length (zipWith); unaligned views
+    x, y = O.uniform(rng, (1000,), dt), O.uniform(rng, (777,), dt)
+    got = host(ab.dotu(dev(x, cuda), dev(y, cuda)))
+    assert abs(complex(got) - complex(O.dot(x, y))) <= 779 * O.EPS[dt] * np.linalg.norm(x) * np.linalg.norm(y) * 2
+    dx, dy = dev(x, cuda), dev(x[::-1].copy(), cuda)
+    got = host(ab.dotu(dx[1:], dy[3:]))
+    ref = O.dot(x[1:], x[::-1][3:].copy())
+    assert abs(complex(got) - complex(ref)) <= 1000 * O.EPS[dt] * np.linalg.norm(x) ** 2 * 2
+
+
+def test_dot_is_reproducible_and_linear(cuda):
+    import torch
+    import accblas_b200 as ab
+    g = torch.Generator(device=cuda).manual_seed(11)
+    n = (1 << 26) + 5
+    x = torch.rand(n, dtype=torch.float64, device=cuda, generator=g) * 2 - 1
+    y = torch.rand(n, dtype=torch.float64, device=cuda, generator=g) * 2 - 1
+    a, b = ab.dot(x, y), ab.dot(x, y)
+    assert torch.equal(a, b)                                  # fixed summation order
+    ones = torch.ones(n, dtype=torch.float64, device=cuda)
+    assert ab.dot(ones, ones).item() == float(n)              # exact in fp64
+    s = ab.dot(x, y).item() + ab.dot(x, ones).item()
+    t = ab.dot(x, y + ones).item()
+    assert abs(s - t) <= n * 2.0 ** -53 * (n ** 0.5) * 4
+
+
+# --------------------------------------------------------------------------- host-buffer ABI
+@pytest.mark.parametrize("dt", DTYPES, ids=ids)
+def test_host_entry_points(dt, cuda):
+    import accblas_b200 as ab
+    rng = np.random.default_rng(7000 + dt)
+    al, A, B = gemm_inputs(rng, dt, "N", "T", 300, 200, 100)
+    C = ab.gemm(al, "N", A, "T", B)
+    assert O.gemm_error_units(C, O.gemm(al, "N", A, "T", B), A, B, 100, al) <= TOL_UNITS_TF32X3
+    al, A, B = gemm_inputs(rng, dt, "N", "N", 4096, 256, 128)        # row-panel pipeline path
+    C = ab.gemm(al, "N", A, "N", B)
+    ref = O.gemm(al, "N", A[::97], "N", B)
+    assert O.gemm_error_units(C[::97], ref, A[::97], B, 128, al) <= TOL_UNITS_TF32X3
+    al, A, x = gemv_inputs(rng, dt, "H", 150, 70)
+    y = ab.gemv(al, "H", A, x)
+    assert O.gemm_error_units(y, O.gemv(al, "H", A, x), A, x, 150, al) <= TOL_UNITS[dt]
+    x, y = O.uniform(rng, (5000,), dt), O.uniform(rng, (5000,), dt)
+    d = ab.dotu(x, y)
+    assert abs(complex(d) - complex(O.dot(x, y))) <= 5002 * O.EPS[dt] * np.linalg.norm(x) * np.linalg.norm(y) * 2
+
+
+def test_launches_are_counted(cuda):
+    import torch
+    import accblas_b200 as ab
+    a = torch.ones((64, 64), dtype=torch.float64, device=cuda)
+    before = ab.launch_count()
+    ab.mXm(a, a)
+    assert ab.launch_count() > before
