@@ -113,10 +113,11 @@ def _ptr(t) -> ctypes.c_void_p:
 # ------------------------------------------------------------------------------------
 # Level 3
 # ------------------------------------------------------------------------------------
-def gemm(alpha, opA, A, opB, B):
+def gemm(alpha, opA, A, opB, B, out=None):
     """``C = alpha * op(A) * op(B)`` -- gemm, BLAS/Level3.hs:57-64.
 
     shape op(A) = (m, k), shape op(B) = (k, n), shape C = (m, n); stored shapes are pre-op.
+    ``out`` (device path only): a contiguous (m, n) tensor to write instead of allocating one.
     """
     oa, ob = _op(opA), _op(opB)
     code = _code(A)
@@ -129,7 +130,12 @@ def gemm(alpha, opA, A, opB, B):
         m = A.shape[0] if oa == N else A.shape[1]          # LLVM/PTX/Level3.hs:57-62
         n = B.shape[1] if ob == N else B.shape[0]
         with torch.cuda.device(A.device):
-            C = torch.empty((m, n), dtype=A.dtype, device=A.device)   # allocateRemote: uninitialised
+            if out is None:
+                C = torch.empty((m, n), dtype=A.dtype, device=A.device)   # allocateRemote: uninitialised
+            else:
+                if tuple(out.shape) != (m, n) or out.dtype != A.dtype or not out.is_contiguous() or not out.is_cuda:
+                    raise ValueError("gemm: out must be a contiguous CUDA tensor of shape (m, n) and A's dtype")
+                C = out
             st = L.accblas_gemm(_stream(A), code, oa, ob, A.shape[0], A.shape[1], B.shape[0], B.shape[1],
                                 al, _ptr(A), _ptr(B), _ptr(C))
         _ffi.check(st, "accblas_gemm")

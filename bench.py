@@ -1,0 +1,401 @@
+#!/usr/bin/env python
+"""bench.py -- the driver's measurement contract for the BLAS hot path.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--extras]
+
+N = 1  workload = BASELINE.json configs[1]: Double gemm n = 8192, `A <> B` (NN); one step = one
+       product of two resident 8192 x 8192 f64 matrices (2 * 8192^3 flop).  value = TFLOP/s with
+       the operands already in HBM; e2e = the same product through the host-buffer C ABI
+       (accblas_gemm_host: pinned host A, B -> device -> C back to host inside the timed region).
+N > 1  workload = configs[4]: Double gemm n = 32768 row-sharded over the ranks (A, B start and C
+       ends on rank 0: scatter A row panels, broadcast B, gather C over NCCL); strong scaling.
+--impl reference   the reference's llvm-native path (one cblas_dgemm RowMajor call,
+       LLVM/Native/Level3.hs:85) on the host cores through oracle/openblas_ref.py (kind "port":
+       the reference is Haskell and cannot be built here; OpenBLAS is the library it calls).
+One JSON line on stdout (rank 0).  Extra per-case numbers (sgemm, zgemm, gemv, dot) go into
+"extras" when --extras is given; they are not the headline.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "accelerate-blas_b200", "python"))
+
+N1 = 8192           # configs[1]
+NMG = 32768         # configs[4]
+METRIC = "GEMM TFLOP/s f32/f64/complex + gemv/dot HBM GB/s at 1/2/4/8 B200"
+DMMA_PEAK_FALLBACK = 36.9   # TFLOP/s, baseline/ubench.cu on this pool (profiles/r01_ubench.jsonl)
+
+
+def measured_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return json.load(f)
+    except OSError:
+        return {}
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.index = index
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except OSError:
+            self.proc = None
+        return self
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), line.strip()))
+
+    def stop(self, t0, t1):
+        if self.proc is not None:
+            self.proc.terminate()
+        sm, mx, reasons = [], 0.0, set()
+        for ts, line in self.rows:
+            if ts < t0 - 0.05 or ts > t1 + 0.15:
+                continue
+            f = [x.strip() for x in line.split(",")]
+            try:
+                sm.append(float(f[1]))
+                mx = max(mx, float(f[2]))
+            except (ValueError, IndexError):
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx or None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def dmma_peak_live():
+    """Issue-rate peak of the FP64 tensor pipe measured on THIS box (baseline/ubench, < 1 s)."""
+    exe = os.path.join(ROOT, "baseline", "ubench")
+    if os.path.exists(exe):
+        try:
+            out = subprocess.run([exe], capture_output=True, text=True, timeout=60).stdout
+            best = 0.0
+            for line in out.splitlines():
+                d = json.loads(line)
+                if d.get("ubench") == "dmma_m8n8k4":
+                    best = max(best, d["tflops"])
+            if best > 0:
+                return best, "baseline/ubench dmma_m8n8k4 issue rate measured live on this GPU"
+        except Exception:
+            pass
+    return DMMA_PEAK_FALLBACK, "baseline/ubench dmma_m8n8k4 issue rate, earlier measurement on this pool (profiles/)"
+
+
+# --------------------------------------------------------------------------------------
+# CPU arm: the reference's llvm-native path (cblas_dgemm RowMajor) on the host cores
+# --------------------------------------------------------------------------------------
+def cpu_dgemm_sample(n, budget_s=12.0):
+    """Times cblas_dgemm(RowMajor, N, N) on a bounded sample of the workload: the first `rows` rows
+    of A against the full B (same k, n; TFLOP/s of a large dgemm does not depend on m)."""
+    import numpy as np
+    from oracle import openblas_ref as R
+    cores = R.host_cores()
+    R.set_threads(cores)
+    rows = 2048 if n >= 4096 else n
+    rng = np.random.default_rng(0x5EED0000 + 16)
+    A = rng.uniform(-1, 1, size=(rows, n))
+    B = rng.uniform(-1, 1, size=(n, n))
+    C = np.empty((rows, n))
+    R.gemm(1.0, "N", A, "N", B, out=C)          # warm-up (thread pool, page faults)
+    ts = []
+    t_all = time.perf_counter()
+    while len(ts) < 3 or (time.perf_counter() - t_all < budget_s and len(ts) < 20):
+        t = time.perf_counter()
+        R.gemm(1.0, "N", A, "N", B, out=C)
+        ts.append(time.perf_counter() - t)
+    best = min(ts)
+    return {"value": round(2.0 * rows * n * n / best * 1e-12, 4), "unit": "TFLOP/s", "cores": cores,
+            "kind": "port",
+            "sample": f"cblas_dgemm RowMajor NN, first {rows} rows of A x B {n}x{n} (k=n={n}), best of {len(ts)}, "
+                      f"OpenBLAS {R.config().split()[1]} via scipy"}, rows, (A, B, C)
+
+
+def run_reference(args):
+    """--impl reference: K timed steps of the CPU path on the same config/metric."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import openblas_ref as R
+    n = N1 if args.gpus == 1 else NMG
+    info, rows, (A, B, C) = cpu_dgemm_sample(N1, budget_s=1.0)
+    for _ in range(max(args.warmup, 1)):
+        R.gemm(1.0, "N", A, "N", B, out=C)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        R.gemm(1.0, "N", A, "N", B, out=C)
+    dt = time.perf_counter() - t0
+    tf = 2.0 * rows * N1 * N1 * args.steps / dt * 1e-12
+    info["value"] = round(tf, 4)
+    info["sample"] = (f"each step = cblas_dgemm RowMajor NN on rows 0..{rows - 1} of A x B {N1}x{N1}; "
+                      f"throughput of the {n}^3 product is the same per flop; OpenBLAS via scipy, {info['cores']} threads")
+    line = {"impl": "reference", "metric": METRIC, "value": round(tf, 4), "unit": "TFLOP/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(dt / args.steps * 1e3, 3),
+            "higher_is_better": True, "scaling": "weak" if args.gpus == 1 else "strong", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic uniform(-1,1)",
+            "config": workload_config(args.gpus), "cpu_baseline": info,
+            "e2e": {"value": round(tf, 4), "unit": "TFLOP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(ngpu):
+    if ngpu == 1:
+        return {"workload": f"Double gemm n={N1} NN via (<>) on 1xB200 (BASELINE.json configs[1])",
+                "m": N1, "n": N1, "k": N1, "opA": "N", "opB": "N", "alpha": 1,
+                "l2": "inputs (1 GiB) exceed the 126 MB L2; no flush needed"}
+    return {"workload": f"Double gemm n={NMG} row-sharded over {ngpu} B200 (BASELINE.json configs[4]); "
+                        "A, B start and C ends on rank 0", "m": NMG, "n": NMG, "k": NMG, "opA": "N", "opB": "N",
+            "alpha": 1, "parallelism": f"rows of A/C split {ngpu} ways, B broadcast, C gathered (NCCL)",
+            "l2": "inputs (16 GiB) exceed the 126 MB L2; no flush needed"}
+
+
+# --------------------------------------------------------------------------------------
+# GPU arm
+# --------------------------------------------------------------------------------------
+def seeded(shape, seed, device):
+    """uniform(-1,1) f64 from a fixed Philox seed."""
+    import torch
+    g = torch.Generator(device=device).manual_seed(seed)
+    return torch.rand(shape, dtype=torch.float64, device=device, generator=g) * 2 - 1
+
+
+def run_single(args):
+    import numpy as np
+    import torch
+    import accblas_b200 as ab
+    dev = torch.device("cuda:0")
+    torch.cuda.set_device(dev)
+    n = N1
+    flops = 2.0 * n * n * n
+    A = seeded((n, n), 0x5EED0000 + 16 + 0, dev)
+    B = seeded((n, n), 0x5EED0000 + 16 + 1, dev)
+    assert ab.kernel_name(1, "N", "N", A.shape, B.shape) == "dgemm_dmma_tma"
+
+    # ---- device-resident: W warm-ups, then exactly K timed steps ----
+    for _ in range(args.warmup):
+        C = ab.mXm(A, B)
+    torch.cuda.synchronize()
+    sampler = ClockSampler(0).start()
+    time.sleep(0.25)
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+    l0 = ab.launch_count()
+    torch.cuda.synchronize()
+    t0 = time.time()
+    ev[0].record()
+    for i in range(args.steps):
+        C = ab.mXm(A, B)
+        ev[i + 1].record()
+    torch.cuda.synchronize()
+    t1 = time.time()
+    launches = ab.launch_count() - l0
+    clocks = sampler.stop(t0, t1)
+    total_ms = ev[0].elapsed_time(ev[-1])
+    per_step = [ev[i].elapsed_time(ev[i + 1]) for i in range(args.steps)]
+    kernel_ms = sum(per_step) / len(per_step)        # one kernel per step: its average launch duration
+    value = flops * args.steps / total_ms * 1e-9
+
+    # spot parity inside the bench (8 rows against the oracle): a fast wrong kernel is not a result
+    from oracle import oracle as O
+    rows = [0, 1, 4095, 8191]
+    Ah, Bh = A[rows].cpu().numpy(), B.cpu().numpy()
+    err = O.gemm_error_units(C[rows].cpu().numpy(), O.gemm(1.0, "N", Ah, "N", Bh), Ah, Bh, n)
+    assert err <= 1.0, f"parity lost in bench: {err}"
+
+    # ---- end to end through the host-buffer C ABI (pinned host memory) ----
+    Ah = torch.empty((n, n), dtype=torch.float64).pin_memory()
+    Bh = torch.empty((n, n), dtype=torch.float64).pin_memory()
+    Ch = torch.empty((n, n), dtype=torch.float64).pin_memory()
+    Ah.copy_(A)
+    Bh.copy_(B)
+    L = ab.lib()
+    import ctypes
+    one = np.array([1.0])
+
+    def e2e_step():
+        st = L.accblas_gemm_host(None, 1, 0, 0, n, n, n, n, one.ctypes.data_as(ctypes.c_void_p),
+                                 ctypes.c_void_p(Ah.data_ptr()), ctypes.c_void_p(Bh.data_ptr()),
+                                 ctypes.c_void_p(Ch.data_ptr()))
+        assert st == 0, st
+    e2e_steps = max(3, min(args.steps, 10))
+    for _ in range(2):
+        e2e_step()
+    torch.cuda.synchronize()
+    t = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e_step()                                   # synchronous: returns with C in host memory
+    e2e_s = (time.perf_counter() - t) / e2e_steps
+    assert torch.equal(Ch[rows], C[rows].cpu()), "e2e result differs from the device-resident result"
+    del Ah, Bh, Ch
+
+    peak, peak_src = dmma_peak_live()
+    cpu, _, _ = cpu_dgemm_sample(n)
+    mp = measured_peaks()
+    line = {
+        "metric": METRIC, "value": round(value, 3), "unit": "TFLOP/s", "n_gpus": 1, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": round(total_ms / args.steps, 4), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic uniform(-1,1), fixed Philox seeds",
+        "config": workload_config(1),
+        "roofline": {"bound": "tensor", "achieved": round(flops / kernel_ms * 1e-9, 3), "peak": round(peak, 2),
+                     "unit": "TFLOP/s", "frac": round(flops / kernel_ms * 1e-9 / peak, 4), "traffic": None,
+                     "kernel": "dgemm_dmma_kernel<true,false>", "flops_per_launch": flops,
+                     "peak_source": peak_src + "; MEASURED_PEAKS.json carries no FP64 figure "
+                                    f"(its bf16 {mp.get('bf16_tflops')} TFLOP/s is a different pipe); nominal FP64 37-40"},
+        "cpu_baseline": cpu,
+        "e2e": {"value": round(flops / e2e_s * 1e-12, 3), "unit": "TFLOP/s", "h2d_bytes_per_step": 2 * 8 * n * n,
+                "d2h_bytes_per_step": 8 * n * n, "ms_per_step": round(e2e_s * 1e3, 3), "steps": e2e_steps,
+                "api": "accblas_gemm_host (pinned host buffers)"},
+        "gpu_launches": int(launches), "clocks": clocks,
+        "parity": {"error_units": round(err, 5), "tolerance_units": 1.0, "rows_checked": len(rows)},
+    }
+    if args.extras:
+        line["extras"] = extras()
+    print(json.dumps(line), flush=True)
+
+
+def run_multi(args):
+    """N > 1: configs[4], Double gemm n = 32768, rows of A/C split over the ranks, B broadcast,
+    C gathered; A, B start and C ends on rank 0.  Timed on the device, max over ranks."""
+    import torch
+    import torch.distributed as dist
+    import accblas_b200 as ab
+    from accblas_b200 import mg
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    local = int(os.environ.get("LOCAL_RANK", rank))
+    dev = torch.device(f"cuda:{local}")
+    torch.cuda.set_device(dev)
+    dist.init_process_group("nccl", device_id=dev)
+    n = args.n_mg
+    flops = 2.0 * n * n * n
+    A = B = C = None
+    if rank == 0:
+        A = seeded((n, n), 0x5EED0000 + 64 + 0, dev)
+        B = seeded((n, n), 0x5EED0000 + 64 + 1, dev)
+        C = torch.empty((n, n), dtype=torch.float64, device=dev)
+
+    def step():
+        return mg.gemm_rowsharded(1.0, "N", A, "N", B, shapeA=(n, n), shapeB=(n, n), dtype=torch.float64,
+                                  device=dev, root=0, subpanels=args.subpanels, out=C)
+    for _ in range(args.warmup):
+        step()
+    torch.cuda.synchronize()
+    dist.barrier()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local).start() if rank == 0 else None
+    l0 = ab.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.time()
+    e0.record()
+    for _ in range(args.steps):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    dist.barrier()
+    torch.cuda.synchronize()
+    t1 = time.time()
+    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    launches = torch.tensor([ab.launch_count() - l0], dtype=torch.int64, device=dev)
+    dist.all_reduce(launches, op=dist.ReduceOp.SUM)
+    total_ms = ms.item()
+    if rank == 0:
+        clocks = sampler.stop(t0, t1)
+        # parity: 4 rows spread over the rank panels against the oracle
+        from oracle import oracle as O
+        rows = [1, n // 2 + 3, n - 1, (n // world) * (world - 1) + 7]
+        Ah, Bh = A[rows].cpu().numpy(), B.cpu().numpy()
+        err = O.gemm_error_units(C[rows].cpu().numpy(), O.gemm(1.0, "N", Ah, "N", Bh), Ah, Bh, n)
+        assert err <= 1.0, f"parity lost in multi-GPU bench: {err}"
+        peak, peak_src = DMMA_PEAK_FALLBACK, "baseline/ubench dmma_m8n8k4 issue rate on this pool (profiles/)"
+        value = flops * args.steps / total_ms * 1e-9
+        comm_bytes = 8.0 * n * n * (1 + 2.0 * (world - 1) / world)     # bcast B + scatter A + gather C (per root link)
+        line = {
+            "metric": METRIC, "value": round(value, 3), "unit": "TFLOP/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": round(total_ms / args.steps, 3), "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic uniform(-1,1), fixed Philox seeds", "config": workload_config(world) | {"m": n, "n": n, "k": n},
+            "roofline": {"bound": "tensor", "achieved": round(value / world, 3), "peak": peak, "unit": "TFLOP/s",
+                         "frac": round(value / world / peak, 4), "traffic": None,
+                         "kernel": "dgemm_dmma_kernel<true,false> per rank; achieved = whole-job rate / ranks "
+                                   "(includes scatter/broadcast/gather time)", "peak_source": peak_src,
+                         "nvlink_bytes_through_root": comm_bytes},
+            "cpu_baseline": None,
+            "e2e": {"value": round(value, 3), "unit": "TFLOP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0,
+                    "note": "operands and result are device-resident on rank 0 by definition of configs[4]; the "
+                            "timed region already contains every inter-GPU transfer"},
+            "gpu_launches": int(launches.item()), "clocks": clocks,
+            "parity": {"error_units": round(err, 5), "tolerance_units": 1.0, "rows_checked": len(rows)},
+        }
+        print(json.dumps(line), flush=True)
+    dist.destroy_process_group()
+
+
+def extras():
+    """Other BASELINE.json configs, one short measurement each (not the headline)."""
+    import torch
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import io
+    import contextlib
+    import perf
+    buf = io.StringIO()
+    with contextlib.redirect_stdout(buf):
+        for ops in ("NT", "TN"):
+            perf.gemm_case("f64", ops[0], ops[1], N1, N1, N1, 3)
+        for ops in ("NN", "NT", "TN"):
+            perf.gemm_case("f32", ops[0], ops[1], N1, N1, N1, 3)
+        perf.gemm_case("f64", "N", "N", 1024, 1024, 1024, 20)
+        perf.gemm_case("c64", "H", "N", 4096, 4096, 4096, 3)
+        perf.gemm_case("c32", "H", "N", 4096, 4096, 4096, 3)
+        perf.gemv_case("f64", "N", 32768, 32768, 20)
+        perf.gemv_case("f64", "T", 32768, 32768, 20)
+        perf.dot_case("f64", 1 << 28, 20)
+    torch.cuda.synchronize()
+    return [json.loads(l) for l in buf.getvalue().splitlines() if l.startswith("{")]
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--extras", action="store_true")
+    ap.add_argument("--n-mg", type=int, default=NMG, dest="n_mg")
+    ap.add_argument("--subpanels", type=int, default=4)
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        return run_reference(args)
+    if world > 1 or args.gpus > 1:
+        if world == 1:
+            raise SystemExit("bench.py --gpus N > 1 must be launched with torch.distributed.run (one rank per GPU)")
+        return run_multi(args)
+    return run_single(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,106 @@
+"""CPU, world_size 2, gloo: the sharding + collective logic of accblas_b200.mg with the local product
+injected (the oracle's OpenBLAS pin stands in for the CUDA library, which needs a GPU)."""
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _local_gemm(alpha, opa, A, opb, B, out=None):
+    from oracle import openblas_ref as R
+    C = torch.from_numpy(R.gemm(alpha, opa, A.numpy(), opb, B.numpy()))
+    if out is not None:
+        out.copy_(C)
+        return out
+    return C
+
+
+def _local_gemv(alpha, opa, A, x):
+    from oracle import openblas_ref as R
+    return torch.from_numpy(R.gemv(alpha, opa, A.numpy(), x.numpy()))
+
+
+def _local_dot(x, y):
+    from oracle import openblas_ref as R
+    return torch.tensor(R.dot(x.numpy(), y.numpy()))
+
+
+def _worker(rank, world, port, q):
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "accelerate-blas_b200", "python"))
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from accblas_b200 import mg
+        from oracle import oracle as O
+        rng = np.random.default_rng(42)          # same stream on both ranks: both can form the expectation
+        res = {}
+        for (oa, ob, m, n, k) in [("N", "N", 300, 70, 90), ("T", "N", 257, 33, 64), ("N", "T", 5, 40, 20),
+                                  ("H", "H", 384, 16, 48)]:
+            for dt in (O.F64, O.C64):
+                A = O.uniform(rng, (m, k) if oa == "N" else (k, m), dt)
+                B = O.uniform(rng, (k, n) if ob == "N" else (n, k), dt)
+                tA, tB = torch.from_numpy(A), torch.from_numpy(B)
+                C = mg.gemm_rowsharded(0.5, oa, tA if rank == 0 else None, ob, tB if rank == 0 else None,
+                                       shapeA=A.shape, shapeB=B.shape, dtype=tA.dtype, device="cpu",
+                                       subpanels=2, local_gemm=_local_gemm)
+                if rank == 0:
+                    ref = O.gemm(0.5, oa, A, ob, B)
+                    res[f"gemm_{oa}{ob}_{dt}"] = O.gemm_error_units(C.numpy(), ref, A, B, k, 0.5)
+                else:
+                    assert C is None
+        # gemv N: rows pre-sharded, x replicated; T: rows and x sharded
+        A = O.uniform(rng, (256, 100), O.F64)
+        x = O.uniform(rng, (100,), O.F64)
+        half = slice(rank * 128, (rank + 1) * 128)
+        y = mg.gemv_sharded(1.0, "N", torch.from_numpy(A[half]), torch.from_numpy(x), local_gemv=_local_gemv)
+        res["gemv_N"] = O.gemm_error_units(y.numpy(), O.gemv(1.0, "N", A, x), A, x, 100)
+        x2 = O.uniform(rng, (256,), O.F64)
+        y = mg.gemv_sharded(1.0, "T", torch.from_numpy(A[half]), torch.from_numpy(x2[half]), local_gemv=_local_gemv)
+        res["gemv_T"] = O.gemm_error_units(y.numpy(), O.gemv(1.0, "T", A, x2), A, x2, 256)
+        a, b = O.uniform(rng, (1000,), O.F64), O.uniform(rng, (1000,), O.F64)
+        h = slice(rank * 500, (rank + 1) * 500)
+        d = mg.dot_sharded(torch.from_numpy(a[h]), torch.from_numpy(b[h]), local_dot=_local_dot)
+        res["dot"] = abs(d.item() - O.dot(a, b)) / (1000 * 2.0 ** -53 * np.linalg.norm(a) * np.linalg.norm(b))
+        q.put((rank, res))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_row_panels():
+    sys.path.insert(0, os.path.join(ROOT, "accelerate-blas_b200", "python"))
+    from accblas_b200.mg import row_panels
+    assert row_panels(32768, 8) == [(i * 4096, 4096) for i in range(8)]
+    p = row_panels(300, 2)
+    assert p == [(0, 256), (256, 44)]
+    p = row_panels(5, 4)
+    assert p[0] == (0, 5) and all(r == 0 for _, r in p[1:])
+    for m, w in [(1000, 3), (129, 8), (0, 2)]:
+        p = row_panels(m, w)
+        assert sum(r for _, r in p) == m and all(p[i][0] + p[i][1] == p[i + 1][0] or p[i + 1][1] == 0 for i in range(w - 1))
+
+
+@pytest.mark.timeout(180)
+def test_world2_gloo():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29500 + os.getpid() % 2000
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    out = dict(q.get(timeout=150) for _ in range(2))
+    for p in procs:
+        p.join(30)
+        assert p.exitcode == 0
+    for rank, res in out.items():
+        assert res, rank
+        for kname, err in res.items():
+            assert err <= 2.0, (rank, kname, err)
+    assert any(k.startswith("gemm_") for k in out[0])
