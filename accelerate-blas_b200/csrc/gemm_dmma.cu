@@ -188,6 +188,182 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
 }
 
 
+// =====================================================================================
+// complex f64 (zgemm): "4M in registers".  Interleaved (re,im) operands are used as stored:
+// one ld.shared.v2.f64 brings (re, im) of a fragment element, and each complex tile product is
+// four DMMAs   Cr += Ar Br;  Cr += (-Ai) Bi;  Ci += Ar Bi;  Ci += Ai Br
+// with the conjugations of `H` folded into the sign flips (integer XOR on the high word).
+// The real and imaginary accumulators of an element live in the same lane, so the epilogue
+// writes interleaved complex numbers with 16-byte stores and no planar pass exists anywhere.
+//   CTA tile 128 x 64 (complex), K-block 8 complex (128 bytes), 8-stage ring of 24 KiB stages,
+//   warps 4 (m) x 2 (n), warp tile 32 x 32 = 4 x 4 complex DMMA tiles (64 accumulator doubles).
+//   k slots: step 0 reads k = 0,2,4,6, step 1 reads k = 1,3,5,7 (conflict-free quarter-warp
+//   ld.shared.v2 under the 128-byte swizzle for both majors).
+// =====================================================================================
+constexpr int ZBM = 128, ZBN = 64, ZBK = 8;
+constexpr int ZSTAGES = 8;
+constexpr int ZA_BYTES = ZBM * ZBK * 16, ZB_BYTES = ZBN * ZBK * 16, ZSTAGE_BYTES = ZA_BYTES + ZB_BYTES;
+constexpr int ZSMEM_BYTES = ZSTAGES * ZSTAGE_BYTES + 1024 + 2 * ZSTAGES * 8;
+
+__device__ __forceinline__ double2 lds128(uint32_t addr) {
+    double2 v;
+    asm volatile("ld.shared.v2.f64 {%0,%1}, [%2];" : "=d"(v.x), "=d"(v.y) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ double flip(double x) {
+    return __hiloint2double(__double2hiint(x) ^ 0x80000000, __double2loint(x));
+}
+
+struct ZgemmParams {
+    int64_t m, n, k;
+    double alr, ali;
+    double2 *C;
+    int tiles_m, tiles_n;
+};
+
+template <bool AK, bool BKM, bool CONJA, bool CONJB>
+__global__ void __launch_bounds__(THREADS, 1)
+zgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
+                  const ZgemmParams p)
+{
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t smem_base = (tma::smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t bar_base = smem_base + ZSTAGES * ZSTAGE_BYTES;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    constexpr int GROUP = 16;
+    int tile_m, tile_n;
+    {
+        const int per_group = GROUP * p.tiles_n;
+        const int grp = blockIdx.x / per_group;
+        const int first_m = grp * GROUP;
+        const int gsz = min(p.tiles_m - first_m, GROUP);
+        const int in_grp = blockIdx.x - grp * per_group;
+        tile_m = first_m + in_grp % gsz;
+        tile_n = in_grp / gsz;
+    }
+    const int m0 = tile_m * ZBM, n0 = tile_n * ZBN;
+    const int kblocks = (int)((p.k + ZBK - 1) / ZBK);
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < ZSTAGES; ++s) {
+            tma::mbar_init(bar_base + 8 * s, 1);
+            tma::mbar_init(bar_base + 8 * (ZSTAGES + s), CONSUMER_WARPS);
+        }
+        tma::fence_barrier_init();
+    }
+    __syncthreads();
+
+    if (warp == CONSUMER_WARPS) {
+        if (lane == 0) {
+            tma::prefetch_tmap(&mapA);
+            tma::prefetch_tmap(&mapB);
+            for (int kb = 0; kb < kblocks; ++kb) {
+                const int s = kb % ZSTAGES;
+                const uint32_t round = kb / ZSTAGES;
+                if (kb >= ZSTAGES) tma::mbar_wait(bar_base + 8 * (ZSTAGES + s), (round - 1) & 1);
+                const uint32_t full = bar_base + 8 * s;
+                const uint32_t sa = smem_base + s * ZSTAGE_BYTES, sb = sa + ZA_BYTES;
+                tma::mbar_expect_tx(full, ZSTAGE_BYTES);
+                const int k0 = kb * ZBK;
+                // tensor maps are over doubles: inner coordinates are 2 x the complex index
+                if (AK) tma::load_2d(sa, &mapA, full, 2 * k0, m0);
+                else
+#pragma unroll
+                    for (int j = 0; j < ZBM / 8; ++j) tma::load_2d(sa + j * 1024, &mapA, full, 2 * (m0 + 8 * j), k0);
+                if (BKM) tma::load_2d(sb, &mapB, full, 2 * k0, n0);
+                else
+#pragma unroll
+                    for (int j = 0; j < ZBN / 8; ++j) tma::load_2d(sb + j * 1024, &mapB, full, 2 * (n0 + 8 * j), k0);
+            }
+        }
+        return;
+    }
+
+    const int g = lane >> 2, t = lane & 3;
+    const int wm = warp >> 1, wn = warp & 1;          // 4 x 2 warps, warp tile 32 x 32 complex
+    uint32_t offA[2], offB[2];
+#pragma unroll
+    for (int s = 0; s < 2; ++s) {
+        const int kk = 2 * t + s;
+        const uint32_t kmaj = g * 128 + (((kk ^ g) & 7) << 4);
+        const uint32_t mnmaj = kk * 128 + (((g ^ kk) & 7) << 4);
+        offA[s] = (uint32_t)(wm * 4 * 1024) + (AK ? kmaj : mnmaj);
+        offB[s] = ZA_BYTES + (uint32_t)(wn * 4 * 1024) + (BKM ? kmaj : mnmaj);
+    }
+
+    double cr[4][4][2], ci[4][4][2];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) cr[i][j][0] = cr[i][j][1] = ci[i][j][0] = ci[i][j][1] = 0.0;
+
+    for (int kb = 0; kb < kblocks; ++kb) {
+        const int s = kb % ZSTAGES;
+        const uint32_t stage = smem_base + s * ZSTAGE_BYTES;
+        tma::mbar_wait(bar_base + 8 * s, (kb / ZSTAGES) & 1);
+        double2 a[2][4], b[2][4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) a[0][i] = lds128(stage + offA[0] + i * 1024);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) b[0][j] = lds128(stage + offB[0] + j * 1024);
+#pragma unroll
+        for (int st = 0; st < 2; ++st) {
+            if (st == 0) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) a[1][i] = lds128(stage + offA[1] + i * 1024);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) b[1][j] = lds128(stage + offB[1] + j * 1024);
+            }
+            double ai[4], nai[4], bi[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {       // ai = Im(op A), nai = -Im(op A): one sign flip either way
+                ai[i] = CONJA ? flip(a[st][i].y) : a[st][i].y;
+                nai[i] = CONJA ? a[st][i].y : flip(a[st][i].y);
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) bi[j] = CONJB ? flip(b[st][j].y) : b[st][j].y;
+            // four passes over the 4 x 4 tile grid: 16 independent DMMAs between dependent ones
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) dmma(cr[i][j][0], cr[i][j][1], a[st][i].x, b[st][j].x);
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) dmma(ci[i][j][0], ci[i][j][1], a[st][i].x, bi[j]);
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) dmma(cr[i][j][0], cr[i][j][1], nai[i], bi[j]);
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) dmma(ci[i][j][0], ci[i][j][1], ai[i], b[st][j].x);
+        }
+        __syncwarp();
+        if (lane == 0) tma::mbar_arrive(bar_base + 8 * (ZSTAGES + s));
+    }
+
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int64_t r = m0 + wm * 32 + i * 8 + g;
+        if (r >= p.m) continue;
+        double2 *crow = p.C + r * p.n;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int64_t c = n0 + wn * 32 + j * 8 + 2 * t;
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                if (c + e < p.n) {
+                    const double xr = cr[i][j][e], xi = ci[i][j][e];
+                    crow[c + e] = make_double2(p.alr * xr - p.ali * xi, p.alr * xi + p.ali * xr);
+                }
+            }
+        }
+    }
+}
+
 // ---------------------------------------------------------------------------------
 // host side (real f64)
 // ---------------------------------------------------------------------------------
@@ -220,14 +396,63 @@ int launch_dgemm(const GemmArgs &g)
     return check_launch("dgemm_dmma_kernel");
 }
 
+template <bool AK, bool BKM, bool CA, bool CB>
+int launch_zgemm(const GemmArgs &g)
+{
+    CUtensorMap mapA, mapB;
+    // maps are over doubles (no complex TMA type): a complex row of c columns is 2c doubles
+    if (!tma::make_2d(&mapA, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 8, g.A, (uint64_t)g.rowsA, 2 * (uint64_t)g.colsA,
+                      AK ? ZBM : ZBK, 16) ||
+        !tma::make_2d(&mapB, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 8, g.B, (uint64_t)g.rowsB, 2 * (uint64_t)g.colsB,
+                      BKM ? ZBN : ZBK, 16))
+        return cuda_fail(cudaErrorInvalidValue, "cuTensorMapEncodeTiled");
+    static thread_local bool attr_done = false;
+    if (!attr_done) {
+        ACC_CUDA(cudaFuncSetAttribute(zgemm_dmma_kernel<AK, BKM, CA, CB>, cudaFuncAttributeMaxDynamicSharedMemorySize, ZSMEM_BYTES));
+        attr_done = true;
+    }
+    ZgemmParams p;
+    p.m = g.m; p.n = g.n; p.k = g.k;
+    p.alr = static_cast<const double *>(g.alpha)[0];
+    p.ali = static_cast<const double *>(g.alpha)[1];
+    p.C = static_cast<double2 *>(g.C);
+    p.tiles_m = (int)((g.m + ZBM - 1) / ZBM);
+    p.tiles_n = (int)((g.n + ZBN - 1) / ZBN);
+    const int64_t tiles = (int64_t)p.tiles_m * p.tiles_n;
+    if (tiles > 0x7fffffff) return ACCBLAS_ERR_SHAPE;
+    zgemm_dmma_kernel<AK, BKM, CA, CB><<<(unsigned)tiles, THREADS, ZSMEM_BYTES, g.stream>>>(mapA, mapB, p);
+    return check_launch("zgemm_dmma_kernel");
+}
+
+template <bool AK, bool BKM>
+int zgemm_conj(const GemmArgs &g)
+{
+    // conjugation only ever comes with a transpose (op H): CA implies !AK, CB implies BKM
+    const bool ca = g.opA == ACCBLAS_OP_H, cb = g.opB == ACCBLAS_OP_H;
+    if constexpr (!AK && BKM) {
+        if (ca && cb) return launch_zgemm<AK, BKM, true, true>(g);
+        if (ca) return launch_zgemm<AK, BKM, true, false>(g);
+        if (cb) return launch_zgemm<AK, BKM, false, true>(g);
+    } else if constexpr (!AK) {
+        if (ca) return launch_zgemm<AK, BKM, true, false>(g);
+    } else if constexpr (BKM) {
+        if (cb) return launch_zgemm<AK, BKM, false, true>(g);
+    }
+    return launch_zgemm<AK, BKM, false, false>(g);
+}
+
 }  // namespace
 
 bool dgemm_dmma_eligible(const GemmArgs &g)
 {
-    if (g.dtype != ACCBLAS_F64) return false;                       // c64: see zgemm below (TODO)
+    if (g.dtype != ACCBLAS_F64 && g.dtype != ACCBLAS_C64) return false;
     if (g.m < 1 || g.n < 1 || g.k < 1) return false;
     // TMA: 16-byte aligned base and row pitch
     if (!aligned16(g.A) || !aligned16(g.B) || !aligned16(g.C)) return false;
+    if (g.dtype == ACCBLAS_C64) {
+        if (g.rowsA > 0x3fffffff || g.colsA > 0x3fffffff || g.rowsB > 0x3fffffff || g.colsB > 0x3fffffff) return false;
+        return g.m * g.n >= 32 * 32 && g.k >= 4;
+    }
     if ((g.colsA & 1) || (g.colsB & 1)) return false;
     if (g.rowsA > 0x7fffffff || g.colsA > 0x7fffffff || g.rowsB > 0x7fffffff || g.colsB > 0x7fffffff) return false;
     // tiny products stay on the SIMT kernel: a 128 x 128 tile would be mostly padding
@@ -238,6 +463,12 @@ bool dgemm_dmma_eligible(const GemmArgs &g)
 int dgemm_dmma(const GemmArgs &g)
 {
     const bool ak = g.opA == ACCBLAS_OP_N, bk = g.opB != ACCBLAS_OP_N;
+    if (g.dtype == ACCBLAS_C64) {
+        if (ak && bk) return zgemm_conj<true, true>(g);
+        if (ak && !bk) return zgemm_conj<true, false>(g);
+        if (!ak && bk) return zgemm_conj<false, true>(g);
+        return zgemm_conj<false, false>(g);
+    }
     if (ak && bk) return launch_dgemm<true, true>(g);
     if (ak && !bk) return launch_dgemm<true, false>(g);
     if (!ak && bk) return launch_dgemm<false, true>(g);
