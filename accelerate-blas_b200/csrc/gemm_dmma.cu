@@ -202,6 +202,7 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
 // =====================================================================================
 constexpr int ZBM = 128, ZBN = 64, ZBK = 8;
 constexpr int ZSTAGES = 8;
+constexpr int ZTHREADS = 384;   // 2 consumer warpgroups + 1 producer warpgroup (setmaxnreg is per warpgroup)
 constexpr int ZA_BYTES = ZBM * ZBK * 16, ZB_BYTES = ZBN * ZBK * 16, ZSTAGE_BYTES = ZA_BYTES + ZB_BYTES;
 constexpr int ZSMEM_BYTES = ZSTAGES * ZSTAGE_BYTES + 1024 + 2 * ZSTAGES * 8;
 
@@ -222,7 +223,7 @@ struct ZgemmParams {
 };
 
 template <bool AK, bool BKM, bool CONJA, bool CONJB>
-__global__ void __launch_bounds__(THREADS, 1)
+__global__ void __launch_bounds__(ZTHREADS, 1)
 zgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
                   const ZgemmParams p)
 {
@@ -254,8 +255,10 @@ zgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
     }
     __syncthreads();
 
-    if (warp == CONSUMER_WARPS) {
-        if (lane == 0) {
+    if (warp >= CONSUMER_WARPS) {
+        // producer warpgroup: hand registers to the consumers (168 at launch -> 40 here, 232 there)
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+        if (warp == CONSUMER_WARPS && lane == 0) {
             tma::prefetch_tmap(&mapA);
             tma::prefetch_tmap(&mapB);
             for (int kb = 0; kb < kblocks; ++kb) {
@@ -280,6 +283,7 @@ zgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
         return;
     }
 
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
     const int g = lane >> 2, t = lane & 3;
     const int wm = warp >> 1, wn = warp & 1;          // 4 x 2 warps, warp tile 32 x 32 complex
     uint32_t offA[2], offB[2];
@@ -420,7 +424,7 @@ int launch_zgemm(const GemmArgs &g)
     p.tiles_n = (int)((g.n + ZBN - 1) / ZBN);
     const int64_t tiles = (int64_t)p.tiles_m * p.tiles_n;
     if (tiles > 0x7fffffff) return ACCBLAS_ERR_SHAPE;
-    zgemm_dmma_kernel<AK, BKM, CA, CB><<<(unsigned)tiles, THREADS, ZSMEM_BYTES, g.stream>>>(mapA, mapB, p);
+    zgemm_dmma_kernel<AK, BKM, CA, CB><<<(unsigned)tiles, ZTHREADS, ZSMEM_BYTES, g.stream>>>(mapA, mapB, p);
     return check_launch("zgemm_dmma_kernel");
 }
 
