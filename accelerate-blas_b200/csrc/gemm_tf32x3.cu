@@ -1,7 +1,438 @@
-// placeholder: replaced by the tcgen05 kernel
+// gemm_tf32x3.cu -- FP32 / complex-FP32 GEMM on the 5th-generation tensor cores (tcgen05.mma
+// kind::tf32, accumulators in TMEM) with FP32-class accuracy through a split-precision scheme.
+// Replaces BLAS.sgemm / BLAS.cgemm at LLVM/PTX/Level3.hs:91,101.  The reference's cuBLAS call runs
+// in the default math mode (true FP32), so plain TF32 would not be parity.
+//
+//   a = a_hi + a_lo,  a_hi = rna_tf32(a),  a_lo = rna_tf32(a - a_hi)      (|a - a_hi - a_lo| <= 2^-22 |a|)
+//   a*b ~= a_hi*b_hi + a_hi*b_lo + a_lo*b_hi                               (dropped a_lo*b_lo <= 2^-22 |ab|)
+//
+// three tensor-core products per K-step, all accumulated in one FP32 TMEM accumulator.
+//
+// Two kernels:
+//  1. pack_split: one O(n^2) pass per operand that (a) applies the op -- transposes to K-major,
+//     conjugates -- (b) for complex types writes the REAL embedding
+//         C_real (m x 2n) = A_real (m x 2k) * Bhat (2k x 2n),
+//         Bhat[2l][2j] = br, Bhat[2l+1][2j] = -bi, Bhat[2l][2j+1] = bi, Bhat[2l+1][2j+1] = br
+//     ("4M": 8mnk real flops, result lands directly in interleaved (re,im) layout, no epilogue
+//     pass), and (c) splits every value into its hi / lo TF32 planes.
+//     Output: P_hi, P_lo, each R x Kp row-major with pitch Kp rounded up to 32 floats (K-major for
+//     both operands, so the GEMM kernel has exactly one layout).
+//  2. sgemm_tf32x3_kernel: TMA (128-byte swizzle) -> 3-stage smem ring -> tcgen05.mma issued by one
+//     thread -> TMEM accumulator -> tcgen05.ld epilogue, warp-specialised
+//     (warp 0 TMA producer, warp 1 MMA issuer, warp 2 TMEM allocator, warps 4-7 epilogue).
+//
+// Workspace (stream-ordered, cudaMallocAsync on the caller's stream): 2 * 4 * (R_A + R_B) * Kp bytes.
 #include "common.cuh"
+#include "tma.cuh"
+#include <cstdlib>
+
 namespace accblas {
-bool sgemm_tc_eligible(const GemmArgs &) { return false; }
-int sgemm_tc(const GemmArgs &) { return ACCBLAS_ERR_SHAPE; }
-size_t sgemm_tc_workspace(const GemmArgs &) { return 0; }
+namespace {
+
+// ------------------------------------------------------------------------------------
+// pack_split
+// ------------------------------------------------------------------------------------
+enum PackMode {
+    PK_REAL = 0,    // P[r][c] = X_op[r][c]
+    PK_CPLX_A = 1,  // P[i][2l+p] = part p of A_op[i][l]          (imag * sign for H)
+    PK_CPLX_B = 2   // P[2j+q][2l+p] = Bhat^T                       (see header)
+};
+
+struct PackArgs {
+    const float *src;      // stored matrix (float view: complex = 2 floats per element)
+    int64_t rows, cols;    // stored shape in ELEMENTS
+    int transposed;        // 1: op-index (r,l) lives at stored [l][r];  0: at stored [r][l]
+    float conj_sign;       // +1, or -1 when the op is H on a complex type
+    int64_t R, Kp;         // output extent (floats)
+    int64_t pitch;         // output row pitch (floats), multiple of 32
+    float *hi, *lo;
+};
+
+__device__ __forceinline__ float to_tf32(float x) {
+    uint32_t r;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+    return __uint_as_float(r);
 }
+
+template <int MODE>
+__device__ __forceinline__ float pack_value(const PackArgs &a, int64_t r, int64_t c)
+{
+    if (MODE == PK_REAL) {
+        return a.transposed ? a.src[c * a.cols + r] : a.src[r * a.cols + c];
+    } else if (MODE == PK_CPLX_A) {
+        const int64_t l = c >> 1;
+        const int p = (int)(c & 1);
+        const int64_t e = a.transposed ? l * a.cols + r : r * a.cols + l;
+        const float v = a.src[2 * e + p];
+        return p ? v * a.conj_sign : v;
+    } else {
+        const int64_t j = r >> 1, l = c >> 1;
+        const int q = (int)(r & 1), p = (int)(c & 1);
+        // op(B)[l][j]: stored [l][j] when op = N (not "transposed" w.r.t. k-major view means
+        // stored [j][l]); `transposed` here means the K-major row j is NOT contiguous in memory
+        const int64_t e = a.transposed ? l * a.cols + j : j * a.cols + l;
+        const float br = a.src[2 * e], bi = a.src[2 * e + 1] * a.conj_sign;
+        return q == p ? br : (q == 0 ? -bi : bi);
+    }
+}
+
+// 32 x 32 output tile per 256-thread block.  When the source is contiguous along the output's
+// row index (transposed), the tile goes through shared memory so both sides stay coalesced.
+template <int MODE>
+__global__ void __launch_bounds__(256)
+pack_split_kernel(const PackArgs a)
+{
+    __shared__ float tile[32][33];
+    const int64_t r0 = (int64_t)blockIdx.y * 32, c0 = (int64_t)blockIdx.x * 32;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;    // 32 x 8
+    if (a.transposed) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int cc = ty + 8 * i;                           // fast index tx walks r
+            const int64_t r = r0 + tx, c = c0 + cc;
+            tile[cc][tx] = (r < a.R && c < a.Kp) ? pack_value<MODE>(a, r, c) : 0.f;
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int rr = ty + 8 * i;
+        const int64_t r = r0 + rr, c = c0 + tx;                  // fast index tx walks c
+        if (r >= a.R || c >= a.pitch) continue;
+        float v = 0.f;
+        if (c < a.Kp) v = a.transposed ? tile[tx][rr] : pack_value<MODE>(a, r, c);
+        const float h = to_tf32(v);
+        const float l = to_tf32(v - h);
+        a.hi[r * a.pitch + c] = h;
+        a.lo[r * a.pitch + c] = l;
+    }
+}
+
+int launch_pack(int mode, const PackArgs &a, cudaStream_t st)
+{
+    dim3 grid((unsigned)((a.pitch + 31) / 32), (unsigned)((a.R + 31) / 32));
+    if (grid.y > 65535u) return ACCBLAS_ERR_SHAPE;     // eligibility keeps R below 2^21
+    switch (mode) {
+    case PK_REAL:   pack_split_kernel<PK_REAL><<<grid, 256, 0, st>>>(a); break;
+    case PK_CPLX_A: pack_split_kernel<PK_CPLX_A><<<grid, 256, 0, st>>>(a); break;
+    default:        pack_split_kernel<PK_CPLX_B><<<grid, 256, 0, st>>>(a); break;
+    }
+    return check_launch("pack_split_kernel");
+}
+
+
+// ------------------------------------------------------------------------------------
+// tcgen05 helpers (inline PTX; SASS: UTCHMMA / LDTM / UTCBAR)
+// ------------------------------------------------------------------------------------
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tmem_alloc(uint32_t slot_smem, uint32_t ncols) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(slot_smem), "r"(ncols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+// D[tmem] (+)= A[smem desc] * B[smem desc], kind::tf32, issued by ONE thread
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+// arrive on an mbarrier when all MMAs issued so far by this thread have completed
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
+        "%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+          "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+          "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+          "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+        : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// K-major, 128-byte-swizzled operand tile: rows of 128 bytes, 8-row groups 1024 bytes apart.
+// (cute::UMMA::SmemDescriptor: start>>4 [0,14), LBO>>4 [16,30) = 1, SBO>>4 [32,46) = 64,
+//  version [46,48) = 1, layout_type [61,64) = 2 = SWIZZLE_128B)
+__device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t saddr) {
+    return (uint64_t)((saddr >> 4) & 0x3fffu) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
+}
+// cute::UMMA::InstrDescriptor: c_format F32 (1) [4,6), a/b_format TF32 (2) [7,10) [10,13),
+// a/b K-major (0) [15],[16], N>>3 [17,23), M>>4 [24,29)
+__host__ __device__ constexpr uint32_t idesc_tf32(int M, int N) {
+    return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+// ------------------------------------------------------------------------------------
+// sgemm_tf32x3_kernel: C_real (M x N) = alpha * P_A (M x Kp) * P_B^T (N x Kp), both K-major
+// ------------------------------------------------------------------------------------
+constexpr int TBM = 128, TBK = 32;          // 32 floats = one 128-byte swizzle row
+constexpr int TTHREADS = 256;
+
+struct SgemmParams {
+    int64_t M, N;          // real extents of C_real
+    int64_t Kp;            // packed inner extent
+    int64_t ldc;           // floats
+    float *C;
+    float alr, ali;        // alpha (ali = 0 for real)
+    int cplx;              // 1: columns are (re,im) pairs, alpha is complex
+    int tiles_m, tiles_n;
+};
+
+template <int TBN, int STAGES>
+struct TcCfg {
+    static constexpr int A_TILE = TBM * TBK * 4;               // 16 KiB
+    static constexpr int B_TILE = TBN * TBK * 4;
+    static constexpr int STAGE = 2 * A_TILE + 2 * B_TILE;      // hi + lo of both operands
+    static constexpr int BAR_OFF = STAGES * STAGE;
+    static constexpr int SMEM = STAGES * STAGE + 1024 + 256;
+};
+
+template <int TBN, int STAGES>
+__global__ void __launch_bounds__(TTHREADS, 1)
+sgemm_tf32x3_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_constant__ CUtensorMap mapAlo,
+                    const __grid_constant__ CUtensorMap mapBhi, const __grid_constant__ CUtensorMap mapBlo,
+                    const SgemmParams p)
+{
+    using Cfg = TcCfg<TBN, STAGES>;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t smem_base = (tma::smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t bar_full = smem_base + Cfg::BAR_OFF;            // full[STAGES]
+    const uint32_t bar_empty = bar_full + 8 * STAGES;              // empty[STAGES]
+    const uint32_t bar_acc = bar_empty + 8 * STAGES;               // accumulator ready
+    const uint32_t tmem_slot = bar_acc + 8;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    constexpr int GROUP = 8;
+    int tile_m, tile_n;
+    {
+        const int per_group = GROUP * p.tiles_n;
+        const int grp = blockIdx.x / per_group;
+        const int first_m = grp * GROUP;
+        const int gsz = min(p.tiles_m - first_m, GROUP);
+        const int in_grp = blockIdx.x - grp * per_group;
+        tile_m = first_m + in_grp % gsz;
+        tile_n = in_grp / gsz;
+    }
+    const int m0 = tile_m * TBM, n0 = tile_n * TBN;
+    const int kblocks = (int)((p.Kp + TBK - 1) / TBK);
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < STAGES; ++s) {
+            tma::mbar_init(bar_full + 8 * s, 1);
+            tma::mbar_init(bar_empty + 8 * s, 1);
+        }
+        tma::mbar_init(bar_acc, 1);
+        tma::fence_barrier_init();
+    }
+    if (warp == 2) tmem_alloc(tmem_slot, TBN);                     // TBN fp32 columns x 128 lanes
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    uint32_t tmem_base;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+
+    if (warp == 0) {
+        // ================================ TMA producer ================================
+        if (lane == 0) {
+            tma::prefetch_tmap(&mapAhi); tma::prefetch_tmap(&mapAlo);
+            tma::prefetch_tmap(&mapBhi); tma::prefetch_tmap(&mapBlo);
+            for (int kb = 0; kb < kblocks; ++kb) {
+                const int s = kb % STAGES;
+                if (kb >= STAGES) tma::mbar_wait(bar_empty + 8 * s, ((kb / STAGES) - 1) & 1);
+                const uint32_t full = bar_full + 8 * s;
+                const uint32_t st = smem_base + s * Cfg::STAGE;
+                tma::mbar_expect_tx(full, Cfg::STAGE);
+                const int k0 = kb * TBK;
+                tma::load_2d(st, &mapAhi, full, k0, m0);
+                tma::load_2d(st + Cfg::A_TILE, &mapAlo, full, k0, m0);
+                tma::load_2d(st + 2 * Cfg::A_TILE, &mapBhi, full, k0, n0);
+                tma::load_2d(st + 2 * Cfg::A_TILE + Cfg::B_TILE, &mapBlo, full, k0, n0);
+            }
+        }
+    } else if (warp == 1) {
+        // ================================ MMA issuer ================================
+        constexpr uint32_t idesc = idesc_tf32(TBM, TBN);
+        for (int kb = 0; kb < kblocks; ++kb) {
+            const int s = kb % STAGES;
+            tma::mbar_wait(bar_full + 8 * s, (kb / STAGES) & 1);
+            tc_fence_after();
+            if (lane == 0) {
+                const uint32_t st = smem_base + s * Cfg::STAGE;
+                const uint64_t ahi = smem_desc_sw128(st), alo = smem_desc_sw128(st + Cfg::A_TILE);
+                const uint64_t bhi = smem_desc_sw128(st + 2 * Cfg::A_TILE);
+                const uint64_t blo = smem_desc_sw128(st + 2 * Cfg::A_TILE + Cfg::B_TILE);
+#pragma unroll
+                for (int k = 0; k < TBK / 8; ++k) {               // UMMA_K = 8 tf32 = 32 bytes = +2 in the address field
+                    const uint64_t adv = (uint64_t)(2 * k);
+                    umma_tf32(tmem_base, alo + adv, bhi + adv, idesc, (kb | k) != 0);   // small terms first
+                    umma_tf32(tmem_base, ahi + adv, blo + adv, idesc, 1);
+                    umma_tf32(tmem_base, ahi + adv, bhi + adv, idesc, 1);
+                }
+                umma_commit(bar_empty + 8 * s);                    // stage reusable once these MMAs retire
+                if (kb == kblocks - 1) umma_commit(bar_acc);       // accumulator complete
+            }
+            __syncwarp();
+        }
+    } else if (warp >= 4) {
+        // ================================ epilogue ================================
+        tma::mbar_wait(bar_acc, 0);
+        tc_fence_after();
+        const int q = warp & 3;                                    // TMEM lane quadrant of this warp
+        const int64_t row = m0 + q * 32 + lane;
+        const bool vec4 = (p.ldc & 3) == 0 && ((reinterpret_cast<uintptr_t>(p.C) & 15u) == 0);
+#pragma unroll 1
+        for (int c0 = 0; c0 < TBN; c0 += 32) {
+            uint32_t v[32];
+            tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, v);
+            tmem_ld_wait();
+            if (row < p.M) {
+                float *crow = p.C + row * p.ldc;
+                const int64_t col0 = n0 + c0;
+                float o[32];
+                if (p.cplx) {
+#pragma unroll
+                    for (int e = 0; e < 32; e += 2) {
+                        const float xr = __uint_as_float(v[e]), xi = __uint_as_float(v[e + 1]);
+                        o[e] = p.alr * xr - p.ali * xi;
+                        o[e + 1] = p.alr * xi + p.ali * xr;
+                    }
+                } else {
+#pragma unroll
+                    for (int e = 0; e < 32; ++e) o[e] = p.alr * __uint_as_float(v[e]);
+                }
+                if (vec4 && col0 + 32 <= p.N) {
+#pragma unroll
+                    for (int e = 0; e < 32; e += 4)
+                        *reinterpret_cast<float4 *>(crow + col0 + e) = make_float4(o[e], o[e + 1], o[e + 2], o[e + 3]);
+                } else {
+#pragma unroll
+                    for (int e = 0; e < 32; ++e)
+                        if (col0 + e < p.N) crow[col0 + e] = o[e];
+                }
+            }
+        }
+        tc_fence_before();
+    }
+    __syncthreads();
+    if (warp == 2) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, TBN);
+    }
+}
+
+// ------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------
+struct TcPlan {
+    int64_t RA, RB, Kp, pitch;     // packed extents (floats)
+    int64_t M, N;                  // C_real extents
+    size_t plane_a, plane_b;       // bytes of one hi (or lo) plane
+};
+
+TcPlan make_plan(const GemmArgs &g)
+{
+    TcPlan t;
+    const bool cx = g.dtype == ACCBLAS_C32;
+    t.RA = g.m;
+    t.RB = cx ? 2 * g.n : g.n;
+    t.Kp = cx ? 2 * g.k : g.k;
+    t.pitch = (t.Kp + 31) / 32 * 32;
+    t.M = g.m;
+    t.N = t.RB;
+    t.plane_a = ((size_t)t.RA * (size_t)t.pitch * 4 + 1023) / 1024 * 1024;
+    t.plane_b = ((size_t)t.RB * (size_t)t.pitch * 4 + 1023) / 1024 * 1024;
+    return t;
+}
+
+template <int TBN, int STAGES>
+int launch_tc(const GemmArgs &g, const TcPlan &t, float *ahi, float *alo, float *bhi, float *blo)
+{
+    using Cfg = TcCfg<TBN, STAGES>;
+    CUtensorMap mAhi, mAlo, mBhi, mBlo;
+    const uint64_t pitch_b = (uint64_t)t.pitch * 4;
+    const CUtensorMapDataType F = CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
+    if (!tma::make_2d(&mAhi, F, 4, ahi, (uint64_t)t.RA, (uint64_t)t.pitch, TBM, TBK, pitch_b) ||
+        !tma::make_2d(&mAlo, F, 4, alo, (uint64_t)t.RA, (uint64_t)t.pitch, TBM, TBK, pitch_b) ||
+        !tma::make_2d(&mBhi, F, 4, bhi, (uint64_t)t.RB, (uint64_t)t.pitch, TBN, TBK, pitch_b) ||
+        !tma::make_2d(&mBlo, F, 4, blo, (uint64_t)t.RB, (uint64_t)t.pitch, TBN, TBK, pitch_b))
+        return cuda_fail(cudaErrorInvalidValue, "cuTensorMapEncodeTiled");
+    static thread_local bool attr_done = false;
+    if (!attr_done) {
+        ACC_CUDA(cudaFuncSetAttribute(sgemm_tf32x3_kernel<TBN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM));
+        attr_done = true;
+    }
+    SgemmParams p;
+    p.M = t.M; p.N = t.N; p.Kp = t.pitch;      // padding columns are zero-filled by pack_split
+    p.ldc = t.N;
+    p.C = static_cast<float *>(g.C);
+    p.alr = static_cast<const float *>(g.alpha)[0];
+    p.cplx = g.dtype == ACCBLAS_C32;
+    p.ali = p.cplx ? static_cast<const float *>(g.alpha)[1] : 0.f;
+    p.tiles_m = (int)((t.M + TBM - 1) / TBM);
+    p.tiles_n = (int)((t.N + TBN - 1) / TBN);
+    const int64_t tiles = (int64_t)p.tiles_m * p.tiles_n;
+    if (tiles > 0x7fffffff) return ACCBLAS_ERR_SHAPE;
+    sgemm_tf32x3_kernel<TBN, STAGES><<<(unsigned)tiles, TTHREADS, Cfg::SMEM, g.stream>>>(mAhi, mAlo, mBhi, mBlo, p);
+    return check_launch("sgemm_tf32x3_kernel");
+}
+
+}  // namespace
+
+bool sgemm_tc_eligible(const GemmArgs &g)
+{
+    if (g.dtype != ACCBLAS_F32 && g.dtype != ACCBLAS_C32) return false;
+    if (g.m < 1 || g.n < 1 || g.k < 1) return false;
+    const TcPlan t = make_plan(g);
+    if (t.RA > 2000000 || t.RB > 2000000 || t.Kp > 0x7fffffff) return false;
+    // the pack pass and its workspace only pay off once the product is large enough
+    if (t.M < 64 || t.N < 64 || t.Kp < 32) return false;
+    if ((double)t.M * (double)t.N * (double)t.Kp < 16.0 * 1024 * 1024) return false;
+    return true;
+}
+
+size_t sgemm_tc_workspace(const GemmArgs &g)
+{
+    const TcPlan t = make_plan(g);
+    return 2 * (t.plane_a + t.plane_b);
+}
+
+int sgemm_tc(const GemmArgs &g)
+{
+    const TcPlan t = make_plan(g);
+    const bool cx = g.dtype == ACCBLAS_C32;
+    char *ws = nullptr;
+    ACC_CUDA(cudaMallocAsync(reinterpret_cast<void **>(&ws), 2 * (t.plane_a + t.plane_b), g.stream));
+    float *ahi = reinterpret_cast<float *>(ws), *alo = reinterpret_cast<float *>(ws + t.plane_a);
+    float *bhi = reinterpret_cast<float *>(ws + 2 * t.plane_a), *blo = reinterpret_cast<float *>(ws + 2 * t.plane_a + t.plane_b);
+
+    PackArgs pa{};
+    pa.src = static_cast<const float *>(g.A); pa.rows = g.rowsA; pa.cols = g.colsA;
+    pa.transposed = g.opA != ACCBLAS_OP_N;                 // op(A)[i][l] lives at stored [l][i]
+    pa.conj_sign = (cx && g.opA == ACCBLAS_OP_H) ? -1.f : 1.f;
+    pa.R = t.RA; pa.Kp = t.Kp; pa.pitch = t.pitch; pa.hi = ahi; pa.lo = alo;
+    PackArgs pb{};
+    pb.src = static_cast<const float *>(g.B); pb.rows = g.rowsB; pb.cols = g.colsB;
+    pb.transposed = g.opB == ACCBLAS_OP_N;                 // K-major row j of op(B)^T is a stored COLUMN when op = N
+    pb.conj_sign = (cx && g.opB == ACCBLAS_OP_H) ? -1.f : 1.f;
+    pb.R = t.RB; pb.Kp = t.Kp; pb.pitch = t.pitch; pb.hi = bhi; pb.lo = blo;
+
+    int s = launch_pack(cx ? PK_CPLX_A : PK_REAL, pa, g.stream);
+    if (s == ACCBLAS_OK) s = launch_pack(cx ? PK_CPLX_B : PK_REAL, pb, g.stream);
+    if (s == ACCBLAS_OK) {
+        static const int tbn = [] { const char *e = getenv("ACCBLAS_TC_TBN"); return e ? atoi(e) : 128; }();
+        s = tbn == 256 ? launch_tc<256, 2>(g, t, ahi, alo, bhi, blo) : launch_tc<128, 3>(g, t, ahi, alo, bhi, blo);
+    }
+    cudaError_t e = cudaFreeAsync(ws, g.stream);
+    if (s == ACCBLAS_OK && e != cudaSuccess) return cuda_fail(e, "cudaFreeAsync");
+    return s;
+}
+
+}  // namespace accblas

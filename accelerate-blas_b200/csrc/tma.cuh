@@ -36,8 +36,13 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
         : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
     return ok != 0;
 }
+// Spin on try_wait (each probe already suspends the thread for a hardware time slice).  A wait that
+// has not completed after ~2^26 probes is a protocol bug: trap instead of hanging the GPU.
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-    while (!mbar_try_wait(bar, parity)) { }
+    uint32_t spins = 0;
+    while (!mbar_try_wait(bar, parity)) {
+        if (++spins > (1u << 26)) __trap();
+    }
 }
 __device__ __forceinline__ void prefetch_tmap(const void *tmap) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(tmap) : "memory");
@@ -75,12 +80,12 @@ inline EncodeTiledFn encode_fn()
 // outside the matrix.  Requires: base 16-byte aligned, cols * esize % 16 == 0,
 // box_cols * esize <= 128.
 inline bool make_2d(CUtensorMap *map, CUtensorMapDataType dt, size_t esize, const void *base, uint64_t rows,
-                    uint64_t cols, uint32_t box_rows, uint32_t box_cols)
+                    uint64_t cols, uint32_t box_rows, uint32_t box_cols, uint64_t pitch_bytes = 0)
 {
     EncodeTiledFn fn = encode_fn();
     if (!fn) return false;
     cuuint64_t dims[2] = {cols, rows};
-    cuuint64_t strides[1] = {cols * esize};
+    cuuint64_t strides[1] = {pitch_bytes ? pitch_bytes : cols * esize};
     cuuint32_t box[2] = {box_cols, box_rows};
     cuuint32_t estr[2] = {1, 1};
     return fn(map, dt, 2, const_cast<void *>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
