@@ -172,9 +172,18 @@ __host__ __device__ constexpr uint32_t idesc_tf32(int M, int N) {
 
 // ------------------------------------------------------------------------------------
 // sgemm_tf32x3_kernel: C_real (M x N) = alpha * P_A (M x Kp) * P_B^T (N x Kp), both K-major
+//
+// Accuracy note.  The tensor core adds each K = 8 product group into the FP32 TMEM accumulator
+// with truncation, so a long accumulation chain drifts (measured: ~k/8 * 3 * ulp(acc)/2, i.e.
+// 1.6e-3 absolute at k = 2048 -- far inside the normwise tolerance but ~50x a true FP32 sum).
+// The chain is therefore cut every KCB K-blocks ("promotion"): the MMA warp alternates between
+// two TMEM accumulators, starting each chunk from zero, and the eight epilogue warps drain the
+// finished chunk with tcgen05.ld and add it into FP32 REGISTER accumulators with round-to-nearest
+// FADDs while the next chunk is being multiplied.  Error then scales like a blocked FP32 sum.
 // ------------------------------------------------------------------------------------
 constexpr int TBM = 128, TBK = 32;          // 32 floats = one 128-byte swizzle row
-constexpr int TTHREADS = 256;
+constexpr int TTHREADS = 384;               // warps 0-3 control warpgroup, warps 4-11 epilogue
+constexpr int EPI_WARPS = 8;
 
 struct SgemmParams {
     int64_t M, N;          // real extents of C_real
@@ -195,19 +204,21 @@ struct TcCfg {
     static constexpr int SMEM = STAGES * STAGE + 1024 + 256;
 };
 
-template <int TBN, int STAGES>
+template <int TBN, int STAGES, int KCB>
 __global__ void __launch_bounds__(TTHREADS, 1)
 sgemm_tf32x3_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_constant__ CUtensorMap mapAlo,
                     const __grid_constant__ CUtensorMap mapBhi, const __grid_constant__ CUtensorMap mapBlo,
                     const SgemmParams p)
 {
     using Cfg = TcCfg<TBN, STAGES>;
+    constexpr int HALF = TBN / 2;                                  // columns per epilogue warp
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem_base = (tma::smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t bar_full = smem_base + Cfg::BAR_OFF;            // full[STAGES]
     const uint32_t bar_empty = bar_full + 8 * STAGES;              // empty[STAGES]
-    const uint32_t bar_acc = bar_empty + 8 * STAGES;               // accumulator ready
-    const uint32_t tmem_slot = bar_acc + 8;
+    const uint32_t bar_accf = bar_empty + 8 * STAGES;              // acc_full[2]  (MMA -> epilogue)
+    const uint32_t bar_acce = bar_accf + 16;                       // acc_empty[2] (epilogue -> MMA)
+    const uint32_t tmem_slot = bar_acce + 16;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
     constexpr int GROUP = 8;
@@ -223,25 +234,30 @@ sgemm_tf32x3_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_con
     }
     const int m0 = tile_m * TBM, n0 = tile_n * TBN;
     const int kblocks = (int)((p.Kp + TBK - 1) / TBK);
+    const int chunks = (kblocks + KCB - 1) / KCB;
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < STAGES; ++s) {
             tma::mbar_init(bar_full + 8 * s, 1);
             tma::mbar_init(bar_empty + 8 * s, 1);
         }
-        tma::mbar_init(bar_acc, 1);
+        for (int b = 0; b < 2; ++b) {
+            tma::mbar_init(bar_accf + 8 * b, 1);
+            tma::mbar_init(bar_acce + 8 * b, EPI_WARPS);
+        }
         tma::fence_barrier_init();
     }
-    if (warp == 2) tmem_alloc(tmem_slot, TBN);                     // TBN fp32 columns x 128 lanes
+    if (warp == 2) tmem_alloc(tmem_slot, 2 * TBN);                 // two accumulators of TBN fp32 columns
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     uint32_t tmem_base;
     asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
 
-    if (warp == 0) {
-        // ================================ TMA producer ================================
-        if (lane == 0) {
+    if (warp < 4) {
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+        if (warp == 0 && lane == 0) {
+            // ================================ TMA producer ================================
             tma::prefetch_tmap(&mapAhi); tma::prefetch_tmap(&mapAlo);
             tma::prefetch_tmap(&mapBhi); tma::prefetch_tmap(&mapBlo);
             for (int kb = 0; kb < kblocks; ++kb) {
@@ -256,75 +272,106 @@ sgemm_tf32x3_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_con
                 tma::load_2d(st + 2 * Cfg::A_TILE, &mapBhi, full, k0, n0);
                 tma::load_2d(st + 2 * Cfg::A_TILE + Cfg::B_TILE, &mapBlo, full, k0, n0);
             }
-        }
-    } else if (warp == 1) {
-        // ================================ MMA issuer ================================
-        constexpr uint32_t idesc = idesc_tf32(TBM, TBN);
-        for (int kb = 0; kb < kblocks; ++kb) {
-            const int s = kb % STAGES;
-            tma::mbar_wait(bar_full + 8 * s, (kb / STAGES) & 1);
-            tc_fence_after();
-            if (lane == 0) {
-                const uint32_t st = smem_base + s * Cfg::STAGE;
-                const uint64_t ahi = smem_desc_sw128(st), alo = smem_desc_sw128(st + Cfg::A_TILE);
-                const uint64_t bhi = smem_desc_sw128(st + 2 * Cfg::A_TILE);
-                const uint64_t blo = smem_desc_sw128(st + 2 * Cfg::A_TILE + Cfg::B_TILE);
-#pragma unroll
-                for (int k = 0; k < TBK / 8; ++k) {               // UMMA_K = 8 tf32 = 32 bytes = +2 in the address field
-                    const uint64_t adv = (uint64_t)(2 * k);
-                    umma_tf32(tmem_base, alo + adv, bhi + adv, idesc, (kb | k) != 0);   // small terms first
-                    umma_tf32(tmem_base, ahi + adv, blo + adv, idesc, 1);
-                    umma_tf32(tmem_base, ahi + adv, bhi + adv, idesc, 1);
+        } else if (warp == 1) {
+            // ================================ MMA issuer ================================
+            constexpr uint32_t idesc = idesc_tf32(TBM, TBN);
+            int kb = 0;
+            for (int c = 0; c < chunks; ++c) {
+                const int b = c & 1;
+                if (c >= 2) {                                       // accumulator b drained by the epilogue?
+                    tma::mbar_wait(bar_acce + 8 * b, ((c >> 1) - 1) & 1);
+                    tc_fence_after();
                 }
-                umma_commit(bar_empty + 8 * s);                    // stage reusable once these MMAs retire
-                if (kb == kblocks - 1) umma_commit(bar_acc);       // accumulator complete
-            }
-            __syncwarp();
-        }
-    } else if (warp >= 4) {
-        // ================================ epilogue ================================
-        tma::mbar_wait(bar_acc, 0);
-        tc_fence_after();
-        const int q = warp & 3;                                    // TMEM lane quadrant of this warp
-        const int64_t row = m0 + q * 32 + lane;
-        const bool vec4 = (p.ldc & 3) == 0 && ((reinterpret_cast<uintptr_t>(p.C) & 15u) == 0);
-#pragma unroll 1
-        for (int c0 = 0; c0 < TBN; c0 += 32) {
-            uint32_t v[32];
-            tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, v);
-            tmem_ld_wait();
-            if (row < p.M) {
-                float *crow = p.C + row * p.ldc;
-                const int64_t col0 = n0 + c0;
-                float o[32];
-                if (p.cplx) {
+                const uint32_t tacc = tmem_base + (uint32_t)(b * TBN);
+                const int kend = min(kb + KCB, kblocks);
+                for (int first = 1; kb < kend; ++kb) {
+                    const int s = kb % STAGES;
+                    tma::mbar_wait(bar_full + 8 * s, (kb / STAGES) & 1);
+                    tc_fence_after();
+                    if (lane == 0) {
+                        const uint32_t st = smem_base + s * Cfg::STAGE;
+                        const uint64_t ahi = smem_desc_sw128(st), alo = smem_desc_sw128(st + Cfg::A_TILE);
+                        const uint64_t bhi = smem_desc_sw128(st + 2 * Cfg::A_TILE);
+                        const uint64_t blo = smem_desc_sw128(st + 2 * Cfg::A_TILE + Cfg::B_TILE);
 #pragma unroll
-                    for (int e = 0; e < 32; e += 2) {
-                        const float xr = __uint_as_float(v[e]), xi = __uint_as_float(v[e + 1]);
-                        o[e] = p.alr * xr - p.ali * xi;
-                        o[e + 1] = p.alr * xi + p.ali * xr;
+                        for (int k = 0; k < TBK / 8; ++k) {       // UMMA_K = 8 tf32 = 32 bytes = +2 in the address field
+                            const uint64_t adv = (uint64_t)(2 * k);
+                            umma_tf32(tacc, alo + adv, bhi + adv, idesc, (first && k == 0) ? 0u : 1u);
+                            umma_tf32(tacc, ahi + adv, blo + adv, idesc, 1);
+                            umma_tf32(tacc, ahi + adv, bhi + adv, idesc, 1);
+                        }
+                        umma_commit(bar_empty + 8 * s);            // stage reusable once these MMAs retire
                     }
-                } else {
-#pragma unroll
-                    for (int e = 0; e < 32; ++e) o[e] = p.alr * __uint_as_float(v[e]);
+                    first = 0;
+                    __syncwarp();
                 }
-                if (vec4 && col0 + 32 <= p.N) {
-#pragma unroll
-                    for (int e = 0; e < 32; e += 4)
-                        *reinterpret_cast<float4 *>(crow + col0 + e) = make_float4(o[e], o[e + 1], o[e + 2], o[e + 3]);
-                } else {
-#pragma unroll
-                    for (int e = 0; e < 32; ++e)
-                        if (col0 + e < p.N) crow[col0 + e] = o[e];
-                }
+                if (lane == 0) umma_commit(bar_accf + 8 * b);      // chunk accumulator complete
+                __syncwarp();
             }
         }
-        tc_fence_before();
+    } else {
+        // ================================ promotion + epilogue ================================
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
+        const int e = warp - 4;
+        const int q = e & 3;                                       // TMEM lane quadrant (warp id % 4)
+        const int h = e >> 2;                                      // column half
+        float acc[HALF];
+#pragma unroll
+        for (int i = 0; i < HALF; ++i) acc[i] = 0.f;
+        for (int c = 0; c < chunks; ++c) {
+            const int b = c & 1;
+            tma::mbar_wait(bar_accf + 8 * b, (c >> 1) & 1);
+            tc_fence_after();
+            const uint32_t t0 = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(b * TBN + h * HALF);
+#pragma unroll
+            for (int c0 = 0; c0 < HALF; c0 += 64) {
+                uint32_t v0[32], v1[32];
+                tmem_ld32(t0 + c0, v0);
+                tmem_ld32(t0 + c0 + 32, v1);
+                tmem_ld_wait();
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                    acc[c0 + i] += __uint_as_float(v0[i]);
+                    acc[c0 + 32 + i] += __uint_as_float(v1[i]);
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) tma::mbar_arrive(bar_acce + 8 * b);
+        }
+        // ---- C = alpha * acc ----
+        const int64_t row = m0 + q * 32 + lane;
+        if (row < p.M) {
+            float *crow = p.C + row * p.ldc;
+            const int64_t col0 = n0 + h * HALF;
+            const bool vec4 = (p.ldc & 3) == 0 && ((reinterpret_cast<uintptr_t>(p.C) & 15u) == 0) && col0 + HALF <= p.N;
+            if (p.cplx) {
+#pragma unroll
+                for (int i = 0; i < HALF; i += 2) {
+                    const float xr = acc[i], xi = acc[i + 1];
+                    acc[i] = p.alr * xr - p.ali * xi;
+                    acc[i + 1] = p.alr * xi + p.ali * xr;
+                }
+            } else {
+#pragma unroll
+                for (int i = 0; i < HALF; ++i) acc[i] *= p.alr;
+            }
+            if (vec4) {
+#pragma unroll
+                for (int i = 0; i < HALF; i += 4)
+                    *reinterpret_cast<float4 *>(crow + col0 + i) = make_float4(acc[i], acc[i + 1], acc[i + 2], acc[i + 3]);
+            } else {
+#pragma unroll
+                for (int i = 0; i < HALF; ++i)
+                    if (col0 + i < p.N) crow[col0 + i] = acc[i];
+            }
+        }
     }
+    tc_fence_before();
     __syncthreads();
     if (warp == 2) {
         tc_fence_after();
-        tmem_dealloc(tmem_base, TBN);
+        tmem_dealloc(tmem_base, 2 * TBN);
     }
 }
 
@@ -352,7 +399,7 @@ TcPlan make_plan(const GemmArgs &g)
     return t;
 }
 
-template <int TBN, int STAGES>
+template <int TBN, int STAGES, int KCB>
 int launch_tc(const GemmArgs &g, const TcPlan &t, float *ahi, float *alo, float *bhi, float *blo)
 {
     using Cfg = TcCfg<TBN, STAGES>;
@@ -366,7 +413,7 @@ int launch_tc(const GemmArgs &g, const TcPlan &t, float *ahi, float *alo, float 
         return cuda_fail(cudaErrorInvalidValue, "cuTensorMapEncodeTiled");
     static thread_local bool attr_done = false;
     if (!attr_done) {
-        ACC_CUDA(cudaFuncSetAttribute(sgemm_tf32x3_kernel<TBN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM));
+        ACC_CUDA(cudaFuncSetAttribute(sgemm_tf32x3_kernel<TBN, STAGES, KCB>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM));
         attr_done = true;
     }
     SgemmParams p;
@@ -380,7 +427,7 @@ int launch_tc(const GemmArgs &g, const TcPlan &t, float *ahi, float *alo, float 
     p.tiles_n = (int)((t.N + TBN - 1) / TBN);
     const int64_t tiles = (int64_t)p.tiles_m * p.tiles_n;
     if (tiles > 0x7fffffff) return ACCBLAS_ERR_SHAPE;
-    sgemm_tf32x3_kernel<TBN, STAGES><<<(unsigned)tiles, TTHREADS, Cfg::SMEM, g.stream>>>(mAhi, mAlo, mBhi, mBlo, p);
+    sgemm_tf32x3_kernel<TBN, STAGES, KCB><<<(unsigned)tiles, TTHREADS, Cfg::SMEM, g.stream>>>(mAhi, mAlo, mBhi, mBlo, p);
     return check_launch("sgemm_tf32x3_kernel");
 }
 
@@ -427,8 +474,11 @@ int sgemm_tc(const GemmArgs &g)
     int s = launch_pack(cx ? PK_CPLX_A : PK_REAL, pa, g.stream);
     if (s == ACCBLAS_OK) s = launch_pack(cx ? PK_CPLX_B : PK_REAL, pb, g.stream);
     if (s == ACCBLAS_OK) {
-        static const int tbn = [] { const char *e = getenv("ACCBLAS_TC_TBN"); return e ? atoi(e) : 128; }();
-        s = tbn == 256 ? launch_tc<256, 2>(g, t, ahi, alo, bhi, blo) : launch_tc<128, 3>(g, t, ahi, alo, bhi, blo);
+        static const int kcb = [] { const char *e = getenv("ACCBLAS_TC_KCB"); return e ? atoi(e) : 2; }();
+        s = kcb == 1 ? launch_tc<256, 2, 1>(g, t, ahi, alo, bhi, blo)
+          : kcb == 4 ? launch_tc<256, 2, 4>(g, t, ahi, alo, bhi, blo)
+          : kcb >= 1000 ? launch_tc<256, 2, 1 << 30>(g, t, ahi, alo, bhi, blo)
+                     : launch_tc<256, 2, 2>(g, t, ahi, alo, bhi, blo);
     }
     cudaError_t e = cudaFreeAsync(ws, g.stream);
     if (s == ACCBLAS_OK && e != cudaSuccess) return cuda_fail(e, "cudaFreeAsync");

@@ -44,5 +44,6 @@ def gemv_inputs(rng, dt, oa, m, n):
 
 # Stated tolerances (DESIGN.md "Parity"): normwise error in units of k * eps * |alpha| * ||A||_F * ||B||_F
 TOL_UNITS = {O.F32: 1.0, O.F64: 1.0, O.C32: 2.0, O.C64: 2.0}
-# the tcgen05 3xTF32 path carries a 2^-22 operand-split error per product on top of fp32 accumulation
-TOL_UNITS_TF32X3 = 4.0
+# the tcgen05 3xTF32 path carries a 2^-22 operand-split error per product; with the chunked FP32
+# promotion of the accumulator it measures 1e-4 .. 3e-4 units, so it gets the same bound as complex
+TOL_UNITS_TF32X3 = 2.0

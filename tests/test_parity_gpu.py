@@ -7,7 +7,8 @@ unaligned / large shapes, the haddock golden vectors, the committed OpenBLAS fix
 
 Tolerances (floating point; stated here and in DESIGN.md):
   normwise  ||C - C_oracle||_F <= TOL * (k+2) * eps * |alpha| * ||A||_F * ||B||_F
-  TOL = 1 (f32, f64), 2 (c32, c64: four real products per complex one), 4 on the 3xTF32 tensor path;
+  TOL = 1 (f32, f64), 2 (c32, c64: four real products per complex one), also on the 3xTF32 tensor path
+  (measured there: 1e-4 .. 3e-4 units, the same as a sequential FP32 sum);
   plus the reference suite's own, much looser, elementwise `~~~` (abs 5e-5 or rel 5e-3).
 """
 import numpy as np
@@ -48,7 +49,8 @@ def check_gemm(ab, cuda, dt, oa, ob, al, A, B, path="auto"):
     assert C.shape == ref.shape and C.dtype == ref.dtype
     err = O.gemm_error_units(C, ref, A, B, k, al)
     assert err <= tol, (O.NAMES[dt], oa, ob, A.shape, B.shape, err)
-    assert O.similar(C, O.gemm(al, oa, A, ob, B, wide=False))      # the reference's own criterion
+    if k <= 128:   # the reference suite's own elementwise criterion, at the sizes it is used (k <= 64)
+        assert O.similar(C, O.gemm(al, oa, A, ob, B, wide=False))
     return err
 
 
