@@ -1,0 +1,73 @@
+{-# LANGUAGE ForeignFunctionInterface #-}
+-- |
+-- Module      : Data.Array.Accelerate.Numeric.LinearAlgebra.LLVM.PTX.B200.FFI
+-- Description : raw bindings to libaccblas_b200.so (include/accblas_b200.h)
+--
+-- SOURCE ONLY: the build image has no GHC, so this module has never been compiled.  It shows the
+-- exact binding a maintainer adds; the executable verification of the C ABI runs through the
+-- ctypes mirror (accelerate-blas_b200/python/accblas_b200/_ffi.py).
+--
+-- cabal: add `extra-libraries: accblas_b200` to the llvm-ptx stanza and drop the `cublas`
+-- dependency (accelerate-blas.cabal:74-84).
+--
+module Data.Array.Accelerate.Numeric.LinearAlgebra.LLVM.PTX.B200.FFI (
+
+  DType(..), dtypeCode, opCode, Status, checkStatus,
+  c_accblas_gemm, c_accblas_gemv, c_accblas_dot,
+
+) where
+
+import Data.Array.Accelerate.Numeric.LinearAlgebra.Type            ( Transpose(..) )
+
+import Control.Exception                                            ( throwIO, ErrorCall(..) )
+import Control.Monad                                                ( when )
+import Data.Int                                                     ( Int64 )
+import Foreign.C.String                                             ( CString, peekCString )
+import Foreign.C.Types                                              ( CInt(..) )
+import Foreign.Ptr                                                  ( Ptr )
+
+-- | accblas_dtype_t; one constructor per NumericR constructor (Type.hs:32-36)
+data DType = F32 | F64 | C32 | C64
+
+dtypeCode :: DType -> CInt
+dtypeCode F32 = 0
+dtypeCode F64 = 1
+dtypeCode C32 = 2
+dtypeCode C64 = 3
+
+-- | accblas_op_t (Type.hs:78-90)
+opCode :: Transpose -> CInt
+opCode N = 0
+opCode T = 1
+opCode H = 2
+
+type Status = CInt
+
+-- The CUstream the backend hands out (`asks ptxStream`) is passed as an opaque pointer; device
+-- buffers are the raw addresses behind `DevicePtr` (useDevicePtr).
+foreign import ccall unsafe "accblas_gemm"
+  c_accblas_gemm :: Ptr () -> CInt -> CInt -> CInt          -- stream, dtype, opA, opB
+                 -> Int64 -> Int64 -> Int64 -> Int64        -- rowsA colsA rowsB colsB
+                 -> Ptr () -> Ptr () -> Ptr () -> Ptr ()    -- alpha(host) A B C
+                 -> IO Status
+
+foreign import ccall unsafe "accblas_gemv"
+  c_accblas_gemv :: Ptr () -> CInt -> CInt                  -- stream, dtype, opA
+                 -> Int64 -> Int64                          -- rowsA colsA
+                 -> Ptr () -> Ptr () -> Ptr () -> Int64     -- alpha(host) A x |x|
+                 -> Ptr () -> IO Status                     -- y
+
+foreign import ccall unsafe "accblas_dot"
+  c_accblas_dot  :: Ptr () -> CInt -> CInt -> Int64         -- stream, dtype, conj_x, n
+                 -> Ptr () -> Ptr () -> Ptr ()              -- x y out(device)
+                 -> IO Status
+
+foreign import ccall unsafe "accblas_status_string"
+  c_accblas_status_string :: CInt -> IO CString
+
+-- | The reference surfaces cuBLAS failures as exceptions from the binding; do the same.
+checkStatus :: String -> Status -> IO ()
+checkStatus loc st =
+  when (st /= 0) $ do
+    msg <- peekCString =<< c_accblas_status_string st
+    throwIO (ErrorCall (loc ++ ": " ++ msg))
