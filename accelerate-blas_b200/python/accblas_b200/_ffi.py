@@ -18,7 +18,14 @@ SYMBOLS = (
     "accblas_gemm_host", "accblas_gemv_host", "accblas_dot_host",
     "accblas_version", "accblas_status_string", "accblas_last_cuda_error",
     "accblas_gemm_kernel_name", "accblas_launch_count", "accblas_set_gemm_path",
+    "accblas_peer_export", "accblas_peer_open", "accblas_peer_close_all", "accblas_peer_copy2d",
 )
+
+
+class PeerHandle(ctypes.Structure):
+    """accblas_peer_handle_t"""
+    _fields_ = [("ipc", ctypes.c_ubyte * 64), ("offset", ctypes.c_uint64), ("size", ctypes.c_uint64),
+                ("device", ctypes.c_int32), ("reserved", ctypes.c_int32)]
 
 
 class AccblasError(RuntimeError):
@@ -62,6 +69,12 @@ def lib() -> ctypes.CDLL:
     L.accblas_launch_count.restype = ctypes.c_uint64
     L.accblas_set_gemm_path.argtypes = [ci]
     L.accblas_set_gemm_path.restype = None
+    L.accblas_peer_export.argtypes = [vp, ctypes.POINTER(PeerHandle)]
+    L.accblas_peer_open.argtypes = [ctypes.POINTER(PeerHandle), ctypes.POINTER(vp)]
+    L.accblas_peer_close_all.argtypes = []
+    L.accblas_peer_copy2d.argtypes = [vp, vp, sz, vp, sz, sz, sz]
+    for f in (L.accblas_peer_export, L.accblas_peer_open, L.accblas_peer_close_all, L.accblas_peer_copy2d):
+        f.restype = ci
     _lib = L
     return L
 

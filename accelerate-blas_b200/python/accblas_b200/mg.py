@@ -4,10 +4,11 @@ The reference has no multi-GPU code; this layer is new and its p
 the single-GPU result.  Decomposition (BASELINE.json north_star / configs[4]):
 
   gemm   rows of op(A) and C are split into contiguous panels, one per rank; B is broadcast; C is
-         gathered.  Operands start and the result ends on `root`.  The scatter of A, the local
-         products and the gather of C are pipelined in sub-panels: while sub-panel i multiplies on
-         the compute stream, sub-panel i+1 is arriving and sub-panel i-1 is leaving on the
-         communicator's stream.
+         gathered.  Operands start and the result ends on `root`.  On CUDA the root's A and C are
+         mapped into every rank through CUDA IPC: A panels are pulled by the copy engines and the
+         gemm kernels store their C tiles straight into the root's HBM over NVLink (transport
+         "peer": the gather is the product's own epilogue).  Transport "p2p" (any backend) moves
+         the panels with grouped send/recv, pipelined in sub-panels against the products.
   gemv   op N: rows of A and y are split (A pre-sharded), x broadcast, y all-gathered.
          op T/H: rows of A and x are split, every rank forms a full-length partial y, all-reduce.
   dot    contiguous slices (pre-sharded), all-reduce of one scalar.
@@ -23,15 +24,18 @@ import torch
 import torch.distributed as dist
 
 
-def row_panels(m: int, world: int, align: int = 128) -> List[Tuple[int, int]]:
+def row_panels(m: int, world: int, align: int = 128, root: int = 0, root_bonus: int = 0) -> List[Tuple[int, int]]:
     """Contiguous (start, rows) per rank; panel heights are multiples of `align` (the CTA tile) except
-    possibly the last non-empty one.  Ranks past the end get (m, 0)."""
-    per = -(-m // world)
-    per = -(-per // align) * align
-    out = []
+    possibly the last non-empty one.  Ranks past the end get (m, 0).  `root_bonus` extra rows go to
+    `root`, which can start multiplying while the others still wait for B."""
+    bonus = max(0, min(int(root_bonus), m)) // align * align if world > 1 else 0
+    per = -(-(m - bonus) // world)
+    per = max(-(-per // align) * align, 0)
+    out, s = [], 0
     for r in range(world):
-        s = min(r * per, m)
-        out.append((s, min(per, m - s)))
+        rows = min(per + (bonus if r == root else 0), m - s)
+        out.append((s, rows))
+        s += rows
     return out
 
 
@@ -40,22 +44,55 @@ def _default_gemm():
     return ab.gemm
 
 
+_ES = {torch.float32: 4, torch.float64: 8, torch.complex64: 8, torch.complex128: 16}
+_CODE = {torch.float32: 0, torch.float64: 1, torch.complex64: 2, torch.complex128: 3}
+# planning constants for the root bonus (measured on this pool: profiles/): real flop rate of the local
+# gemm and the rate at which NCCL delivers B to the other ranks
+_FLOPS = {torch.float32: 230e12, torch.float64: 36e12, torch.complex64: 228e12, torch.complex128: 36e12}
+_BCAST_BPS = 450e9
+
+
+def root_bonus_rows(m: int, n: int, k: int, dtype, world: int) -> int:
+    """Rows of head start for the root: what it multiplies while B is still on its way to the others."""
+    if world <= 1 or dtype not in _FLOPS:
+        return 0
+    t_b = _ES[dtype] * k * n / _BCAST_BPS
+    flops_row = (8.0 if dtype.is_complex else 2.0) * n * k
+    rows = t_b * _FLOPS[dtype] / flops_row * (world - 1) / world
+    return int(min(rows, m // (2 * world))) // 128 * 128
+
+
 def gemm_rowsharded(alpha, opA, A: Optional[torch.Tensor], opB, B: Optional[torch.Tensor], *,
                     shapeA: Tuple[int, int], shapeB: Tuple[int, int], dtype: torch.dtype, device,
                     root: int = 0, group=None, subpanels: int = 4,
-                    local_gemm: Optional[Callable] = None, out: Optional[torch.Tensor] = None):
+                    local_gemm: Optional[Callable] = None, out: Optional[torch.Tensor] = None,
+                    transport: str = "auto", root_bonus: Optional[int] = None):
     """C = alpha * op(A) * op(B) with rows of op(A)/C split over the ranks of `group`.
 
     A, B are given on `root` only (None elsewhere); shapeA/shapeB/dtype are known everywhere.
     Returns C on root (written into `out` if given), None on the other ranks.
+
+    transport = "peer" (default on CUDA): the other ranks map the root's A and C through CUDA IPC
+        (accblas_peer_*): A row panels are pulled by the copy engines, and each rank's gemm kernel
+        stores its C tiles directly into the root's HBM over NVLink -- the gather is fused into the
+        product's epilogue.  NCCL carries only the broadcast of B and the completion handshake.
+    transport = "p2p": scatter / gather with grouped send/recv on the communicator, pipelined in
+        sub-panels (works on any backend; this is what the gloo CPU test drives).
     """
-    gemm = local_gemm or _default_gemm()
     rank, world = dist.get_rank(group), dist.get_world_size(group)
     opa = {"N": 0, "T": 1, "H": 2}.get(opA, opA)
     opb = {"N": 0, "T": 1, "H": 2}.get(opB, opB)
     m, k = (shapeA[0], shapeA[1]) if opa == 0 else (shapeA[1], shapeA[0])
     n = shapeB[1] if opb == 0 else shapeB[0]
-    panels = row_panels(m, world)
+    if transport == "auto":
+        transport = "peer" if (torch.device(device).type == "cuda" and local_gemm is None) else "p2p"
+    if transport == "peer":
+        if root_bonus is None:
+            root_bonus = root_bonus_rows(m, n, k, dtype, world)
+        return _gemm_rowsharded_peer(alpha, opa, A, opb, B, shapeA, shapeB, (m, n, k), dtype, device, root, group,
+                                     rank, world, out, root_bonus)
+    gemm = local_gemm or _default_gemm()
+    panels = row_panels(m, world, root=root, root_bonus=root_bonus or 0)
     my_start, my_rows = panels[rank]
 
     # ---- B: broadcast (every rank needs all of it) ----
@@ -94,7 +131,15 @@ def gemm_rowsharded(alpha, opA, A: Optional[torch.Tensor], opB, B: Optional[torc
                     ops.append(dist.P2POp(dist.isend, t, r, group))
             if ops:
                 works += dist.batch_isend_irecv(ops)
-        for i in range(depth):
+        bwork.wait()
+        mine = subs(my_start, my_rows)
+        # The receive of sub-panel i is posted AFTER the root's own i-th product: the communicator's
+        # stream waits for it, so the receive kernel starts when the others are about to deliver
+        # instead of spinning on SMs the root's products need.
+        for i in range(max(depth, len(mine))):
+            if i < len(mine):
+                s, rows = mine[i]
+                gemm(alpha, opa, a_slice(s, rows), opb, B, out=C[s:s + rows])
             ops = []
             for r in remote:
                 if i < len(rsubs[r]):
@@ -102,26 +147,110 @@ def gemm_rowsharded(alpha, opA, A: Optional[torch.Tensor], opB, B: Optional[torc
                     ops.append(dist.P2POp(dist.irecv, C[s:s + rows], r, group))
             if ops:
                 works += dist.batch_isend_irecv(ops)
-        bwork.wait()
-        for (s, rows) in subs(my_start, my_rows):
-            gemm(alpha, opa, a_slice(s, rows), opb, B, out=C[s:s + rows])
         for w in works:
             w.wait()
         return C
 
     mine = subs(my_start, my_rows)
     bufs = [torch.empty(a_shape(rows), dtype=dtype, device=device) for (_, rows) in mine]
-    rworks = [dist.irecv(b, src=root, group=group) for b in bufs]
+    rworks = [dist.batch_isend_irecv([dist.P2POp(dist.irecv, b, root, group)])[0] for b in bufs]
     bwork.wait()
     sends, keep = [], []
     for (s, rows), buf, w in zip(mine, bufs, rworks):
         w.wait()
         c = gemm(alpha, opa, buf, opb, B)
         keep.append(c)
-        sends.append(dist.isend(c, dst=root, group=group))
+        sends += dist.batch_isend_irecv([dist.P2POp(dist.isend, c, root, group)])
     for w in sends:
         w.wait()
     return None
+
+
+def _gemm_rowsharded_peer(alpha, opa, A, opb, B, shapeA, shapeB, mnk, dtype, device, root, group, rank, world,
+                          out, root_bonus):
+    """transport = "peer": IPC-mapped root operands, copy-engine scatter, gather fused into the epilogue."""
+    import ctypes
+    import numpy as np
+    from . import _ffi
+    L = _ffi.lib()
+    m, n, k = mnk
+    es, code = _ES[dtype], _CODE[dtype]
+    device = torch.device(device)
+    panels = row_panels(m, world, root=root, root_bonus=root_bonus)
+    start, rows = panels[rank]
+    hsz = ctypes.sizeof(_ffi.PeerHandle)
+    alpha_buf = np.array([alpha], dtype={0: np.float32, 1: np.float64, 2: np.complex64, 3: np.complex128}[code])
+    al = alpha_buf.ctypes.data_as(ctypes.c_void_p)
+
+    def stream():
+        return ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+    def local_product(a_ptr, a_rows, c_ptr):
+        rA, cA = (a_rows, k) if opa == 0 else (k, a_rows)
+        st = L.accblas_gemm(stream(), code, opa, opb, rA, cA, shapeB[0], shapeB[1], al,
+                            ctypes.c_void_p(a_ptr), ctypes.c_void_p(B.data_ptr()), ctypes.c_void_p(c_ptr))
+        _ffi.check(st, "accblas_gemm (row panel)")
+
+    with torch.cuda.device(device):
+        # ---- handles of the root's A and C: 2 x 88 bytes, every call (the mapping itself is cached) ----
+        if rank == root:
+            if not (A.is_contiguous() and B.is_contiguous()):
+                raise ValueError("gemm_rowsharded: operands must be dense row-major (as Accelerate's are)")
+            C = out if out is not None else torch.empty((m, n), dtype=dtype, device=device)
+            hs = (_ffi.PeerHandle * 2)()
+            for i, t in enumerate((A, C)):
+                st = L.accblas_peer_export(ctypes.c_void_p(t.data_ptr()), ctypes.byref(hs[i]))
+                if st != 0:
+                    raise _ffi.AccblasError(st, "accblas_peer_export",
+                                            "operand is not a cudaMalloc allocation (expandable segments / "
+                                            "cudaMallocAsync backend?): use transport='p2p'")
+            hbuf = torch.frombuffer(bytearray(bytes(hs)), dtype=torch.uint8).to(device)
+        else:
+            hbuf = torch.empty(2 * hsz, dtype=torch.uint8, device=device)
+            B = torch.empty(shapeB, dtype=dtype, device=device)
+        dist.broadcast(hbuf, src=root, group=group)
+        bwork = dist.broadcast(B, src=root, group=group, async_op=True)
+
+        if rank == root:
+            # the root multiplies its own panel while B is still travelling to the others
+            if rows:
+                a_off = start * k * es if opa == 0 else start * es
+                if opa == 0:
+                    local_product(A.data_ptr() + a_off, rows, C.data_ptr() + start * n * es)
+                else:   # column slab of the stored matrix: densify locally (tight leading dimension)
+                    slab = A[:, start:start + rows].contiguous()
+                    local_product(slab.data_ptr(), rows, C.data_ptr() + start * n * es)
+            bwork.wait()
+        else:
+            raw = bytes(hbuf.cpu().numpy().tobytes())
+            hs = (_ffi.PeerHandle * 2).from_buffer_copy(raw)
+            mapped = []
+            for i in range(2):
+                p = ctypes.c_void_p()
+                _ffi.check(L.accblas_peer_open(ctypes.byref(hs[i]), ctypes.byref(p)), "accblas_peer_open")
+                mapped.append(p.value)
+            a_root, c_root = mapped
+            if rows:
+                # scatter: pull this rank's panel of op(A) with the copy engines (overlaps the broadcast)
+                a_loc = torch.empty((rows, k) if opa == 0 else (k, rows), dtype=dtype, device=device)
+                if opa == 0:
+                    st = L.accblas_peer_copy2d(stream(), ctypes.c_void_p(a_loc.data_ptr()), rows * k * es,
+                                               ctypes.c_void_p(a_root + start * k * es), rows * k * es,
+                                               rows * k * es, 1)
+                else:
+                    st = L.accblas_peer_copy2d(stream(), ctypes.c_void_p(a_loc.data_ptr()), rows * es,
+                                               ctypes.c_void_p(a_root + start * es), m * es, rows * es, k)
+                _ffi.check(st, "accblas_peer_copy2d")
+                bwork.wait()
+                # product + gather in one kernel: C tiles are stored into the root's HBM
+                local_product(a_loc.data_ptr(), rows, c_root + start * n * es)
+            else:
+                bwork.wait()
+        # completion handshake, stream ordered on every rank: when it has run on the root, every
+        # peer's kernel (and with it its remote stores) has finished
+        done = torch.zeros(1, dtype=torch.float32, device=device)
+        dist.all_reduce(done, group=group)
+    return C if rank == root else None
 
 
 def gemv_sharded(alpha, opA, A_local: torch.Tensor, x: torch.Tensor, *, group=None,

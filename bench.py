@@ -169,7 +169,8 @@ def workload_config(ngpu):
                 "l2": "inputs (1 GiB) exceed the 126 MB L2; no flush needed"}
     return {"workload": f"Double gemm n={NMG} row-sharded over {ngpu} B200 (BASELINE.json configs[4]); "
                         "A, B start and C ends on rank 0", "m": NMG, "n": NMG, "k": NMG, "opA": "N", "opB": "N",
-            "alpha": 1, "parallelism": f"rows of A/C split {ngpu} ways, B broadcast, C gathered (NCCL)",
+            "alpha": 1, "parallelism": f"rows of A/C split {ngpu} ways; B broadcast (NCCL); A panels pulled by copy engines and C tiles "
+                                    "stored into rank 0's HBM by the gemm epilogue over NVLink (CUDA IPC peer memory)",
             "l2": "inputs (16 GiB) exceed the 126 MB L2; no flush needed"}
 
 
@@ -287,6 +288,10 @@ def run_multi(args):
     local = int(os.environ.get("LOCAL_RANK", rank))
     dev = torch.device(f"cuda:{local}")
     torch.cuda.set_device(dev)
+    # NCCL prints its version banner on stdout; the contract is ONE JSON line there
+    sys.stdout.flush()
+    saved_stdout = os.dup(1)
+    os.dup2(2, 1)
     dist.init_process_group("nccl", device_id=dev)
     n = args.n_mg
     flops = 2.0 * n * n * n
@@ -298,7 +303,7 @@ def run_multi(args):
 
     def step():
         return mg.gemm_rowsharded(1.0, "N", A, "N", B, shapeA=(n, n), shapeB=(n, n), dtype=torch.float64,
-                                  device=dev, root=0, subpanels=args.subpanels, out=C)
+                                  device=dev, root=0, subpanels=args.subpanels, out=C, transport=args.transport)
     for _ in range(args.warmup):
         step()
     torch.cuda.synchronize()
@@ -321,6 +326,20 @@ def run_multi(args):
     launches = torch.tensor([ab.launch_count() - l0], dtype=torch.int64, device=dev)
     dist.all_reduce(launches, op=dist.ReduceOp.SUM)
     total_ms = ms.item()
+    # untimed extra: what the broadcast of B alone costs (explains the gap to N x single-GPU)
+    Bx = B if rank == 0 else torch.empty((n, n), dtype=torch.float64, device=dev)
+    dist.broadcast(Bx, src=0)
+    torch.cuda.synchronize()
+    dist.barrier()
+    torch.cuda.synchronize()
+    b0, b1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    b0.record()
+    dist.broadcast(Bx, src=0)
+    b1.record()
+    torch.cuda.synchronize()
+    bms = torch.tensor([b0.elapsed_time(b1)], dtype=torch.float64, device=dev)
+    dist.all_reduce(bms, op=dist.ReduceOp.MAX)
+    del Bx
     if rank == 0:
         clocks = sampler.stop(t0, t1)
         # parity: 4 rows spread over the rank panels against the oracle
@@ -349,8 +368,13 @@ def run_multi(args):
             "gpu_launches": int(launches.item()), "clocks": clocks,
             "parity": {"error_units": round(err, 5), "tolerance_units": 1.0, "rows_checked": len(rows)},
         }
-        print(json.dumps(line), flush=True)
+        line["config"]["transport"] = args.transport
+        line["broadcast_B_ms"] = round(bms.item(), 3)
     dist.destroy_process_group()
+    sys.stdout.flush()
+    os.dup2(saved_stdout, 1)
+    if rank == 0:
+        print(json.dumps(line), flush=True)
 
 
 def extras():
@@ -385,6 +409,8 @@ def main():
     ap.add_argument("--extras", action="store_true")
     ap.add_argument("--n-mg", type=int, default=NMG, dest="n_mg")
     ap.add_argument("--subpanels", type=int, default=4)
+    ap.add_argument("--transport", default="peer", choices=["peer", "p2p"],
+                    help="multi-GPU data path: IPC peer memory (gather fused into the gemm epilogue) or NCCL send/recv")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     world = int(os.environ.get("WORLD_SIZE", "1"))

@@ -133,6 +133,34 @@ int accblas_dot_host(accblas_stream_t stream, int dtype, int conj_x, int64_t n,
                      const void *x_host, const void *y_host, void *out_host);
 
 /* ------------------------------------------------------------------------------------
+ * Peer memory (one process per GPU, NVLink / NVSwitch).  NEW: the reference has no multi-GPU
+ * path; its only provision is one cuBLAS handle per CUDA context (LLVM/PTX/Context.hs:50-65).
+ * BASELINE.json configs[4] shards gemm by rows of op(A)/C with the operands on a root GPU.
+ * These entry points let a peer rank map the root's arrays, so that
+ *   - the row panel of A is pulled by the copy engines (no SMs on either side), and
+ *   - accblas_gemm is handed a C pointer INSIDE THE ROOT'S HBM: the epilogue's stores are
+ *     the gather (fused, tile by tile, no collective kernel).
+ * The handle is plain bytes: ship it with any transport (torch.distributed, MPI, a pipe).
+ * ---------------------------------------------------------------------------------- */
+typedef struct {
+    unsigned char ipc[64]; /* cudaIpcMemHandle_t of the allocation                      */
+    uint64_t offset;       /* byte offset of the exported pointer inside the allocation */
+    uint64_t size;         /* bytes of the allocation                                   */
+    int32_t device;        /* exporting process's device ordinal (informational)        */
+    int32_t reserved;
+} accblas_peer_handle_t;
+
+/* Describe the cudaMalloc allocation that contains dev_ptr (call in the owning process). */
+int accblas_peer_export(const void *dev_ptr, accblas_peer_handle_t *out);
+/* Map it in another process on the same box; *mapped corresponds to the exporter's dev_ptr.
+ * Mappings are cached per process and stay valid until accblas_peer_close_all(). */
+int accblas_peer_open(const accblas_peer_handle_t *h, void **mapped);
+int accblas_peer_close_all(void);
+/* Pitched device-to-device copy on `stream` (copy engines; either side may be peer-mapped). */
+int accblas_peer_copy2d(accblas_stream_t stream, void *dst, size_t dst_pitch, const void *src,
+                        size_t src_pitch, size_t width_bytes, size_t rows);
+
+/* ------------------------------------------------------------------------------------
  * Introspection / tuning.  None of these change results beyond the stated tolerance.
  * ---------------------------------------------------------------------------------- */
 int accblas_version(void);                     /* ACCBLAS_B200_VERSION */
