@@ -28,12 +28,21 @@
 namespace accblas {
 namespace {
 
-constexpr int BM = 128, BN = 128, BK = 16;
-constexpr int STAGES = 6;
+constexpr int BN = 128, BK = 16;
 constexpr int CONSUMER_WARPS = 8;
 constexpr int THREADS = (CONSUMER_WARPS + 1) * 32;
-constexpr int A_BYTES = BM * BK * 8, B_BYTES = BN * BK * 8, STAGE_BYTES = A_BYTES + B_BYTES;
-constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 2 * STAGES * 8;
+constexpr int B_BYTES = BN * BK * 8;
+// Two CTA tiles: MI = 8 -> 128 x 128 (one CTA per SM, 6 stages), the throughput shape; MI = 4 -> 64 x 128
+// (two CTAs per SM, 4 stages each) for products whose 128 x 128 tiling leaves SMs idle in the last
+// wave (dgemm 1024^3 is 64 big tiles on 148 SMs).  MI = 8-row DMMA tiles per warp along m.
+template <int MI> struct Cfg {
+    static constexpr int BM = 16 * MI;
+    static constexpr int STAGES = MI == 8 ? 6 : 4;
+    static constexpr int A_BYTES = BM * BK * 8;
+    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 2 * STAGES * 8;
+    static constexpr int MIN_CTAS = MI == 8 ? 1 : 2;
+};
 
 __device__ __forceinline__ void dmma(double &d0, double &d1, double a, double b) {
     asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
@@ -57,11 +66,13 @@ struct DgemmParams {
 };
 
 // AK: op(A) is K-major in memory (opA == N).  BKM: op(B) is K-major in memory (opB == T).
-template <bool AK, bool BKM>
-__global__ void __launch_bounds__(THREADS, 1)
+template <bool AK, bool BKM, int MI>
+__global__ void __launch_bounds__(THREADS, Cfg<MI>::MIN_CTAS)
 dgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
                   const DgemmParams p)
 {
+    constexpr int BM = Cfg<MI>::BM, STAGES = Cfg<MI>::STAGES, A_BYTES = Cfg<MI>::A_BYTES,
+                  STAGE_BYTES = Cfg<MI>::STAGE_BYTES;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem_base = (tma::smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t bar_base = smem_base + STAGES * STAGE_BYTES;      // full[STAGES], empty[STAGES]
@@ -120,7 +131,7 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
 
     // ================================ consumers ================================
     const int g = lane >> 2, t = lane & 3;
-    const int wm = warp >> 2, wn = warp & 3;          // 2 x 4 warps, warp tile 64 x 32
+    const int wm = warp >> 2, wn = warp & 3;          // 2 x 4 warps, warp tile (8 MI) x 32
     // per-lane byte offsets of the four k-steps inside a stage tile (frag / box offsets are added
     // as immediates below)
     uint32_t offA[4], offB[4];
@@ -129,19 +140,19 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
         const int kk = kslot(s, t);
         const uint32_t kmaj = g * 128 + ((((kk >> 1) ^ g) & 7) << 4) + (kk & 1) * 8;
         const uint32_t mnmaj = kk * 128 + ((((g >> 1) ^ (kk & 7)) & 7) << 4) + (g & 1) * 8;
-        offA[s] = AK ? (uint32_t)(wm * 64 * 128) + kmaj : (uint32_t)(wm * 4 * 2048) + mnmaj;
+        offA[s] = AK ? (uint32_t)(wm * MI * 8 * 128) + kmaj : (uint32_t)(wm * (MI / 2) * 2048) + mnmaj;
         offB[s] = A_BYTES + (BKM ? (uint32_t)(wn * 32 * 128) + kmaj : (uint32_t)(wn * 2 * 2048) + mnmaj);
     }
 
-    double acc[8][4][2];
+    double acc[MI][4][2];
 #pragma unroll
-    for (int i = 0; i < 8; ++i)
+    for (int i = 0; i < MI; ++i)
 #pragma unroll
         for (int j = 0; j < 4; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
 
-    auto load_frags = [&](uint32_t stage, int s, double (&a)[8], double (&b)[4]) {
+    auto load_frags = [&](uint32_t stage, int s, double (&a)[MI], double (&b)[4]) {
 #pragma unroll
-        for (int i = 0; i < 8; ++i)
+        for (int i = 0; i < MI; ++i)
             a[i] = lds64(stage + (AK ? offA[s] + i * 1024 : (offA[s] ^ ((i & 1) << 6)) + (i >> 1) * 2048));
 #pragma unroll
         for (int j = 0; j < 4; ++j)
@@ -152,13 +163,13 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
         const int s = kb % STAGES;
         const uint32_t stage = smem_base + s * STAGE_BYTES;
         tma::mbar_wait(bar_base + 8 * s, (kb / STAGES) & 1);
-        double a[2][8], b[2][4];
+        double a[2][MI], b[2][4];
         load_frags(stage, 0, a[0], b[0]);
 #pragma unroll
         for (int st = 0; st < 4; ++st) {
             if (st < 3) load_frags(stage, st + 1, a[(st + 1) & 1], b[(st + 1) & 1]);
 #pragma unroll
-            for (int i = 0; i < 8; ++i)
+            for (int i = 0; i < MI; ++i)
 #pragma unroll
                 for (int j = 0; j < 4; ++j) dmma(acc[i][j][0], acc[i][j][1], a[st & 1][i], b[st & 1][j]);
         }
@@ -169,8 +180,8 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
     // ---- epilogue: C = alpha * acc (never read C) ----
     const bool vec = (p.n & 1) == 0;
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-        const int64_t r = m0 + wm * 64 + i * 8 + g;
+    for (int i = 0; i < MI; ++i) {
+        const int64_t r = m0 + wm * MI * 8 + i * 8 + g;
         if (r >= p.m) continue;
         double *crow = p.C + r * p.n;
 #pragma unroll
@@ -373,9 +384,24 @@ zgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
 // ---------------------------------------------------------------------------------
 bool aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
-template <bool AK, bool BKM>
-int launch_dgemm(const GemmArgs &g)
+// Time of a tiling in units of "one full wave of 128 x 128 tiles": two co-resident 64 x 128 CTAs share
+// the SM's DMMA pipe, so a wave of 296 half tiles costs the same as a wave of 148 full ones, and a
+// last wave of at most one CTA per SM costs half.
+bool prefer_small_tile(int64_t m, int64_t n)
 {
+    const int sms = sm_count();
+    const int64_t t128 = ((m + 127) / 128) * ((n + BN - 1) / BN);
+    const int64_t t64 = ((m + 63) / 64) * ((n + BN - 1) / BN);
+    const double big = (double)((t128 + sms - 1) / sms);
+    const int64_t rem = t64 % (2 * sms);
+    const double small = (double)(t64 / (2 * sms)) + (rem == 0 ? 0.0 : rem <= sms ? 0.5 : 1.0);
+    return small < big;
+}
+
+template <bool AK, bool BKM, int MI>
+int launch_dgemm_mi(const GemmArgs &g)
+{
+    constexpr int BM = Cfg<MI>::BM, SMEM_BYTES = Cfg<MI>::SMEM_BYTES;
     CUtensorMap mapA, mapB;
     // K-major operand: box = 16 (k) x 128 rows; MN-major operand: box = 16 (m|n) x 16 (k)
     if (!tma::make_2d(&mapA, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 8, g.A, (uint64_t)g.rowsA, (uint64_t)g.colsA,
@@ -385,7 +411,7 @@ int launch_dgemm(const GemmArgs &g)
         return cuda_fail(cudaErrorInvalidValue, "cuTensorMapEncodeTiled");
     static thread_local bool attr_done = false;
     if (!attr_done) {
-        ACC_CUDA(cudaFuncSetAttribute(dgemm_dmma_kernel<AK, BKM>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+        ACC_CUDA(cudaFuncSetAttribute(dgemm_dmma_kernel<AK, BKM, MI>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
         attr_done = true;
     }
     DgemmParams p;
@@ -396,8 +422,14 @@ int launch_dgemm(const GemmArgs &g)
     p.tiles_n = (int)((g.n + BN - 1) / BN);
     const int64_t tiles = (int64_t)p.tiles_m * p.tiles_n;
     if (tiles > 0x7fffffff) return ACCBLAS_ERR_SHAPE;
-    dgemm_dmma_kernel<AK, BKM><<<(unsigned)tiles, THREADS, SMEM_BYTES, g.stream>>>(mapA, mapB, p);
+    dgemm_dmma_kernel<AK, BKM, MI><<<(unsigned)tiles, THREADS, SMEM_BYTES, g.stream>>>(mapA, mapB, p);
     return check_launch("dgemm_dmma_kernel");
+}
+
+template <bool AK, bool BKM>
+int launch_dgemm(const GemmArgs &g)
+{
+    return prefer_small_tile(g.m, g.n) ? launch_dgemm_mi<AK, BKM, 4>(g) : launch_dgemm_mi<AK, BKM, 8>(g);
 }
 
 template <bool AK, bool BKM, bool CA, bool CB>

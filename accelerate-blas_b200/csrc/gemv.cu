@@ -30,6 +30,53 @@ template <typename T> struct GnRows { static constexpr int value = sizeof(T) == 
 constexpr int GN_MAX_ROWS = 8;
 constexpr int GN_MAX_WARPS = 16;
 
+// NR rows starting at `row0` (all valid): every thread strides along the rows in 16-byte vectors.  The
+// row addresses are row0 + r * n with r a compile-time constant -- no per-row offset registers (an
+// earlier version kept a clamped offset per row and spilled under the 64-register cap of 2 x 512
+// threads per SM, which cost 12 % of the bandwidth).
+template <typename T, bool ALIGNED, int NR>
+__device__ __forceinline__ void gemv_n_rows(int64_t n, int64_t nv, T alpha, const T *__restrict__ row0,
+                                            const T *__restrict__ x, T *__restrict__ yout,
+                                            T (*red)[GN_MAX_WARPS])
+{
+    constexpr int VEC = ALIGNED ? 16 / sizeof(T) : 1;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+    T acc[NR];
+#pragma unroll
+    for (int r = 0; r < NR; ++r) acc[r] = Scalar<T>::zero();
+    if (ALIGNED) {
+        for (int64_t v = threadIdx.x; v < nv; v += blockDim.x) {
+            Vec16<T> xv, av[NR];
+#pragma unroll
+            for (int r = 0; r < NR; ++r)
+                av[r].raw = ldg_stream(reinterpret_cast<const int4 *>(row0 + r * n) + v);
+            xv.raw = ldg_cached(reinterpret_cast<const int4 *>(x) + v);
+#pragma unroll
+            for (int r = 0; r < NR; ++r)
+#pragma unroll
+                for (int e = 0; e < VEC; ++e) acc[r] = fma_acc(av[r].e[e], xv.e[e], acc[r]);
+        }
+    } else {
+        for (int64_t j = threadIdx.x; j < n; j += blockDim.x) {
+            const T xj = x[j];
+#pragma unroll
+            for (int r = 0; r < NR; ++r) acc[r] = fma_acc(row0[r * n + j], xj, acc[r]);
+        }
+    }
+#pragma unroll
+    for (int r = 0; r < NR; ++r) {
+        acc[r] = warp_sum(acc[r]);
+        if (lane == 0) red[r][warp] = acc[r];
+    }
+    __syncthreads();
+    if (threadIdx.x < NR) {
+        T s = Scalar<T>::zero();
+        for (int w = 0; w < nwarps; ++w) s = add_s(s, red[threadIdx.x][w]);
+        yout[threadIdx.x] = mul_s(alpha, s);
+    }
+    __syncthreads();
+}
+
 template <typename T, bool ALIGNED>
 __global__ void __launch_bounds__(512, 2)
 gemv_n_kernel(int64_t m, int64_t n, T alpha, const T *__restrict__ A, const T *__restrict__ x,
@@ -38,53 +85,13 @@ gemv_n_kernel(int64_t m, int64_t n, T alpha, const T *__restrict__ A, const T *_
     constexpr int VEC = ALIGNED ? 16 / sizeof(T) : 1;
     constexpr int GN_ROWS = GnRows<T>::value;
     __shared__ T red[GN_ROWS][GN_MAX_WARPS];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
-    const int64_t nunits = (m + GN_ROWS - 1) / GN_ROWS;
+    const int64_t nfull = m / GN_ROWS;
     const int64_t nv = n / VEC;
-
-    for (int64_t u = blockIdx.x; u < nunits; u += gridDim.x) {
-        const int64_t r0 = u * GN_ROWS;
-        // rows past the end re-read row m-1 (discarded at the store): offsets stay in bounds
-        const T *row0 = A + r0 * n;
-        int64_t roff[GN_ROWS];
-#pragma unroll
-        for (int r = 0; r < GN_ROWS; ++r) roff[r] = ((r0 + r < m) ? r : (m - 1 - r0)) * n;
-        T acc[GN_ROWS];
-#pragma unroll
-        for (int r = 0; r < GN_ROWS; ++r) acc[r] = Scalar<T>::zero();
-
-        if (ALIGNED) {
-            for (int64_t v = threadIdx.x; v < nv; v += blockDim.x) {
-                Vec16<T> xv, av[GN_ROWS];
-#pragma unroll
-                for (int r = 0; r < GN_ROWS; ++r)
-                    av[r].raw = ldg_stream(reinterpret_cast<const int4 *>(row0 + roff[r]) + v);
-                xv.raw = ldg_cached(reinterpret_cast<const int4 *>(x) + v);
-#pragma unroll
-                for (int r = 0; r < GN_ROWS; ++r)
-#pragma unroll
-                    for (int e = 0; e < VEC; ++e) acc[r] = fma_acc(av[r].e[e], xv.e[e], acc[r]);
-            }
-        } else {
-            for (int64_t j = threadIdx.x; j < n; j += blockDim.x) {
-                const T xj = x[j];
-#pragma unroll
-                for (int r = 0; r < GN_ROWS; ++r) acc[r] = fma_acc(row0[roff[r] + j], xj, acc[r]);
-            }
-        }
-#pragma unroll
-        for (int r = 0; r < GN_ROWS; ++r) {
-            acc[r] = warp_sum(acc[r]);
-            if (lane == 0) red[r][warp] = acc[r];
-        }
-        __syncthreads();
-        if (threadIdx.x < GN_ROWS && r0 + threadIdx.x < m) {
-            T s = Scalar<T>::zero();
-            for (int w = 0; w < nwarps; ++w) s = add_s(s, red[threadIdx.x][w]);
-            y[r0 + threadIdx.x] = mul_s(alpha, s);
-        }
-        __syncthreads();
-    }
+    for (int64_t u = blockIdx.x; u < nfull; u += gridDim.x)
+        gemv_n_rows<T, ALIGNED, GN_ROWS>(n, nv, alpha, A + u * GN_ROWS * n, x, y + u * GN_ROWS, red);
+    // the (at most GN_ROWS - 1) rows past the last full unit, one at a time, spread over the CTAs
+    for (int64_t r = nfull * GN_ROWS + blockIdx.x; r < m; r += gridDim.x)
+        gemv_n_rows<T, ALIGNED, 1>(n, nv, alpha, A + r * n, x, y + r, red);
 }
 
 // ------------------------------------------------------------------ op = T / H --------

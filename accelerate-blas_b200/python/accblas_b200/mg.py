@@ -49,7 +49,7 @@ _CODE = {torch.float32: 0, torch.float64: 1, torch.complex64: 2, torch.complex12
 # planning constants for the root bonus (measured on this pool: profiles/): real flop rate of the local
 # gemm and the rate at which NCCL delivers B to the other ranks
 _FLOPS = {torch.float32: 230e12, torch.float64: 36e12, torch.complex64: 228e12, torch.complex128: 36e12}
-_BCAST_BPS = 450e9
+_BCAST_BPS = 670e9   # 8.6 GB in 12.8 ms at 8 ranks, 12.3 ms at 2 (profiles/r01_bench_n8_peer.json)
 
 
 def root_bonus_rows(m: int, n: int, k: int, dtype, world: int) -> int:

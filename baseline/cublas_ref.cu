@@ -36,12 +36,19 @@ static cublasHandle_t H;
 static const char *filter = "";
 static int iters_override = 0;
 
+// Calls are enqueued back to back with an event between them (the same method as tools/perf.py): the GPU
+// never idles between launches, so no launch latency is billed to the kernel.
 template <typename F> float time_ms(F f, int warm, int iters, float *best) {
-    cudaEvent_t a, b; cudaEventCreate(&a); cudaEventCreate(&b);
+    std::vector<cudaEvent_t> ev(iters + 1);
+    for (auto &e : ev) cudaEventCreate(&e);
     for (int i = 0; i < warm; ++i) f();
     CK(cudaDeviceSynchronize());
+    cudaEventRecord(ev[0]);
+    for (int i = 0; i < iters; ++i) { f(); cudaEventRecord(ev[i + 1]); }
+    CK(cudaDeviceSynchronize());
     std::vector<float> t(iters);
-    for (int i = 0; i < iters; ++i) { cudaEventRecord(a); f(); cudaEventRecord(b); cudaEventSynchronize(b); cudaEventElapsedTime(&t[i], a, b); }
+    for (int i = 0; i < iters; ++i) cudaEventElapsedTime(&t[i], ev[i], ev[i + 1]);
+    for (auto &e : ev) cudaEventDestroy(e);
     std::sort(t.begin(), t.end());
     *best = t[0];
     return t[iters / 2];
@@ -118,6 +125,8 @@ int main(int argc, char **argv) {
     CK(cublasSetAtomicsMode(H, CUBLAS_ATOMICS_ALLOWED));              // PTX/Context.hs:59
     gemm_case('d', 'N', 'N', 1024, 1024, 1024, 50);
     gemm_case('d', 'N', 'N', 1000, 1000, 1000, 50);
+    for (long n : {100L, 250L, 500L, 512L, 2048L, 4096L}) gemm_case('d', 'N', 'N', n, n, n, 50);
+    for (long n : {100L, 250L, 500L, 1000L}) gemm_case('s', 'N', 'N', n, n, n, 50);
     for (const char *ops : {"NN", "NT", "TN"}) {
         gemm_case('d', ops[0], ops[1], 8192, 8192, 8192, 10);
         gemm_case('s', ops[0], ops[1], 8192, 8192, 8192, 10);

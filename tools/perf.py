@@ -29,18 +29,20 @@ def rnd(shape, dt, seed):
 
 
 def timeit(fn, iters, warm=3):
+    """Per-call device time with the calls enqueued back to back (events between calls, one
+    synchronize at the end): the GPU never idles waiting for Python, so a launch-latency gap is not
+    billed to the kernel.  When the host is the slower side (tiny products) this is the API's
+    sustained time per call."""
     for _ in range(warm):
         fn()
     torch.cuda.synchronize()
-    ts = []
-    for _ in range(iters):
-        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        a.record()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(iters + 1)]
+    ev[0].record()
+    for i in range(iters):
         fn()
-        b.record()
-        b.synchronize()
-        ts.append(a.elapsed_time(b))
-    ts.sort()
+        ev[i + 1].record()
+    torch.cuda.synchronize()
+    ts = sorted(ev[i].elapsed_time(ev[i + 1]) for i in range(iters))
     return ts[len(ts) // 2], ts[0]
 
 
@@ -72,8 +74,10 @@ def dot_case(dt, n, iters=30):
 
 
 def suite():
-    for n in (1024, 1000, 2048, 4096):
-        gemm_case("f64", "N", "N", n, n, n, 20)
+    for n in (100, 250, 500, 512, 1000, 1024, 2048, 4096):
+        gemm_case("f64", "N", "N", n, n, n, 50)
+    for n in (100, 250, 500, 1000):
+        gemm_case("f32", "N", "N", n, n, n, 50)
     for ops in ("NN", "NT", "TN", "TT"):
         gemm_case("f64", ops[0], ops[1], 8192, 8192, 8192, 5)
     for ops in ("NN", "NT", "TN"):
