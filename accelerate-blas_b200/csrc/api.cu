@@ -63,6 +63,12 @@ bool overlaps(const void *a, size_t na, const void *b, size_t nb)
     return a0 < b0 + nb && b0 < a0 + na;
 }
 
+// elements spanned by a rows x cols view with row pitch ld
+size_t span(int64_t rows, int64_t cols, int64_t ld)
+{
+    return rows > 0 && cols > 0 ? (size_t)(rows - 1) * (size_t)ld + (size_t)cols : 0;
+}
+
 // shape derivation shared by the device and host entry points (LLVM/PTX/Level3.hs:54-65)
 int derive_gemm(GemmArgs &g)
 {
@@ -74,6 +80,11 @@ int derive_gemm(GemmArgs &g)
     g.n = g.opB == ACCBLAS_OP_N ? g.colsB : g.rowsB;
     const int64_t kb = g.opB == ACCBLAS_OP_N ? g.rowsB : g.colsB;
     if (g.k != kb) return ACCBLAS_ERR_SHAPE;     // the reference never checks this
+    // row pitches: 0 = tight (what the reference always passes, LLVM/PTX/Level3.hs:64-65,91)
+    if (g.lda == 0) g.lda = g.colsA;
+    if (g.ldb == 0) g.ldb = g.colsB;
+    if (g.ldc == 0) g.ldc = g.n;
+    if (g.lda < g.colsA || g.ldb < g.colsB || g.ldc < g.n) return ACCBLAS_ERR_SHAPE;
     if (!is_complex(g.dtype)) {                  // H on a real type is T (BLAS/Level3.hs:100,110)
         if (g.opA == ACCBLAS_OP_H) g.opA = ACCBLAS_OP_T;
         if (g.opB == ACCBLAS_OP_H) g.opB = ACCBLAS_OP_T;
@@ -92,6 +103,8 @@ Family pick_family(const GemmArgs &g)
     return FAM_GENERIC;
 }
 
+}  // namespace
+
 int gemm_device(GemmArgs &g)
 {
     ACC_TRY(derive_gemm(g));
@@ -99,13 +112,13 @@ int gemm_device(GemmArgs &g)
     if (!g.C || !g.alpha) return ACCBLAS_ERR_NULL;
     const size_t es = elem_size(g.dtype);
     if (g.k == 0) {                                                    // alpha * (empty sum) = 0
-        ACC_CUDA(cudaMemsetAsync(g.C, 0, es * (size_t)g.m * (size_t)g.n, g.stream));
+        ACC_CUDA(cudaMemset2DAsync(g.C, es * (size_t)g.ldc, 0, es * (size_t)g.n, (size_t)g.m, g.stream));
         return ACCBLAS_OK;
     }
     if (!g.A || !g.B) return ACCBLAS_ERR_NULL;
-    const size_t bytesC = es * (size_t)g.m * (size_t)g.n;
-    if (overlaps(g.C, bytesC, g.A, es * (size_t)g.rowsA * (size_t)g.colsA) ||
-        overlaps(g.C, bytesC, g.B, es * (size_t)g.rowsB * (size_t)g.colsB))
+    const size_t bytesC = es * span(g.m, g.n, g.ldc);
+    if (overlaps(g.C, bytesC, g.A, es * span(g.rowsA, g.colsA, g.lda)) ||
+        overlaps(g.C, bytesC, g.B, es * span(g.rowsB, g.colsB, g.ldb)))
         return ACCBLAS_ERR_ALIAS;
     ACC_TRY(device_check());
     const Family f = pick_family(g);
@@ -117,6 +130,7 @@ int gemm_device(GemmArgs &g)
     }
 }
 
+namespace {
 // RAII for stream-ordered scratch used by the host-buffer entry points
 struct Scratch {
     void *p = nullptr;
@@ -161,6 +175,20 @@ int accblas_gemm(accblas_stream_t stream, int dtype, int opA, int opB, int64_t r
     GemmArgs g{};
     g.dtype = dtype; g.opA = opA; g.opB = opB;
     g.rowsA = rowsA; g.colsA = colsA; g.rowsB = rowsB; g.colsB = colsB;
+    g.alpha = alpha_host; g.A = A; g.B = B; g.C = C;
+    g.stream = static_cast<cudaStream_t>(stream);
+    return gemm_device(g);
+}
+
+int accblas_gemm_ld(accblas_stream_t stream, int dtype, int opA, int opB, int64_t rowsA, int64_t colsA,
+                    int64_t rowsB, int64_t colsB, const void *alpha_host, const void *A, int64_t lda,
+                    const void *B, int64_t ldb, void *C, int64_t ldc)
+{
+    if (lda < 0 || ldb < 0 || ldc < 0) return ACCBLAS_ERR_SHAPE;
+    GemmArgs g{};
+    g.dtype = dtype; g.opA = opA; g.opB = opB;
+    g.rowsA = rowsA; g.colsA = colsA; g.rowsB = rowsB; g.colsB = colsB;
+    g.lda = lda; g.ldb = ldb; g.ldc = ldc;
     g.alpha = alpha_host; g.A = A; g.B = B; g.C = C;
     g.stream = static_cast<cudaStream_t>(stream);
     return gemm_device(g);
@@ -239,83 +267,8 @@ int accblas_gemm_host(accblas_stream_t stream, int dtype, int opA, int opB, int6
     if (g.m == 0 || g.n == 0) return ACCBLAS_OK;
     if (!C_host || !alpha_host) return ACCBLAS_ERR_NULL;
     if (g.k > 0 && (!A_host || !B_host)) return ACCBLAS_ERR_NULL;
-    const size_t es = elem_size(dtype);
-    const size_t bytesA = es * (size_t)rowsA * (size_t)colsA, bytesB = es * (size_t)rowsB * (size_t)colsB;
-    const size_t bytesC = es * (size_t)g.m * (size_t)g.n;
-    cudaStream_t s = g.stream;
-    Scratch dA(s), dB(s), dC(s);
-    ACC_CUDA(dA.alloc(bytesA));
-    ACC_CUDA(dB.alloc(bytesB));
-    ACC_CUDA(dC.alloc(bytesC));
-
-    // Row-panel pipeline when op(A) = A: panel p of A uploads on a side stream while panel
-    // p-1 multiplies, and finished panels of C download behind the next multiply.
-    const int64_t panels = (g.opA == ACCBLAS_OP_N && g.k > 0 && g.m >= 2048) ? std::min<int64_t>(8, g.m / 1024) : 1;
-    if (panels <= 1) {
-        if (bytesA) ACC_CUDA(cudaMemcpyAsync(dA.p, A_host, bytesA, cudaMemcpyHostToDevice, s));
-        if (bytesB) ACC_CUDA(cudaMemcpyAsync(dB.p, B_host, bytesB, cudaMemcpyHostToDevice, s));
-        g.A = dA.p; g.B = dB.p; g.C = dC.p;
-        g.opA = opA; g.opB = opB;
-        ACC_TRY(gemm_device(g));
-        ACC_CUDA(cudaMemcpyAsync(C_host, dC.p, bytesC, cudaMemcpyDeviceToHost, s));
-        ACC_CUDA(cudaStreamSynchronize(s));
-        return ACCBLAS_OK;
-    }
-
-    cudaStream_t up = nullptr, down = nullptr;
-    ACC_CUDA(cudaStreamCreateWithFlags(&up, cudaStreamNonBlocking));
-    ACC_CUDA(cudaStreamCreateWithFlags(&down, cudaStreamNonBlocking));
-    cudaEvent_t ev_start, ev_b, ev_up[8], ev_mm[8], ev_done;
-    cudaEventCreateWithFlags(&ev_start, cudaEventDisableTiming);
-    cudaEventCreateWithFlags(&ev_b, cudaEventDisableTiming);
-    cudaEventCreateWithFlags(&ev_done, cudaEventDisableTiming);
-    for (int i = 0; i < 8; ++i) {
-        cudaEventCreateWithFlags(&ev_up[i], cudaEventDisableTiming);
-        cudaEventCreateWithFlags(&ev_mm[i], cudaEventDisableTiming);
-    }
-    int status = ACCBLAS_OK;
-    cudaEventRecord(ev_start, s);                 // allocations are ordered on s
-    cudaStreamWaitEvent(up, ev_start, 0);
-    cudaStreamWaitEvent(down, ev_start, 0);
-    cudaMemcpyAsync(dB.p, B_host, bytesB, cudaMemcpyHostToDevice, up);
-    cudaEventRecord(ev_b, up);
-    const int64_t rows_per = ((g.m + panels - 1) / panels + 127) / 128 * 128;
-    int np = 0;
-    for (int64_t r0 = 0; r0 < g.m; r0 += rows_per, ++np) {
-        const int64_t rows = std::min<int64_t>(rows_per, g.m - r0);
-        const char *ah = static_cast<const char *>(A_host) + es * (size_t)r0 * (size_t)colsA;
-        char *ad = static_cast<char *>(dA.p) + es * (size_t)r0 * (size_t)colsA;
-        cudaMemcpyAsync(ad, ah, es * (size_t)rows * (size_t)colsA, cudaMemcpyHostToDevice, up);
-        cudaEventRecord(ev_up[np], up);
-    }
-    np = 0;
-    cudaStreamWaitEvent(s, ev_b, 0);
-    for (int64_t r0 = 0; r0 < g.m && status == ACCBLAS_OK; r0 += rows_per, ++np) {
-        const int64_t rows = std::min<int64_t>(rows_per, g.m - r0);
-        cudaStreamWaitEvent(s, ev_up[np], 0);
-        GemmArgs p = g;
-        p.opA = opA; p.opB = opB;
-        p.rowsA = rows;
-        p.A = static_cast<char *>(dA.p) + es * (size_t)r0 * (size_t)colsA;
-        p.B = dB.p;
-        p.C = static_cast<char *>(dC.p) + es * (size_t)r0 * (size_t)g.n;
-        status = gemm_device(p);
-        cudaEventRecord(ev_mm[np], s);
-        cudaStreamWaitEvent(down, ev_mm[np], 0);
-        cudaMemcpyAsync(static_cast<char *>(C_host) + es * (size_t)r0 * (size_t)g.n, p.C,
-                        es * (size_t)rows * (size_t)g.n, cudaMemcpyDeviceToHost, down);
-    }
-    cudaEventRecord(ev_done, down);
-    cudaStreamWaitEvent(s, ev_done, 0);
-    cudaError_t e = cudaStreamSynchronize(s);
-    cudaError_t e2 = cudaStreamSynchronize(up);
-    cudaEventDestroy(ev_start); cudaEventDestroy(ev_b); cudaEventDestroy(ev_done);
-    for (int i = 0; i < 8; ++i) { cudaEventDestroy(ev_up[i]); cudaEventDestroy(ev_mm[i]); }
-    cudaStreamDestroy(up); cudaStreamDestroy(down);
-    if (status != ACCBLAS_OK) return status;
-    if (e != cudaSuccess) return cuda_fail(e, "accblas_gemm_host sync");
-    if (e2 != cudaSuccess) return cuda_fail(e2, "accblas_gemm_host sync(up)");
-    return ACCBLAS_OK;
+    ACC_TRY(device_check());
+    return gemm_host_pipeline(g, A_host, B_host, C_host);
 }
 
 int accblas_gemv_host(accblas_stream_t stream, int dtype, int opA, int64_t rowsA, int64_t colsA,

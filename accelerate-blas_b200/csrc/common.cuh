@@ -122,12 +122,16 @@ struct GemmArgs {
     int dtype, opA, opB;
     int64_t rowsA, colsA, rowsB, colsB;   // stored (pre-op) shapes
     int64_t m, n, k;                      // derived: C is m x n, inner extent k
+    int64_t lda, ldb, ldc;                // row pitches in ELEMENTS (0 = tight: colsA, colsB, n)
     const void *alpha;                    // host pointer, one element
     const void *A, *B;
     void *C;
     cudaStream_t stream;
 };
 
+int gemm_device(GemmArgs &g);                         // api.cu : validate + dispatch one device-resident product
+int gemm_host_pipeline(const GemmArgs &g, const void *A_host, const void *B_host,
+                       void *C_host);                 // host_pipeline.cu : upload / multiply / download wavefront
 int gemm_generic(const GemmArgs &g);                  // gemm_generic.cu : any shape
 bool dgemm_dmma_eligible(const GemmArgs &g);          // gemm_dmma.cu    : f64 / c64 on DMMA
 int  dgemm_dmma(const GemmArgs &g);

@@ -59,7 +59,7 @@ __device__ __forceinline__ int kslot(int s, int t) {
 }
 
 struct DgemmParams {
-    int64_t m, n, k;
+    int64_t m, n, k, ldc;
     double alpha;
     double *C;
     int tiles_m, tiles_n;
@@ -178,12 +178,12 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
     }
 
     // ---- epilogue: C = alpha * acc (never read C) ----
-    const bool vec = (p.n & 1) == 0;
+    const bool vec = ((p.n | p.ldc) & 1) == 0;
 #pragma unroll
     for (int i = 0; i < MI; ++i) {
         const int64_t r = m0 + wm * MI * 8 + i * 8 + g;
         if (r >= p.m) continue;
-        double *crow = p.C + r * p.n;
+        double *crow = p.C + r * p.ldc;
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
             const int64_t c = n0 + wn * 32 + j * 8 + 2 * t;
@@ -227,7 +227,7 @@ __device__ __forceinline__ double flip(double x) {
 }
 
 struct ZgemmParams {
-    int64_t m, n, k;
+    int64_t m, n, k, ldc;
     double alr, ali;
     double2 *C;
     int tiles_m, tiles_n;
@@ -364,7 +364,7 @@ zgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
     for (int i = 0; i < 4; ++i) {
         const int64_t r = m0 + wm * 32 + i * 8 + g;
         if (r >= p.m) continue;
-        double2 *crow = p.C + r * p.n;
+        double2 *crow = p.C + r * p.ldc;
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
             const int64_t c = n0 + wn * 32 + j * 8 + 2 * t;
@@ -405,9 +405,9 @@ int launch_dgemm_mi(const GemmArgs &g)
     CUtensorMap mapA, mapB;
     // K-major operand: box = 16 (k) x 128 rows; MN-major operand: box = 16 (m|n) x 16 (k)
     if (!tma::make_2d(&mapA, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 8, g.A, (uint64_t)g.rowsA, (uint64_t)g.colsA,
-                      AK ? BM : BK, 16) ||
+                      AK ? BM : BK, 16, (uint64_t)g.lda * 8) ||
         !tma::make_2d(&mapB, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 8, g.B, (uint64_t)g.rowsB, (uint64_t)g.colsB,
-                      BKM ? BN : BK, 16))
+                      BKM ? BN : BK, 16, (uint64_t)g.ldb * 8))
         return cuda_fail(cudaErrorInvalidValue, "cuTensorMapEncodeTiled");
     static thread_local bool attr_done = false;
     if (!attr_done) {
@@ -415,7 +415,7 @@ int launch_dgemm_mi(const GemmArgs &g)
         attr_done = true;
     }
     DgemmParams p;
-    p.m = g.m; p.n = g.n; p.k = g.k;
+    p.m = g.m; p.n = g.n; p.k = g.k; p.ldc = g.ldc;
     p.alpha = *static_cast<const double *>(g.alpha);
     p.C = static_cast<double *>(g.C);
     p.tiles_m = (int)((g.m + BM - 1) / BM);
@@ -438,9 +438,9 @@ int launch_zgemm(const GemmArgs &g)
     CUtensorMap mapA, mapB;
     // maps are over doubles (no complex TMA type): a complex row of c columns is 2c doubles
     if (!tma::make_2d(&mapA, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 8, g.A, (uint64_t)g.rowsA, 2 * (uint64_t)g.colsA,
-                      AK ? ZBM : ZBK, 16) ||
+                      AK ? ZBM : ZBK, 16, (uint64_t)g.lda * 16) ||
         !tma::make_2d(&mapB, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 8, g.B, (uint64_t)g.rowsB, 2 * (uint64_t)g.colsB,
-                      BKM ? ZBN : ZBK, 16))
+                      BKM ? ZBN : ZBK, 16, (uint64_t)g.ldb * 16))
         return cuda_fail(cudaErrorInvalidValue, "cuTensorMapEncodeTiled");
     static thread_local bool attr_done = false;
     if (!attr_done) {
@@ -448,7 +448,7 @@ int launch_zgemm(const GemmArgs &g)
         attr_done = true;
     }
     ZgemmParams p;
-    p.m = g.m; p.n = g.n; p.k = g.k;
+    p.m = g.m; p.n = g.n; p.k = g.k; p.ldc = g.ldc;
     p.alr = static_cast<const double *>(g.alpha)[0];
     p.ali = static_cast<const double *>(g.alpha)[1];
     p.C = static_cast<double2 *>(g.C);
@@ -489,7 +489,7 @@ bool dgemm_dmma_eligible(const GemmArgs &g)
         if (g.rowsA > 0x3fffffff || g.colsA > 0x3fffffff || g.rowsB > 0x3fffffff || g.colsB > 0x3fffffff) return false;
         return g.m * g.n >= 32 * 32 && g.k >= 4;
     }
-    if ((g.colsA & 1) || (g.colsB & 1)) return false;
+    if ((g.lda & 1) || (g.ldb & 1)) return false;          // row pitch must be a multiple of 16 bytes
     if (g.rowsA > 0x7fffffff || g.colsA > 0x7fffffff || g.rowsB > 0x7fffffff || g.colsB > 0x7fffffff) return false;
     // tiny products stay on the SIMT kernel: a 128 x 128 tile would be mostly padding
     if (g.m * g.n < 64 * 64 || g.k < 8) return false;

@@ -16,17 +16,17 @@ namespace {
 
 constexpr int BM = 64, BN = 64, BK = 16, TM = 4, TN = 4, NT = 256;
 
-// Read element (r, c) of a stored rows x cols row-major matrix, 0 outside.
+// Read element (r, c) of a stored rows x cols row-major matrix with row pitch ld, 0 outside.
 template <typename T>
-__device__ __forceinline__ T ld_guard(const T *__restrict__ p, int64_t rows, int64_t cols, int64_t r, int64_t c) {
-    return (r < rows && c < cols) ? p[r * cols + c] : Scalar<T>::zero();
+__device__ __forceinline__ T ld_guard(const T *__restrict__ p, int64_t rows, int64_t cols, int64_t ld, int64_t r, int64_t c) {
+    return (r < rows && c < cols) ? p[r * ld + c] : Scalar<T>::zero();
 }
 
 template <typename T, bool TA, bool TB>
 __global__ void __launch_bounds__(NT)
 gemm_generic_kernel(int64_t m, int64_t n, int64_t k, int64_t rowsA, int64_t colsA, int64_t rowsB,
-                    int64_t colsB, bool conjA, bool conjB, T alpha, const T *__restrict__ A,
-                    const T *__restrict__ B, T *__restrict__ C)
+                    int64_t colsB, int64_t lda, int64_t ldb, int64_t ldc, bool conjA, bool conjB, T alpha,
+                    const T *__restrict__ A, const T *__restrict__ B, T *__restrict__ C)
 {
     __shared__ T As[BK][BM + 1];
     __shared__ T Bs[BK][BN + 1];
@@ -46,8 +46,8 @@ gemm_generic_kernel(int64_t m, int64_t n, int64_t k, int64_t rowsA, int64_t cols
         for (int e = tid; e < BM * BK; e += NT) {
             int mm, kk;
             T v;
-            if (!TA) { kk = e % BK; mm = e / BK; v = ld_guard(A, rowsA, colsA, m0 + mm, k0 + kk); }
-            else     { mm = e % BM; kk = e / BM; v = ld_guard(A, rowsA, colsA, k0 + kk, m0 + mm); }
+            if (!TA) { kk = e % BK; mm = e / BK; v = ld_guard(A, rowsA, colsA, lda, m0 + mm, k0 + kk); }
+            else     { mm = e % BM; kk = e / BM; v = ld_guard(A, rowsA, colsA, lda, k0 + kk, m0 + mm); }
             if (conjA) v = conj_s(v);
             As[kk][mm] = v;
         }
@@ -56,8 +56,8 @@ gemm_generic_kernel(int64_t m, int64_t n, int64_t k, int64_t rowsA, int64_t cols
         for (int e = tid; e < BN * BK; e += NT) {
             int nn, kk;
             T v;
-            if (!TB) { nn = e % BN; kk = e / BN; v = ld_guard(B, rowsB, colsB, k0 + kk, n0 + nn); }
-            else     { kk = e % BK; nn = e / BK; v = ld_guard(B, rowsB, colsB, n0 + nn, k0 + kk); }
+            if (!TB) { nn = e % BN; kk = e / BN; v = ld_guard(B, rowsB, colsB, ldb, k0 + kk, n0 + nn); }
+            else     { kk = e % BK; nn = e / BK; v = ld_guard(B, rowsB, colsB, ldb, n0 + nn, k0 + kk); }
             if (conjB) v = conj_s(v);
             Bs[kk][nn] = v;
         }
@@ -83,7 +83,7 @@ gemm_generic_kernel(int64_t m, int64_t n, int64_t k, int64_t rowsA, int64_t cols
 #pragma unroll
         for (int j = 0; j < TN; ++j) {
             const int64_t c = n0 + tx + 16 * j;
-            if (c < n) C[r * n + c] = mul_s(alpha, acc[i][j]);   // beta = 0: C is never read
+            if (c < n) C[r * ldc + c] = mul_s(alpha, acc[i][j]);   // beta = 0: C is never read
         }
     }
 }
@@ -101,7 +101,8 @@ int launch_typed(const GemmArgs &g)
     T *C = static_cast<T *>(g.C);
 #define GO(TA_, TB_)                                                                             \
     gemm_generic_kernel<T, TA_, TB_><<<grid, NT, 0, g.stream>>>(g.m, g.n, g.k, g.rowsA, g.colsA,   \
-                                                                g.rowsB, g.colsB, ca, cb, alpha, A, B, C)
+                                                                g.rowsB, g.colsB, g.lda, g.ldb, g.ldc, ca, cb,  \
+                                                                alpha, A, B, C)
     if (!ta && !tb) GO(false, false);
     else if (!ta && tb) GO(false, true);
     else if (ta && !tb) GO(true, false);

@@ -41,6 +41,7 @@ enum PackMode {
 struct PackArgs {
     const float *src;      // stored matrix (float view: complex = 2 floats per element)
     int64_t rows, cols;    // stored shape in ELEMENTS
+    int64_t ld;            // stored row pitch in ELEMENTS
     int transposed;        // 1: op-index (r,l) lives at stored [l][r];  0: at stored [r][l]
     float conj_sign;       // +1, or -1 when the op is H on a complex type
     int64_t R, Kp;         // output extent (floats)
@@ -58,11 +59,11 @@ template <int MODE>
 __device__ __forceinline__ float pack_value(const PackArgs &a, int64_t r, int64_t c)
 {
     if (MODE == PK_REAL) {
-        return a.transposed ? a.src[c * a.cols + r] : a.src[r * a.cols + c];
+        return a.transposed ? a.src[c * a.ld + r] : a.src[r * a.ld + c];
     } else if (MODE == PK_CPLX_A) {
         const int64_t l = c >> 1;
         const int p = (int)(c & 1);
-        const int64_t e = a.transposed ? l * a.cols + r : r * a.cols + l;
+        const int64_t e = a.transposed ? l * a.ld + r : r * a.ld + l;
         const float v = a.src[2 * e + p];
         return p ? v * a.conj_sign : v;
     } else {
@@ -70,7 +71,7 @@ __device__ __forceinline__ float pack_value(const PackArgs &a, int64_t r, int64_
         const int q = (int)(r & 1), p = (int)(c & 1);
         // op(B)[l][j]: stored [l][j] when op = N (not "transposed" w.r.t. k-major view means
         // stored [j][l]); `transposed` here means the K-major row j is NOT contiguous in memory
-        const int64_t e = a.transposed ? l * a.cols + j : j * a.cols + l;
+        const int64_t e = a.transposed ? l * a.ld + j : j * a.ld + l;
         const float br = a.src[2 * e], bi = a.src[2 * e + 1] * a.conj_sign;
         return q == p ? br : (q == 0 ? -bi : bi);
     }
@@ -418,7 +419,7 @@ int launch_tc(const GemmArgs &g, const TcPlan &t, float *ahi, float *alo, float 
     }
     SgemmParams p;
     p.M = t.M; p.N = t.N; p.Kp = t.pitch;      // padding columns are zero-filled by pack_split
-    p.ldc = t.N;
+    p.ldc = (g.dtype == ACCBLAS_C32 ? 2 : 1) * g.ldc;
     p.C = static_cast<float *>(g.C);
     p.alr = static_cast<const float *>(g.alpha)[0];
     p.cplx = g.dtype == ACCBLAS_C32;
@@ -461,12 +462,12 @@ int sgemm_tc(const GemmArgs &g)
     float *bhi = reinterpret_cast<float *>(ws + 2 * t.plane_a), *blo = reinterpret_cast<float *>(ws + 2 * t.plane_a + t.plane_b);
 
     PackArgs pa{};
-    pa.src = static_cast<const float *>(g.A); pa.rows = g.rowsA; pa.cols = g.colsA;
+    pa.src = static_cast<const float *>(g.A); pa.rows = g.rowsA; pa.cols = g.colsA; pa.ld = g.lda;
     pa.transposed = g.opA != ACCBLAS_OP_N;                 // op(A)[i][l] lives at stored [l][i]
     pa.conj_sign = (cx && g.opA == ACCBLAS_OP_H) ? -1.f : 1.f;
     pa.R = t.RA; pa.Kp = t.Kp; pa.pitch = t.pitch; pa.hi = ahi; pa.lo = alo;
     PackArgs pb{};
-    pb.src = static_cast<const float *>(g.B); pb.rows = g.rowsB; pb.cols = g.colsB;
+    pb.src = static_cast<const float *>(g.B); pb.rows = g.rowsB; pb.cols = g.colsB; pb.ld = g.ldb;
     pb.transposed = g.opB == ACCBLAS_OP_N;                 // K-major row j of op(B)^T is a stored COLUMN when op = N
     pb.conj_sign = (cx && g.opB == ACCBLAS_OP_H) ? -1.f : 1.f;
     pb.R = t.RB; pb.Kp = t.Kp; pb.pitch = t.pitch; pb.hi = bhi; pb.lo = blo;

@@ -92,6 +92,19 @@ def _dev_operand(a, code: int, ndim: int, name: str):
     return a if a.is_contiguous() else a.contiguous()
 
 
+def _row_strided(a) -> bool:
+    """rank-2 view whose rows are dense and whose row pitch is at least the row length: a window of
+    a larger row-major matrix, which accblas_gemm_ld takes as (pointer, lda) without a copy."""
+    return a.dim() == 2 and a.shape[0] > 0 and a.shape[1] > 0 and a.stride(1) == 1 and a.stride(0) >= a.shape[1]
+
+
+def _dev_matrix(a, code: int, name: str):
+    if _is_torch(a) and a.is_cuda and _code(a) == code and _row_strided(a):
+        return a, a.stride(0)
+    a = _dev_operand(a, code, 2, name)
+    return a, a.shape[1]
+
+
 def _host_operand(a, code: int, ndim: int, name: str) -> np.ndarray:
     a = np.asarray(a)
     if _code(a) != code:
@@ -125,19 +138,25 @@ def gemm(alpha, opA, A, opB, B, out=None):
     L = lib()
     if _is_torch(A):
         torch = _torch()
-        A = _dev_operand(A, code, 2, "gemm: A")
-        B = _dev_operand(B, code, 2, "gemm: B")
+        A, lda = _dev_matrix(A, code, "gemm: A")
+        B, ldb = _dev_matrix(B, code, "gemm: B")
         m = A.shape[0] if oa == N else A.shape[1]          # LLVM/PTX/Level3.hs:57-62
         n = B.shape[1] if ob == N else B.shape[0]
         with torch.cuda.device(A.device):
             if out is None:
                 C = torch.empty((m, n), dtype=A.dtype, device=A.device)   # allocateRemote: uninitialised
             else:
-                if tuple(out.shape) != (m, n) or out.dtype != A.dtype or not out.is_contiguous() or not out.is_cuda:
-                    raise ValueError("gemm: out must be a contiguous CUDA tensor of shape (m, n) and A's dtype")
+                if tuple(out.shape) != (m, n) or out.dtype != A.dtype or not out.is_cuda or \
+                        not (out.is_contiguous() or _row_strided(out)):
+                    raise ValueError("gemm: out must be a CUDA tensor of shape (m, n) and A's dtype with dense rows")
                 C = out
-            st = L.accblas_gemm(_stream(A), code, oa, ob, A.shape[0], A.shape[1], B.shape[0], B.shape[1],
-                                al, _ptr(A), _ptr(B), _ptr(C))
+            ldc = C.stride(0) if (m > 0 and n > 0 and not C.is_contiguous()) else n
+            if lda == A.shape[1] and ldb == B.shape[1] and ldc == n:
+                st = L.accblas_gemm(_stream(A), code, oa, ob, A.shape[0], A.shape[1], B.shape[0], B.shape[1],
+                                    al, _ptr(A), _ptr(B), _ptr(C))
+            else:   # windows of larger matrices: explicit row pitches
+                st = L.accblas_gemm_ld(_stream(A), code, oa, ob, A.shape[0], A.shape[1], B.shape[0], B.shape[1],
+                                       al, _ptr(A), lda, _ptr(B), ldb, _ptr(C), ldc)
         _ffi.check(st, "accblas_gemm")
         return C
     A = _host_operand(A, code, 2, "gemm: A")

@@ -14,7 +14,7 @@ LIB_PATH = os.environ.get("ACCBLAS_B200_LIB", os.path.join(PKG_ROOT, "lib", "lib
 
 # every symbol include/accblas_b200.h declares (tests/test_abi.py checks this list against the header)
 SYMBOLS = (
-    "accblas_gemm", "accblas_gemm_workspace_bytes", "accblas_gemv", "accblas_dot",
+    "accblas_gemm", "accblas_gemm_ld", "accblas_gemm_workspace_bytes", "accblas_gemv", "accblas_dot",
     "accblas_gemm_host", "accblas_gemv_host", "accblas_dot_host",
     "accblas_version", "accblas_status_string", "accblas_last_cuda_error",
     "accblas_gemm_kernel_name", "accblas_launch_count", "accblas_set_gemm_path",
@@ -52,6 +52,8 @@ def lib() -> ctypes.CDLL:
     i64, vp, ci, sz = ctypes.c_int64, ctypes.c_void_p, ctypes.c_int, ctypes.c_size_t
     L.accblas_gemm.argtypes = [vp, ci, ci, ci, i64, i64, i64, i64, vp, vp, vp, vp]
     L.accblas_gemm_host.argtypes = L.accblas_gemm.argtypes
+    L.accblas_gemm_ld.argtypes = [vp, ci, ci, ci, i64, i64, i64, i64, vp, vp, i64, vp, i64, vp, i64]
+    L.accblas_gemm_ld.restype = ci
     L.accblas_gemv.argtypes = [vp, ci, ci, i64, i64, vp, vp, vp, i64, vp]
     L.accblas_gemv_host.argtypes = L.accblas_gemv.argtypes
     L.accblas_dot.argtypes = [vp, ci, ci, i64, vp, vp, vp]

@@ -84,6 +84,17 @@ int accblas_gemm(accblas_stream_t stream, int dtype, int opA, int opB,
                  int64_t rowsA, int64_t colsA, int64_t rowsB, int64_t colsB,
                  const void *alpha_host, const void *A, const void *B, void *C);
 
+/* The same product on WINDOWS of larger row-major arrays: lda, ldb, ldc are row pitches in
+ * elements (>= the window's column count; 0 = tight).  The reference always passes tight
+ * pitches (lda = colsA, ldb = colsB, ldc = n, LLVM/PTX/Level3.hs:64-65,91) because Accelerate
+ * arrays are dense; this entry point is what accblas_gemm_host's upload/multiply/download
+ * wavefront and the multi-GPU row panels are built from, and what a caller holding a slice
+ * (Accelerate `slice`/`backpermute` fused away) can use without materialising it. */
+int accblas_gemm_ld(accblas_stream_t stream, int dtype, int opA, int opB,
+                    int64_t rowsA, int64_t colsA, int64_t rowsB, int64_t colsB,
+                    const void *alpha_host, const void *A, int64_t lda, const void *B, int64_t ldb,
+                    void *C, int64_t ldc);
+
 /* Bytes of stream-ordered scratch accblas_gemm will take from the device's default
  * memory pool for this problem (0 for the direct kernels).  Informational. */
 size_t accblas_gemm_workspace_bytes(int dtype, int opA, int opB,
@@ -120,8 +131,10 @@ int accblas_dot(accblas_stream_t stream, int dtype, int conj_x, int64_t n,
  * `use` uploads the host arrays, the hook runs, the result is copied back
  * (test/Test/BLAS/Level3.hs:52-54; bench/Bench/Accelerate.hs:111-114).  A, B, x, y, C,
  * out are HOST pointers (pinned memory gives full PCIe rate, pageable works);
- * uploads are pipelined against the kernels in row panels.  Synchronous: returns when
- * the result is in host memory.  `stream` orders the work like above.
+ * gemm overlaps upload, multiply and download as a wavefront over a block grid of C: step t
+ * uploads row panel t of op(A) and column panel t of op(B), which releases the L-shaped strip
+ * C[t, 0..t-1] + C[0..t, t] for multiplication (csrc/host_pipeline.cu).  Synchronous: returns
+ * when the result is in host memory.  `stream` orders the work like above.
  * ---------------------------------------------------------------------------------- */
 int accblas_gemm_host(accblas_stream_t stream, int dtype, int opA, int opB,
                       int64_t rowsA, int64_t colsA, int64_t rowsB, int64_t colsB,

@@ -291,6 +291,63 @@ def test_host_entry_points(dt, cuda):
     assert abs(complex(d) - complex(O.dot(x, y))) <= 5002 * O.EPS[dt] * np.linalg.norm(x) * np.linalg.norm(y) * 2
 
 
+@pytest.mark.parametrize("dt", DTYPES, ids=ids)
+def test_gemm_strided_windows(dt, cuda):
+    """accblas_gemm_ld: operands and result are windows of larger row-major arrays (row pitch >
+    column count).  Every kernel family is reached: even pitches (TMA paths), odd pitches (SIMT),
+    a product large enough for the tcgen05 path.  Elements of the parent of C outside the window
+    must stay untouched."""
+    import torch
+    import accblas_b200 as ab
+    rng = np.random.default_rng(7500 + dt)
+    for (m, n, k, pad, off) in [(256, 256, 256, 64, 32), (200, 136, 72, 8, 2), (130, 70, 50, 3, 1), (33, 17, 9, 5, 0)]:
+        for oa in OPN:
+            for ob in OPN:
+                al, A, B = gemm_inputs(rng, dt, oa, ob, m, n, k)
+                PA = O.uniform(rng, (A.shape[0] + 3, A.shape[1] + pad), dt)
+                PB = O.uniform(rng, (B.shape[0] + 2, B.shape[1] + pad), dt)
+                PA[1:1 + A.shape[0], off:off + A.shape[1]] = A
+                PB[2:2 + B.shape[0], off:off + B.shape[1]] = B
+                dPA, dPB = dev(PA, cuda), dev(PB, cuda)
+                sentinel = 7.0
+                dPC = torch.full((m + 4, n + pad), sentinel, dtype=dPA.dtype, device=cuda)
+                vA = dPA[1:1 + A.shape[0], off:off + A.shape[1]]
+                vB = dPB[2:2 + B.shape[0], off:off + B.shape[1]]
+                vC = dPC[3:3 + m, off:off + n]
+                assert not vA.is_contiguous() and not vC.is_contiguous()
+                ab.gemm(al, oa, vA, ob, vB, out=vC)
+                PC = host(dPC)
+                C = PC[3:3 + m, off:off + n]
+                ref = O.gemm(al, oa, A, ob, B, wide=True)
+                err = O.gemm_error_units(np.ascontiguousarray(C), ref, A, B, k, al)
+                assert err <= TOL_UNITS_TF32X3, (O.NAMES[dt], oa, ob, m, n, k, err)
+                PC[3:3 + m, off:off + n] = sentinel
+                assert np.all(PC == sentinel), "gemm_ld wrote outside its window"
+
+
+@pytest.mark.parametrize("dt", DTYPES, ids=ids)
+def test_host_pipeline_wavefront(dt, cuda):
+    """accblas_gemm_host on shapes that split into several row / column panels (csrc/host_pipeline.cu):
+    P x Q block grids with P != Q, ragged last panels, every op pair; checked on sampled rows."""
+    import accblas_b200 as ab
+    rng = np.random.default_rng(7700 + dt)
+    for (m, n, k) in [(1536, 1100, 96), (700, 2100, 64), (2304, 520, 40)]:
+        for oa in OPN:
+            for ob in OPN:
+                al, A, B = gemm_inputs(rng, dt, oa, ob, m, n, k)
+                C = ab.gemm(al, oa, A, ob, B)
+                rows = np.arange(0, m, 41)
+                Asub = A[rows] if oa == "N" else np.ascontiguousarray(A[:, rows])
+                ref = O.gemm(al, oa, Asub, ob, B, wide=True)
+                err = O.gemm_error_units(np.ascontiguousarray(C[rows]), ref, Asub, B, k, al)
+                assert err <= TOL_UNITS_TF32X3, (O.NAMES[dt], oa, ob, m, n, k, err)
+    # linearity over the whole result at a larger size (all blocks of the wavefront are covered)
+    al, A, B = gemm_inputs(rng, dt, "N", "N", 2048, 2048, 256)
+    A2 = O.uniform(rng, A.shape, dt)
+    C1, C2, C12 = ab.gemm(al, "N", A, "N", B), ab.gemm(al, "N", A2, "N", B), ab.gemm(al, "N", A + A2, "N", B)
+    assert O.gemm_error_units(C12, C1 + C2, A + A2, B, 256, al) <= 3 * TOL_UNITS_TF32X3
+
+
 def test_launches_are_counted(cuda):
     import torch
     import accblas_b200 as ab
