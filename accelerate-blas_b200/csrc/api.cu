@@ -92,12 +92,13 @@ int derive_gemm(GemmArgs &g)
     return ACCBLAS_OK;
 }
 
-enum Family { FAM_NONE, FAM_GENERIC, FAM_DMMA, FAM_TC };
+enum Family { FAM_NONE, FAM_GENERIC, FAM_DMMA, FAM_TC, FAM_RANK1 };
 
 Family pick_family(const GemmArgs &g)
 {
     if (g.m == 0 || g.n == 0) return FAM_NONE;
     if (g_gemm_path == 1) return FAM_GENERIC;
+    if (g.k == 1 && g_gemm_path == 0) return FAM_RANK1;          // `><`: a store stream, not a contraction
     if ((g.dtype == ACCBLAS_F64 || g.dtype == ACCBLAS_C64) && dgemm_dmma_eligible(g)) return FAM_DMMA;
     if ((g.dtype == ACCBLAS_F32 || g.dtype == ACCBLAS_C32) && sgemm_tc_eligible(g)) return FAM_TC;
     return FAM_GENERIC;
@@ -126,6 +127,7 @@ int gemm_device(GemmArgs &g)
     switch (f) {
     case FAM_DMMA: return dgemm_dmma(g);
     case FAM_TC:   return sgemm_tc(g);
+    case FAM_RANK1: return gemm_rank1(g);
     default:       return gemm_generic(g);
     }
 }
@@ -205,6 +207,7 @@ const char *accblas_gemm_kernel_name(int dtype, int opA, int opB, int64_t rowsA,
     case FAM_NONE: return "none";
     case FAM_DMMA: return g.dtype == ACCBLAS_F64 ? "dgemm_dmma_tma" : "zgemm_dmma_tma";
     case FAM_TC:   return g.dtype == ACCBLAS_F32 ? "sgemm_tf32x3_tcgen05" : "cgemm_tf32x3_tcgen05";
+    case FAM_RANK1: return "gemm_rank1_outer";
     default:       return "gemm_simt_generic";
     }
 }
@@ -249,6 +252,43 @@ int accblas_dot(accblas_stream_t stream, int dtype, int conj_x, int64_t n, const
     if (n > 0 && (!x || !y)) return ACCBLAS_ERR_NULL;
     ACC_TRY(device_check());
     return dot_dispatch(static_cast<cudaStream_t>(stream), dtype, conj_x, n, x, y, out_dev);
+}
+
+int accblas_sdot(accblas_stream_t stream, int dtype, int64_t n, const void *z_host, const void *x,
+                 const void *y, void *out_dev)
+{
+    if (bad_dtype(dtype)) return ACCBLAS_ERR_DTYPE;
+    if (n < 0) return ACCBLAS_ERR_SHAPE;
+    if (!out_dev || !z_host) return ACCBLAS_ERR_NULL;
+    if (n > 0 && (!x || !y)) return ACCBLAS_ERR_NULL;
+    ACC_TRY(device_check());
+    return sdot_dispatch(static_cast<cudaStream_t>(stream), dtype, n, z_host, x, y, out_dev);
+}
+
+int accblas_asum(accblas_stream_t stream, int dtype, int64_t n, const void *x, void *out_dev)
+{
+    if (bad_dtype(dtype)) return ACCBLAS_ERR_DTYPE;
+    if (n < 0) return ACCBLAS_ERR_SHAPE;
+    if (!out_dev || (n > 0 && !x)) return ACCBLAS_ERR_NULL;
+    ACC_TRY(device_check());
+    return asum_dispatch(static_cast<cudaStream_t>(stream), dtype, n, x, out_dev);
+}
+
+static int iamax_entry(accblas_stream_t stream, int dtype, int want_max, int64_t n, const void *x, int64_t *out_dev)
+{
+    if (bad_dtype(dtype)) return ACCBLAS_ERR_DTYPE;
+    if (n <= 0) return ACCBLAS_ERR_SHAPE;           // fold1 over an empty vector is an error in the reference too
+    if (!out_dev || !x) return ACCBLAS_ERR_NULL;
+    ACC_TRY(device_check());
+    return iamax_dispatch(static_cast<cudaStream_t>(stream), dtype, want_max, n, x, out_dev);
+}
+int accblas_amax(accblas_stream_t stream, int dtype, int64_t n, const void *x, int64_t *out_dev)
+{
+    return iamax_entry(stream, dtype, 1, n, x, out_dev);
+}
+int accblas_amin(accblas_stream_t stream, int dtype, int64_t n, const void *x, int64_t *out_dev)
+{
+    return iamax_entry(stream, dtype, 0, n, x, out_dev);
 }
 
 // -------------------------------------------------------------------------------------
@@ -319,6 +359,78 @@ int accblas_dot_host(accblas_stream_t stream, int dtype, int conj_x, int64_t n, 
     ACC_CUDA(cudaMemcpyAsync(out_host, dout.p, es, cudaMemcpyDeviceToHost, s));
     ACC_CUDA(cudaStreamSynchronize(s));
     return ACCBLAS_OK;
+}
+
+// One-vector / two-vector Level-1 host wrappers: upload, reduce, download the scalar.
+static int level1_host(cudaStream_t s, size_t es, int64_t n, const void *x_host, const void *y_host,
+                       size_t out_bytes, void *out_host, int (*run)(cudaStream_t, const void *, const void *, void *, void *),
+                       void *ctx)
+{
+    Scratch dx(s), dy(s), dout(s);
+    ACC_CUDA(dx.alloc(es * (size_t)n));
+    if (y_host) ACC_CUDA(dy.alloc(es * (size_t)n));
+    ACC_CUDA(dout.alloc(out_bytes));
+    if (n > 0) {
+        ACC_CUDA(cudaMemcpyAsync(dx.p, x_host, es * (size_t)n, cudaMemcpyHostToDevice, s));
+        if (y_host) ACC_CUDA(cudaMemcpyAsync(dy.p, y_host, es * (size_t)n, cudaMemcpyHostToDevice, s));
+    }
+    ACC_TRY(run(s, dx.p, y_host ? dy.p : nullptr, dout.p, ctx));
+    ACC_CUDA(cudaMemcpyAsync(out_host, dout.p, out_bytes, cudaMemcpyDeviceToHost, s));
+    ACC_CUDA(cudaStreamSynchronize(s));
+    return ACCBLAS_OK;
+}
+
+struct L1Ctx { int dtype; int64_t n; const void *z; int want_max; };
+
+int accblas_sdot_host(accblas_stream_t stream, int dtype, int64_t n, const void *z_host, const void *x_host,
+                      const void *y_host, void *out_host)
+{
+    if (bad_dtype(dtype)) return ACCBLAS_ERR_DTYPE;
+    if (n < 0) return ACCBLAS_ERR_SHAPE;
+    if (!out_host || !z_host || (n > 0 && (!x_host || !y_host))) return ACCBLAS_ERR_NULL;
+    L1Ctx c{dtype, n, z_host, 0};
+    static const char dummy = 0;
+    return level1_host(static_cast<cudaStream_t>(stream), elem_size(dtype), n, x_host, y_host ? y_host : &dummy,
+                       elem_size(dtype), out_host,
+                       [](cudaStream_t s, const void *x, const void *y, void *o, void *cv) {
+                           auto *c = static_cast<L1Ctx *>(cv);
+                           return accblas_sdot(s, c->dtype, c->n, c->z, x, y, o);
+                       }, &c);
+}
+
+int accblas_asum_host(accblas_stream_t stream, int dtype, int64_t n, const void *x_host, void *out_host)
+{
+    if (bad_dtype(dtype)) return ACCBLAS_ERR_DTYPE;
+    if (n < 0) return ACCBLAS_ERR_SHAPE;
+    if (!out_host || (n > 0 && !x_host)) return ACCBLAS_ERR_NULL;
+    L1Ctx c{dtype, n, nullptr, 0};
+    const size_t ob = (dtype == ACCBLAS_F32 || dtype == ACCBLAS_C32) ? 4 : 8;
+    return level1_host(static_cast<cudaStream_t>(stream), elem_size(dtype), n, x_host, nullptr, ob, out_host,
+                       [](cudaStream_t s, const void *x, const void *, void *o, void *cv) {
+                           auto *c = static_cast<L1Ctx *>(cv);
+                           return accblas_asum(s, c->dtype, c->n, x, o);
+                       }, &c);
+}
+
+static int iamax_host(accblas_stream_t stream, int dtype, int want_max, int64_t n, const void *x_host, int64_t *out_host)
+{
+    if (bad_dtype(dtype)) return ACCBLAS_ERR_DTYPE;
+    if (n <= 0) return ACCBLAS_ERR_SHAPE;
+    if (!out_host || !x_host) return ACCBLAS_ERR_NULL;
+    L1Ctx c{dtype, n, nullptr, want_max};
+    return level1_host(static_cast<cudaStream_t>(stream), elem_size(dtype), n, x_host, nullptr, 8, out_host,
+                       [](cudaStream_t s, const void *x, const void *, void *o, void *cv) {
+                           auto *c = static_cast<L1Ctx *>(cv);
+                           return iamax_entry(s, c->dtype, c->want_max, c->n, x, static_cast<int64_t *>(o));
+                       }, &c);
+}
+int accblas_amax_host(accblas_stream_t stream, int dtype, int64_t n, const void *x_host, int64_t *out_host)
+{
+    return iamax_host(stream, dtype, 1, n, x_host, out_host);
+}
+int accblas_amin_host(accblas_stream_t stream, int dtype, int64_t n, const void *x_host, int64_t *out_host)
+{
+    return iamax_host(stream, dtype, 0, n, x_host, out_host);
 }
 
 }  // extern "C"

@@ -133,6 +133,7 @@ int gemm_device(GemmArgs &g);                         // api.cu : validate + dis
 int gemm_host_pipeline(const GemmArgs &g, const void *A_host, const void *B_host,
                        void *C_host);                 // host_pipeline.cu : upload / multiply / download wavefront
 int gemm_generic(const GemmArgs &g);                  // gemm_generic.cu : any shape
+int gemm_rank1(const GemmArgs &g);                    // gemm_generic.cu : k == 1 (outer product `><`)
 bool dgemm_dmma_eligible(const GemmArgs &g);          // gemm_dmma.cu    : f64 / c64 on DMMA
 int  dgemm_dmma(const GemmArgs &g);
 bool sgemm_tc_eligible(const GemmArgs &g);            // gemm_tf32x3.cu  : f32 / c32 on tcgen05
@@ -143,5 +144,10 @@ int gemv_dispatch(cudaStream_t s, int dtype, int opA, int64_t rowsA, int64_t col
                   const void *alpha, const void *A, const void *x, void *y);          // gemv.cu
 int dot_dispatch(cudaStream_t s, int dtype, int conj_x, int64_t n,
                  const void *x, const void *y, void *out);                            // dot.cu
+
+int sdot_dispatch(cudaStream_t s, int dtype, int64_t n, const void *z_host,
+                  const void *x, const void *y, void *out);                           // level1.cu
+int asum_dispatch(cudaStream_t s, int dtype, int64_t n, const void *x, void *out);
+int iamax_dispatch(cudaStream_t s, int dtype, int want_max, int64_t n, const void *x, int64_t *out);
 
 }  // namespace accblas

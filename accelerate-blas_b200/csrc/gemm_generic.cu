@@ -111,7 +111,83 @@ int launch_typed(const GemmArgs &g)
     return check_launch("gemm_generic_kernel");
 }
 
+// ---------------------------------------------------------------------------------------
+// k = 1: the outer product `x >< y = (len x, 1) <> (1, len y)` (LinearAlgebra.hs:73-78) and every
+// other product with inner extent 1.  C[i][j] = (alpha * a_i) * b_j is a pure store stream:
+// m * n * sizeof(T) bytes, no reuse worth a tile.  Each thread owns a 16-byte column vector and
+// walks ROWS_PER_CTA rows; a_i, b_j come through the read-only path (b_j is re-used from registers
+// across the rows).  Element strides cover all op / pitch cases: op(A)[i] = A[i * sa], op(B)[j] = B[j * sb].
+// ---------------------------------------------------------------------------------------
+constexpr int R1_THREADS = 256, R1_ROWS = 8;
+
+template <typename T>
+__global__ void __launch_bounds__(R1_THREADS)
+gemm_rank1_kernel(int64_t m, int64_t n, int64_t sa, int64_t sb, int64_t ldc, bool conjA, bool conjB, T alpha,
+                  const T *__restrict__ A, const T *__restrict__ B, T *__restrict__ C, bool vec_ok)
+{
+    constexpr int VEC = 16 / sizeof(T);
+    const int64_t j0 = ((int64_t)blockIdx.x * R1_THREADS + threadIdx.x) * VEC;
+    const int64_t i0 = (int64_t)blockIdx.y * R1_ROWS;
+    if (j0 >= n) return;
+    T b[VEC];
+#pragma unroll
+    for (int e = 0; e < VEC; ++e) {
+        b[e] = j0 + e < n ? __ldg(B + (j0 + e) * sb) : Scalar<T>::zero();
+        if (conjB) b[e] = conj_s(b[e]);
+    }
+    const bool full = vec_ok && j0 + VEC <= n;
+#pragma unroll
+    for (int r = 0; r < R1_ROWS; ++r) {
+        const int64_t i = i0 + r;
+        if (i >= m) break;
+        T a = __ldg(A + i * sa);
+        if (conjA) a = conj_s(a);
+        a = mul_s(alpha, a);                                   // (alpha * a) * b, BLAS/Level3.hs:89
+        T *crow = C + i * ldc + j0;
+        if (full) {
+            union { int4 raw; T e[VEC]; } v;
+#pragma unroll
+            for (int e = 0; e < VEC; ++e) v.e[e] = mul_s(a, b[e]);
+            *reinterpret_cast<int4 *>(crow) = v.raw;
+        } else {
+#pragma unroll
+            for (int e = 0; e < VEC; ++e)
+                if (j0 + e < n) crow[e] = mul_s(a, b[e]);
+        }
+    }
+}
+
+template <typename T>
+int launch_rank1(const GemmArgs &g)
+{
+    constexpr int VEC = 16 / sizeof(T);
+    const T alpha = *static_cast<const T *>(g.alpha);
+    const bool ca = Scalar<T>::cplx && g.opA == ACCBLAS_OP_H, cb = Scalar<T>::cplx && g.opB == ACCBLAS_OP_H;
+    // op(A) is m x 1: stored (m x 1, pitch lda) for N, stored (1 x m) for T/H
+    const int64_t sa = g.opA == ACCBLAS_OP_N ? g.lda : 1;
+    // op(B) is 1 x n: stored (1 x n) for N, stored (n x 1, pitch ldb) for T/H
+    const int64_t sb = g.opB == ACCBLAS_OP_N ? 1 : g.ldb;
+    const bool vec_ok = (reinterpret_cast<uintptr_t>(g.C) & 15u) == 0 && (g.ldc % VEC) == 0;
+    dim3 grid((unsigned)((g.n + (int64_t)R1_THREADS * VEC - 1) / ((int64_t)R1_THREADS * VEC)),
+              (unsigned)((g.m + R1_ROWS - 1) / R1_ROWS));
+    if (grid.y > 65535u) return gemm_generic(g);               // enormous m: the tiled kernel's grid fits
+    gemm_rank1_kernel<T><<<grid, R1_THREADS, 0, g.stream>>>(g.m, g.n, sa, sb, g.ldc, ca, cb, alpha,
+                                                            static_cast<const T *>(g.A), static_cast<const T *>(g.B),
+                                                            static_cast<T *>(g.C), vec_ok);
+    return check_launch("gemm_rank1_kernel");
+}
+
 }  // namespace
+
+int gemm_rank1(const GemmArgs &g)
+{
+    switch (g.dtype) {
+    case ACCBLAS_F32: return launch_rank1<float>(g);
+    case ACCBLAS_F64: return launch_rank1<double>(g);
+    case ACCBLAS_C32: return launch_rank1<float2>(g);
+    default:          return launch_rank1<double2>(g);
+    }
+}
 
 int gemm_generic(const GemmArgs &g)
 {

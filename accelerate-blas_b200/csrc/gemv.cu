@@ -16,6 +16,7 @@
 //      per-split partial rows are summed in split order by a second tiny kernel
 //      (deterministic, no atomics).
 #include "common.cuh"
+#include <cstdlib>
 
 namespace accblas {
 namespace {
@@ -159,6 +160,70 @@ gemv_t_kernel(int64_t m, int64_t n, int64_t rows_per_split, T alpha, const T *__
     }
 }
 
+// Small and medium matrices (the reference's own benchmark shapes, 200 x 400 .. 2000 x 3000,
+// bench/Bench/Accelerate.hs:53-58): ONE launch, no scratch.  A CTA owns a slab of SLAB_CV 16-byte
+// column vectors (128 contiguous bytes of every row) and splits the rows over SLAB_RG row groups;
+// a warp load touches 4 rows x 128 bytes = four whole lines.  The row groups are summed through
+// shared memory in a fixed order (deterministic).  Parallelism is columns / SLAB_CV CTAs, which is
+// enough to fill the GPU exactly where the two-pass kernel above is launch-bound.
+constexpr int SLAB_CV = 8, SLAB_RG = 32, SLAB_UNROLL = 8;
+
+template <typename T, bool CONJ, bool ALIGNED>
+__global__ void __launch_bounds__(SLAB_CV * SLAB_RG)
+gemv_t_slab_kernel(int64_t m, int64_t n, T alpha, const T *__restrict__ A, const T *__restrict__ x,
+                   T *__restrict__ y)
+{
+    constexpr int VEC = ALIGNED ? 16 / sizeof(T) : 1;
+    __shared__ T red[SLAB_RG][SLAB_CV * VEC + 1];
+    const int cv = threadIdx.x % SLAB_CV, rg = threadIdx.x / SLAB_CV;
+    const int64_t nv = (n + VEC - 1) / VEC;
+    const int64_t v = (int64_t)blockIdx.x * SLAB_CV + cv;
+    const bool active = v < nv;
+    T acc[VEC];
+#pragma unroll
+    for (int e = 0; e < VEC; ++e) acc[e] = Scalar<T>::zero();
+    if (active) {
+        const char *p = reinterpret_cast<const char *>(A) + v * (int64_t)(VEC * sizeof(T));
+        const int64_t pitch = n * (int64_t)sizeof(T);
+        int64_t r = rg;
+        for (; r + (int64_t)(SLAB_UNROLL - 1) * SLAB_RG < m; r += (int64_t)SLAB_UNROLL * SLAB_RG) {
+            Vec16<T> av[SLAB_UNROLL];
+            T xi[SLAB_UNROLL];
+#pragma unroll
+            for (int u = 0; u < SLAB_UNROLL; ++u) {
+                const int64_t rr = r + (int64_t)u * SLAB_RG;
+                if (ALIGNED) av[u].raw = ldg_stream(p + rr * pitch);
+                else av[u].e[0] = *reinterpret_cast<const T *>(p + rr * pitch);
+                xi[u] = __ldg(x + rr);
+            }
+#pragma unroll
+            for (int u = 0; u < SLAB_UNROLL; ++u)
+#pragma unroll
+                for (int e = 0; e < VEC; ++e) acc[e] = fma_acc(CONJ ? conj_s(av[u].e[e]) : av[u].e[e], xi[u], acc[e]);
+        }
+        for (; r < m; r += SLAB_RG) {
+            Vec16<T> av;
+            if (ALIGNED) av.raw = ldg_stream(p + r * pitch);
+            else av.e[0] = *reinterpret_cast<const T *>(p + r * pitch);
+            const T xi = __ldg(x + r);
+#pragma unroll
+            for (int e = 0; e < VEC; ++e) acc[e] = fma_acc(CONJ ? conj_s(av.e[e]) : av.e[e], xi, acc[e]);
+        }
+    }
+#pragma unroll
+    for (int e = 0; e < VEC; ++e) red[rg][cv * VEC + e] = acc[e];
+    __syncthreads();
+    if (threadIdx.x < SLAB_CV * VEC) {
+        const int64_t j = (int64_t)blockIdx.x * SLAB_CV * VEC + threadIdx.x;
+        if (j < n) {
+            T s = Scalar<T>::zero();
+#pragma unroll 8
+            for (int g = 0; g < SLAB_RG; ++g) s = add_s(s, red[g][threadIdx.x]);
+            y[j] = mul_s(alpha, s);
+        }
+    }
+}
+
 template <typename T>
 __global__ void __launch_bounds__(256)
 gemv_t_reduce_kernel(int64_t n, int splits, T alpha, const T *__restrict__ partial, T *__restrict__ y)
@@ -216,6 +281,15 @@ int gemv_typed(cudaStream_t st, int opA, int64_t rowsA, int64_t colsA, const voi
 
     const bool conj = Scalar<T>::cplx && opA == ACCBLAS_OP_H;
     const int64_t nv = aligned ? colsA / VEC : colsA;
+    static const int64_t slab_max = [] { const char *e = getenv("ACCBLAS_GEMV_T_SLAB_MAX"); return e ? atoll(e) : (int64_t)64 << 20; }();
+    if ((int64_t)sizeof(T) * rowsA * colsA <= slab_max) {       // one launch, no scratch
+        const unsigned grid = (unsigned)((nv + SLAB_CV - 1) / SLAB_CV);
+#define GO(CJ, AL) gemv_t_slab_kernel<T, CJ, AL><<<grid, SLAB_CV * SLAB_RG, 0, st>>>(rowsA, colsA, alpha, A, x, y)
+        if (aligned) { if (conj) GO(true, true); else GO(false, true); }
+        else         { if (conj) GO(true, false); else GO(false, false); }
+#undef GO
+        return check_launch("gemv_t_slab_kernel");
+    }
     const int64_t gx = (nv + GT_THREADS - 1) / GT_THREADS;
     static thread_local int occ_t = 0;
     if (!occ_t) occ_t = occupancy(gemv_t_kernel<T, false, true>, GT_THREADS);

@@ -237,3 +237,208 @@ int sdot_typed(cudaStream_t st, int64_t n, const void *z_host, const T *x, const
     }
     return s;
 }
+
+// =============================================================================================
+// asum: sum of magnitudes, accumulated in double, rounded once to the element's base type
+// =============================================================================================
+template <typename T, bool ALIGNED>
+__global__ void __launch_bounds__(L1_THREADS, 2)
+asum_partial_kernel(int64_t n, const T *__restrict__ x, double *__restrict__ partial,
+                    typename Scalar<T>::real *__restrict__ out)
+{
+    __shared__ double red[L1_THREADS / 32];
+    double acc[L1_UNROLL];
+#pragma unroll
+    for (int u = 0; u < L1_UNROLL; ++u) acc[u] = 0.0;
+    for_each1<T, ALIGNED>(n, x, [&](int u, int64_t, T a) {
+        if constexpr (Scalar<T>::cplx) acc[u] += (double)fabs(a.x) + (double)fabs(a.y);
+        else acc[u] += (double)fabs(a);
+    });
+    double s = (acc[0] + acc[1]) + (acc[2] + acc[3]);
+    s = block_sum(s, red);
+    if (threadIdx.x == 0) {
+        if (gridDim.x == 1) *out = (typename Scalar<T>::real)s;
+        else partial[blockIdx.x] = s;
+    }
+}
+
+template <typename R>
+__global__ void __launch_bounds__(L1_THREADS)
+asum_final_kernel(int nparts, const double *__restrict__ partial, R *__restrict__ out)
+{
+    __shared__ double red[L1_THREADS / 32];
+    double s = 0.0;
+    for (int i = threadIdx.x; i < nparts; i += L1_THREADS) s += partial[i];
+    s = block_sum(s, red);
+    if (threadIdx.x == 0) *out = (R)s;
+}
+
+template <typename T>
+int asum_typed(cudaStream_t st, int64_t n, const T *x, void *out_v)
+{
+    using R = typename Scalar<T>::real;
+    R *out = static_cast<R *>(out_v);
+    if (n == 0) {                                  // sum of nothing
+        ACC_CUDA(cudaMemsetAsync(out, 0, sizeof(R), st));
+        return ACCBLAS_OK;
+    }
+    const bool al = aligned16(x);
+    const int grid = grid_for<T>(n, al);
+    double *partial = nullptr;
+    if (grid > 1) ACC_CUDA(cudaMallocAsync(reinterpret_cast<void **>(&partial), sizeof(double) * (size_t)grid, st));
+    if (al) asum_partial_kernel<T, true><<<grid, L1_THREADS, 0, st>>>(n, x, partial, out);
+    else    asum_partial_kernel<T, false><<<grid, L1_THREADS, 0, st>>>(n, x, partial, out);
+    int s = check_launch("asum_partial_kernel");
+    if (grid > 1) {
+        if (s == ACCBLAS_OK) {
+            asum_final_kernel<R><<<1, L1_THREADS, 0, st>>>(grid, partial, out);
+            s = check_launch("asum_final_kernel");
+        }
+        cudaError_t e = cudaFreeAsync(partial, st);
+        if (s == ACCBLAS_OK && e != cudaSuccess) return cuda_fail(e, "cudaFreeAsync");
+    }
+    return s;
+}
+
+// =============================================================================================
+// amax / amin: (magnitude, index) pairs; combine = better magnitude, then LARGER index
+// =============================================================================================
+template <typename R> struct Best { R v; int64_t i; };
+
+template <bool MAX, typename R>
+__device__ __forceinline__ bool better(R v, int64_t i, R bv, int64_t bi)
+{
+    // "better or equal-and-later": the reference's cmp keeps the right operand unless the left is
+    // strictly better (BLAS/Level1.hs:124,141).  bi < 0 marks an empty slot.
+    if (bi < 0) return true;
+    if (i < 0) return false;
+    return MAX ? (v > bv || (v == bv && i > bi)) : (v < bv || (v == bv && i > bi));
+}
+
+template <bool MAX, typename R>
+__device__ __forceinline__ Best<R> warp_best(Best<R> b)
+{
+#pragma unroll
+    for (int m = 16; m > 0; m >>= 1) {
+        const R ov = __shfl_xor_sync(0xffffffffu, b.v, m);
+        const int64_t oi = __shfl_xor_sync(0xffffffffu, b.i, m);
+        if (better<MAX>(ov, oi, b.v, b.i)) { b.v = ov; b.i = oi; }
+    }
+    return b;
+}
+
+template <bool MAX, typename R>
+__device__ __forceinline__ Best<R> block_best(Best<R> b, R *sv, int64_t *si)
+{
+    b = warp_best<MAX>(b);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) { sv[warp] = b.v; si[warp] = b.i; }
+    __syncthreads();
+    if (warp == 0) {
+        if (lane < (int)(blockDim.x >> 5)) { b.v = sv[lane]; b.i = si[lane]; }
+        else { b.v = (R)0; b.i = -1; }
+        b = warp_best<MAX>(b);
+    }
+    return b;   // valid in warp 0
+}
+
+template <typename T, bool MAX, bool ALIGNED>
+__global__ void __launch_bounds__(L1_THREADS, 2)
+iamax_partial_kernel(int64_t n, const T *__restrict__ x, typename Scalar<T>::real *__restrict__ pv,
+                     int64_t *__restrict__ pi, int64_t *__restrict__ out)
+{
+    using R = typename Scalar<T>::real;
+    __shared__ R sv[L1_THREADS / 32];
+    __shared__ int64_t si[L1_THREADS / 32];
+    Best<R> b[L1_UNROLL];
+#pragma unroll
+    for (int u = 0; u < L1_UNROLL; ++u) { b[u].v = (R)0; b[u].i = -1; }
+    for_each1<T, ALIGNED>(n, x, [&](int u, int64_t i, T a) {
+        const R v = mag(a);
+        if (better<MAX>(v, i, b[u].v, b[u].i)) { b[u].v = v; b[u].i = i; }
+    });
+#pragma unroll
+    for (int u = 1; u < L1_UNROLL; ++u)
+        if (better<MAX>(b[u].v, b[u].i, b[0].v, b[0].i)) b[0] = b[u];
+    Best<R> r = block_best<MAX>(b[0], sv, si);
+    if (threadIdx.x == 0) {
+        if (gridDim.x == 1) *out = r.i;
+        else { pv[blockIdx.x] = r.v; pi[blockIdx.x] = r.i; }
+    }
+}
+
+template <typename R, bool MAX>
+__global__ void __launch_bounds__(L1_THREADS)
+iamax_final_kernel(int nparts, const R *__restrict__ pv, const int64_t *__restrict__ pi, int64_t *__restrict__ out)
+{
+    __shared__ R sv[L1_THREADS / 32];
+    __shared__ int64_t si[L1_THREADS / 32];
+    Best<R> b; b.v = (R)0; b.i = -1;
+    for (int i = threadIdx.x; i < nparts; i += L1_THREADS)
+        if (better<MAX>(pv[i], pi[i], b.v, b.i)) { b.v = pv[i]; b.i = pi[i]; }
+    b = block_best<MAX>(b, sv, si);
+    if (threadIdx.x == 0) *out = b.i;
+}
+
+template <typename T, bool MAX>
+int iamax_typed(cudaStream_t st, int64_t n, const T *x, int64_t *out)
+{
+    using R = typename Scalar<T>::real;
+    const bool al = aligned16(x);
+    const int grid = grid_for<T>(n, al);
+    char *ws = nullptr;
+    R *pv = nullptr; int64_t *pi = nullptr;
+    if (grid > 1) {
+        ACC_CUDA(cudaMallocAsync(reinterpret_cast<void **>(&ws), 16 * (size_t)grid, st));
+        pi = reinterpret_cast<int64_t *>(ws);
+        pv = reinterpret_cast<R *>(ws + 8 * (size_t)grid);
+    }
+    if (al) iamax_partial_kernel<T, MAX, true><<<grid, L1_THREADS, 0, st>>>(n, x, pv, pi, out);
+    else    iamax_partial_kernel<T, MAX, false><<<grid, L1_THREADS, 0, st>>>(n, x, pv, pi, out);
+    int s = check_launch("iamax_partial_kernel");
+    if (grid > 1) {
+        if (s == ACCBLAS_OK) {
+            iamax_final_kernel<R, MAX><<<1, L1_THREADS, 0, st>>>(grid, pv, pi, out);
+            s = check_launch("iamax_final_kernel");
+        }
+        cudaError_t e = cudaFreeAsync(ws, st);
+        if (s == ACCBLAS_OK && e != cudaSuccess) return cuda_fail(e, "cudaFreeAsync");
+    }
+    return s;
+}
+
+}  // namespace
+
+int sdot_dispatch(cudaStream_t s, int dtype, int64_t n, const void *z_host, const void *x, const void *y, void *out)
+{
+    switch (dtype) {
+    case ACCBLAS_F32: return sdot_typed<float>(s, n, z_host, (const float *)x, (const float *)y, (float *)out);
+    case ACCBLAS_F64: return sdot_typed<double>(s, n, z_host, (const double *)x, (const double *)y, (double *)out);
+    case ACCBLAS_C32: return sdot_typed<float2>(s, n, z_host, (const float2 *)x, (const float2 *)y, (float2 *)out);
+    default:          return sdot_typed<double2>(s, n, z_host, (const double2 *)x, (const double2 *)y, (double2 *)out);
+    }
+}
+
+int asum_dispatch(cudaStream_t s, int dtype, int64_t n, const void *x, void *out)
+{
+    switch (dtype) {
+    case ACCBLAS_F32: return asum_typed<float>(s, n, (const float *)x, out);
+    case ACCBLAS_F64: return asum_typed<double>(s, n, (const double *)x, out);
+    case ACCBLAS_C32: return asum_typed<float2>(s, n, (const float2 *)x, out);
+    default:          return asum_typed<double2>(s, n, (const double2 *)x, out);
+    }
+}
+
+int iamax_dispatch(cudaStream_t s, int dtype, int want_max, int64_t n, const void *x, int64_t *out)
+{
+#define GO(T) (want_max ? iamax_typed<T, true>(s, n, (const T *)x, out) : iamax_typed<T, false>(s, n, (const T *)x, out))
+    switch (dtype) {
+    case ACCBLAS_F32: return GO(float);
+    case ACCBLAS_F64: return GO(double);
+    case ACCBLAS_C32: return GO(float2);
+    default:          return GO(double2);
+    }
+#undef GO
+}
+
+}  // namespace accblas

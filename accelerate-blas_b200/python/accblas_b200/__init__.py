@@ -34,7 +34,7 @@ import numpy as np
 from . import _ffi
 from ._ffi import AccblasError, lib  # noqa: F401
 
-__all__ = ["N", "T", "H", "gemm", "gemv", "dotu", "dotc", "mXm", "mXv", "vXm", "dot", "outer",
+__all__ = ["N", "T", "H", "gemm", "gemv", "dotu", "dotc", "sdot", "asum", "amax", "amin", "mXm", "mXv", "vXm", "dot", "outer",
            "AccblasError", "kernel_name", "launch_count", "set_gemm_path", "version"]
 
 # Transpose -- Type.hs:78-90
@@ -234,6 +234,71 @@ def dotc(x, y):
     if _code(x) not in (C32, C64):
         raise TypeError("dotc: Numeric (Complex e) required (BLAS/Level1.hs:85)")
     return _dot(x, y, True)
+
+
+def sdot(z, x, y):
+    """``z + sum_i x_i * y_i`` with double-precision products and accumulation, rounded once to
+    the element type -- sdot, BLAS/Level1.hs:44-62."""
+    code = _code(x)
+    z_keep, zp = _alpha_buf(z, code)
+    L = lib()
+    if _is_torch(x):
+        torch = _torch()
+        x = _dev_operand(x, code, 1, "sdot: x")
+        y = _dev_operand(y, code, 1, "sdot: y")
+        n = min(x.shape[0], y.shape[0])
+        with torch.cuda.device(x.device):
+            out = torch.empty((), dtype=x.dtype, device=x.device)
+            st = L.accblas_sdot(_stream(x), code, n, zp, _ptr(x), _ptr(y), _ptr(out))
+        _ffi.check(st, "accblas_sdot")
+        return out
+    x = _host_operand(x, code, 1, "sdot: x")
+    y = _host_operand(y, code, 1, "sdot: y")
+    out = np.zeros((1,), dtype=x.dtype)
+    st = L.accblas_sdot_host(None, code, min(x.shape[0], y.shape[0]), zp, _ptr(x), _ptr(y), _ptr(out))
+    _ffi.check(st, "accblas_sdot_host")
+    return out[0]
+
+
+def _reduce1(x, fn_dev, fn_host, out_np_dtype, where):
+    code = _code(x)
+    L = lib()
+    if _is_torch(x):
+        torch = _torch()
+        x = _dev_operand(x, code, 1, where + ": x")
+        tdt = {np.dtype(np.float32): torch.float32, np.dtype(np.float64): torch.float64,
+               np.dtype(np.int64): torch.int64}[np.dtype(out_np_dtype(code))]
+        with torch.cuda.device(x.device):
+            out = torch.empty((), dtype=tdt, device=x.device)
+            st = getattr(L, fn_dev)(_stream(x), code, x.shape[0], _ptr(x), _ptr(out))
+        _ffi.check(st, fn_dev)
+        return out
+    x = _host_operand(x, code, 1, where + ": x")
+    out = np.zeros((1,), dtype=out_np_dtype(code))
+    st = getattr(L, fn_host)(None, code, x.shape[0], _ptr(x), _ptr(out))
+    _ffi.check(st, fn_host)
+    return out[0]
+
+
+def _base(code):
+    return np.float32 if code in (F32, C32) else np.float64
+
+
+def asum(x):
+    """``sum_i |x_i|`` (complex: ``|re| + |im|``), in the element's base type -- asum, BLAS/Level1.hs:100-109."""
+    return _reduce1(x, "accblas_asum", "accblas_asum_host", _base, "asum")
+
+
+def amax(x):
+    """Index (int64) of the element of largest magnitude, the LAST one among ties -- amax,
+    BLAS/Level1.hs:115-126 (`cmp ix iy = snd ix > snd iy ? ix : iy`)."""
+    return _reduce1(x, "accblas_amax", "accblas_amax_host", lambda c: np.int64, "amax")
+
+
+def amin(x):
+    """Index (int64) of the element of smallest magnitude, the LAST one among ties -- amin,
+    BLAS/Level1.hs:132-143."""
+    return _reduce1(x, "accblas_amin", "accblas_amin_host", lambda c: np.int64, "amin")
 
 
 # ------------------------------------------------------------------------------------

@@ -16,6 +16,8 @@ LIB_PATH = os.environ.get("ACCBLAS_B200_LIB", os.path.join(PKG_ROOT, "lib", "lib
 SYMBOLS = (
     "accblas_gemm", "accblas_gemm_ld", "accblas_gemm_workspace_bytes", "accblas_gemv", "accblas_dot",
     "accblas_gemm_host", "accblas_gemv_host", "accblas_dot_host",
+    "accblas_sdot", "accblas_asum", "accblas_amax", "accblas_amin",
+    "accblas_sdot_host", "accblas_asum_host", "accblas_amax_host", "accblas_amin_host",
     "accblas_version", "accblas_status_string", "accblas_last_cuda_error",
     "accblas_gemm_kernel_name", "accblas_launch_count", "accblas_set_gemm_path",
     "accblas_peer_export", "accblas_peer_open", "accblas_peer_close_all", "accblas_peer_copy2d",
@@ -58,6 +60,13 @@ def lib() -> ctypes.CDLL:
     L.accblas_gemv_host.argtypes = L.accblas_gemv.argtypes
     L.accblas_dot.argtypes = [vp, ci, ci, i64, vp, vp, vp]
     L.accblas_dot_host.argtypes = L.accblas_dot.argtypes
+    L.accblas_sdot.argtypes = [vp, ci, i64, vp, vp, vp, vp]
+    L.accblas_sdot_host.argtypes = L.accblas_sdot.argtypes
+    for f in (L.accblas_asum, L.accblas_asum_host, L.accblas_amax, L.accblas_amax_host, L.accblas_amin,
+              L.accblas_amin_host):
+        f.argtypes = [vp, ci, i64, vp, vp]
+        f.restype = ci
+    L.accblas_sdot.restype = L.accblas_sdot_host.restype = ci
     for f in (L.accblas_gemm, L.accblas_gemm_host, L.accblas_gemv, L.accblas_gemv_host, L.accblas_dot,
               L.accblas_dot_host, L.accblas_version):
         f.restype = ci

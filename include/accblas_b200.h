@@ -127,6 +127,27 @@ int accblas_dot(accblas_stream_t stream, int dtype, int conj_x, int64_t n,
                 const void *x, const void *y, void *out_dev);
 
 /* ------------------------------------------------------------------------------------
+ * The other Level-1 reductions of the reference (BLAS/Level1.hs).  Like dot they are plain
+ * Accelerate folds there -- NEW hooks, one pass over HBM each, result in DEVICE memory.
+ *
+ *   sdot z xs ys  (Level1.hs:44-62)   out = z + sum_i x_i * y_i with every product and the sum in
+ *                 DOUBLE precision whatever the element type, rounded once to `dtype` at the end
+ *                 (`dsdot` / `zsdot`).  z_host: one element of `dtype` in host memory.
+ *   asum xs       (Level1.hs:100-109) out = sum_i |x_i|, complex: |re| + |im|.  The result has the
+ *                 element's BASE type (NumericBaseT: float for F32/C32, double for F64/C64).
+ *   amax / amin   (Level1.hs:115-143) 0-based index (int64, the reference's `Int`) of the element
+ *                 of largest / smallest magnitude (same magnitude as asum, computed in the
+ *                 element's precision).  On ties the LAST such index is returned: the reference's
+ *                 `cmp ix iy = snd ix > snd iy ? ix : iy` keeps the right operand (cblas_i?amax
+ *                 returns the first).  n == 0 is ACCBLAS_ERR_SHAPE (fold1 of an empty array).
+ * ---------------------------------------------------------------------------------- */
+int accblas_sdot(accblas_stream_t stream, int dtype, int64_t n, const void *z_host,
+                 const void *x, const void *y, void *out_dev);
+int accblas_asum(accblas_stream_t stream, int dtype, int64_t n, const void *x, void *out_dev);
+int accblas_amax(accblas_stream_t stream, int dtype, int64_t n, const void *x, int64_t *out_dev);
+int accblas_amin(accblas_stream_t stream, int dtype, int64_t n, const void *x, int64_t *out_dev);
+
+/* ------------------------------------------------------------------------------------
  * Host-buffer entry points: what `run (A <> B)` does end to end in the reference --
  * `use` uploads the host arrays, the hook runs, the result is copied back
  * (test/Test/BLAS/Level3.hs:52-54; bench/Bench/Accelerate.hs:111-114).  A, B, x, y, C,
@@ -144,6 +165,12 @@ int accblas_gemv_host(accblas_stream_t stream, int dtype, int opA, int64_t rowsA
                       void *y_host);
 int accblas_dot_host(accblas_stream_t stream, int dtype, int conj_x, int64_t n,
                      const void *x_host, const void *y_host, void *out_host);
+
+int accblas_sdot_host(accblas_stream_t stream, int dtype, int64_t n, const void *z_host,
+                      const void *x_host, const void *y_host, void *out_host);
+int accblas_asum_host(accblas_stream_t stream, int dtype, int64_t n, const void *x_host, void *out_host);
+int accblas_amax_host(accblas_stream_t stream, int dtype, int64_t n, const void *x_host, int64_t *out_host);
+int accblas_amin_host(accblas_stream_t stream, int dtype, int64_t n, const void *x_host, int64_t *out_host);
 
 /* ------------------------------------------------------------------------------------
  * Peer memory (one process per GPU, NVLink / NVSwitch).  NEW: the reference has no multi-GPU

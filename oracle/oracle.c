@@ -13,6 +13,8 @@
  *   mXv   src/Data/Array/Accelerate/Numeric/LinearAlgebra/BLAS/Level2.hs:79-93
  *   dotu  src/Data/Array/Accelerate/Numeric/LinearAlgebra/BLAS/Level1.hs:73-74
  *   dotc  src/Data/Array/Accelerate/Numeric/LinearAlgebra/BLAS/Level1.hs:85-92
+ *   sdot  src/Data/Array/Accelerate/Numeric/LinearAlgebra/BLAS/Level1.hs:44-62
+ *   asum / amax / amin   src/.../BLAS/Level1.hs:100-109, 115-126, 132-143
  *
  * shape rules follow the hooks:
  *   gemm  src/.../LLVM/PTX/Level3.hs:54-65   (m,k) = opA==N ? (rowsA,colsA) : (colsA,rowsA);
@@ -234,4 +236,103 @@ int oracle_dot(int dtype, int wide, int conj_x, int64_t n,
     return 0;
 }
 
-int oracle_abi_version(void) { return 1; }
+/*
+ * sdot z xs ys (Level1.hs:44-62): every element is converted to double (complex double), the
+ * products are summed by a left fold STARTING FROM z (`fold (+) z' (zipWith (*) xs' ys')`), and the
+ * result is converted back to the element type.  literal (wide = 0) is that double-precision fold;
+ * wide = 1 carries the sum in long double (the truth error bounds are measured against).
+ */
+int oracle_sdot(int dtype, int wide, int64_t n, const void *z, const void *x, const void *y, void *out)
+{
+    if (bad_dtype(dtype) || n < 0) return 1;
+    const int cplx = dtype == DT_C32 || dtype == DT_C64;
+    const int f32 = dtype == DT_F32 || dtype == DT_C32;
+#define LD(p, i) (f32 ? (double)((const float *)(p))[i] : ((const double *)(p))[i])
+    if (!cplx) {
+        if (wide) { long double s = LD(z, 0); for (int64_t i = 0; i < n; ++i) s += (long double)LD(x, i) * (long double)LD(y, i);
+                    if (f32) *(float *)out = (float)(double)s; else *(double *)out = (double)s; }
+        else      { double s = LD(z, 0); for (int64_t i = 0; i < n; ++i) s = s + LD(x, i) * LD(y, i);
+                    if (f32) *(float *)out = (float)s; else *(double *)out = s; }
+    } else {
+        if (wide) {
+            long double sr = LD(z, 0), si = LD(z, 1);
+            for (int64_t i = 0; i < n; ++i) {
+                long double ar = LD(x, 2*i), ai = LD(x, 2*i+1), br = LD(y, 2*i), bi = LD(y, 2*i+1);
+                sr += ar * br - ai * bi; si += ar * bi + ai * br;
+            }
+            if (f32) { ((float *)out)[0] = (float)(double)sr; ((float *)out)[1] = (float)(double)si; }
+            else     { ((double *)out)[0] = (double)sr; ((double *)out)[1] = (double)si; }
+        } else {
+            double sr = LD(z, 0), si = LD(z, 1);
+            for (int64_t i = 0; i < n; ++i) {
+                double ar = LD(x, 2*i), ai = LD(x, 2*i+1), br = LD(y, 2*i), bi = LD(y, 2*i+1);
+                double p1 = ar * br, p2 = ai * bi, p3 = ar * bi, p4 = ai * br;
+                sr = sr + (p1 - p2); si = si + (p3 + p4);
+            }
+            if (f32) { ((float *)out)[0] = (float)sr; ((float *)out)[1] = (float)si; }
+            else     { ((double *)out)[0] = sr; ((double *)out)[1] = si; }
+        }
+    }
+    return 0;
+}
+
+/*
+ * asum (Level1.hs:100-109): `sum . map abs`, complex `mag c = abs (real c) + abs (imag c)`; the
+ * result has the element's base type.  literal = element-precision left fold; wide = long double.
+ */
+int oracle_asum(int dtype, int wide, int64_t n, const void *x, void *out)
+{
+    if (bad_dtype(dtype) || n < 0) return 1;
+    const int cplx = dtype == DT_C32 || dtype == DT_C64;
+    const int f32 = dtype == DT_F32 || dtype == DT_C32;
+    if (f32) {
+        const float *a = x;
+        if (wide) { long double s = 0; for (int64_t i = 0; i < n; ++i) s += cplx ? (long double)__builtin_fabsf(a[2*i]) + __builtin_fabsf(a[2*i+1]) : (long double)__builtin_fabsf(a[i]);
+                    *(float *)out = (float)(double)s; }
+        else      { float s = 0; for (int64_t i = 0; i < n; ++i) { float m = cplx ? __builtin_fabsf(a[2*i]) + __builtin_fabsf(a[2*i+1]) : __builtin_fabsf(a[i]); s = s + m; }
+                    *(float *)out = s; }
+    } else {
+        const double *a = x;
+        if (wide) { long double s = 0; for (int64_t i = 0; i < n; ++i) s += cplx ? (long double)__builtin_fabs(a[2*i]) + __builtin_fabs(a[2*i+1]) : (long double)__builtin_fabs(a[i]);
+                    *(double *)out = (double)s; }
+        else      { double s = 0; for (int64_t i = 0; i < n; ++i) { double m = cplx ? __builtin_fabs(a[2*i]) + __builtin_fabs(a[2*i+1]) : __builtin_fabs(a[i]); s = s + m; }
+                    *(double *)out = s; }
+    }
+    return 0;
+}
+
+/*
+ * amax / amin (Level1.hs:115-143): `fold1 cmp . indexed . map mag` with
+ *   cmp ix iy = snd ix > snd iy ? ix : iy        (amax;  `<` for amin)
+ * restated as the sequential left fold: the accumulator is ix, the next element iy, so the next
+ * element replaces the accumulator unless the accumulator is STRICTLY better -- on ties the later
+ * index wins.  Magnitudes are computed in the element's own precision.  Returns the 0-based index
+ * in *out (int64, Haskell Int); n == 0 is an error (fold1 of an empty array).
+ */
+int oracle_iamax(int dtype, int want_max, int64_t n, const void *x, int64_t *out)
+{
+    if (bad_dtype(dtype) || n <= 0) return 1;
+    const int cplx = dtype == DT_C32 || dtype == DT_C64;
+    int64_t best = 0;
+    if (dtype == DT_F32 || dtype == DT_C32) {
+        const float *a = x;
+        volatile float bv = cplx ? __builtin_fabsf(a[0]) + __builtin_fabsf(a[1]) : __builtin_fabsf(a[0]);
+        for (int64_t i = 1; i < n; ++i) {
+            volatile float v = cplx ? __builtin_fabsf(a[2*i]) + __builtin_fabsf(a[2*i+1]) : __builtin_fabsf(a[i]);
+            const int keep = want_max ? (bv > v) : (bv < v);
+            if (!keep) { bv = v; best = i; }
+        }
+    } else {
+        const double *a = x;
+        volatile double bv = cplx ? __builtin_fabs(a[0]) + __builtin_fabs(a[1]) : __builtin_fabs(a[0]);
+        for (int64_t i = 1; i < n; ++i) {
+            volatile double v = cplx ? __builtin_fabs(a[2*i]) + __builtin_fabs(a[2*i+1]) : __builtin_fabs(a[i]);
+            const int keep = want_max ? (bv > v) : (bv < v);
+            if (!keep) { bv = v; best = i; }
+        }
+    }
+    *out = best;
+    return 0;
+}
+
+int oracle_abi_version(void) { return 2; }

@@ -50,7 +50,10 @@ def lib() -> ctypes.CDLL:
         L.oracle_gemm.argtypes = [ci, ci, ci, ci, i64, i64, i64, i64, vp, vp, vp, vp]
         L.oracle_gemv.argtypes = [ci, ci, ci, i64, i64, vp, vp, vp, i64, vp]
         L.oracle_dot.argtypes = [ci, ci, ci, i64, vp, vp, vp]
-        for f in (L.oracle_gemm, L.oracle_gemv, L.oracle_dot):
+        L.oracle_sdot.argtypes = [ci, ci, i64, vp, vp, vp, vp]
+        L.oracle_asum.argtypes = [ci, ci, i64, vp, vp]
+        L.oracle_iamax.argtypes = [ci, ci, i64, vp, ctypes.POINTER(ctypes.c_int64)]
+        for f in (L.oracle_gemm, L.oracle_gemv, L.oracle_dot, L.oracle_sdot, L.oracle_asum, L.oracle_iamax):
             f.restype = ci
         _lib = L
     return _lib
@@ -110,6 +113,46 @@ def dot(x: np.ndarray, y: np.ndarray, conj: bool = False, wide: bool = True):
     if rc:
         raise ValueError("oracle_dot: bad arguments")
     return out[0]
+
+
+def sdot(z, x: np.ndarray, y: np.ndarray, wide: bool = True):
+    """sdot z xs ys -- BLAS/Level1.hs:44-62: z + sum x_i y_i in double precision, rounded once."""
+    x = np.ascontiguousarray(x)
+    y = np.ascontiguousarray(y, dtype=x.dtype)
+    n = min(x.shape[0], y.shape[0])
+    zz = np.array([z], dtype=x.dtype)
+    out = np.zeros((1,), dtype=x.dtype)
+    if lib().oracle_sdot(_code(x), int(wide), n, _p(zz), _p(x), _p(y), _p(out)):
+        raise ValueError("oracle_sdot: bad arguments")
+    return out[0]
+
+
+def asum(x: np.ndarray, wide: bool = True):
+    """asum -- BLAS/Level1.hs:100-109; result in the element's base type."""
+    x = np.ascontiguousarray(x)
+    base = np.float32 if _code(x) in (F32, C32) else np.float64
+    out = np.zeros((1,), dtype=base)
+    if lib().oracle_asum(_code(x), int(wide), x.shape[0], _p(x), _p(out)):
+        raise ValueError("oracle_asum: bad arguments")
+    return out[0]
+
+
+def _iamax(x: np.ndarray, want_max: bool) -> int:
+    x = np.ascontiguousarray(x)
+    out = ctypes.c_int64(-1)
+    if lib().oracle_iamax(_code(x), int(want_max), x.shape[0], _p(x), ctypes.byref(out)):
+        raise ValueError("oracle_iamax: empty vector (fold1) or bad dtype")
+    return int(out.value)
+
+
+def amax(x: np.ndarray) -> int:
+    """amax -- BLAS/Level1.hs:115-126 (last index among equal maxima)."""
+    return _iamax(x, True)
+
+
+def amin(x: np.ndarray) -> int:
+    """amin -- BLAS/Level1.hs:132-143 (last index among equal minima)."""
+    return _iamax(x, False)
 
 
 # ---------------------------------------------------------------------------------

@@ -214,6 +214,19 @@ def test_gemv_edges(dt, cuda):
         assert O.gemm_error_units(y, O.gemv(al, oa, A, xx), A, xx, xx.shape[0], al) <= TOL_UNITS[dt]
 
 
+@pytest.mark.parametrize("dt", DTYPES, ids=ids)
+def test_gemv_two_pass_path(dt, cuda):
+    """Matrices above 64 MiB take the split-row two-pass T/H kernel (below: the one-launch slab kernel)."""
+    import accblas_b200 as ab
+    rng = np.random.default_rng(5700 + dt)
+    m, n = 4200, 4100
+    for oa in OPN:
+        al, A, x = gemv_inputs(rng, dt, oa, m, n)
+        y = host(ab.gemv(al, oa, dev(A, cuda), dev(x, cuda)))
+        err = O.gemm_error_units(y, O.gemv(al, oa, A, x, wide=True), A, x, x.shape[0], al)
+        assert err <= TOL_UNITS[dt], (O.NAMES[dt], oa, err)
+
+
 def test_gemv_large_roundtrip(cuda):
     """BASELINE-size-independent property at a large shape: A (x1 + x2) == A x1 + A x2, and
     e_i^T A == row i, A e_j == column j (exact)."""
