@@ -12,6 +12,7 @@ namespace accblas {
 thread_local uint64_t g_launches = 0;
 thread_local char g_cuda_err[256] = {0};
 thread_local int g_gemm_path = 0;
+thread_local int g_tuning[ACCBLAS_TUNE_COUNT] = {-1, -1, -1, -1, -1, -1, -1, -1};
 
 int cuda_fail(cudaError_t e, const char *where)
 {
@@ -92,7 +93,11 @@ int derive_gemm(GemmArgs &g)
     return ACCBLAS_OK;
 }
 
-enum Family { FAM_NONE, FAM_GENERIC, FAM_DMMA, FAM_TC, FAM_RANK1 };
+enum Family { FAM_NONE, FAM_GENERIC, FAM_DMMA, FAM_TC, FAM_RANK1, FAM_MMA };
+
+// f32 / c32: the tcgen05 path (pack pass + 128 x 256 tiles) wins once the product fills the GPU with
+// such tiles; below that the one-launch mma.sync path does (profiles/r01_sgemm_families.jsonl)
+constexpr double kTcMinWork = 1.5e9;     // real-equivalent m * n * k (between 1024^3 and 1536^3)
 
 Family pick_family(const GemmArgs &g)
 {
@@ -100,10 +105,20 @@ Family pick_family(const GemmArgs &g)
     if (g_gemm_path == 1) return FAM_GENERIC;
     if (g.k == 1 && g_gemm_path == 0) return FAM_RANK1;          // `><`: a store stream, not a contraction
     if ((g.dtype == ACCBLAS_F64 || g.dtype == ACCBLAS_C64) && dgemm_dmma_eligible(g)) return FAM_DMMA;
-    if ((g.dtype == ACCBLAS_F32 || g.dtype == ACCBLAS_C32) && sgemm_tc_eligible(g)) return FAM_TC;
+    if (g.dtype == ACCBLAS_F32 || g.dtype == ACCBLAS_C32) {
+        const bool tc = sgemm_tc_eligible(g), mma = sgemm_mma_eligible(g);
+        const int want = g_tuning[ACCBLAS_TUNE_SGEMM_FAMILY];
+        if (want == 1 && mma) return FAM_MMA;
+        if (want == 2 && tc) return FAM_TC;
+        const double work = (g.dtype == ACCBLAS_C32 ? 4.0 : 1.0) * (double)g.m * (double)g.n * (double)g.k;
+        if (tc && (work >= kTcMinWork || !mma)) return FAM_TC;
+        if (mma) return FAM_MMA;
+    }
     return FAM_GENERIC;
 }
 
+int run_family(Family f, const GemmArgs &g);
+int gemm_repitched(const GemmArgs &g);
 }  // namespace
 
 int gemm_device(GemmArgs &g)
@@ -124,13 +139,66 @@ int gemm_device(GemmArgs &g)
     ACC_TRY(device_check());
     const Family f = pick_family(g);
     if (g_gemm_path == 2 && f == FAM_GENERIC) return ACCBLAS_ERR_SHAPE;
+    if (f == FAM_GENERIC && g_gemm_path == 0 && (double)g.m * (double)g.n * (double)g.k >= 48.0 * 48.0 * 48.0)
+        return gemm_repitched(g);
+    return run_family(f, g);
+}
+
+namespace {
+int run_family(Family f, const GemmArgs &g)
+{
     switch (f) {
     case FAM_DMMA: return dgemm_dmma(g);
     case FAM_TC:   return sgemm_tc(g);
     case FAM_RANK1: return gemm_rank1(g);
+    case FAM_MMA:  return sgemm_mma(g);
     default:       return gemm_generic(g);
     }
 }
+
+// The TMA-fed families need 16-byte aligned bases and row pitches.  Dense Accelerate arrays with an
+// odd column count (the reference benchmarks 250 x 250 Floats: 1000-byte rows) miss that by a few
+// bytes, which used to send them to the SIMT kernel at half cuBLAS's speed.  Instead: copy the
+// offending operand(s) once into stream-ordered scratch with the pitch rounded up (an O(n^2) strided
+// D2D copy on the caller's stream) and run the tensor family on the copy.  C keeps its own layout
+// (the epilogues fall back to scalar stores); a misaligned C base stays on the SIMT kernel.
+int gemm_repitched(const GemmArgs &g)
+{
+    const size_t es = elem_size(g.dtype);
+    const int64_t q = (int64_t)(16 / es);                              // elements per 16 bytes
+    auto bad = [&](const void *p, int64_t ld) { return (reinterpret_cast<uintptr_t>(p) & 15u) != 0 || (ld % q) != 0; };
+    const bool fixA = bad(g.A, g.lda), fixB = bad(g.B, g.ldb);
+    if ((!fixA && !fixB) || (reinterpret_cast<uintptr_t>(g.C) & 15u) != 0) return gemm_generic(g);
+    GemmArgs h = g;
+    const int64_t lda = fixA ? (g.colsA + q - 1) / q * q : g.lda, ldb = fixB ? (g.colsB + q - 1) / q * q : g.ldb;
+    h.lda = lda; h.ldb = ldb;
+    if (fixA) h.A = nullptr;                                            // "aligned" for the eligibility test
+    if (fixB) h.B = nullptr;
+    const Family f = pick_family(h);
+    if (f == FAM_GENERIC || f == FAM_NONE) return gemm_generic(g);
+    const size_t bytesA = fixA ? (es * (size_t)lda * (size_t)g.rowsA + 255) / 256 * 256 : 0;
+    const size_t bytesB = fixB ? es * (size_t)ldb * (size_t)g.rowsB : 0;
+    char *ws = nullptr;
+    ACC_CUDA(cudaMallocAsync(reinterpret_cast<void **>(&ws), bytesA + bytesB, g.stream));
+    int st = ACCBLAS_OK;
+    cudaError_t e = cudaSuccess;
+    if (fixA) {
+        e = cudaMemcpy2DAsync(ws, es * (size_t)lda, g.A, es * (size_t)g.lda, es * (size_t)g.colsA, (size_t)g.rowsA,
+                              cudaMemcpyDeviceToDevice, g.stream);
+        h.A = ws;
+    }
+    if (fixB && e == cudaSuccess) {
+        e = cudaMemcpy2DAsync(ws + bytesA, es * (size_t)ldb, g.B, es * (size_t)g.ldb, es * (size_t)g.colsB, (size_t)g.rowsB,
+                              cudaMemcpyDeviceToDevice, g.stream);
+        h.B = ws + bytesA;
+    }
+    if (e == cudaSuccess) st = run_family(pick_family(h), h);
+    cudaError_t e2 = cudaFreeAsync(ws, g.stream);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaMemcpy2DAsync (re-pitch)");
+    if (st == ACCBLAS_OK && e2 != cudaSuccess) return cuda_fail(e2, "cudaFreeAsync");
+    return st;
+}
+}  // namespace
 
 namespace {
 // RAII for stream-ordered scratch used by the host-buffer entry points
@@ -170,6 +238,10 @@ const char *accblas_status_string(int s)
 const char *accblas_last_cuda_error(void) { return g_cuda_err; }
 uint64_t accblas_launch_count(void) { return g_launches; }
 void accblas_set_gemm_path(int path) { g_gemm_path = (path >= 0 && path <= 2) ? path : 0; }
+void accblas_set_tuning(int knob, int value)
+{
+    if (knob >= 0 && knob < ACCBLAS_TUNE_COUNT) g_tuning[knob] = value;
+}
 
 int accblas_gemm(accblas_stream_t stream, int dtype, int opA, int opB, int64_t rowsA, int64_t colsA,
                  int64_t rowsB, int64_t colsB, const void *alpha_host, const void *A, const void *B, void *C)
@@ -203,11 +275,20 @@ const char *accblas_gemm_kernel_name(int dtype, int opA, int opB, int64_t rowsA,
     g.dtype = dtype; g.opA = opA; g.opB = opB;
     g.rowsA = rowsA; g.colsA = colsA; g.rowsB = rowsB; g.colsB = colsB;
     if (derive_gemm(g) != ACCBLAS_OK) return "invalid";
-    switch (pick_family(g)) {
+    Family f = pick_family(g);
+    if (f == FAM_GENERIC && g_gemm_path == 0 && (double)g.m * (double)g.n * (double)g.k >= 48.0 * 48.0 * 48.0) {
+        const int64_t q = (int64_t)(16 / elem_size(g.dtype));         // what gemm_repitched would run
+        GemmArgs h = g;
+        h.lda = (g.colsA + q - 1) / q * q;
+        h.ldb = (g.colsB + q - 1) / q * q;
+        f = pick_family(h);
+    }
+    switch (f) {
     case FAM_NONE: return "none";
     case FAM_DMMA: return g.dtype == ACCBLAS_F64 ? "dgemm_dmma_tma" : "zgemm_dmma_tma";
     case FAM_TC:   return g.dtype == ACCBLAS_F32 ? "sgemm_tf32x3_tcgen05" : "cgemm_tf32x3_tcgen05";
     case FAM_RANK1: return "gemm_rank1_outer";
+    case FAM_MMA:  return g.dtype == ACCBLAS_F32 ? "sgemm_tf32x3_mma" : "cgemm_tf32x3_mma";
     default:       return "gemm_simt_generic";
     }
 }

@@ -13,6 +13,7 @@ namespace accblas {
 extern thread_local uint64_t g_launches;      // kernels enqueued by this thread
 extern thread_local char g_cuda_err[256];     // text of the last CUDA failure
 extern thread_local int g_gemm_path;          // accblas_set_gemm_path
+extern thread_local int g_tuning[ACCBLAS_TUNE_COUNT];   // accblas_set_tuning (-1 = automatic)
 
 int cuda_fail(cudaError_t e, const char *where);   // records text, returns ACCBLAS_ERR_CUDA
 inline int check_launch(const char *where) {
@@ -139,6 +140,8 @@ int  dgemm_dmma(const GemmArgs &g);
 bool sgemm_tc_eligible(const GemmArgs &g);            // gemm_tf32x3.cu  : f32 / c32 on tcgen05
 int  sgemm_tc(const GemmArgs &g);
 size_t sgemm_tc_workspace(const GemmArgs &g);
+bool sgemm_mma_eligible(const GemmArgs &g);           // gemm_mma_tf32.cu : f32 / c32 on mma.sync, small / medium
+int  sgemm_mma(const GemmArgs &g);
 
 int gemv_dispatch(cudaStream_t s, int dtype, int opA, int64_t rowsA, int64_t colsA,
                   const void *alpha, const void *A, const void *x, void *y);          // gemv.cu

@@ -28,21 +28,31 @@
 namespace accblas {
 namespace {
 
-constexpr int BN = 128, BK = 16;
-constexpr int CONSUMER_WARPS = 8;
-constexpr int THREADS = (CONSUMER_WARPS + 1) * 32;
-constexpr int B_BYTES = BN * BK * 8;
-// Two CTA tiles: MI = 8 -> 128 x 128 (one CTA per SM, 6 stages), the throughput shape; MI = 4 -> 64 x 128
-// (two CTAs per SM, 4 stages each) for products whose 128 x 128 tiling leaves SMs idle in the last
-// wave (dgemm 1024^3 is 64 big tiles on 148 SMs).  MI = 8-row DMMA tiles per warp along m.
-template <int MI> struct Cfg {
-    static constexpr int BM = 16 * MI;
-    static constexpr int STAGES = MI == 8 ? 6 : 4;
-    static constexpr int A_BYTES = BM * BK * 8;
+constexpr int BK = 16;
+// CTA tiles.  A tile is WM x WN consumer warps, each owning MI x NJ DMMA tiles (8 x 8):
+//   128 x 128 (2x4 warps of 64 x 32): the throughput shape, one CTA per SM, 6 stages;
+//    64 x 128 (2x4 warps of 32 x 32): two CTAs per SM, for products whose 128 x 128 tiling leaves SMs
+//             idle in the last wave (dgemm 1024^3 is 64 big tiles on 148 SMs);
+//    64 x  64 (2x4 warps of 32 x 16) and 32 x 32 (2x2 warps of 16 x 16): the FP64 pipe runs 64 FMA/clk/SM,
+//             so even a 100^3 product is compute-bound on the two SMs a 128-wide tiling would use --
+//             small products are spread over as many SMs as possible (the reference's own benchmark
+//             shapes are 100^3 .. 1000^3, bench/Bench/Accelerate.hs:92-116).
+template <int MI_, int NJ_, int WM_, int WN_, int STAGES_, int MIN_CTAS_> struct Tile {
+    static constexpr int MI = MI_, NJ = NJ_, WM = WM_, WN = WN_;
+    static constexpr int BM = 8 * MI * WM, BN = 8 * NJ * WN;
+    static constexpr int CONSUMER_WARPS = WM * WN;
+    static constexpr int THREADS = (CONSUMER_WARPS + 1) * 32;
+    static constexpr int STAGES = STAGES_;
+    static constexpr int A_BYTES = BM * BK * 8, B_BYTES = BN * BK * 8;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
     static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 2 * STAGES * 8;
-    static constexpr int MIN_CTAS = MI == 8 ? 1 : 2;
+    static constexpr int MIN_CTAS = MIN_CTAS_;
+    static_assert(MI % 2 == 0 && NJ % 2 == 0, "MN-major operands come in 16-wide boxes");
 };
+using Tile128x128 = Tile<8, 4, 2, 4, 6, 1>;
+using Tile64x128  = Tile<4, 4, 2, 4, 4, 2>;
+using Tile64x64   = Tile<4, 2, 2, 4, 4, 3>;
+using Tile32x32   = Tile<2, 2, 2, 2, 3, 7>;   // 7 CTAs per SM: 1024 tiles (dgemm 1024^3) are ONE resident wave
 
 __device__ __forceinline__ void dmma(double &d0, double &d1, double a, double b) {
     asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
@@ -66,13 +76,13 @@ struct DgemmParams {
 };
 
 // AK: op(A) is K-major in memory (opA == N).  BKM: op(B) is K-major in memory (opB == T).
-template <bool AK, bool BKM, int MI>
-__global__ void __launch_bounds__(THREADS, Cfg<MI>::MIN_CTAS)
+template <bool AK, bool BKM, typename TL>
+__global__ void __launch_bounds__(TL::THREADS, TL::MIN_CTAS)
 dgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
                   const DgemmParams p)
 {
-    constexpr int BM = Cfg<MI>::BM, STAGES = Cfg<MI>::STAGES, A_BYTES = Cfg<MI>::A_BYTES,
-                  STAGE_BYTES = Cfg<MI>::STAGE_BYTES;
+    constexpr int MI = TL::MI, NJ = TL::NJ, BM = TL::BM, BN = TL::BN, STAGES = TL::STAGES,
+                  A_BYTES = TL::A_BYTES, STAGE_BYTES = TL::STAGE_BYTES, CONSUMER_WARPS = TL::CONSUMER_WARPS;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem_base = (tma::smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t bar_base = smem_base + STAGES * STAGE_BYTES;      // full[STAGES], empty[STAGES]
@@ -131,7 +141,7 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
 
     // ================================ consumers ================================
     const int g = lane >> 2, t = lane & 3;
-    const int wm = warp >> 2, wn = warp & 3;          // 2 x 4 warps, warp tile (8 MI) x 32
+    const int wm = warp / TL::WN, wn = warp % TL::WN;  // WM x WN warps, warp tile (8 MI) x (8 NJ)
     // per-lane byte offsets of the four k-steps inside a stage tile (frag / box offsets are added
     // as immediates below)
     uint32_t offA[4], offB[4];
@@ -141,21 +151,21 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
         const uint32_t kmaj = g * 128 + ((((kk >> 1) ^ g) & 7) << 4) + (kk & 1) * 8;
         const uint32_t mnmaj = kk * 128 + ((((g >> 1) ^ (kk & 7)) & 7) << 4) + (g & 1) * 8;
         offA[s] = AK ? (uint32_t)(wm * MI * 8 * 128) + kmaj : (uint32_t)(wm * (MI / 2) * 2048) + mnmaj;
-        offB[s] = A_BYTES + (BKM ? (uint32_t)(wn * 32 * 128) + kmaj : (uint32_t)(wn * 2 * 2048) + mnmaj);
+        offB[s] = A_BYTES + (BKM ? (uint32_t)(wn * NJ * 8 * 128) + kmaj : (uint32_t)(wn * (NJ / 2) * 2048) + mnmaj);
     }
 
-    double acc[MI][4][2];
+    double acc[MI][NJ][2];
 #pragma unroll
     for (int i = 0; i < MI; ++i)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
+        for (int j = 0; j < NJ; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
 
-    auto load_frags = [&](uint32_t stage, int s, double (&a)[MI], double (&b)[4]) {
+    auto load_frags = [&](uint32_t stage, int s, double (&a)[MI], double (&b)[NJ]) {
 #pragma unroll
         for (int i = 0; i < MI; ++i)
             a[i] = lds64(stage + (AK ? offA[s] + i * 1024 : (offA[s] ^ ((i & 1) << 6)) + (i >> 1) * 2048));
 #pragma unroll
-        for (int j = 0; j < 4; ++j)
+        for (int j = 0; j < NJ; ++j)
             b[j] = lds64(stage + (BKM ? offB[s] + j * 1024 : (offB[s] ^ ((j & 1) << 6)) + (j >> 1) * 2048));
     };
 
@@ -163,7 +173,7 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
         const int s = kb % STAGES;
         const uint32_t stage = smem_base + s * STAGE_BYTES;
         tma::mbar_wait(bar_base + 8 * s, (kb / STAGES) & 1);
-        double a[2][MI], b[2][4];
+        double a[2][MI], b[2][NJ];
         load_frags(stage, 0, a[0], b[0]);
 #pragma unroll
         for (int st = 0; st < 4; ++st) {
@@ -171,9 +181,9 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
 #pragma unroll
             for (int i = 0; i < MI; ++i)
 #pragma unroll
-                for (int j = 0; j < 4; ++j) dmma(acc[i][j][0], acc[i][j][1], a[st & 1][i], b[st & 1][j]);
+                for (int j = 0; j < NJ; ++j) dmma(acc[i][j][0], acc[i][j][1], a[st & 1][i], b[st & 1][j]);
         }
-        __syncwarp();
+        tma::consumer_release_fence();
         if (lane == 0) tma::mbar_arrive(bar_base + 8 * (STAGES + s));   // stage consumed by this warp
     }
 
@@ -185,8 +195,8 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
         if (r >= p.m) continue;
         double *crow = p.C + r * p.ldc;
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const int64_t c = n0 + wn * 32 + j * 8 + 2 * t;
+        for (int j = 0; j < NJ; ++j) {
+            const int64_t c = n0 + wn * NJ * 8 + j * 8 + 2 * t;
             const double v0 = p.alpha * acc[i][j][0], v1 = p.alpha * acc[i][j][1];
             if (vec) {
                 if (c < p.n) *reinterpret_cast<double2 *>(crow + c) = make_double2(v0, v1);
@@ -211,11 +221,27 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
 //   k slots: step 0 reads k = 0,2,4,6, step 1 reads k = 1,3,5,7 (conflict-free quarter-warp
 //   ld.shared.v2 under the 128-byte swizzle for both majors).
 // =====================================================================================
-constexpr int ZBM = 128, ZBN = 64, ZBK = 8;
-constexpr int ZSTAGES = 8;
-constexpr int ZTHREADS = 384;   // 2 consumer warpgroups + 1 producer warpgroup (setmaxnreg is per warpgroup)
-constexpr int ZA_BYTES = ZBM * ZBK * 16, ZB_BYTES = ZBN * ZBK * 16, ZSTAGE_BYTES = ZA_BYTES + ZB_BYTES;
-constexpr int ZSMEM_BYTES = ZSTAGES * ZSTAGE_BYTES + 1024 + 2 * ZSTAGES * 8;
+constexpr int ZBK = 8;
+// Complex tiles (extents in complex elements), WM x WN consumer warps of MI x NJ complex DMMA tiles:
+//   128 x 64 (4x2 warps of 32 x 32): throughput shape; 2 consumer warpgroups + 1 producer warpgroup with
+//            setmaxnreg (which works per warpgroup), 8 stages;
+//    64 x 64 (2x2 warps of 32 x 32) and 32 x 32 (2x2 warps of 16 x 16): small products spread over more SMs
+//            (see the real tiles above); one producer warp, no register re-partitioning needed.
+template <int MI_, int NJ_, int WM_, int WN_, int STAGES_, int MIN_CTAS_, bool REGSPLIT_> struct ZTile {
+    static constexpr int MI = MI_, NJ = NJ_, WM = WM_, WN = WN_;
+    static constexpr int BM = 8 * MI * WM, BN = 8 * NJ * WN;
+    static constexpr int CONSUMER_WARPS = WM * WN;
+    static constexpr bool REGSPLIT = REGSPLIT_;
+    static constexpr int THREADS = (CONSUMER_WARPS + (REGSPLIT ? 4 : 1)) * 32;
+    static constexpr int STAGES = STAGES_;
+    static constexpr int A_BYTES = BM * ZBK * 16, B_BYTES = BN * ZBK * 16, STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 2 * STAGES * 8;
+    static constexpr int MIN_CTAS = MIN_CTAS_;
+    static_assert(!REGSPLIT || CONSUMER_WARPS % 4 == 0, "setmaxnreg needs whole warpgroups");
+};
+using ZTile128x64 = ZTile<4, 4, 4, 2, 8, 1, true>;
+using ZTile64x64  = ZTile<4, 4, 2, 2, 6, 1, false>;
+using ZTile32x32  = ZTile<2, 2, 2, 2, 4, 5, false>;
 
 __device__ __forceinline__ double2 lds128(uint32_t addr) {
     double2 v;
@@ -233,11 +259,13 @@ struct ZgemmParams {
     int tiles_m, tiles_n;
 };
 
-template <bool AK, bool BKM, bool CONJA, bool CONJB>
-__global__ void __launch_bounds__(ZTHREADS, 1)
+template <bool AK, bool BKM, bool CONJA, bool CONJB, typename TL>
+__global__ void __launch_bounds__(TL::THREADS, TL::MIN_CTAS)
 zgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
                   const ZgemmParams p)
 {
+    constexpr int MI = TL::MI, NJ = TL::NJ, ZBM = TL::BM, ZBN = TL::BN, ZSTAGES = TL::STAGES,
+                  ZA_BYTES = TL::A_BYTES, ZSTAGE_BYTES = TL::STAGE_BYTES, CONSUMER_WARPS = TL::CONSUMER_WARPS;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem_base = (tma::smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t bar_base = smem_base + ZSTAGES * ZSTAGE_BYTES;
@@ -268,7 +296,7 @@ zgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
 
     if (warp >= CONSUMER_WARPS) {
         // producer warpgroup: hand registers to the consumers (168 at launch -> 40 here, 232 there)
-        asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+        if constexpr (TL::REGSPLIT) asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
         if (warp == CONSUMER_WARPS && lane == 0) {
             tma::prefetch_tmap(&mapA);
             tma::prefetch_tmap(&mapB);
@@ -294,80 +322,80 @@ zgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
         return;
     }
 
-    asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
+    if constexpr (TL::REGSPLIT) asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
     const int g = lane >> 2, t = lane & 3;
-    const int wm = warp >> 1, wn = warp & 1;          // 4 x 2 warps, warp tile 32 x 32 complex
+    const int wm = warp / TL::WN, wn = warp % TL::WN;  // WM x WN warps, warp tile (8 MI) x (8 NJ) complex
     uint32_t offA[2], offB[2];
 #pragma unroll
     for (int s = 0; s < 2; ++s) {
         const int kk = 2 * t + s;
         const uint32_t kmaj = g * 128 + (((kk ^ g) & 7) << 4);
         const uint32_t mnmaj = kk * 128 + (((g ^ kk) & 7) << 4);
-        offA[s] = (uint32_t)(wm * 4 * 1024) + (AK ? kmaj : mnmaj);
-        offB[s] = ZA_BYTES + (uint32_t)(wn * 4 * 1024) + (BKM ? kmaj : mnmaj);
+        offA[s] = (uint32_t)(wm * MI * 1024) + (AK ? kmaj : mnmaj);
+        offB[s] = ZA_BYTES + (uint32_t)(wn * NJ * 1024) + (BKM ? kmaj : mnmaj);
     }
 
-    double cr[4][4][2], ci[4][4][2];
+    double cr[MI][NJ][2], ci[MI][NJ][2];
 #pragma unroll
-    for (int i = 0; i < 4; ++i)
+    for (int i = 0; i < MI; ++i)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) cr[i][j][0] = cr[i][j][1] = ci[i][j][0] = ci[i][j][1] = 0.0;
+        for (int j = 0; j < NJ; ++j) cr[i][j][0] = cr[i][j][1] = ci[i][j][0] = ci[i][j][1] = 0.0;
 
     for (int kb = 0; kb < kblocks; ++kb) {
         const int s = kb % ZSTAGES;
         const uint32_t stage = smem_base + s * ZSTAGE_BYTES;
         tma::mbar_wait(bar_base + 8 * s, (kb / ZSTAGES) & 1);
-        double2 a[2][4], b[2][4];
+        double2 a[2][MI], b[2][NJ];
 #pragma unroll
-        for (int i = 0; i < 4; ++i) a[0][i] = lds128(stage + offA[0] + i * 1024);
+        for (int i = 0; i < MI; ++i) a[0][i] = lds128(stage + offA[0] + i * 1024);
 #pragma unroll
-        for (int j = 0; j < 4; ++j) b[0][j] = lds128(stage + offB[0] + j * 1024);
+        for (int j = 0; j < NJ; ++j) b[0][j] = lds128(stage + offB[0] + j * 1024);
 #pragma unroll
         for (int st = 0; st < 2; ++st) {
             if (st == 0) {
 #pragma unroll
-                for (int i = 0; i < 4; ++i) a[1][i] = lds128(stage + offA[1] + i * 1024);
+                for (int i = 0; i < MI; ++i) a[1][i] = lds128(stage + offA[1] + i * 1024);
 #pragma unroll
-                for (int j = 0; j < 4; ++j) b[1][j] = lds128(stage + offB[1] + j * 1024);
+                for (int j = 0; j < NJ; ++j) b[1][j] = lds128(stage + offB[1] + j * 1024);
             }
-            double ai[4], nai[4], bi[4];
+            double ai[MI], nai[MI], bi[NJ];
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {       // ai = Im(op A), nai = -Im(op A): one sign flip either way
+            for (int i = 0; i < MI; ++i) {       // ai = Im(op A), nai = -Im(op A): one sign flip either way
                 ai[i] = CONJA ? flip(a[st][i].y) : a[st][i].y;
                 nai[i] = CONJA ? a[st][i].y : flip(a[st][i].y);
             }
 #pragma unroll
-            for (int j = 0; j < 4; ++j) bi[j] = CONJB ? flip(b[st][j].y) : b[st][j].y;
+            for (int j = 0; j < NJ; ++j) bi[j] = CONJB ? flip(b[st][j].y) : b[st][j].y;
             // four passes over the 4 x 4 tile grid: 16 independent DMMAs between dependent ones
 #pragma unroll
-            for (int i = 0; i < 4; ++i)
+            for (int i = 0; i < MI; ++i)
 #pragma unroll
-                for (int j = 0; j < 4; ++j) dmma(cr[i][j][0], cr[i][j][1], a[st][i].x, b[st][j].x);
+                for (int j = 0; j < NJ; ++j) dmma(cr[i][j][0], cr[i][j][1], a[st][i].x, b[st][j].x);
 #pragma unroll
-            for (int i = 0; i < 4; ++i)
+            for (int i = 0; i < MI; ++i)
 #pragma unroll
-                for (int j = 0; j < 4; ++j) dmma(ci[i][j][0], ci[i][j][1], a[st][i].x, bi[j]);
+                for (int j = 0; j < NJ; ++j) dmma(ci[i][j][0], ci[i][j][1], a[st][i].x, bi[j]);
 #pragma unroll
-            for (int i = 0; i < 4; ++i)
+            for (int i = 0; i < MI; ++i)
 #pragma unroll
-                for (int j = 0; j < 4; ++j) dmma(cr[i][j][0], cr[i][j][1], nai[i], bi[j]);
+                for (int j = 0; j < NJ; ++j) dmma(cr[i][j][0], cr[i][j][1], nai[i], bi[j]);
 #pragma unroll
-            for (int i = 0; i < 4; ++i)
+            for (int i = 0; i < MI; ++i)
 #pragma unroll
-                for (int j = 0; j < 4; ++j) dmma(ci[i][j][0], ci[i][j][1], ai[i], b[st][j].x);
+                for (int j = 0; j < NJ; ++j) dmma(ci[i][j][0], ci[i][j][1], ai[i], b[st][j].x);
         }
-        __syncwarp();
+        tma::consumer_release_fence();
         if (lane == 0) tma::mbar_arrive(bar_base + 8 * (ZSTAGES + s));
     }
 
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        const int64_t r = m0 + wm * 32 + i * 8 + g;
+    for (int i = 0; i < MI; ++i) {
+        const int64_t r = m0 + wm * MI * 8 + i * 8 + g;
         if (r >= p.m) continue;
         double2 *crow = p.C + r * p.ldc;
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const int64_t c = n0 + wn * 32 + j * 8 + 2 * t;
+        for (int j = 0; j < NJ; ++j) {
+            const int64_t c = n0 + wn * NJ * 8 + j * 8 + 2 * t;
 #pragma unroll
             for (int e = 0; e < 2; ++e) {
                 if (c + e < p.n) {
@@ -384,26 +412,43 @@ zgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
 // ---------------------------------------------------------------------------------
 bool aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
-// Time of a tiling in units of "one full wave of 128 x 128 tiles": two co-resident 64 x 128 CTAs share
-// the SM's DMMA pipe, so a wave of 296 half tiles costs the same as a wave of 148 full ones, and a
-// last wave of at most one CTA per SM costs half.
-bool prefer_small_tile(int64_t m, int64_t n)
+// Tile choice.  Every resident CTA of an SM shares its one FP64 tensor pipe (64 FMA/clk), so a launch
+// lasts as long as the busiest SM: ceil(tiles / SMs) tiles of BM x BN x k FMAs, stretched by the
+// efficiency the tile shape reaches on the pipe (smaller tiles spend more issue slots on shared-memory
+// fragment loads per DMMA) plus a per-tile prologue/epilogue expressed in k-equivalents.
+// The efficiencies are measured (profiles/r01_dmma_tiles.jsonl).
+struct TileModel { int bm, bn; double eff; double fixed_k; double eff_alone; };
+// eff: pipe efficiency with the SM full of such CTAs, relative to 128 x 128 (4096^3: 3858 / 3977 / 3991 /
+// 3926 us); eff_alone: with ONE such CTA on the SM (a 4-warp CTA cannot keep the pipe busy by itself).
+constexpr TileModel kTileModel[4] = {
+    {128, 128, 1.000, 32.0, 1.00},
+    {64, 128, 0.970, 32.0, 0.97},
+    {64, 64, 0.967, 32.0, 0.90},
+    {32, 32, 0.975, 32.0, 0.50},
+};
+
+int pick_tile(int64_t m, int64_t n, int64_t k)
 {
+    if (g_tuning[ACCBLAS_TUNE_DMMA_TILE] >= 0 && g_tuning[ACCBLAS_TUNE_DMMA_TILE] < 4) return g_tuning[ACCBLAS_TUNE_DMMA_TILE];
     const int sms = sm_count();
-    const int64_t t128 = ((m + 127) / 128) * ((n + BN - 1) / BN);
-    const int64_t t64 = ((m + 63) / 64) * ((n + BN - 1) / BN);
-    const double big = (double)((t128 + sms - 1) / sms);
-    const int64_t rem = t64 % (2 * sms);
-    const double small = (double)(t64 / (2 * sms)) + (rem == 0 ? 0.0 : rem <= sms ? 0.5 : 1.0);
-    return small < big;
+    int best = 0;
+    double best_cost = 0.0;
+    for (int c = 0; c < 4; ++c) {
+        const TileModel &t = kTileModel[c];
+        const int64_t tiles = ((m + t.bm - 1) / t.bm) * ((n + t.bn - 1) / t.bn);
+        const double per_sm = (double)((tiles + sms - 1) / sms);
+        const double cost = per_sm * (double)t.bm * (double)t.bn * ((double)k + t.fixed_k) / (per_sm > 1.0 ? t.eff : t.eff_alone);
+        if (c == 0 || cost < best_cost * 0.999) { best = c; best_cost = cost; }
+    }
+    return best;
 }
 
-template <bool AK, bool BKM, int MI>
-int launch_dgemm_mi(const GemmArgs &g)
+template <bool AK, bool BKM, typename TL>
+int launch_dgemm_tile(const GemmArgs &g)
 {
-    constexpr int BM = Cfg<MI>::BM, SMEM_BYTES = Cfg<MI>::SMEM_BYTES;
+    constexpr int BM = TL::BM, BN = TL::BN, SMEM_BYTES = TL::SMEM_BYTES;
     CUtensorMap mapA, mapB;
-    // K-major operand: box = 16 (k) x 128 rows; MN-major operand: box = 16 (m|n) x 16 (k)
+    // K-major operand: box = 16 (k) x BM|BN rows; MN-major operand: box = 16 (m|n) x 16 (k)
     if (!tma::make_2d(&mapA, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 8, g.A, (uint64_t)g.rowsA, (uint64_t)g.colsA,
                       AK ? BM : BK, 16, (uint64_t)g.lda * 8) ||
         !tma::make_2d(&mapB, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 8, g.B, (uint64_t)g.rowsB, (uint64_t)g.colsB,
@@ -411,7 +456,7 @@ int launch_dgemm_mi(const GemmArgs &g)
         return cuda_fail(cudaErrorInvalidValue, "cuTensorMapEncodeTiled");
     static thread_local bool attr_done = false;
     if (!attr_done) {
-        ACC_CUDA(cudaFuncSetAttribute(dgemm_dmma_kernel<AK, BKM, MI>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+        ACC_CUDA(cudaFuncSetAttribute(dgemm_dmma_kernel<AK, BKM, TL>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
         attr_done = true;
     }
     DgemmParams p;
@@ -422,19 +467,25 @@ int launch_dgemm_mi(const GemmArgs &g)
     p.tiles_n = (int)((g.n + BN - 1) / BN);
     const int64_t tiles = (int64_t)p.tiles_m * p.tiles_n;
     if (tiles > 0x7fffffff) return ACCBLAS_ERR_SHAPE;
-    dgemm_dmma_kernel<AK, BKM, MI><<<(unsigned)tiles, THREADS, SMEM_BYTES, g.stream>>>(mapA, mapB, p);
+    dgemm_dmma_kernel<AK, BKM, TL><<<(unsigned)tiles, TL::THREADS, SMEM_BYTES, g.stream>>>(mapA, mapB, p);
     return check_launch("dgemm_dmma_kernel");
 }
 
 template <bool AK, bool BKM>
 int launch_dgemm(const GemmArgs &g)
 {
-    return prefer_small_tile(g.m, g.n) ? launch_dgemm_mi<AK, BKM, 4>(g) : launch_dgemm_mi<AK, BKM, 8>(g);
+    switch (pick_tile(g.m, g.n, g.k)) {
+    case 1:  return launch_dgemm_tile<AK, BKM, Tile64x128>(g);
+    case 2:  return launch_dgemm_tile<AK, BKM, Tile64x64>(g);
+    case 3:  return launch_dgemm_tile<AK, BKM, Tile32x32>(g);
+    default: return launch_dgemm_tile<AK, BKM, Tile128x128>(g);
+    }
 }
 
-template <bool AK, bool BKM, bool CA, bool CB>
-int launch_zgemm(const GemmArgs &g)
+template <bool AK, bool BKM, bool CA, bool CB, typename TL>
+int launch_zgemm_tile(const GemmArgs &g)
 {
+    constexpr int ZBM = TL::BM, ZBN = TL::BN;
     CUtensorMap mapA, mapB;
     // maps are over doubles (no complex TMA type): a complex row of c columns is 2c doubles
     if (!tma::make_2d(&mapA, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 8, g.A, (uint64_t)g.rowsA, 2 * (uint64_t)g.colsA,
@@ -444,7 +495,7 @@ int launch_zgemm(const GemmArgs &g)
         return cuda_fail(cudaErrorInvalidValue, "cuTensorMapEncodeTiled");
     static thread_local bool attr_done = false;
     if (!attr_done) {
-        ACC_CUDA(cudaFuncSetAttribute(zgemm_dmma_kernel<AK, BKM, CA, CB>, cudaFuncAttributeMaxDynamicSharedMemorySize, ZSMEM_BYTES));
+        ACC_CUDA(cudaFuncSetAttribute(zgemm_dmma_kernel<AK, BKM, CA, CB, TL>, cudaFuncAttributeMaxDynamicSharedMemorySize, TL::SMEM_BYTES));
         attr_done = true;
     }
     ZgemmParams p;
@@ -456,8 +507,41 @@ int launch_zgemm(const GemmArgs &g)
     p.tiles_n = (int)((g.n + ZBN - 1) / ZBN);
     const int64_t tiles = (int64_t)p.tiles_m * p.tiles_n;
     if (tiles > 0x7fffffff) return ACCBLAS_ERR_SHAPE;
-    zgemm_dmma_kernel<AK, BKM, CA, CB><<<(unsigned)tiles, ZTHREADS, ZSMEM_BYTES, g.stream>>>(mapA, mapB, p);
+    zgemm_dmma_kernel<AK, BKM, CA, CB, TL><<<(unsigned)tiles, TL::THREADS, TL::SMEM_BYTES, g.stream>>>(mapA, mapB, p);
     return check_launch("zgemm_dmma_kernel");
+}
+
+// same cost model as pick_tile; a complex tile element costs four real FMAs
+constexpr TileModel kZTileModel[3] = {
+    {128, 64, 1.000, 16.0, 1.00},
+    {64, 64, 0.880, 16.0, 0.88},
+    {32, 32, 0.975, 16.0, 0.60},
+};
+
+int pick_ztile(int64_t m, int64_t n, int64_t k)
+{
+    if (g_tuning[ACCBLAS_TUNE_ZMMA_TILE] >= 0 && g_tuning[ACCBLAS_TUNE_ZMMA_TILE] < 3) return g_tuning[ACCBLAS_TUNE_ZMMA_TILE];
+    const int sms = sm_count();
+    int best = 0;
+    double best_cost = 0.0;
+    for (int c = 0; c < 3; ++c) {
+        const TileModel &t = kZTileModel[c];
+        const int64_t tiles = ((m + t.bm - 1) / t.bm) * ((n + t.bn - 1) / t.bn);
+        const double per_sm = (double)((tiles + sms - 1) / sms);
+        const double cost = per_sm * (double)t.bm * (double)t.bn * ((double)k + t.fixed_k) / (per_sm > 1.0 ? t.eff : t.eff_alone);
+        if (c == 0 || cost < best_cost * 0.999) { best = c; best_cost = cost; }
+    }
+    return best;
+}
+
+template <bool AK, bool BKM, bool CA, bool CB>
+int launch_zgemm(const GemmArgs &g)
+{
+    switch (pick_ztile(g.m, g.n, g.k)) {
+    case 1:  return launch_zgemm_tile<AK, BKM, CA, CB, ZTile64x64>(g);
+    case 2:  return launch_zgemm_tile<AK, BKM, CA, CB, ZTile32x32>(g);
+    default: return launch_zgemm_tile<AK, BKM, CA, CB, ZTile128x64>(g);
+    }
 }
 
 template <bool AK, bool BKM>

@@ -33,30 +33,41 @@ struct Scratch {
     ~Scratch() { if (p) cudaFreeAsync(p, s); }
 };
 
-struct Events {
-    std::vector<cudaEvent_t> ev;
-    cudaEvent_t make() {
-        cudaEvent_t e = nullptr;
-        cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
-        ev.push_back(e);
-        return e;
-    }
-    ~Events() { for (auto e : ev) if (e) cudaEventDestroy(e); }
-};
-
+// The side streams and events of the wavefront are per-thread, per-device resources created on first
+// use and kept (creating four streams costs ~0.3 ms, more than a 1000^3 product).  They carry no state
+// between calls: every call starts by making them wait on the caller's stream and ends by joining them
+// back, and accblas_gemm_host is synchronous, so a thread never has two pipelines in flight.
 struct Streams {
     cudaStream_t up = nullptr, down = nullptr, row = nullptr, col = nullptr;
+    std::vector<cudaEvent_t> events;
+    size_t used = 0;
     cudaError_t create() {
+        if (up) return cudaSuccess;
         cudaError_t e;
         if ((e = cudaStreamCreateWithFlags(&up, cudaStreamNonBlocking)) != cudaSuccess) return e;
         if ((e = cudaStreamCreateWithFlags(&down, cudaStreamNonBlocking)) != cudaSuccess) return e;
         if ((e = cudaStreamCreateWithFlags(&row, cudaStreamNonBlocking)) != cudaSuccess) return e;
         return cudaStreamCreateWithFlags(&col, cudaStreamNonBlocking);
     }
-    ~Streams() {
-        for (cudaStream_t s : {up, down, row, col}) if (s) cudaStreamDestroy(s);
+    cudaEvent_t make() {                       // next pooled event (valid until the next call's reset)
+        if (used == events.size()) {
+            cudaEvent_t e = nullptr;
+            cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
+            events.push_back(e);
+        }
+        return events[used++];
     }
 };
+
+Streams &thread_streams()
+{
+    static thread_local Streams per_device[64];
+    int dev = 0;
+    cudaGetDevice(&dev);
+    Streams &s = per_device[(dev >= 0 && dev < 64) ? dev : 0];
+    s.used = 0;
+    return s;
+}
 
 // panel extent: a multiple of 128, at most `maxp` panels, at least 512 wide
 int64_t panel_extent(int64_t extent, int maxp)
@@ -96,7 +107,10 @@ int gemm_host_pipeline(const GemmArgs &g0, const void *A_host, const void *B_hos
     const int64_t pm = panel_extent(g.m, maxp), pn = panel_extent(g.n, maxp);
     const int P = (int)((g.m + pm - 1) / pm), Q = (int)((g.n + pn - 1) / pn);
 
-    if (P * Q == 1 || g.k == 0) {                // one block: nothing to overlap
+    // below ~1 ms of PCIe traffic the wavefront's extra launches and events cost more than they hide
+    const int force = g_tuning[ACCBLAS_TUNE_HOST_PIPELINE];
+    const bool small = force == 1 ? false : force == 0 ? true : bytesA + bytesB + bytesC < ((size_t)48 << 20);
+    if (P * Q == 1 || g.k == 0 || small) {
         if (bytesA) ACC_CUDA(cudaMemcpyAsync(dA.p, A_host, bytesA, cudaMemcpyHostToDevice, s));
         if (bytesB) ACC_CUDA(cudaMemcpyAsync(dB.p, B_host, bytesB, cudaMemcpyHostToDevice, s));
         GemmArgs one = g;
@@ -107,9 +121,9 @@ int gemm_host_pipeline(const GemmArgs &g0, const void *A_host, const void *B_hos
         return ACCBLAS_OK;
     }
 
-    Streams st;
+    Streams &st = thread_streams();
     ACC_CUDA(st.create());
-    Events evs;
+    Streams &evs = st;
     cudaEvent_t ev_start = evs.make();
     ACC_CUDA(cudaEventRecord(ev_start, s));      // the allocations are ordered on s
     for (cudaStream_t x : {st.up, st.down, st.row, st.col}) ACC_CUDA(cudaStreamWaitEvent(x, ev_start, 0));

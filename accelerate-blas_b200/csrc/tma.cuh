@@ -21,6 +21,16 @@ __device__ __forceinline__ void fence_barrier_init() {
 __device__ __forceinline__ void fence_proxy_async() {
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }
+// Before a consumer warp hands a stage back to the TMA producer: the warp's ld.shared reads of the
+// stage (generic proxy) must be COMPLETE before the producer's next cp.async.bulk (async proxy) may
+// overwrite it.  The mbarrier release/acquire chain alone does not order accesses across the two
+// proxies, and ptxas is free to hoist the arrive above the MMAs that consume the loaded registers
+// (it did, in the 32 x 32 complex tile: SYNCS.ARRIVE right behind the last LDS.128, wrong results
+// under load).  The proxy fence orders the reads; __syncwarp extends it to the whole warp.
+__device__ __forceinline__ void consumer_release_fence() {
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    __syncwarp();
+}
 __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
 }

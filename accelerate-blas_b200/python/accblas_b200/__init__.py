@@ -35,7 +35,7 @@ from . import _ffi
 from ._ffi import AccblasError, lib  # noqa: F401
 
 __all__ = ["N", "T", "H", "gemm", "gemv", "dotu", "dotc", "sdot", "asum", "amax", "amin", "mXm", "mXv", "vXm", "dot", "outer",
-           "AccblasError", "kernel_name", "launch_count", "set_gemm_path", "version"]
+           "AccblasError", "kernel_name", "launch_count", "set_gemm_path", "set_tuning", "version"]
 
 # Transpose -- Type.hs:78-90
 N, T, H = 0, 1, 2
@@ -345,6 +345,14 @@ def set_gemm_path(path: Union[int, str]) -> None:
     """0/'auto', 1/'generic' (SIMT), 2/'tensor' (error if the problem does not qualify)."""
     table = {"auto": 0, "generic": 1, "tensor": 2}
     lib().accblas_set_gemm_path(table.get(path, path))
+
+
+TUNE_DMMA_TILE, TUNE_ZMMA_TILE = 0, 1
+
+
+def set_tuning(knob: int, value: int) -> None:
+    """accblas_set_tuning: force a kernel variant on this thread (value < 0: automatic)."""
+    lib().accblas_set_tuning(int(knob), int(value))
 
 
 def version() -> int:

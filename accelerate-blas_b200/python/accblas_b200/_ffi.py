@@ -19,7 +19,7 @@ SYMBOLS = (
     "accblas_sdot", "accblas_asum", "accblas_amax", "accblas_amin",
     "accblas_sdot_host", "accblas_asum_host", "accblas_amax_host", "accblas_amin_host",
     "accblas_version", "accblas_status_string", "accblas_last_cuda_error",
-    "accblas_gemm_kernel_name", "accblas_launch_count", "accblas_set_gemm_path",
+    "accblas_gemm_kernel_name", "accblas_launch_count", "accblas_set_gemm_path", "accblas_set_tuning",
     "accblas_peer_export", "accblas_peer_open", "accblas_peer_close_all", "accblas_peer_copy2d",
 )
 
@@ -80,6 +80,8 @@ def lib() -> ctypes.CDLL:
     L.accblas_launch_count.restype = ctypes.c_uint64
     L.accblas_set_gemm_path.argtypes = [ci]
     L.accblas_set_gemm_path.restype = None
+    L.accblas_set_tuning.argtypes = [ci, ci]
+    L.accblas_set_tuning.restype = None
     L.accblas_peer_export.argtypes = [vp, ctypes.POINTER(PeerHandle)]
     L.accblas_peer_open.argtypes = [ctypes.POINTER(PeerHandle), ctypes.POINTER(vp)]
     L.accblas_peer_close_all.argtypes = []

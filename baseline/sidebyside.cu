@@ -190,11 +190,76 @@ static void host_case(int dt, char opA, char opB, long m, long n, long k, int it
     cudaFree(dA); cudaFree(dB); cudaFree(dC); cudaFreeHost(hA); cudaFreeHost(hB); cudaFreeHost(hC);
 }
 
+// every CTA tile of the DMMA family on a ladder of sizes: calibrates the tile-choice cost model
+static void tile_sweep() {
+    for (int dt : {1, 3}) {
+        const int knob = dt == 1 ? ACCBLAS_TUNE_DMMA_TILE : ACCBLAS_TUNE_ZMMA_TILE, ntiles = dt == 1 ? 4 : 3;
+        for (long n : {100L, 160L, 250L, 384L, 500L, 512L, 768L, 1000L, 1024L, 1280L, 1536L, 2048L, 3072L, 4096L, 8192L}) {
+            if (dt == 3 && n > 4096) continue;
+            if (dt == 1 && n == 8192 && 0) continue;
+            void *A = dev_random(dt, (size_t)n * n, 1), *B = dev_random(dt, (size_t)n * n, 2), *C = dev_random(dt, (size_t)n * n, 3);
+            double one[2] = {1.0, 0.0};
+            printf("{\"sweep\":\"%cgemm_NN\",\"n\":%ld", DT[dt], n);
+            for (int tile = -1; tile < ntiles; ++tile) {
+                accblas_set_tuning(knob, tile);
+                auto ours = [&]() { CK(accblas_gemm(nullptr, dt, 0, 0, n, n, n, n, one, A, B, C)); };
+                float best, med = time_ms(ours, 3, n <= 1024 ? 100 : 20, &best);
+                if (tile < 0) printf(",\"auto_us\":%.1f", med * 1e3); else printf(",\"tile%d_us\":%.1f", tile, med * 1e3);
+            }
+            accblas_set_tuning(knob, -1);
+            auto theirs = [&]() {
+                if (dt == 1) { double al = 1, be = 0; CK(cublasDgemm(H, CUBLAS_OP_N, CUBLAS_OP_N, n, n, n, &al, (double *)B, n, (double *)A, n, &be, (double *)C, n)); }
+                else { cuDoubleComplex al = {1, 0}, be = {0, 0}; CK(cublasZgemm(H, CUBLAS_OP_N, CUBLAS_OP_N, n, n, n, &al, (cuDoubleComplex *)B, n, (cuDoubleComplex *)A, n, &be, (cuDoubleComplex *)C, n)); }
+            };
+            float best, med = time_ms(theirs, 3, n <= 1024 ? 100 : 20, &best);
+            printf(",\"cublas_us\":%.1f}\n", med * 1e3);
+            fflush(stdout);
+            cudaFree(A); cudaFree(B); cudaFree(C);
+        }
+    }
+}
+
+// f32 / c32: mma.sync family (each tile) against the tcgen05 family and cuBLAS on a ladder of sizes
+static void family_sweep() {
+    for (int dt : {0, 2}) {
+        for (long n : {100L, 160L, 250L, 384L, 500L, 768L, 1000L, 1024L, 1536L, 2048L, 3072L, 4096L}) {
+            if (dt == 2 && n > 2048) continue;
+            void *A = dev_random(dt, (size_t)n * n, 1), *B = dev_random(dt, (size_t)n * n, 2), *C = dev_random(dt, (size_t)n * n, 3);
+            float one[2] = {1.f, 0.f};
+            auto ours = [&]() { CK(accblas_gemm(nullptr, dt, 0, 0, n, n, n, n, one, A, B, C)); };
+            const int it = n <= 1024 ? 100 : 20;
+            float best;
+            printf("{\"sweep\":\"%cgemm_NN\",\"n\":%ld", DT[dt], n);
+            printf(",\"auto_us\":%.1f,\"auto_kernel\":\"%s\"", time_ms(ours, 3, it, &best) * 1e3, accblas_gemm_kernel_name(dt, 0, 0, n, n, n, n));
+            accblas_set_tuning(ACCBLAS_TUNE_SGEMM_FAMILY, 1);
+            for (int tile = 0; tile < 3; ++tile) {
+                if (dt == 2 && tile == 1) continue;
+                accblas_set_tuning(ACCBLAS_TUNE_SMMA_TILE, tile);
+                printf(",\"mma_tile%d_us\":%.1f", tile, time_ms(ours, 3, it, &best) * 1e3);
+            }
+            accblas_set_tuning(ACCBLAS_TUNE_SMMA_TILE, -1);
+            accblas_set_tuning(ACCBLAS_TUNE_SGEMM_FAMILY, 2);
+            if (strstr(accblas_gemm_kernel_name(dt, 0, 0, n, n, n, n), "tcgen05"))
+                printf(",\"tcgen05_us\":%.1f", time_ms(ours, 3, it, &best) * 1e3);
+            accblas_set_tuning(ACCBLAS_TUNE_SGEMM_FAMILY, -1);
+            auto theirs = [&]() {
+                if (dt == 0) { float al = 1, be = 0; CK(cublasSgemm(H, CUBLAS_OP_N, CUBLAS_OP_N, n, n, n, &al, (float *)B, n, (float *)A, n, &be, (float *)C, n)); }
+                else { cuComplex al = {1, 0}, be = {0, 0}; CK(cublasCgemm(H, CUBLAS_OP_N, CUBLAS_OP_N, n, n, n, &al, (cuComplex *)B, n, (cuComplex *)A, n, &be, (cuComplex *)C, n)); }
+            };
+            printf(",\"cublas_us\":%.1f}\n", time_ms(theirs, 3, it, &best) * 1e3);
+            fflush(stdout);
+            cudaFree(A); cudaFree(B); cudaFree(C);
+        }
+    }
+}
+
 int main(int argc, char **argv) {
     if (argc > 1) filter = argv[1];
     if (argc > 2) iters_override = atoi(argv[2]);
     CK(cublasCreate(&H));
     CK(cublasSetAtomicsMode(H, CUBLAS_ATOMICS_ALLOWED));              // LLVM/PTX/Context.hs:59
+    if (!strcmp(filter, "tiles")) { tile_sweep(); return 0; }
+    if (!strcmp(filter, "families")) { family_sweep(); return 0; }
     // --- the reference's own benchmark shapes (bench/Bench/Accelerate.hs) ---
     for (int dt = 0; dt < 4; ++dt)
         for (long n : {100L, 250L, 500L, 1000L}) gemm_case(dt, 'N', 'N', n, n, n, 200);

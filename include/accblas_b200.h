@@ -208,7 +208,8 @@ const char *accblas_status_string(int status); /* static string        */
 /* cudaGetLastError text captured by the last ACCBLAS_ERR_CUDA on this thread ("" if none) */
 const char *accblas_last_cuda_error(void);
 /* Name of the kernel family the dispatcher picks for this gemm problem, e.g.
- * "dgemm_dmma_tma", "sgemm_tf32x3_tcgen05", "gemm_simt_generic".  Static string. */
+ * "dgemm_dmma_tma", "sgemm_tf32x3_tcgen05", "sgemm_tf32x3_mma", "gemm_rank1_outer",
+ * "gemm_simt_generic".  Static string. */
 const char *accblas_gemm_kernel_name(int dtype, int opA, int opB,
                                      int64_t rowsA, int64_t colsA, int64_t rowsB, int64_t colsB);
 /* Number of kernel launches this thread has enqueued through the library (bench.py's
@@ -217,6 +218,22 @@ uint64_t accblas_launch_count(void);
 /* Force a kernel family for gemm on this thread: 0 = auto, 1 = generic SIMT,
  * 2 = tensor path only (error ACCBLAS_ERR_SHAPE if the problem does not qualify). */
 void accblas_set_gemm_path(int path);
+
+/* Per-thread tuning knobs for benchmarking the kernel variants against each other
+ * (tools/perf.py, baseline/sidebyside).  value < 0 restores the automatic choice.  Results
+ * stay within the stated tolerance whatever the setting. */
+typedef enum {
+    ACCBLAS_TUNE_DMMA_TILE = 0, /* f64 gemm CTA tile: 0 = 128x128, 1 = 64x128, 2 = 64x64, 3 = 32x32 */
+    ACCBLAS_TUNE_ZMMA_TILE = 1, /* c64 gemm CTA tile: 0 = 128x64, 1 = 64x64, 2 = 32x32            */
+    ACCBLAS_TUNE_SGEMM_FAMILY = 2, /* f32/c32 gemm: 1 = mma.sync path, 2 = tcgen05 path (if eligible)    */
+    ACCBLAS_TUNE_SMMA_TILE = 3, /* mma.sync path CTA tile: 0 = 128x64 (c32: 64x64), 1 = 64x64, 2 = 32x32 */
+    ACCBLAS_TUNE_HOST_PIPELINE = 4, /* accblas_gemm_host: 1 = wavefront even for small transfers, 0 = never */
+    ACCBLAS_TUNE_RESERVED5 = 5,
+    ACCBLAS_TUNE_RESERVED6 = 6,
+    ACCBLAS_TUNE_RESERVED7 = 7,
+    ACCBLAS_TUNE_COUNT = 8
+} accblas_tune_t;
+void accblas_set_tuning(int knob, int value);
 
 #ifdef __cplusplus
 }

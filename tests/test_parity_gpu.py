@@ -34,7 +34,7 @@ def host(t):
 
 def tol_for(ab, dt, oa, ob, A, B):
     name = ab.kernel_name(dt, oa, ob, A.shape, B.shape)
-    return TOL_UNITS_TF32X3 if "tf32x3" in name else TOL_UNITS[dt]
+    return TOL_UNITS_TF32X3 if "tf32x3" in name else TOL_UNITS[dt]   # tcgen05 and mma.sync 3xTF32 families
 
 
 def check_gemm(ab, cuda, dt, oa, ob, al, A, B, path="auto"):
@@ -116,6 +116,88 @@ def test_gemm_all_ops_medium(dt, oa, ob, cuda):
     for (m, n, k) in [(256, 384, 320), (200, 136, 72), (129, 65, 33), (130, 258, 514)]:
         al, A, B = gemm_inputs(rng, dt, oa, ob, m, n, k)
         check_gemm(ab, cuda, dt, oa, ob, al, A, B)
+
+
+@pytest.mark.parametrize("dt,knob,tiles", [(O.F64, 0, 4), (O.C64, 1, 3)], ids=["f64", "c64"])
+def test_gemm_every_dmma_tile(dt, knob, tiles, cuda):
+    """Each CTA tile shape of the DMMA family, forced through accblas_set_tuning, on every op pair at
+    ragged extents (tile edges in m, n and k) and at one size with several tiles per dimension."""
+    import accblas_b200 as ab
+    rng = np.random.default_rng(2700 + dt)
+    try:
+        for tile in range(tiles):
+            ab.set_tuning(knob, tile)
+            for oa in OPN:
+                for ob in OPN:
+                    for (m, n, k) in [(200, 136, 72), (66, 34, 10), (300, 260, 130)]:
+                        al, A, B = gemm_inputs(rng, dt, oa, ob, m, n, k)
+                        assert m < 128 or "dmma" in ab.kernel_name(dt, oa, ob, A.shape, B.shape)
+                        check_gemm(ab, cuda, dt, oa, ob, al, A, B)
+    finally:
+        ab.set_tuning(knob, -1)
+
+
+@pytest.mark.parametrize("dt", [O.F32, O.C32], ids=ids)
+def test_gemm_mma_tf32_family(dt, cuda):
+    """The one-launch mma.sync 3xTF32 family (f32 / c32, small and medium products), every CTA tile, every
+    op pair, ragged extents, a k long enough for several accumulation chunks, windows of larger arrays."""
+    import accblas_b200 as ab
+    rng = np.random.default_rng(2800 + dt)
+    try:
+        ab.set_tuning(2, 1)                       # ACCBLAS_TUNE_SGEMM_FAMILY = mma.sync
+        for tile in range(3):
+            ab.set_tuning(3, tile)                # ACCBLAS_TUNE_SMMA_TILE
+            for oa in OPN:
+                for ob in OPN:
+                    for (m, n, k) in [(200, 136, 72), (68, 36, 12), (300, 260, 1100)]:
+                        al, A, B = gemm_inputs(rng, dt, oa, ob, m, n, k)
+                        assert "mma" in ab.kernel_name(dt, oa, ob, A.shape, B.shape)
+                        C = host(ab.gemm(al, oa, dev(A, cuda), ob, dev(B, cuda)))
+                        err = O.gemm_error_units(C, O.gemm(al, oa, A, ob, B, wide=True), A, B, k, al)
+                        assert err <= TOL_UNITS_TF32X3, (O.NAMES[dt], tile, oa, ob, m, n, k, err)
+                        if k <= 128:
+                            assert O.similar(C, O.gemm(al, oa, A, ob, B, wide=False))
+        ab.set_tuning(3, -1)
+        # auto tile + windows (row pitch > columns)
+        import torch
+        for oa, ob in [("N", "N"), ("T", "H"), ("H", "T")]:
+            al, A, B = gemm_inputs(rng, dt, oa, ob, 150, 90, 200)
+            PA = dev(O.uniform(rng, (A.shape[0] + 2, A.shape[1] + 8), dt), cuda)
+            PB = dev(O.uniform(rng, (B.shape[0] + 1, B.shape[1] + 4), dt), cuda)
+            PA[1:1 + A.shape[0], 4:4 + A.shape[1]] = dev(A, cuda)
+            PB[1:1 + B.shape[0], 4:4 + B.shape[1]] = dev(B, cuda)
+            PC = torch.zeros((152, 96), dtype=PA.dtype, device=cuda)
+            ab.gemm(al, oa, PA[1:1 + A.shape[0], 4:4 + A.shape[1]], ob, PB[1:1 + B.shape[0], 4:4 + B.shape[1]], out=PC[1:151, 4:94])
+            C = np.ascontiguousarray(host(PC)[1:151, 4:94])
+            assert O.gemm_error_units(C, O.gemm(al, oa, A, ob, B, wide=True), A, B, 200, al) <= TOL_UNITS_TF32X3
+    finally:
+        ab.set_tuning(2, -1)
+        ab.set_tuning(3, -1)
+
+
+@pytest.mark.parametrize("dt", DTYPES, ids=ids)
+def test_gemm_many_small_tiles_short_k(dt, cuda):
+    """Hundreds of co-resident 32 x 32 CTAs whose smem ring wraps after a few K-blocks: the regime in
+    which a consumer's stage release raced the producer's refill (fixed by the proxy fence in
+    tma::consumer_release_fence).  The WHOLE result is compared, three times."""
+    import accblas_b200 as ab
+    rng = np.random.default_rng(2900 + dt)
+    knob, tile = {O.F64: (0, 3), O.C64: (1, 2), O.F32: (3, 2), O.C32: (3, 2)}[dt]
+    try:
+        ab.set_tuning(knob, tile)
+        if dt in (O.F32, O.C32):
+            ab.set_tuning(2, 1)
+        for (m, n, k) in [(768, 768, 96), (1024, 1024, 64)]:
+            for oa, ob in [("N", "N"), ("T", "N"), ("N", "H")]:
+                al, A, B = gemm_inputs(rng, dt, oa, ob, m, n, k)
+                ref = O.gemm(al, oa, A, ob, B, wide=True)
+                dA, dB = dev(A, cuda), dev(B, cuda)
+                for rep in range(3):
+                    err = O.gemm_error_units(host(ab.gemm(al, oa, dA, ob, dB)), ref, A, B, k, al)
+                    assert err <= TOL_UNITS_TF32X3, (O.NAMES[dt], oa, ob, m, n, k, rep, err)
+    finally:
+        ab.set_tuning(knob, -1)
+        ab.set_tuning(2, -1)
 
 
 @pytest.mark.parametrize("dt", DTYPES, ids=ids)
@@ -344,16 +426,20 @@ def test_host_pipeline_wavefront(dt, cuda):
     P x Q block grids with P != Q, ragged last panels, every op pair; checked on sampled rows."""
     import accblas_b200 as ab
     rng = np.random.default_rng(7700 + dt)
-    for (m, n, k) in [(1536, 1100, 96), (700, 2100, 64), (2304, 520, 40)]:
-        for oa in OPN:
-            for ob in OPN:
-                al, A, B = gemm_inputs(rng, dt, oa, ob, m, n, k)
-                C = ab.gemm(al, oa, A, ob, B)
-                rows = np.arange(0, m, 41)
-                Asub = A[rows] if oa == "N" else np.ascontiguousarray(A[:, rows])
-                ref = O.gemm(al, oa, Asub, ob, B, wide=True)
-                err = O.gemm_error_units(np.ascontiguousarray(C[rows]), ref, Asub, B, k, al)
-                assert err <= TOL_UNITS_TF32X3, (O.NAMES[dt], oa, ob, m, n, k, err)
+    ab.set_tuning(4, 1)                           # ACCBLAS_TUNE_HOST_PIPELINE: wavefront whatever the size
+    try:
+        for (m, n, k) in [(1536, 1100, 96), (700, 2100, 64), (2304, 520, 40)]:
+            for oa in OPN:
+                for ob in OPN:
+                    al, A, B = gemm_inputs(rng, dt, oa, ob, m, n, k)
+                    C = ab.gemm(al, oa, A, ob, B)
+                    rows = np.arange(0, m, 41)
+                    Asub = A[rows] if oa == "N" else np.ascontiguousarray(A[:, rows])
+                    ref = O.gemm(al, oa, Asub, ob, B, wide=True)
+                    err = O.gemm_error_units(np.ascontiguousarray(C[rows]), ref, Asub, B, k, al)
+                    assert err <= TOL_UNITS_TF32X3, (O.NAMES[dt], oa, ob, m, n, k, err)
+    finally:
+        ab.set_tuning(4, -1)
     # linearity over the whole result at a larger size (all blocks of the wavefront are covered)
     al, A, B = gemm_inputs(rng, dt, "N", "N", 2048, 2048, 256)
     A2 = O.uniform(rng, A.shape, dt)
