@@ -228,7 +228,7 @@ typedef enum {
     ACCBLAS_TUNE_SGEMM_FAMILY = 2, /* f32/c32 gemm: 1 = mma.sync path, 2 = tcgen05 path (if eligible)    */
     ACCBLAS_TUNE_SMMA_TILE = 3, /* mma.sync path CTA tile: 0 = 128x64 (c32: 64x64), 1 = 64x64, 2 = 32x32 */
     ACCBLAS_TUNE_HOST_PIPELINE = 4, /* accblas_gemm_host: 1 = wavefront even for small transfers, 0 = never */
-    ACCBLAS_TUNE_RESERVED5 = 5,
+    ACCBLAS_TUNE_RASTER_GROUP = 5,  /* f64 gemm: tile rows per rasterisation group (default 16)              */
     ACCBLAS_TUNE_RESERVED6 = 6,
     ACCBLAS_TUNE_RESERVED7 = 7,
     ACCBLAS_TUNE_COUNT = 8
