@@ -303,8 +303,8 @@ size_t accblas_gemm_workspace_bytes(int dtype, int opA, int opB, int64_t rowsA, 
     return pick_family(g) == FAM_TC ? sgemm_tc_workspace(g) : 0;
 }
 
-int accblas_gemv(accblas_stream_t stream, int dtype, int opA, int64_t rowsA, int64_t colsA,
-                 const void *alpha_host, const void *A, const void *x, int64_t lenx, void *y)
+static int gemv_entry(accblas_stream_t stream, int dtype, int opA, int64_t rowsA, int64_t colsA,
+                      const void *alpha_host, bool alpha_dev, const void *A, const void *x, int64_t lenx, void *y)
 {
     if (bad_dtype(dtype)) return ACCBLAS_ERR_DTYPE;
     if (bad_op(opA)) return ACCBLAS_ERR_OP;
@@ -321,7 +321,30 @@ int accblas_gemv(accblas_stream_t stream, int dtype, int opA, int64_t rowsA, int
         return ACCBLAS_ERR_ALIAS;
     ACC_TRY(device_check());
     if (!is_complex(dtype) && opA == ACCBLAS_OP_H) opA = ACCBLAS_OP_T;
-    return gemv_dispatch(static_cast<cudaStream_t>(stream), dtype, opA, rowsA, colsA, alpha_host, A, x, y);
+    return gemv_dispatch(static_cast<cudaStream_t>(stream), dtype, opA, rowsA, colsA, alpha_host, alpha_dev, A, x, y);
+}
+
+int accblas_gemv(accblas_stream_t stream, int dtype, int opA, int64_t rowsA, int64_t colsA,
+                 const void *alpha_host, const void *A, const void *x, int64_t lenx, void *y)
+{
+    return gemv_entry(stream, dtype, opA, rowsA, colsA, alpha_host, false, A, x, lenx, y);
+}
+
+int accblas_gemv_alpha_dev(accblas_stream_t stream, int dtype, int opA, int64_t rowsA, int64_t colsA,
+                           const void *alpha_dev, const void *A, const void *x, int64_t lenx, void *y)
+{
+    return gemv_entry(stream, dtype, opA, rowsA, colsA, alpha_dev, true, A, x, lenx, y);
+}
+
+int accblas_gemm_alpha_dev(accblas_stream_t stream, int dtype, int opA, int opB, int64_t rowsA, int64_t colsA,
+                           int64_t rowsB, int64_t colsB, const void *alpha_dev, const void *A, const void *B, void *C)
+{
+    GemmArgs g{};
+    g.dtype = dtype; g.opA = opA; g.opB = opB;
+    g.rowsA = rowsA; g.colsA = colsA; g.rowsB = rowsB; g.colsB = colsB;
+    g.alpha = alpha_dev; g.alpha_dev = true; g.A = A; g.B = B; g.C = C;
+    g.stream = static_cast<cudaStream_t>(stream);
+    return gemm_device(g);
 }
 
 int accblas_dot(accblas_stream_t stream, int dtype, int conj_x, int64_t n, const void *x, const void *y,

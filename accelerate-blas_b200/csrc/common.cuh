@@ -116,6 +116,20 @@ __device__ __forceinline__ int4 ldg_cached(const void *p) {
     return __ldg(reinterpret_cast<const int4 *>(p));
 }
 
+// alpha as a kernel argument: a value read on the host at call time (the reference's convention,
+// LLVM/PTX/Level3.hs:81,89) or a device pointer dereferenced by the kernel (no host round trip).
+template <typename T> struct Alpha {
+    T v;
+    const T *dev;
+    __device__ __forceinline__ T get() const { return dev ? *dev : v; }
+};
+template <typename T> inline Alpha<T> make_alpha(const void *p, bool on_device) {
+    Alpha<T> a;
+    if (on_device) { a.v = Scalar<T>::zero(); a.dev = static_cast<const T *>(p); }
+    else { a.v = *static_cast<const T *>(p); a.dev = nullptr; }
+    return a;
+}
+
 // ----------------------------------------------------------------------------------
 // kernel-family entry points (one translation unit each)
 // ----------------------------------------------------------------------------------
@@ -124,7 +138,8 @@ struct GemmArgs {
     int64_t rowsA, colsA, rowsB, colsB;   // stored (pre-op) shapes
     int64_t m, n, k;                      // derived: C is m x n, inner extent k
     int64_t lda, ldb, ldc;                // row pitches in ELEMENTS (0 = tight: colsA, colsB, n)
-    const void *alpha;                    // host pointer, one element
+    const void *alpha;                    // one element: host pointer, or device pointer if alpha_dev
+    bool alpha_dev;                       // alpha is read by the kernel (accblas_*_alpha_dev entry points)
     const void *A, *B;
     void *C;
     cudaStream_t stream;
@@ -144,7 +159,7 @@ bool sgemm_mma_eligible(const GemmArgs &g);           // gemm_mma_tf32.cu : f32 
 int  sgemm_mma(const GemmArgs &g);
 
 int gemv_dispatch(cudaStream_t s, int dtype, int opA, int64_t rowsA, int64_t colsA,
-                  const void *alpha, const void *A, const void *x, void *y);          // gemv.cu
+                  const void *alpha, bool alpha_dev, const void *A, const void *x, void *y);   // gemv.cu
 int dot_dispatch(cudaStream_t s, int dtype, int conj_x, int64_t n,
                  const void *x, const void *y, void *out);                            // dot.cu
 

@@ -70,7 +70,7 @@ __device__ __forceinline__ int kslot(int s, int t) {
 
 struct DgemmParams {
     int64_t m, n, k, ldc;
-    double alpha;
+    Alpha<double> alpha;
     double *C;
     int tiles_m, tiles_n, group;
 };
@@ -191,6 +191,7 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
 
     // ---- epilogue: C = alpha * acc (never read C) ----
     const bool vec = ((p.n | p.ldc) & 1) == 0;
+    const double alpha = p.alpha.get();
 #pragma unroll
     for (int i = 0; i < MI; ++i) {
         const int64_t r = m0 + wm * MI * 8 + i * 8 + g;
@@ -199,7 +200,7 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
 #pragma unroll
         for (int j = 0; j < NJ; ++j) {
             const int64_t c = n0 + wn * NJ * 8 + j * 8 + 2 * t;
-            const double v0 = p.alpha * acc[i][j][0], v1 = p.alpha * acc[i][j][1];
+            const double v0 = alpha * acc[i][j][0], v1 = alpha * acc[i][j][1];
             if (vec) {
                 if (c < p.n) *reinterpret_cast<double2 *>(crow + c) = make_double2(v0, v1);
             } else {
@@ -256,7 +257,7 @@ __device__ __forceinline__ double flip(double x) {
 
 struct ZgemmParams {
     int64_t m, n, k, ldc;
-    double alr, ali;
+    Alpha<double2> alpha;
     double2 *C;
     int tiles_m, tiles_n;
 };
@@ -390,6 +391,7 @@ zgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
         if (lane == 0) tma::mbar_arrive(bar_base + 8 * (ZSTAGES + s));
     }
 
+    const double2 al = p.alpha.get();
 #pragma unroll
     for (int i = 0; i < MI; ++i) {
         const int64_t r = m0 + wm * MI * 8 + i * 8 + g;
@@ -402,7 +404,7 @@ zgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
             for (int e = 0; e < 2; ++e) {
                 if (c + e < p.n) {
                     const double xr = cr[i][j][e], xi = ci[i][j][e];
-                    crow[c + e] = make_double2(p.alr * xr - p.ali * xi, p.alr * xi + p.ali * xr);
+                    crow[c + e] = make_double2(al.x * xr - al.y * xi, al.x * xi + al.y * xr);
                 }
             }
         }
@@ -463,7 +465,7 @@ int launch_dgemm_tile(const GemmArgs &g)
     }
     DgemmParams p;
     p.m = g.m; p.n = g.n; p.k = g.k; p.ldc = g.ldc;
-    p.alpha = *static_cast<const double *>(g.alpha);
+    p.alpha = make_alpha<double>(g.alpha, g.alpha_dev);
     p.C = static_cast<double *>(g.C);
     p.tiles_m = (int)((g.m + BM - 1) / BM);
     p.tiles_n = (int)((g.n + BN - 1) / BN);
@@ -503,8 +505,7 @@ int launch_zgemm_tile(const GemmArgs &g)
     }
     ZgemmParams p;
     p.m = g.m; p.n = g.n; p.k = g.k; p.ldc = g.ldc;
-    p.alr = static_cast<const double *>(g.alpha)[0];
-    p.ali = static_cast<const double *>(g.alpha)[1];
+    p.alpha = make_alpha<double2>(g.alpha, g.alpha_dev);
     p.C = static_cast<double2 *>(g.C);
     p.tiles_m = (int)((g.m + ZBM - 1) / ZBM);
     p.tiles_n = (int)((g.n + ZBN - 1) / ZBN);

@@ -25,9 +25,10 @@ __device__ __forceinline__ T ld_guard(const T *__restrict__ p, int64_t rows, int
 template <typename T, bool TA, bool TB>
 __global__ void __launch_bounds__(NT)
 gemm_generic_kernel(int64_t m, int64_t n, int64_t k, int64_t rowsA, int64_t colsA, int64_t rowsB,
-                    int64_t colsB, int64_t lda, int64_t ldb, int64_t ldc, bool conjA, bool conjB, T alpha,
+                    int64_t colsB, int64_t lda, int64_t ldb, int64_t ldc, bool conjA, bool conjB, Alpha<T> alpha_,
                     const T *__restrict__ A, const T *__restrict__ B, T *__restrict__ C)
 {
+    const T alpha = alpha_.get();
     __shared__ T As[BK][BM + 1];
     __shared__ T Bs[BK][BN + 1];
     const int tid = threadIdx.x;
@@ -94,7 +95,7 @@ int launch_typed(const GemmArgs &g)
     const bool ta = g.opA != ACCBLAS_OP_N, tb = g.opB != ACCBLAS_OP_N;
     const bool ca = Scalar<T>::cplx && g.opA == ACCBLAS_OP_H;
     const bool cb = Scalar<T>::cplx && g.opB == ACCBLAS_OP_H;
-    const T alpha = *static_cast<const T *>(g.alpha);
+    const Alpha<T> alpha = make_alpha<T>(g.alpha, g.alpha_dev);
     dim3 grid((unsigned)((g.n + BN - 1) / BN), (unsigned)((g.m + BM - 1) / BM));
     if (grid.y > 65535u) return ACCBLAS_ERR_SHAPE;
     const T *A = static_cast<const T *>(g.A), *B = static_cast<const T *>(g.B);
@@ -122,9 +123,10 @@ constexpr int R1_THREADS = 256, R1_ROWS = 8;
 
 template <typename T>
 __global__ void __launch_bounds__(R1_THREADS)
-gemm_rank1_kernel(int64_t m, int64_t n, int64_t sa, int64_t sb, int64_t ldc, bool conjA, bool conjB, T alpha,
+gemm_rank1_kernel(int64_t m, int64_t n, int64_t sa, int64_t sb, int64_t ldc, bool conjA, bool conjB, Alpha<T> alpha_,
                   const T *__restrict__ A, const T *__restrict__ B, T *__restrict__ C, bool vec_ok)
 {
+    const T alpha = alpha_.get();
     constexpr int VEC = 16 / sizeof(T);
     const int64_t j0 = ((int64_t)blockIdx.x * R1_THREADS + threadIdx.x) * VEC;
     const int64_t i0 = (int64_t)blockIdx.y * R1_ROWS;
@@ -161,7 +163,7 @@ template <typename T>
 int launch_rank1(const GemmArgs &g)
 {
     constexpr int VEC = 16 / sizeof(T);
-    const T alpha = *static_cast<const T *>(g.alpha);
+    const Alpha<T> alpha = make_alpha<T>(g.alpha, g.alpha_dev);
     const bool ca = Scalar<T>::cplx && g.opA == ACCBLAS_OP_H, cb = Scalar<T>::cplx && g.opB == ACCBLAS_OP_H;
     // op(A) is m x 1: stored (m x 1, pitch lda) for N, stored (1 x m) for T/H
     const int64_t sa = g.opA == ACCBLAS_OP_N ? g.lda : 1;

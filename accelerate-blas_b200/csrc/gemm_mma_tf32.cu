@@ -80,7 +80,8 @@ using STile32  = STile<1, 2, 2, 2, 3, 7>;   //  32 x  32, 4 warps of 16 x 16
 
 struct SgemmMmaParams {
     int64_t m, n, k, ldc;
-    float alr, ali;
+    Alpha<float> alpha;        // real kernels
+    Alpha<float2> calpha;      // complex kernels
     float *C;
     int tiles_m, tiles_n;
 };
@@ -228,6 +229,7 @@ sgemm_mma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
 
     // ---- epilogue: C = alpha * (tot + acc), never read C ----
     const bool vec = ((p.n | p.ldc) & 1) == 0;
+    const float alr = p.alpha.get();
 #pragma unroll
     for (int i = 0; i < MI; ++i)
 #pragma unroll
@@ -238,8 +240,8 @@ sgemm_mma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
 #pragma unroll
             for (int j = 0; j < NJ; ++j) {
                 const int64_t c = n0 + wn * NJ * 8 + j * 8 + 2 * t;
-                const float v0 = p.alr * (tot[i][j][2 * hr] + acc[i][j][2 * hr]);
-                const float v1 = p.alr * (tot[i][j][2 * hr + 1] + acc[i][j][2 * hr + 1]);
+                const float v0 = alr * (tot[i][j][2 * hr] + acc[i][j][2 * hr]);
+                const float v1 = alr * (tot[i][j][2 * hr + 1] + acc[i][j][2 * hr + 1]);
                 if (vec) {
                     if (c < p.n) *reinterpret_cast<float2 *>(crow + c) = make_float2(v0, v1);
                 } else {
@@ -388,6 +390,7 @@ cgemm_mma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
     }
 
     float2 *C = reinterpret_cast<float2 *>(p.C);
+    const float2 al = p.calpha.get();
 #pragma unroll
     for (int i = 0; i < MI; ++i)
 #pragma unroll
@@ -403,7 +406,7 @@ cgemm_mma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                     if (c < p.n) {
                         const float xr = tre[i][j][2 * hr + e] + are[i][j][2 * hr + e];
                         const float xi = tim[i][j][2 * hr + e] + aim[i][j][2 * hr + e];
-                        crow[c] = make_float2(p.alr * xr - p.ali * xi, p.alr * xi + p.ali * xr);
+                        crow[c] = make_float2(al.x * xr - al.y * xi, al.x * xi + al.y * xr);
                     }
                 }
         }
@@ -431,7 +434,7 @@ int launch_sgemm_mma(const GemmArgs &g)
     }
     SgemmMmaParams p;
     p.m = g.m; p.n = g.n; p.k = g.k; p.ldc = g.ldc;
-    p.alr = *static_cast<const float *>(g.alpha); p.ali = 0.f;
+    p.alpha = make_alpha<float>(g.alpha, g.alpha_dev); p.calpha = Alpha<float2>{make_float2(0.f, 0.f), nullptr};
     p.C = static_cast<float *>(g.C);
     p.tiles_m = (int)((g.m + BM - 1) / BM);
     p.tiles_n = (int)((g.n + BN - 1) / BN);
@@ -458,8 +461,7 @@ int launch_cgemm_mma(const GemmArgs &g)
     }
     SgemmMmaParams p;
     p.m = g.m; p.n = g.n; p.k = g.k; p.ldc = g.ldc;
-    p.alr = static_cast<const float *>(g.alpha)[0];
-    p.ali = static_cast<const float *>(g.alpha)[1];
+    p.calpha = make_alpha<float2>(g.alpha, g.alpha_dev); p.alpha = Alpha<float>{0.f, nullptr};
     p.C = static_cast<float *>(g.C);
     p.tiles_m = (int)((g.m + BM - 1) / BM);
     p.tiles_n = (int)((g.n + BN - 1) / BN);

@@ -191,7 +191,7 @@ struct SgemmParams {
     int64_t Kp;            // packed inner extent
     int64_t ldc;           // floats
     float *C;
-    float alr, ali;        // alpha (ali = 0 for real)
+    Alpha<float2> alpha;   // (re, im); im = 0 for real
     int cplx;              // 1: columns are (re,im) pairs, alpha is complex
     int tiles_m, tiles_n;
 };
@@ -342,6 +342,8 @@ sgemm_tf32x3_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_con
         }
         // ---- C = alpha * acc ----
         const int64_t row = m0 + q * 32 + lane;
+        const float2 al = p.alpha.dev ? (p.cplx ? *p.alpha.dev : make_float2(*reinterpret_cast<const float *>(p.alpha.dev), 0.f))
+                                      : p.alpha.v;
         if (row < p.M) {
             float *crow = p.C + row * p.ldc;
             const int64_t col0 = n0 + h * HALF;
@@ -350,12 +352,12 @@ sgemm_tf32x3_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_con
 #pragma unroll
                 for (int i = 0; i < HALF; i += 2) {
                     const float xr = acc[i], xi = acc[i + 1];
-                    acc[i] = p.alr * xr - p.ali * xi;
-                    acc[i + 1] = p.alr * xi + p.ali * xr;
+                    acc[i] = al.x * xr - al.y * xi;
+                    acc[i + 1] = al.x * xi + al.y * xr;
                 }
             } else {
 #pragma unroll
-                for (int i = 0; i < HALF; ++i) acc[i] *= p.alr;
+                for (int i = 0; i < HALF; ++i) acc[i] *= al.x;
             }
             if (vec4) {
 #pragma unroll
@@ -421,9 +423,10 @@ int launch_tc(const GemmArgs &g, const TcPlan &t, float *ahi, float *alo, float 
     p.M = t.M; p.N = t.N; p.Kp = t.pitch;      // padding columns are zero-filled by pack_split
     p.ldc = (g.dtype == ACCBLAS_C32 ? 2 : 1) * g.ldc;
     p.C = static_cast<float *>(g.C);
-    p.alr = static_cast<const float *>(g.alpha)[0];
     p.cplx = g.dtype == ACCBLAS_C32;
-    p.ali = p.cplx ? static_cast<const float *>(g.alpha)[1] : 0.f;
+    if (g.alpha_dev) p.alpha = Alpha<float2>{make_float2(0.f, 0.f), static_cast<const float2 *>(g.alpha)};
+    else p.alpha = Alpha<float2>{make_float2(static_cast<const float *>(g.alpha)[0],
+                                            p.cplx ? static_cast<const float *>(g.alpha)[1] : 0.f), nullptr};
     p.tiles_m = (int)((t.M + TBM - 1) / TBM);
     p.tiles_n = (int)((t.N + TBN - 1) / TBN);
     const int64_t tiles = (int64_t)p.tiles_m * p.tiles_n;

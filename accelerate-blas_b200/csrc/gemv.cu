@@ -80,9 +80,10 @@ __device__ __forceinline__ void gemv_n_rows(int64_t n, int64_t nv, T alpha, cons
 
 template <typename T, bool ALIGNED>
 __global__ void __launch_bounds__(512, 2)
-gemv_n_kernel(int64_t m, int64_t n, T alpha, const T *__restrict__ A, const T *__restrict__ x,
+gemv_n_kernel(int64_t m, int64_t n, Alpha<T> alpha_, const T *__restrict__ A, const T *__restrict__ x,
               T *__restrict__ y)
 {
+    const T alpha = alpha_.get();
     constexpr int VEC = ALIGNED ? 16 / sizeof(T) : 1;
     constexpr int GN_ROWS = GnRows<T>::value;
     __shared__ T red[GN_ROWS][GN_MAX_WARPS];
@@ -102,9 +103,10 @@ constexpr int GT_XCHUNK = 1024;     // rows of x staged per shared-memory refill
 
 template <typename T, bool CONJ, bool ALIGNED>
 __global__ void __launch_bounds__(GT_THREADS, 3)
-gemv_t_kernel(int64_t m, int64_t n, int64_t rows_per_split, T alpha, const T *__restrict__ A,
+gemv_t_kernel(int64_t m, int64_t n, int64_t rows_per_split, Alpha<T> alpha_, const T *__restrict__ A,
               const T *__restrict__ x, T *__restrict__ out /* y, or partial[split][n] */, bool direct)
 {
+    const T alpha = alpha_.get();
     constexpr int VEC = ALIGNED ? 16 / sizeof(T) : 1;
     __shared__ T xs[GT_XCHUNK];
     const int64_t nv = (n + VEC - 1) / VEC;    // ALIGNED guarantees n % VEC == 0
@@ -170,9 +172,10 @@ constexpr int SLAB_CV = 8, SLAB_RG = 32, SLAB_UNROLL = 8;
 
 template <typename T, bool CONJ, bool ALIGNED>
 __global__ void __launch_bounds__(SLAB_CV * SLAB_RG)
-gemv_t_slab_kernel(int64_t m, int64_t n, T alpha, const T *__restrict__ A, const T *__restrict__ x,
+gemv_t_slab_kernel(int64_t m, int64_t n, Alpha<T> alpha_, const T *__restrict__ A, const T *__restrict__ x,
                    T *__restrict__ y)
 {
+    const T alpha = alpha_.get();
     constexpr int VEC = ALIGNED ? 16 / sizeof(T) : 1;
     __shared__ T red[SLAB_RG][SLAB_CV * VEC + 1];
     const int cv = threadIdx.x % SLAB_CV, rg = threadIdx.x / SLAB_CV;
@@ -226,8 +229,9 @@ gemv_t_slab_kernel(int64_t m, int64_t n, T alpha, const T *__restrict__ A, const
 
 template <typename T>
 __global__ void __launch_bounds__(256)
-gemv_t_reduce_kernel(int64_t n, int splits, T alpha, const T *__restrict__ partial, T *__restrict__ y)
+gemv_t_reduce_kernel(int64_t n, int splits, Alpha<T> alpha_, const T *__restrict__ partial, T *__restrict__ y)
 {
+    const T alpha = alpha_.get();
     const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= n) return;
     T s = Scalar<T>::zero();
@@ -249,10 +253,10 @@ template <typename K> int occupancy(K kernel, int threads)
 }
 
 template <typename T>
-int gemv_typed(cudaStream_t st, int opA, int64_t rowsA, int64_t colsA, const void *alpha_p,
+int gemv_typed(cudaStream_t st, int opA, int64_t rowsA, int64_t colsA, const void *alpha_p, bool alpha_dev,
                const void *A_, const void *x_, void *y_)
 {
-    const T alpha = *static_cast<const T *>(alpha_p);
+    const Alpha<T> alpha = make_alpha<T>(alpha_p, alpha_dev);
     const T *A = static_cast<const T *>(A_), *x = static_cast<const T *>(x_);
     T *y = static_cast<T *>(y_);
     const int64_t leny = opA == ACCBLAS_OP_N ? rowsA : colsA;
@@ -325,14 +329,14 @@ int gemv_typed(cudaStream_t st, int opA, int64_t rowsA, int64_t colsA, const voi
 
 }  // namespace
 
-int gemv_dispatch(cudaStream_t s, int dtype, int opA, int64_t rowsA, int64_t colsA, const void *alpha,
+int gemv_dispatch(cudaStream_t s, int dtype, int opA, int64_t rowsA, int64_t colsA, const void *alpha, bool alpha_dev,
                   const void *A, const void *x, void *y)
 {
     switch (dtype) {
-    case ACCBLAS_F32: return gemv_typed<float>(s, opA, rowsA, colsA, alpha, A, x, y);
-    case ACCBLAS_F64: return gemv_typed<double>(s, opA, rowsA, colsA, alpha, A, x, y);
-    case ACCBLAS_C32: return gemv_typed<float2>(s, opA, rowsA, colsA, alpha, A, x, y);
-    default:          return gemv_typed<double2>(s, opA, rowsA, colsA, alpha, A, x, y);
+    case ACCBLAS_F32: return gemv_typed<float>(s, opA, rowsA, colsA, alpha, alpha_dev, A, x, y);
+    case ACCBLAS_F64: return gemv_typed<double>(s, opA, rowsA, colsA, alpha, alpha_dev, A, x, y);
+    case ACCBLAS_C32: return gemv_typed<float2>(s, opA, rowsA, colsA, alpha, alpha_dev, A, x, y);
+    default:          return gemv_typed<double2>(s, opA, rowsA, colsA, alpha, alpha_dev, A, x, y);
     }
 }
 

@@ -14,6 +14,8 @@ module Data.Array.Accelerate.Numeric.LinearAlgebra.LLVM.PTX.B200.FFI (
 
   DType(..), dtypeCode, opCode, Status, checkStatus,
   c_accblas_gemm, c_accblas_gemv, c_accblas_dot,
+  c_accblas_gemm_alpha_dev, c_accblas_gemv_alpha_dev,
+  c_accblas_sdot, c_accblas_asum, c_accblas_amax, c_accblas_amin,
 
 ) where
 
@@ -61,6 +63,33 @@ foreign import ccall unsafe "accblas_dot"
   c_accblas_dot  :: Ptr () -> CInt -> CInt -> Int64         -- stream, dtype, conj_x, n
                  -> Ptr () -> Ptr () -> Ptr ()              -- x y out(device)
                  -> IO Status
+
+-- alpha as the device Scalar it already is (BLAS/Level3.hs:64): no indexRemote, no stream sync
+foreign import ccall unsafe "accblas_gemm_alpha_dev"
+  c_accblas_gemm_alpha_dev :: Ptr () -> CInt -> CInt -> CInt
+                           -> Int64 -> Int64 -> Int64 -> Int64
+                           -> Ptr () -> Ptr () -> Ptr () -> Ptr ()    -- alpha(DEVICE) A B C
+                           -> IO Status
+
+foreign import ccall unsafe "accblas_gemv_alpha_dev"
+  c_accblas_gemv_alpha_dev :: Ptr () -> CInt -> CInt
+                           -> Int64 -> Int64
+                           -> Ptr () -> Ptr () -> Ptr () -> Int64     -- alpha(DEVICE) A x |x|
+                           -> Ptr () -> IO Status
+
+-- the remaining Level-1 reductions (BLAS/Level1.hs:44-62, 100-143); results in device memory
+foreign import ccall unsafe "accblas_sdot"
+  c_accblas_sdot :: Ptr () -> CInt -> Int64 -> Ptr ()       -- stream, dtype, n, z(host)
+                 -> Ptr () -> Ptr () -> Ptr () -> IO Status -- x y out(device)
+
+foreign import ccall unsafe "accblas_asum"
+  c_accblas_asum :: Ptr () -> CInt -> Int64 -> Ptr () -> Ptr () -> IO Status   -- out: base type
+
+foreign import ccall unsafe "accblas_amax"
+  c_accblas_amax :: Ptr () -> CInt -> Int64 -> Ptr () -> Ptr () -> IO Status   -- out: Int (64-bit)
+
+foreign import ccall unsafe "accblas_amin"
+  c_accblas_amin :: Ptr () -> CInt -> Int64 -> Ptr () -> Ptr () -> IO Status
 
 foreign import ccall unsafe "accblas_status_string"
   c_accblas_status_string :: CInt -> IO CString

@@ -18,7 +18,7 @@
 -- cuBLAS, and the gemm detour for complex-H gemv (LLVM/PTX/Level2.hs:52-69).
 -- What is new: the backend's stream is passed down (the reference never called setStream).
 --
-module Data.Array.Accelerate.Numeric.LinearAlgebra.LLVM.PTX.B200.Hooks ( gemm, gemv, dot ) where
+module Data.Array.Accelerate.Numeric.LinearAlgebra.LLVM.PTX.B200.Hooks ( gemm, gemmAlphaDev, gemv, dot, tag, raw, streamPtr ) where
 
 import Data.Array.Accelerate.Numeric.LinearAlgebra.Type
 import Data.Array.Accelerate.Numeric.LinearAlgebra.LLVM.PTX.Base            ( withArray, withV2 )
@@ -72,6 +72,31 @@ gemm nR opA opB = ForeignAcc "ptx.gemm" $ \((((), alpha), matA), matB) -> do
             c_accblas_gemm (streamPtr stream) (dtypeCode (tag nR)) (opCode opA) (opCode opB)
                            (fromIntegral rowsA) (fromIntegral colsA) (fromIntegral rowsB) (fromIntegral colsB)
                            pAlpha (raw pA) (raw pB) (raw pC)
+  put future matC
+  return future
+
+-- | The same hook without the blocking `indexRemote`: alpha stays the device Scalar that
+-- BLAS/Level3.hs:64 builds (`unit alpha`) and the kernel reads it (accblas_gemm_alpha_dev).  This removes
+-- the one host synchronisation the reference pays per product (LLVM/PTX/Level3.hs:81).
+gemmAlphaDev :: NumericR s e -> Transpose -> Transpose
+             -> ForeignAcc (((((), Scalar e), Matrix e), Matrix e) -> Matrix e)
+gemmAlphaDev nR opA opB = ForeignAcc "ptx.gemm" $ \((((), alpha), matA), matB) -> do
+  let (((), rowsA), colsA) = shape matA
+      (((), rowsB), colsB) = shape matB
+      m = if opA == N then rowsA else colsA
+      n = if opB == N then colsB else rowsB
+  future <- new
+  stream <- asks ptxStream
+  matC   <- allocateRemote (ArrayR dim2 (eltOf nR)) (((), m), n)
+  ()     <- liftPar $
+    withArray nR alpha stream    $ \pAlpha ->
+     withArray nR matA stream    $ \pA ->
+      withArray nR matB stream   $ \pB ->
+       withArray nR matC stream  $ \pC -> liftIO $
+          checkStatus "accblas_gemm_alpha_dev" =<<
+            c_accblas_gemm_alpha_dev (streamPtr stream) (dtypeCode (tag nR)) (opCode opA) (opCode opB)
+                                     (fromIntegral rowsA) (fromIntegral colsA) (fromIntegral rowsB) (fromIntegral colsB)
+                                     (raw pAlpha) (raw pA) (raw pB) (raw pC)
   put future matC
   return future
 

@@ -82,6 +82,16 @@ def _alpha_buf(alpha, code: int):
     return buf, buf.ctypes.data_as(ctypes.c_void_p)
 
 
+def _alpha_on_device(alpha, code: int) -> bool:
+    """alpha given as a one-element CUDA tensor (the reference's device `Scalar e`, BLAS/Level3.hs:64):
+    the kernel reads it, no host round trip (accblas_*_alpha_dev)."""
+    if not (_is_torch(alpha) and alpha.is_cuda):
+        return False
+    if alpha.numel() != 1 or _code(alpha) != code:
+        raise TypeError("alpha on the device must be a one-element tensor of the operands' element type")
+    return True
+
+
 def _dev_operand(a, code: int, ndim: int, name: str):
     if not _is_torch(a) or not a.is_cuda:
         raise TypeError(f"{name}: expected a CUDA tensor when the first operand is one")
@@ -134,8 +144,20 @@ def gemm(alpha, opA, A, opB, B, out=None):
     """
     oa, ob = _op(opA), _op(opB)
     code = _code(A)
-    al_keep, al = _alpha_buf(alpha, code)
     L = lib()
+    if _is_torch(A) and _alpha_on_device(alpha, code):
+        torch = _torch()
+        A = _dev_operand(A, code, 2, "gemm: A")
+        B = _dev_operand(B, code, 2, "gemm: B")
+        m = A.shape[0] if oa == N else A.shape[1]
+        n = B.shape[1] if ob == N else B.shape[0]
+        with torch.cuda.device(A.device):
+            C = torch.empty((m, n), dtype=A.dtype, device=A.device) if out is None else out
+            st = L.accblas_gemm_alpha_dev(_stream(A), code, oa, ob, A.shape[0], A.shape[1], B.shape[0], B.shape[1],
+                                          _ptr(alpha), _ptr(A), _ptr(B), _ptr(C))
+        _ffi.check(st, "accblas_gemm_alpha_dev")
+        return C
+    al_keep, al = _alpha_buf(alpha, code)
     if _is_torch(A):
         torch = _torch()
         A, lda = _dev_matrix(A, code, "gemm: A")
@@ -177,8 +199,10 @@ def gemv(alpha, opA, A, x):
     """``y = alpha * op(A) * x`` -- gemv, BLAS/Level2.hs:57-63."""
     oa = _op(opA)
     code = _code(A)
-    al_keep, al = _alpha_buf(alpha, code)
     L = lib()
+    on_dev = _is_torch(A) and _alpha_on_device(alpha, code)
+    if not on_dev:
+        al_keep, al = _alpha_buf(alpha, code)
     if _is_torch(A):
         torch = _torch()
         A = _dev_operand(A, code, 2, "gemv: A")
@@ -186,8 +210,9 @@ def gemv(alpha, opA, A, x):
         leny = A.shape[0] if oa == N else A.shape[1]       # LLVM/PTX/Level2.hs:80-82
         with torch.cuda.device(A.device):
             y = torch.empty((leny,), dtype=A.dtype, device=A.device)
-            st = L.accblas_gemv(_stream(A), code, oa, A.shape[0], A.shape[1], al, _ptr(A), _ptr(x),
-                                x.shape[0], _ptr(y))
+            fn = L.accblas_gemv_alpha_dev if on_dev else L.accblas_gemv
+            st = fn(_stream(A), code, oa, A.shape[0], A.shape[1], _ptr(alpha) if on_dev else al, _ptr(A), _ptr(x),
+                    x.shape[0], _ptr(y))
         _ffi.check(st, "accblas_gemv")
         return y
     A = _host_operand(A, code, 2, "gemv: A")

@@ -95,6 +95,16 @@ int accblas_gemm_ld(accblas_stream_t stream, int dtype, int opA, int opB,
                     const void *alpha_host, const void *A, int64_t lda, const void *B, int64_t ldb,
                     void *C, int64_t ldc);
 
+/* alpha in DEVICE memory, read by the kernel: the reference turns `alpha :: Exp e` into a device
+ * Scalar (BLAS/Level3.hs:64) and then copies it back with a blocking indexRemote before every call
+ * (LLVM/PTX/Level3.hs:81; LLVM/PTX/Level2.hs:99) because cuBLAS is used in host-pointer mode.  These
+ * variants take that device Scalar as it is: no device-to-host copy, no stream synchronisation. */
+int accblas_gemm_alpha_dev(accblas_stream_t stream, int dtype, int opA, int opB,
+                           int64_t rowsA, int64_t colsA, int64_t rowsB, int64_t colsB,
+                           const void *alpha_dev, const void *A, const void *B, void *C);
+int accblas_gemv_alpha_dev(accblas_stream_t stream, int dtype, int opA, int64_t rowsA, int64_t colsA,
+                           const void *alpha_dev, const void *A, const void *x, int64_t lenx, void *y);
+
 /* Bytes of stream-ordered scratch accblas_gemm will take from the device's default
  * memory pool for this problem (0 for the direct kernels).  Informational. */
 size_t accblas_gemm_workspace_bytes(int dtype, int opA, int opB,

@@ -447,6 +447,32 @@ def test_host_pipeline_wavefront(dt, cuda):
     assert O.gemm_error_units(C12, C1 + C2, A + A2, B, 256, al) <= 3 * TOL_UNITS_TF32X3
 
 
+@pytest.mark.parametrize("dt", DTYPES, ids=ids)
+def test_alpha_on_device(dt, cuda):
+    """accblas_gemm_alpha_dev / accblas_gemv_alpha_dev: alpha read by the kernel from device memory gives
+    bit-identical results to alpha passed by host pointer, in every kernel family."""
+    import torch
+    import accblas_b200 as ab
+    rng = np.random.default_rng(7900 + dt)
+    shapes = [(40, 24, 1), (30, 20, 10), (200, 136, 72), (129, 65, 33), (512, 512, 512)]
+    if dt in (O.F32, O.C32):
+        shapes.append((1280, 1280, 1280))               # tcgen05 family
+    for (m, n, k) in shapes:
+        for oa, ob in [("N", "N"), ("H", "T")]:
+            al, A, B = gemm_inputs(rng, dt, oa, ob, m, n, k)
+            dA, dB = dev(A, cuda), dev(B, cuda)
+            dal = dev(np.array([al], dtype=A.dtype), cuda)
+            C0 = ab.gemm(al, oa, dA, ob, dB)
+            C1 = ab.gemm(dal, oa, dA, ob, dB)
+            assert torch.equal(C0, C1), (O.NAMES[dt], m, n, k, oa, ob, ab.kernel_name(dt, oa, ob, A.shape, B.shape))
+    for (m, n) in [(67, 130), (1000, 2000), (4200, 4100)]:
+        for oa in OPN:
+            al, A, x = gemv_inputs(rng, dt, oa, m, n)
+            dA, dx = dev(A, cuda), dev(x, cuda)
+            dal = dev(np.array([al], dtype=A.dtype), cuda)
+            assert torch.equal(ab.gemv(al, oa, dA, dx), ab.gemv(dal, oa, dA, dx)), (O.NAMES[dt], m, n, oa)
+
+
 def test_launches_are_counted(cuda):
     import torch
     import accblas_b200 as ab
