@@ -20,3 +20,9 @@ cap zgemm_hn_4096   zgemm_dmma      2 $P gemm c64 H N 4096 4096 4096 3
 cap gemv_n_f64      gemv_n_kernel   2 $P gemv f64 N 32768 32768 3
 cap gemv_t_f64      gemv_t_kernel   2 $P gemv f64 T 32768 32768 3
 cap dot_f64         dot_partial     2 $P dot f64 268435456 3
+cap dgemm_nn_500    dgemm_dmma      2 $P gemm f64 N N 500 500 500 3
+cap sgemm_mma_1000  sgemm_mma       2 $P gemm f32 N N 1000 1000 1000 3
+cap cgemm_mma_500   cgemm_mma       2 $P gemm c32 N N 500 500 500 3
+cap gemv_t_slab     gemv_t_slab     2 $P gemv f64 T 2000 3000 3
+cap asum_f64        asum_partial    2 $P asum f64 268435456 3
+cap amax_f32        iamax_partial   2 $P amax f32 134217728 3

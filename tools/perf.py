@@ -73,6 +73,16 @@ def dot_case(dt, n, iters=30):
                       "gbs_median": round(by / med * 1e-6, 1), "gbs_best": round(by / best * 1e-6, 1)}), flush=True)
 
 
+def l1_case(name, dt, n, iters=30):
+    x, y = rnd((n,), dt, 5), rnd((n,), dt, 6)
+    fn = {"asum": lambda: ab.asum(x), "amax": lambda: ab.amax(x), "amin": lambda: ab.amin(x),
+          "sdot": lambda: ab.sdot(0.5, x, y)}[name]
+    med, best = timeit(fn, iters)
+    by = (2 if name == "sdot" else 1) * ES[dt] * n
+    print(json.dumps({"case": f"{dt}{name}_{n}", "ms_median": round(med, 4), "ms_best": round(best, 4),
+                      "gbs_median": round(by / med * 1e-6, 1), "gbs_best": round(by / best * 1e-6, 1)}), flush=True)
+
+
 def suite():
     for n in (100, 250, 500, 512, 1000, 1024, 2048, 4096):
         gemm_case("f64", "N", "N", n, n, n, 50)
@@ -94,6 +104,9 @@ def suite():
     for dt in ("f64", "f32", "c64", "c32"):
         dot_case(dt, 1 << 28 if dt == "f64" else 1 << 27)
     dot_case("f64", 1 << 20)
+    for name in ("sdot", "asum", "amax", "amin"):
+        for dt in ("f64", "f32", "c64", "c32"):
+            l1_case(name, dt, 1 << 28 if dt == "f64" else 1 << 27)
 
 
 if __name__ == "__main__":
@@ -104,5 +117,7 @@ if __name__ == "__main__":
         gemm_case(a[1], a[2], a[3], int(a[4]), int(a[5]), int(a[6]), int(a[7]) if len(a) > 7 else 10)
     elif a[0] == "gemv":
         gemv_case(a[1], a[2], int(a[3]), int(a[4]), int(a[5]) if len(a) > 5 else 30)
+    elif a[0] in ("asum", "amax", "amin", "sdot"):
+        l1_case(a[0], a[1], int(a[2]), int(a[3]) if len(a) > 3 else 30)
     elif a[0] == "dot":
         dot_case(a[1], int(a[2]), int(a[3]) if len(a) > 3 else 30)
