@@ -69,10 +69,10 @@ Streams &thread_streams()
     return s;
 }
 
-// panel extent: a multiple of 128, at most `maxp` panels, at least 512 wide
+// panel extent: a multiple of 128, at most `maxp` panels, at least 256 wide
 int64_t panel_extent(int64_t extent, int maxp)
 {
-    int64_t w = std::max<int64_t>(512, (extent + maxp - 1) / maxp);
+    int64_t w = std::max<int64_t>(256, (extent + maxp - 1) / maxp);
     return (w + 127) / 128 * 128;
 }
 
@@ -103,7 +103,8 @@ int gemm_host_pipeline(const GemmArgs &g0, const void *A_host, const void *B_hos
     ACC_CUDA(dC.alloc(bytesC));
 
     // the tcgen05 family re-packs the operand views of every strip: fewer, larger panels there
-    const int maxp = (g.dtype == ACCBLAS_F32 || g.dtype == ACCBLAS_C32) ? 8 : 16;
+    const int maxp = g_tuning[ACCBLAS_TUNE_HOST_PANELS] > 0 ? g_tuning[ACCBLAS_TUNE_HOST_PANELS]
+                   : (g.dtype == ACCBLAS_F32 || g.dtype == ACCBLAS_C32) ? 8 : 32;   // swept: tools/exp/host_panels.py
     const int64_t pm = panel_extent(g.m, maxp), pn = panel_extent(g.n, maxp);
     const int P = (int)((g.m + pm - 1) / pm), Q = (int)((g.n + pn - 1) / pn);
 

@@ -87,6 +87,23 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
+def ncu_traffic(name="r01_dgemm_nn_8192_ncu.txt"):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the committed
+    `ncu --set full` summary of the same kernel and shape (profiles/; tools/ncu_capture.sh)."""
+    unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    total, seen = 0.0, 0
+    try:
+        with open(os.path.join(ROOT, "profiles", name)) as f:
+            for line in f:
+                t = line.split()
+                if len(t) >= 3 and t[0] in ("dram__bytes_read.sum", "dram__bytes_write.sum") and t[1] in unit:
+                    total += float(t[2].strip("[]',")) * unit[t[1]]
+                    seen += 1
+    except (OSError, ValueError):
+        return None
+    return round(total) if seen == 2 else None
+
+
 def dmma_peak_live():
     """Issue-rate peak of the FP64 tensor pipe measured on THIS box (baseline/ubench, < 1 s)."""
     exe = os.path.join(ROOT, "baseline", "ubench")
@@ -261,8 +278,10 @@ def run_single(args):
         "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic uniform(-1,1), fixed Philox seeds",
         "config": workload_config(1),
         "roofline": {"bound": "tensor", "achieved": round(flops / kernel_ms * 1e-9, 3), "peak": round(peak, 2),
-                     "unit": "TFLOP/s", "frac": round(flops / kernel_ms * 1e-9 / peak, 4), "traffic": None,
-                     "kernel": "dgemm_dmma_kernel<true,false>", "flops_per_launch": flops,
+                     "unit": "TFLOP/s", "frac": round(flops / kernel_ms * 1e-9 / peak, 4), "traffic": ncu_traffic(),
+                     "traffic_unit": "bytes per launch (dram read + write, profiles/r01_dgemm_nn_8192_ncu.txt); "
+                                     "algorithmic bytes 1 610 612 736",
+                     "kernel": "dgemm_dmma_kernel<true,false,Tile128x128>", "flops_per_launch": flops,
                      "peak_source": peak_src + "; MEASURED_PEAKS.json carries no FP64 figure "
                                     f"(its bf16 {mp.get('bf16_tflops')} TFLOP/s is a different pipe); nominal FP64 37-40"},
         "cpu_baseline": cpu,

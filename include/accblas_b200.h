@@ -239,7 +239,7 @@ typedef enum {
     ACCBLAS_TUNE_SMMA_TILE = 3, /* mma.sync path CTA tile: 0 = 128x64 (c32: 64x64), 1 = 64x64, 2 = 32x32 */
     ACCBLAS_TUNE_HOST_PIPELINE = 4, /* accblas_gemm_host: 1 = wavefront even for small transfers, 0 = never */
     ACCBLAS_TUNE_RASTER_GROUP = 5,  /* f64 gemm: tile rows per rasterisation group (default 16)              */
-    ACCBLAS_TUNE_RESERVED6 = 6,
+    ACCBLAS_TUNE_HOST_PANELS = 6,   /* accblas_gemm_host: maximum panels per dimension of the wavefront     */
     ACCBLAS_TUNE_RESERVED7 = 7,
     ACCBLAS_TUNE_COUNT = 8
 } accblas_tune_t;
