@@ -278,6 +278,7 @@ int gemv_typed(cudaStream_t st, int opA, int64_t rowsA, int64_t colsA, const voi
         if (!occ_a) { occ_a = occupancy(gemv_n_kernel<T, true>, 512); occ_u = occupancy(gemv_n_kernel<T, false>, 512); }
         int64_t grid = (int64_t)sm_count() * (al ? occ_a : occ_u) * (512 / threads);
         if (grid > units) grid = units;
+        else grid = (units + (units + grid - 1) / grid - 1) / ((units + grid - 1) / grid);   // same rounds, even load
         if (al) gemv_n_kernel<T, true><<<(unsigned)grid, threads, 0, st>>>(rowsA, colsA, alpha, A, x, y);
         else    gemv_n_kernel<T, false><<<(unsigned)grid, threads, 0, st>>>(rowsA, colsA, alpha, A, x, y);
         return check_launch("gemv_n_kernel");

@@ -352,24 +352,28 @@ iamax_partial_kernel(int64_t n, const T *__restrict__ x, typename Scalar<T>::rea
     __shared__ int64_t si[L1_THREADS / 32];
     Best<R> b[L1_UNROLL];
 #pragma unroll
-    for (int u = 0; u < L1_UNROLL; ++u) { b[u].v = (R)0; b[u].i = -1; }
+    // Within a slot the indices arrive in increasing order, so "equal magnitude: later index wins" is just
+    // >= (<= for amin) against the running best: one compare per element, the 64-bit index is only written on
+    // an update.  Magnitudes are >= 0, so -1 / +inf make the first element of a slot win; a slot that saw
+    // nothing (or only NaNs, which never compare true) keeps index -1 and loses every combine below.
+    for (int u = 0; u < L1_UNROLL; ++u) { b[u].v = MAX ? (R)-1 : (R)INFINITY; b[u].i = -1; }
     for_each1<T, ALIGNED>(n, x, [&](int u, int64_t i, T a) {
         const R v = mag(a);
-        if (better<MAX>(v, i, b[u].v, b[u].i)) { b[u].v = v; b[u].i = i; }
+        if (MAX ? v >= b[u].v : v <= b[u].v) { b[u].v = v; b[u].i = i; }
     });
 #pragma unroll
     for (int u = 1; u < L1_UNROLL; ++u)
         if (better<MAX>(b[u].v, b[u].i, b[0].v, b[0].i)) b[0] = b[u];
     Best<R> r = block_best<MAX>(b[0], sv, si);
     if (threadIdx.x == 0) {
-        if (gridDim.x == 1) *out = r.i;
+        if (gridDim.x == 1) *out = r.i < 0 ? n - 1 : r.i;   // all NaN: the reference's fold ends on the last index
         else { pv[blockIdx.x] = r.v; pi[blockIdx.x] = r.i; }
     }
 }
 
 template <typename R, bool MAX>
 __global__ void __launch_bounds__(L1_THREADS)
-iamax_final_kernel(int nparts, const R *__restrict__ pv, const int64_t *__restrict__ pi, int64_t *__restrict__ out)
+iamax_final_kernel(int nparts, int64_t n, const R *__restrict__ pv, const int64_t *__restrict__ pi, int64_t *__restrict__ out)
 {
     __shared__ R sv[L1_THREADS / 32];
     __shared__ int64_t si[L1_THREADS / 32];
@@ -377,7 +381,7 @@ iamax_final_kernel(int nparts, const R *__restrict__ pv, const int64_t *__restri
     for (int i = threadIdx.x; i < nparts; i += L1_THREADS)
         if (better<MAX>(pv[i], pi[i], b.v, b.i)) { b.v = pv[i]; b.i = pi[i]; }
     b = block_best<MAX>(b, sv, si);
-    if (threadIdx.x == 0) *out = b.i;
+    if (threadIdx.x == 0) *out = b.i < 0 ? n - 1 : b.i;
 }
 
 template <typename T, bool MAX>
@@ -398,7 +402,7 @@ int iamax_typed(cudaStream_t st, int64_t n, const T *x, int64_t *out)
     int s = check_launch("iamax_partial_kernel");
     if (grid > 1) {
         if (s == ACCBLAS_OK) {
-            iamax_final_kernel<R, MAX><<<1, L1_THREADS, 0, st>>>(grid, pv, pi, out);
+            iamax_final_kernel<R, MAX><<<1, L1_THREADS, 0, st>>>(grid, n, pv, pi, out);
             s = check_launch("iamax_final_kernel");
         }
         cudaError_t e = cudaFreeAsync(ws, st);
