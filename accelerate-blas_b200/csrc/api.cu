@@ -93,7 +93,7 @@ int derive_gemm(GemmArgs &g)
     return ACCBLAS_OK;
 }
 
-enum Family { FAM_NONE, FAM_GENERIC, FAM_DMMA, FAM_TC, FAM_RANK1, FAM_MMA };
+enum Family { FAM_NONE, FAM_GENERIC, FAM_DMMA, FAM_TC, FAM_RANK1, FAM_MMA, FAM_Z3M };
 
 // f32 / c32: the tcgen05 path (pack pass + 128 x 256 tiles) wins once the product fills the GPU with
 // such tiles; below that the one-launch mma.sync path does (profiles/r01_sgemm_families.jsonl)
@@ -104,7 +104,8 @@ Family pick_family(const GemmArgs &g)
     if (g.m == 0 || g.n == 0) return FAM_NONE;
     if (g_gemm_path == 1) return FAM_GENERIC;
     if (g.k == 1 && g_gemm_path == 0) return FAM_RANK1;          // `><`: a store stream, not a contraction
-    if ((g.dtype == ACCBLAS_F64 || g.dtype == ACCBLAS_C64) && dgemm_dmma_eligible(g)) return FAM_DMMA;
+    if ((g.dtype == ACCBLAS_F64 || g.dtype == ACCBLAS_C64) && dgemm_dmma_eligible(g))
+        return g.dtype == ACCBLAS_C64 && zgemm_3m_wanted(g) ? FAM_Z3M : FAM_DMMA;
     if (g.dtype == ACCBLAS_F32 || g.dtype == ACCBLAS_C32) {
         const bool tc = sgemm_tc_eligible(g), mma = sgemm_mma_eligible(g);
         const int want = g_tuning[ACCBLAS_TUNE_SGEMM_FAMILY];
@@ -152,6 +153,7 @@ int run_family(Family f, const GemmArgs &g)
     case FAM_TC:   return sgemm_tc(g);
     case FAM_RANK1: return gemm_rank1(g);
     case FAM_MMA:  return sgemm_mma(g);
+    case FAM_Z3M:  return zgemm_3m(g);
     default:       return gemm_generic(g);
     }
 }
@@ -289,6 +291,7 @@ const char *accblas_gemm_kernel_name(int dtype, int opA, int opB, int64_t rowsA,
     case FAM_TC:   return g.dtype == ACCBLAS_F32 ? "sgemm_tf32x3_tcgen05" : "cgemm_tf32x3_tcgen05";
     case FAM_RANK1: return "gemm_rank1_outer";
     case FAM_MMA:  return g.dtype == ACCBLAS_F32 ? "sgemm_tf32x3_mma" : "cgemm_tf32x3_mma";
+    case FAM_Z3M:  return "zgemm_3m_dmma";
     default:       return "gemm_simt_generic";
     }
 }
@@ -300,7 +303,8 @@ size_t accblas_gemm_workspace_bytes(int dtype, int opA, int opB, int64_t rowsA, 
     g.dtype = dtype; g.opA = opA; g.opB = opB;
     g.rowsA = rowsA; g.colsA = colsA; g.rowsB = rowsB; g.colsB = colsB;
     if (derive_gemm(g) != ACCBLAS_OK) return 0;
-    return pick_family(g) == FAM_TC ? sgemm_tc_workspace(g) : 0;
+    const Family f = pick_family(g);
+    return f == FAM_TC ? sgemm_tc_workspace(g) : f == FAM_Z3M ? zgemm_3m_workspace(g) : 0;
 }
 
 static int gemv_entry(accblas_stream_t stream, int dtype, int opA, int64_t rowsA, int64_t colsA,

@@ -152,6 +152,10 @@ int gemm_generic(const GemmArgs &g);                  // gemm_generic.cu : any s
 int gemm_rank1(const GemmArgs &g);                    // gemm_generic.cu : k == 1 (outer product `><`)
 bool dgemm_dmma_eligible(const GemmArgs &g);          // gemm_dmma.cu    : f64 / c64 on DMMA
 int  dgemm_dmma(const GemmArgs &g);
+bool zgemm_3m_eligible(const GemmArgs &g);            // gemm_3m.cu      : c64 as three real DMMA products
+bool zgemm_3m_wanted(const GemmArgs &g);              //                   (knob + cost model)
+int  zgemm_3m(const GemmArgs &g);
+size_t zgemm_3m_workspace(const GemmArgs &g);
 bool sgemm_tc_eligible(const GemmArgs &g);            // gemm_tf32x3.cu  : f32 / c32 on tcgen05
 int  sgemm_tc(const GemmArgs &g);
 size_t sgemm_tc_workspace(const GemmArgs &g);

@@ -240,7 +240,7 @@ typedef enum {
     ACCBLAS_TUNE_HOST_PIPELINE = 4, /* accblas_gemm_host: 1 = wavefront even for small transfers, 0 = never */
     ACCBLAS_TUNE_RASTER_GROUP = 5,  /* f64 gemm: tile rows per rasterisation group (default 16)              */
     ACCBLAS_TUNE_HOST_PANELS = 6,   /* accblas_gemm_host: maximum panels per dimension of the wavefront     */
-    ACCBLAS_TUNE_RESERVED7 = 7,
+    ACCBLAS_TUNE_ZGEMM_3M = 7,      /* c64 gemm: 0 = always 4M in registers, 1 = 3M (three real products) whenever possible */
     ACCBLAS_TUNE_COUNT = 8
 } accblas_tune_t;
 void accblas_set_tuning(int knob, int value);

@@ -473,6 +473,40 @@ def test_alpha_on_device(dt, cuda):
             assert torch.equal(ab.gemv(al, oa, dA, dx), ab.gemv(dal, oa, dA, dx)), (O.NAMES[dt], m, n, oa)
 
 
+@pytest.mark.parametrize("force", [1, -1], ids=["forced", "auto"])
+def test_zgemm_3m(force, cuda):
+    """Complex-double gemm as three real DMMA products (csrc/gemm_3m.cu): every op pair, ragged and odd
+    extents (plane pitch padding), alpha on the host and on the device, against the wide oracle under the
+    stated complex tolerance; and the 4M kernel pinned by the knob gives the same product within it."""
+    import torch
+    import accblas_b200 as ab
+    rng = np.random.default_rng(9100 + force)
+    shapes = [(200, 136, 72), (129, 65, 33), (301, 259, 131)] if force == 1 else [(2048, 2048, 2048)]
+    try:
+        ab.set_tuning(ab.TUNE_ZGEMM_3M, force)
+        for (m, n, k) in shapes:
+            for oa in OPN:
+                for ob in (OPN if force == 1 else "NH"):
+                    al, A, B = gemm_inputs(rng, O.C64, oa, ob, m, n, k)
+                    assert ab.kernel_name(O.C64, oa, ob, A.shape, B.shape) == "zgemm_3m_dmma"
+                    dA, dB = dev(A, cuda), dev(B, cuda)
+                    C = host(ab.gemm(al, oa, dA, ob, dB))
+                    rows = np.arange(m) if m <= 512 else rng.choice(m, size=8, replace=False)
+                    Asub = A[rows] if oa == "N" else np.ascontiguousarray(A[:, rows])
+                    ref = O.gemm(al, oa, Asub, ob, B, wide=True)
+                    err = O.gemm_error_units(C[rows], ref, Asub, B, k, al)
+                    assert err <= TOL_UNITS[O.C64], (oa, ob, m, n, k, err)
+                    dal = dev(np.array([al], dtype=A.dtype), cuda)
+                    assert torch.equal(ab.gemm(dal, oa, dA, ob, dB), torch.from_numpy(C).to(cuda))
+                    ab.set_tuning(ab.TUNE_ZGEMM_3M, 0)
+                    assert ab.kernel_name(O.C64, oa, ob, A.shape, B.shape) == "zgemm_dmma_tma"
+                    C4 = host(ab.gemm(al, oa, dA, ob, dB))
+                    ab.set_tuning(ab.TUNE_ZGEMM_3M, force)
+                    assert O.gemm_error_units(C, C4, A, B, k, al) <= 2 * TOL_UNITS[O.C64]
+    finally:
+        ab.set_tuning(ab.TUNE_ZGEMM_3M, -1)
+
+
 def test_launches_are_counted(cuda):
     import torch
     import accblas_b200 as ab
