@@ -12,7 +12,7 @@ namespace accblas {
 thread_local uint64_t g_launches = 0;
 thread_local char g_cuda_err[256] = {0};
 thread_local int g_gemm_path = 0;
-thread_local int g_tuning[ACCBLAS_TUNE_COUNT] = {-1, -1, -1, -1, -1, -1, -1, -1};
+thread_local int g_tuning[ACCBLAS_TUNE_COUNT] = {-1, -1, -1, -1, -1, -1, -1, -1, -1, -1, -1, -1};
 
 int cuda_fail(cudaError_t e, const char *where)
 {
@@ -97,7 +97,7 @@ enum Family { FAM_NONE, FAM_GENERIC, FAM_DMMA, FAM_TC, FAM_RANK1, FAM_MMA, FAM_Z
 
 // f32 / c32: the tcgen05 path (pack pass + 128 x 256 tiles) wins once the product fills the GPU with
 // such tiles; below that the one-launch mma.sync path does (profiles/r01_sgemm_families.jsonl)
-constexpr double kTcMinWork = 1.5e9;     // real-equivalent m * n * k (between 1024^3 and 1536^3)
+constexpr double kTcMinWork = 7.0e8;     // real-equivalent m * n * k (between 768^3 and 1000^3 since the 128 x 64 tile)
 
 Family pick_family(const GemmArgs &g)
 {
@@ -158,6 +158,21 @@ int run_family(Family f, const GemmArgs &g)
     }
 }
 
+struct RepitchArgs {
+    const char *src; char *dst;
+    int64_t rows, words, src_pitch, dst_pitch;      // extents and pitches in copy words (rows == 0: nothing to do)
+};
+template <typename W>
+__global__ void __launch_bounds__(256) repitch_kernel(const RepitchArgs a, const RepitchArgs b)
+{
+    const RepitchArgs &r = blockIdx.z == 0 ? a : b;
+    const int64_t c = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    if (c >= r.words) return;
+    const W *src = reinterpret_cast<const W *>(r.src);
+    W *dst = reinterpret_cast<W *>(r.dst);
+    for (int64_t row = blockIdx.y; row < r.rows; row += gridDim.y) dst[row * r.dst_pitch + c] = src[row * r.src_pitch + c];
+}
+
 // The TMA-fed families need 16-byte aligned bases and row pitches.  Dense Accelerate arrays with an
 // odd column count (the reference benchmarks 250 x 250 Floats: 1000-byte rows) miss that by a few
 // bytes, which used to send them to the SIMT kernel at half cuBLAS's speed.  Instead: copy the
@@ -182,21 +197,27 @@ int gemm_repitched(const GemmArgs &g)
     const size_t bytesB = fixB ? es * (size_t)ldb * (size_t)g.rowsB : 0;
     char *ws = nullptr;
     ACC_CUDA(cudaMallocAsync(reinterpret_cast<void **>(&ws), bytesA + bytesB, g.stream));
-    int st = ACCBLAS_OK;
-    cudaError_t e = cudaSuccess;
+    // one launch copies both operands (blockIdx.z): at the sizes where this path matters (250^3 Floats take
+    // ~15 us in all) a second copy launch is a visible fraction of the call
+    const size_t w = es < 8 ? es : 8;                                  // copy word: 4 bytes (f32) or 8
+    RepitchArgs ra{}, rb{};
     if (fixA) {
-        e = cudaMemcpy2DAsync(ws, es * (size_t)lda, g.A, es * (size_t)g.lda, es * (size_t)g.colsA, (size_t)g.rowsA,
-                              cudaMemcpyDeviceToDevice, g.stream);
+        ra = RepitchArgs{static_cast<const char *>(g.A), ws, g.rowsA, (int64_t)(es * (size_t)g.colsA / w),
+                         (int64_t)(es * (size_t)g.lda / w), (int64_t)(es * (size_t)lda / w)};
         h.A = ws;
     }
-    if (fixB && e == cudaSuccess) {
-        e = cudaMemcpy2DAsync(ws + bytesA, es * (size_t)ldb, g.B, es * (size_t)g.ldb, es * (size_t)g.colsB, (size_t)g.rowsB,
-                              cudaMemcpyDeviceToDevice, g.stream);
+    if (fixB) {
+        rb = RepitchArgs{static_cast<const char *>(g.B), ws + bytesA, g.rowsB, (int64_t)(es * (size_t)g.colsB / w),
+                         (int64_t)(es * (size_t)g.ldb / w), (int64_t)(es * (size_t)ldb / w)};
         h.B = ws + bytesA;
     }
-    if (e == cudaSuccess) st = run_family(pick_family(h), h);
+    const int64_t words = std::max(ra.words, rb.words), rows = std::max(ra.rows, rb.rows);
+    dim3 grid((unsigned)((words + 255) / 256), (unsigned)std::min<int64_t>(rows, 32768), 2);
+    if (w == 4) repitch_kernel<uint32_t><<<grid, 256, 0, g.stream>>>(ra, rb);
+    else        repitch_kernel<uint64_t><<<grid, 256, 0, g.stream>>>(ra, rb);
+    int st = check_launch("repitch_kernel");
+    if (st == ACCBLAS_OK) st = run_family(pick_family(h), h);
     cudaError_t e2 = cudaFreeAsync(ws, g.stream);
-    if (e != cudaSuccess) return cuda_fail(e, "cudaMemcpy2DAsync (re-pitch)");
     if (st == ACCBLAS_OK && e2 != cudaSuccess) return cuda_fail(e2, "cudaFreeAsync");
     return st;
 }

@@ -25,6 +25,7 @@
 #include "common.cuh"
 #include "tma.cuh"
 #include <cstdlib>
+#include <algorithm>
 
 namespace accblas {
 namespace {
@@ -79,12 +80,13 @@ __device__ __forceinline__ float pack_value(const PackArgs &a, int64_t r, int64_
 
 // 32 x 32 output tile per 256-thread block.  When the source is contiguous along the output's
 // row index (transposed), the tile goes through shared memory so both sides stay coalesced.
+// Both operands are packed by ONE launch (blockIdx.z = 0: A, 1: B): the mid-size products this family
+// now serves (1000^3 takes ~40 us in all) are sensitive to every extra launch.
 template <int MODE>
-__global__ void __launch_bounds__(256)
-pack_split_kernel(const PackArgs a)
+__device__ __forceinline__ void pack_split_tile(const PackArgs &a, float (&tile)[32][33])
 {
-    __shared__ float tile[32][33];
     const int64_t r0 = (int64_t)blockIdx.y * 32, c0 = (int64_t)blockIdx.x * 32;
+    if (r0 >= a.R || c0 >= a.pitch) return;                      // uniform per block (grid covers the larger operand)
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;    // 32 x 8
     if (a.transposed) {
 #pragma unroll
@@ -109,15 +111,21 @@ pack_split_kernel(const PackArgs a)
     }
 }
 
-int launch_pack(int mode, const PackArgs &a, cudaStream_t st)
+template <int MODE_A, int MODE_B>
+__global__ void __launch_bounds__(256)
+pack_split_kernel(const PackArgs a, const PackArgs b)
 {
-    dim3 grid((unsigned)((a.pitch + 31) / 32), (unsigned)((a.R + 31) / 32));
+    __shared__ float tile[32][33];
+    if (blockIdx.z == 0) pack_split_tile<MODE_A>(a, tile);
+    else pack_split_tile<MODE_B>(b, tile);
+}
+
+int launch_pack(bool cplx, const PackArgs &a, const PackArgs &b, cudaStream_t st)
+{
+    dim3 grid((unsigned)((std::max(a.pitch, b.pitch) + 31) / 32), (unsigned)((std::max(a.R, b.R) + 31) / 32), 2);
     if (grid.y > 65535u) return ACCBLAS_ERR_SHAPE;     // eligibility keeps R below 2^21
-    switch (mode) {
-    case PK_REAL:   pack_split_kernel<PK_REAL><<<grid, 256, 0, st>>>(a); break;
-    case PK_CPLX_A: pack_split_kernel<PK_CPLX_A><<<grid, 256, 0, st>>>(a); break;
-    default:        pack_split_kernel<PK_CPLX_B><<<grid, 256, 0, st>>>(a); break;
-    }
+    if (cplx) pack_split_kernel<PK_CPLX_A, PK_CPLX_B><<<grid, 256, 0, st>>>(a, b);
+    else      pack_split_kernel<PK_REAL, PK_REAL><<<grid, 256, 0, st>>>(a, b);
     return check_launch("pack_split_kernel");
 }
 
@@ -324,17 +332,25 @@ sgemm_tf32x3_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_con
             tma::mbar_wait(bar_accf + 8 * b, (c >> 1) & 1);
             tc_fence_after();
             const uint32_t t0 = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(b * TBN + h * HALF);
+            if constexpr (HALF >= 64) {
 #pragma unroll
-            for (int c0 = 0; c0 < HALF; c0 += 64) {
-                uint32_t v0[32], v1[32];
-                tmem_ld32(t0 + c0, v0);
-                tmem_ld32(t0 + c0 + 32, v1);
+                for (int c0 = 0; c0 < HALF; c0 += 64) {
+                    uint32_t v0[32], v1[32];
+                    tmem_ld32(t0 + c0, v0);
+                    tmem_ld32(t0 + c0 + 32, v1);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) {
+                        acc[c0 + i] += __uint_as_float(v0[i]);
+                        acc[c0 + 32 + i] += __uint_as_float(v1[i]);
+                    }
+                }
+            } else {                                               // 128 x 64 tile: 32 columns per warp
+                uint32_t v0[32];
+                tmem_ld32(t0, v0);
                 tmem_ld_wait();
 #pragma unroll
-                for (int i = 0; i < 32; ++i) {
-                    acc[c0 + i] += __uint_as_float(v0[i]);
-                    acc[c0 + 32 + i] += __uint_as_float(v1[i]);
-                }
+                for (int i = 0; i < 32; ++i) acc[i] += __uint_as_float(v0[i]);
             }
             tc_fence_before();
             __syncwarp();
@@ -400,6 +416,32 @@ TcPlan make_plan(const GemmArgs &g)
     t.plane_a = ((size_t)t.RA * (size_t)t.pitch * 4 + 1023) / 1024 * 1024;
     t.plane_b = ((size_t)t.RB * (size_t)t.pitch * 4 + 1023) / 1024 * 1024;
     return t;
+}
+
+// CTA tile choice (always 128 rows: UMMA M = 128 fills the 128 TMEM lanes).  A launch lasts
+// ceil(tiles / SMs) waves of one tile per SM; the cost of a K = 8 step of a 128 x TBN tile is measured
+// (8192^3 forced onto each tile, profiles/r01_tc_tiles.jsonl): 1 : 0.65 : 0.51 for TBN = 256 / 128 / 64 --
+// the narrower the tile, the more its shared-memory operand reads ((128 + TBN) * 32 bytes per step)
+// outweigh its tensor time (128 * TBN * 8 multiply-adds).
+// The narrow tiles fill the GPU for the mid-size products (1024^3 is 32 tiles of 128 x 256 on 148 SMs)
+// and trim the partial last wave of the large ones.
+int pick_tc_tile(const TcPlan &t)
+{
+    const int forced = g_tuning[ACCBLAS_TUNE_TC_TILE];
+    if (forced >= 0 && forced <= 2) return forced;
+    static const int tbn[3] = {256, 128, 64};
+    static const double step_cost[3] = {134.0, 87.0, 68.0};
+    const int sms = sm_count();
+    const int64_t tm = (t.M + TBM - 1) / TBM;
+    int best = 0;
+    double best_cost = 0.0;
+    for (int c = 0; c < 3; ++c) {
+        const int64_t tiles = tm * ((t.N + tbn[c] - 1) / tbn[c]);
+        // per tile: the K loop plus a prologue / epilogue worth ~40 K-steps of the widest tile
+        const double cost = (double)((tiles + sms - 1) / sms) * (step_cost[c] * (double)(t.pitch / 8) + 40.0 * 134.0);
+        if (c == 0 || cost < best_cost * 0.97) { best = c; best_cost = cost; }
+    }
+    return best;
 }
 
 template <int TBN, int STAGES, int KCB>
@@ -475,11 +517,13 @@ int sgemm_tc(const GemmArgs &g)
     pb.conj_sign = (cx && g.opB == ACCBLAS_OP_H) ? -1.f : 1.f;
     pb.R = t.RB; pb.Kp = t.Kp; pb.pitch = t.pitch; pb.hi = bhi; pb.lo = blo;
 
-    int s = launch_pack(cx ? PK_CPLX_A : PK_REAL, pa, g.stream);
-    if (s == ACCBLAS_OK) s = launch_pack(cx ? PK_CPLX_B : PK_REAL, pb, g.stream);
+    int s = launch_pack(cx, pa, pb, g.stream);
     if (s == ACCBLAS_OK) {
         static const int kcb = [] { const char *e = getenv("ACCBLAS_TC_KCB"); return e ? atoi(e) : 2; }();
-        s = kcb == 1 ? launch_tc<256, 2, 1>(g, t, ahi, alo, bhi, blo)
+        const int tile = pick_tc_tile(t);
+        s = tile == 1 ? launch_tc<128, 3, 2>(g, t, ahi, alo, bhi, blo)
+          : tile == 2 ? launch_tc<64, 4, 2>(g, t, ahi, alo, bhi, blo)
+          : kcb == 1 ? launch_tc<256, 2, 1>(g, t, ahi, alo, bhi, blo)
           : kcb == 4 ? launch_tc<256, 2, 4>(g, t, ahi, alo, bhi, blo)
           : kcb >= 1000 ? launch_tc<256, 2, 1 << 30>(g, t, ahi, alo, bhi, blo)
                      : launch_tc<256, 2, 2>(g, t, ahi, alo, bhi, blo);

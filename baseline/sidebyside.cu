@@ -223,7 +223,7 @@ static void tile_sweep() {
 static void family_sweep() {
     for (int dt : {0, 2}) {
         for (long n : {100L, 160L, 250L, 384L, 500L, 768L, 1000L, 1024L, 1536L, 2048L, 3072L, 4096L}) {
-            if (dt == 2 && n > 2048) continue;
+            if (dt == 2 && n > 3072) continue;
             void *A = dev_random(dt, (size_t)n * n, 1), *B = dev_random(dt, (size_t)n * n, 2), *C = dev_random(dt, (size_t)n * n, 3);
             float one[2] = {1.f, 0.f};
             auto ours = [&]() { CK(accblas_gemm(nullptr, dt, 0, 0, n, n, n, n, one, A, B, C)); };
@@ -240,7 +240,11 @@ static void family_sweep() {
             accblas_set_tuning(ACCBLAS_TUNE_SMMA_TILE, -1);
             accblas_set_tuning(ACCBLAS_TUNE_SGEMM_FAMILY, 2);
             if (strstr(accblas_gemm_kernel_name(dt, 0, 0, n, n, n, n), "tcgen05"))
-                printf(",\"tcgen05_us\":%.1f", time_ms(ours, 3, it, &best) * 1e3);
+                for (int tile = 0; tile < 3; ++tile) {               // 128 x 256 / 128 x 128 / 128 x 64
+                    accblas_set_tuning(ACCBLAS_TUNE_TC_TILE, tile);
+                    printf(",\"tcgen05_tile%d_us\":%.1f", tile, time_ms(ours, 3, it, &best) * 1e3);
+                }
+            accblas_set_tuning(ACCBLAS_TUNE_TC_TILE, -1);
             accblas_set_tuning(ACCBLAS_TUNE_SGEMM_FAMILY, -1);
             auto theirs = [&]() {
                 if (dt == 0) { float al = 1, be = 0; CK(cublasSgemm(H, CUBLAS_OP_N, CUBLAS_OP_N, n, n, n, &al, (float *)B, n, (float *)A, n, &be, (float *)C, n)); }

@@ -241,7 +241,8 @@ typedef enum {
     ACCBLAS_TUNE_RASTER_GROUP = 5,  /* f64 gemm: tile rows per rasterisation group (default 16)              */
     ACCBLAS_TUNE_HOST_PANELS = 6,   /* accblas_gemm_host: maximum panels per dimension of the wavefront     */
     ACCBLAS_TUNE_ZGEMM_3M = 7,      /* c64 gemm: 0 = always 4M in registers, 1 = 3M (three real products) whenever possible */
-    ACCBLAS_TUNE_COUNT = 8
+    ACCBLAS_TUNE_TC_TILE = 8,       /* tcgen05 f32/c32 gemm CTA tile: 0 = 128x256, 1 = 128x128, 2 = 128x64                  */
+    ACCBLAS_TUNE_COUNT = 12
 } accblas_tune_t;
 void accblas_set_tuning(int knob, int value);
 

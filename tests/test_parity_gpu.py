@@ -175,6 +175,29 @@ def test_gemm_mma_tf32_family(dt, cuda):
         ab.set_tuning(3, -1)
 
 
+@pytest.mark.parametrize("dt", [O.F32, O.C32], ids=ids)
+def test_gemm_every_tc_tile(dt, cuda):
+    """The tcgen05 3xTF32 family forced onto each CTA tile (128 x 256 / 128 x 128 / 128 x 64), every op pair,
+    ragged extents in m, n and k (tile edges, odd pitches), a k long enough for many promotion chunks."""
+    import accblas_b200 as ab
+    rng = np.random.default_rng(2900 + dt)
+    try:
+        ab.set_tuning(2, 2)                       # ACCBLAS_TUNE_SGEMM_FAMILY = tcgen05
+        for tile in range(3):
+            ab.set_tuning(8, tile)                # ACCBLAS_TUNE_TC_TILE
+            for oa in OPN:
+                for ob in OPN:
+                    for (m, n, k) in [(300, 260, 330), (129, 193, 1500)]:
+                        al, A, B = gemm_inputs(rng, dt, oa, ob, m, n, k)
+                        assert "tcgen05" in ab.kernel_name(dt, oa, ob, A.shape, B.shape)
+                        C = host(ab.gemm(al, oa, dev(A, cuda), ob, dev(B, cuda)))
+                        err = O.gemm_error_units(C, O.gemm(al, oa, A, ob, B, wide=True), A, B, k, al)
+                        assert err <= TOL_UNITS_TF32X3, (O.NAMES[dt], tile, oa, ob, m, n, k, err)
+    finally:
+        ab.set_tuning(2, -1)
+        ab.set_tuning(8, -1)
+
+
 @pytest.mark.parametrize("dt", DTYPES, ids=ids)
 def test_gemm_many_small_tiles_short_k(dt, cuda):
     """Hundreds of co-resident 32 x 32 CTAs whose smem ring wraps after a few K-blocks: the regime in
