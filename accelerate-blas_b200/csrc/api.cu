@@ -93,7 +93,7 @@ int derive_gemm(GemmArgs &g)
     return ACCBLAS_OK;
 }
 
-enum Family { FAM_NONE, FAM_GENERIC, FAM_DMMA, FAM_TC, FAM_RANK1, FAM_MMA, FAM_Z3M };
+enum Family { FAM_NONE, FAM_GENERIC, FAM_DMMA, FAM_TC, FAM_RANK1, FAM_MMA, FAM_Z3M, FAM_C3M };
 
 // f32 / c32: the tcgen05 path (pack pass + 128 x 256 tiles) wins once the product fills the GPU with
 // such tiles; below that the one-launch mma.sync path does (profiles/r01_sgemm_families.jsonl)
@@ -110,9 +110,9 @@ Family pick_family(const GemmArgs &g)
         const bool tc = sgemm_tc_eligible(g), mma = sgemm_mma_eligible(g);
         const int want = g_tuning[ACCBLAS_TUNE_SGEMM_FAMILY];
         if (want == 1 && mma) return FAM_MMA;
-        if (want == 2 && tc) return FAM_TC;
+        if (want == 2 && tc) return cgemm_3m_wanted(g) ? FAM_C3M : FAM_TC;
         const double work = (g.dtype == ACCBLAS_C32 ? 4.0 : 1.0) * (double)g.m * (double)g.n * (double)g.k;
-        if (tc && (work >= kTcMinWork || !mma)) return FAM_TC;
+        if (tc && (work >= kTcMinWork || !mma)) return cgemm_3m_wanted(g) ? FAM_C3M : FAM_TC;
         if (mma) return FAM_MMA;
     }
     return FAM_GENERIC;
@@ -154,6 +154,7 @@ int run_family(Family f, const GemmArgs &g)
     case FAM_RANK1: return gemm_rank1(g);
     case FAM_MMA:  return sgemm_mma(g);
     case FAM_Z3M:  return zgemm_3m(g);
+    case FAM_C3M:  return cgemm_3m(g);
     default:       return gemm_generic(g);
     }
 }
@@ -313,6 +314,7 @@ const char *accblas_gemm_kernel_name(int dtype, int opA, int opB, int64_t rowsA,
     case FAM_RANK1: return "gemm_rank1_outer";
     case FAM_MMA:  return g.dtype == ACCBLAS_F32 ? "sgemm_tf32x3_mma" : "cgemm_tf32x3_mma";
     case FAM_Z3M:  return "zgemm_3m_dmma";
+    case FAM_C3M:  return "cgemm_3m_tf32x3_tcgen05";
     default:       return "gemm_simt_generic";
     }
 }
@@ -325,7 +327,7 @@ size_t accblas_gemm_workspace_bytes(int dtype, int opA, int opB, int64_t rowsA, 
     g.rowsA = rowsA; g.colsA = colsA; g.rowsB = rowsB; g.colsB = colsB;
     if (derive_gemm(g) != ACCBLAS_OK) return 0;
     const Family f = pick_family(g);
-    return f == FAM_TC ? sgemm_tc_workspace(g) : f == FAM_Z3M ? zgemm_3m_workspace(g) : 0;
+    return f == FAM_TC ? sgemm_tc_workspace(g) : f == FAM_Z3M ? zgemm_3m_workspace(g) : f == FAM_C3M ? cgemm_3m_workspace(g) : 0;
 }
 
 static int gemv_entry(accblas_stream_t stream, int dtype, int opA, int64_t rowsA, int64_t colsA,

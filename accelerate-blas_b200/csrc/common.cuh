@@ -159,6 +159,9 @@ size_t zgemm_3m_workspace(const GemmArgs &g);
 bool sgemm_tc_eligible(const GemmArgs &g);            // gemm_tf32x3.cu  : f32 / c32 on tcgen05
 int  sgemm_tc(const GemmArgs &g);
 size_t sgemm_tc_workspace(const GemmArgs &g);
+bool cgemm_3m_wanted(const GemmArgs &g);              //                   c32 as three real tcgen05 products
+int  cgemm_3m(const GemmArgs &g);
+size_t cgemm_3m_workspace(const GemmArgs &g);
 bool sgemm_mma_eligible(const GemmArgs &g);           // gemm_mma_tf32.cu : f32 / c32 on mma.sync, small / medium
 int  sgemm_mma(const GemmArgs &g);
 

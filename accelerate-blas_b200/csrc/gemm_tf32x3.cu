@@ -131,6 +131,99 @@ int launch_pack(bool cplx, const PackArgs &a, const PackArgs &b, cudaStream_t st
 
 
 // ------------------------------------------------------------------------------------
+// 3M for complex-float products: op(X) = Xr + i Xi is packed as THREE real K-major operands
+//   P0 = Xr,  P1 = s * Xi,  P2 = Xr + s * Xi      (s = -1 under H), each split into hi / lo planes,
+// so that C = alpha * ((P0a P0b - P1a P1b) + i (P2a P2b - P0a P0b - P1a P1b)) takes three real products
+// of extent m x n x k instead of the one m x 2n x 2k product of the real embedding (6 mnk against 8 mnk).
+// Same 32 x 32 tiling as pack_split; R / Kp / pitch count complex elements here.
+// ------------------------------------------------------------------------------------
+struct Pack3Args {
+    const float2 *src;     // stored complex matrix
+    int64_t ld;            // stored row pitch (complex elements)
+    int transposed;        // 1: op-index (r,l) lives at stored [l][r]
+    float conj_sign;
+    int64_t R, Kp, pitch;  // output extent and row pitch (floats), pitch multiple of 32
+    float *hi[3], *lo[3];
+};
+
+__device__ __forceinline__ void pack_split3_tile(const Pack3Args &a, float2 (&tile)[32][33])
+{
+    const int64_t r0 = (int64_t)blockIdx.y * 32, c0 = (int64_t)blockIdx.x * 32;
+    if (r0 >= a.R || c0 >= a.pitch) return;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    if (a.transposed) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int cc = ty + 8 * i;
+            const int64_t r = r0 + tx, c = c0 + cc;
+            tile[cc][tx] = (r < a.R && c < a.Kp) ? a.src[c * a.ld + r] : make_float2(0.f, 0.f);
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int rr = ty + 8 * i;
+        const int64_t r = r0 + rr, c = c0 + tx;
+        if (r >= a.R || c >= a.pitch) continue;
+        float2 z = make_float2(0.f, 0.f);
+        if (c < a.Kp) z = a.transposed ? tile[tx][rr] : a.src[r * a.ld + c];
+        const float im = z.y * a.conj_sign;
+        const float v[3] = {z.x, im, z.x + im};
+#pragma unroll
+        for (int p = 0; p < 3; ++p) {
+            const float h = to_tf32(v[p]);
+            a.hi[p][r * a.pitch + c] = h;
+            a.lo[p][r * a.pitch + c] = to_tf32(v[p] - h);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256) pack_split3_kernel(const Pack3Args a, const Pack3Args b)
+{
+    __shared__ float2 tile[32][33];
+    pack_split3_tile(blockIdx.z == 0 ? a : b, tile);
+}
+
+struct Combine3Args {
+    const float *t[3];     // m x n real products, row pitch ldt (multiple of 4 floats)
+    float2 *C;
+    int64_t m, n, ldt, ldc;
+    Alpha<float2> alpha;
+};
+
+// one thread = four consecutive columns: three 16-byte loads, two 16-byte stores (when C allows)
+__global__ void __launch_bounds__(256) combine3_kernel(const Combine3Args a)
+{
+    const float2 al = a.alpha.get();
+    const int64_t quads = a.ldt / 4, total = a.m * quads;
+    const bool vec = (a.ldc & 1) == 0 && (reinterpret_cast<uintptr_t>(a.C) & 15u) == 0;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = i / quads, c = (i - r * quads) * 4;
+        if (c >= a.n) continue;
+        const int64_t o = r * a.ldt + c;
+        const float4 t1 = *reinterpret_cast<const float4 *>(a.t[0] + o);
+        const float4 t2 = *reinterpret_cast<const float4 *>(a.t[1] + o);
+        const float4 t3 = *reinterpret_cast<const float4 *>(a.t[2] + o);
+        const float x1[4] = {t1.x, t1.y, t1.z, t1.w}, x2[4] = {t2.x, t2.y, t2.z, t2.w}, x3[4] = {t3.x, t3.y, t3.z, t3.w};
+        float2 out[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            const float xr = x1[e] - x2[e], xi = (x3[e] - x1[e]) - x2[e];
+            out[e] = make_float2(al.x * xr - al.y * xi, al.x * xi + al.y * xr);
+        }
+        float2 *dst = a.C + r * a.ldc + c;
+        if (vec && c + 4 <= a.n) {
+            *reinterpret_cast<float4 *>(dst) = make_float4(out[0].x, out[0].y, out[1].x, out[1].y);
+            *reinterpret_cast<float4 *>(dst + 2) = make_float4(out[2].x, out[2].y, out[3].x, out[3].y);
+        } else {
+#pragma unroll
+            for (int e = 0; e < 4; ++e)
+                if (c + e < a.n) dst[e] = out[e];
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------
 // tcgen05 helpers (inline PTX; SASS: UTCHMMA / LDTM / UTCBAR)
 // ------------------------------------------------------------------------------------
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
@@ -477,6 +570,82 @@ int launch_tc(const GemmArgs &g, const TcPlan &t, float *ahi, float *alo, float 
     return check_launch("sgemm_tf32x3_kernel");
 }
 
+// ---- 3M for c32 (see pack_split3_kernel) ----
+struct Tc3Plan {
+    TcPlan t;              // one real m x n x k product
+    int64_t ldt;           // row pitch of the T planes (floats)
+    size_t plane_t;
+};
+
+Tc3Plan make_plan3(const GemmArgs &g)
+{
+    Tc3Plan q;
+    q.t.RA = g.m; q.t.RB = g.n; q.t.Kp = g.k;
+    q.t.pitch = (g.k + 31) / 32 * 32;
+    q.t.M = g.m; q.t.N = g.n;
+    q.t.plane_a = ((size_t)g.m * (size_t)q.t.pitch * 4 + 1023) / 1024 * 1024;
+    q.t.plane_b = ((size_t)g.n * (size_t)q.t.pitch * 4 + 1023) / 1024 * 1024;
+    q.ldt = (g.n + 3) / 4 * 4;
+    q.plane_t = ((size_t)g.m * (size_t)q.ldt * 4 + 1023) / 1024 * 1024;
+    return q;
+}
+
+int cgemm_3m_run(const GemmArgs &g)
+{
+    const Tc3Plan q = make_plan3(g);
+    const size_t pa = q.t.plane_a, pb = q.t.plane_b, pt = q.plane_t;
+    char *ws = nullptr;
+    ACC_CUDA(cudaMallocAsync(reinterpret_cast<void **>(&ws), 6 * (pa + pb) + 3 * pt, g.stream));
+    char *wa = ws, *wb = ws + 6 * pa, *wt = wb + 6 * pb;
+    Pack3Args a{}, b{};
+    a.src = static_cast<const float2 *>(g.A); a.ld = g.lda;
+    a.transposed = g.opA != ACCBLAS_OP_N;
+    a.conj_sign = g.opA == ACCBLAS_OP_H ? -1.f : 1.f;
+    a.R = g.m; a.Kp = g.k; a.pitch = q.t.pitch;
+    b.src = static_cast<const float2 *>(g.B); b.ld = g.ldb;
+    b.transposed = g.opB == ACCBLAS_OP_N;                  // K-major row j of op(B)^T is a stored column when op = N
+    b.conj_sign = g.opB == ACCBLAS_OP_H ? -1.f : 1.f;
+    b.R = g.n; b.Kp = g.k; b.pitch = q.t.pitch;
+    for (int p = 0; p < 3; ++p) {
+        a.hi[p] = reinterpret_cast<float *>(wa + (2 * p) * pa); a.lo[p] = reinterpret_cast<float *>(wa + (2 * p + 1) * pa);
+        b.hi[p] = reinterpret_cast<float *>(wb + (2 * p) * pb); b.lo[p] = reinterpret_cast<float *>(wb + (2 * p + 1) * pb);
+    }
+    int s = ACCBLAS_OK;
+    {
+        dim3 grid((unsigned)((q.t.pitch + 31) / 32), (unsigned)((std::max(a.R, b.R) + 31) / 32), 2);
+        if (grid.y > 65535u) s = ACCBLAS_ERR_SHAPE;
+        else {
+            pack_split3_kernel<<<grid, 256, 0, g.stream>>>(a, b);
+            s = check_launch("pack_split3_kernel");
+        }
+    }
+    static const float one = 1.f;
+    const int tile = pick_tc_tile(q.t);
+    for (int p = 0; p < 3 && s == ACCBLAS_OK; ++p) {
+        GemmArgs h = g;
+        h.dtype = ACCBLAS_F32;
+        h.alpha = &one; h.alpha_dev = false;
+        h.C = wt + p * pt; h.ldc = q.ldt;
+        s = tile == 1 ? launch_tc<128, 3, 2>(h, q.t, a.hi[p], a.lo[p], b.hi[p], b.lo[p])
+          : tile == 2 ? launch_tc<64, 4, 2>(h, q.t, a.hi[p], a.lo[p], b.hi[p], b.lo[p])
+                      : launch_tc<256, 2, 2>(h, q.t, a.hi[p], a.lo[p], b.hi[p], b.lo[p]);
+    }
+    if (s == ACCBLAS_OK) {
+        Combine3Args c{};
+        for (int p = 0; p < 3; ++p) c.t[p] = reinterpret_cast<const float *>(wt + p * pt);
+        c.C = static_cast<float2 *>(g.C);
+        c.m = g.m; c.n = g.n; c.ldt = q.ldt; c.ldc = g.ldc;
+        c.alpha = make_alpha<float2>(g.alpha, g.alpha_dev);
+        const int64_t total = c.m * (c.ldt / 4);
+        const int64_t want = (total + 255) / 256, cap = (int64_t)sm_count() * 32;
+        combine3_kernel<<<(unsigned)std::max<int64_t>(1, std::min(want, cap)), 256, 0, g.stream>>>(c);
+        s = check_launch("combine3_kernel");
+    }
+    cudaError_t e = cudaFreeAsync(ws, g.stream);
+    if (s == ACCBLAS_OK && e != cudaSuccess) return cuda_fail(e, "cudaFreeAsync");
+    return s;
+}
+
 }  // namespace
 
 bool sgemm_tc_eligible(const GemmArgs &g)
@@ -532,5 +701,26 @@ int sgemm_tc(const GemmArgs &g)
     if (s == ACCBLAS_OK && e != cudaSuccess) return cuda_fail(e, "cudaFreeAsync");
     return s;
 }
+
+size_t cgemm_3m_workspace(const GemmArgs &g)
+{
+    const Tc3Plan q = make_plan3(g);
+    return 6 * (q.t.plane_a + q.t.plane_b) + 3 * q.plane_t;
+}
+
+// 3M pays once the tensor time saved (a quarter of the 4M product, at the ~250 TFLOP/s the kernel sustains)
+// outweighs the extra streaming pass (combine + the wider T planes) and three launches instead of one.
+bool cgemm_3m_wanted(const GemmArgs &g)
+{
+    const int knob = g_tuning[ACCBLAS_TUNE_CGEMM_3M];
+    if (knob == 0 || g.dtype != ACCBLAS_C32 || !sgemm_tc_eligible(g)) return false;
+    if (g.m < 128 || g.n < 64 || g.k < 32) return false;
+    if (knob == 1) return true;
+    const double save = 2.0 * (double)g.m * (double)g.n * (double)g.k / 250.0e12;
+    const double cost = 32.0 * (double)g.m * (double)g.n / 4.0e12 + 10.0e-6;
+    return save > cost;          // measured crossover ~1536^3 (profiles/r01_cgemm_3m.jsonl)
+}
+
+int cgemm_3m(const GemmArgs &g) { return cgemm_3m_run(g); }
 
 }  // namespace accblas

@@ -242,6 +242,7 @@ typedef enum {
     ACCBLAS_TUNE_HOST_PANELS = 6,   /* accblas_gemm_host: maximum panels per dimension of the wavefront     */
     ACCBLAS_TUNE_ZGEMM_3M = 7,      /* c64 gemm: 0 = always 4M in registers, 1 = 3M (three real products) whenever possible */
     ACCBLAS_TUNE_TC_TILE = 8,       /* tcgen05 f32/c32 gemm CTA tile: 0 = 128x256, 1 = 128x128, 2 = 128x64                  */
+    ACCBLAS_TUNE_CGEMM_3M = 9,      /* c32 gemm on tcgen05: 0 = always the 4M real embedding, 1 = 3M whenever possible     */
     ACCBLAS_TUNE_COUNT = 12
 } accblas_tune_t;
 void accblas_set_tuning(int knob, int value);

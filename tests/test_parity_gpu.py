@@ -530,6 +530,38 @@ def test_zgemm_3m(force, cuda):
         ab.set_tuning(ab.TUNE_ZGEMM_3M, -1)
 
 
+def test_cgemm_3m(cuda):
+    """Complex-float gemm as three real tcgen05 3xTF32 products (pack_split3 / 3 x sgemm_tf32x3 / combine3):
+    every op pair and CTA tile at ragged extents, alpha on host and device, against the wide oracle under the
+    stated tolerance of the 3xTF32 path; 4M (real embedding) pinned by the knob agrees within it."""
+    import torch
+    import accblas_b200 as ab
+    rng = np.random.default_rng(9300)
+    try:
+        ab.set_tuning(2, 2)                       # tcgen05 family
+        for tile, shapes in [(2, [(300, 260, 330), (129, 67, 1500)]), (1, [(257, 300, 200)]), (0, [(200, 520, 130)])]:
+            ab.set_tuning(8, tile)
+            for (m, n, k) in shapes:
+                for oa in OPN:
+                    for ob in OPN:
+                        al, A, B = gemm_inputs(rng, O.C32, oa, ob, m, n, k)
+                        dA, dB = dev(A, cuda), dev(B, cuda)
+                        ab.set_tuning(ab.TUNE_CGEMM_3M, 1)
+                        assert ab.kernel_name(O.C32, oa, ob, A.shape, B.shape) == "cgemm_3m_tf32x3_tcgen05"
+                        C = host(ab.gemm(al, oa, dA, ob, dB))
+                        dal = dev(np.array([al], dtype=A.dtype), cuda)
+                        assert torch.equal(ab.gemm(dal, oa, dA, ob, dB), torch.from_numpy(C).to(cuda))
+                        ab.set_tuning(ab.TUNE_CGEMM_3M, 0)
+                        assert ab.kernel_name(O.C32, oa, ob, A.shape, B.shape) == "cgemm_tf32x3_tcgen05"
+                        C4 = host(ab.gemm(al, oa, dA, ob, dB))
+                        err = O.gemm_error_units(C, O.gemm(al, oa, A, ob, B, wide=True), A, B, k, al)
+                        assert err <= TOL_UNITS_TF32X3, (tile, oa, ob, m, n, k, err)
+                        assert O.gemm_error_units(C, C4, A, B, k, al) <= 2 * TOL_UNITS_TF32X3
+    finally:
+        for knob in (2, 8, ab.TUNE_CGEMM_3M):
+            ab.set_tuning(knob, -1)
+
+
 def test_launches_are_counted(cuda):
     import torch
     import accblas_b200 as ab
