@@ -57,6 +57,27 @@ def test_kernel_selection_names():
     assert ab.kernel_name(1, "N", "N", (3, 5), (5, 2)) == "gemm_simt_generic"
     assert ab.kernel_name(1, "N", "N", (3, 5), (4, 2)) == "invalid"
     assert ab.kernel_name(1, "N", "N", (0, 5), (5, 2)) == "none"
+    # dispatch policy (csrc/api.cu pick_family), host logic only: families by dtype and size
+    sq = lambda n: ((n, n), (n, n))  # noqa: E731
+    assert ab.kernel_name(1, "N", "T", *sq(8192)) == "dgemm_dmma_tma"
+    assert ab.kernel_name(0, "N", "N", *sq(8192)) == "sgemm_tf32x3_tcgen05"
+    assert ab.kernel_name(0, "N", "N", *sq(1000)) == "sgemm_tf32x3_tcgen05"      # 128 x 64 tcgen05 tile
+    assert ab.kernel_name(0, "N", "N", *sq(500)) == "sgemm_tf32x3_mma"
+    assert ab.kernel_name(0, "N", "N", *sq(250)) == "sgemm_tf32x3_mma"           # via the re-pitch copy
+    assert ab.kernel_name(3, "H", "N", *sq(4096)) == "zgemm_3m_dmma"
+    assert ab.kernel_name(3, "H", "N", *sq(1000)) == "zgemm_dmma_tma"
+    assert ab.kernel_name(2, "H", "N", *sq(4096)) == "cgemm_3m_tf32x3_tcgen05"
+    assert ab.kernel_name(2, "H", "N", *sq(1000)) == "cgemm_tf32x3_tcgen05"
+    assert ab.kernel_name(2, "N", "N", *sq(250)) == "cgemm_tf32x3_mma"
+    assert ab.kernel_name(1, "N", "N", (4096, 1), (1, 4096)) == "gemm_rank1_outer"
+    try:
+        ab.set_tuning(ab.TUNE_ZGEMM_3M, 0)
+        ab.set_tuning(ab.TUNE_CGEMM_3M, 0)
+        assert ab.kernel_name(3, "H", "N", *sq(4096)) == "zgemm_dmma_tma"
+        assert ab.kernel_name(2, "H", "N", *sq(4096)) == "cgemm_tf32x3_tcgen05"
+    finally:
+        ab.set_tuning(ab.TUNE_ZGEMM_3M, -1)
+        ab.set_tuning(ab.TUNE_CGEMM_3M, -1)
 
 
 def test_python_mirror_rejects_bad_inputs():
