@@ -359,6 +359,7 @@ def run_multi(args):
     bms = torch.tensor([b0.elapsed_time(b1)], dtype=torch.float64, device=dev)
     dist.all_reduce(bms, op=dist.ReduceOp.MAX)
     del Bx
+    l12 = mg_level12_extras(dev, rank, world) if args.n_mg >= 4096 else []
     if rank == 0:
         clocks = sampler.stop(t0, t1)
         # parity: 4 rows spread over the rank panels against the oracle
@@ -389,11 +390,73 @@ def run_multi(args):
         }
         line["config"]["transport"] = args.transport
         line["broadcast_B_ms"] = round(bms.item(), 3)
+        line["extras"] = l12
     dist.destroy_process_group()
     sys.stdout.flush()
     os.dup2(saved_stdout, 1)
     if rank == 0:
         print(json.dumps(line), flush=True)
+
+
+def mg_level12_extras(dev, rank, world, iters=20):
+    """configs[2] on N GPUs: dgemv 32768 x 32768 (N and T) with the rows of A pre-sharded over the ranks
+    (moving 8 GiB of A would cost more than the product) and ddot n = 2^28 on pre-sharded slices.  The
+    timed region holds the local kernel AND the exchange (all-gather of y slices / all-reduce of the
+    partial y / all-reduce of one scalar, NCCL over NVLink); device events, max over ranks; GB/s =
+    algorithmic bytes of the WHOLE product / that time.  Checked against the oracle on a few entries."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from accblas_b200 import mg
+    from oracle import oracle as O
+    m = n = 32768
+    rows = m // world
+    A = seeded((rows, n), 0x5EED0000 + 32 + 16 * rank, dev)
+    x = seeded((n,), 0x5EED0000 + 33, dev)
+    xs = seeded((rows,), 0x5EED0000 + 34 + 16 * rank, dev)
+    nd = (1 << 28) // world
+    u, v = seeded((nd,), 0x5EED0000 + 35 + 16 * rank, dev), seeded((nd,), 0x5EED0000 + 36 + 16 * rank, dev)
+    out = []
+
+    def timed(name, fn, nbytes):
+        for _ in range(3):
+            r = fn()
+        torch.cuda.synchronize()
+        dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(iters):
+            r = fn()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = torch.tensor([e0.elapsed_time(e1) / iters], dtype=torch.float64, device=dev)
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        out.append({"case": name, "ms": round(ms.item(), 4), "gbs": round(nbytes / ms.item() * 1e-6, 1),
+                    "per_gpu_gbs": round(nbytes / ms.item() * 1e-6 / world, 1)})
+        return r
+
+    y = timed(f"f64gemv_N_{m}x{n}_rows/{world}", lambda: mg.gemv_sharded(1.0, "N", A, x), 8.0 * (m * n + m + n))
+    pick = [0, rows // 2, rows - 1]
+    ref = O.gemv(1.0, "N", A[pick].cpu().numpy(), x.cpu().numpy())
+    got = y[[rank * rows + i for i in pick]].cpu().numpy()
+    ok = float(np.max(np.abs(got - ref))) <= n * 2.0 ** -53 * float(torch.linalg.norm(x)) * float(torch.linalg.norm(A[pick], dim=1).max())
+    yt = timed(f"f64gemv_T_{m}x{n}_rows/{world}", lambda: mg.gemv_sharded(1.0, "T", A, xs), 8.0 * (m * n + m + n))
+    cols = [0, n // 3, n - 1]
+    part = torch.from_numpy(O.gemv(1.0, "T", np.ascontiguousarray(A[:, cols].cpu().numpy()), xs.cpu().numpy())).to(dev)
+    dist.all_reduce(part, op=dist.ReduceOp.SUM)
+    bound = m * 2.0 ** -53 * float(torch.linalg.norm(A[:, cols], dim=0).max()) * float(torch.linalg.norm(xs)) * world
+    ok = ok and float((yt[cols] - part).abs().max()) <= bound
+    d = timed(f"f64dot_{1 << 28}_slices/{world}", lambda: mg.dot_sharded(u, v), 2.0 * 8 * (1 << 28) + 8)
+    dref = torch.tensor([float(O.dot(u[:1 << 20].cpu().numpy(), v[:1 << 20].cpu().numpy()))], dtype=torch.float64, device=dev)
+    dgot = mg.dot_sharded(u[:1 << 20], v[:1 << 20])
+    dist.all_reduce(dref, op=dist.ReduceOp.SUM)
+    tot = float((1 << 20) * world)
+    ok = ok and abs(float(dgot) - float(dref)) <= tot * 2.0 ** -53 * tot / 3 and bool(torch.isfinite(d))
+    flag = torch.tensor([1 if ok else 0], dtype=torch.int64, device=dev)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    assert flag.item() == 1, "parity lost in the sharded gemv / dot extras"
+    return out
 
 
 def extras():
