@@ -5,6 +5,7 @@
 #include "common.cuh"
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
 #include <algorithm>
 
 namespace accblas {
@@ -12,7 +13,32 @@ namespace accblas {
 thread_local uint64_t g_launches = 0;
 thread_local char g_cuda_err[256] = {0};
 thread_local int g_gemm_path = 0;
-thread_local int g_tuning[ACCBLAS_TUNE_COUNT] = {-1, -1, -1, -1, -1, -1, -1, -1, -1, -1, -1, -1};
+namespace {
+struct TuningDefaults {
+    int v[ACCBLAS_TUNE_COUNT];
+    TuningDefaults()
+    {
+        for (int &x : v) x = -1;
+        const char *e = getenv("ACCBLAS_TUNE");
+        while (e && *e) {                                   // "knob=value,knob=value"
+            char *end = nullptr;
+            const long knob = strtol(e, &end, 10);
+            if (end == e || *end != '=') break;
+            e = end + 1;
+            const long val = strtol(e, &end, 10);
+            if (end == e) break;
+            if (knob >= 0 && knob < ACCBLAS_TUNE_COUNT) v[knob] = (int)val;
+            e = *end == ',' ? end + 1 : end;
+        }
+    }
+};
+}  // namespace
+Tuning::Tuning()
+{
+    static const TuningDefaults d;
+    for (int i = 0; i < ACCBLAS_TUNE_COUNT; ++i) v[i] = d.v[i];
+}
+thread_local Tuning g_tuning;
 
 int cuda_fail(cudaError_t e, const char *where)
 {

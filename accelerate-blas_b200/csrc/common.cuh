@@ -13,7 +13,15 @@ namespace accblas {
 extern thread_local uint64_t g_launches;      // kernels enqueued by this thread
 extern thread_local char g_cuda_err[256];     // text of the last CUDA failure
 extern thread_local int g_gemm_path;          // accblas_set_gemm_path
-extern thread_local int g_tuning[ACCBLAS_TUNE_COUNT];   // accblas_set_tuning (-1 = automatic)
+// accblas_set_tuning (-1 = automatic).  Per thread; a new thread starts from the process-wide defaults
+// in the environment variable ACCBLAS_TUNE ("knob=value,knob=value", e.g. "7=0,9=0" pins 4M complex
+// products) -- the way to pin a choice from a host runtime whose FFI calls hop between OS threads.
+struct Tuning {
+    int v[ACCBLAS_TUNE_COUNT];
+    Tuning();
+    int &operator[](int i) { return v[i]; }
+};
+extern thread_local Tuning g_tuning;
 
 int cuda_fail(cudaError_t e, const char *where);   // records text, returns ACCBLAS_ERR_CUDA
 inline int check_launch(const char *where) {

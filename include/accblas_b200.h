@@ -245,6 +245,8 @@ typedef enum {
     ACCBLAS_TUNE_CGEMM_3M = 9,      /* c32 gemm on tcgen05: 0 = always the 4M real embedding, 1 = 3M whenever possible     */
     ACCBLAS_TUNE_COUNT = 12
 } accblas_tune_t;
+/* Process-wide defaults for threads that never call this: environment variable
+ * ACCBLAS_TUNE="knob=value,knob=value" (read once). */
 void accblas_set_tuning(int knob, int value);
 
 #ifdef __cplusplus

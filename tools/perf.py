@@ -111,8 +111,7 @@ def suite():
 
 if __name__ == "__main__":
     a = sys.argv[1:]
-    for kv in filter(None, os.environ.get("ACCBLAS_TUNE", "").split(",")):     # e.g. ACCBLAS_TUNE=7=0,0=1
-        ab.set_tuning(int(kv.split("=")[0]), int(kv.split("=")[1]))
+    # kernel variants are forced with the library's own environment variable, e.g. ACCBLAS_TUNE=7=0,0=1
     if not a or a[0] == "suite":
         suite()
     elif a[0] == "gemm":
