@@ -268,9 +268,9 @@ def gemv_sharded(alpha, opA, A_local: torch.Tensor, x: torch.Tensor, *, group=No
     world = dist.get_world_size(group)
     y = local_gemv(alpha, opa, A_local, x)
     if opa == 0:
-        parts = [torch.empty_like(y) for _ in range(world)]
-        dist.all_gather(parts, y, group=group)
-        return torch.cat(parts)
+        full = torch.empty((world * y.shape[0],), dtype=y.dtype, device=y.device)
+        dist.all_gather_into_tensor(full, y, group=group)      # one collective, no list / cat copies
+        return full
     if torch.is_complex(y):
         yr = torch.view_as_real(y)
         dist.all_reduce(yr, op=dist.ReduceOp.SUM, group=group)
