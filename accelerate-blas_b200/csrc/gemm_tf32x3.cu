@@ -82,47 +82,68 @@ __device__ __forceinline__ float pack_value(const PackArgs &a, int64_t r, int64_
 // row index (transposed), the tile goes through shared memory so both sides stay coalesced.
 // Both operands are packed by ONE launch (blockIdx.z = 0: A, 1: B): the mid-size products this family
 // now serves (1000^3 takes ~40 us in all) are sensitive to every extra launch.
+// A block packs 32 rows x (PK_NT * 32) columns: all its loads are issued before the first store, so a
+// thread keeps PK_NT * 4 loads in flight (the 32 x 32 version kept 4 and sat at 4.2 TB/s, latency-bound).
+constexpr int PK_NT = 4;
+
 template <int MODE>
-__device__ __forceinline__ void pack_split_tile(const PackArgs &a, float (&tile)[32][33])
+__device__ __forceinline__ void pack_split_tile(const PackArgs &a, float (&tile)[PK_NT][32][33])
 {
-    const int64_t r0 = (int64_t)blockIdx.y * 32, c0 = (int64_t)blockIdx.x * 32;
+    const int64_t r0 = (int64_t)blockIdx.y * 32, c0 = (int64_t)blockIdx.x * (32 * PK_NT);
     if (r0 >= a.R || c0 >= a.pitch) return;                      // uniform per block (grid covers the larger operand)
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;    // 32 x 8
+    float v[PK_NT][4];
     if (a.transposed) {
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            const int cc = ty + 8 * i;                           // fast index tx walks r
-            const int64_t r = r0 + tx, c = c0 + cc;
-            tile[cc][tx] = (r < a.R && c < a.Kp) ? pack_value<MODE>(a, r, c) : 0.f;
-        }
+        for (int t = 0; t < PK_NT; ++t)
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int cc = ty + 8 * i;                       // fast index tx walks r
+                const int64_t r = r0 + tx, c = c0 + 32 * t + cc;
+                v[t][i] = (r < a.R && c < a.Kp) ? pack_value<MODE>(a, r, c) : 0.f;
+            }
+#pragma unroll
+        for (int t = 0; t < PK_NT; ++t)
+#pragma unroll
+            for (int i = 0; i < 4; ++i) tile[t][ty + 8 * i][tx] = v[t][i];
         __syncthreads();
+#pragma unroll
+        for (int t = 0; t < PK_NT; ++t)
+#pragma unroll
+            for (int i = 0; i < 4; ++i) v[t][i] = tile[t][tx][ty + 8 * i];
+    } else {
+#pragma unroll
+        for (int t = 0; t < PK_NT; ++t)
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int64_t r = r0 + ty + 8 * i, c = c0 + 32 * t + tx;   // fast index tx walks c
+                v[t][i] = (r < a.R && c < a.Kp) ? pack_value<MODE>(a, r, c) : 0.f;
+            }
     }
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        const int rr = ty + 8 * i;
-        const int64_t r = r0 + rr, c = c0 + tx;                  // fast index tx walks c
-        if (r >= a.R || c >= a.pitch) continue;
-        float v = 0.f;
-        if (c < a.Kp) v = a.transposed ? tile[tx][rr] : pack_value<MODE>(a, r, c);
-        const float h = to_tf32(v);
-        const float l = to_tf32(v - h);
-        a.hi[r * a.pitch + c] = h;
-        a.lo[r * a.pitch + c] = l;
-    }
+    for (int t = 0; t < PK_NT; ++t)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int64_t r = r0 + ty + 8 * i, c = c0 + 32 * t + tx;
+            if (r >= a.R || c >= a.pitch) continue;
+            const float h = to_tf32(v[t][i]);
+            a.hi[r * a.pitch + c] = h;
+            a.lo[r * a.pitch + c] = to_tf32(v[t][i] - h);
+        }
 }
 
 template <int MODE_A, int MODE_B>
 __global__ void __launch_bounds__(256)
 pack_split_kernel(const PackArgs a, const PackArgs b)
 {
-    __shared__ float tile[32][33];
+    __shared__ float tile[PK_NT][32][33];
     if (blockIdx.z == 0) pack_split_tile<MODE_A>(a, tile);
     else pack_split_tile<MODE_B>(b, tile);
 }
 
 int launch_pack(bool cplx, const PackArgs &a, const PackArgs &b, cudaStream_t st)
 {
-    dim3 grid((unsigned)((std::max(a.pitch, b.pitch) + 31) / 32), (unsigned)((std::max(a.R, b.R) + 31) / 32), 2);
+    dim3 grid((unsigned)((std::max(a.pitch, b.pitch) + 32 * PK_NT - 1) / (32 * PK_NT)), (unsigned)((std::max(a.R, b.R) + 31) / 32), 2);
     if (grid.y > 65535u) return ACCBLAS_ERR_SHAPE;     // eligibility keeps R below 2^21
     if (cplx) pack_split_kernel<PK_CPLX_A, PK_CPLX_B><<<grid, 256, 0, st>>>(a, b);
     else      pack_split_kernel<PK_REAL, PK_REAL><<<grid, 256, 0, st>>>(a, b);
