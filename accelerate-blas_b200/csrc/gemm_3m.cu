@@ -154,7 +154,10 @@ int zgemm_3m(const GemmArgs &g)
 {
     const size_t pa = plane_bytes(g.rowsA, g.colsA), pb = plane_bytes(g.rowsB, g.colsB), pt = plane_bytes(g.m, g.n);
     char *ws = nullptr;
-    ACC_CUDA(cudaMallocAsync(reinterpret_cast<void **>(&ws), 3 * (pa + pb + pt), g.stream));
+    if (cudaMallocAsync(reinterpret_cast<void **>(&ws), 3 * (pa + pb + pt), g.stream) != cudaSuccess) {
+        (void)cudaGetLastError();                          // no room for the planes: the in-register 4M kernel needs none
+        return dgemm_dmma(g);
+    }
     char *wa = ws, *wb = ws + 3 * pa, *wt = wb + 3 * pb;
     int st = launch_split(g.stream, g.A, g.rowsA, g.colsA, g.lda, g.opA == ACCBLAS_OP_H, wa);
     if (st == ACCBLAS_OK) st = launch_split(g.stream, g.B, g.rowsB, g.colsB, g.ldb, g.opB == ACCBLAS_OP_H, wb);

@@ -616,7 +616,10 @@ int cgemm_3m_run(const GemmArgs &g)
     const Tc3Plan q = make_plan3(g);
     const size_t pa = q.t.plane_a, pb = q.t.plane_b, pt = q.plane_t;
     char *ws = nullptr;
-    ACC_CUDA(cudaMallocAsync(reinterpret_cast<void **>(&ws), 6 * (pa + pb) + 3 * pt, g.stream));
+    if (cudaMallocAsync(reinterpret_cast<void **>(&ws), 6 * (pa + pb) + 3 * pt, g.stream) != cudaSuccess) {
+        (void)cudaGetLastError();                          // no room for 3M's planes: the 4M embedding needs a third of them
+        return sgemm_tc(g);
+    }
     char *wa = ws, *wb = ws + 6 * pa, *wt = wb + 6 * pb;
     Pack3Args a{}, b{};
     a.src = static_cast<const float2 *>(g.A); a.ld = g.lda;
