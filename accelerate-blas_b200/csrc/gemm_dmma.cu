@@ -73,6 +73,7 @@ struct DgemmParams {
     Alpha<double> alpha;
     double *C;
     int tiles_m, tiles_n, group;
+    int snake_waves;     // CTAs per resident wave (0: every tile walks K forwards)
 };
 
 // AK: op(A) is K-major in memory (opA == N).  BKM: op(B) is K-major in memory (opB == T).
@@ -120,6 +121,10 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
             tma::prefetch_tmap(&mapB);
             // (L2 eviction hints -- evict_last on A, evict_first on B, tma::load_2d_hint -- were measured:
             //  DRAM traffic 6.9 GB per 8192^3 launch with or without them, time unchanged; left out.)
+            // Successive waves of CTAs (one CTA per SM: blockIdx / gridDim-independent SM count) walk K in
+            // opposite directions: a wave ends with the K-tail of its panels in L2, and the next wave -- which
+            // shares its A panels under the grouped rasterisation -- starts on exactly that tail.
+            const bool rev = p.snake_waves > 0 && ((blockIdx.x / p.snake_waves) & 1);
             for (int kb = 0; kb < kblocks; ++kb) {
                 const int s = kb % STAGES;
                 const uint32_t round = kb / STAGES;
@@ -127,7 +132,7 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
                 const uint32_t full = bar_base + 8 * s;
                 const uint32_t sa = smem_base + s * STAGE_BYTES, sb = sa + A_BYTES;
                 tma::mbar_expect_tx(full, STAGE_BYTES);
-                const int k0 = kb * BK;
+                const int k0 = (rev ? kblocks - 1 - kb : kb) * BK;
                 if (AK) tma::load_2d(sa, &mapA, full, k0, m0);
                 else
 #pragma unroll
@@ -470,6 +475,7 @@ int launch_dgemm_tile(const GemmArgs &g)
     p.tiles_m = (int)((g.m + BM - 1) / BM);
     p.tiles_n = (int)((g.n + BN - 1) / BN);
     p.group = g_tuning[ACCBLAS_TUNE_RASTER_GROUP] > 0 ? g_tuning[ACCBLAS_TUNE_RASTER_GROUP] : 16;
+    p.snake_waves = g_tuning[ACCBLAS_TUNE_SNAKE_K] == 0 ? 0 : sm_count() * TL::MIN_CTAS;
     const int64_t tiles = (int64_t)p.tiles_m * p.tiles_n;
     if (tiles > 0x7fffffff) return ACCBLAS_ERR_SHAPE;
     dgemm_dmma_kernel<AK, BKM, TL><<<(unsigned)tiles, TL::THREADS, SMEM_BYTES, g.stream>>>(mapA, mapB, p);
