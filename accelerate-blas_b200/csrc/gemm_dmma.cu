@@ -24,6 +24,7 @@
 //     (C is write-only: beta = 0, LLVM/PTX/Level3.hs:90).
 #include "common.cuh"
 #include "tma.cuh"
+#include <algorithm>
 
 namespace accblas {
 namespace {
@@ -216,6 +217,215 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
     }
 }
 
+
+// =====================================================================================
+// Stream-K variant of the 128 x 128 real kernel: ONE persistent CTA per SM, the (tile, K-block) iteration
+// space cut into equal contiguous ranges, so a product whose tile count is not a multiple of the SM count
+// (dgemm 1024^3: 64 tiles, 2048^3: 256 tiles on 148 SMs) still loads every SM evenly.
+// A range is a sequence of segments (one tile, K-blocks [ks, ke)):
+//   whole tile  (ks == 0, ke == kblocks)  -> the usual epilogue;
+//   tile tail   (ks > 0): only ever the FIRST segment of a CTA -> accumulators go to the CTA's workspace
+//                slot in fragment layout, then a release flag;
+//   tile head   (ks == 0, ke < kblocks): only ever the LAST segment of a CTA -> waits for the flags of the
+//                following CTAs that hold the rest of the tile (work they did at the very start of their
+//                lives, so the wait is short and cannot chain), adds their partials in CTA order
+//                (deterministic), runs the epilogue.
+// All CTAs are co-resident (grid <= SM count, one CTA per SM by shared memory), so the flag wait cannot deadlock.
+// =====================================================================================
+struct StreamKParams {
+    DgemmParams p;
+    int kblocks;
+    long long total;        // tiles * kblocks
+    int base, rem;          // CTA c owns base + (c < rem) iterations starting at c * base + min(c, rem)
+    double *ws;             // gridDim.x slots of 128 x 128 doubles
+    unsigned *flags;        // gridDim.x words, zeroed before the launch
+};
+
+__device__ __forceinline__ unsigned ld_acquire_gpu(const unsigned *p) {
+    unsigned v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_gpu(unsigned *p, unsigned v) {
+    asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void tile_coords(const DgemmParams &p, int tile, int &tile_m, int &tile_n) {
+    const int per_group = p.group * p.tiles_n;
+    const int grp = tile / per_group;
+    const int first_m = grp * p.group;
+    const int gsz = min(p.tiles_m - first_m, p.group);
+    const int in_grp = tile - grp * per_group;
+    tile_m = first_m + in_grp % gsz;
+    tile_n = in_grp / gsz;
+}
+
+template <bool AK, bool BKM>
+__global__ void __launch_bounds__(Tile128x128::THREADS, 1)
+dgemm_dmma_streamk_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
+                          const StreamKParams q)
+{
+    using TL = Tile128x128;
+    constexpr int MI = TL::MI, NJ = TL::NJ, BM = TL::BM, BN = TL::BN, STAGES = TL::STAGES,
+                  A_BYTES = TL::A_BYTES, STAGE_BYTES = TL::STAGE_BYTES, CONSUMER_WARPS = TL::CONSUMER_WARPS;
+    const DgemmParams &p = q.p;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t smem_base = (tma::smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t bar_base = smem_base + STAGES * STAGE_BYTES;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int kblocks = q.kblocks;
+    const int cta = blockIdx.x;
+    const int it_begin = cta * q.base + min(cta, q.rem);           // host guarantees total < 2^31
+    const int it_end = it_begin + q.base + (cta < q.rem ? 1 : 0);
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < STAGES; ++s) {
+            tma::mbar_init(bar_base + 8 * s, 1);
+            tma::mbar_init(bar_base + 8 * (STAGES + s), CONSUMER_WARPS);
+        }
+        tma::fence_barrier_init();
+    }
+    __syncthreads();
+
+    if (warp == CONSUMER_WARPS) {
+        // ================================ producer ================================
+        if (lane == 0) {
+            tma::prefetch_tmap(&mapA);
+            tma::prefetch_tmap(&mapB);
+            int g = 0;                                            // K-blocks issued so far (ring position)
+            for (int it = it_begin; it < it_end;) {
+                const int tile = it / kblocks, ks = it - tile * kblocks;
+                const int ke = min(kblocks, ks + (it_end - it));
+                int tile_m, tile_n;
+                tile_coords(p, tile, tile_m, tile_n);
+                const int m0 = tile_m * BM, n0 = tile_n * BN;
+                const bool rev = p.snake_waves > 0 && ((tile / p.snake_waves) & 1);
+                for (int kb = ks; kb < ke; ++kb, ++g) {
+                    const int s = g % STAGES;
+                    if (g >= STAGES) tma::mbar_wait(bar_base + 8 * (STAGES + s), ((g / STAGES) - 1) & 1);
+                    const uint32_t full = bar_base + 8 * s;
+                    const uint32_t sa = smem_base + s * STAGE_BYTES, sb = sa + A_BYTES;
+                    tma::mbar_expect_tx(full, STAGE_BYTES);
+                    const int k0 = (rev ? kblocks - 1 - kb : kb) * BK;
+                    if (AK) tma::load_2d(sa, &mapA, full, k0, m0);
+                    else
+#pragma unroll
+                        for (int j = 0; j < BM / 16; ++j) tma::load_2d(sa + j * 2048, &mapA, full, m0 + 16 * j, k0);
+                    if (BKM) tma::load_2d(sb, &mapB, full, k0, n0);
+                    else
+#pragma unroll
+                        for (int j = 0; j < BN / 16; ++j) tma::load_2d(sb + j * 2048, &mapB, full, n0 + 16 * j, k0);
+                }
+                it += ke - ks;
+            }
+        }
+        return;
+    }
+    // ================================ consumers ================================
+    const int gq = lane >> 2, t = lane & 3;
+    const int wm = warp / TL::WN, wn = warp % TL::WN;
+    uint32_t offA[4], offB[4];
+#pragma unroll
+    for (int s = 0; s < 4; ++s) {
+        const int kk = kslot(s, t);
+        const uint32_t kmaj = gq * 128 + ((((kk >> 1) ^ gq) & 7) << 4) + (kk & 1) * 8;
+        const uint32_t mnmaj = kk * 128 + ((((gq >> 1) ^ (kk & 7)) & 7) << 4) + (gq & 1) * 8;
+        offA[s] = AK ? (uint32_t)(wm * MI * 8 * 128) + kmaj : (uint32_t)(wm * (MI / 2) * 2048) + mnmaj;
+        offB[s] = A_BYTES + (BKM ? (uint32_t)(wn * NJ * 8 * 128) + kmaj : (uint32_t)(wn * (NJ / 2) * 2048) + mnmaj);
+    }
+    auto load_frags = [&](uint32_t stage, int s, double (&a)[MI], double (&b)[NJ]) {
+#pragma unroll
+        for (int i = 0; i < MI; ++i)
+            a[i] = lds64(stage + (AK ? offA[s] + i * 1024 : (offA[s] ^ ((i & 1) << 6)) + (i >> 1) * 2048));
+#pragma unroll
+        for (int j = 0; j < NJ; ++j)
+            b[j] = lds64(stage + (BKM ? offB[s] + j * 1024 : (offB[s] ^ ((j & 1) << 6)) + (j >> 1) * 2048));
+    };
+    const bool vec = ((p.n | p.ldc) & 1) == 0;
+    const double alpha = p.alpha.get();
+    constexpr int SLOT = BM * BN;                                  // doubles per workspace slot
+    int g = 0;                                                    // K-blocks consumed so far (ring position)
+    for (int it = it_begin; it < it_end;) {
+        const int tile = it / kblocks, ks = it - tile * kblocks;
+        const int ke = min(kblocks, ks + (it_end - it));
+        double acc[MI][NJ][2];
+#pragma unroll
+        for (int i = 0; i < MI; ++i)
+#pragma unroll
+            for (int j = 0; j < NJ; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
+        for (int kb = ks; kb < ke; ++kb, ++g) {
+            const int s = g % STAGES;
+            const uint32_t stage = smem_base + s * STAGE_BYTES;
+            tma::mbar_wait(bar_base + 8 * s, (g / STAGES) & 1);
+            double a[2][MI], b[2][NJ];
+            load_frags(stage, 0, a[0], b[0]);
+#pragma unroll
+            for (int st = 0; st < 4; ++st) {
+                if (st < 3) load_frags(stage, st + 1, a[(st + 1) & 1], b[(st + 1) & 1]);
+#pragma unroll
+                for (int i = 0; i < MI; ++i)
+#pragma unroll
+                    for (int j = 0; j < NJ; ++j) dmma(acc[i][j][0], acc[i][j][1], a[st & 1][i], b[st & 1][j]);
+            }
+            tma::consumer_release_fence();
+            if (lane == 0) tma::mbar_arrive(bar_base + 8 * (STAGES + s));
+        }
+        if (ks > 0) {
+            // ---- tile tail: hand the partial sums to the CTA that owns the head of this tile ----
+            double2 *slot = reinterpret_cast<double2 *>(q.ws + (size_t)cta * SLOT);
+#pragma unroll
+            for (int i = 0; i < MI; ++i)
+#pragma unroll
+                for (int j = 0; j < NJ; ++j)
+                    slot[((warp * MI + i) * NJ + j) * 32 + lane] = make_double2(acc[i][j][0], acc[i][j][1]);
+            __threadfence();
+            asm volatile("bar.sync 1, %0;" ::"n"(CONSUMER_WARPS * 32) : "memory");
+            if (threadIdx.x == 0) st_release_gpu(q.flags + cta, 1u);
+        } else {
+            if (ke < kblocks) {
+                // ---- tile head: add the partial sums of the CTAs holding K-blocks [ke, kblocks) ----
+                int pos = ke;
+                for (int c2 = cta + 1; pos < kblocks; ++c2) {
+                    unsigned spins = 0;
+                    while (ld_acquire_gpu(q.flags + c2) == 0u) {
+                        __nanosleep(100);
+                        if (++spins > (1u << 24)) __trap();
+                    }
+                    const double2 *slot = reinterpret_cast<const double2 *>(q.ws + (size_t)c2 * SLOT);
+#pragma unroll
+                    for (int i = 0; i < MI; ++i)
+#pragma unroll
+                        for (int j = 0; j < NJ; ++j) {
+                            const double2 v = __ldcg(&slot[((warp * MI + i) * NJ + j) * 32 + lane]);
+                            acc[i][j][0] += v.x;
+                            acc[i][j][1] += v.y;
+                        }
+                    pos += min(q.base + (c2 < q.rem ? 1 : 0), kblocks - pos);
+                }
+            }
+            int tile_m, tile_n;
+            tile_coords(p, tile, tile_m, tile_n);
+            const int m0 = tile_m * BM, n0 = tile_n * BN;
+#pragma unroll
+            for (int i = 0; i < MI; ++i) {
+                const int64_t r = m0 + wm * MI * 8 + i * 8 + gq;
+                if (r >= p.m) continue;
+                double *crow = p.C + r * p.ldc;
+#pragma unroll
+                for (int j = 0; j < NJ; ++j) {
+                    const int64_t c = n0 + wn * NJ * 8 + j * 8 + 2 * t;
+                    const double v0 = alpha * acc[i][j][0], v1 = alpha * acc[i][j][1];
+                    if (vec) {
+                        if (c < p.n) *reinterpret_cast<double2 *>(crow + c) = make_double2(v0, v1);
+                    } else {
+                        if (c < p.n) crow[c] = v0;
+                        if (c + 1 < p.n) crow[c + 1] = v1;
+                    }
+                }
+            }
+        }
+        it += ke - ks;
+    }
+}
 
 // =====================================================================================
 // complex f64 (zgemm): "4M in registers".  Interleaved (re,im) operands are used as stored:
@@ -436,7 +646,7 @@ constexpr TileModel kTileModel[4] = {
     {32, 32, 0.975, 32.0, 0.50},
 };
 
-int pick_tile(int64_t m, int64_t n, int64_t k)
+int pick_tile(int64_t m, int64_t n, int64_t k, double *cost_out = nullptr)
 {
     if (g_tuning[ACCBLAS_TUNE_DMMA_TILE] >= 0 && g_tuning[ACCBLAS_TUNE_DMMA_TILE] < 4) return g_tuning[ACCBLAS_TUNE_DMMA_TILE];
     const int sms = sm_count();
@@ -449,6 +659,7 @@ int pick_tile(int64_t m, int64_t n, int64_t k)
         const double cost = per_sm * (double)t.bm * (double)t.bn * ((double)k + t.fixed_k) / (per_sm > 1.0 ? t.eff : t.eff_alone);
         if (c == 0 || cost < best_cost * 0.999) { best = c; best_cost = cost; }
     }
+    if (cost_out) *cost_out = best_cost;
     return best;
 }
 
@@ -482,10 +693,78 @@ int launch_dgemm_tile(const GemmArgs &g)
     return check_launch("dgemm_dmma_kernel");
 }
 
+// Stream-K launch (128 x 128 tiles, one persistent CTA per SM).  Scratch: one accumulator slot per CTA + flags.
+template <bool AK, bool BKM>
+int launch_dgemm_streamk(const GemmArgs &g)
+{
+    using TL = Tile128x128;
+    CUtensorMap mapA, mapB;
+    if (!tma::make_2d(&mapA, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 8, g.A, (uint64_t)g.rowsA, (uint64_t)g.colsA,
+                      AK ? TL::BM : BK, 16, (uint64_t)g.lda * 8) ||
+        !tma::make_2d(&mapB, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 8, g.B, (uint64_t)g.rowsB, (uint64_t)g.colsB,
+                      BKM ? TL::BN : BK, 16, (uint64_t)g.ldb * 8))
+        return cuda_fail(cudaErrorInvalidValue, "cuTensorMapEncodeTiled");
+    static thread_local bool attr_done = false;
+    if (!attr_done) {
+        ACC_CUDA(cudaFuncSetAttribute(dgemm_dmma_streamk_kernel<AK, BKM>, cudaFuncAttributeMaxDynamicSharedMemorySize, TL::SMEM_BYTES));
+        attr_done = true;
+    }
+    StreamKParams q;
+    DgemmParams &p = q.p;
+    p.m = g.m; p.n = g.n; p.k = g.k; p.ldc = g.ldc;
+    p.alpha = make_alpha<double>(g.alpha, g.alpha_dev);
+    p.C = static_cast<double *>(g.C);
+    p.tiles_m = (int)((g.m + TL::BM - 1) / TL::BM);
+    p.tiles_n = (int)((g.n + TL::BN - 1) / TL::BN);
+    p.group = g_tuning[ACCBLAS_TUNE_RASTER_GROUP] > 0 ? g_tuning[ACCBLAS_TUNE_RASTER_GROUP] : 16;
+    p.snake_waves = g_tuning[ACCBLAS_TUNE_SNAKE_K] == 0 ? 0 : sm_count();
+    q.kblocks = (int)((g.k + BK - 1) / BK);
+    q.total = (long long)p.tiles_m * p.tiles_n * q.kblocks;
+    const int grid = (int)std::min<long long>(sm_count(), q.total);
+    q.base = (int)(q.total / grid);
+    q.rem = (int)(q.total % grid);
+    const size_t ws_bytes = (size_t)grid * TL::BM * TL::BN * 8;
+    char *ws = nullptr;
+    ACC_CUDA(cudaMallocAsync(reinterpret_cast<void **>(&ws), ws_bytes + 4096, g.stream));
+    q.ws = reinterpret_cast<double *>(ws);
+    q.flags = reinterpret_cast<unsigned *>(ws + ws_bytes);
+    cudaError_t e = cudaMemsetAsync(q.flags, 0, 4096, g.stream);
+    int st = ACCBLAS_OK;
+    if (e == cudaSuccess) {
+        dgemm_dmma_streamk_kernel<AK, BKM><<<(unsigned)grid, TL::THREADS, TL::SMEM_BYTES, g.stream>>>(mapA, mapB, q);
+        st = check_launch("dgemm_dmma_streamk_kernel");
+    }
+    const cudaError_t e2 = cudaFreeAsync(ws, g.stream);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaMemsetAsync (stream-K flags)");
+    if (st == ACCBLAS_OK && e2 != cudaSuccess) return cuda_fail(e2, "cudaFreeAsync");
+    return st;
+}
+
+// Stream-K pays when a product of at least one full wave of 128 x 128 tiles leaves a partial last wave: measured
+// (profiles/r01_streamk.jsonl) 2048^3 (256 tiles, wave efficiency 0.865) 522 -> 510 us, 2560^3 (0.90) 1013 -> 975,
+// 3072^3 (0.973) 1680 -> 1663; at 0.988 (4096^3, 8192^3) it is a wash, and below one wave the small data-parallel
+// tiles win (1024^3: 75.8 against 86.0 us) because the scratch, the flag memset and the fixups cost ~30 us.
+bool want_streamk(int64_t m, int64_t n, int64_t k, double best_cost)
+{
+    (void)best_cost;
+    const int knob = g_tuning[ACCBLAS_TUNE_STREAMK];
+    if (knob == 0 || g_tuning[ACCBLAS_TUNE_DMMA_TILE] >= 0) return false;
+    const int sms = sm_count();
+    if (sms > 1024) return false;                                  // flag block is 4 KiB
+    const int64_t tiles = ((m + 127) / 128) * ((n + 127) / 128), kblocks = (k + BK - 1) / BK;
+    if (tiles * kblocks < 4 * (int64_t)sms || kblocks < 4 || tiles * kblocks > 0x7fffffff) return false;
+    if (knob == 1) return true;
+    const int64_t waves = (tiles + sms - 1) / sms;
+    return tiles >= sms && (double)tiles < 0.98 * (double)(waves * sms) && k >= 512;
+}
+
 template <bool AK, bool BKM>
 int launch_dgemm(const GemmArgs &g)
 {
-    switch (pick_tile(g.m, g.n, g.k)) {
+    double best_cost = 0.0;
+    const int tile = pick_tile(g.m, g.n, g.k, &best_cost);
+    if (want_streamk(g.m, g.n, g.k, best_cost)) return launch_dgemm_streamk<AK, BKM>(g);
+    switch (tile) {
     case 1:  return launch_dgemm_tile<AK, BKM, Tile64x128>(g);
     case 2:  return launch_dgemm_tile<AK, BKM, Tile64x64>(g);
     case 3:  return launch_dgemm_tile<AK, BKM, Tile32x32>(g);

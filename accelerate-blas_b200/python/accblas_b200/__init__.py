@@ -377,6 +377,7 @@ TUNE_SGEMM_FAMILY, TUNE_SMMA_TILE, TUNE_HOST_PIPELINE, TUNE_RASTER_GROUP, TUNE_H
 TUNE_TC_TILE = 8        # tcgen05 f32/c32 gemm CTA tile: 0 = 128x256, 1 = 128x128, 2 = 128x64
 TUNE_CGEMM_3M = 9       # c32 gemm on tcgen05: 0 = 4M real embedding, 1 = 3M whenever possible, -1 = cost model
 TUNE_SNAKE_K = 10       # f64 gemm: 0 = every tile walks K forwards
+TUNE_STREAMK = 11       # f64 gemm: 0 = never stream-K, 1 = whenever possible
 TUNE_ZGEMM_3M = 7       # 0: complex-double gemm always 4M in registers, 1: 3M whenever possible, -1: cost model
 
 

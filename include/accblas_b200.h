@@ -244,6 +244,7 @@ typedef enum {
     ACCBLAS_TUNE_TC_TILE = 8,       /* tcgen05 f32/c32 gemm CTA tile: 0 = 128x256, 1 = 128x128, 2 = 128x64                  */
     ACCBLAS_TUNE_CGEMM_3M = 9,      /* c32 gemm on tcgen05: 0 = always the 4M real embedding, 1 = 3M whenever possible     */
     ACCBLAS_TUNE_SNAKE_K = 10,      /* f64 gemm: 0 = every tile walks K forwards (default: alternate per wave of CTAs)       */
+    ACCBLAS_TUNE_STREAMK = 11,      /* f64 gemm: 0 = never the persistent stream-K kernel, 1 = whenever possible               */
     ACCBLAS_TUNE_COUNT = 12
 } accblas_tune_t;
 /* Process-wide defaults for threads that never call this: environment variable

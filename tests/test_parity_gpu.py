@@ -562,6 +562,34 @@ def test_cgemm_3m(cuda):
             ab.set_tuning(knob, -1)
 
 
+def test_dgemm_streamk(cuda):
+    """The persistent stream-K variant of the 128 x 128 DMMA kernel (forced): tiles cut across several CTAs
+    (few K-blocks per CTA), whole tiles plus head / tail fixups, ragged edges, every op pair; against the wide
+    oracle on sampled rows and against the data-parallel kernel on the whole matrix; run-to-run bit equality."""
+    import torch
+    import accblas_b200 as ab
+    rng = np.random.default_rng(9500)
+    try:
+        for (m, n, k) in [(640, 512, 512), (1000, 900, 777), (300, 260, 4000), (2048, 2048, 640)]:
+            for oa, ob in [("N", "N"), ("T", "N"), ("N", "T"), ("T", "T")]:
+                al, A, B = gemm_inputs(rng, O.F64, oa, ob, m, n, k)
+                dA, dB = dev(A, cuda), dev(B, cuda)
+                ab.set_tuning(ab.TUNE_STREAMK, 1)
+                C1 = ab.gemm(al, oa, dA, ob, dB)
+                C1b = ab.gemm(al, oa, dA, ob, dB)
+                ab.set_tuning(ab.TUNE_STREAMK, 0)
+                C0 = ab.gemm(al, oa, dA, ob, dB)
+                assert torch.equal(C1, C1b), (m, n, k, oa, ob)
+                C = host(C1)
+                assert O.gemm_error_units(C, host(C0), A, B, k, al) <= 2 * TOL_UNITS[O.F64], (m, n, k, oa, ob)
+                rows = rng.choice(m, size=6, replace=False)
+                Asub = A[rows] if oa == "N" else np.ascontiguousarray(A[:, rows])
+                err = O.gemm_error_units(C[rows], O.gemm(al, oa, Asub, ob, B, wide=True), Asub, B, k, al)
+                assert err <= TOL_UNITS[O.F64], (m, n, k, oa, ob, err)
+    finally:
+        ab.set_tuning(ab.TUNE_STREAMK, -1)
+
+
 def test_launches_are_counted(cuda):
     import torch
     import accblas_b200 as ab
