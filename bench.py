@@ -266,7 +266,11 @@ def run_single(args):
     for _ in range(e2e_steps):
         e2e_step()                                   # synchronous: returns with C in host memory
     e2e_s = (time.perf_counter() - t) / e2e_steps
-    assert torch.equal(Ch[rows], C[rows].cpu()), "e2e result differs from the device-resident result"
+    # the host path multiplies sub-blocks (other tile counts, other K walking order per tile): same tolerance
+    # units as the parity check, a hundredth of the bound
+    d_units = float(torch.linalg.norm(Ch[rows] - C[rows].cpu())) / (
+        n * 2.0 ** -53 * float(torch.linalg.norm(A[rows])) * float(torch.linalg.norm(B)))
+    assert d_units <= 0.01, f"e2e result differs from the device-resident result by {d_units} units"
     del Ah, Bh, Ch
 
     peak, peak_src = dmma_peak_live()
