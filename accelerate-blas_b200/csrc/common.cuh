@@ -40,6 +40,20 @@ inline int check_launch(const char *where) {
         if (_s != ACCBLAS_OK) return _s;                                   \
     } while (0)
 
+// cudaFuncSetAttribute (dynamic shared memory opt-in) is per DEVICE: a `static thread_local AttrOnce` beside each
+// kernel instantiation remembers on which devices this thread has already done it, so a thread that serves
+// several GPUs sets the attribute once on each.
+struct AttrOnce {
+    uint64_t mask = 0;
+    bool need() {
+        int d = 0;
+        if (cudaGetDevice(&d) != cudaSuccess || d < 0 || d > 63) return true;
+        if ((mask >> d) & 1u) return false;
+        mask |= 1ull << d;
+        return true;
+    }
+};
+
 int sm_count();                                  // SMs of the current device (cached per device)
 int device_check();                              // ACCBLAS_OK iff current device is CC 10.x
 

@@ -674,10 +674,9 @@ int launch_dgemm_tile(const GemmArgs &g)
         !tma::make_2d(&mapB, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 8, g.B, (uint64_t)g.rowsB, (uint64_t)g.colsB,
                       BKM ? BN : BK, 16, (uint64_t)g.ldb * 8))
         return cuda_fail(cudaErrorInvalidValue, "cuTensorMapEncodeTiled");
-    static thread_local bool attr_done = false;
-    if (!attr_done) {
+    static thread_local AttrOnce attr_once;
+    if (attr_once.need()) {
         ACC_CUDA(cudaFuncSetAttribute(dgemm_dmma_kernel<AK, BKM, TL>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-        attr_done = true;
     }
     DgemmParams p;
     p.m = g.m; p.n = g.n; p.k = g.k; p.ldc = g.ldc;
@@ -704,10 +703,9 @@ int launch_dgemm_streamk(const GemmArgs &g)
         !tma::make_2d(&mapB, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 8, g.B, (uint64_t)g.rowsB, (uint64_t)g.colsB,
                       BKM ? TL::BN : BK, 16, (uint64_t)g.ldb * 8))
         return cuda_fail(cudaErrorInvalidValue, "cuTensorMapEncodeTiled");
-    static thread_local bool attr_done = false;
-    if (!attr_done) {
+    static thread_local AttrOnce attr_once;
+    if (attr_once.need()) {
         ACC_CUDA(cudaFuncSetAttribute(dgemm_dmma_streamk_kernel<AK, BKM>, cudaFuncAttributeMaxDynamicSharedMemorySize, TL::SMEM_BYTES));
-        attr_done = true;
     }
     StreamKParams q;
     DgemmParams &p = q.p;
@@ -783,10 +781,9 @@ int launch_zgemm_tile(const GemmArgs &g)
         !tma::make_2d(&mapB, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 8, g.B, (uint64_t)g.rowsB, 2 * (uint64_t)g.colsB,
                       BKM ? ZBN : ZBK, 16, (uint64_t)g.ldb * 16))
         return cuda_fail(cudaErrorInvalidValue, "cuTensorMapEncodeTiled");
-    static thread_local bool attr_done = false;
-    if (!attr_done) {
+    static thread_local AttrOnce attr_once;
+    if (attr_once.need()) {
         ACC_CUDA(cudaFuncSetAttribute(zgemm_dmma_kernel<AK, BKM, CA, CB, TL>, cudaFuncAttributeMaxDynamicSharedMemorySize, TL::SMEM_BYTES));
-        attr_done = true;
     }
     ZgemmParams p;
     p.m = g.m; p.n = g.n; p.k = g.k; p.ldc = g.ldc;

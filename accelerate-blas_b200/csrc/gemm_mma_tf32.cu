@@ -427,10 +427,9 @@ int launch_sgemm_mma(const GemmArgs &g)
     if (!tma::make_2d(&mapA, F, 4, g.A, (uint64_t)g.rowsA, (uint64_t)g.colsA, AK ? BM : 32, 32, (uint64_t)g.lda * 4) ||
         !tma::make_2d(&mapB, F, 4, g.B, (uint64_t)g.rowsB, (uint64_t)g.colsB, BKM ? BN : 32, 32, (uint64_t)g.ldb * 4))
         return cuda_fail(cudaErrorInvalidValue, "cuTensorMapEncodeTiled");
-    static thread_local bool attr_done = false;
-    if (!attr_done) {
+    static thread_local AttrOnce attr_once;
+    if (attr_once.need()) {
         ACC_CUDA(cudaFuncSetAttribute(sgemm_mma_kernel<AK, BKM, TL>, cudaFuncAttributeMaxDynamicSharedMemorySize, TL::SMEM_BYTES));
-        attr_done = true;
     }
     SgemmMmaParams p;
     p.m = g.m; p.n = g.n; p.k = g.k; p.ldc = g.ldc;
@@ -454,10 +453,9 @@ int launch_cgemm_mma(const GemmArgs &g)
     if (!tma::make_2d(&mapA, F, 4, g.A, (uint64_t)g.rowsA, 2 * (uint64_t)g.colsA, AK ? BM : 16, 32, (uint64_t)g.lda * 8) ||
         !tma::make_2d(&mapB, F, 4, g.B, (uint64_t)g.rowsB, 2 * (uint64_t)g.colsB, BKM ? BN : 16, 32, (uint64_t)g.ldb * 8))
         return cuda_fail(cudaErrorInvalidValue, "cuTensorMapEncodeTiled");
-    static thread_local bool attr_done = false;
-    if (!attr_done) {
+    static thread_local AttrOnce attr_once;
+    if (attr_once.need()) {
         ACC_CUDA(cudaFuncSetAttribute(cgemm_mma_kernel<AK, BKM, CA, CB, TL>, cudaFuncAttributeMaxDynamicSharedMemorySize, TL::SMEM_BYTES));
-        attr_done = true;
     }
     SgemmMmaParams p;
     p.m = g.m; p.n = g.n; p.k = g.k; p.ldc = g.ldc;

@@ -570,10 +570,9 @@ int launch_tc(const GemmArgs &g, const TcPlan &t, float *ahi, float *alo, float 
         !tma::make_2d(&mBhi, F, 4, bhi, (uint64_t)t.RB, (uint64_t)t.pitch, TBN, TBK, pitch_b) ||
         !tma::make_2d(&mBlo, F, 4, blo, (uint64_t)t.RB, (uint64_t)t.pitch, TBN, TBK, pitch_b))
         return cuda_fail(cudaErrorInvalidValue, "cuTensorMapEncodeTiled");
-    static thread_local bool attr_done = false;
-    if (!attr_done) {
+    static thread_local AttrOnce attr_once;
+    if (attr_once.need()) {
         ACC_CUDA(cudaFuncSetAttribute(sgemm_tf32x3_kernel<TBN, STAGES, KCB>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM));
-        attr_done = true;
     }
     SgemmParams p;
     p.M = t.M; p.N = t.N; p.Kp = t.pitch;      // padding columns are zero-filled by pack_split
