@@ -353,7 +353,8 @@ size_t accblas_gemm_workspace_bytes(int dtype, int opA, int opB, int64_t rowsA, 
     g.rowsA = rowsA; g.colsA = colsA; g.rowsB = rowsB; g.colsB = colsB;
     if (derive_gemm(g) != ACCBLAS_OK) return 0;
     const Family f = pick_family(g);
-    return f == FAM_TC ? sgemm_tc_workspace(g) : f == FAM_Z3M ? zgemm_3m_workspace(g) : f == FAM_C3M ? cgemm_3m_workspace(g) : 0;
+    return f == FAM_TC ? sgemm_tc_workspace(g) : f == FAM_Z3M ? zgemm_3m_workspace(g) : f == FAM_C3M ? cgemm_3m_workspace(g)
+         : f == FAM_DMMA ? dgemm_dmma_workspace(g) : 0;
 }
 
 static int gemv_entry(accblas_stream_t stream, int dtype, int opA, int64_t rowsA, int64_t colsA,

@@ -866,6 +866,13 @@ bool dgemm_dmma_eligible(const GemmArgs &g)
     return true;
 }
 
+size_t dgemm_dmma_workspace(const GemmArgs &g)
+{
+    if (g.dtype != ACCBLAS_F64 || !want_streamk(g.m, g.n, g.k, 0.0)) return 0;
+    const long long total = ((g.m + 127) / 128) * ((g.n + 127) / 128) * ((g.k + BK - 1) / BK);
+    return (size_t)std::min<long long>(sm_count(), total) * 128 * 128 * 8 + 4096;     // accumulator slots + flags
+}
+
 int dgemm_dmma(const GemmArgs &g)
 {
     const bool ak = g.opA == ACCBLAS_OP_N, bk = g.opB != ACCBLAS_OP_N;
