@@ -316,6 +316,11 @@ struct SgemmParams {
     Alpha<float2> alpha;   // (re, im); im = 0 for real
     int cplx;              // 1: columns are (re,im) pairs, alpha is complex
     int tiles_m, tiles_n;
+    // plane batching (3M): the grid holds `planes` independent products of the same extents whose operands are
+    // stacked along the row dimension of the tensor maps; 0 tiles_per_plane = a single product
+    int tiles_per_plane;
+    int plane_rows_a, plane_rows_b;      // row offset of plane p in the A / B maps: p * plane_rows_*
+    int64_t plane_stride_c;              // floats between the C planes
 };
 
 template <int TBN, int STAGES>
@@ -345,17 +350,23 @@ sgemm_tf32x3_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_con
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
     constexpr int GROUP = 8;
-    int tile_m, tile_n;
+    int tile_m, tile_n, plane = 0, bid;
     {
+        bid = blockIdx.x;
+        if (p.tiles_per_plane > 0) {
+            plane = bid / p.tiles_per_plane;
+            bid -= plane * p.tiles_per_plane;
+        }
         const int per_group = GROUP * p.tiles_n;
-        const int grp = blockIdx.x / per_group;
+        const int grp = bid / per_group;
         const int first_m = grp * GROUP;
         const int gsz = min(p.tiles_m - first_m, GROUP);
-        const int in_grp = blockIdx.x - grp * per_group;
+        const int in_grp = bid - grp * per_group;
         tile_m = first_m + in_grp % gsz;
         tile_n = in_grp / gsz;
     }
     const int m0 = tile_m * TBM, n0 = tile_n * TBN;
+    const int ma = m0 + plane * p.plane_rows_a, nb = n0 + plane * p.plane_rows_b;   // rows in the stacked maps
     const int kblocks = (int)((p.Kp + TBK - 1) / TBK);
     const int chunks = (kblocks + KCB - 1) / KCB;
 
@@ -390,10 +401,10 @@ sgemm_tf32x3_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_con
                 const uint32_t st = smem_base + s * Cfg::STAGE;
                 tma::mbar_expect_tx(full, Cfg::STAGE);
                 const int k0 = kb * TBK;
-                tma::load_2d(st, &mapAhi, full, k0, m0);
-                tma::load_2d(st + Cfg::A_TILE, &mapAlo, full, k0, m0);
-                tma::load_2d(st + 2 * Cfg::A_TILE, &mapBhi, full, k0, n0);
-                tma::load_2d(st + 2 * Cfg::A_TILE + Cfg::B_TILE, &mapBlo, full, k0, n0);
+                tma::load_2d(st, &mapAhi, full, k0, ma);
+                tma::load_2d(st + Cfg::A_TILE, &mapAlo, full, k0, ma);
+                tma::load_2d(st + 2 * Cfg::A_TILE, &mapBhi, full, k0, nb);
+                tma::load_2d(st + 2 * Cfg::A_TILE + Cfg::B_TILE, &mapBlo, full, k0, nb);
             }
         } else if (warp == 1) {
             // ================================ MMA issuer ================================
@@ -475,7 +486,7 @@ sgemm_tf32x3_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_con
         const float2 al = p.alpha.dev ? (p.cplx ? *p.alpha.dev : make_float2(*reinterpret_cast<const float *>(p.alpha.dev), 0.f))
                                       : p.alpha.v;
         if (row < p.M) {
-            float *crow = p.C + row * p.ldc;
+            float *crow = p.C + plane * p.plane_stride_c + row * p.ldc;
             const int64_t col0 = n0 + h * HALF;
             const bool vec4 = (p.ldc & 3) == 0 && ((reinterpret_cast<uintptr_t>(p.C) & 15u) == 0) && col0 + HALF <= p.N;
             if (p.cplx) {
@@ -539,7 +550,7 @@ TcPlan make_plan(const GemmArgs &g)
 // outweigh its tensor time (128 * TBN * 8 multiply-adds).
 // The narrow tiles fill the GPU for the mid-size products (1024^3 is 32 tiles of 128 x 256 on 148 SMs)
 // and trim the partial last wave of the large ones.
-int pick_tc_tile(const TcPlan &t)
+int pick_tc_tile(const TcPlan &t, int planes = 1)
 {
     const int forced = g_tuning[ACCBLAS_TUNE_TC_TILE];
     if (forced >= 0 && forced <= 2) return forced;
@@ -550,7 +561,7 @@ int pick_tc_tile(const TcPlan &t)
     int best = 0;
     double best_cost = 0.0;
     for (int c = 0; c < 3; ++c) {
-        const int64_t tiles = tm * ((t.N + tbn[c] - 1) / tbn[c]);
+        const int64_t tiles = tm * ((t.N + tbn[c] - 1) / tbn[c]) * planes;
         // per tile: the K loop plus a prologue / epilogue worth ~40 K-steps of the widest tile
         const double cost = (double)((tiles + sms - 1) / sms) * (step_cost[c] * (double)(t.pitch / 8) + 40.0 * 134.0);
         if (c == 0 || cost < best_cost * 0.97) { best = c; best_cost = cost; }
@@ -559,16 +570,20 @@ int pick_tc_tile(const TcPlan &t)
 }
 
 template <int TBN, int STAGES, int KCB>
-int launch_tc(const GemmArgs &g, const TcPlan &t, float *ahi, float *alo, float *bhi, float *blo)
+int launch_tc(const GemmArgs &g, const TcPlan &t, float *ahi, float *alo, float *bhi, float *blo,
+              int planes = 1, int plane_rows_a = 0, int plane_rows_b = 0, int64_t plane_stride_c = 0)
 {
     using Cfg = TcCfg<TBN, STAGES>;
     CUtensorMap mAhi, mAlo, mBhi, mBlo;
     const uint64_t pitch_b = (uint64_t)t.pitch * 4;
     const CUtensorMapDataType F = CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
-    if (!tma::make_2d(&mAhi, F, 4, ahi, (uint64_t)t.RA, (uint64_t)t.pitch, TBM, TBK, pitch_b) ||
-        !tma::make_2d(&mAlo, F, 4, alo, (uint64_t)t.RA, (uint64_t)t.pitch, TBM, TBK, pitch_b) ||
-        !tma::make_2d(&mBhi, F, 4, bhi, (uint64_t)t.RB, (uint64_t)t.pitch, TBN, TBK, pitch_b) ||
-        !tma::make_2d(&mBlo, F, 4, blo, (uint64_t)t.RB, (uint64_t)t.pitch, TBN, TBK, pitch_b))
+    // stacked planes: the maps cover all of them (plane p starts at row p * plane_rows_*)
+    const uint64_t rows_a = planes > 1 ? (uint64_t)planes * (uint64_t)plane_rows_a : (uint64_t)t.RA;
+    const uint64_t rows_b = planes > 1 ? (uint64_t)planes * (uint64_t)plane_rows_b : (uint64_t)t.RB;
+    if (!tma::make_2d(&mAhi, F, 4, ahi, rows_a, (uint64_t)t.pitch, TBM, TBK, pitch_b) ||
+        !tma::make_2d(&mAlo, F, 4, alo, rows_a, (uint64_t)t.pitch, TBM, TBK, pitch_b) ||
+        !tma::make_2d(&mBhi, F, 4, bhi, rows_b, (uint64_t)t.pitch, TBN, TBK, pitch_b) ||
+        !tma::make_2d(&mBlo, F, 4, blo, rows_b, (uint64_t)t.pitch, TBN, TBK, pitch_b))
         return cuda_fail(cudaErrorInvalidValue, "cuTensorMapEncodeTiled");
     static thread_local AttrOnce attr_once;
     if (attr_once.need()) {
@@ -584,8 +599,10 @@ int launch_tc(const GemmArgs &g, const TcPlan &t, float *ahi, float *alo, float 
                                             p.cplx ? static_cast<const float *>(g.alpha)[1] : 0.f), nullptr};
     p.tiles_m = (int)((t.M + TBM - 1) / TBM);
     p.tiles_n = (int)((t.N + TBN - 1) / TBN);
-    const int64_t tiles = (int64_t)p.tiles_m * p.tiles_n;
+    const int64_t tiles = (int64_t)p.tiles_m * p.tiles_n * planes;
     if (tiles > 0x7fffffff) return ACCBLAS_ERR_SHAPE;
+    p.tiles_per_plane = planes > 1 ? p.tiles_m * p.tiles_n : 0;
+    p.plane_rows_a = plane_rows_a; p.plane_rows_b = plane_rows_b; p.plane_stride_c = plane_stride_c;
     sgemm_tf32x3_kernel<TBN, STAGES, KCB><<<(unsigned)tiles, TTHREADS, Cfg::SMEM, g.stream>>>(mAhi, mAlo, mBhi, mBlo, p);
     return check_launch("sgemm_tf32x3_kernel");
 }
@@ -594,6 +611,7 @@ int launch_tc(const GemmArgs &g, const TcPlan &t, float *ahi, float *alo, float 
 struct Tc3Plan {
     TcPlan t;              // one real m x n x k product
     int64_t ldt;           // row pitch of the T planes (floats)
+    int64_t rows_a, rows_b; // padded rows of one A / B plane
     size_t plane_t;
 };
 
@@ -603,8 +621,12 @@ Tc3Plan make_plan3(const GemmArgs &g)
     q.t.RA = g.m; q.t.RB = g.n; q.t.Kp = g.k;
     q.t.pitch = (g.k + 31) / 32 * 32;
     q.t.M = g.m; q.t.N = g.n;
-    q.t.plane_a = ((size_t)g.m * (size_t)q.t.pitch * 4 + 1023) / 1024 * 1024;
-    q.t.plane_b = ((size_t)g.n * (size_t)q.t.pitch * 4 + 1023) / 1024 * 1024;
+    // planes are stacked along the rows of one tensor map per operand: pad the row counts to the largest tile so a
+    // TMA box never runs into the next plane's valid rows (rows past m / n only feed outputs that are not stored)
+    q.rows_a = (g.m + 127) / 128 * 128;
+    q.rows_b = (g.n + 255) / 256 * 256;
+    q.t.plane_a = (size_t)q.rows_a * (size_t)q.t.pitch * 4;
+    q.t.plane_b = (size_t)q.rows_b * (size_t)q.t.pitch * 4;
     q.ldt = (g.n + 3) / 4 * 4;
     q.plane_t = ((size_t)g.m * (size_t)q.ldt * 4 + 1023) / 1024 * 1024;
     return q;
@@ -630,8 +652,8 @@ int cgemm_3m_run(const GemmArgs &g)
     b.conj_sign = g.opB == ACCBLAS_OP_H ? -1.f : 1.f;
     b.R = g.n; b.Kp = g.k; b.pitch = q.t.pitch;
     for (int p = 0; p < 3; ++p) {
-        a.hi[p] = reinterpret_cast<float *>(wa + (2 * p) * pa); a.lo[p] = reinterpret_cast<float *>(wa + (2 * p + 1) * pa);
-        b.hi[p] = reinterpret_cast<float *>(wb + (2 * p) * pb); b.lo[p] = reinterpret_cast<float *>(wb + (2 * p + 1) * pb);
+        a.hi[p] = reinterpret_cast<float *>(wa + p * pa); a.lo[p] = reinterpret_cast<float *>(wa + (3 + p) * pa);
+        b.hi[p] = reinterpret_cast<float *>(wb + p * pb); b.lo[p] = reinterpret_cast<float *>(wb + (3 + p) * pb);
     }
     int s = ACCBLAS_OK;
     {
@@ -643,15 +665,18 @@ int cgemm_3m_run(const GemmArgs &g)
         }
     }
     static const float one = 1.f;
-    const int tile = pick_tc_tile(q.t);
-    for (int p = 0; p < 3 && s == ACCBLAS_OK; ++p) {
+    const int tile = pick_tc_tile(q.t, 3);
+    if (s == ACCBLAS_OK) {
+        // ONE launch for the three products (planes stacked in the maps): 3 x tiles share the waves
         GemmArgs h = g;
         h.dtype = ACCBLAS_F32;
         h.alpha = &one; h.alpha_dev = false;
-        h.C = wt + p * pt; h.ldc = q.ldt;
-        s = tile == 1 ? launch_tc<128, 3, 2>(h, q.t, a.hi[p], a.lo[p], b.hi[p], b.lo[p])
-          : tile == 2 ? launch_tc<64, 4, 2>(h, q.t, a.hi[p], a.lo[p], b.hi[p], b.lo[p])
-                      : launch_tc<256, 2, 2>(h, q.t, a.hi[p], a.lo[p], b.hi[p], b.lo[p]);
+        h.C = wt; h.ldc = q.ldt;
+        const int ra = (int)q.rows_a, rb = (int)q.rows_b;
+        const int64_t sc = (int64_t)(pt / 4);
+        s = tile == 1 ? launch_tc<128, 3, 2>(h, q.t, a.hi[0], a.lo[0], b.hi[0], b.lo[0], 3, ra, rb, sc)
+          : tile == 2 ? launch_tc<64, 4, 2>(h, q.t, a.hi[0], a.lo[0], b.hi[0], b.lo[0], 3, ra, rb, sc)
+                      : launch_tc<256, 2, 2>(h, q.t, a.hi[0], a.lo[0], b.hi[0], b.lo[0], 3, ra, rb, sc);
     }
     if (s == ACCBLAS_OK) {
         Combine3Args c{};
