@@ -127,3 +127,13 @@ def test_no_cpu_fallback_in_product():
                 m = re.search(r"oracle|openblas|\bcblas_|cublas", src, re.I)
                 assert not m, f"{path}: {m.group(0)}"
     assert seen >= 8
+
+
+def test_cpp_mirror_builds_and_links():
+    """include/accblas_b200.hpp (the C++ host-side mirror of the reference's operator interface) compiles with a
+    plain g++ and links against the library; running it needs a GPU (tests/test_parity_gpu.py)."""
+    import subprocess
+    cpp = os.path.join(ROOT, "tests", "cpp")
+    subprocess.check_call(["make", "-s", "-C", cpp])
+    out = subprocess.run(["ldd", os.path.join(cpp, "hpp_check")], capture_output=True, text=True).stdout
+    assert "libaccblas_b200.so" in out and "not found" not in out.split("libaccblas_b200.so")[1].splitlines()[0]

@@ -590,6 +590,18 @@ def test_dgemm_streamk(cuda):
         ab.set_tuning(ab.TUNE_STREAMK, -1)
 
 
+def test_cpp_host_mirror(cuda):
+    """The C++ mirror of the reference's interface (include/accblas_b200.hpp) through its own test program:
+    haddock known answers, random gemm / gemv / dot over 4 dtypes x N/T/H, Level-1 extras, error behaviour."""
+    import os
+    import subprocess
+    exe = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "cpp", "hpp_check")
+    if not os.path.exists(exe):
+        subprocess.check_call(["make", "-s", "-C", os.path.dirname(exe)])
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "hpp_check ok" in r.stdout, r.stdout[-3000:] + r.stderr[-2000:]
+
+
 def test_launches_are_counted(cuda):
     import torch
     import accblas_b200 as ab
