@@ -318,6 +318,56 @@ int accblas_gemm_ld(accblas_stream_t stream, int dtype, int opA, int opB, int64_
     return gemm_device(g);
 }
 
+// Strided batch of independent products with identical shapes and flags.  Small products (the ones the SIMT
+// kernel serves) run as ONE launch with the batch on gridDim.z; products a tensor family takes are enqueued one
+// after the other on the stream (each already fills the GPU).
+int accblas_gemm_strided_batched(accblas_stream_t stream, int dtype, int opA, int opB, int64_t rowsA, int64_t colsA,
+                                 int64_t rowsB, int64_t colsB, const void *alpha_host, const void *A, int64_t strideA,
+                                 const void *B, int64_t strideB, void *C, int64_t strideC, int64_t batch)
+{
+    if (batch < 0 || strideA < 0 || strideB < 0 || strideC < 0) return ACCBLAS_ERR_SHAPE;
+    GemmArgs g{};
+    g.dtype = dtype; g.opA = opA; g.opB = opB;
+    g.rowsA = rowsA; g.colsA = colsA; g.rowsB = rowsB; g.colsB = colsB;
+    g.alpha = alpha_host; g.A = A; g.B = B; g.C = C;
+    g.stream = static_cast<cudaStream_t>(stream);
+    ACC_TRY(derive_gemm(g));
+    if (batch == 0 || g.m == 0 || g.n == 0) return ACCBLAS_OK;
+    if (batch > 1 && strideC < g.m * g.n) return ACCBLAS_ERR_ALIAS;           // outputs of the batch must not overlap
+    if (g.k > 0 && ((strideA != 0 && strideA < g.rowsA * g.colsA) || (strideB != 0 && strideB < g.rowsB * g.colsB)))
+        return ACCBLAS_ERR_SHAPE;
+    const size_t es = elem_size(dtype);
+    auto at = [&](const void *p, int64_t stride, int64_t b) {
+        return p ? static_cast<const void *>(static_cast<const char *>(p) + es * (size_t)stride * (size_t)b) : p;
+    };
+    if (batch > 1 && g.k > 0 && g.A && g.B && g.C && g.alpha && g_gemm_path != 2 && pick_family(g) == FAM_GENERIC &&
+        (double)g.m * (double)g.n * (double)g.k < 48.0 * 48.0 * 48.0) {
+        // every product of the batch is tiny: one z-batched launch per 65535 products
+        ACC_TRY(device_check());
+        const size_t spanC = es * ((size_t)strideC * (size_t)(batch - 1) + (size_t)g.m * (size_t)g.n);
+        if (overlaps(g.C, spanC, g.A, es * ((size_t)strideA * (size_t)(batch - 1) + span(g.rowsA, g.colsA, g.lda))) ||
+            overlaps(g.C, spanC, g.B, es * ((size_t)strideB * (size_t)(batch - 1) + span(g.rowsB, g.colsB, g.ldb))))
+            return ACCBLAS_ERR_ALIAS;
+        for (int64_t b0 = 0; b0 < batch; b0 += 65535) {
+            GemmArgs h = g;
+            h.batch = std::min<int64_t>(65535, batch - b0);
+            h.strideA = strideA; h.strideB = strideB; h.strideC = strideC;
+            h.A = at(A, strideA, b0); h.B = at(B, strideB, b0); h.C = const_cast<void *>(at(C, strideC, b0));
+            ACC_TRY(gemm_generic(h));
+        }
+        return ACCBLAS_OK;
+    }
+    for (int64_t b = 0; b < batch; ++b) {
+        GemmArgs h{};
+        h.dtype = dtype; h.opA = opA; h.opB = opB;
+        h.rowsA = rowsA; h.colsA = colsA; h.rowsB = rowsB; h.colsB = colsB;
+        h.alpha = alpha_host; h.stream = g.stream;
+        h.A = at(A, strideA, b); h.B = at(B, strideB, b); h.C = const_cast<void *>(at(C, strideC, b));
+        ACC_TRY(gemm_device(h));
+    }
+    return ACCBLAS_OK;
+}
+
 const char *accblas_gemm_kernel_name(int dtype, int opA, int opB, int64_t rowsA, int64_t colsA,
                                      int64_t rowsB, int64_t colsB)
 {

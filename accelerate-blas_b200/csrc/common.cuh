@@ -165,6 +165,9 @@ struct GemmArgs {
     const void *A, *B;
     void *C;
     cudaStream_t stream;
+    // strided batch (accblas_gemm_strided_batched): `batch` independent products, operand b of the batch at
+    // base + b * stride (elements; stride 0 = the same operand for every product).  batch <= 1: one product.
+    int64_t batch, strideA, strideB, strideC;
 };
 
 int gemm_device(GemmArgs &g);                         // api.cu : validate + dispatch one device-resident product

@@ -26,8 +26,12 @@ template <typename T, bool TA, bool TB>
 __global__ void __launch_bounds__(NT)
 gemm_generic_kernel(int64_t m, int64_t n, int64_t k, int64_t rowsA, int64_t colsA, int64_t rowsB,
                     int64_t colsB, int64_t lda, int64_t ldb, int64_t ldc, bool conjA, bool conjB, Alpha<T> alpha_,
-                    const T *__restrict__ A, const T *__restrict__ B, T *__restrict__ C)
+                    const T *__restrict__ A, const T *__restrict__ B, T *__restrict__ C,
+                    int64_t strideA, int64_t strideB, int64_t strideC)
 {
+    A += (int64_t)blockIdx.z * strideA;                        // strided batch: one product per grid plane
+    B += (int64_t)blockIdx.z * strideB;
+    C += (int64_t)blockIdx.z * strideC;
     const T alpha = alpha_.get();
     __shared__ T As[BK][BM + 1];
     __shared__ T Bs[BK][BN + 1];
@@ -96,14 +100,15 @@ int launch_typed(const GemmArgs &g)
     const bool ca = Scalar<T>::cplx && g.opA == ACCBLAS_OP_H;
     const bool cb = Scalar<T>::cplx && g.opB == ACCBLAS_OP_H;
     const Alpha<T> alpha = make_alpha<T>(g.alpha, g.alpha_dev);
-    dim3 grid((unsigned)((g.n + BN - 1) / BN), (unsigned)((g.m + BM - 1) / BM));
-    if (grid.y > 65535u) return ACCBLAS_ERR_SHAPE;
+    const int64_t batch = g.batch > 1 ? g.batch : 1;
+    dim3 grid((unsigned)((g.n + BN - 1) / BN), (unsigned)((g.m + BM - 1) / BM), (unsigned)batch);
+    if (grid.y > 65535u || batch > 65535) return ACCBLAS_ERR_SHAPE;      // callers chunk larger batches
     const T *A = static_cast<const T *>(g.A), *B = static_cast<const T *>(g.B);
     T *C = static_cast<T *>(g.C);
 #define GO(TA_, TB_)                                                                             \
     gemm_generic_kernel<T, TA_, TB_><<<grid, NT, 0, g.stream>>>(g.m, g.n, g.k, g.rowsA, g.colsA,   \
                                                                 g.rowsB, g.colsB, g.lda, g.ldb, g.ldc, ca, cb,  \
-                                                                alpha, A, B, C)
+                                                                alpha, A, B, C, g.strideA, g.strideB, g.strideC)
     if (!ta && !tb) GO(false, false);
     else if (!ta && tb) GO(false, true);
     else if (ta && !tb) GO(true, false);

@@ -34,7 +34,7 @@ import numpy as np
 from . import _ffi
 from ._ffi import AccblasError, lib  # noqa: F401
 
-__all__ = ["N", "T", "H", "gemm", "gemv", "dotu", "dotc", "sdot", "asum", "amax", "amin", "mXm", "mXv", "vXm", "dot", "outer",
+__all__ = ["N", "T", "H", "gemm", "gemm_batched", "gemv", "dotu", "dotc", "sdot", "asum", "amax", "amin", "mXm", "mXv", "vXm", "dot", "outer",
            "AccblasError", "kernel_name", "launch_count", "set_gemm_path", "set_tuning", "version"]
 
 # Transpose -- Type.hs:78-90
@@ -189,6 +189,36 @@ def gemm(alpha, opA, A, opB, B, out=None):
     st = L.accblas_gemm_host(None, code, oa, ob, A.shape[0], A.shape[1], B.shape[0], B.shape[1],
                              al, _ptr(A), _ptr(B), _ptr(C))
     _ffi.check(st, "accblas_gemm_host")
+    return C
+
+
+def gemm_batched(alpha, opA, A, opB, B):
+    """``C[b] = alpha * op(A[b]) * op(B[b])`` for a stack of products (accblas_gemm_strided_batched).
+
+    A, B: contiguous CUDA tensors of rank 3 (batch, rows, cols) -- or rank 2, which is broadcast over the batch
+    (stride 0).  Not an operator of the reference: Accelerate has no batched product.
+    """
+    oa, ob = _op(opA), _op(opB)
+    code = _code(A)
+    torch = _torch()
+    A = _dev_operand(A, code, A.dim(), "gemm_batched: A")
+    B = _dev_operand(B, code, B.dim(), "gemm_batched: B")
+    if A.dim() not in (2, 3) or B.dim() not in (2, 3) or (A.dim() == 2 and B.dim() == 2):
+        raise ValueError("gemm_batched: operands must be rank 3 (at most one of them rank 2)")
+    batch = A.shape[0] if A.dim() == 3 else B.shape[0]
+    if A.dim() == 3 and B.dim() == 3 and A.shape[0] != B.shape[0]:
+        raise ValueError("gemm_batched: batch extents differ")
+    ra, ca = A.shape[-2], A.shape[-1]
+    rb, cb = B.shape[-2], B.shape[-1]
+    m = ra if oa == N else ca
+    n = cb if ob == N else rb
+    al_keep, al = _alpha_buf(alpha, code)
+    with torch.cuda.device(A.device):
+        C = torch.empty((batch, m, n), dtype=A.dtype, device=A.device)
+        st = lib().accblas_gemm_strided_batched(_stream(A), code, oa, ob, ra, ca, rb, cb, al,
+                                                _ptr(A), ra * ca if A.dim() == 3 else 0,
+                                                _ptr(B), rb * cb if B.dim() == 3 else 0, _ptr(C), m * n, batch)
+    _ffi.check(st, "accblas_gemm_strided_batched")
     return C
 
 

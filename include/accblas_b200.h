@@ -95,6 +95,16 @@ int accblas_gemm_ld(accblas_stream_t stream, int dtype, int opA, int opB,
                     const void *alpha_host, const void *A, int64_t lda, const void *B, int64_t ldb,
                     void *C, int64_t ldc);
 
+/* `batch` independent products with identical shapes and flags: operand b of the batch lives at
+ * base + b * stride (strides in ELEMENTS; strideA / strideB = 0 re-uses one operand for every product;
+ * strideC >= m * n).  The reference has no batched operator (Accelerate would express it as a fold over a
+ * rank-3 array and lose the foreign hook); this is SURVEY.md section 8(f) rank 3.  Tiny products run as one
+ * launch with the batch on the grid, larger ones are enqueued back to back on `stream`. */
+int accblas_gemm_strided_batched(accblas_stream_t stream, int dtype, int opA, int opB,
+                                 int64_t rowsA, int64_t colsA, int64_t rowsB, int64_t colsB,
+                                 const void *alpha_host, const void *A, int64_t strideA,
+                                 const void *B, int64_t strideB, void *C, int64_t strideC, int64_t batch);
+
 /* alpha in DEVICE memory, read by the kernel: the reference turns `alpha :: Exp e` into a device
  * Scalar (BLAS/Level3.hs:64) and then copies it back with a blocking indexRemote before every call
  * (LLVM/PTX/Level3.hs:81; LLVM/PTX/Level2.hs:99) because cuBLAS is used in host-pointer mode.  These

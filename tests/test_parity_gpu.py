@@ -602,6 +602,34 @@ def test_cpp_host_mirror(cuda):
     assert r.returncode == 0 and "hpp_check ok" in r.stdout, r.stdout[-3000:] + r.stderr[-2000:]
 
 
+@pytest.mark.parametrize("dt", DTYPES, ids=ids)
+def test_gemm_strided_batched(dt, cuda):
+    """accblas_gemm_strided_batched: tiny products (one z-batched SIMT launch), tensor-path products (enqueued
+    back to back), a broadcast operand (stride 0); every product against the oracle."""
+    import torch
+    import accblas_b200 as ab
+    rng = np.random.default_rng(9700 + dt)
+    for (batch, m, n, k, oa, ob) in [(7, 5, 9, 13, "N", "N"), (3, 33, 20, 17, "H", "T"), (4, 136, 72, 200, "T", "N")]:
+        As = [gemm_inputs(rng, dt, oa, ob, m, n, k) for _ in range(batch)]
+        al = As[0][0]
+        A = np.stack([a for (_, a, _) in As])
+        B = np.stack([b for (_, _, b) in As])
+        before = ab.launch_count()
+        C = host(ab.gemm_batched(al, oa, dev(A, cuda), ob, dev(B, cuda)))
+        launches = ab.launch_count() - before
+        assert launches == (1 if m * n * k < 48 ** 3 else batch), (launches, m, n, k)
+        for b in range(batch):
+            err = O.gemm_error_units(C[b], O.gemm(al, oa, A[b], ob, B[b], wide=True), A[b], B[b], k, al)
+            assert err <= TOL_UNITS_TF32X3, (O.NAMES[dt], b, m, n, k, err)
+        # B broadcast over the batch
+        Cb = host(ab.gemm_batched(al, oa, dev(A, cuda), ob, dev(B[0], cuda)))
+        for b in range(batch):
+            assert O.gemm_error_units(Cb[b], O.gemm(al, oa, A[b], ob, B[0], wide=True), A[b], B[0], k, al) <= TOL_UNITS_TF32X3
+    with pytest.raises(ab.AccblasError):
+        ab.gemm_batched(1, "N", torch.zeros((2, 3, 4), dtype=dev(A, cuda).dtype, device=cuda), "N",
+                        torch.zeros((2, 5, 2), dtype=dev(A, cuda).dtype, device=cuda))
+
+
 def test_launches_are_counted(cuda):
     import torch
     import accblas_b200 as ab
