@@ -292,3 +292,53 @@ def dot_sharded(x_local: torch.Tensor, y_local: torch.Tensor, *, conj: bool = Fa
     else:
         dist.all_reduce(d, op=dist.ReduceOp.SUM, group=group)
     return d.reshape(())
+
+
+# ----------------------------------------------------------------------------------------------------------
+# 2-D block sharding: for products whose operands do not fit one GPU.
+# The ranks form a pr x pc grid (rank = i * pc + j).  Rank (i, j) holds
+#   block (i, j) of op(A): rows [i * m/pr, ...) x K-columns [j * k/pc, ...)     in its STORED (pre-op) layout,
+#   block (i, j) of op(B): K-rows [i * k/pr, ...) x columns [j * n/pc, ...)     in its stored layout,
+# and receives block (i, j) of C.  C_ij = op(A)_(i,:) * op(B)_(:,j): the A blocks are all-gathered along the
+# process ROW, the B blocks along the process COLUMN, then ONE local product runs -- the library has no
+# beta = 1 accumulation (the reference never needs it: beta = 0, LLVM/PTX/Level3.hs:90), so instead of SUMMA's
+# K-step loop the whole K extent of the row / column panel is assembled first.  Per-rank memory is
+# m k / pr + k n / pc + m n / (pr pc) elements; the bytes moved are SUMMA's.
+# ----------------------------------------------------------------------------------------------------------
+_GRID_GROUPS = {}
+
+
+def _grid_groups(pr: int, pc: int, group=None):
+    """Row and column process groups of the pr x pc grid (every rank creates every group, as torch requires)."""
+    key = (pr, pc, id(group))
+    if key not in _GRID_GROUPS:
+        base = list(range(pr * pc)) if group is None else dist.get_process_group_ranks(group)
+        rows = [dist.new_group([base[i * pc + j] for j in range(pc)]) for i in range(pr)]
+        cols = [dist.new_group([base[i * pc + j] for i in range(pr)]) for j in range(pc)]
+        _GRID_GROUPS[key] = (rows, cols)
+    return _GRID_GROUPS[key]
+
+
+def gemm_2d(alpha, opA, A_blk: torch.Tensor, opB, B_blk: torch.Tensor, *, grid: Tuple[int, int], group=None,
+            local_gemm: Optional[Callable] = None) -> torch.Tensor:
+    """Block (i, j) of C = alpha * op(A) * op(B) on a pr x pc grid of ranks (see above); blocks must be equal-sized."""
+    pr, pc = grid
+    world = dist.get_world_size(group)
+    if pr * pc != world:
+        raise ValueError(f"gemm_2d: grid {pr} x {pc} does not match the {world} ranks")
+    opa = {"N": 0, "T": 1, "H": 2}.get(opA, opA)
+    opb = {"N": 0, "T": 1, "H": 2}.get(opB, opB)
+    local_gemm = local_gemm or _default_gemm()
+    rank = dist.get_rank(group)
+    i, j = divmod(rank, pc)
+    rows, cols = _grid_groups(pr, pc, group)
+    A_blk, B_blk = A_blk.contiguous(), B_blk.contiguous()
+    # op(A)_(i,:): K runs along the stored columns for N, along the stored rows for T / H
+    parts = [torch.empty_like(A_blk) for _ in range(pc)]
+    dist.all_gather(parts, A_blk, group=rows[i])
+    A_panel = torch.cat(parts, dim=1 if opa == 0 else 0) if pc > 1 else A_blk
+    # op(B)_(:,j): K runs along the stored rows for N, along the stored columns for T / H
+    parts = [torch.empty_like(B_blk) for _ in range(pr)]
+    dist.all_gather(parts, B_blk, group=cols[j])
+    B_panel = torch.cat(parts, dim=0 if opb == 0 else 1) if pr > 1 else B_blk
+    return local_gemm(alpha, opa, A_panel, opb, B_panel)

@@ -74,6 +74,60 @@ def _worker(rank, world, port, q):
         dist.destroy_process_group()
 
 
+def _worker_2d(rank, world, port, q):
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "accelerate-blas_b200", "python"))
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from accblas_b200 import mg
+        from oracle import oracle as O
+        rng = np.random.default_rng(43)          # same stream on every rank
+        res = {}
+        for (pr, pc) in [(2, 2), (1, 4), (4, 1)]:
+            i, j = divmod(rank, pc)
+            for (oa, ob, m, n, k) in [("N", "N", 48, 40, 64), ("T", "N", 16, 24, 32), ("N", "H", 8, 12, 16), ("H", "T", 20, 4, 8)]:
+                for dt in (O.F64, O.C64):
+                    A = O.uniform(rng, (m, k) if oa == "N" else (k, m), dt)
+                    B = O.uniform(rng, (k, n) if ob == "N" else (n, k), dt)
+                    mb, nb, ka, kb = m // pr, n // pc, k // pc, k // pr
+                    opA = A if oa == "N" else A.T            # index op(A) (m x k) / op(B) (k x n), then store pre-op
+                    opB = B if ob == "N" else B.T
+                    a_blk = opA[i * mb:(i + 1) * mb, j * ka:(j + 1) * ka]
+                    b_blk = opB[i * kb:(i + 1) * kb, j * nb:(j + 1) * nb]
+                    a_blk = np.ascontiguousarray(a_blk if oa == "N" else a_blk.T)
+                    b_blk = np.ascontiguousarray(b_blk if ob == "N" else b_blk.T)
+                    C = mg.gemm_2d(0.5, oa, torch.from_numpy(a_blk), ob, torch.from_numpy(b_blk), grid=(pr, pc),
+                                   local_gemm=_local_gemm)
+                    ref = O.gemm(0.5, oa, A, ob, B)[i * mb:(i + 1) * mb, j * nb:(j + 1) * nb]
+                    assert tuple(C.shape) == ref.shape
+                    res[f"gemm2d_{pr}x{pc}_{oa}{ob}_{dt}"] = float(np.linalg.norm(C.numpy() - ref)) / (
+                        (k + 2) * 2.0 ** -53 * 0.5 * np.linalg.norm(A) * np.linalg.norm(B))
+        q.put((rank, res))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(240)
+def test_world4_gloo_2d_blocks():
+    """mg.gemm_2d: 2 x 2, 1 x 4 and 4 x 1 grids, every op pair class, real and complex, blocks in stored layout."""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 31500 + os.getpid() % 2000
+    procs = [ctx.Process(target=_worker_2d, args=(r, 4, port, q)) for r in range(4)]
+    for p in procs:
+        p.start()
+    out = dict(q.get(timeout=200) for _ in range(4))
+    for p in procs:
+        p.join(30)
+        assert p.exitcode == 0
+    for rank, res in out.items():
+        assert len(res) == 24, (rank, len(res))
+        for kname, err in res.items():
+            assert err <= 2.0, (rank, kname, err)
+
+
 def test_row_panels():
     sys.path.insert(0, os.path.join(ROOT, "accelerate-blas_b200", "python"))
     from accblas_b200.mg import row_panels

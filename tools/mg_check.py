@@ -44,6 +44,26 @@ def main():
                         cases += 1
                     else:
                         assert C is None
+    # 2-D block sharding (mg.gemm_2d) on the grids this world size allows
+    for (pr, pc) in [(1, world), (world, 1)] + ([(2, world // 2)] if world >= 4 and world % 2 == 0 else []):
+        gi, gj = divmod(rank, pc)
+        for (oa, ob, mb, nb, kb) in [("N", "N", 256, 192, 128), ("T", "N", 130, 64, 96), ("H", "H", 64, 72, 200)]:
+            for dt, tdt in ((O.F64, torch.float64), (O.C32, torch.complex64)):
+                m, n, k = mb * pr, nb * pc, kb * pr * pc
+                A = O.uniform(rng, (m, k) if oa == "N" else (k, m), dt)
+                B = O.uniform(rng, (k, n) if ob == "N" else (n, k), dt)
+                opA = A if oa == "N" else A.T
+                opB = B if ob == "N" else B.T
+                a_blk = opA[gi * mb:(gi + 1) * mb, gj * (k // pc):(gj + 1) * (k // pc)]
+                b_blk = opB[gi * (k // pr):(gi + 1) * (k // pr), gj * nb:(gj + 1) * nb]
+                a_blk = np.ascontiguousarray(a_blk if oa == "N" else a_blk.T)
+                b_blk = np.ascontiguousarray(b_blk if ob == "N" else b_blk.T)
+                C = mg.gemm_2d(0.5, oa, torch.from_numpy(a_blk).to(dev), ob, torch.from_numpy(b_blk).to(dev), grid=(pr, pc))
+                ref = O.gemm(0.5, oa, A, ob, B)[gi * mb:(gi + 1) * mb, gj * nb:(gj + 1) * nb]
+                eps = 2.0 ** -53 if dt == O.F64 else 2.0 ** -24
+                err = float(np.linalg.norm(C.cpu().numpy() - ref)) / ((k + 2) * eps * 0.5 * np.linalg.norm(A) * np.linalg.norm(B))
+                assert err <= 2.0, ("gemm_2d", pr, pc, oa, ob, dt, err)
+                cases += 1
     # gemv / dot on pre-sharded operands
     m, n = 512 * world, 384
     A = O.uniform(rng, (m, n), O.F64)
