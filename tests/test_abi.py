@@ -50,6 +50,14 @@ def test_argument_validation_needs_no_gpu():
     assert L.accblas_gemv(None, 1, 1, 2, 3, p, p, p, 3, p) == 3
     assert L.accblas_dot(None, 1, 0, -1, p, p, p) == 3
     assert L.accblas_dot(None, 1, 0, 4, p, p, None) == 4
+    # strided batch: negative stride / batch, outputs that would overlap, operand stride inside one operand
+    sb = L.accblas_gemm_strided_batched
+    assert sb(None, 1, 0, 0, 2, 3, 3, 2, p, p, -1, p, 6, p, 4, 2) == 3
+    assert sb(None, 1, 0, 0, 2, 3, 3, 2, p, p, 6, p, 6, p, 4, -2) == 3
+    assert sb(None, 1, 0, 0, 2, 3, 3, 2, p, p, 6, p, 6, p, 3, 2) == 8           # strideC < m * n
+    assert sb(None, 1, 0, 0, 2, 3, 3, 2, p, p, 5, p, 6, p, 4, 2) == 3           # 0 < strideA < rowsA * colsA
+    assert sb(None, 1, 0, 0, 2, 3, 4, 2, p, p, 6, p, 8, p, 4, 2) == 3           # inner extents differ
+    assert sb(None, 1, 0, 0, 2, 3, 3, 2, p, p, 6, p, 6, p, 4, 0) == 0           # empty batch
 
 
 def test_kernel_selection_names():
