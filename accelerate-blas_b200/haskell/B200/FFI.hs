@@ -16,6 +16,7 @@ module Data.Array.Accelerate.Numeric.LinearAlgebra.LLVM.PTX.B200.FFI (
   c_accblas_gemm, c_accblas_gemv, c_accblas_dot,
   c_accblas_gemm_alpha_dev, c_accblas_gemv_alpha_dev,
   c_accblas_sdot, c_accblas_asum, c_accblas_amax, c_accblas_amin,
+  c_accblas_gemm_strided_batched, c_accblas_set_tuning,
 
 ) where
 
@@ -90,6 +91,20 @@ foreign import ccall unsafe "accblas_amax"
 
 foreign import ccall unsafe "accblas_amin"
   c_accblas_amin :: Ptr () -> CInt -> Int64 -> Ptr () -> Ptr () -> IO Status
+
+-- strided batch of equal-shaped products (no operator of the reference uses it yet; a future batched
+-- `(<>)` over rank-3 arrays would): strides in elements, stride 0 = the same operand for every product
+foreign import ccall unsafe "accblas_gemm_strided_batched"
+  c_accblas_gemm_strided_batched :: Ptr () -> CInt -> CInt -> CInt
+                                 -> Int64 -> Int64 -> Int64 -> Int64
+                                 -> Ptr () -> Ptr () -> Int64 -> Ptr () -> Int64    -- alpha(host) A strideA B strideB
+                                 -> Ptr () -> Int64 -> Int64 -> IO Status           -- C strideC batch
+
+-- per-thread kernel-choice knobs (accblas_tune_t); e.g. `c_accblas_set_tuning 7 0 >> c_accblas_set_tuning 9 0`
+-- pins complex products to 4M.  Haskell FFI calls may hop between OS threads: prefer ACCBLAS_TUNE in the
+-- environment (INTEGRATION.md) unless the caller runs in a bound thread.
+foreign import ccall unsafe "accblas_set_tuning"
+  c_accblas_set_tuning :: CInt -> CInt -> IO ()
 
 foreign import ccall unsafe "accblas_status_string"
   c_accblas_status_string :: CInt -> IO CString
