@@ -340,8 +340,6 @@ dgemm_dmma_streamk_kernel(const __grid_constant__ CUtensorMap mapA, const __grid
         for (int j = 0; j < NJ; ++j)
             b[j] = lds64(stage + (BKM ? offB[s] + j * 1024 : (offB[s] ^ ((j & 1) << 6)) + (j >> 1) * 2048));
     };
-    const bool vec = ((p.n | p.ldc) & 1) == 0;
-    const double alpha = p.alpha.get();
     constexpr int SLOT = BM * BN;                                  // doubles per workspace slot
     int g = 0;                                                    // K-blocks consumed so far (ring position)
     for (int it = it_begin; it < it_end;) {
@@ -405,6 +403,8 @@ dgemm_dmma_streamk_kernel(const __grid_constant__ CUtensorMap mapA, const __grid
             int tile_m, tile_n;
             tile_coords(p, tile, tile_m, tile_n);
             const int m0 = tile_m * BM, n0 = tile_n * BN;
+            const bool vec = ((p.n | p.ldc) & 1) == 0;            // epilogue-only values: not live across the K loop
+            const double alpha = p.alpha.get();
 #pragma unroll
             for (int i = 0; i < MI; ++i) {
                 const int64_t r = m0 + wm * MI * 8 + i * 8 + gq;
