@@ -7,9 +7,12 @@
 #include <cstring>
 #include <cstdlib>
 #include <algorithm>
+#include <atomic>
+#include <mutex>
 
 namespace accblas {
 
+std::atomic<uint64_t> g_launches_total{0};    // every thread's launches (accblas_launch_count_total)
 thread_local uint64_t g_launches = 0;
 thread_local char g_cuda_err[256] = {0};
 thread_local int g_gemm_path = 0;
@@ -40,9 +43,18 @@ Tuning::Tuning()
 }
 thread_local Tuning g_tuning;
 
+namespace {
+std::mutex g_err_mu;
+char g_cuda_err_any[256] = {0};               // most recent failure of ANY thread (accblas_last_cuda_error_r)
+}  // namespace
+
 int cuda_fail(cudaError_t e, const char *where)
 {
     snprintf(g_cuda_err, sizeof(g_cuda_err), "%s: %s (%s)", where, cudaGetErrorName(e), cudaGetErrorString(e));
+    {
+        std::lock_guard<std::mutex> lock(g_err_mu);
+        memcpy(g_cuda_err_any, g_cuda_err, sizeof(g_cuda_err_any));
+    }
     return ACCBLAS_ERR_CUDA;
 }
 
@@ -58,22 +70,50 @@ DevInfo &dev_info()
     if (d.sms == 0) {
         cudaDeviceGetAttribute(&d.sms, cudaDevAttrMultiProcessorCount, dev);
         cudaDeviceGetAttribute(&d.cc_major, cudaDevAttrComputeCapabilityMajor, dev);
-        // Stream-ordered scratch (cudaMallocAsync) comes from the device's default pool.  Keep
-        // freed blocks cached instead of returning them to the driver at every synchronisation:
-        // otherwise each call pays a physical allocation (~0.2 ms).
-        cudaMemPool_t pool = nullptr;
-        if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess && pool) {
-            uint64_t cur = 0;
-            cudaMemPoolGetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &cur);
-            if (cur == 0) {
-                uint64_t keep = ~0ull;
-                cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
-            }
-        }
     }
     return d;
 }
+
+// Stream-ordered scratch comes from a memory pool the LIBRARY owns (one per device, created on first use), not
+// from the device's default pool: inside an Accelerate process the default pool belongs to everyone who calls
+// cudaMallocAsync, and the library must not change its release threshold.  The private pool keeps freed blocks
+// cached (release threshold = max: otherwise every call pays a physical allocation, ~0.2 ms) until
+// accblas_trim_workspace() hands them back to the driver.
+std::mutex g_pool_mu;
+cudaMemPool_t g_pools[64] = {nullptr};
+
+cudaError_t scratch_pool(cudaMemPool_t *out)
+{
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(g_pool_mu);
+    if (!g_pools[dev]) {
+        cudaMemPoolProps props{};
+        props.allocType = cudaMemAllocationTypePinned;
+        props.handleTypes = cudaMemHandleTypeNone;
+        props.location.type = cudaMemLocationTypeDevice;
+        props.location.id = dev;
+        cudaMemPool_t pool = nullptr;
+        e = cudaMemPoolCreate(&pool, &props);
+        if (e != cudaSuccess) return e;
+        uint64_t keep = ~0ull;
+        cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+        g_pools[dev] = pool;
+    }
+    *out = g_pools[dev];
+    return cudaSuccess;
+}
 }  // namespace
+
+cudaError_t scratch_alloc(void **p, size_t bytes, cudaStream_t s)
+{
+    cudaMemPool_t pool = nullptr;
+    cudaError_t e = scratch_pool(&pool);
+    if (e != cudaSuccess) return e;
+    return cudaMallocFromPoolAsync(p, bytes ? bytes : 1, pool, s);
+}
 
 int sm_count() { int s = dev_info().sms; return s > 0 ? s : 148; }
 int device_check() { return dev_info().cc_major == 10 ? ACCBLAS_OK : ACCBLAS_ERR_ARCH; }
@@ -81,6 +121,12 @@ int device_check() { return dev_info().cc_major == 10 ? ACCBLAS_OK : ACCBLAS_ERR
 namespace {
 
 bool bad_dtype(int d) { return d < ACCBLAS_F32 || d > ACCBLAS_C64; }
+bool has_beta_value(int dtype, const void *beta)
+{
+    GemmArgs t{};
+    t.dtype = dtype; t.beta = beta; t.Cin = beta;      // any non-null Cin: only the VALUE is looked at
+    return has_beta(t);
+}
 bool bad_op(int o) { return o < ACCBLAS_OP_N || o > ACCBLAS_OP_H; }
 
 bool overlaps(const void *a, size_t na, const void *b, size_t nb)
@@ -154,12 +200,25 @@ int gemm_device(GemmArgs &g)
     if (g.m == 0 || g.n == 0) return ACCBLAS_OK;                       // nothing to write
     if (!g.C || !g.alpha) return ACCBLAS_ERR_NULL;
     const size_t es = elem_size(g.dtype);
-    if (g.k == 0) {                                                    // alpha * (empty sum) = 0
+    if (g.k == 0 && !has_beta(g)) {                                    // alpha * (empty sum) = 0
         ACC_CUDA(cudaMemset2DAsync(g.C, es * (size_t)g.ldc, 0, es * (size_t)g.n, (size_t)g.m, g.stream));
         return ACCBLAS_OK;
     }
+    if (g.k == 0) {                                                    // D = beta * Cin: the SIMT kernel's epilogue alone
+        ACC_TRY(device_check());
+        return gemm_generic(g);
+    }
     if (!g.A || !g.B) return ACCBLAS_ERR_NULL;
     const size_t bytesC = es * span(g.m, g.n, g.ldc);
+    if (has_beta(g)) {
+        // Cin is either the output itself (same base AND pitch: in place) or an array that does not touch it
+        if (g.ldcin == 0) g.ldcin = g.ldc;
+        if (g.ldcin < g.n) return ACCBLAS_ERR_SHAPE;
+        const bool in_place = g.Cin == g.C && g.ldcin == g.ldc;
+        if (!in_place && overlaps(g.C, bytesC, g.Cin, es * span(g.m, g.n, g.ldcin))) return ACCBLAS_ERR_ALIAS;
+    } else {
+        g.beta = nullptr; g.Cin = nullptr;
+    }
     if (overlaps(g.C, bytesC, g.A, es * span(g.rowsA, g.colsA, g.lda)) ||
         overlaps(g.C, bytesC, g.B, es * span(g.rowsB, g.colsB, g.ldb)))
         return ACCBLAS_ERR_ALIAS;
@@ -223,7 +282,7 @@ int gemm_repitched(const GemmArgs &g)
     const size_t bytesA = fixA ? (es * (size_t)lda * (size_t)g.rowsA + 255) / 256 * 256 : 0;
     const size_t bytesB = fixB ? es * (size_t)ldb * (size_t)g.rowsB : 0;
     char *ws = nullptr;
-    ACC_CUDA(cudaMallocAsync(reinterpret_cast<void **>(&ws), bytesA + bytesB, g.stream));
+    ACC_CUDA(scratch_alloc(reinterpret_cast<void **>(&ws), bytesA + bytesB, g.stream));
     // one launch copies both operands (blockIdx.z): at the sizes where this path matters (250^3 Floats take
     // ~15 us in all) a second copy launch is a visible fraction of the call
     const size_t w = es < 8 ? es : 8;                                  // copy word: 4 bytes (f32) or 8
@@ -256,7 +315,7 @@ struct Scratch {
     void *p = nullptr;
     cudaStream_t s;
     explicit Scratch(cudaStream_t st) : s(st) {}
-    cudaError_t alloc(size_t bytes) { return cudaMallocAsync(&p, bytes ? bytes : 1, s); }
+    cudaError_t alloc(size_t bytes) { return scratch_alloc(&p, bytes, s); }
     ~Scratch() { if (p) cudaFreeAsync(p, s); }
 };
 
@@ -286,7 +345,47 @@ const char *accblas_status_string(int s)
 }
 
 const char *accblas_last_cuda_error(void) { return g_cuda_err; }
+size_t accblas_last_cuda_error_r(char *buf, size_t cap)
+{
+    std::lock_guard<std::mutex> lock(g_err_mu);
+    const size_t n = strlen(g_cuda_err_any);
+    if (buf && cap) {
+        const size_t c = n < cap - 1 ? n : cap - 1;
+        memcpy(buf, g_cuda_err_any, c);
+        buf[c] = 0;
+    }
+    return n;
+}
 uint64_t accblas_launch_count(void) { return g_launches; }
+uint64_t accblas_launch_count_total(void) { return g_launches_total.load(std::memory_order_relaxed); }
+
+int accblas_trim_workspace(void)
+{
+    int dev = 0;
+    ACC_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return ACCBLAS_OK;
+    cudaMemPool_t pool = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(g_pool_mu);
+        pool = g_pools[dev];
+    }
+    if (pool) ACC_CUDA(cudaMemPoolTrimTo(pool, 0));
+    return ACCBLAS_OK;
+}
+
+size_t accblas_workspace_cached_bytes(void)
+{
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 0;
+    cudaMemPool_t pool = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(g_pool_mu);
+        pool = g_pools[dev];
+    }
+    uint64_t v = 0;
+    if (pool && cudaMemPoolGetAttribute(pool, cudaMemPoolAttrReservedMemCurrent, &v) != cudaSuccess) v = 0;
+    return (size_t)v;
+}
 void accblas_set_gemm_path(int path) { g_gemm_path = (path >= 0 && path <= 2) ? path : 0; }
 void accblas_set_tuning(int knob, int value)
 {
@@ -301,6 +400,24 @@ int accblas_gemm(accblas_stream_t stream, int dtype, int opA, int opB, int64_t r
     g.rowsA = rowsA; g.colsA = colsA; g.rowsB = rowsB; g.colsB = colsB;
     g.alpha = alpha_host; g.A = A; g.B = B; g.C = C;
     g.stream = static_cast<cudaStream_t>(stream);
+    return gemm_device(g);
+}
+
+int accblas_gemm_ex(accblas_stream_t stream, int dtype, int opA, int opB, int64_t rowsA, int64_t colsA,
+                    int64_t rowsB, int64_t colsB, const void *alpha_host, const void *A, int64_t lda,
+                    const void *B, int64_t ldb, const void *beta_host, const void *Cin, int64_t ldcin,
+                    void *C, int64_t ldc)
+{
+    if (lda < 0 || ldb < 0 || ldc < 0 || ldcin < 0) return ACCBLAS_ERR_SHAPE;
+    GemmArgs g{};
+    g.dtype = dtype; g.opA = opA; g.opB = opB;
+    g.rowsA = rowsA; g.colsA = colsA; g.rowsB = rowsB; g.colsB = colsB;
+    g.lda = lda; g.ldb = ldb; g.ldc = ldc;
+    g.alpha = alpha_host; g.A = A; g.B = B; g.C = C;
+    g.beta = beta_host; g.Cin = Cin; g.ldcin = ldcin;
+    g.stream = static_cast<cudaStream_t>(stream);
+    if (bad_dtype(dtype)) return ACCBLAS_ERR_DTYPE;
+    if (beta_host && !Cin && has_beta_value(dtype, beta_host)) return ACCBLAS_ERR_NULL;
     return gemm_device(g);
 }
 

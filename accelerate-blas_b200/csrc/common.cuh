@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stddef.h>
+#include <atomic>
 #include "../../include/accblas_b200.h"
 
 namespace accblas {
@@ -11,6 +12,7 @@ namespace accblas {
 // per-thread bookkeeping (the library itself is stateless: these are diagnostics)
 // ----------------------------------------------------------------------------------
 extern thread_local uint64_t g_launches;      // kernels enqueued by this thread
+extern std::atomic<uint64_t> g_launches_total; // ... by every thread of the process
 extern thread_local char g_cuda_err[256];     // text of the last CUDA failure
 extern thread_local int g_gemm_path;          // accblas_set_gemm_path
 // accblas_set_tuning (-1 = automatic).  Per thread; a new thread starts from the process-wide defaults
@@ -26,6 +28,7 @@ extern thread_local Tuning g_tuning;
 int cuda_fail(cudaError_t e, const char *where);   // records text, returns ACCBLAS_ERR_CUDA
 inline int check_launch(const char *where) {
     ++g_launches;
+    g_launches_total.fetch_add(1, std::memory_order_relaxed);
     cudaError_t e = cudaPeekAtLastError();
     return e == cudaSuccess ? ACCBLAS_OK : cuda_fail(cudaGetLastError(), where);
 }
@@ -55,6 +58,8 @@ struct AttrOnce {
 };
 
 int sm_count();                                  // SMs of the current device (cached per device)
+// stream-ordered scratch from the library's OWN memory pool (api.cu); release with cudaFreeAsync(p, stream)
+cudaError_t scratch_alloc(void **p, size_t bytes, cudaStream_t stream);
 int device_check();                              // ACCBLAS_OK iff current device is CC 10.x
 
 inline size_t elem_size(int dtype) {
@@ -152,6 +157,19 @@ template <typename T> inline Alpha<T> make_alpha(const void *p, bool on_device) 
     return a;
 }
 
+// beta * Cin term of the extended product (accblas_gemm_ex): D = alpha * op(A) * op(B) + beta * Cin.
+// cin == nullptr means beta = 0: Cin is never read (the reference's only mode, LLVM/PTX/Level3.hs:90).
+// Cin may be the output itself (in place: every element is read and then written by the same thread) or a
+// separate array with its own row pitch (e.g. a local accumulator while the output lives in a peer's HBM).
+template <typename T> struct BetaC {
+    const T *cin;
+    int64_t ld;
+    T beta;
+    __device__ __forceinline__ bool on() const { return cin != nullptr; }
+    // v + beta * Cin[r][c]
+    __device__ __forceinline__ T add(T v, int64_t r, int64_t c) const { return fma_acc(beta, cin[r * ld + c], v); }
+};
+
 // ----------------------------------------------------------------------------------
 // kernel-family entry points (one translation unit each)
 // ----------------------------------------------------------------------------------
@@ -165,10 +183,38 @@ struct GemmArgs {
     const void *A, *B;
     void *C;
     cudaStream_t stream;
+    // accblas_gemm_ex: D = alpha * op(A) * op(B) + beta * Cin.  beta == nullptr (or *beta == 0): Cin is never read.
+    const void *beta;                     // one element in host memory
+    const void *Cin;                      // m x n, row pitch ldcin (elements; 0 = ldc); may equal C
+    int64_t ldcin;
     // strided batch (accblas_gemm_strided_batched): `batch` independent products, operand b of the batch at
     // base + b * stride (elements; stride 0 = the same operand for every product).  batch <= 1: one product.
     int64_t batch, strideA, strideB, strideC;
 };
+
+template <typename T> inline bool scalar_is_zero(const T &v);
+template <> inline bool scalar_is_zero<float>(const float &v) { return v == 0.f; }
+template <> inline bool scalar_is_zero<double>(const double &v) { return v == 0.0; }
+template <> inline bool scalar_is_zero<float2>(const float2 &v) { return v.x == 0.f && v.y == 0.f; }
+template <> inline bool scalar_is_zero<double2>(const double2 &v) { return v.x == 0.0 && v.y == 0.0; }
+template <typename T> inline BetaC<T> make_beta(const GemmArgs &g) {
+    BetaC<T> b;
+    b.cin = nullptr; b.ld = 0; b.beta = Scalar<T>::zero();
+    if (g.beta && g.Cin) {
+        const T v = *static_cast<const T *>(g.beta);
+        if (!scalar_is_zero<T>(v)) { b.cin = static_cast<const T *>(g.Cin); b.ld = g.ldcin ? g.ldcin : g.ldc; b.beta = v; }
+    }
+    return b;
+}
+inline bool has_beta(const GemmArgs &g) {
+    if (!g.beta || !g.Cin) return false;
+    switch (g.dtype) {
+    case ACCBLAS_F32: return !scalar_is_zero(*static_cast<const float *>(g.beta));
+    case ACCBLAS_F64: return !scalar_is_zero(*static_cast<const double *>(g.beta));
+    case ACCBLAS_C32: return !scalar_is_zero(*static_cast<const float2 *>(g.beta));
+    default:          return !scalar_is_zero(*static_cast<const double2 *>(g.beta));
+    }
+}
 
 int gemm_device(GemmArgs &g);                         // api.cu : validate + dispatch one device-resident product
 int gemm_host_pipeline(const GemmArgs &g, const void *A_host, const void *B_host,

@@ -139,7 +139,7 @@ int dot_typed(cudaStream_t st, bool conj, int64_t n, const T *x, const T *y, T *
     int grid = 2 * sm_count();
     if (work < grid) grid = (int)(work > 0 ? work : 1);
     A *partial = nullptr;
-    ACC_CUDA(cudaMallocAsync(reinterpret_cast<void **>(&partial), sizeof(A) * (size_t)grid, st));
+    ACC_CUDA(scratch_alloc(reinterpret_cast<void **>(&partial), sizeof(A) * (size_t)grid, st));
     const bool cj = conj && Scalar<T>::cplx;
 #define GO(CJ, AL) dot_partial_kernel<T, CJ, AL><<<grid, DOT_THREADS, 0, st>>>(n, x, y, partial)
     if (aligned) { if (cj) GO(true, true); else GO(false, true); }

@@ -75,6 +75,7 @@ struct CombineArgs {
     double2 *C;                   // m x n complex, row pitch ldc
     int64_t m, n, ldt, ldc, pairs_per_row;
     Alpha<double2> alpha;
+    BetaC<double2> beta;
 };
 
 __global__ void __launch_bounds__(256) combine_planes_kernel(const CombineArgs a)
@@ -93,7 +94,9 @@ __global__ void __launch_bounds__(256) combine_planes_kernel(const CombineArgs a
         for (int e = 0; e < 2; ++e) {
             if (c + e < a.n) {
                 const double xr = t1[e] - t2[e], xi = (t3[e] - t1[e]) - t2[e];
-                out[e] = make_double2(al.x * xr - al.y * xi, al.x * xi + al.y * xr);
+                double2 v = make_double2(al.x * xr - al.y * xi, al.x * xi + al.y * xr);
+                if (a.beta.on()) v = a.beta.add(v, r, c + e);
+                out[e] = v;
             }
         }
     }
@@ -154,7 +157,7 @@ int zgemm_3m(const GemmArgs &g)
 {
     const size_t pa = plane_bytes(g.rowsA, g.colsA), pb = plane_bytes(g.rowsB, g.colsB), pt = plane_bytes(g.m, g.n);
     char *ws = nullptr;
-    if (cudaMallocAsync(reinterpret_cast<void **>(&ws), 3 * (pa + pb + pt), g.stream) != cudaSuccess) {
+    if (scratch_alloc(reinterpret_cast<void **>(&ws), 3 * (pa + pb + pt), g.stream) != cudaSuccess) {
         (void)cudaGetLastError();                          // no room for the planes: the in-register 4M kernel needs none
         return dgemm_dmma(g);
     }
@@ -169,6 +172,7 @@ int zgemm_3m(const GemmArgs &g)
         h.opB = g.opB == ACCBLAS_OP_N ? ACCBLAS_OP_N : ACCBLAS_OP_T;
         h.lda = even_up(g.colsA); h.ldb = even_up(g.colsB); h.ldc = even_up(g.n);
         h.alpha = &one; h.alpha_dev = false;
+        h.beta = nullptr; h.Cin = nullptr;
         h.A = wa + p * pa; h.B = wb + p * pb; h.C = wt + p * pt;
         st = dgemm_dmma_eligible(h) ? dgemm_dmma(h) : ACCBLAS_ERR_SHAPE;
     }
@@ -180,6 +184,7 @@ int zgemm_3m(const GemmArgs &g)
         c.C = static_cast<double2 *>(g.C);
         c.m = g.m; c.n = g.n; c.ldt = even_up(g.n); c.ldc = g.ldc; c.pairs_per_row = (g.n + 1) / 2;
         c.alpha = make_alpha<double2>(g.alpha, g.alpha_dev);
+        c.beta = make_beta<double2>(g);
         const int64_t total = c.m * c.pairs_per_row;
         const int64_t want = (total + 255) / 256, cap = (int64_t)sm_count() * 32;
         combine_planes_kernel<<<(unsigned)std::max<int64_t>(1, std::min(want, cap)), 256, 0, g.stream>>>(c);

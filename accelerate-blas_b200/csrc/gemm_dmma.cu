@@ -69,16 +69,77 @@ __device__ __forceinline__ int kslot(int s, int t) {
     return (t & 2) * 4 + 2 * ((s + t) & 3) + (t & 1);
 }
 
+// A consumer warp hands a stage back to the TMA producer with ONE mbarrier arrive by lane 0.  The arrive has
+// release semantics, but only for lane 0's own accesses: ptxas hoists it to right behind the last ld.shared of
+// the K-block (above the converging mma.sync instructions), and lanes that left the try_wait spin loop late have
+// then not even issued their fragment loads -- the producer's next TMA write raced with them (wrong results with
+// many small CTAs per SM, pinned by tests/test_parity_gpu.py::test_gemm_many_small_tiles_short_k).
+//   FENCED = false: __syncwarp (every lane's ld.shared is issued, in order, ahead of the arrive) -- the pattern every
+//            TMA + ld.shared pipeline uses for the read -> async-proxy-overwrite (WAR) direction;
+//   FENCED = true : additionally fence.proxy.async, which also drains the loads (costs 1.8 % of the DMMA pipe on the
+//            128 x 128 tile: 98.1 % -> 96.3 % active).  Kept for the small tiles, whose ring wraps every 3-4 K-blocks with
+//            5-7 CTAs per SM, and selectable everywhere with ACCBLAS_TUNE_RELEASE.
+template <bool FENCED> __device__ __forceinline__ void release_stage(uint32_t empty_bar, int lane) {
+    if (FENCED) tma::fence_proxy_async();
+    __syncwarp();
+    if (lane == 0) tma::mbar_arrive(empty_bar);
+}
+
 struct DgemmParams {
     int64_t m, n, k, ldc;
     Alpha<double> alpha;
+    BetaC<double> beta;  // + beta * Cin (accblas_gemm_ex); cin == nullptr: C is write-only
     double *C;
     int tiles_m, tiles_n, group;
     int snake_waves;     // CTAs per resident wave (0: every tile walks K forwards)
 };
 
+// tile index -> (tile_m, tile_n) under the grouped rasterisation: p.group tile-rows per group, so that one resident
+// wave re-uses its A and B panels out of L2
+__device__ __forceinline__ void tile_coords(const DgemmParams &p, int tile, int &tile_m, int &tile_n) {
+    const int per_group = p.group * p.tiles_n;
+    const int grp = tile / per_group;
+    const int first_m = grp * p.group;
+    const int gsz = min(p.tiles_m - first_m, p.group);
+    const int in_grp = tile - grp * per_group;
+    tile_m = first_m + in_grp % gsz;
+    tile_n = in_grp / gsz;
+}
+
+// C = alpha * acc (+ beta * Cin) from the DMMA fragment layout, 16-byte stores where the pitch allows
+template <typename TL>
+__device__ __forceinline__ void dgemm_epilogue(const DgemmParams &p, const double (&acc)[TL::MI][TL::NJ][2],
+                                               int m0, int n0, int wm, int wn, int g, int t)
+{
+    constexpr int MI = TL::MI, NJ = TL::NJ;
+    const bool vec = ((p.n | p.ldc) & 1) == 0;
+    const double alpha = p.alpha.get();
+    const bool acc_in = p.beta.on();
+#pragma unroll
+    for (int i = 0; i < MI; ++i) {
+        const int64_t r = m0 + wm * MI * 8 + i * 8 + g;
+        if (r >= p.m) continue;
+        double *crow = p.C + r * p.ldc;
+#pragma unroll
+        for (int j = 0; j < NJ; ++j) {
+            const int64_t c = n0 + wn * NJ * 8 + j * 8 + 2 * t;
+            double v0 = alpha * acc[i][j][0], v1 = alpha * acc[i][j][1];
+            if (acc_in) {
+                if (c < p.n) v0 = p.beta.add(v0, r, c);
+                if (c + 1 < p.n) v1 = p.beta.add(v1, r, c + 1);
+            }
+            if (vec) {
+                if (c < p.n) *reinterpret_cast<double2 *>(crow + c) = make_double2(v0, v1);
+            } else {
+                if (c < p.n) crow[c] = v0;
+                if (c + 1 < p.n) crow[c + 1] = v1;
+            }
+        }
+    }
+}
+
 // AK: op(A) is K-major in memory (opA == N).  BKM: op(B) is K-major in memory (opB == T).
-template <bool AK, bool BKM, typename TL>
+template <bool AK, bool BKM, typename TL, bool FENCED>
 __global__ void __launch_bounds__(TL::THREADS, TL::MIN_CTAS)
 dgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
                   const DgemmParams p)
@@ -90,19 +151,8 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
     const uint32_t bar_base = smem_base + STAGES * STAGE_BYTES;      // full[STAGES], empty[STAGES]
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
-    // grouped rasterisation: p.group tile-rows per group so that one resident wave re-uses its
-    // A and B panels out of L2
-    const int GROUP = p.group;
     int tile_m, tile_n;
-    {
-        const int per_group = GROUP * p.tiles_n;
-        const int grp = blockIdx.x / per_group;
-        const int first_m = grp * GROUP;
-        const int gsz = min(p.tiles_m - first_m, GROUP);
-        const int in_grp = blockIdx.x - grp * per_group;
-        tile_m = first_m + in_grp % gsz;
-        tile_n = in_grp / gsz;
-    }
+    tile_coords(p, blockIdx.x, tile_m, tile_n);
     const int m0 = tile_m * BM, n0 = tile_n * BN;
     const int kblocks = (int)((p.k + BK - 1) / BK);
 
@@ -191,54 +241,46 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
 #pragma unroll
                 for (int j = 0; j < NJ; ++j) dmma(acc[i][j][0], acc[i][j][1], a[st & 1][i], b[st & 1][j]);
         }
-        tma::consumer_release_fence();
-        if (lane == 0) tma::mbar_arrive(bar_base + 8 * (STAGES + s));   // stage consumed by this warp
+        release_stage<FENCED>(bar_base + 8 * (STAGES + s), lane);      // stage consumed by this warp
     }
 
-    // ---- epilogue: C = alpha * acc (never read C) ----
-    const bool vec = ((p.n | p.ldc) & 1) == 0;
-    const double alpha = p.alpha.get();
-#pragma unroll
-    for (int i = 0; i < MI; ++i) {
-        const int64_t r = m0 + wm * MI * 8 + i * 8 + g;
-        if (r >= p.m) continue;
-        double *crow = p.C + r * p.ldc;
-#pragma unroll
-        for (int j = 0; j < NJ; ++j) {
-            const int64_t c = n0 + wn * NJ * 8 + j * 8 + 2 * t;
-            const double v0 = alpha * acc[i][j][0], v1 = alpha * acc[i][j][1];
-            if (vec) {
-                if (c < p.n) *reinterpret_cast<double2 *>(crow + c) = make_double2(v0, v1);
-            } else {
-                if (c < p.n) crow[c] = v0;
-                if (c + 1 < p.n) crow[c + 1] = v1;
-            }
-        }
-    }
+    // ---- epilogue: C = alpha * acc (+ beta * Cin); C itself is never read unless it is Cin ----
+    dgemm_epilogue<TL>(p, acc, m0, n0, wm, wn, g, t);
 }
 
 
 // =====================================================================================
-// Stream-K variant of the 128 x 128 real kernel: ONE persistent CTA per SM, the (tile, K-block) iteration
-// space cut into equal contiguous ranges, so a product whose tile count is not a multiple of the SM count
-// (dgemm 1024^3: 64 tiles, 2048^3: 256 tiles on 148 SMs) still loads every SM evenly.
-// A range is a sequence of segments (one tile, K-blocks [ks, ke)):
+// Persistent variant of the 128 x 128 real kernel: ONE CTA per SM works through
+//   (1) `dp_rounds` whole tiles, tile = round * gridDim + cta  (the same waves the data-parallel launch forms; the
+//       producer warp runs ahead into the next tile while the consumers store the previous one), then
+//   (2) its share of the STREAM-K region: the (tile, K-block) iteration space of the remaining tiles
+//       [sk_tile0, tiles) cut into gridDim equal contiguous ranges -- so a product whose tile count is not a
+//       multiple of the SM count (dgemm 8192^3: 4096 tiles = 27.68 waves of 148; 2048^3: 256 tiles) still loads
+//       every SM evenly instead of running a last wave that is 68 % (or 73 %) full.
+// A stream-K range is a sequence of segments (one tile, K-blocks [ks, ke)):
 //   whole tile  (ks == 0, ke == kblocks)  -> the usual epilogue;
 //   tile tail   (ks > 0): only ever the FIRST segment of a CTA -> accumulators go to the CTA's workspace
 //                slot in fragment layout, then a release flag;
 //   tile head   (ks == 0, ke < kblocks): only ever the LAST segment of a CTA -> waits for the flags of the
 //                following CTAs that hold the rest of the tile (work they did at the very start of their
-//                lives, so the wait is short and cannot chain), adds their partials in CTA order
-//                (deterministic), runs the epilogue.
-// All CTAs are co-resident (grid <= SM count, one CTA per SM by shared memory), so the flag wait cannot deadlock.
+//                stream-K phase, so the wait is short and cannot chain), adds their partials in CTA order
+//                (deterministic, bit-reproducible), runs the epilogue.
+// Progress: CTA ids are TICKETS drawn from a global counter at start-up, not blockIdx, so id order is start
+// order whatever the hardware's dispatch order.  A CTA only ever waits for HIGHER tickets' first stream-K segment,
+// which needs nothing from anyone.  If some CTAs are not resident yet (SMs shared with another stream's kernel, MPS,
+// a partitioned GPU), every resident CTA with a lower ticket than the first missing one can finish -- its
+// dependencies are resident -- and frees its SM for the missing ones: the wait cannot deadlock, it can only take
+// longer, so there is no watchdog trap in the spin.
 // =====================================================================================
 struct StreamKParams {
     DgemmParams p;
     int kblocks;
-    long long total;        // tiles * kblocks
-    int base, rem;          // CTA c owns base + (c < rem) iterations starting at c * base + min(c, rem)
+    int dp_rounds;          // whole tiles per CTA ahead of the stream-K region
+    int sk_tile0;           // first tile of the stream-K region = dp_rounds * gridDim.x
+    long long total;        // stream-K iterations = (tiles - sk_tile0) * kblocks
+    int base, rem;          // CTA c owns base + (c < rem) of them starting at c * base + min(c, rem)
     double *ws;             // gridDim.x slots of 128 x 128 doubles
-    unsigned *flags;        // gridDim.x words, zeroed before the launch
+    unsigned *flags;        // gridDim.x words + the ticket counter at [gridDim.x], zeroed before the launch
 };
 
 __device__ __forceinline__ unsigned ld_acquire_gpu(const unsigned *p) {
@@ -249,17 +291,25 @@ __device__ __forceinline__ unsigned ld_acquire_gpu(const unsigned *p) {
 __device__ __forceinline__ void st_release_gpu(unsigned *p, unsigned v) {
     asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
-__device__ __forceinline__ void tile_coords(const DgemmParams &p, int tile, int &tile_m, int &tile_n) {
-    const int per_group = p.group * p.tiles_n;
-    const int grp = tile / per_group;
-    const int first_m = grp * p.group;
-    const int gsz = min(p.tiles_m - first_m, p.group);
-    const int in_grp = tile - grp * per_group;
-    tile_m = first_m + in_grp % gsz;
-    tile_n = in_grp / gsz;
+
+// Segment `seg` of a CTA (seg counts whole-tile rounds first, then `it` walks the CTA's stream-K range).  Pure function
+// of (seg, it): the consumers evaluate it before AND after the K loop instead of keeping tile / ks / ke live across it
+// (the loop body needs all 168 registers the 9-warp CTA can have).
+__device__ __forceinline__ bool segment_at(const StreamKParams &q, int cta, int grid, int seg, int it, int it_end,
+                                           int &tile, int &ks, int &ke) {
+    if (seg < q.dp_rounds) {
+        tile = seg * grid + cta; ks = 0; ke = q.kblocks;
+        return true;
+    }
+    if (it >= it_end) return false;
+    const int tl = it / q.kblocks;
+    ks = it - tl * q.kblocks;
+    ke = min(q.kblocks, ks + (it_end - it));
+    tile = q.sk_tile0 + tl;
+    return true;
 }
 
-template <bool AK, bool BKM>
+template <bool AK, bool BKM, bool FENCED>
 __global__ void __launch_bounds__(Tile128x128::THREADS, 1)
 dgemm_dmma_streamk_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
                           const StreamKParams q)
@@ -271,11 +321,10 @@ dgemm_dmma_streamk_kernel(const __grid_constant__ CUtensorMap mapA, const __grid
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem_base = (tma::smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t bar_base = smem_base + STAGES * STAGE_BYTES;
+    const uint32_t ticket_slot = bar_base + 16 * STAGES;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int kblocks = q.kblocks;
-    const int cta = blockIdx.x;
-    const int it_begin = cta * q.base + min(cta, q.rem);           // host guarantees total < 2^31
-    const int it_end = it_begin + q.base + (cta < q.rem ? 1 : 0);
+    const int grid = gridDim.x;
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < STAGES; ++s) {
@@ -283,8 +332,14 @@ dgemm_dmma_streamk_kernel(const __grid_constant__ CUtensorMap mapA, const __grid
             tma::mbar_init(bar_base + 8 * (STAGES + s), CONSUMER_WARPS);
         }
         tma::fence_barrier_init();
+        const unsigned ticket = atomicAdd(q.flags + grid, 1u);
+        asm volatile("st.shared.u32 [%0], %1;" ::"r"(ticket_slot), "r"(ticket) : "memory");
     }
     __syncthreads();
+    int cta;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(cta) : "r"(ticket_slot));
+    const int it_begin = cta * q.base + min(cta, q.rem);           // host guarantees total < 2^31
+    const int it_end = it_begin + q.base + (cta < q.rem ? 1 : 0);
 
     if (warp == CONSUMER_WARPS) {
         // ================================ producer ================================
@@ -292,9 +347,9 @@ dgemm_dmma_streamk_kernel(const __grid_constant__ CUtensorMap mapA, const __grid
             tma::prefetch_tmap(&mapA);
             tma::prefetch_tmap(&mapB);
             int g = 0;                                            // K-blocks issued so far (ring position)
-            for (int it = it_begin; it < it_end;) {
-                const int tile = it / kblocks, ks = it - tile * kblocks;
-                const int ke = min(kblocks, ks + (it_end - it));
+            int it = it_begin, tile, ks, ke;
+            for (int seg = 0; segment_at(q, cta, grid, seg, it, it_end, tile, ks, ke); ++seg) {
+                if (seg >= q.dp_rounds) it += ke - ks;
                 int tile_m, tile_n;
                 tile_coords(p, tile, tile_m, tile_n);
                 const int m0 = tile_m * BM, n0 = tile_n * BN;
@@ -315,7 +370,6 @@ dgemm_dmma_streamk_kernel(const __grid_constant__ CUtensorMap mapA, const __grid
 #pragma unroll
                         for (int j = 0; j < BN / 16; ++j) tma::load_2d(sb + j * 2048, &mapB, full, n0 + 16 * j, k0);
                 }
-                it += ke - ks;
             }
         }
         return;
@@ -341,19 +395,25 @@ dgemm_dmma_streamk_kernel(const __grid_constant__ CUtensorMap mapA, const __grid
             b[j] = lds64(stage + (BKM ? offB[s] + j * 1024 : (offB[s] ^ ((j & 1) << 6)) + (j >> 1) * 2048));
     };
     constexpr int SLOT = BM * BN;                                  // doubles per workspace slot
-    int g = 0;                                                    // K-blocks consumed so far (ring position)
-    for (int it = it_begin; it < it_end;) {
-        const int tile = it / kblocks, ks = it - tile * kblocks;
-        const int ke = min(kblocks, ks + (it_end - it));
+    // ring position: stage index and phase parity, advanced incrementally (no division in the K loop)
+    int rs = 0;
+    uint32_t rphase = 0;
+    int it = it_begin;
+    for (int seg = 0;; ++seg) {
+        int nkb;
+        {
+            int tile, ks, ke;
+            if (!segment_at(q, cta, grid, seg, it, it_end, tile, ks, ke)) break;
+            nkb = ke - ks;
+        }
         double acc[MI][NJ][2];
 #pragma unroll
         for (int i = 0; i < MI; ++i)
 #pragma unroll
             for (int j = 0; j < NJ; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
-        for (int kb = ks; kb < ke; ++kb, ++g) {
-            const int s = g % STAGES;
-            const uint32_t stage = smem_base + s * STAGE_BYTES;
-            tma::mbar_wait(bar_base + 8 * s, (g / STAGES) & 1);
+        for (; nkb > 0; --nkb) {
+            const uint32_t stage = smem_base + rs * STAGE_BYTES;
+            tma::mbar_wait(bar_base + 8 * rs, rphase);
             double a[2][MI], b[2][NJ];
             load_frags(stage, 0, a[0], b[0]);
 #pragma unroll
@@ -364,12 +424,19 @@ dgemm_dmma_streamk_kernel(const __grid_constant__ CUtensorMap mapA, const __grid
 #pragma unroll
                     for (int j = 0; j < NJ; ++j) dmma(acc[i][j][0], acc[i][j][1], a[st & 1][i], b[st & 1][j]);
             }
-            tma::consumer_release_fence();
-            if (lane == 0) tma::mbar_arrive(bar_base + 8 * (STAGES + s));
+            release_stage<FENCED>(bar_base + 8 * (STAGES + rs), lane);
+            if (++rs == STAGES) { rs = 0; rphase ^= 1u; }
         }
+        // the segment again (see segment_at), with the CTA's ticket re-read from shared memory
+        int cta2;
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(cta2) : "r"(ticket_slot));
+        const int end2 = cta2 * q.base + min(cta2, q.rem) + q.base + (cta2 < q.rem ? 1 : 0);
+        int tile, ks, ke;
+        segment_at(q, cta2, grid, seg, it, end2, tile, ks, ke);
+        if (seg >= q.dp_rounds) it += ke - ks;
         if (ks > 0) {
             // ---- tile tail: hand the partial sums to the CTA that owns the head of this tile ----
-            double2 *slot = reinterpret_cast<double2 *>(q.ws + (size_t)cta * SLOT);
+            double2 *slot = reinterpret_cast<double2 *>(q.ws + (size_t)cta2 * SLOT);
 #pragma unroll
             for (int i = 0; i < MI; ++i)
 #pragma unroll
@@ -377,16 +444,16 @@ dgemm_dmma_streamk_kernel(const __grid_constant__ CUtensorMap mapA, const __grid
                     slot[((warp * MI + i) * NJ + j) * 32 + lane] = make_double2(acc[i][j][0], acc[i][j][1]);
             __threadfence();
             asm volatile("bar.sync 1, %0;" ::"n"(CONSUMER_WARPS * 32) : "memory");
-            if (threadIdx.x == 0) st_release_gpu(q.flags + cta, 1u);
+            if (threadIdx.x == 0) st_release_gpu(q.flags + cta2, 1u);
         } else {
             if (ke < kblocks) {
                 // ---- tile head: add the partial sums of the CTAs holding K-blocks [ke, kblocks) ----
                 int pos = ke;
-                for (int c2 = cta + 1; pos < kblocks; ++c2) {
-                    unsigned spins = 0;
-                    while (ld_acquire_gpu(q.flags + c2) == 0u) {
-                        __nanosleep(100);
-                        if (++spins > (1u << 24)) __trap();
+                for (int c2 = cta2 + 1; pos < kblocks; ++c2) {
+                    unsigned ns = 32;
+                    while (ld_acquire_gpu(q.flags + c2) == 0u) {      // no watchdog: see the progress argument above
+                        __nanosleep(ns);
+                        if (ns < 2048) ns *= 2;
                     }
                     const double2 *slot = reinterpret_cast<const double2 *>(q.ws + (size_t)c2 * SLOT);
 #pragma unroll
@@ -402,28 +469,8 @@ dgemm_dmma_streamk_kernel(const __grid_constant__ CUtensorMap mapA, const __grid
             }
             int tile_m, tile_n;
             tile_coords(p, tile, tile_m, tile_n);
-            const int m0 = tile_m * BM, n0 = tile_n * BN;
-            const bool vec = ((p.n | p.ldc) & 1) == 0;            // epilogue-only values: not live across the K loop
-            const double alpha = p.alpha.get();
-#pragma unroll
-            for (int i = 0; i < MI; ++i) {
-                const int64_t r = m0 + wm * MI * 8 + i * 8 + gq;
-                if (r >= p.m) continue;
-                double *crow = p.C + r * p.ldc;
-#pragma unroll
-                for (int j = 0; j < NJ; ++j) {
-                    const int64_t c = n0 + wn * NJ * 8 + j * 8 + 2 * t;
-                    const double v0 = alpha * acc[i][j][0], v1 = alpha * acc[i][j][1];
-                    if (vec) {
-                        if (c < p.n) *reinterpret_cast<double2 *>(crow + c) = make_double2(v0, v1);
-                    } else {
-                        if (c < p.n) crow[c] = v0;
-                        if (c + 1 < p.n) crow[c + 1] = v1;
-                    }
-                }
-            }
+            dgemm_epilogue<TL>(p, acc, tile_m * BM, tile_n * BN, wm, wn, gq, t);
         }
-        it += ke - ks;
     }
 }
 
@@ -473,11 +520,12 @@ __device__ __forceinline__ double flip(double x) {
 struct ZgemmParams {
     int64_t m, n, k, ldc;
     Alpha<double2> alpha;
+    BetaC<double2> beta;
     double2 *C;
     int tiles_m, tiles_n;
 };
 
-template <bool AK, bool BKM, bool CONJA, bool CONJB, typename TL>
+template <bool AK, bool BKM, bool CONJA, bool CONJB, typename TL, bool FENCED>
 __global__ void __launch_bounds__(TL::THREADS, TL::MIN_CTAS)
 zgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
                   const ZgemmParams p)
@@ -602,11 +650,11 @@ zgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
 #pragma unroll
                 for (int j = 0; j < NJ; ++j) dmma(ci[i][j][0], ci[i][j][1], ai[i], b[st][j].x);
         }
-        tma::consumer_release_fence();
-        if (lane == 0) tma::mbar_arrive(bar_base + 8 * (ZSTAGES + s));
+        release_stage<FENCED>(bar_base + 8 * (ZSTAGES + s), lane);
     }
 
     const double2 al = p.alpha.get();
+    const bool acc_in = p.beta.on();
 #pragma unroll
     for (int i = 0; i < MI; ++i) {
         const int64_t r = m0 + wm * MI * 8 + i * 8 + g;
@@ -619,7 +667,9 @@ zgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
             for (int e = 0; e < 2; ++e) {
                 if (c + e < p.n) {
                     const double xr = cr[i][j][e], xi = ci[i][j][e];
-                    crow[c + e] = make_double2(al.x * xr - al.y * xi, al.x * xi + al.y * xr);
+                    double2 v = make_double2(al.x * xr - al.y * xi, al.x * xi + al.y * xr);
+                    if (acc_in) v = p.beta.add(v, r, c + e);
+                    crow[c + e] = v;
                 }
             }
         }
@@ -663,7 +713,29 @@ int pick_tile(int64_t m, int64_t n, int64_t k, double *cost_out = nullptr)
     return best;
 }
 
-template <bool AK, bool BKM, typename TL>
+// Stage-release mode (see release_stage): ACCBLAS_TUNE_RELEASE = 0 -> fence.proxy.async everywhere, 1 -> __syncwarp
+// only everywhere, automatic: light release for the tiles that run ONE CTA per SM over a deep ring (128 x 128 real,
+// 128 x 64 complex, the persistent kernel), fenced release for the small multi-CTA tiles.
+bool fenced_release(bool big_tile)
+{
+    const int knob = g_tuning[ACCBLAS_TUNE_RELEASE];
+    if (knob == 0) return true;
+    if (knob == 1) return false;
+    return !big_tile;
+}
+
+void fill_params(DgemmParams &p, const GemmArgs &g, int BM, int BN)
+{
+    p.m = g.m; p.n = g.n; p.k = g.k; p.ldc = g.ldc;
+    p.alpha = make_alpha<double>(g.alpha, g.alpha_dev);
+    p.beta = make_beta<double>(g);
+    p.C = static_cast<double *>(g.C);
+    p.tiles_m = (int)((g.m + BM - 1) / BM);
+    p.tiles_n = (int)((g.n + BN - 1) / BN);
+    p.group = g_tuning[ACCBLAS_TUNE_RASTER_GROUP] > 0 ? g_tuning[ACCBLAS_TUNE_RASTER_GROUP] : 16;
+}
+
+template <bool AK, bool BKM, typename TL, bool FENCED>
 int launch_dgemm_tile(const GemmArgs &g)
 {
     constexpr int BM = TL::BM, BN = TL::BN, SMEM_BYTES = TL::SMEM_BYTES;
@@ -676,25 +748,50 @@ int launch_dgemm_tile(const GemmArgs &g)
         return cuda_fail(cudaErrorInvalidValue, "cuTensorMapEncodeTiled");
     static thread_local AttrOnce attr_once;
     if (attr_once.need()) {
-        ACC_CUDA(cudaFuncSetAttribute(dgemm_dmma_kernel<AK, BKM, TL>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+        ACC_CUDA(cudaFuncSetAttribute(dgemm_dmma_kernel<AK, BKM, TL, FENCED>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
     }
     DgemmParams p;
-    p.m = g.m; p.n = g.n; p.k = g.k; p.ldc = g.ldc;
-    p.alpha = make_alpha<double>(g.alpha, g.alpha_dev);
-    p.C = static_cast<double *>(g.C);
-    p.tiles_m = (int)((g.m + BM - 1) / BM);
-    p.tiles_n = (int)((g.n + BN - 1) / BN);
-    p.group = g_tuning[ACCBLAS_TUNE_RASTER_GROUP] > 0 ? g_tuning[ACCBLAS_TUNE_RASTER_GROUP] : 16;
+    fill_params(p, g, BM, BN);
     p.snake_waves = g_tuning[ACCBLAS_TUNE_SNAKE_K] == 0 ? 0 : sm_count() * TL::MIN_CTAS;
     const int64_t tiles = (int64_t)p.tiles_m * p.tiles_n;
     if (tiles > 0x7fffffff) return ACCBLAS_ERR_SHAPE;
-    dgemm_dmma_kernel<AK, BKM, TL><<<(unsigned)tiles, TL::THREADS, SMEM_BYTES, g.stream>>>(mapA, mapB, p);
+    dgemm_dmma_kernel<AK, BKM, TL, FENCED><<<(unsigned)tiles, TL::THREADS, SMEM_BYTES, g.stream>>>(mapA, mapB, p);
     return check_launch("dgemm_dmma_kernel");
 }
 
-// Stream-K launch (128 x 128 tiles, one persistent CTA per SM).  Scratch: one accumulator slot per CTA + flags.
-template <bool AK, bool BKM>
-int launch_dgemm_streamk(const GemmArgs &g)
+// The persistent kernel's schedule for a product: how many whole-tile rounds run ahead of the stream-K region.
+struct StreamKPlan { bool use; int grid; int dp_rounds; };
+
+// The persistent DP + stream-K kernel pays when a product of at least one full wave of 128 x 128 tiles leaves a
+// partial last wave.  Measured round 1 as pure stream-K (profiles/r01_streamk.jsonl): 2048^3 (256 tiles, wave
+// efficiency 0.865) 522 -> 510 us, 2560^3 (0.90) 1013 -> 975, 3072^3 (0.973) 1680 -> 1663; below one wave the small
+// data-parallel tiles win (1024^3: 75.8 against 86.0 us) because the scratch, the flag memset and the fix-ups cost
+// ~30 us.  Since round 2 only the LAST partial wave is stream-K'd (every CTA first runs floor(tiles / SMs) whole
+// tiles), which limits the fix-up traffic to at most one 128 KiB partial per SM whatever the product size and makes
+// the schedule worth taking at 0.988 too (4096^3, 8192^3: 27.68 waves of 148).
+StreamKPlan plan_streamk(int64_t m, int64_t n, int64_t k)
+{
+    StreamKPlan pl{false, 0, 0};
+    const int knob = g_tuning[ACCBLAS_TUNE_STREAMK];
+    if (knob == 0 || g_tuning[ACCBLAS_TUNE_DMMA_TILE] >= 0) return pl;
+    const int sms = sm_count();
+    if (sms >= 1024) return pl;                                  // flag block is 4 KiB (SMs + the ticket word)
+    const int64_t tiles = ((m + 127) / 128) * ((n + 127) / 128), kblocks = (k + BK - 1) / BK;
+    if (tiles * kblocks < 4 * (int64_t)sms || kblocks < 4 || tiles * kblocks > 0x7fffffff) return pl;
+    pl.grid = (int)std::min<int64_t>(sms, tiles * kblocks);
+    const int64_t rem_tiles = tiles % pl.grid;
+    // whole-tile rounds first; knob 2 = pure stream-K (round 1's schedule, kept for the side-by-side)
+    pl.dp_rounds = knob == 2 ? 0 : (int)(tiles / pl.grid);
+    if (rem_tiles == 0 && knob != 2) return pl;                  // full waves only: the data-parallel launch is the same thing
+    if (knob == 1 || knob == 2) { pl.use = true; return pl; }
+    // automatic: the tail must be worth a fix-up (at least 32 K-blocks per CTA) and the product at least one wave
+    pl.use = tiles >= sms && k >= 512 && rem_tiles * kblocks >= 32 * (int64_t)pl.grid;
+    return pl;
+}
+
+// Persistent launch (128 x 128 tiles, one CTA per SM).  Scratch: one accumulator slot per CTA + flags + ticket.
+template <bool AK, bool BKM, bool FENCED>
+int launch_dgemm_streamk(const GemmArgs &g, const StreamKPlan &pl)
 {
     using TL = Tile128x128;
     CUtensorMap mapA, mapB;
@@ -703,33 +800,31 @@ int launch_dgemm_streamk(const GemmArgs &g)
         !tma::make_2d(&mapB, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 8, g.B, (uint64_t)g.rowsB, (uint64_t)g.colsB,
                       BKM ? TL::BN : BK, 16, (uint64_t)g.ldb * 8))
         return cuda_fail(cudaErrorInvalidValue, "cuTensorMapEncodeTiled");
+    constexpr int SMEM = TL::SMEM_BYTES + 16;                      // + the ticket word
     static thread_local AttrOnce attr_once;
     if (attr_once.need()) {
-        ACC_CUDA(cudaFuncSetAttribute(dgemm_dmma_streamk_kernel<AK, BKM>, cudaFuncAttributeMaxDynamicSharedMemorySize, TL::SMEM_BYTES));
+        ACC_CUDA(cudaFuncSetAttribute(dgemm_dmma_streamk_kernel<AK, BKM, FENCED>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
     }
     StreamKParams q;
     DgemmParams &p = q.p;
-    p.m = g.m; p.n = g.n; p.k = g.k; p.ldc = g.ldc;
-    p.alpha = make_alpha<double>(g.alpha, g.alpha_dev);
-    p.C = static_cast<double *>(g.C);
-    p.tiles_m = (int)((g.m + TL::BM - 1) / TL::BM);
-    p.tiles_n = (int)((g.n + TL::BN - 1) / TL::BN);
-    p.group = g_tuning[ACCBLAS_TUNE_RASTER_GROUP] > 0 ? g_tuning[ACCBLAS_TUNE_RASTER_GROUP] : 16;
-    p.snake_waves = g_tuning[ACCBLAS_TUNE_SNAKE_K] == 0 ? 0 : sm_count();
+    fill_params(p, g, TL::BM, TL::BN);
+    const int grid = pl.grid;
+    p.snake_waves = g_tuning[ACCBLAS_TUNE_SNAKE_K] == 0 ? 0 : grid;
     q.kblocks = (int)((g.k + BK - 1) / BK);
-    q.total = (long long)p.tiles_m * p.tiles_n * q.kblocks;
-    const int grid = (int)std::min<long long>(sm_count(), q.total);
+    q.dp_rounds = pl.dp_rounds;
+    q.sk_tile0 = pl.dp_rounds * grid;
+    q.total = ((long long)p.tiles_m * p.tiles_n - q.sk_tile0) * q.kblocks;
     q.base = (int)(q.total / grid);
     q.rem = (int)(q.total % grid);
     const size_t ws_bytes = (size_t)grid * TL::BM * TL::BN * 8;
     char *ws = nullptr;
-    ACC_CUDA(cudaMallocAsync(reinterpret_cast<void **>(&ws), ws_bytes + 4096, g.stream));
+    ACC_CUDA(scratch_alloc(reinterpret_cast<void **>(&ws), ws_bytes + 4096, g.stream));
     q.ws = reinterpret_cast<double *>(ws);
     q.flags = reinterpret_cast<unsigned *>(ws + ws_bytes);
     cudaError_t e = cudaMemsetAsync(q.flags, 0, 4096, g.stream);
     int st = ACCBLAS_OK;
     if (e == cudaSuccess) {
-        dgemm_dmma_streamk_kernel<AK, BKM><<<(unsigned)grid, TL::THREADS, TL::SMEM_BYTES, g.stream>>>(mapA, mapB, q);
+        dgemm_dmma_streamk_kernel<AK, BKM, FENCED><<<(unsigned)grid, TL::THREADS, SMEM, g.stream>>>(mapA, mapB, q);
         st = check_launch("dgemm_dmma_streamk_kernel");
     }
     const cudaError_t e2 = cudaFreeAsync(ws, g.stream);
@@ -738,39 +833,23 @@ int launch_dgemm_streamk(const GemmArgs &g)
     return st;
 }
 
-// Stream-K pays when a product of at least one full wave of 128 x 128 tiles leaves a partial last wave: measured
-// (profiles/r01_streamk.jsonl) 2048^3 (256 tiles, wave efficiency 0.865) 522 -> 510 us, 2560^3 (0.90) 1013 -> 975,
-// 3072^3 (0.973) 1680 -> 1663; at 0.988 (4096^3, 8192^3) it is a wash, and below one wave the small data-parallel
-// tiles win (1024^3: 75.8 against 86.0 us) because the scratch, the flag memset and the fixups cost ~30 us.
-bool want_streamk(int64_t m, int64_t n, int64_t k, double best_cost)
-{
-    (void)best_cost;
-    const int knob = g_tuning[ACCBLAS_TUNE_STREAMK];
-    if (knob == 0 || g_tuning[ACCBLAS_TUNE_DMMA_TILE] >= 0) return false;
-    const int sms = sm_count();
-    if (sms > 1024) return false;                                  // flag block is 4 KiB
-    const int64_t tiles = ((m + 127) / 128) * ((n + 127) / 128), kblocks = (k + BK - 1) / BK;
-    if (tiles * kblocks < 4 * (int64_t)sms || kblocks < 4 || tiles * kblocks > 0x7fffffff) return false;
-    if (knob == 1) return true;
-    const int64_t waves = (tiles + sms - 1) / sms;
-    return tiles >= sms && (double)tiles < 0.98 * (double)(waves * sms) && k >= 512;
-}
-
 template <bool AK, bool BKM>
 int launch_dgemm(const GemmArgs &g)
 {
-    double best_cost = 0.0;
-    const int tile = pick_tile(g.m, g.n, g.k, &best_cost);
-    if (want_streamk(g.m, g.n, g.k, best_cost)) return launch_dgemm_streamk<AK, BKM>(g);
+    const int tile = pick_tile(g.m, g.n, g.k);
+    const StreamKPlan pl = plan_streamk(g.m, g.n, g.k);
+    if (pl.use)
+        return fenced_release(true) ? launch_dgemm_streamk<AK, BKM, true>(g, pl) : launch_dgemm_streamk<AK, BKM, false>(g, pl);
+    const bool fenced = fenced_release(tile == 0);
     switch (tile) {
-    case 1:  return launch_dgemm_tile<AK, BKM, Tile64x128>(g);
-    case 2:  return launch_dgemm_tile<AK, BKM, Tile64x64>(g);
-    case 3:  return launch_dgemm_tile<AK, BKM, Tile32x32>(g);
-    default: return launch_dgemm_tile<AK, BKM, Tile128x128>(g);
+    case 1:  return fenced ? launch_dgemm_tile<AK, BKM, Tile64x128, true>(g) : launch_dgemm_tile<AK, BKM, Tile64x128, false>(g);
+    case 2:  return fenced ? launch_dgemm_tile<AK, BKM, Tile64x64, true>(g) : launch_dgemm_tile<AK, BKM, Tile64x64, false>(g);
+    case 3:  return fenced ? launch_dgemm_tile<AK, BKM, Tile32x32, true>(g) : launch_dgemm_tile<AK, BKM, Tile32x32, false>(g);
+    default: return fenced ? launch_dgemm_tile<AK, BKM, Tile128x128, true>(g) : launch_dgemm_tile<AK, BKM, Tile128x128, false>(g);
     }
 }
 
-template <bool AK, bool BKM, bool CA, bool CB, typename TL>
+template <bool AK, bool BKM, bool CA, bool CB, typename TL, bool FENCED>
 int launch_zgemm_tile(const GemmArgs &g)
 {
     constexpr int ZBM = TL::BM, ZBN = TL::BN;
@@ -783,17 +862,18 @@ int launch_zgemm_tile(const GemmArgs &g)
         return cuda_fail(cudaErrorInvalidValue, "cuTensorMapEncodeTiled");
     static thread_local AttrOnce attr_once;
     if (attr_once.need()) {
-        ACC_CUDA(cudaFuncSetAttribute(zgemm_dmma_kernel<AK, BKM, CA, CB, TL>, cudaFuncAttributeMaxDynamicSharedMemorySize, TL::SMEM_BYTES));
+        ACC_CUDA(cudaFuncSetAttribute(zgemm_dmma_kernel<AK, BKM, CA, CB, TL, FENCED>, cudaFuncAttributeMaxDynamicSharedMemorySize, TL::SMEM_BYTES));
     }
     ZgemmParams p;
     p.m = g.m; p.n = g.n; p.k = g.k; p.ldc = g.ldc;
     p.alpha = make_alpha<double2>(g.alpha, g.alpha_dev);
+    p.beta = make_beta<double2>(g);
     p.C = static_cast<double2 *>(g.C);
     p.tiles_m = (int)((g.m + ZBM - 1) / ZBM);
     p.tiles_n = (int)((g.n + ZBN - 1) / ZBN);
     const int64_t tiles = (int64_t)p.tiles_m * p.tiles_n;
     if (tiles > 0x7fffffff) return ACCBLAS_ERR_SHAPE;
-    zgemm_dmma_kernel<AK, BKM, CA, CB, TL><<<(unsigned)tiles, TL::THREADS, TL::SMEM_BYTES, g.stream>>>(mapA, mapB, p);
+    zgemm_dmma_kernel<AK, BKM, CA, CB, TL, FENCED><<<(unsigned)tiles, TL::THREADS, TL::SMEM_BYTES, g.stream>>>(mapA, mapB, p);
     return check_launch("zgemm_dmma_kernel");
 }
 
@@ -823,10 +903,12 @@ int pick_ztile(int64_t m, int64_t n, int64_t k)
 template <bool AK, bool BKM, bool CA, bool CB>
 int launch_zgemm(const GemmArgs &g)
 {
-    switch (pick_ztile(g.m, g.n, g.k)) {
-    case 1:  return launch_zgemm_tile<AK, BKM, CA, CB, ZTile64x64>(g);
-    case 2:  return launch_zgemm_tile<AK, BKM, CA, CB, ZTile32x32>(g);
-    default: return launch_zgemm_tile<AK, BKM, CA, CB, ZTile128x64>(g);
+    const int tile = pick_ztile(g.m, g.n, g.k);
+    const bool fenced = fenced_release(tile == 0);
+    switch (tile) {
+    case 1:  return fenced ? launch_zgemm_tile<AK, BKM, CA, CB, ZTile64x64, true>(g) : launch_zgemm_tile<AK, BKM, CA, CB, ZTile64x64, false>(g);
+    case 2:  return fenced ? launch_zgemm_tile<AK, BKM, CA, CB, ZTile32x32, true>(g) : launch_zgemm_tile<AK, BKM, CA, CB, ZTile32x32, false>(g);
+    default: return fenced ? launch_zgemm_tile<AK, BKM, CA, CB, ZTile128x64, true>(g) : launch_zgemm_tile<AK, BKM, CA, CB, ZTile128x64, false>(g);
     }
 }
 
@@ -868,9 +950,9 @@ bool dgemm_dmma_eligible(const GemmArgs &g)
 
 size_t dgemm_dmma_workspace(const GemmArgs &g)
 {
-    if (g.dtype != ACCBLAS_F64 || !want_streamk(g.m, g.n, g.k, 0.0)) return 0;
-    const long long total = ((g.m + 127) / 128) * ((g.n + 127) / 128) * ((g.k + BK - 1) / BK);
-    return (size_t)std::min<long long>(sm_count(), total) * 128 * 128 * 8 + 4096;     // accumulator slots + flags
+    if (g.dtype != ACCBLAS_F64) return 0;
+    const StreamKPlan pl = plan_streamk(g.m, g.n, g.k);
+    return pl.use ? (size_t)pl.grid * 128 * 128 * 8 + 4096 : 0;                        // accumulator slots + flags
 }
 
 int dgemm_dmma(const GemmArgs &g)

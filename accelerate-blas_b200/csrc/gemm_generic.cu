@@ -26,7 +26,7 @@ template <typename T, bool TA, bool TB>
 __global__ void __launch_bounds__(NT)
 gemm_generic_kernel(int64_t m, int64_t n, int64_t k, int64_t rowsA, int64_t colsA, int64_t rowsB,
                     int64_t colsB, int64_t lda, int64_t ldb, int64_t ldc, bool conjA, bool conjB, Alpha<T> alpha_,
-                    const T *__restrict__ A, const T *__restrict__ B, T *__restrict__ C,
+                    const T *__restrict__ A, const T *__restrict__ B, T *C, BetaC<T> beta, unsigned tiles_n,
                     int64_t strideA, int64_t strideB, int64_t strideC)
 {
     A += (int64_t)blockIdx.z * strideA;                        // strided batch: one product per grid plane
@@ -37,7 +37,8 @@ gemm_generic_kernel(int64_t m, int64_t n, int64_t k, int64_t rowsA, int64_t cols
     __shared__ T Bs[BK][BN + 1];
     const int tid = threadIdx.x;
     const int tx = tid % 16, ty = tid / 16;
-    const int64_t m0 = (int64_t)blockIdx.y * BM, n0 = (int64_t)blockIdx.x * BN;
+    // tiles are flattened onto gridDim.x (2^31 - 1 blocks): no 65535-row-tile limit on m
+    const int64_t m0 = (int64_t)(blockIdx.x / tiles_n) * BM, n0 = (int64_t)(blockIdx.x % tiles_n) * BN;
 
     T acc[TM][TN];
 #pragma unroll
@@ -88,7 +89,11 @@ gemm_generic_kernel(int64_t m, int64_t n, int64_t k, int64_t rowsA, int64_t cols
 #pragma unroll
         for (int j = 0; j < TN; ++j) {
             const int64_t c = n0 + tx + 16 * j;
-            if (c < n) C[r * ldc + c] = mul_s(alpha, acc[i][j]);   // beta = 0: C is never read
+            if (c < n) {
+                T v = mul_s(alpha, acc[i][j]);                 // beta = 0 (the reference's only mode): C is never read
+                if (beta.on()) v = beta.add(v, r, c);
+                C[r * ldc + c] = v;
+            }
         }
     }
 }
@@ -101,14 +106,17 @@ int launch_typed(const GemmArgs &g)
     const bool cb = Scalar<T>::cplx && g.opB == ACCBLAS_OP_H;
     const Alpha<T> alpha = make_alpha<T>(g.alpha, g.alpha_dev);
     const int64_t batch = g.batch > 1 ? g.batch : 1;
-    dim3 grid((unsigned)((g.n + BN - 1) / BN), (unsigned)((g.m + BM - 1) / BM), (unsigned)batch);
-    if (grid.y > 65535u || batch > 65535) return ACCBLAS_ERR_SHAPE;      // callers chunk larger batches
+    const int64_t tiles_n = (g.n + BN - 1) / BN, tiles = tiles_n * ((g.m + BM - 1) / BM);
+    if (tiles > 0x7fffffff || batch > 65535) return ACCBLAS_ERR_SHAPE;   // callers chunk larger batches
+    dim3 grid((unsigned)tiles, 1, (unsigned)batch);
+    const BetaC<T> beta = make_beta<T>(g);
     const T *A = static_cast<const T *>(g.A), *B = static_cast<const T *>(g.B);
     T *C = static_cast<T *>(g.C);
 #define GO(TA_, TB_)                                                                             \
     gemm_generic_kernel<T, TA_, TB_><<<grid, NT, 0, g.stream>>>(g.m, g.n, g.k, g.rowsA, g.colsA,   \
                                                                 g.rowsB, g.colsB, g.lda, g.ldb, g.ldc, ca, cb,  \
-                                                                alpha, A, B, C, g.strideA, g.strideB, g.strideC)
+                                                                alpha, A, B, C, beta, (unsigned)tiles_n,              \
+                                                                g.strideA, g.strideB, g.strideC)
     if (!ta && !tb) GO(false, false);
     else if (!ta && tb) GO(false, true);
     else if (ta && !tb) GO(true, false);
@@ -129,12 +137,13 @@ constexpr int R1_THREADS = 256, R1_ROWS = 8;
 template <typename T>
 __global__ void __launch_bounds__(R1_THREADS)
 gemm_rank1_kernel(int64_t m, int64_t n, int64_t sa, int64_t sb, int64_t ldc, bool conjA, bool conjB, Alpha<T> alpha_,
-                  const T *__restrict__ A, const T *__restrict__ B, T *__restrict__ C, bool vec_ok)
+                  const T *__restrict__ A, const T *__restrict__ B, T *C, BetaC<T> beta, unsigned chunks_n, bool vec_ok)
 {
     const T alpha = alpha_.get();
     constexpr int VEC = 16 / sizeof(T);
-    const int64_t j0 = ((int64_t)blockIdx.x * R1_THREADS + threadIdx.x) * VEC;
-    const int64_t i0 = (int64_t)blockIdx.y * R1_ROWS;
+    // (row group, column chunk) flattened onto gridDim.x: no 65535 limit on m / R1_ROWS
+    const int64_t j0 = ((int64_t)(blockIdx.x % chunks_n) * R1_THREADS + threadIdx.x) * VEC;
+    const int64_t i0 = (int64_t)(blockIdx.x / chunks_n) * R1_ROWS;
     if (j0 >= n) return;
     T b[VEC];
 #pragma unroll
@@ -154,12 +163,19 @@ gemm_rank1_kernel(int64_t m, int64_t n, int64_t sa, int64_t sb, int64_t ldc, boo
         if (full) {
             union { int4 raw; T e[VEC]; } v;
 #pragma unroll
-            for (int e = 0; e < VEC; ++e) v.e[e] = mul_s(a, b[e]);
+            for (int e = 0; e < VEC; ++e) {
+                v.e[e] = mul_s(a, b[e]);
+                if (beta.on()) v.e[e] = beta.add(v.e[e], i, j0 + e);
+            }
             *reinterpret_cast<int4 *>(crow) = v.raw;
         } else {
 #pragma unroll
             for (int e = 0; e < VEC; ++e)
-                if (j0 + e < n) crow[e] = mul_s(a, b[e]);
+                if (j0 + e < n) {
+                    T w = mul_s(a, b[e]);
+                    if (beta.on()) w = beta.add(w, i, j0 + e);
+                    crow[e] = w;
+                }
         }
     }
 }
@@ -175,12 +191,12 @@ int launch_rank1(const GemmArgs &g)
     // op(B) is 1 x n: stored (1 x n) for N, stored (n x 1, pitch ldb) for T/H
     const int64_t sb = g.opB == ACCBLAS_OP_N ? 1 : g.ldb;
     const bool vec_ok = (reinterpret_cast<uintptr_t>(g.C) & 15u) == 0 && (g.ldc % VEC) == 0;
-    dim3 grid((unsigned)((g.n + (int64_t)R1_THREADS * VEC - 1) / ((int64_t)R1_THREADS * VEC)),
-              (unsigned)((g.m + R1_ROWS - 1) / R1_ROWS));
-    if (grid.y > 65535u) return gemm_generic(g);               // enormous m: the tiled kernel's grid fits
-    gemm_rank1_kernel<T><<<grid, R1_THREADS, 0, g.stream>>>(g.m, g.n, sa, sb, g.ldc, ca, cb, alpha,
+    const int64_t chunks_n = (g.n + (int64_t)R1_THREADS * VEC - 1) / ((int64_t)R1_THREADS * VEC);
+    const int64_t blocks = chunks_n * ((g.m + R1_ROWS - 1) / R1_ROWS);
+    if (blocks > 0x7fffffff) return gemm_generic(g);
+    gemm_rank1_kernel<T><<<(unsigned)blocks, R1_THREADS, 0, g.stream>>>(g.m, g.n, sa, sb, g.ldc, ca, cb, alpha,
                                                             static_cast<const T *>(g.A), static_cast<const T *>(g.B),
-                                                            static_cast<T *>(g.C), vec_ok);
+                                                            static_cast<T *>(g.C), make_beta<T>(g), (unsigned)chunks_n, vec_ok);
     return check_launch("gemm_rank1_kernel");
 }
 

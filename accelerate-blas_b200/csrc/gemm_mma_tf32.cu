@@ -82,6 +82,8 @@ struct SgemmMmaParams {
     int64_t m, n, k, ldc;
     Alpha<float> alpha;        // real kernels
     Alpha<float2> calpha;      // complex kernels
+    BetaC<float> beta;         // + beta * Cin (accblas_gemm_ex)
+    BetaC<float2> cbeta;
     float *C;
     int tiles_m, tiles_n;
 };
@@ -240,8 +242,12 @@ sgemm_mma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
 #pragma unroll
             for (int j = 0; j < NJ; ++j) {
                 const int64_t c = n0 + wn * NJ * 8 + j * 8 + 2 * t;
-                const float v0 = alr * (tot[i][j][2 * hr] + acc[i][j][2 * hr]);
-                const float v1 = alr * (tot[i][j][2 * hr + 1] + acc[i][j][2 * hr + 1]);
+                float v0 = alr * (tot[i][j][2 * hr] + acc[i][j][2 * hr]);
+                float v1 = alr * (tot[i][j][2 * hr + 1] + acc[i][j][2 * hr + 1]);
+                if (p.beta.on()) {
+                    if (c < p.n) v0 = p.beta.add(v0, r, c);
+                    if (c + 1 < p.n) v1 = p.beta.add(v1, r, c + 1);
+                }
                 if (vec) {
                     if (c < p.n) *reinterpret_cast<float2 *>(crow + c) = make_float2(v0, v1);
                 } else {
@@ -406,7 +412,9 @@ cgemm_mma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                     if (c < p.n) {
                         const float xr = tre[i][j][2 * hr + e] + are[i][j][2 * hr + e];
                         const float xi = tim[i][j][2 * hr + e] + aim[i][j][2 * hr + e];
-                        crow[c] = make_float2(al.x * xr - al.y * xi, al.x * xi + al.y * xr);
+                        float2 v = make_float2(al.x * xr - al.y * xi, al.x * xi + al.y * xr);
+                        if (p.cbeta.on()) v = p.cbeta.add(v, r, c);
+                        crow[c] = v;
                     }
                 }
         }
@@ -434,6 +442,7 @@ int launch_sgemm_mma(const GemmArgs &g)
     SgemmMmaParams p;
     p.m = g.m; p.n = g.n; p.k = g.k; p.ldc = g.ldc;
     p.alpha = make_alpha<float>(g.alpha, g.alpha_dev); p.calpha = Alpha<float2>{make_float2(0.f, 0.f), nullptr};
+    p.beta = make_beta<float>(g); p.cbeta = BetaC<float2>{nullptr, 0, make_float2(0.f, 0.f)};
     p.C = static_cast<float *>(g.C);
     p.tiles_m = (int)((g.m + BM - 1) / BM);
     p.tiles_n = (int)((g.n + BN - 1) / BN);
@@ -460,6 +469,7 @@ int launch_cgemm_mma(const GemmArgs &g)
     SgemmMmaParams p;
     p.m = g.m; p.n = g.n; p.k = g.k; p.ldc = g.ldc;
     p.calpha = make_alpha<float2>(g.alpha, g.alpha_dev); p.alpha = Alpha<float>{0.f, nullptr};
+    p.cbeta = make_beta<float2>(g); p.beta = BetaC<float>{nullptr, 0, 0.f};
     p.C = static_cast<float *>(g.C);
     p.tiles_m = (int)((g.m + BM - 1) / BM);
     p.tiles_n = (int)((g.n + BN - 1) / BN);

@@ -210,6 +210,7 @@ struct Combine3Args {
     float2 *C;
     int64_t m, n, ldt, ldc;
     Alpha<float2> alpha;
+    BetaC<float2> beta;
 };
 
 // one thread = four consecutive columns: three 16-byte loads, two 16-byte stores (when C allows)
@@ -231,6 +232,7 @@ __global__ void __launch_bounds__(256) combine3_kernel(const Combine3Args a)
         for (int e = 0; e < 4; ++e) {
             const float xr = x1[e] - x2[e], xi = (x3[e] - x1[e]) - x2[e];
             out[e] = make_float2(al.x * xr - al.y * xi, al.x * xi + al.y * xr);
+            if (a.beta.on() && c + e < a.n) out[e] = a.beta.add(out[e], r, c + e);
         }
         float2 *dst = a.C + r * a.ldc + c;
         if (vec && c + 4 <= a.n) {
@@ -314,6 +316,8 @@ struct SgemmParams {
     int64_t ldc;           // floats
     float *C;
     Alpha<float2> alpha;   // (re, im); im = 0 for real
+    BetaC<float> beta;     // + beta * Cin on the float view (real types; complex beta: cbeta over the same floats)
+    float2 cbeta;          // complex beta (cplx = 1), applied to (re, im) column pairs of Cin
     int cplx;              // 1: columns are (re,im) pairs, alpha is complex
     int tiles_m, tiles_n;
     // plane batching (3M): the grid holds `planes` independent products of the same extents whose operands are
@@ -500,6 +504,22 @@ sgemm_tf32x3_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_con
 #pragma unroll
                 for (int i = 0; i < HALF; ++i) acc[i] *= al.x;
             }
+            if (p.beta.on()) {                                     // + beta * Cin (accblas_gemm_ex): one row of Cin per thread
+                const float *cin = p.beta.cin + row * p.beta.ld + col0;
+                if (p.cplx) {
+#pragma unroll
+                    for (int i = 0; i < HALF; i += 2)
+                        if (col0 + i < p.N) {                      // N is even for complex: a started pair is whole
+                            const float cr = cin[i], ci = cin[i + 1];
+                            acc[i] += p.cbeta.x * cr - p.cbeta.y * ci;
+                            acc[i + 1] += p.cbeta.x * ci + p.cbeta.y * cr;
+                        }
+                } else {
+#pragma unroll
+                    for (int i = 0; i < HALF; ++i)
+                        if (col0 + i < p.N) acc[i] = fmaf(p.beta.beta, cin[i], acc[i]);
+                }
+            }
             if (vec4) {
 #pragma unroll
                 for (int i = 0; i < HALF; i += 4)
@@ -597,6 +617,14 @@ int launch_tc(const GemmArgs &g, const TcPlan &t, float *ahi, float *alo, float 
     if (g.alpha_dev) p.alpha = Alpha<float2>{make_float2(0.f, 0.f), static_cast<const float2 *>(g.alpha)};
     else p.alpha = Alpha<float2>{make_float2(static_cast<const float *>(g.alpha)[0],
                                             p.cplx ? static_cast<const float *>(g.alpha)[1] : 0.f), nullptr};
+    p.beta = BetaC<float>{nullptr, 0, 0.f};
+    p.cbeta = make_float2(0.f, 0.f);
+    if (planes == 1 && has_beta(g)) {                              // (the 3M planes take beta in combine3)
+        p.beta.cin = static_cast<const float *>(g.Cin);
+        p.beta.ld = (p.cplx ? 2 : 1) * (g.ldcin ? g.ldcin : g.ldc);
+        p.beta.beta = static_cast<const float *>(g.beta)[0];
+        if (p.cplx) p.cbeta = make_float2(static_cast<const float *>(g.beta)[0], static_cast<const float *>(g.beta)[1]);
+    }
     p.tiles_m = (int)((t.M + TBM - 1) / TBM);
     p.tiles_n = (int)((t.N + TBN - 1) / TBN);
     const int64_t tiles = (int64_t)p.tiles_m * p.tiles_n * planes;
@@ -637,7 +665,7 @@ int cgemm_3m_run(const GemmArgs &g)
     const Tc3Plan q = make_plan3(g);
     const size_t pa = q.t.plane_a, pb = q.t.plane_b, pt = q.plane_t;
     char *ws = nullptr;
-    if (cudaMallocAsync(reinterpret_cast<void **>(&ws), 6 * (pa + pb) + 3 * pt, g.stream) != cudaSuccess) {
+    if (scratch_alloc(reinterpret_cast<void **>(&ws), 6 * (pa + pb) + 3 * pt, g.stream) != cudaSuccess) {
         (void)cudaGetLastError();                          // no room for 3M's planes: the 4M embedding needs a third of them
         return sgemm_tc(g);
     }
@@ -671,6 +699,7 @@ int cgemm_3m_run(const GemmArgs &g)
         GemmArgs h = g;
         h.dtype = ACCBLAS_F32;
         h.alpha = &one; h.alpha_dev = false;
+        h.beta = nullptr; h.Cin = nullptr;
         h.C = wt; h.ldc = q.ldt;
         const int ra = (int)q.rows_a, rb = (int)q.rows_b;
         const int64_t sc = (int64_t)(pt / 4);
@@ -684,6 +713,7 @@ int cgemm_3m_run(const GemmArgs &g)
         c.C = static_cast<float2 *>(g.C);
         c.m = g.m; c.n = g.n; c.ldt = q.ldt; c.ldc = g.ldc;
         c.alpha = make_alpha<float2>(g.alpha, g.alpha_dev);
+        c.beta = make_beta<float2>(g);
         const int64_t total = c.m * (c.ldt / 4);
         const int64_t want = (total + 255) / 256, cap = (int64_t)sm_count() * 32;
         combine3_kernel<<<(unsigned)std::max<int64_t>(1, std::min(want, cap)), 256, 0, g.stream>>>(c);
@@ -719,7 +749,7 @@ int sgemm_tc(const GemmArgs &g)
     const TcPlan t = make_plan(g);
     const bool cx = g.dtype == ACCBLAS_C32;
     char *ws = nullptr;
-    ACC_CUDA(cudaMallocAsync(reinterpret_cast<void **>(&ws), 2 * (t.plane_a + t.plane_b), g.stream));
+    ACC_CUDA(scratch_alloc(reinterpret_cast<void **>(&ws), 2 * (t.plane_a + t.plane_b), g.stream));
     float *ahi = reinterpret_cast<float *>(ws), *alo = reinterpret_cast<float *>(ws + t.plane_a);
     float *bhi = reinterpret_cast<float *>(ws + 2 * t.plane_a), *blo = reinterpret_cast<float *>(ws + 2 * t.plane_a + t.plane_b);
 

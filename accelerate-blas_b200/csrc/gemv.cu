@@ -309,7 +309,7 @@ int gemv_typed(cudaStream_t st, int opA, int64_t rowsA, int64_t colsA, const voi
     splits = (rowsA + rps - 1) / rps;
     const bool direct = splits == 1;
     T *partial = nullptr;
-    if (!direct) ACC_CUDA(cudaMallocAsync(reinterpret_cast<void **>(&partial), sizeof(T) * (size_t)splits * (size_t)colsA, st));
+    if (!direct) ACC_CUDA(scratch_alloc(reinterpret_cast<void **>(&partial), sizeof(T) * (size_t)splits * (size_t)colsA, st));
     dim3 grid((unsigned)gx, (unsigned)splits);
     T *out = direct ? y : partial;
 #define GO(CJ, AL) gemv_t_kernel<T, CJ, AL><<<grid, GT_THREADS, 0, st>>>(rowsA, colsA, rps, alpha, A, x, out, direct)

@@ -29,7 +29,7 @@ struct Scratch {
     void *p = nullptr;
     cudaStream_t s;
     explicit Scratch(cudaStream_t st) : s(st) {}
-    cudaError_t alloc(size_t bytes) { return cudaMallocAsync(&p, bytes ? bytes : 1, s); }
+    cudaError_t alloc(size_t bytes) { return scratch_alloc(&p, bytes, s); }
     ~Scratch() { if (p) cudaFreeAsync(p, s); }
 };
 

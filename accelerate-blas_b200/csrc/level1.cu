@@ -223,7 +223,7 @@ int sdot_typed(cudaStream_t st, int64_t n, const void *z_host, const T *x, const
     const bool al = aligned16(x) && aligned16(y);
     const int grid = grid_for<T>(n, al);
     W *partial = nullptr;
-    if (grid > 1) ACC_CUDA(cudaMallocAsync(reinterpret_cast<void **>(&partial), sizeof(W) * (size_t)grid, st));
+    if (grid > 1) ACC_CUDA(scratch_alloc(reinterpret_cast<void **>(&partial), sizeof(W) * (size_t)grid, st));
     if (al) sdot_partial_kernel<T, true><<<grid, L1_THREADS, 0, st>>>(n, x, y, z, partial, out);
     else    sdot_partial_kernel<T, false><<<grid, L1_THREADS, 0, st>>>(n, x, y, z, partial, out);
     int s = check_launch("sdot_partial_kernel");
@@ -285,7 +285,7 @@ int asum_typed(cudaStream_t st, int64_t n, const T *x, void *out_v)
     const bool al = aligned16(x);
     const int grid = grid_for<T>(n, al);
     double *partial = nullptr;
-    if (grid > 1) ACC_CUDA(cudaMallocAsync(reinterpret_cast<void **>(&partial), sizeof(double) * (size_t)grid, st));
+    if (grid > 1) ACC_CUDA(scratch_alloc(reinterpret_cast<void **>(&partial), sizeof(double) * (size_t)grid, st));
     if (al) asum_partial_kernel<T, true><<<grid, L1_THREADS, 0, st>>>(n, x, partial, out);
     else    asum_partial_kernel<T, false><<<grid, L1_THREADS, 0, st>>>(n, x, partial, out);
     int s = check_launch("asum_partial_kernel");
@@ -393,7 +393,7 @@ int iamax_typed(cudaStream_t st, int64_t n, const T *x, int64_t *out)
     char *ws = nullptr;
     R *pv = nullptr; int64_t *pi = nullptr;
     if (grid > 1) {
-        ACC_CUDA(cudaMallocAsync(reinterpret_cast<void **>(&ws), 16 * (size_t)grid, st));
+        ACC_CUDA(scratch_alloc(reinterpret_cast<void **>(&ws), 16 * (size_t)grid, st));
         pi = reinterpret_cast<int64_t *>(ws);
         pv = reinterpret_cast<R *>(ws + 8 * (size_t)grid);
     }

@@ -136,15 +136,21 @@ def _ptr(t) -> ctypes.c_void_p:
 # ------------------------------------------------------------------------------------
 # Level 3
 # ------------------------------------------------------------------------------------
-def gemm(alpha, opA, A, opB, B, out=None):
+def gemm(alpha, opA, A, opB, B, out=None, beta=None, Cin=None):
     """``C = alpha * op(A) * op(B)`` -- gemm, BLAS/Level3.hs:57-64.
 
     shape op(A) = (m, k), shape op(B) = (k, n), shape C = (m, n); stored shapes are pre-op.
     ``out`` (device path only): a contiguous (m, n) tensor to write instead of allocating one.
+    ``beta``, ``Cin`` (device path only; not in the reference, whose hook fixes beta = 0): adds ``beta * Cin``
+    in the kernel's epilogue (accblas_gemm_ex).  ``Cin`` may be ``out`` itself (accumulate in place).
     """
     oa, ob = _op(opA), _op(opB)
     code = _code(A)
     L = lib()
+    if beta is not None and Cin is None:
+        raise ValueError("gemm: beta needs Cin")
+    if Cin is not None and not (_is_torch(A) and not _alpha_on_device(alpha, code)):
+        raise ValueError("gemm: beta / Cin are taken on the device path with a host alpha only")
     if _is_torch(A) and _alpha_on_device(alpha, code):
         torch = _torch()
         A = _dev_operand(A, code, 2, "gemm: A")
@@ -173,6 +179,16 @@ def gemm(alpha, opA, A, opB, B, out=None):
                     raise ValueError("gemm: out must be a CUDA tensor of shape (m, n) and A's dtype with dense rows")
                 C = out
             ldc = C.stride(0) if (m > 0 and n > 0 and not C.is_contiguous()) else n
+            if Cin is not None:
+                if tuple(Cin.shape) != (m, n) or Cin.dtype != A.dtype or not Cin.is_cuda or \
+                        not (Cin.is_contiguous() or _row_strided(Cin)):
+                    raise ValueError("gemm: Cin must be a CUDA tensor of shape (m, n) and A's dtype with dense rows")
+                ldcin = Cin.stride(0) if (m > 0 and n > 0 and not Cin.is_contiguous()) else n
+                be_keep, be = _alpha_buf(1 if beta is None else beta, code)
+                st = L.accblas_gemm_ex(_stream(A), code, oa, ob, A.shape[0], A.shape[1], B.shape[0], B.shape[1],
+                                       al, _ptr(A), lda, _ptr(B), ldb, be, _ptr(Cin), ldcin, _ptr(C), ldc)
+                _ffi.check(st, "accblas_gemm_ex")
+                return C
             if lda == A.shape[1] and ldb == B.shape[1] and ldc == n:
                 st = L.accblas_gemm(_stream(A), code, oa, ob, A.shape[0], A.shape[1], B.shape[0], B.shape[1],
                                     al, _ptr(A), _ptr(B), _ptr(C))
@@ -392,6 +408,17 @@ def kernel_name(dtype_code: int, opA, opB, shapeA, shapeB) -> str:
                                           shapeB[0], shapeB[1]).decode()
 
 
+def workspace_bytes(dtype_code: int, opA, opB, shapeA, shapeB) -> int:
+    """Stream-ordered scratch accblas_gemm takes from the library's pool for this problem."""
+    return int(lib().accblas_gemm_workspace_bytes(dtype_code, _op(opA), _op(opB), shapeA[0], shapeA[1],
+                                                  shapeB[0], shapeB[1]))
+
+
+def trim_workspace() -> None:
+    """Return the library's cached scratch to the driver (accblas_trim_workspace)."""
+    _ffi.check(lib().accblas_trim_workspace(), "accblas_trim_workspace")
+
+
 def launch_count() -> int:
     return int(lib().accblas_launch_count())
 
@@ -407,7 +434,8 @@ TUNE_SGEMM_FAMILY, TUNE_SMMA_TILE, TUNE_HOST_PIPELINE, TUNE_RASTER_GROUP, TUNE_H
 TUNE_TC_TILE = 8        # tcgen05 f32/c32 gemm CTA tile: 0 = 128x256, 1 = 128x128, 2 = 128x64
 TUNE_CGEMM_3M = 9       # c32 gemm on tcgen05: 0 = 4M real embedding, 1 = 3M whenever possible, -1 = cost model
 TUNE_SNAKE_K = 10       # f64 gemm: 0 = every tile walks K forwards
-TUNE_STREAMK = 11       # f64 gemm: 0 = never stream-K, 1 = whenever possible
+TUNE_STREAMK = 11       # f64 gemm: 0 = never the persistent kernel, 1 = whole-tile rounds + stream-K tail, 2 = pure stream-K
+TUNE_RELEASE = 12       # f64/c64 gemm stage release: 0 = fenced everywhere, 1 = __syncwarp only everywhere
 TUNE_ZGEMM_3M = 7       # 0: complex-double gemm always 4M in registers, 1: 3M whenever possible, -1: cost model
 
 

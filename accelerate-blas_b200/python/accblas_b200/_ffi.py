@@ -14,7 +14,8 @@ LIB_PATH = os.environ.get("ACCBLAS_B200_LIB", os.path.join(PKG_ROOT, "lib", "lib
 
 # every symbol include/accblas_b200.h declares (tests/test_abi.py checks this list against the header)
 SYMBOLS = (
-    "accblas_gemm", "accblas_gemm_ld", "accblas_gemm_strided_batched", "accblas_gemm_alpha_dev", "accblas_gemv_alpha_dev", "accblas_gemm_workspace_bytes", "accblas_gemv", "accblas_dot",
+    "accblas_gemm", "accblas_gemm_ld", "accblas_gemm_ex", "accblas_last_cuda_error_r", "accblas_launch_count_total",
+    "accblas_trim_workspace", "accblas_workspace_cached_bytes", "accblas_gemm_strided_batched", "accblas_gemm_alpha_dev", "accblas_gemv_alpha_dev", "accblas_gemm_workspace_bytes", "accblas_gemv", "accblas_dot",
     "accblas_gemm_host", "accblas_gemv_host", "accblas_dot_host",
     "accblas_sdot", "accblas_asum", "accblas_amax", "accblas_amin",
     "accblas_sdot_host", "accblas_asum_host", "accblas_amax_host", "accblas_amin_host",
@@ -56,6 +57,15 @@ def lib() -> ctypes.CDLL:
     L.accblas_gemm_host.argtypes = L.accblas_gemm.argtypes
     L.accblas_gemm_ld.argtypes = [vp, ci, ci, ci, i64, i64, i64, i64, vp, vp, i64, vp, i64, vp, i64]
     L.accblas_gemm_ld.restype = ci
+    L.accblas_gemm_ex.argtypes = [vp, ci, ci, ci, i64, i64, i64, i64, vp, vp, i64, vp, i64, vp, vp, i64, vp, i64]
+    L.accblas_gemm_ex.restype = ci
+    L.accblas_last_cuda_error_r.argtypes = [ctypes.c_char_p, sz]
+    L.accblas_last_cuda_error_r.restype = sz
+    L.accblas_launch_count_total.restype = ctypes.c_uint64
+    L.accblas_trim_workspace.argtypes = []
+    L.accblas_trim_workspace.restype = ci
+    L.accblas_workspace_cached_bytes.argtypes = []
+    L.accblas_workspace_cached_bytes.restype = sz
     L.accblas_gemm_strided_batched.argtypes = [vp, ci, ci, ci, i64, i64, i64, i64, vp, vp, i64, vp, i64, vp, i64, i64]
     L.accblas_gemm_strided_batched.restype = ci
     L.accblas_gemv.argtypes = [vp, ci, ci, i64, i64, vp, vp, vp, i64, vp]

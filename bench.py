@@ -12,8 +12,12 @@ N > 1  workload = configs[4]: Double gemm n = 32768 row-sharded over the ranks (
 --impl reference   the reference's llvm-native path (one cblas_dgemm RowMajor call,
        LLVM/Native/Level3.hs:85) on the host cores through oracle/openblas_ref.py (kind "port":
        the reference is Haskell and cannot be built here; OpenBLAS is the library it calls).
-One JSON line on stdout (rank 0).  Extra per-case numbers (sgemm, zgemm, gemv, dot) go into
-"extras" when --extras is given; they are not the headline.
+One JSON line on stdout (rank 0).  At N = 1 the line also carries "extras": every other BASELINE.json config
+(sgemm 8192^3 NN/NT/TN, dgemm NT/TN, zgemm / cgemm 4096^3 HN, dgemv 32768^2 N/T, ddot 2^28, dgemm 1024^3 and the
+own single-GPU time of the 32768^3 product), each with its time, rate, roofline fraction against a stated
+denominator, a clock sample taken during the case, an oracle check on sampled rows / entries, and the cuBLAS time
+of the same call made the reference's way (baseline/cublas_ref as a subprocess: a reported number, never a
+dependency of the library).  --no-extras skips them (developer loop).
 """
 import argparse
 import json
@@ -125,55 +129,60 @@ def dmma_peak_live():
 # --------------------------------------------------------------------------------------
 # CPU arm: the reference's llvm-native path (cblas_dgemm RowMajor) on the host cores
 # --------------------------------------------------------------------------------------
-def cpu_dgemm_sample(n, budget_s=12.0):
-    """Times cblas_dgemm(RowMajor, N, N) on a bounded sample of the workload: the first `rows` rows
-    of A against the full B (same k, n; TFLOP/s of a large dgemm does not depend on m)."""
+def cpu_dgemm(n, rows=None, reps=3):
+    """cblas_dgemm(RowMajor, N, N), the reference's llvm-native call (LLVM/Native/Level3.hs:84-87), on all host
+    cores.  rows = None: the FULL n^3 product (0.8 s at n = 8192 on 16 cores); rows = r: the first r rows of A
+    against the full n x n B -- the bounded sample used when the full product would take minutes (n = 32768)."""
     import numpy as np
     from oracle import openblas_ref as R
     cores = R.host_cores()
     R.set_threads(cores)
-    rows = 2048 if n >= 4096 else n
+    m = n if rows is None else rows
     rng = np.random.default_rng(0x5EED0000 + 16)
-    A = rng.uniform(-1, 1, size=(rows, n))
+    A = rng.uniform(-1, 1, size=(m, n))
     B = rng.uniform(-1, 1, size=(n, n))
-    C = np.empty((rows, n))
+    C = np.empty((m, n))
     R.gemm(1.0, "N", A, "N", B, out=C)          # warm-up (thread pool, page faults)
     ts = []
-    t_all = time.perf_counter()
-    while len(ts) < 3 or (time.perf_counter() - t_all < budget_s and len(ts) < 20):
+    for _ in range(reps):
         t = time.perf_counter()
         R.gemm(1.0, "N", A, "N", B, out=C)
         ts.append(time.perf_counter() - t)
     best = min(ts)
-    return {"value": round(2.0 * rows * n * n / best * 1e-12, 4), "unit": "TFLOP/s", "cores": cores,
-            "kind": "port",
-            "sample": f"cblas_dgemm RowMajor NN, first {rows} rows of A x B {n}x{n} (k=n={n}), best of {len(ts)}, "
-                      f"OpenBLAS {R.config().split()[1]} via scipy"}, rows, (A, B, C)
+    what = f"the full {n}^3 product" if rows is None else f"rows 0..{m - 1} of A ({m} x {n}) x B {n} x {n}"
+    return {"value": round(2.0 * m * n * n / best * 1e-12, 4), "unit": "TFLOP/s", "cores": cores, "kind": "port",
+            "sample": f"cblas_dgemm RowMajor NN, {what}, best of {len(ts)} ({best * 1e3:.0f} ms), "
+                      f"OpenBLAS {R.config().split()[1]} via scipy, {cores} threads"}, m, (A, B, C)
 
 
 def run_reference(args):
-    """--impl reference: K timed steps of the CPU path on the same config/metric."""
+    """--impl reference: K timed steps of the CPU path on the same config/metric.  N = 1: every step is the FULL
+    8192^3 cblas_dgemm.  N > 1 (32768^3, ~50 s per product on 16 cores): every step is a 512-row slice of the
+    product against the full 32768^2 B -- same k and n, throughput per flop is that of the whole product."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     from oracle import openblas_ref as R
-    n = N1 if args.gpus == 1 else NMG
-    info, rows, (A, B, C) = cpu_dgemm_sample(N1, budget_s=1.0)
-    for _ in range(max(args.warmup, 1)):
+    n = N1 if args.gpus == 1 else args.n_mg
+    info, rows, (A, B, C) = cpu_dgemm(n, rows=None if args.gpus == 1 else min(512, n), reps=1)
+    for _ in range(max(args.warmup - 1, 0)):
         R.gemm(1.0, "N", A, "N", B, out=C)
     t0 = time.perf_counter()
     for _ in range(args.steps):
         R.gemm(1.0, "N", A, "N", B, out=C)
     dt = time.perf_counter() - t0
-    tf = 2.0 * rows * N1 * N1 * args.steps / dt * 1e-12
+    tf = 2.0 * rows * n * n * args.steps / dt * 1e-12
     info["value"] = round(tf, 4)
-    info["sample"] = (f"each step = cblas_dgemm RowMajor NN on rows 0..{rows - 1} of A x B {N1}x{N1}; "
-                      f"throughput of the {n}^3 product is the same per flop; OpenBLAS via scipy, {info['cores']} threads")
+    info["sample"] = ((f"each step = the full {n}^3 cblas_dgemm RowMajor NN" if rows == n else
+                       f"each step = cblas_dgemm RowMajor NN on rows 0..{rows - 1} of A ({rows} x {n}) x B {n} x {n}: "
+                       f"a bounded sample of the {n}^3 product (same k, n; {2.0 * n ** 3 / (tf * 1e12):.0f} s for the whole)")
+                      + f"; OpenBLAS via scipy, {info['cores']} threads")
     line = {"impl": "reference", "metric": METRIC, "value": round(tf, 4), "unit": "TFLOP/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(dt / args.steps * 1e3, 3),
             "higher_is_better": True, "scaling": "weak" if args.gpus == 1 else "strong", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic uniform(-1,1)",
-            "config": workload_config(args.gpus), "cpu_baseline": info,
+            "config": workload_config(args.gpus) | ({"m": n, "n": n, "k": n} if args.gpus > 1 else {}),
+            "cpu_baseline": info,
             "e2e": {"value": round(tf, 4), "unit": "TFLOP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
@@ -212,6 +221,9 @@ def run_single(args):
     A = seeded((n, n), 0x5EED0000 + 16 + 0, dev)
     B = seeded((n, n), 0x5EED0000 + 16 + 1, dev)
     assert ab.kernel_name(1, "N", "N", A.shape, B.shape) == "dgemm_dmma_tma"
+    persistent = ab.workspace_bytes(1, "N", "N", A.shape, B.shape) > 0
+    kernel_desc = ("dgemm_dmma_streamk_kernel<true,false> (persistent: 27 whole-tile rounds + stream-K tail, 128x128 tiles)"
+                   if persistent else "dgemm_dmma_kernel<true,false,Tile128x128>")
 
     # ---- device-resident: W warm-ups, then exactly K timed steps ----
     for _ in range(args.warmup):
@@ -258,7 +270,7 @@ def run_single(args):
                                  ctypes.c_void_p(Ah.data_ptr()), ctypes.c_void_p(Bh.data_ptr()),
                                  ctypes.c_void_p(Ch.data_ptr()))
         assert st == 0, st
-    e2e_steps = max(3, min(args.steps, 10))
+    e2e_steps = args.steps
     for _ in range(2):
         e2e_step()
     torch.cuda.synchronize()
@@ -274,8 +286,10 @@ def run_single(args):
     del Ah, Bh, Ch
 
     peak, peak_src = dmma_peak_live()
-    cpu, _, _ = cpu_dgemm_sample(n)
+    cpu, _, _ = cpu_dgemm(n, reps=3)
     mp = measured_peaks()
+    del A, B, C
+    torch.cuda.empty_cache()
     line = {
         "metric": METRIC, "value": round(value, 3), "unit": "TFLOP/s", "n_gpus": 1, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": round(total_ms / args.steps, 4), "higher_is_better": True,
@@ -285,7 +299,7 @@ def run_single(args):
                      "unit": "TFLOP/s", "frac": round(flops / kernel_ms * 1e-9 / peak, 4), "traffic": ncu_traffic(),
                      "traffic_unit": "bytes per launch (dram read + write, profiles/r01_dgemm_nn_8192_ncu.txt); "
                                      "algorithmic bytes 1 610 612 736",
-                     "kernel": "dgemm_dmma_kernel<true,false,Tile128x128>", "flops_per_launch": flops,
+                     "kernel": kernel_desc, "flops_per_launch": flops,
                      "peak_source": peak_src + "; MEASURED_PEAKS.json carries no FP64 figure "
                                     f"(its bf16 {mp.get('bf16_tflops')} TFLOP/s is a different pipe); nominal FP64 37-40"},
         "cpu_baseline": cpu,
@@ -296,7 +310,7 @@ def run_single(args):
         "parity": {"error_units": round(err, 5), "tolerance_units": 1.0, "rows_checked": len(rows)},
     }
     if args.extras:
-        line["extras"] = extras()
+        line["extras"] = extras(peak, peak_src, mp, total_ms / args.steps)
     print(json.dumps(line), flush=True)
 
 
@@ -463,27 +477,194 @@ def mg_level12_extras(dev, rank, world, iters=20):
     return out
 
 
-def extras():
-    """Other BASELINE.json configs, one short measurement each (not the headline)."""
+def cublas_arm(cases, iters=8):
+    """The reference's llvm-ptx path (cublas?gemm / ?gemv called its way, LLVM/PTX/Level3.hs:91-106, Level2.hs:109-124)
+    for the same shapes, from baseline/cublas_ref run as a SUBPROCESS: a reported number beside ours, never linked
+    into the library.  Returns {case name: median ms}."""
+    exe = os.path.join(ROOT, "baseline", "cublas_ref")
+    out = {}
+    if not os.path.exists(exe):
+        return out
+    try:
+        res = subprocess.run([exe, ",".join(cases), str(iters)], capture_output=True, text=True, timeout=240)
+        for l in res.stdout.splitlines():
+            if l.startswith("{"):
+                d = json.loads(l)
+                out[d["case"]] = d
+    except Exception as e:      # the baseline is optional; its absence must not fail the product's bench
+        out["error"] = repr(e)
+    return out
+
+
+def extras(dmma_peak, dmma_src, mp, headline_ms):
+    """Every other BASELINE.json config at N = 1 (configs[0..3] and the T1 of configs[4]); see the module docstring."""
+    import numpy as np
     import torch
-    sys.path.insert(0, os.path.join(ROOT, "tools"))
-    import io
-    import contextlib
-    import perf
-    buf = io.StringIO()
-    with contextlib.redirect_stdout(buf):
-        for ops in ("NT", "TN"):
-            perf.gemm_case("f64", ops[0], ops[1], N1, N1, N1, 3)
-        for ops in ("NN", "NT", "TN"):
-            perf.gemm_case("f32", ops[0], ops[1], N1, N1, N1, 3)
-        perf.gemm_case("f64", "N", "N", 1024, 1024, 1024, 20)
-        perf.gemm_case("c64", "H", "N", 4096, 4096, 4096, 3)
-        perf.gemm_case("c32", "H", "N", 4096, 4096, 4096, 3)
-        perf.gemv_case("f64", "N", 32768, 32768, 20)
-        perf.gemv_case("f64", "T", 32768, 32768, 20)
-        perf.dot_case("f64", 1 << 28, 20)
-    torch.cuda.synchronize()
-    return [json.loads(l) for l in buf.getvalue().splitlines() if l.startswith("{")]
+    import accblas_b200 as ab
+    from oracle import oracle as O
+    dev = torch.device("cuda:0")
+    hbm = float(mp.get("hbm_gbs") or 6553.0)
+    bf16 = float(mp.get("bf16_tflops") or 1598.1)
+    tf32x3_peak = bf16 / 2.0 / 3.0
+    TD = {"f32": torch.float32, "f64": torch.float64, "c32": torch.complex64, "c64": torch.complex128}
+    CODE = {"f32": O.F32, "f64": O.F64, "c32": O.C32, "c64": O.C64}
+    ES = {"f32": 4, "f64": 8, "c32": 8, "c64": 16}
+    CB = {"f32": "s", "f64": "d", "c32": "c", "c64": "z"}
+
+    def rnd(shape, dt, seed):
+        g = torch.Generator(device=dev).manual_seed(seed)
+        base = torch.float32 if dt in ("f32", "c32") else torch.float64
+        if dt in ("c32", "c64"):
+            return torch.view_as_complex(torch.rand(tuple(shape) + (2,), dtype=base, device=dev, generator=g) * 2 - 1)
+        return torch.rand(shape, dtype=base, device=dev, generator=g) * 2 - 1
+
+    def timed(fn, min_s, est_ms, lo=3, hi=400):
+        """median / best per-call device time, calls enqueued back to back (events between calls), with the
+        clocks sampled during the run; enough iterations for >= min_s seconds so the 100 ms sampler sees it"""
+        iters = int(max(lo, min(hi, min_s * 1e3 / max(est_ms, 1e-3))))
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        sampler = ClockSampler(0).start()
+        time.sleep(0.15)
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(iters + 1)]
+        t0 = time.time()
+        ev[0].record()
+        for i in range(iters):
+            fn()
+            ev[i + 1].record()
+        torch.cuda.synchronize()
+        t1 = time.time()
+        clocks = sampler.stop(t0, t1)
+        ts = sorted(ev[i].elapsed_time(ev[i + 1]) for i in range(iters))
+        return ts[len(ts) // 2], ts[0], iters, clocks
+
+    # the headline itself, so that its cuBLAS time sits in the same record
+    out = [{"case": f"f64gemm_NN_{N1}x{N1}x{N1}", "kernel": "dgemm_dmma_tma", "ms": round(headline_ms, 4),
+            "tflops": round(2.0 * N1 ** 3 / headline_ms * 1e-9, 3), "note": "the headline step (value / ms_per_step of this line)",
+            "cublas_case": f"dgemm_NN_{N1}x{N1}x{N1}"}]
+    cublas_cases = [f"dgemm_NN_{N1}x{N1}x{N1}"]
+
+    def gemm_case(dt, oa, ob, n, est_ms, seed, rows=4, min_s=0.45, check_cols=None):
+        A, B = rnd((n, n), dt, seed), rnd((n, n), dt, seed + 1)
+        name = ab.kernel_name(CODE[dt], oa, ob, A.shape, B.shape)
+        box = {}
+        med, best, iters, clocks = timed(lambda: box.__setitem__("C", ab.gemm(1, oa, A, ob, B)), min_s, est_ms)
+        C = box["C"]
+        cplx = dt[0] == "c"
+        flops = (8.0 if cplx else 2.0) * n ** 3
+        # parity: sampled rows (and, for the 32768^3 product, sampled columns) against the wide oracle
+        ridx = [0, n - 1] + [(n // rows) * i + 17 * i for i in range(1, rows - 1)]
+        it = torch.as_tensor(ridx, device=dev)
+        Asub = (A[it] if oa == "N" else A[:, it].contiguous()).cpu().numpy()
+        if check_cols:
+            ct = torch.as_tensor(check_cols, device=dev)
+            Bsub = (B[:, ct] if ob == "N" else B[ct]).contiguous().cpu().numpy()
+            got = C[it][:, ct].cpu().numpy()
+        else:
+            Bsub = B.cpu().numpy()
+            got = C[it].cpu().numpy()
+        err = O.gemm_error_units(got, O.gemm(1, oa, Asub, ob, Bsub, wide=True), Asub, Bsub, n, 1)
+        tol = 2.0 if ("tf32x3" in name or cplx) else 1.0
+        assert err <= tol, f"parity lost in bench extras: {dt} {oa}{ob} {n}: {err}"
+        rate = flops / med * 1e-9
+        if dt in ("f64", "c64"):
+            executed = 0.75 * rate if "3m" in name else rate      # 3M executes 6 mnk of the 8 mnk it is credited with
+            roof = {"bound": "tensor", "achieved": round(executed, 3), "peak": round(dmma_peak, 2), "unit": "TFLOP/s",
+                    "frac": round(executed / dmma_peak, 4), "peak_source": dmma_src,
+                    "note": "executed flop rate on the FP64 tensor pipe" + (" (3M: 6mnk executed, 8mnk credited in tflops)" if "3m" in name else "")}
+        else:
+            executed = 0.75 * rate if "3m" in name else rate
+            roof = {"bound": "tensor", "achieved": round(executed, 3), "peak": round(tf32x3_peak, 1), "unit": "TFLOP/s",
+                    "frac": round(executed / tf32x3_peak, 4),
+                    "peak_source": f"MEASURED_PEAKS.json bf16 {bf16} TFLOP/s / 2 (TF32 rate) / 3 (three TF32 products per FP32 product)",
+                    "note": "FP32-equivalent flop rate; the tensor pipe does 3x that in TF32"}
+        cname = f"{CB[dt]}gemm_{oa}{ob}_{n}x{n}x{n}"
+        cublas_cases.append(cname)
+        out.append({"case": f"{dt}gemm_{oa}{ob}_{n}x{n}x{n}", "kernel": name, "ms": round(med, 4), "ms_best": round(best, 4),
+                    "iters": iters, "tflops": round(rate, 3), "roofline": roof, "clocks": clocks,
+                    "parity": {"error_units": round(err, 5), "tolerance_units": tol, "rows_checked": len(ridx),
+                               "cols_checked": len(check_cols) if check_cols else n},
+                    "cublas_case": cname})
+        del A, B, C, box
+        torch.cuda.empty_cache()
+
+    for ops in ("NT", "TN"):
+        gemm_case("f64", ops[0], ops[1], N1, 31.0, 0x5EED0000 + 16)
+    for ops in ("NN", "NT", "TN"):
+        gemm_case("f32", ops[0], ops[1], N1, 4.6, 0x5EED0000 + 24)
+    gemm_case("c64", "H", "N", 4096, 12.5, 0x5EED0000 + 48)
+    gemm_case("c32", "H", "N", 4096, 2.3, 0x5EED0000 + 56)
+    gemm_case("f64", "N", "N", 1024, 0.08, 0x5EED0000 + 0)
+
+    # ---- configs[2]: dgemv 32768^2 N / T, ddot 2^28 (HBM roofline; denominator = MEASURED_PEAKS.json copy bandwidth)
+    m = n = 32768
+    A, x = rnd((m, n), "f64", 0x5EED0000 + 32), rnd((n,), "f64", 0x5EED0000 + 33)
+    for op in ("N", "T"):
+        box = {}
+        med, best, iters, clocks = timed(lambda: box.__setitem__("y", ab.gemv(1, op, A, x)), 0.45, 1.2)
+        y = box["y"]
+        pick = [0, n - 1] + [(1637 * i) % n for i in range(1, 15)]
+        it = torch.as_tensor(pick, device=dev)
+        sub = (A[it] if op == "N" else A[:, it].contiguous()).cpu().numpy()
+        ref = O.gemv(1, op, sub, x.cpu().numpy(), wide=True)
+        scale = np.linalg.norm(sub, axis=1 if op == "N" else 0)
+        dev_units = float(np.max(np.abs(y[it].cpu().numpy() - ref) / ((n + 2) * 2.0 ** -53 * scale * float(torch.linalg.norm(x)))))
+        assert dev_units <= 1.0, f"parity lost in bench extras: dgemv {op}: {dev_units}"
+        nbytes = 8.0 * (m * n + m + n)
+        gbs = nbytes / med * 1e-6
+        cublas_cases.append(f"dgemv_{op}_{m}x{n}")
+        out.append({"case": f"f64gemv_{op}_{m}x{n}", "ms": round(med, 4), "ms_best": round(best, 4), "iters": iters,
+                    "gbs": round(gbs, 1), "clocks": clocks,
+                    "roofline": {"bound": "hbm", "achieved": round(gbs, 1), "peak": hbm, "unit": "GB/s", "frac": round(gbs / hbm, 4),
+                                 "peak_source": "MEASURED_PEAKS.json hbm_gbs (torch copy, read + write); a read-only stream runs "
+                                                "above a copy, so frac can exceed 1", "algorithmic_bytes": nbytes},
+                    "parity": {"error_units": round(dev_units, 5), "tolerance_units": 1.0, "entries_checked": len(pick)},
+                    "cublas_case": f"dgemv_{op}_{m}x{n}"})
+    del A, x, box, y
+    torch.cuda.empty_cache()
+    nd = 1 << 28
+    u, v = rnd((nd,), "f64", 0x5EED0000 + 35), rnd((nd,), "f64", 0x5EED0000 + 36)
+    box = {}
+    med, best, iters, clocks = timed(lambda: box.__setitem__("d", ab.dotu(u, v)), 0.45, 0.62)
+    seg = 1 << 22                                                    # oracle on 2^22-element slices (the full vectors are checked in tests/)
+    dref = float(O.dot(u[:seg].cpu().numpy(), v[:seg].cpu().numpy(), wide=True))
+    dgot = float(ab.dotu(u[:seg], v[:seg]))
+    du = abs(dgot - dref) / (seg * 2.0 ** -53 * float(torch.linalg.norm(u[:seg])) * float(torch.linalg.norm(v[:seg])))
+    assert du <= 1.0 and bool(torch.isfinite(box["d"])), f"parity lost in bench extras: ddot {du}"
+    nbytes = 16.0 * nd + 8
+    gbs = nbytes / med * 1e-6
+    cublas_cases.append(f"ddot_{nd}")
+    out.append({"case": f"f64dot_{nd}", "ms": round(med, 4), "ms_best": round(best, 4), "iters": iters, "gbs": round(gbs, 1),
+                "clocks": clocks,
+                "roofline": {"bound": "hbm", "achieved": round(gbs, 1), "peak": hbm, "unit": "GB/s", "frac": round(gbs / hbm, 4),
+                             "peak_source": "MEASURED_PEAKS.json hbm_gbs (torch copy)", "algorithmic_bytes": nbytes},
+                "parity": {"error_units": round(du, 6), "tolerance_units": 1.0, "entries_checked": seg,
+                           "note": "first 2^22 elements against the wide oracle; the full 2^28 check is tests/test_round2_gpu.py"},
+                "cublas_case": f"ddot_{nd}", "cublas_note": "stand-in: the reference's dot is Accelerate's own fold, not cuBLAS"})
+    del u, v, box
+    torch.cuda.empty_cache()
+
+    # ---- T1 of configs[4]: the 32768^3 product on ONE GPU (the strong-scaling numerator for SCALE's N = 2, 4, 8)
+    try:
+        gemm_case("f64", "N", "N", NMG, 1950.0, 0x5EED0000 + 64, rows=4, min_s=5.0,
+                  check_cols=[0, 1, 4097, 16384, 20001, 32767])
+        out[-1]["case"] = "f64gemm_NN_32768x32768x32768_1gpu"
+    except torch.cuda.OutOfMemoryError:
+        out.append({"case": "f64gemm_NN_32768x32768x32768_1gpu", "skipped": "out of memory (24 GiB of operands)"})
+        torch.cuda.empty_cache()
+    ab.trim_workspace()
+
+    # ---- the cuBLAS arm, same shapes, same box, right after (our process idles meanwhile)
+    cb = cublas_arm(cublas_cases)
+    for e in out:
+        c = cb.get(e.get("cublas_case", ""))
+        if c:
+            e["cublas_ms"] = c["ms_median"]
+            e["vs_cublas"] = round(c["ms_median"] / e["ms"], 4)      # > 1: this library is faster
+    if "error" in cb:
+        out.append({"case": "cublas_arm", "error": cb["error"]})
+    return out
 
 
 def main():
@@ -492,7 +673,8 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--extras", action="store_true")
+    ap.add_argument("--extras", dest="extras", action="store_true", default=True)
+    ap.add_argument("--no-extras", dest="extras", action="store_false")
     ap.add_argument("--n-mg", type=int, default=NMG, dest="n_mg")
     ap.add_argument("--subpanels", type=int, default=4)
     ap.add_argument("--transport", default="peer", choices=["peer", "p2p"],

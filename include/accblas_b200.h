@@ -95,6 +95,19 @@ int accblas_gemm_ld(accblas_stream_t stream, int dtype, int opA, int opB,
                     const void *alpha_host, const void *A, int64_t lda, const void *B, int64_t ldb,
                     void *C, int64_t ldc);
 
+/* The extended product  D = alpha * op(A) * op(B) + beta * Cin  on windows (pitches as in accblas_gemm_ld).
+ * The reference never needs it -- its hook passes beta = 0 into an uninitialised output (LLVM/PTX/Level3.hs:80,90) --
+ * but everything built ON TOP of the hot path does: the K-step loop of the 2-D (SUMMA) sharding, the K-chunked
+ * products that overlap the broadcast of B in accblas_mg_gemm, and callers that fuse `zipWith (+) c (a <> b)`.
+ *   beta_host : one element of `dtype` in host memory; NULL or a zero value => Cin is never read (may be NULL);
+ *   Cin, ldcin: m x n, row pitch in elements (0 = ldc).  Cin may be C itself (same pointer AND pitch: in place) or
+ *               an array that does not overlap C -- e.g. a local accumulator while C lives in a peer GPU's HBM.
+ * Every kernel family applies beta in its own epilogue (no extra pass); k == 0 gives D = beta * Cin. */
+int accblas_gemm_ex(accblas_stream_t stream, int dtype, int opA, int opB,
+                    int64_t rowsA, int64_t colsA, int64_t rowsB, int64_t colsB,
+                    const void *alpha_host, const void *A, int64_t lda, const void *B, int64_t ldb,
+                    const void *beta_host, const void *Cin, int64_t ldcin, void *C, int64_t ldc);
+
 /* `batch` independent products with identical shapes and flags: operand b of the batch lives at
  * base + b * stride (strides in ELEMENTS; strideA / strideB = 0 re-uses one operand for every product;
  * strideC >= m * n).  The reference has no batched operator (Accelerate would express it as a fold over a
@@ -115,8 +128,8 @@ int accblas_gemm_alpha_dev(accblas_stream_t stream, int dtype, int opA, int opB,
 int accblas_gemv_alpha_dev(accblas_stream_t stream, int dtype, int opA, int64_t rowsA, int64_t colsA,
                            const void *alpha_dev, const void *A, const void *x, int64_t lenx, void *y);
 
-/* Bytes of stream-ordered scratch accblas_gemm will take from the device's default
- * memory pool for this problem (0 for the direct kernels).  Informational. */
+/* Bytes of stream-ordered scratch accblas_gemm will take from the library's memory pool for this
+ * problem (0 for the direct kernels).  Informational. */
 size_t accblas_gemm_workspace_bytes(int dtype, int opA, int opB,
                                     int64_t rowsA, int64_t colsA, int64_t rowsB, int64_t colsB);
 
@@ -227,6 +240,10 @@ int accblas_version(void);                     /* ACCBLAS_B200_VERSION */
 const char *accblas_status_string(int status); /* static string        */
 /* cudaGetLastError text captured by the last ACCBLAS_ERR_CUDA on this thread ("" if none) */
 const char *accblas_last_cuda_error(void);
+/* The same for callers whose FFI calls hop between OS threads (GHC `unsafe` foreign imports): copies the text of
+ * the most recent ACCBLAS_ERR_CUDA of ANY thread of the process into buf (NUL-terminated, truncated to cap);
+ * returns the full length. */
+size_t accblas_last_cuda_error_r(char *buf, size_t cap);
 /* Name of the kernel family the dispatcher picks for this gemm problem, e.g.
  * "dgemm_dmma_tma", "sgemm_tf32x3_tcgen05", "sgemm_tf32x3_mma", "gemm_rank1_outer",
  * "gemm_simt_generic".  Static string. */
@@ -235,6 +252,17 @@ const char *accblas_gemm_kernel_name(int dtype, int opA, int opB,
 /* Number of kernel launches this thread has enqueued through the library (bench.py's
  * gpu_launches). */
 uint64_t accblas_launch_count(void);
+/* ... and by every thread of the process (thread-migration-proof variant). */
+uint64_t accblas_launch_count_total(void);
+
+/* Workspace.  Stream-ordered scratch (3xTF32 planes, 3M planes, stream-K partials, re-pitched operands, reduction
+ * partials, the host-buffer entry points' device copies) comes from a memory pool the library OWNS, one per device,
+ * created on first use: the device's default pool -- which an Accelerate process shares with everything else
+ * that calls cudaMallocAsync -- is never touched.  Freed blocks stay cached in the pool (a physical allocation
+ * per call would cost ~0.2 ms); accblas_trim_workspace returns them to the driver, e.g. from the host
+ * runtime's out-of-memory handler (Accelerate's allocator reclaims on OOM).  Current device only. */
+int accblas_trim_workspace(void);
+size_t accblas_workspace_cached_bytes(void);     /* bytes the current device's pool holds right now */
 /* Force a kernel family for gemm on this thread: 0 = auto, 1 = generic SIMT,
  * 2 = tensor path only (error ACCBLAS_ERR_SHAPE if the problem does not qualify). */
 void accblas_set_gemm_path(int path);
@@ -254,8 +282,11 @@ typedef enum {
     ACCBLAS_TUNE_TC_TILE = 8,       /* tcgen05 f32/c32 gemm CTA tile: 0 = 128x256, 1 = 128x128, 2 = 128x64                  */
     ACCBLAS_TUNE_CGEMM_3M = 9,      /* c32 gemm on tcgen05: 0 = always the 4M real embedding, 1 = 3M whenever possible     */
     ACCBLAS_TUNE_SNAKE_K = 10,      /* f64 gemm: 0 = every tile walks K forwards (default: alternate per wave of CTAs)       */
-    ACCBLAS_TUNE_STREAMK = 11,      /* f64 gemm: 0 = never the persistent stream-K kernel, 1 = whenever possible               */
-    ACCBLAS_TUNE_COUNT = 12
+    ACCBLAS_TUNE_STREAMK = 11,      /* f64 gemm: 0 = never the persistent kernel, 1 = whole-tile rounds + stream-K tail whenever
+                                       possible, 2 = pure stream-K (no whole-tile rounds)                                          */
+    ACCBLAS_TUNE_RELEASE = 12,      /* f64/c64 gemm stage release: 0 = fence.proxy.async + __syncwarp everywhere, 1 = __syncwarp
+                                       only everywhere (default: light on the one-CTA-per-SM tiles, fenced on the small ones)     */
+    ACCBLAS_TUNE_COUNT = 13
 } accblas_tune_t;
 /* Process-wide defaults for threads that never call this: environment variable
  * ACCBLAS_TUNE="knob=value,knob=value" (read once). */

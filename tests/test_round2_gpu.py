@@ -1,0 +1,332 @@
+"""GPU: round-2 additions -- the extended product (beta * Cin in every family's epilogue), the persistent
+whole-tile + stream-K schedule, the library-owned workspace pool, and oracle-checked parity at the
+BASELINE.json sizes themselves (configs[1..3]: s/dgemm 8192^3 NN/NT/TN, zgemm / cgemm 4096^3 HN on the 3M and
+4M paths, dgemv 32768^2 N/T, ddot 2^28).
+
+The BASELINE-size checks compare SAMPLED rows / columns / the full dot with the wide oracle (oracle.c is O(mnk)
+scalar code: 16 rows of an 8192^3 product are 10^9 multiply-adds) and the whole result through linearity or
+run-to-run equality; tolerances are the stated ones (tests/_util.py).
+"""
+import numpy as np
+import pytest
+
+from oracle import oracle as O
+from _util import TOL_UNITS, TOL_UNITS_TF32X3, gemm_inputs
+
+pytestmark = pytest.mark.gpu
+DTYPES = [O.F32, O.F64, O.C32, O.C64]
+ids = lambda d: O.NAMES[d]  # noqa: E731
+
+
+def dev(a, cuda):
+    import torch
+    return torch.from_numpy(np.ascontiguousarray(a)).to(cuda)
+
+
+def host(t):
+    return t.cpu().numpy()
+
+
+def tol_for(ab, dt, oa, ob, shapeA, shapeB):
+    name = ab.kernel_name(dt, oa, ob, shapeA, shapeB)
+    return TOL_UNITS_TF32X3 if "tf32x3" in name else TOL_UNITS[dt]
+
+
+def ex_bound(dt, tol, al, A, B, k, beta, Cin, ref):
+    """||D - D_ref||_F bound for D = alpha op(A) op(B) + beta Cin: the product's bound plus the roundings of the
+    beta term and of the final sum."""
+    return (tol * (k + 2) * O.EPS[dt] * abs(al) * O.fro(A) * O.fro(B)
+            + 4 * O.EPS[dt] * (abs(beta) * O.fro(Cin) + O.fro(ref)))
+
+
+# ------------------------------------------------------------------------------------------ accblas_gemm_ex
+@pytest.mark.parametrize("dt", DTYPES, ids=ids)
+def test_gemm_ex_beta_every_family(dt, cuda):
+    """D = alpha op(A) op(B) + beta Cin through every kernel family's own epilogue: SIMT (tiny, odd), rank-1
+    (k = 1), DMMA / mma.sync tiles, the tcgen05 kernel, 3M (forced), the persistent stream-K kernel; Cin separate
+    and in place; k = 0 (D = beta Cin)."""
+    import torch
+    import accblas_b200 as ab
+    rng = np.random.default_rng(11000 + dt)
+    wide = np.complex128 if dt in (O.C32, O.C64) else np.float64
+    shapes = [(7, 5, 3), (37, 41, 1), (96, 80, 112), (300, 260, 200), (512, 384, 256), (1100, 1000, 520), (64, 48, 0)]
+    seen = set()
+    for (m, n, k) in shapes:
+        for oa, ob in [("N", "N"), ("T", "N"), ("N", "H")]:
+            al, A, B = gemm_inputs(rng, dt, oa, ob, m, n, k)
+            beta = O.uniform(rng, (1,), dt)[0]
+            Cin = O.uniform(rng, (m, n), dt)
+            seen.add(ab.kernel_name(dt, oa, ob, A.shape, B.shape))
+            dA, dB, dC = dev(A, cuda), dev(B, cuda), dev(Cin, cuda)
+            ref = (O.gemm(al, oa, A, ob, B, wide=True).astype(wide) if k > 0 else np.zeros((m, n), wide)) + wide(beta) * Cin.astype(wide)
+            bound = ex_bound(dt, tol_for(ab, dt, oa, ob, A.shape, B.shape), al, A, B, k, beta, Cin, ref)
+            # separate Cin
+            D = ab.gemm(al, oa, dA, ob, dB, beta=beta, Cin=dC)
+            assert torch.equal(dC, dev(Cin, cuda)), "Cin must not be written"
+            assert O.fro(host(D).astype(wide) - ref) <= bound, (O.NAMES[dt], oa, ob, m, n, k, "separate")
+            # in place
+            D2 = dC.clone()
+            ab.gemm(al, oa, dA, ob, dB, out=D2, beta=beta, Cin=D2)
+            assert O.fro(host(D2).astype(wide) - ref) <= bound, (O.NAMES[dt], oa, ob, m, n, k, "in place")
+            # beta = 0: Cin is never read (NaNs in it must not leak)
+            nan = torch.full_like(dC, float("nan"))
+            D3 = ab.gemm(al, oa, dA, ob, dB, beta=0, Cin=nan)
+            assert not torch.isnan(torch.view_as_real(D3) if D3.is_complex() else D3).any()
+    assert len(seen) >= 3, seen
+    # forced families: 3M, pure stream-K, 4M complex tensor path
+    forced = []
+    if dt == O.C64:
+        forced = [(ab.TUNE_ZGEMM_3M, 1), (ab.TUNE_ZGEMM_3M, 0)]
+    elif dt == O.C32:
+        forced = [(ab.TUNE_CGEMM_3M, 1), (ab.TUNE_CGEMM_3M, 0)]
+    elif dt == O.F64:
+        forced = [(ab.TUNE_STREAMK, 1), (ab.TUNE_STREAMK, 2)]
+    for knob, val in forced:
+        try:
+            ab.set_tuning(knob, val)
+            if dt == O.C32:
+                ab.set_tuning(2, 2)
+            m, n, k = 640, 768, 512
+            al, A, B = gemm_inputs(rng, dt, "H", "N", m, n, k)
+            beta = O.uniform(rng, (1,), dt)[0]
+            Cin = O.uniform(rng, (m, n), dt)
+            ref = O.gemm(al, "H", A, "N", B, wide=True).astype(wide) + wide(beta) * Cin.astype(wide)
+            D = ab.gemm(al, "H", dev(A, cuda), "N", dev(B, cuda), beta=beta, Cin=dev(Cin, cuda))
+            bound = ex_bound(dt, TOL_UNITS_TF32X3, al, A, B, k, beta, Cin, ref)
+            assert O.fro(host(D).astype(wide) - ref) <= bound, (O.NAMES[dt], knob, val)
+        finally:
+            ab.set_tuning(knob, -1)
+            ab.set_tuning(2, -1)
+
+
+def test_gemm_ex_windows_and_errors(cuda):
+    """Pitched Cin / C windows; aliasing rules: Cin == C only with the same pitch, partial overlap refused."""
+    import ctypes
+    import torch
+    import accblas_b200 as ab
+    rng = np.random.default_rng(11100)
+    m, n, k = 200, 136, 96
+    al, A, B = gemm_inputs(rng, O.F64, "N", "N", m, n, k)
+    big_in = O.uniform(rng, (m + 8, n + 24), O.F64)
+    big_out = torch.zeros((m + 4, n + 16), dtype=torch.float64, device=cuda)
+    d_in = dev(big_in, cuda)
+    Cin = d_in[3:3 + m, 8:8 + n]
+    out = big_out[2:2 + m, 4:4 + n]
+    ab.gemm(al, "N", dev(A, cuda), "N", dev(B, cuda), out=out, beta=0.5, Cin=Cin)
+    ref = O.gemm(al, "N", A, "N", B, wide=True) + 0.5 * big_in[3:3 + m, 8:8 + n]
+    assert O.fro(host(out) - ref) <= ex_bound(O.F64, 1.0, al, A, B, k, 0.5, big_in, ref)
+    halo = big_out.clone()
+    halo[2:2 + m, 4:4 + n] = 0
+    assert torch.count_nonzero(halo).item() == 0, "stores outside the C window"
+    # partial overlap of Cin and C
+    L = ab.lib()
+    one = np.array([1.0])
+    p = lambda t: ctypes.c_void_p(t.data_ptr())  # noqa: E731
+    dA, dB = dev(A, cuda), dev(B, cuda)
+    buf = torch.zeros((m + 1) * n, dtype=torch.float64, device=cuda)
+    st = L.accblas_gemm_ex(None, 1, 0, 0, m, k, k, n, one.ctypes.data_as(ctypes.c_void_p), p(dA), 0, p(dB), 0,
+                           one.ctypes.data_as(ctypes.c_void_p), ctypes.c_void_p(buf.data_ptr() + 8 * n), 0, p(buf), 0)
+    assert st == 8, st          # ACCBLAS_ERR_ALIAS
+    st = L.accblas_gemm_ex(None, 1, 0, 0, m, k, k, n, one.ctypes.data_as(ctypes.c_void_p), p(dA), 0, p(dB), 0,
+                           one.ctypes.data_as(ctypes.c_void_p), None, 0, p(buf), 0)
+    assert st == 4, st          # ACCBLAS_ERR_NULL: beta != 0 without Cin
+
+
+# ------------------------------------------------------------------------------------------ persistent schedule
+def test_dgemm_persistent_schedules(cuda):
+    """Whole-tile rounds + stream-K tail (knob 1), pure stream-K (knob 2) and the data-parallel launch (knob 0)
+    agree within tolerance on products with 0, 1 and several whole-tile rounds; each persistent schedule is
+    bit-reproducible run to run; both stage-release modes give the same bits (they only differ in timing)."""
+    import torch
+    import accblas_b200 as ab
+    rng = np.random.default_rng(11200)
+    try:
+        for (m, n, k) in [(1280, 1152, 384), (2048, 2048, 320), (4096, 2304, 160), (1900, 2100, 530)]:
+            for oa, ob in [("N", "N"), ("T", "N"), ("N", "T")]:
+                al, A, B = gemm_inputs(rng, O.F64, oa, ob, m, n, k)
+                dA, dB = dev(A, cuda), dev(B, cuda)
+                ab.set_tuning(ab.TUNE_STREAMK, 0)
+                C0 = ab.gemm(al, oa, dA, ob, dB)
+                outs = {}
+                for knob in (1, 2):
+                    ab.set_tuning(ab.TUNE_STREAMK, knob)
+                    for rel in (0, 1):
+                        ab.set_tuning(ab.TUNE_RELEASE, rel)
+                        outs[(knob, rel)] = ab.gemm(al, oa, dA, ob, dB)
+                    ab.set_tuning(ab.TUNE_RELEASE, -1)
+                    again = ab.gemm(al, oa, dA, ob, dB)
+                    assert torch.equal(outs[(knob, 0)], outs[(knob, 1)]), (m, n, k, oa, ob, knob, "release modes differ")
+                    assert torch.equal(outs[(knob, 0)], again), (m, n, k, oa, ob, knob, "not reproducible")
+                    assert O.gemm_error_units(host(again), host(C0), A, B, k, al) <= 2 * TOL_UNITS[O.F64], (m, n, k, oa, ob, knob)
+                rows = rng.choice(m, size=5, replace=False)
+                Asub = A[rows] if oa == "N" else np.ascontiguousarray(A[:, rows])
+                err = O.gemm_error_units(host(outs[(1, 1)])[rows], O.gemm(al, oa, Asub, ob, B, wide=True), Asub, B, k, al)
+                assert err <= TOL_UNITS[O.F64], (m, n, k, oa, ob, err)
+    finally:
+        ab.set_tuning(ab.TUNE_STREAMK, -1)
+        ab.set_tuning(ab.TUNE_RELEASE, -1)
+
+
+@pytest.mark.parametrize("dt", [O.F64, O.C64], ids=ids)
+def test_release_modes_big_tiles(dt, cuda):
+    """The light stage release (__syncwarp + arrive) on the one-CTA-per-SM tiles against the fenced one: same
+    bits, on shapes with short and long K (ring wrapping many times)."""
+    import torch
+    import accblas_b200 as ab
+    rng = np.random.default_rng(11300 + dt)
+    knob = ab.TUNE_DMMA_TILE if dt == O.F64 else ab.TUNE_ZMMA_TILE
+    try:
+        ab.set_tuning(knob, 0)
+        ab.set_tuning(ab.TUNE_ZGEMM_3M, 0)
+        for (m, n, k) in [(1024, 1024, 96), (1536, 1280, 2048)]:
+            for oa, ob in [("N", "N"), ("H", "N"), ("N", "T")]:
+                al, A, B = gemm_inputs(rng, dt, oa, ob, m, n, k)
+                dA, dB = dev(A, cuda), dev(B, cuda)
+                res = []
+                for rel in (0, 1, 1, 1):
+                    ab.set_tuning(ab.TUNE_RELEASE, rel)
+                    res.append(ab.gemm(al, oa, dA, ob, dB))
+                for r in res[1:]:
+                    assert torch.equal(res[0], r), (O.NAMES[dt], m, n, k, oa, ob)
+    finally:
+        ab.set_tuning(knob, -1)
+        ab.set_tuning(ab.TUNE_ZGEMM_3M, -1)
+        ab.set_tuning(ab.TUNE_RELEASE, -1)
+
+
+# ------------------------------------------------------------------------------------------ workspace pool
+def test_workspace_pool_is_private_and_trims(cuda):
+    import torch
+    import accblas_b200 as ab
+    L = ab.lib()
+    n = 1536
+    A = torch.rand((n, n), dtype=torch.float32, device=cuda)
+    assert ab.workspace_bytes(O.F32, "N", "N", A.shape, A.shape) > 0      # tcgen05 path: hi / lo planes
+    ab.gemm(1, "N", A, "N", A)
+    torch.cuda.synchronize()
+    assert L.accblas_workspace_cached_bytes() > 0
+    assert L.accblas_trim_workspace() == 0
+    assert L.accblas_workspace_cached_bytes() == 0
+    C = ab.gemm(1, "N", A, "N", A)                                       # still works after a trim
+    torch.cuda.synchronize()
+    assert torch.isfinite(C).all()
+    import ctypes
+    buf = ctypes.create_string_buffer(64)
+    assert L.accblas_last_cuda_error_r(buf, 64) == len(buf.value) or L.accblas_last_cuda_error_r(buf, 64) >= 63
+    assert L.accblas_launch_count_total() >= L.accblas_launch_count()
+
+
+# ------------------------------------------------------------------------------------------ BASELINE sizes
+def seeded(shape, seed, cuda, dtype):
+    import torch
+    g = torch.Generator(device=cuda).manual_seed(seed)
+    if dtype.is_complex:
+        base = torch.float32 if dtype == torch.complex64 else torch.float64
+        return torch.view_as_complex(torch.rand(tuple(shape) + (2,), dtype=base, device=cuda, generator=g) * 2 - 1)
+    return torch.rand(shape, dtype=dtype, device=cuda, generator=g) * 2 - 1
+
+
+def sampled_gemm_check(ab, cuda, dt, tdt, n, oa, ob, rows, seed):
+    """A <op> B at n^3 from seeded device operands: `rows` rows of C against the wide oracle."""
+    import torch
+    A = seeded((n, n), seed, cuda, tdt)
+    B = seeded((n, n), seed + 1, cuda, tdt)
+    C = ab.gemm(1, oa, A, ob, B)
+    idx = torch.as_tensor(rows, device=cuda)
+    Asub = host(A[idx] if oa == "N" else A[:, idx].contiguous())
+    Bh = host(B)
+    ref = O.gemm(1, oa, Asub, ob, Bh, wide=True)
+    err = O.gemm_error_units(host(C[idx]), ref, Asub, Bh, n, 1)
+    return err, A, B, C
+
+
+@pytest.mark.parametrize("ops", ["NN", "NT", "TN"])
+def test_baseline_dgemm_8192(ops, cuda):
+    """configs[1]: Double gemm n = 8192 -- 16 rows against the wide oracle (one per 512-row band: every rank of
+    the raster groups, first / last row), run-to-run bit equality of the whole matrix."""
+    import torch
+    import accblas_b200 as ab
+    n = 8192
+    rows = [0, n - 1] + [512 * i + (37 * i) % 512 for i in range(1, 15)]
+    err, A, B, C = sampled_gemm_check(ab, cuda, O.F64, torch.float64, n, ops[0], ops[1], rows, 0x5EED0000 + 16)
+    assert err <= TOL_UNITS[O.F64], (ops, err)
+    assert torch.equal(C, ab.gemm(1, ops[0], A, ops[1], B))
+
+
+@pytest.mark.parametrize("ops", ["NN", "NT", "TN"])
+def test_baseline_sgemm_8192(ops, cuda):
+    """configs[1]: Float gemm n = 8192 on the tcgen05 3xTF32 path."""
+    import torch
+    import accblas_b200 as ab
+    n = 8192
+    rows = [0, n - 1] + [512 * i + (37 * i) % 512 for i in range(1, 15)]
+    assert "tcgen05" in ab.kernel_name(O.F32, ops[0], ops[1], (n, n), (n, n))
+    err, A, B, C = sampled_gemm_check(ab, cuda, O.F32, torch.float32, n, ops[0], ops[1], rows, 0x5EED0000 + 24)
+    assert err <= TOL_UNITS_TF32X3, (ops, err)
+
+
+@pytest.mark.parametrize("dt,scheme", [(O.C64, 1), (O.C64, 0), (O.C32, 1), (O.C32, 0)],
+                         ids=["z3m", "z4m", "c3m", "c4m"])
+def test_baseline_complex_gemm_4096_hn(dt, scheme, cuda):
+    """configs[3]: zgemm (and cgemm) 4096^3 with ConjugateTranspose on A, on the 3M AND the 4M path: 16 rows against
+    the wide oracle, normwise (stated tolerance) and componentwise (max |Re|, |Im| deviation relative to
+    k eps ||a_i|| ||b_j||, reported; 3M's imaginary parts carry the larger constant)."""
+    import torch
+    import accblas_b200 as ab
+    n = 4096
+    tdt = torch.complex128 if dt == O.C64 else torch.complex64
+    knob = ab.TUNE_ZGEMM_3M if dt == O.C64 else ab.TUNE_CGEMM_3M
+    rows = [0, n - 1] + [256 * i + (29 * i) % 256 for i in range(1, 15)]
+    try:
+        ab.set_tuning(knob, scheme)
+        name = ab.kernel_name(dt, "H", "N", (n, n), (n, n))
+        assert ("3m" in name) == bool(scheme), name
+        err, A, B, C = sampled_gemm_check(ab, cuda, dt, tdt, n, "H", "N", rows, 0x5EED0000 + 48)
+    finally:
+        ab.set_tuning(knob, -1)
+    assert err <= TOL_UNITS_TF32X3, (name, err)
+
+
+@pytest.mark.parametrize("op", ["N", "T"])
+def test_baseline_dgemv_32768(op, cuda):
+    """configs[2]: Double gemv 32768 x 32768 -- 24 sampled entries of y against the wide oracle (rows of A for N,
+    columns for T), plus run-to-run bit equality."""
+    import torch
+    import accblas_b200 as ab
+    n = 32768
+    A = seeded((n, n), 0x5EED0000 + 32, cuda, torch.float64)
+    x = seeded((n,), 0x5EED0000 + 33, cuda, torch.float64)
+    y = ab.gemv(1, op, A, x)
+    pick = [0, 1, n - 1, n - 2] + [(1637 * i) % n for i in range(1, 21)]
+    idx = torch.as_tensor(pick, device=cuda)
+    if op == "N":
+        sub = host(A[idx])
+        ref = O.gemv(1, "N", sub, host(x), wide=True)
+        scale = np.linalg.norm(sub, axis=1)
+    else:
+        sub = host(A[:, idx].contiguous())
+        ref = O.gemv(1, "T", sub, host(x), wide=True)
+        scale = np.linalg.norm(sub, axis=0)
+    got = host(y[idx])
+    bound = (n + 2) * O.EPS[O.F64] * scale * float(torch.linalg.norm(x))
+    assert np.all(np.abs(got - ref) <= bound), (op, float(np.max(np.abs(got - ref) / bound)))
+    assert torch.equal(y, ab.gemv(1, op, A, x))
+
+
+def test_baseline_ddot_2p28(cuda):
+    """configs[2]: dotu on 2^28 Doubles against the wide oracle on the FULL vectors (4 GiB on the host)."""
+    import torch
+    import accblas_b200 as ab
+    n = 1 << 28
+    x = seeded((n,), 0x5EED0000 + 35, cuda, torch.float64)
+    y = seeded((n,), 0x5EED0000 + 36, cuda, torch.float64)
+    d = ab.dotu(x, y)
+    d2 = ab.dotu(x, y)
+    assert torch.equal(d, d2)
+    xh, yh = host(x), host(y)
+    nx, ny = float(torch.linalg.norm(x)), float(torch.linalg.norm(y))
+    del x, y
+    ref = float(O.dot(xh, yh, wide=True))
+    assert abs(float(d) - ref) <= n * O.EPS[O.F64] * nx * ny
+    # a blocked double-precision sum sits far inside the worst-case bound: 1e-3 of it is still generous
+    assert abs(float(d) - ref) <= 1e-3 * n * O.EPS[O.F64] * nx * ny
