@@ -187,6 +187,8 @@ struct GemmArgs {
     const void *beta;                     // one element in host memory
     const void *Cin;                      // m x n, row pitch ldcin (elements; 0 = ldc); may equal C
     int64_t ldcin;
+    bool no_persistent;                   // never the persistent (one CTA per SM) schedule: set by callers that run several
+                                          // products CONCURRENTLY on different streams (the host wavefront)
     // strided batch (accblas_gemm_strided_batched): `batch` independent products, operand b of the batch at
     // base + b * stride (elements; stride 0 = the same operand for every product).  batch <= 1: one product.
     int64_t batch, strideA, strideB, strideC;

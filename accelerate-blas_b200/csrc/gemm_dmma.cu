@@ -69,24 +69,41 @@ __device__ __forceinline__ int kslot(int s, int t) {
     return (t & 2) * 4 + 2 * ((s + t) & 3) + (t & 1);
 }
 
-// A consumer warp hands a stage back to the TMA producer with ONE mbarrier arrive by lane 0.  The arrive has
-// release semantics, but only for lane 0's own accesses: ptxas hoists it to right behind the last ld.shared of
-// the K-block (above the converging mma.sync instructions), and lanes that left the try_wait spin loop late have
-// then not even issued their fragment loads -- the producer's next TMA write raced with them (wrong results with
-// many small CTAs per SM, pinned by tests/test_parity_gpu.py::test_gemm_many_small_tiles_short_k).
-//   FENCED = false: __syncwarp (every lane's ld.shared is issued, in order, ahead of the arrive) -- the pattern every
-//            TMA + ld.shared pipeline uses for the read -> async-proxy-overwrite (WAR) direction;
-//   FENCED = true : additionally fence.proxy.async, which also drains the loads (costs 1.8 % of the DMMA pipe on the
-//            128 x 128 tile: 98.1 % -> 96.3 % active).  Kept for the small tiles, whose ring wraps every 3-4 K-blocks with
-//            5-7 CTAs per SM, and selectable everywhere with ACCBLAS_TUNE_RELEASE.
-template <bool FENCED> __device__ __forceinline__ void release_stage(uint32_t empty_bar, int lane) {
-    if (FENCED) tma::fence_proxy_async();
+// A consumer warp hands a stage back to the TMA producer with ONE mbarrier arrive by lane 0.  ptxas hoists that
+// arrive to right behind the last ld.shared of the K-block -- above the mma.sync instructions that consume the
+// loaded registers -- so at the moment the producer sees it, fragment loads of the stage can still be in flight (or,
+// for lanes that left the try_wait spin loop late, not even issued), and its next TMA write into the stage races
+// with them.  Found in round 1 with many small CTAs per SM (tests/test_parity_gpu.py::
+// test_gemm_many_small_tiles_short_k); three ways to close it (REL, selectable with ACCBLAS_TUNE_RELEASE):
+//   REL_FENCED  (0): fence.proxy.async + __syncwarp + arrive.  The fence drains the warp's loads.  Costs ~0.5 % of
+//                    the 128 x 128 tile's time (measured round 2: 30.74 -> 30.59 ms at 8192^3 without it).
+//   REL_LIGHT   (1): __syncwarp + arrive.  NOT SOUND, not instantiated by the dispatcher: 3 mismatches in 720 runs of the
+//                    32 x 32 complex tile and a run-to-run difference of the persistent kernel at 2048^3 (round 2,
+//                    profiles/r02_dgemm_release_schedule.jsonl) -- the loads CAN still be in flight.  It is only the
+//                    second half of the delayed release below.
+//   REL_DELAYED (2): the stage of K-block i is released at the top of K-block i + 1, after the wait on the next
+//                    stage's full barrier.  A warp issues in order and an mma.sync cannot issue before its operand
+//                    registers are written, so by then every ld.shared of stage i has completed: no fence needed, sound
+//                    by construction, for one stage less of prefetch depth.  The release sits in another basic block
+//                    (behind the spin loop), so ptxas cannot hoist it above the MMAs.
+enum { REL_FENCED = 0, REL_LIGHT = 1, REL_DELAYED = 2 };
+template <int REL> __device__ __forceinline__ void release_stage(uint32_t empty_bar, int lane) {
+    if (REL == REL_FENCED) tma::fence_proxy_async();
     __syncwarp();
     if (lane == 0) tma::mbar_arrive(empty_bar);
+}
+// the two halves of a K-block's release protocol.  Under REL_DELAYED the stage released at the top of a K-block is the
+// PREVIOUS ring slot (derived from the current one: no register is carried across the loop body, which has none to spare).
+template <int REL, int NSTAGES> __device__ __forceinline__ void release_before(uint32_t empty_base, int s, bool first, int lane) {
+    if (REL == REL_DELAYED && !first) release_stage<REL_LIGHT>(empty_base + 8 * (s == 0 ? NSTAGES - 1 : s - 1), lane);
+}
+template <int REL> __device__ __forceinline__ void release_after(uint32_t empty_bar, int lane) {
+    if (REL != REL_DELAYED) release_stage<REL>(empty_bar, lane);
 }
 
 struct DgemmParams {
     int64_t m, n, k, ldc;
+    int a_one_box, b_one_box;   // MN-major operand fetched as ONE 3-D TMA box per stage (tma::make_mn3d)
     Alpha<double> alpha;
     BetaC<double> beta;  // + beta * Cin (accblas_gemm_ex); cin == nullptr: C is write-only
     double *C;
@@ -139,7 +156,7 @@ __device__ __forceinline__ void dgemm_epilogue(const DgemmParams &p, const doubl
 }
 
 // AK: op(A) is K-major in memory (opA == N).  BKM: op(B) is K-major in memory (opB == T).
-template <bool AK, bool BKM, typename TL, bool FENCED>
+template <bool AK, bool BKM, typename TL, int REL>
 __global__ void __launch_bounds__(TL::THREADS, TL::MIN_CTAS)
 dgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
                   const DgemmParams p)
@@ -185,10 +202,12 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
                 tma::mbar_expect_tx(full, STAGE_BYTES);
                 const int k0 = (rev ? kblocks - 1 - kb : kb) * BK;
                 if (AK) tma::load_2d(sa, &mapA, full, k0, m0);
+                else if (p.a_one_box) tma::load_3d(sa, &mapA, full, 0, k0, m0 >> 4);
                 else
 #pragma unroll
                     for (int j = 0; j < BM / 16; ++j) tma::load_2d(sa + j * 2048, &mapA, full, m0 + 16 * j, k0);
                 if (BKM) tma::load_2d(sb, &mapB, full, k0, n0);
+                else if (p.b_one_box) tma::load_3d(sb, &mapB, full, 0, k0, n0 >> 4);
                 else
 #pragma unroll
                     for (int j = 0; j < BN / 16; ++j) tma::load_2d(sb + j * 2048, &mapB, full, n0 + 16 * j, k0);
@@ -231,6 +250,7 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
         const int s = kb % STAGES;
         const uint32_t stage = smem_base + s * STAGE_BYTES;
         tma::mbar_wait(bar_base + 8 * s, (kb / STAGES) & 1);
+        release_before<REL, STAGES>(bar_base + 8 * STAGES, s, kb == 0, lane);
         double a[2][MI], b[2][NJ];
         load_frags(stage, 0, a[0], b[0]);
 #pragma unroll
@@ -241,7 +261,7 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
 #pragma unroll
                 for (int j = 0; j < NJ; ++j) dmma(acc[i][j][0], acc[i][j][1], a[st & 1][i], b[st & 1][j]);
         }
-        release_stage<FENCED>(bar_base + 8 * (STAGES + s), lane);      // stage consumed by this warp
+        release_after<REL>(bar_base + 8 * (STAGES + s), lane);          // stage consumed by this warp
     }
 
     // ---- epilogue: C = alpha * acc (+ beta * Cin); C itself is never read unless it is Cin ----
@@ -309,7 +329,7 @@ __device__ __forceinline__ bool segment_at(const StreamKParams &q, int cta, int 
     return true;
 }
 
-template <bool AK, bool BKM, bool FENCED>
+template <bool AK, bool BKM, int REL>
 __global__ void __launch_bounds__(Tile128x128::THREADS, 1)
 dgemm_dmma_streamk_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
                           const StreamKParams q)
@@ -362,10 +382,12 @@ dgemm_dmma_streamk_kernel(const __grid_constant__ CUtensorMap mapA, const __grid
                     tma::mbar_expect_tx(full, STAGE_BYTES);
                     const int k0 = (rev ? kblocks - 1 - kb : kb) * BK;
                     if (AK) tma::load_2d(sa, &mapA, full, k0, m0);
+                    else if (p.a_one_box) tma::load_3d(sa, &mapA, full, 0, k0, m0 >> 4);
                     else
 #pragma unroll
                         for (int j = 0; j < BM / 16; ++j) tma::load_2d(sa + j * 2048, &mapA, full, m0 + 16 * j, k0);
                     if (BKM) tma::load_2d(sb, &mapB, full, k0, n0);
+                    else if (p.b_one_box) tma::load_3d(sb, &mapB, full, 0, k0, n0 >> 4);
                     else
 #pragma unroll
                         for (int j = 0; j < BN / 16; ++j) tma::load_2d(sb + j * 2048, &mapB, full, n0 + 16 * j, k0);
@@ -397,7 +419,7 @@ dgemm_dmma_streamk_kernel(const __grid_constant__ CUtensorMap mapA, const __grid
     constexpr int SLOT = BM * BN;                                  // doubles per workspace slot
     // ring position: stage index and phase parity, advanced incrementally (no division in the K loop)
     int rs = 0;
-    uint32_t rphase = 0;
+    uint32_t rround = 0;                                           // times the ring has wrapped: phase parity = rround & 1
     int it = it_begin;
     for (int seg = 0;; ++seg) {
         int nkb;
@@ -413,7 +435,8 @@ dgemm_dmma_streamk_kernel(const __grid_constant__ CUtensorMap mapA, const __grid
             for (int j = 0; j < NJ; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
         for (; nkb > 0; --nkb) {
             const uint32_t stage = smem_base + rs * STAGE_BYTES;
-            tma::mbar_wait(bar_base + 8 * rs, rphase);
+            tma::mbar_wait(bar_base + 8 * rs, rround & 1u);
+            release_before<REL, STAGES>(bar_base + 8 * STAGES, rs, (rs | rround) == 0, lane);
             double a[2][MI], b[2][NJ];
             load_frags(stage, 0, a[0], b[0]);
 #pragma unroll
@@ -424,8 +447,8 @@ dgemm_dmma_streamk_kernel(const __grid_constant__ CUtensorMap mapA, const __grid
 #pragma unroll
                     for (int j = 0; j < NJ; ++j) dmma(acc[i][j][0], acc[i][j][1], a[st & 1][i], b[st & 1][j]);
             }
-            release_stage<FENCED>(bar_base + 8 * (STAGES + rs), lane);
-            if (++rs == STAGES) { rs = 0; rphase ^= 1u; }
+            release_after<REL>(bar_base + 8 * (STAGES + rs), lane);
+            if (++rs == STAGES) { rs = 0; ++rround; }
         }
         // the segment again (see segment_at), with the CTA's ticket re-read from shared memory
         int cta2;
@@ -525,7 +548,7 @@ struct ZgemmParams {
     int tiles_m, tiles_n;
 };
 
-template <bool AK, bool BKM, bool CONJA, bool CONJB, typename TL, bool FENCED>
+template <bool AK, bool BKM, bool CONJA, bool CONJB, typename TL, int REL>
 __global__ void __launch_bounds__(TL::THREADS, TL::MIN_CTAS)
 zgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
                   const ZgemmParams p)
@@ -611,6 +634,7 @@ zgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
         const int s = kb % ZSTAGES;
         const uint32_t stage = smem_base + s * ZSTAGE_BYTES;
         tma::mbar_wait(bar_base + 8 * s, (kb / ZSTAGES) & 1);
+        release_before<REL, ZSTAGES>(bar_base + 8 * ZSTAGES, s, kb == 0, lane);
         double2 a[2][MI], b[2][NJ];
 #pragma unroll
         for (int i = 0; i < MI; ++i) a[0][i] = lds128(stage + offA[0] + i * 1024);
@@ -650,7 +674,7 @@ zgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
 #pragma unroll
                 for (int j = 0; j < NJ; ++j) dmma(ci[i][j][0], ci[i][j][1], ai[i], b[st][j].x);
         }
-        release_stage<FENCED>(bar_base + 8 * (ZSTAGES + s), lane);
+        release_after<REL>(bar_base + 8 * (ZSTAGES + s), lane);
     }
 
     const double2 al = p.alpha.get();
@@ -713,15 +737,35 @@ int pick_tile(int64_t m, int64_t n, int64_t k, double *cost_out = nullptr)
     return best;
 }
 
-// Stage-release mode (see release_stage): ACCBLAS_TUNE_RELEASE = 0 -> fence.proxy.async everywhere, 1 -> __syncwarp
-// only everywhere, automatic: light release for the tiles that run ONE CTA per SM over a deep ring (128 x 128 real,
-// 128 x 64 complex, the persistent kernel), fenced release for the small multi-CTA tiles.
-bool fenced_release(bool big_tile)
+// Stage-release mode (see release_stage).  Measured at 8192^3 (profiles/r02_dgemm_release_schedule.jsonl, ms, NN / NT / TN / TT):
+//   data-parallel 128 x 128:   fenced 30.74 / 30.61 / 31.03 / 30.51     delayed 30.65 / 30.61 / 30.72 / 30.54
+//   persistent (rounds + SK):  fenced 30.44 / 30.45 / 30.72 / 30.50     delayed 30.58 / 30.43 / 31.00 / 30.38
+// (the delayed persistent variants of NN / NT spill: the loop body has no register left for the previous slot).
+// Automatic choice: delayed on the data-parallel 128 x 128 tile, fenced in the persistent kernel, on the small
+// multi-CTA tiles (whose 3-4 stage ring cannot spare a stage) and in the complex kernels.
+// ACCBLAS_TUNE_RELEASE = 0 / 2 forces fenced / delayed everywhere.  The light release (1) is not built: it races.
+int release_mode(bool dp_big_tile)
 {
     const int knob = g_tuning[ACCBLAS_TUNE_RELEASE];
-    if (knob == 0) return true;
-    if (knob == 1) return false;
-    return !big_tile;
+    if (knob == 0) return REL_FENCED;
+    if (knob == 2) return REL_DELAYED;
+    return dp_big_tile ? REL_DELAYED : REL_FENCED;
+}
+
+// tensor maps of one operand: K-major -> one 2-D box of BK x rows; MN-major -> one 3-D box when the extent allows
+// (tma::make_mn3d), else BM/16 (BN/16) 2-D boxes of 16 x 16
+bool make_operand_map(CUtensorMap *map, bool kmajor, const void *base, int64_t rows, int64_t cols, int64_t ld, int tile_extent,
+                      int *one_box)
+{
+    *one_box = 0;
+    if (kmajor)
+        return tma::make_2d(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 8, base, (uint64_t)rows, (uint64_t)cols, tile_extent, 16, (uint64_t)ld * 8);
+    if (g_tuning[ACCBLAS_TUNE_MN_ONEBOX] != 0 && cols % 16 == 0 &&
+        tma::make_mn3d(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 8, base, (uint64_t)rows, (uint64_t)cols, 16, BK, tile_extent / 16, (uint64_t)ld * 8)) {
+        *one_box = 1;
+        return true;
+    }
+    return tma::make_2d(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 8, base, (uint64_t)rows, (uint64_t)cols, BK, 16, (uint64_t)ld * 8);
 }
 
 void fill_params(DgemmParams &p, const GemmArgs &g, int BM, int BN)
@@ -735,27 +779,24 @@ void fill_params(DgemmParams &p, const GemmArgs &g, int BM, int BN)
     p.group = g_tuning[ACCBLAS_TUNE_RASTER_GROUP] > 0 ? g_tuning[ACCBLAS_TUNE_RASTER_GROUP] : 16;
 }
 
-template <bool AK, bool BKM, typename TL, bool FENCED>
+template <bool AK, bool BKM, typename TL, int REL>
 int launch_dgemm_tile(const GemmArgs &g)
 {
     constexpr int BM = TL::BM, BN = TL::BN, SMEM_BYTES = TL::SMEM_BYTES;
     CUtensorMap mapA, mapB;
-    // K-major operand: box = 16 (k) x BM|BN rows; MN-major operand: box = 16 (m|n) x 16 (k)
-    if (!tma::make_2d(&mapA, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 8, g.A, (uint64_t)g.rowsA, (uint64_t)g.colsA,
-                      AK ? BM : BK, 16, (uint64_t)g.lda * 8) ||
-        !tma::make_2d(&mapB, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 8, g.B, (uint64_t)g.rowsB, (uint64_t)g.colsB,
-                      BKM ? BN : BK, 16, (uint64_t)g.ldb * 8))
+    DgemmParams p;
+    if (!make_operand_map(&mapA, AK, g.A, g.rowsA, g.colsA, g.lda, BM, &p.a_one_box) ||
+        !make_operand_map(&mapB, BKM, g.B, g.rowsB, g.colsB, g.ldb, BN, &p.b_one_box))
         return cuda_fail(cudaErrorInvalidValue, "cuTensorMapEncodeTiled");
     static thread_local AttrOnce attr_once;
     if (attr_once.need()) {
-        ACC_CUDA(cudaFuncSetAttribute(dgemm_dmma_kernel<AK, BKM, TL, FENCED>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+        ACC_CUDA(cudaFuncSetAttribute(dgemm_dmma_kernel<AK, BKM, TL, REL>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
     }
-    DgemmParams p;
     fill_params(p, g, BM, BN);
     p.snake_waves = g_tuning[ACCBLAS_TUNE_SNAKE_K] == 0 ? 0 : sm_count() * TL::MIN_CTAS;
     const int64_t tiles = (int64_t)p.tiles_m * p.tiles_n;
     if (tiles > 0x7fffffff) return ACCBLAS_ERR_SHAPE;
-    dgemm_dmma_kernel<AK, BKM, TL, FENCED><<<(unsigned)tiles, TL::THREADS, SMEM_BYTES, g.stream>>>(mapA, mapB, p);
+    dgemm_dmma_kernel<AK, BKM, TL, REL><<<(unsigned)tiles, TL::THREADS, SMEM_BYTES, g.stream>>>(mapA, mapB, p);
     return check_launch("dgemm_dmma_kernel");
 }
 
@@ -790,23 +831,21 @@ StreamKPlan plan_streamk(int64_t m, int64_t n, int64_t k)
 }
 
 // Persistent launch (128 x 128 tiles, one CTA per SM).  Scratch: one accumulator slot per CTA + flags + ticket.
-template <bool AK, bool BKM, bool FENCED>
+template <bool AK, bool BKM, int REL>
 int launch_dgemm_streamk(const GemmArgs &g, const StreamKPlan &pl)
 {
     using TL = Tile128x128;
     CUtensorMap mapA, mapB;
-    if (!tma::make_2d(&mapA, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 8, g.A, (uint64_t)g.rowsA, (uint64_t)g.colsA,
-                      AK ? TL::BM : BK, 16, (uint64_t)g.lda * 8) ||
-        !tma::make_2d(&mapB, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 8, g.B, (uint64_t)g.rowsB, (uint64_t)g.colsB,
-                      BKM ? TL::BN : BK, 16, (uint64_t)g.ldb * 8))
+    StreamKParams q;
+    DgemmParams &p = q.p;
+    if (!make_operand_map(&mapA, AK, g.A, g.rowsA, g.colsA, g.lda, TL::BM, &p.a_one_box) ||
+        !make_operand_map(&mapB, BKM, g.B, g.rowsB, g.colsB, g.ldb, TL::BN, &p.b_one_box))
         return cuda_fail(cudaErrorInvalidValue, "cuTensorMapEncodeTiled");
     constexpr int SMEM = TL::SMEM_BYTES + 16;                      // + the ticket word
     static thread_local AttrOnce attr_once;
     if (attr_once.need()) {
-        ACC_CUDA(cudaFuncSetAttribute(dgemm_dmma_streamk_kernel<AK, BKM, FENCED>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+        ACC_CUDA(cudaFuncSetAttribute(dgemm_dmma_streamk_kernel<AK, BKM, REL>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
     }
-    StreamKParams q;
-    DgemmParams &p = q.p;
     fill_params(p, g, TL::BM, TL::BN);
     const int grid = pl.grid;
     p.snake_waves = g_tuning[ACCBLAS_TUNE_SNAKE_K] == 0 ? 0 : grid;
@@ -824,7 +863,7 @@ int launch_dgemm_streamk(const GemmArgs &g, const StreamKPlan &pl)
     cudaError_t e = cudaMemsetAsync(q.flags, 0, 4096, g.stream);
     int st = ACCBLAS_OK;
     if (e == cudaSuccess) {
-        dgemm_dmma_streamk_kernel<AK, BKM, FENCED><<<(unsigned)grid, TL::THREADS, SMEM, g.stream>>>(mapA, mapB, q);
+        dgemm_dmma_streamk_kernel<AK, BKM, REL><<<(unsigned)grid, TL::THREADS, SMEM, g.stream>>>(mapA, mapB, q);
         st = check_launch("dgemm_dmma_streamk_kernel");
     }
     const cudaError_t e2 = cudaFreeAsync(ws, g.stream);
@@ -833,23 +872,30 @@ int launch_dgemm_streamk(const GemmArgs &g, const StreamKPlan &pl)
     return st;
 }
 
+template <bool AK, bool BKM, typename TL>
+int launch_dgemm_tile_rel(const GemmArgs &g, int rel)
+{
+    return rel == REL_DELAYED ? launch_dgemm_tile<AK, BKM, TL, REL_DELAYED>(g) : launch_dgemm_tile<AK, BKM, TL, REL_FENCED>(g);
+}
+
 template <bool AK, bool BKM>
 int launch_dgemm(const GemmArgs &g)
 {
     const int tile = pick_tile(g.m, g.n, g.k);
-    const StreamKPlan pl = plan_streamk(g.m, g.n, g.k);
+    const StreamKPlan pl = g.no_persistent ? StreamKPlan{false, 0, 0} : plan_streamk(g.m, g.n, g.k);
     if (pl.use)
-        return fenced_release(true) ? launch_dgemm_streamk<AK, BKM, true>(g, pl) : launch_dgemm_streamk<AK, BKM, false>(g, pl);
-    const bool fenced = fenced_release(tile == 0);
+        return release_mode(false) == REL_DELAYED ? launch_dgemm_streamk<AK, BKM, REL_DELAYED>(g, pl)
+                                                  : launch_dgemm_streamk<AK, BKM, REL_FENCED>(g, pl);
+    const int rel = release_mode(tile == 0);
     switch (tile) {
-    case 1:  return fenced ? launch_dgemm_tile<AK, BKM, Tile64x128, true>(g) : launch_dgemm_tile<AK, BKM, Tile64x128, false>(g);
-    case 2:  return fenced ? launch_dgemm_tile<AK, BKM, Tile64x64, true>(g) : launch_dgemm_tile<AK, BKM, Tile64x64, false>(g);
-    case 3:  return fenced ? launch_dgemm_tile<AK, BKM, Tile32x32, true>(g) : launch_dgemm_tile<AK, BKM, Tile32x32, false>(g);
-    default: return fenced ? launch_dgemm_tile<AK, BKM, Tile128x128, true>(g) : launch_dgemm_tile<AK, BKM, Tile128x128, false>(g);
+    case 1:  return launch_dgemm_tile_rel<AK, BKM, Tile64x128>(g, rel);
+    case 2:  return launch_dgemm_tile_rel<AK, BKM, Tile64x64>(g, rel);
+    case 3:  return launch_dgemm_tile_rel<AK, BKM, Tile32x32>(g, rel);
+    default: return launch_dgemm_tile_rel<AK, BKM, Tile128x128>(g, rel);
     }
 }
 
-template <bool AK, bool BKM, bool CA, bool CB, typename TL, bool FENCED>
+template <bool AK, bool BKM, bool CA, bool CB, typename TL, int REL>
 int launch_zgemm_tile(const GemmArgs &g)
 {
     constexpr int ZBM = TL::BM, ZBN = TL::BN;
@@ -862,7 +908,7 @@ int launch_zgemm_tile(const GemmArgs &g)
         return cuda_fail(cudaErrorInvalidValue, "cuTensorMapEncodeTiled");
     static thread_local AttrOnce attr_once;
     if (attr_once.need()) {
-        ACC_CUDA(cudaFuncSetAttribute(zgemm_dmma_kernel<AK, BKM, CA, CB, TL, FENCED>, cudaFuncAttributeMaxDynamicSharedMemorySize, TL::SMEM_BYTES));
+        ACC_CUDA(cudaFuncSetAttribute(zgemm_dmma_kernel<AK, BKM, CA, CB, TL, REL>, cudaFuncAttributeMaxDynamicSharedMemorySize, TL::SMEM_BYTES));
     }
     ZgemmParams p;
     p.m = g.m; p.n = g.n; p.k = g.k; p.ldc = g.ldc;
@@ -873,7 +919,7 @@ int launch_zgemm_tile(const GemmArgs &g)
     p.tiles_n = (int)((g.n + ZBN - 1) / ZBN);
     const int64_t tiles = (int64_t)p.tiles_m * p.tiles_n;
     if (tiles > 0x7fffffff) return ACCBLAS_ERR_SHAPE;
-    zgemm_dmma_kernel<AK, BKM, CA, CB, TL, FENCED><<<(unsigned)tiles, TL::THREADS, TL::SMEM_BYTES, g.stream>>>(mapA, mapB, p);
+    zgemm_dmma_kernel<AK, BKM, CA, CB, TL, REL><<<(unsigned)tiles, TL::THREADS, TL::SMEM_BYTES, g.stream>>>(mapA, mapB, p);
     return check_launch("zgemm_dmma_kernel");
 }
 
@@ -904,11 +950,12 @@ template <bool AK, bool BKM, bool CA, bool CB>
 int launch_zgemm(const GemmArgs &g)
 {
     const int tile = pick_ztile(g.m, g.n, g.k);
-    const bool fenced = fenced_release(tile == 0);
+    // complex kernels: fenced or delayed only (the light release is known to race on the 32 x 32 tile)
+    const bool delayed = g_tuning[ACCBLAS_TUNE_RELEASE] == 2;
     switch (tile) {
-    case 1:  return fenced ? launch_zgemm_tile<AK, BKM, CA, CB, ZTile64x64, true>(g) : launch_zgemm_tile<AK, BKM, CA, CB, ZTile64x64, false>(g);
-    case 2:  return fenced ? launch_zgemm_tile<AK, BKM, CA, CB, ZTile32x32, true>(g) : launch_zgemm_tile<AK, BKM, CA, CB, ZTile32x32, false>(g);
-    default: return fenced ? launch_zgemm_tile<AK, BKM, CA, CB, ZTile128x64, true>(g) : launch_zgemm_tile<AK, BKM, CA, CB, ZTile128x64, false>(g);
+    case 1:  return delayed ? launch_zgemm_tile<AK, BKM, CA, CB, ZTile64x64, REL_DELAYED>(g) : launch_zgemm_tile<AK, BKM, CA, CB, ZTile64x64, REL_FENCED>(g);
+    case 2:  return delayed ? launch_zgemm_tile<AK, BKM, CA, CB, ZTile32x32, REL_DELAYED>(g) : launch_zgemm_tile<AK, BKM, CA, CB, ZTile32x32, REL_FENCED>(g);
+    default: return delayed ? launch_zgemm_tile<AK, BKM, CA, CB, ZTile128x64, REL_DELAYED>(g) : launch_zgemm_tile<AK, BKM, CA, CB, ZTile128x64, REL_FENCED>(g);
     }
 }
 

@@ -134,6 +134,7 @@ int gemm_host_pipeline(const GemmArgs &g0, const void *A_host, const void *B_hos
     auto product = [&](int64_t r0, int64_t h, int64_t c0, int64_t w, cudaStream_t on) -> int {
         GemmArgs v = g;
         v.stream = on;
+        v.no_persistent = true;                  // two strips multiply concurrently: a one-CTA-per-SM schedule would serialise them
         v.lda = g.colsA; v.ldb = g.colsB; v.ldc = g.n;
         if (an) { v.A = static_cast<char *>(dA.p) + es * (size_t)r0 * (size_t)g.colsA; v.rowsA = h; }
         else    { v.A = static_cast<char *>(dA.p) + es * (size_t)r0; v.colsA = h; }

@@ -64,6 +64,13 @@ __device__ __forceinline__ void load_2d(uint32_t dst, const void *tmap, uint32_t
         ::"r"(dst), "l"(tmap), "r"(bar), "r"(c0), "r"(c1) : "memory");
 }
 
+// 3-D tiled load (an MN-major operand panel as ONE box: see make_mn3d)
+__device__ __forceinline__ void load_3d(uint32_t dst, const void *tmap, uint32_t bar, int c0, int c1, int c2) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+        ::"r"(dst), "l"(tmap), "r"(bar), "r"(c0), "r"(c1), "r"(c2) : "memory");
+}
+
 // L2 eviction policies for TMA loads.  In a grouped rasterisation the row panels of A are re-read by
 // every wave of the group while a panel of B is used by one wave and is then dead: keeping A
 // (evict_last) and letting B go first (evict_first) turns part of the per-wave A re-reads into L2 hits.
@@ -118,6 +125,26 @@ inline bool make_2d(CUtensorMap *map, CUtensorMapDataType dt, size_t esize, cons
     cuuint32_t box[2] = {box_cols, box_rows};
     cuuint32_t estr[2] = {1, 1};
     return fn(map, dt, 2, const_cast<void *>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+              CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+// An MN-major operand (rows = K, cols = the m or n extent, `cols` a multiple of `inner`) viewed as a 3-D tensor
+//   dim0 = `inner` consecutive columns (one 128-byte swizzle row), dim1 = the K rows, dim2 = column group,
+// so that ONE box {inner, box_k, groups} lands as `groups` consecutive [box_k][inner] sub-tiles -- exactly the
+// shared-memory layout the kernels read when the panel is fetched as `groups` separate 2-D boxes, for one TMA
+// instruction instead of eight.  dim2's stride (128 bytes) is smaller than dim1's (the row pitch): if the driver
+// refuses such a map the caller keeps the 2-D boxes.
+inline bool make_mn3d(CUtensorMap *map, CUtensorMapDataType dt, size_t esize, const void *base, uint64_t rows_k,
+                      uint64_t cols, uint32_t inner, uint32_t box_k, uint32_t groups, uint64_t pitch_bytes)
+{
+    EncodeTiledFn fn = encode_fn();
+    if (!fn || cols % inner != 0) return false;
+    cuuint64_t dims[3] = {inner, rows_k, cols / inner};
+    cuuint64_t strides[2] = {pitch_bytes, (cuuint64_t)inner * esize};
+    cuuint32_t box[3] = {inner, box_k, groups};
+    cuuint32_t estr[3] = {1, 1, 1};
+    return fn(map, dt, 3, const_cast<void *>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
               CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }

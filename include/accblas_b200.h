@@ -284,9 +284,12 @@ typedef enum {
     ACCBLAS_TUNE_SNAKE_K = 10,      /* f64 gemm: 0 = every tile walks K forwards (default: alternate per wave of CTAs)       */
     ACCBLAS_TUNE_STREAMK = 11,      /* f64 gemm: 0 = never the persistent kernel, 1 = whole-tile rounds + stream-K tail whenever
                                        possible, 2 = pure stream-K (no whole-tile rounds)                                          */
-    ACCBLAS_TUNE_RELEASE = 12,      /* f64/c64 gemm stage release: 0 = fence.proxy.async + __syncwarp everywhere, 1 = __syncwarp
-                                       only everywhere (default: light on the one-CTA-per-SM tiles, fenced on the small ones)     */
-    ACCBLAS_TUNE_COUNT = 13
+    ACCBLAS_TUNE_RELEASE = 12,      /* f64/c64 gemm stage release: 0 = fence.proxy.async + arrive everywhere, 2 = release delayed
+                                       by one K-block (no fence needed) everywhere; default: delayed on the data-parallel 128x128
+                                       f64 tile, fenced elsewhere (csrc/gemm_dmma.cu: release_mode)                                 */
+    ACCBLAS_TUNE_MN_ONEBOX = 13,    /* f64 gemm: 0 = fetch an MN-major operand panel as 16 x 16 TMA boxes (round 1), default: as ONE
+                                       3-D box per stage when the extent is a multiple of 16                                       */
+    ACCBLAS_TUNE_COUNT = 14
 } accblas_tune_t;
 /* Process-wide defaults for threads that never call this: environment variable
  * ACCBLAS_TUNE="knob=value,knob=value" (read once). */

@@ -150,17 +150,17 @@ def test_dgemm_persistent_schedules(cuda):
                 outs = {}
                 for knob in (1, 2):
                     ab.set_tuning(ab.TUNE_STREAMK, knob)
-                    for rel in (0, 1):
+                    for rel in (0, 2):
                         ab.set_tuning(ab.TUNE_RELEASE, rel)
                         outs[(knob, rel)] = ab.gemm(al, oa, dA, ob, dB)
                     ab.set_tuning(ab.TUNE_RELEASE, -1)
                     again = ab.gemm(al, oa, dA, ob, dB)
-                    assert torch.equal(outs[(knob, 0)], outs[(knob, 1)]), (m, n, k, oa, ob, knob, "release modes differ")
+                    assert torch.equal(outs[(knob, 0)], outs[(knob, 2)]), (m, n, k, oa, ob, knob, "release modes differ")
                     assert torch.equal(outs[(knob, 0)], again), (m, n, k, oa, ob, knob, "not reproducible")
                     assert O.gemm_error_units(host(again), host(C0), A, B, k, al) <= 2 * TOL_UNITS[O.F64], (m, n, k, oa, ob, knob)
                 rows = rng.choice(m, size=5, replace=False)
                 Asub = A[rows] if oa == "N" else np.ascontiguousarray(A[:, rows])
-                err = O.gemm_error_units(host(outs[(1, 1)])[rows], O.gemm(al, oa, Asub, ob, B, wide=True), Asub, B, k, al)
+                err = O.gemm_error_units(host(outs[(1, 2)])[rows], O.gemm(al, oa, Asub, ob, B, wide=True), Asub, B, k, al)
                 assert err <= TOL_UNITS[O.F64], (m, n, k, oa, ob, err)
     finally:
         ab.set_tuning(ab.TUNE_STREAMK, -1)
@@ -169,25 +169,27 @@ def test_dgemm_persistent_schedules(cuda):
 
 @pytest.mark.parametrize("dt", [O.F64, O.C64], ids=ids)
 def test_release_modes_big_tiles(dt, cuda):
-    """The light stage release (__syncwarp + arrive) on the one-CTA-per-SM tiles against the fenced one: same
-    bits, on shapes with short and long K (ring wrapping many times)."""
+    """The delayed stage release (no proxy fence; the stage of K-block i is handed back at the top of K-block i + 1)
+    against the fenced one, on every tile of the family: same bits, on shapes with short and long K (ring
+    wrapping many times), small tiles with many CTAs per SM included."""
     import torch
     import accblas_b200 as ab
     rng = np.random.default_rng(11300 + dt)
     knob = ab.TUNE_DMMA_TILE if dt == O.F64 else ab.TUNE_ZMMA_TILE
     try:
-        ab.set_tuning(knob, 0)
         ab.set_tuning(ab.TUNE_ZGEMM_3M, 0)
-        for (m, n, k) in [(1024, 1024, 96), (1536, 1280, 2048)]:
-            for oa, ob in [("N", "N"), ("H", "N"), ("N", "T")]:
-                al, A, B = gemm_inputs(rng, dt, oa, ob, m, n, k)
-                dA, dB = dev(A, cuda), dev(B, cuda)
-                res = []
-                for rel in (0, 1, 1, 1):
-                    ab.set_tuning(ab.TUNE_RELEASE, rel)
-                    res.append(ab.gemm(al, oa, dA, ob, dB))
-                for r in res[1:]:
-                    assert torch.equal(res[0], r), (O.NAMES[dt], m, n, k, oa, ob)
+        for tile in range(4 if dt == O.F64 else 3):
+            ab.set_tuning(knob, tile)
+            for (m, n, k) in [(1024, 1024, 96), (1536, 1280, 1024)]:
+                for oa, ob in [("N", "N"), ("H", "N"), ("N", "T")]:
+                    al, A, B = gemm_inputs(rng, dt, oa, ob, m, n, k)
+                    dA, dB = dev(A, cuda), dev(B, cuda)
+                    res = []
+                    for rel in (0, 2, 2, 2, 2):
+                        ab.set_tuning(ab.TUNE_RELEASE, rel)
+                        res.append(ab.gemm(al, oa, dA, ob, dB))
+                    for r in res[1:]:
+                        assert torch.equal(res[0], r), (O.NAMES[dt], tile, m, n, k, oa, ob)
     finally:
         ab.set_tuning(knob, -1)
         ab.set_tuning(ab.TUNE_ZGEMM_3M, -1)
