@@ -436,6 +436,7 @@ TUNE_CGEMM_3M = 9       # c32 gemm on tcgen05: 0 = 4M real embedding, 1 = 3M whe
 TUNE_SNAKE_K = 10       # f64 gemm: 0 = every tile walks K forwards
 TUNE_STREAMK = 11       # f64 gemm: 0 = never the persistent kernel, 1 = whole-tile rounds + stream-K tail, 2 = pure stream-K
 TUNE_RELEASE = 12       # f64/c64 gemm stage release: 0 = fenced everywhere, 2 = delayed by one K-block everywhere
+TUNE_MG_SELF_PEER = 14  # accblas_mg_gemm_plan: 1 = the root runs the peers' pull / K-chunk pipeline itself (test hook)
 TUNE_MN_ONEBOX = 13     # f64 gemm: 0 = MN-major operand panels as 16 x 16 boxes, default one 3-D box per stage
 TUNE_ZGEMM_3M = 7       # 0: complex-double gemm always 4M in registers, 1: 3M whenever possible, -1: cost model
 

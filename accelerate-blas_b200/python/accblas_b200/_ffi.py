@@ -22,6 +22,9 @@ SYMBOLS = (
     "accblas_version", "accblas_status_string", "accblas_last_cuda_error",
     "accblas_gemm_kernel_name", "accblas_launch_count", "accblas_set_gemm_path", "accblas_set_tuning",
     "accblas_peer_export", "accblas_peer_open", "accblas_peer_close_all", "accblas_peer_copy2d",
+    "accblas_mg_unique_id", "accblas_mg_init", "accblas_mg_finalize", "accblas_mg_rank", "accblas_mg_world",
+    "accblas_mg_row_panel", "accblas_mg_k_chunks", "accblas_mg_gemm", "accblas_mg_gemm_plan", "accblas_mg_gemm_run",
+    "accblas_mg_gemm_plan_destroy", "accblas_mg_gemv", "accblas_mg_dot",
 )
 
 
@@ -102,6 +105,24 @@ def lib() -> ctypes.CDLL:
     L.accblas_peer_close_all.argtypes = []
     L.accblas_peer_copy2d.argtypes = [vp, vp, sz, vp, sz, sz, sz]
     for f in (L.accblas_peer_export, L.accblas_peer_open, L.accblas_peer_close_all, L.accblas_peer_copy2d):
+        f.restype = ci
+    pi64 = ctypes.POINTER(i64)
+    L.accblas_mg_unique_id.argtypes = [vp]
+    L.accblas_mg_init.argtypes = [ctypes.POINTER(vp), ci, ci, vp]
+    L.accblas_mg_finalize.argtypes = [vp]
+    L.accblas_mg_rank.argtypes = [vp]
+    L.accblas_mg_world.argtypes = [vp]
+    L.accblas_mg_row_panel.argtypes = [i64, ci, ci, pi64, pi64]
+    L.accblas_mg_k_chunks.argtypes = [i64, pi64, pi64, ci]
+    L.accblas_mg_gemm.argtypes = [vp, vp, ci, ci, ci, i64, i64, i64, i64, vp, vp, vp, vp, ci]
+    L.accblas_mg_gemm_plan.argtypes = [vp, ci, ci, ci, i64, i64, i64, i64, vp, vp, vp, ci, ctypes.POINTER(vp)]
+    L.accblas_mg_gemm_run.argtypes = [vp, vp, vp]
+    L.accblas_mg_gemm_plan_destroy.argtypes = [vp]
+    L.accblas_mg_gemv.argtypes = [vp, vp, ci, ci, i64, i64, vp, vp, vp, i64, vp]
+    L.accblas_mg_dot.argtypes = [vp, vp, ci, ci, i64, vp, vp, vp]
+    for f in (L.accblas_mg_unique_id, L.accblas_mg_init, L.accblas_mg_finalize, L.accblas_mg_rank, L.accblas_mg_world,
+              L.accblas_mg_row_panel, L.accblas_mg_k_chunks, L.accblas_mg_gemm, L.accblas_mg_gemm_plan,
+              L.accblas_mg_gemm_run, L.accblas_mg_gemm_plan_destroy, L.accblas_mg_gemv, L.accblas_mg_dot):
         f.restype = ci
     _lib = L
     return L

@@ -3,12 +3,13 @@
 The reference has no multi-GPU code; this layer is new and its parity oracle is
 the single-GPU result.  Decomposition (BASELINE.json north_star / configs[4]):
 
-  gemm   rows of op(A) and C are split into contiguous panels, one per rank; B is broadcast; C is
-         gathered.  Operands start and the result ends on `root`.  On CUDA the root's A and C are
-         mapped into every rank through CUDA IPC: A panels are pulled by the copy engines and the
-         gemm kernels store their C tiles straight into the root's HBM over NVLink (transport
-         "peer": the gather is the product's own epilogue).  Transport "p2p" (any backend) moves
-         the panels with grouped send/recv, pipelined in sub-panels against the products.
+  gemm   rows of op(A) and C are split into contiguous panels, one per rank; operands start and the
+         result ends on `root`.  On CUDA (transport "peer") this module is a ctypes caller of the C
+         ABI's accblas_mg_gemm / accblas_mg_gemm_plan (csrc/mg.cu): the root's A, B, C are mapped into
+         every rank through CUDA IPC, A panels and B are pulled by the copy engines in K-chunks that
+         overlap the chunk products, and the last chunk's kernel stores its C tiles straight into the
+         root's HBM over NVLink.  Transport "p2p" (any backend) moves the panels with grouped
+         send/recv, pipelined in sub-panels against the products (what the gloo CPU test drives).
   gemv   op N: rows of A and y are split (A pre-sharded), x broadcast, y all-gathered.
          op T/H: rows of A and x are split, every rank forms a full-length partial y, all-reduce.
   dot    contiguous slices (pre-sharded), all-reduce of one scalar.
@@ -20,6 +21,7 @@ from __future__ import annotations
 
 from typing import Callable, List, Optional, Tuple
 
+import numpy as np
 import torch
 import torch.distributed as dist
 
@@ -46,6 +48,7 @@ def _default_gemm():
 
 _ES = {torch.float32: 4, torch.float64: 8, torch.complex64: 8, torch.complex128: 16}
 _CODE = {torch.float32: 0, torch.float64: 1, torch.complex64: 2, torch.complex128: 3}
+_NP = {torch.float32: np.float32, torch.float64: np.float64, torch.complex64: np.complex64, torch.complex128: np.complex128}
 # planning constants for the root bonus (measured on this pool: profiles/): real flop rate of the local
 # gemm and the rate at which NCCL delivers B to the other ranks
 _FLOPS = {torch.float32: 230e12, torch.float64: 36e12, torch.complex64: 228e12, torch.complex128: 36e12}
@@ -166,90 +169,133 @@ def gemm_rowsharded(alpha, opA, A: Optional[torch.Tensor], opB, B: Optional[torc
     return None
 
 
+# ----------------------------------------------------------------------------------------------------------
+# The C ABI's multi-GPU entry points (accblas_mg_*, csrc/mg.cu).  torch.distributed only ships the 128 bootstrap
+# bytes; every transfer, token and exchange below happens inside libaccblas_b200.so.
+# ----------------------------------------------------------------------------------------------------------
+class Comm:
+    """accblas_mg_comm_t of this process (one per process group, created collectively)."""
+
+    def __init__(self, device, group=None):
+        import ctypes
+        from . import _ffi
+        self._ffi, self._ct = _ffi, ctypes
+        self.L = _ffi.lib()
+        self.group = group
+        self.device = torch.device(device)
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        ident = ctypes.create_string_buffer(128)
+        if self.rank == 0:
+            _ffi.check(self.L.accblas_mg_unique_id(ident), "accblas_mg_unique_id")
+        box = [bytes(ident.raw)]
+        src = 0 if group is None else dist.get_global_rank(group, 0)
+        dist.broadcast_object_list(box, src=src, group=group)
+        self.handle = ctypes.c_void_p()
+        with torch.cuda.device(self.device):
+            _ffi.check(self.L.accblas_mg_init(ctypes.byref(self.handle), self.rank, self.world, box[0]), "accblas_mg_init")
+
+    def _stream(self):
+        return self._ct.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def close(self):
+        if self.handle:
+            self.L.accblas_mg_finalize(self.handle)
+            self.handle = None
+
+    # ---- gemm ----
+    def gemm_plan(self, opA, A, opB, B, *, shapeA, shapeB, dtype, out=None, root=0):
+        return GemmPlan(self, opA, A, opB, B, shapeA, shapeB, dtype, out, root)
+
+    # ---- gemv / dot over the exchange buffer ----
+    def gemv(self, alpha, opA, A_local: torch.Tensor, x: torch.Tensor, out: Optional[torch.Tensor] = None):
+        ct = self._ct
+        opa = {"N": 0, "T": 1, "H": 2}.get(opA, opA)
+        A_local, x = A_local.contiguous(), x.contiguous()
+        rows, cols = A_local.shape
+        leny = self.world * rows if opa == 0 else cols
+        y = out if out is not None else torch.empty((leny,), dtype=A_local.dtype, device=A_local.device)
+        al = np.array([alpha], dtype=_NP[A_local.dtype])
+        with torch.cuda.device(self.device):
+            st = self.L.accblas_mg_gemv(self.handle, self._stream(), _CODE[A_local.dtype], opa, rows, cols,
+                                        al.ctypes.data_as(ct.c_void_p), ct.c_void_p(A_local.data_ptr()),
+                                        ct.c_void_p(x.data_ptr()), x.shape[0], ct.c_void_p(y.data_ptr()))
+        self._ffi.check(st, "accblas_mg_gemv")
+        return y
+
+    def dot(self, x: torch.Tensor, y: torch.Tensor, conj: bool = False):
+        ct = self._ct
+        x, y = x.contiguous(), y.contiguous()
+        out = torch.empty((), dtype=x.dtype, device=x.device)
+        with torch.cuda.device(self.device):
+            st = self.L.accblas_mg_dot(self.handle, self._stream(), _CODE[x.dtype], int(conj), min(x.shape[0], y.shape[0]),
+                                       ct.c_void_p(x.data_ptr()), ct.c_void_p(y.data_ptr()), ct.c_void_p(out.data_ptr()))
+        self._ffi.check(st, "accblas_mg_dot")
+        return out
+
+
+class GemmPlan:
+    """accblas_mg_plan_t: the root's A, B, C mapped into every rank, local replicas allocated; run() is the product."""
+
+    def __init__(self, comm: Comm, opA, A, opB, B, shapeA, shapeB, dtype, out, root):
+        ct = comm._ct
+        self.comm = comm
+        self.opa = {"N": 0, "T": 1, "H": 2}.get(opA, opA)
+        self.opb = {"N": 0, "T": 1, "H": 2}.get(opB, opB)
+        m = shapeA[0] if self.opa == 0 else shapeA[1]
+        n = shapeB[1] if self.opb == 0 else shapeB[0]
+        self.dtype, self.root = dtype, root
+        self.C = None
+        ptr = lambda t: ct.c_void_p(t.data_ptr() if t is not None else 0)  # noqa: E731
+        if comm.rank == root:
+            if not (A.is_contiguous() and B.is_contiguous()):
+                raise ValueError("gemm plan: operands must be dense row-major (as Accelerate's are)")
+            self.C = out if out is not None else torch.empty((m, n), dtype=dtype, device=comm.device)
+            if not self.C.is_contiguous():
+                raise ValueError("gemm plan: out must be contiguous")
+            self._keep = (A, B, self.C)
+        else:
+            A = B = None
+        self.handle = ct.c_void_p()
+        with torch.cuda.device(comm.device):
+            st = comm.L.accblas_mg_gemm_plan(comm.handle, _CODE[dtype], self.opa, self.opb, shapeA[0], shapeA[1], shapeB[0],
+                                             shapeB[1], ptr(A), ptr(B), ptr(self.C), root, ct.byref(self.handle))
+        comm._ffi.check(st, "accblas_mg_gemm_plan")
+
+    def run(self, alpha=1.0):
+        ct = self.comm._ct
+        al = np.array([alpha], dtype=_NP[self.dtype])
+        with torch.cuda.device(self.comm.device):
+            st = self.comm.L.accblas_mg_gemm_run(self.handle, self.comm._stream(), al.ctypes.data_as(ct.c_void_p))
+        self.comm._ffi.check(st, "accblas_mg_gemm_run")
+        return self.C
+
+    def destroy(self):
+        if self.handle:
+            self.comm.L.accblas_mg_gemm_plan_destroy(self.handle)
+            self.handle = None
+
+
+_COMMS = {}
+
+
+def get_comm(device, group=None) -> Comm:
+    """The process's communicator for `group` (created collectively on first use, then cached)."""
+    key = (id(group), torch.device(device).index)
+    if key not in _COMMS:
+        _COMMS[key] = Comm(device, group)
+    return _COMMS[key]
+
+
 def _gemm_rowsharded_peer(alpha, opa, A, opb, B, shapeA, shapeB, mnk, dtype, device, root, group, rank, world,
                           out, root_bonus):
-    """transport = "peer": IPC-mapped root operands, copy-engine scatter, gather fused into the epilogue."""
-    import ctypes
-    import numpy as np
-    from . import _ffi
-    L = _ffi.lib()
-    m, n, k = mnk
-    es, code = _ES[dtype], _CODE[dtype]
-    device = torch.device(device)
-    panels = row_panels(m, world, root=root, root_bonus=root_bonus)
-    start, rows = panels[rank]
-    hsz = ctypes.sizeof(_ffi.PeerHandle)
-    alpha_buf = np.array([alpha], dtype={0: np.float32, 1: np.float64, 2: np.complex64, 3: np.complex128}[code])
-    al = alpha_buf.ctypes.data_as(ctypes.c_void_p)
-
-    def stream():
-        return ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream)
-
-    def local_product(a_ptr, a_rows, c_ptr):
-        rA, cA = (a_rows, k) if opa == 0 else (k, a_rows)
-        st = L.accblas_gemm(stream(), code, opa, opb, rA, cA, shapeB[0], shapeB[1], al,
-                            ctypes.c_void_p(a_ptr), ctypes.c_void_p(B.data_ptr()), ctypes.c_void_p(c_ptr))
-        _ffi.check(st, "accblas_gemm (row panel)")
-
-    with torch.cuda.device(device):
-        # ---- handles of the root's A and C: 2 x 88 bytes, every call (the mapping itself is cached) ----
-        if rank == root:
-            if not (A.is_contiguous() and B.is_contiguous()):
-                raise ValueError("gemm_rowsharded: operands must be dense row-major (as Accelerate's are)")
-            C = out if out is not None else torch.empty((m, n), dtype=dtype, device=device)
-            hs = (_ffi.PeerHandle * 2)()
-            for i, t in enumerate((A, C)):
-                st = L.accblas_peer_export(ctypes.c_void_p(t.data_ptr()), ctypes.byref(hs[i]))
-                if st != 0:
-                    raise _ffi.AccblasError(st, "accblas_peer_export",
-                                            "operand is not a cudaMalloc allocation (expandable segments / "
-                                            "cudaMallocAsync backend?): use transport='p2p'")
-            hbuf = torch.frombuffer(bytearray(bytes(hs)), dtype=torch.uint8).to(device)
-        else:
-            hbuf = torch.empty(2 * hsz, dtype=torch.uint8, device=device)
-            B = torch.empty(shapeB, dtype=dtype, device=device)
-        dist.broadcast(hbuf, src=root, group=group)
-        bwork = dist.broadcast(B, src=root, group=group, async_op=True)
-
-        if rank == root:
-            # the root multiplies its own panel while B is still travelling to the others
-            if rows:
-                a_off = start * k * es if opa == 0 else start * es
-                if opa == 0:
-                    local_product(A.data_ptr() + a_off, rows, C.data_ptr() + start * n * es)
-                else:   # column slab of the stored matrix: densify locally (tight leading dimension)
-                    slab = A[:, start:start + rows].contiguous()
-                    local_product(slab.data_ptr(), rows, C.data_ptr() + start * n * es)
-            bwork.wait()
-        else:
-            raw = bytes(hbuf.cpu().numpy().tobytes())
-            hs = (_ffi.PeerHandle * 2).from_buffer_copy(raw)
-            mapped = []
-            for i in range(2):
-                p = ctypes.c_void_p()
-                _ffi.check(L.accblas_peer_open(ctypes.byref(hs[i]), ctypes.byref(p)), "accblas_peer_open")
-                mapped.append(p.value)
-            a_root, c_root = mapped
-            if rows:
-                # scatter: pull this rank's panel of op(A) with the copy engines (overlaps the broadcast)
-                a_loc = torch.empty((rows, k) if opa == 0 else (k, rows), dtype=dtype, device=device)
-                if opa == 0:
-                    st = L.accblas_peer_copy2d(stream(), ctypes.c_void_p(a_loc.data_ptr()), rows * k * es,
-                                               ctypes.c_void_p(a_root + start * k * es), rows * k * es,
-                                               rows * k * es, 1)
-                else:
-                    st = L.accblas_peer_copy2d(stream(), ctypes.c_void_p(a_loc.data_ptr()), rows * es,
-                                               ctypes.c_void_p(a_root + start * es), m * es, rows * es, k)
-                _ffi.check(st, "accblas_peer_copy2d")
-                bwork.wait()
-                # product + gather in one kernel: C tiles are stored into the root's HBM
-                local_product(a_loc.data_ptr(), rows, c_root + start * n * es)
-            else:
-                bwork.wait()
-        # completion handshake, stream ordered on every rank: when it has run on the root, every
-        # peer's kernel (and with it its remote stores) has finished
-        done = torch.zeros(1, dtype=torch.float32, device=device)
-        dist.all_reduce(done, group=group)
+    """transport = "peer": one accblas_mg_gemm (plan + run + destroy) through the C ABI."""
+    comm = get_comm(device, group)
+    plan = comm.gemm_plan(opa, A, opb, B, shapeA=shapeA, shapeB=shapeB, dtype=dtype, out=out, root=root)
+    try:
+        C = plan.run(alpha)
+        torch.cuda.current_stream(torch.device(device)).synchronize()
+    finally:
+        plan.destroy()
     return C if rank == root else None
 
 
@@ -261,6 +307,8 @@ def gemv_sharded(alpha, opA, A_local: torch.Tensor, x: torch.Tensor, *, group=No
           full y on every rank (all-gather of the row slices; panels must be equal-sized).
     op T/H: x is this rank's slice of the vector; returns the full y on every rank (all-reduce).
     """
+    if local_gemv is None and A_local.is_cuda:
+        return get_comm(A_local.device, group).gemv(alpha, opA, A_local, x)      # exchange over peer memory (C ABI)
     if local_gemv is None:
         import accblas_b200 as ab
         local_gemv = ab.gemv
@@ -282,6 +330,8 @@ def gemv_sharded(alpha, opA, A_local: torch.Tensor, x: torch.Tensor, *, group=No
 def dot_sharded(x_local: torch.Tensor, y_local: torch.Tensor, *, conj: bool = False, group=None,
                 local_dot: Optional[Callable] = None):
     """dotu / dotc over pre-sharded slices: local reduction + all-reduce of one scalar."""
+    if local_dot is None and x_local.is_cuda:
+        return get_comm(x_local.device, group).dot(x_local, y_local, conj)        # exchange over peer memory (C ABI)
     if local_dot is None:
         import accblas_b200 as ab
         local_dot = ab.dotc if conj else ab.dotu
@@ -295,15 +345,16 @@ def dot_sharded(x_local: torch.Tensor, y_local: torch.Tensor, *, conj: bool = Fa
 
 
 # ----------------------------------------------------------------------------------------------------------
-# 2-D block sharding: for products whose operands do not fit one GPU.
+# 2-D block sharding: SUMMA, for products whose operands do not fit one GPU.
 # The ranks form a pr x pc grid (rank = i * pc + j).  Rank (i, j) holds
 #   block (i, j) of op(A): rows [i * m/pr, ...) x K-columns [j * k/pc, ...)     in its STORED (pre-op) layout,
 #   block (i, j) of op(B): K-rows [i * k/pr, ...) x columns [j * n/pc, ...)     in its stored layout,
-# and receives block (i, j) of C.  C_ij = op(A)_(i,:) * op(B)_(:,j): the A blocks are all-gathered along the
-# process ROW, the B blocks along the process COLUMN, then ONE local product runs -- the library has no
-# beta = 1 accumulation (the reference never needs it: beta = 0, LLVM/PTX/Level3.hs:90), so instead of SUMMA's
-# K-step loop the whole K extent of the row / column panel is assembled first.  Per-rank memory is
-# m k / pr + k n / pc + m n / (pr pc) elements; the bytes moved are SUMMA's.
+# and receives block (i, j) of C.  K is cut into L = lcm(pr, pc) steps of k / L (the common refinement of the two
+# block distributions).  Step t: the process-ROW broadcasts the K-slab t of op(A)_(i,:) from the rank that owns it,
+# the process-COLUMN broadcasts the K-slab t of op(B)_(:,j), and every rank accumulates
+#       C_ij = alpha * slab_A * slab_B + C_ij          (beta = 1 in the product's epilogue: accblas_gemm_ex)
+# The broadcasts of step t + 1 are in flight while step t multiplies (two slab buffers per operand).
+# Per-rank memory: the three blocks + two K-slabs of each operand -- never a whole row / column panel.
 # ----------------------------------------------------------------------------------------------------------
 _GRID_GROUPS = {}
 
@@ -315,13 +366,23 @@ def _grid_groups(pr: int, pc: int, group=None):
         base = list(range(pr * pc)) if group is None else dist.get_process_group_ranks(group)
         rows = [dist.new_group([base[i * pc + j] for j in range(pc)]) for i in range(pr)]
         cols = [dist.new_group([base[i * pc + j] for i in range(pr)]) for j in range(pc)]
-        _GRID_GROUPS[key] = (rows, cols)
+        _GRID_GROUPS[key] = (rows, cols, base)
     return _GRID_GROUPS[key]
+
+
+def summa_steps(pr: int, pc: int):
+    """[(owner column of the A slab, slab index inside that block, owner row of the B slab, slab index inside it)]
+    for the L = lcm(pr, pc) K-steps."""
+    from math import gcd
+    L = pr * pc // gcd(pr, pc)
+    return [(t // (L // pc), t % (L // pc), t // (L // pr), t % (L // pr)) for t in range(L)]
 
 
 def gemm_2d(alpha, opA, A_blk: torch.Tensor, opB, B_blk: torch.Tensor, *, grid: Tuple[int, int], group=None,
             local_gemm: Optional[Callable] = None) -> torch.Tensor:
-    """Block (i, j) of C = alpha * op(A) * op(B) on a pr x pc grid of ranks (see above); blocks must be equal-sized."""
+    """Block (i, j) of C = alpha * op(A) * op(B) on a pr x pc grid of ranks (SUMMA, see above); blocks must be
+    equal-sized and the K extent of a block divisible by lcm(pr, pc) / pc (resp. / pr).
+    local_gemm(alpha, opa, A, opb, B, out=, beta=, Cin=) defaults to accblas_b200.gemm."""
     pr, pc = grid
     world = dist.get_world_size(group)
     if pr * pc != world:
@@ -331,14 +392,49 @@ def gemm_2d(alpha, opA, A_blk: torch.Tensor, opB, B_blk: torch.Tensor, *, grid: 
     local_gemm = local_gemm or _default_gemm()
     rank = dist.get_rank(group)
     i, j = divmod(rank, pc)
-    rows, cols = _grid_groups(pr, pc, group)
+    rows, cols, base = _grid_groups(pr, pc, group)
     A_blk, B_blk = A_blk.contiguous(), B_blk.contiguous()
-    # op(A)_(i,:): K runs along the stored columns for N, along the stored rows for T / H
-    parts = [torch.empty_like(A_blk) for _ in range(pc)]
-    dist.all_gather(parts, A_blk, group=rows[i])
-    A_panel = torch.cat(parts, dim=1 if opa == 0 else 0) if pc > 1 else A_blk
-    # op(B)_(:,j): K runs along the stored rows for N, along the stored columns for T / H
-    parts = [torch.empty_like(B_blk) for _ in range(pr)]
-    dist.all_gather(parts, B_blk, group=cols[j])
-    B_panel = torch.cat(parts, dim=0 if opb == 0 else 1) if pr > 1 else B_blk
-    return local_gemm(alpha, opa, A_panel, opb, B_panel)
+    steps = summa_steps(pr, pc)
+    L = len(steps)
+    # K extents: op(A) block is mb x ka with ka = k / pc; op(B) block is kb x nb with kb = k / pr; a step moves kk = k / L
+    ka = A_blk.shape[1] if opa == 0 else A_blk.shape[0]
+    kb = B_blk.shape[0] if opb == 0 else B_blk.shape[1]
+    mb = A_blk.shape[0] if opa == 0 else A_blk.shape[1]
+    nb = B_blk.shape[1] if opb == 0 else B_blk.shape[0]
+    if ka * pc != kb * pr or (ka * pc) % L:
+        raise ValueError("gemm_2d: the K extents of the blocks do not tile the common refinement")
+    kk = ka * pc // L
+
+    def a_slab(s):      # K-slab s of my op(A) block, in stored layout, contiguous
+        return (A_blk[:, s * kk:(s + 1) * kk] if opa == 0 else A_blk[s * kk:(s + 1) * kk]).contiguous()
+
+    def b_slab(s):
+        return (B_blk[s * kk:(s + 1) * kk] if opb == 0 else B_blk[:, s * kk:(s + 1) * kk]).contiguous()
+
+    a_shape = (mb, kk) if opa == 0 else (kk, mb)
+    b_shape = (kk, nb) if opb == 0 else (nb, kk)
+
+    def post(t):        # start the two broadcasts of step t; returns (A slab, B slab, works)
+        ja, sa, ib, sb = steps[t]
+        abuf = a_slab(sa) if ja == j else torch.empty(a_shape, dtype=A_blk.dtype, device=A_blk.device)
+        bbuf = b_slab(sb) if ib == i else torch.empty(b_shape, dtype=B_blk.dtype, device=B_blk.device)
+        works = []
+        if pc > 1:
+            works.append(dist.broadcast(abuf, src=base[i * pc + ja], group=rows[i], async_op=True))
+        if pr > 1:
+            works.append(dist.broadcast(bbuf, src=base[ib * pc + j], group=cols[j], async_op=True))
+        return abuf, bbuf, works
+
+    C = torch.empty((mb, nb), dtype=A_blk.dtype, device=A_blk.device)
+    nxt = post(0)
+    for t in range(L):
+        abuf, bbuf, works = nxt
+        if t + 1 < L:
+            nxt = post(t + 1)                       # step t + 1 travels while step t multiplies
+        for w in works:
+            w.wait()
+        if t == 0:
+            local_gemm(alpha, opa, abuf, opb, bbuf, out=C)
+        else:
+            local_gemm(alpha, opa, abuf, opb, bbuf, out=C, beta=1, Cin=C)
+    return C

@@ -338,9 +338,22 @@ def run_multi(args):
         B = seeded((n, n), 0x5EED0000 + 64 + 1, dev)
         C = torch.empty((n, n), dtype=torch.float64, device=dev)
 
-    def step():
-        return mg.gemm_rowsharded(1.0, "N", A, "N", B, shapeA=(n, n), shapeB=(n, n), dtype=torch.float64,
-                                  device=dev, root=0, subpanels=args.subpanels, out=C, transport=args.transport)
+    # parity of the sharded paths BEFORE anything is timed (tools/mg_check.py, quick subset: C-ABI peer pipeline, plan / run,
+    # SUMMA, gemv / dot exchanges, every rank): a mismatch fails the bench
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import mg_check
+    mg_cases, mg_worst = mg_check.check(dev, rank, world, quick=True)
+
+    if args.transport == "peer":
+        comm = mg.get_comm(dev)
+        plan = comm.gemm_plan("N", A, "N", B, shapeA=(n, n), shapeB=(n, n), dtype=torch.float64, out=C, root=0)
+
+        def step():
+            return plan.run(1.0)                 # accblas_mg_gemm_run: no handle exchange, no host synchronisation
+    else:
+        def step():
+            return mg.gemm_rowsharded(1.0, "N", A, "N", B, shapeA=(n, n), shapeB=(n, n), dtype=torch.float64,
+                                      device=dev, root=0, subpanels=args.subpanels, out=C, transport=args.transport)
     for _ in range(args.warmup):
         step()
     torch.cuda.synchronize()
@@ -363,20 +376,30 @@ def run_multi(args):
     launches = torch.tensor([ab.launch_count() - l0], dtype=torch.int64, device=dev)
     dist.all_reduce(launches, op=dist.ReduceOp.SUM)
     total_ms = ms.item()
-    # untimed extra: what the broadcast of B alone costs (explains the gap to N x single-GPU)
-    Bx = B if rank == 0 else torch.empty((n, n), dtype=torch.float64, device=dev)
-    dist.broadcast(Bx, src=0)
+    # untimed extra: what ONE rank's panel product costs with its operands already local (explains the gap between
+    # the step and pure compute: first-chunk exposure, per-chunk launches, the tokens, the tail)
+    if args.transport == "peer":
+        plan.destroy()
+    rows = -(-n // world)
+    rows = -(-rows // 128) * 128
+    Ap = seeded((min(rows, n), n), 0x5EED0000 + 80 + rank, dev)
+    Bl = B if rank == 0 else seeded((n, n), 0x5EED0000 + 65, dev)
+    Cp = torch.empty((Ap.shape[0], n), dtype=torch.float64, device=dev)
+    ab.gemm(1.0, "N", Ap, "N", Bl, out=Cp)
     torch.cuda.synchronize()
     dist.barrier()
-    torch.cuda.synchronize()
     b0, b1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     b0.record()
-    dist.broadcast(Bx, src=0)
+    for _ in range(2):
+        ab.gemm(1.0, "N", Ap, "N", Bl, out=Cp)
     b1.record()
     torch.cuda.synchronize()
-    bms = torch.tensor([b0.elapsed_time(b1)], dtype=torch.float64, device=dev)
+    bms = torch.tensor([b0.elapsed_time(b1) / 2], dtype=torch.float64, device=dev)
     dist.all_reduce(bms, op=dist.ReduceOp.MAX)
-    del Bx
+    del Ap, Cp
+    if rank != 0:
+        del Bl
+    torch.cuda.empty_cache()
     l12 = mg_level12_extras(dev, rank, world) if args.n_mg >= 4096 else []
     if rank == 0:
         clocks = sampler.stop(t0, t1)
@@ -396,8 +419,8 @@ def run_multi(args):
             "data": "synthetic uniform(-1,1), fixed Philox seeds", "config": workload_config(world) | {"m": n, "n": n, "k": n},
             "roofline": {"bound": "tensor", "achieved": round(value / world, 3), "peak": peak, "unit": "TFLOP/s",
                          "frac": round(value / world / peak, 4), "traffic": None,
-                         "kernel": "dgemm_dmma_kernel<true,false> per rank; achieved = whole-job rate / ranks "
-                                   "(includes scatter/broadcast/gather time)", "peak_source": peak_src,
+                         "kernel": "dgemm_dmma (persistent schedule) per rank, K-chunked; achieved = whole-job rate / ranks "
+                                   "(includes every inter-GPU transfer)", "peak_source": peak_src,
                          "nvlink_bytes_through_root": comm_bytes},
             "cpu_baseline": None,
             "e2e": {"value": round(value, 3), "unit": "TFLOP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0,
@@ -407,7 +430,10 @@ def run_multi(args):
             "parity": {"error_units": round(err, 5), "tolerance_units": 1.0, "rows_checked": len(rows)},
         }
         line["config"]["transport"] = args.transport
-        line["broadcast_B_ms"] = round(bms.item(), 3)
+        line["config"]["api"] = "accblas_mg_gemm_plan / accblas_mg_gemm_run (C ABI, csrc/mg.cu)" if args.transport == "peer" else "mg.gemm_rowsharded (p2p)"
+        line["panel_product_ms"] = round(bms.item(), 3)
+        line["overhead_vs_panel_product_ms"] = round(total_ms / args.steps - bms.item(), 3)
+        line["mg_check"] = {"cases": mg_cases, "worst_gemm_error_units": round(mg_worst, 5), "when": "before timing, every rank"}
         line["extras"] = l12
     dist.destroy_process_group()
     sys.stdout.flush()

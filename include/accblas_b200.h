@@ -234,6 +234,61 @@ int accblas_peer_copy2d(accblas_stream_t stream, void *dst, size_t dst_pitch, co
                         size_t src_pitch, size_t width_bytes, size_t rows);
 
 /* ------------------------------------------------------------------------------------
+ * Multi-GPU (one process per GPU of one NVLink / NVSwitch box).  NEW: the reference is single-GPU (one cuBLAS
+ * handle per CUDA context, LLVM/PTX/Context.hs:50-65); BASELINE.json configs[4] and SURVEY.md section 8(e) define the
+ * decomposition.  A host runtime with one OS process per device (e.g. one Accelerate `PTX` context each) calls these
+ * the way it calls accblas_gemm; `comm` is created once per process.
+ *
+ *   accblas_mg_unique_id   rank 0: 128 bootstrap bytes; ship them to the other ranks with any transport.
+ *   accblas_mg_init        collective; uses the CUDA device current on the calling thread.  Loads NCCL with dlopen
+ *                          (libnccl.so.2 or $ACCBLAS_NCCL_LIB) -- the library itself links only cudart.
+ *   accblas_mg_gemm        C = alpha * op(A) * op(B), operands and result on `root` (pass NULL elsewhere); rows of
+ *                          op(A) / C are split over the ranks (accblas_mg_row_panel).  Peers PULL their A panel and B
+ *                          from the root's HBM with the copy engines in K-chunks (accblas_mg_k_chunks), multiply
+ *                          each chunk as it lands (beta = 1 accumulation, accblas_gemm_ex) and store the last chunk's
+ *                          result straight into the root's C over NVLink (gather fused into the epilogue).  The
+ *                          root's A, B, C must come from cudaMalloc (CUDA IPC).  Collective, stream-ordered: when
+ *                          the call's work has completed on the root's stream, C is complete.
+ *   accblas_mg_gemm_plan / _run / _plan_destroy
+ *                          the same, split: the plan exchanges the IPC handles and allocates the peers' replicas
+ *                          once, so that a loop over the same arrays pays no handle exchange or host
+ *                          synchronisation per product.
+ *   accblas_mg_gemv        y = alpha * op(A) * x with the ROWS of the stored A pre-sharded (A_local = rows_local x colsA;
+ *                          equal panels).  op N: x (colsA) replicated, every rank receives the full y
+ *                          (world * rows_local).  op T / H: x = this rank's slice (rows_local); every rank receives the
+ *                          full y (colsA), partials summed in rank order.
+ *   accblas_mg_dot         dotu / dotc over pre-sharded slices; every rank receives the scalar in out_dev.
+ *                          gemv / dot exchange through IPC-mapped buffers with flags (no collective kernel);
+ *                          at most 1 MiB of y per rank (ACCBLAS_ERR_WORKSPACE beyond).  Calls on one communicator
+ *                          must be issued in the same order by every rank, on streams ordered one after another.
+ * ---------------------------------------------------------------------------------- */
+#define ACCBLAS_MG_ID_BYTES 128
+typedef struct accblas_mg_comm_s *accblas_mg_comm_t;
+typedef struct accblas_mg_plan_s *accblas_mg_plan_t;
+int accblas_mg_unique_id(void *id_out);
+int accblas_mg_init(accblas_mg_comm_t *comm, int rank, int world, const void *id_bytes);
+int accblas_mg_finalize(accblas_mg_comm_t comm);
+int accblas_mg_rank(accblas_mg_comm_t comm);
+int accblas_mg_world(accblas_mg_comm_t comm);
+/* this rank's panel of the m rows: 128-aligned contiguous panels, ranks past the end get rows = 0 */
+int accblas_mg_row_panel(int64_t m, int world, int rank, int64_t *start, int64_t *rows);
+/* the K-chunks of the pipelined product (k0[i], dk[i]); returns their number (<= cap) */
+int accblas_mg_k_chunks(int64_t k, int64_t *k0_out, int64_t *dk_out, int cap);
+int accblas_mg_gemm(accblas_mg_comm_t comm, accblas_stream_t stream, int dtype, int opA, int opB,
+                    int64_t rowsA, int64_t colsA, int64_t rowsB, int64_t colsB,
+                    const void *alpha_host, const void *A, const void *B, void *C, int root);
+int accblas_mg_gemm_plan(accblas_mg_comm_t comm, int dtype, int opA, int opB,
+                         int64_t rowsA, int64_t colsA, int64_t rowsB, int64_t colsB,
+                         const void *A, const void *B, void *C, int root, accblas_mg_plan_t *plan);
+int accblas_mg_gemm_run(accblas_mg_plan_t plan, accblas_stream_t stream, const void *alpha_host);
+int accblas_mg_gemm_plan_destroy(accblas_mg_plan_t plan);
+int accblas_mg_gemv(accblas_mg_comm_t comm, accblas_stream_t stream, int dtype, int opA,
+                    int64_t rows_local, int64_t colsA, const void *alpha_host,
+                    const void *A_local, const void *x, int64_t lenx, void *y_full);
+int accblas_mg_dot(accblas_mg_comm_t comm, accblas_stream_t stream, int dtype, int conj_x, int64_t n_local,
+                   const void *x_local, const void *y_local, void *out_dev);
+
+/* ------------------------------------------------------------------------------------
  * Introspection / tuning.  None of these change results beyond the stated tolerance.
  * ---------------------------------------------------------------------------------- */
 int accblas_version(void);                     /* ACCBLAS_B200_VERSION */
@@ -289,7 +344,9 @@ typedef enum {
                                        f64 tile, fenced elsewhere (csrc/gemm_dmma.cu: release_mode)                                 */
     ACCBLAS_TUNE_MN_ONEBOX = 13,    /* f64 gemm: 0 = fetch an MN-major operand panel as 16 x 16 TMA boxes (round 1), default: as ONE
                                        3-D box per stage when the extent is a multiple of 16                                       */
-    ACCBLAS_TUNE_COUNT = 14
+    ACCBLAS_TUNE_MG_SELF_PEER = 14, /* accblas_mg_gemm_plan: 1 = the root also runs the peers' pull / K-chunk pipeline on its own
+                                       arrays (test hook: exercises that path on a one-GPU box)                                    */
+    ACCBLAS_TUNE_COUNT = 15
 } accblas_tune_t;
 /* Process-wide defaults for threads that never call this: environment variable
  * ACCBLAS_TUNE="knob=value,knob=value" (read once). */

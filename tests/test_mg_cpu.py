@@ -12,9 +12,11 @@ import torch.multiprocessing as mp
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-def _local_gemm(alpha, opa, A, opb, B, out=None):
+def _local_gemm(alpha, opa, A, opb, B, out=None, beta=None, Cin=None):
     from oracle import openblas_ref as R
     C = torch.from_numpy(R.gemm(alpha, opa, A.numpy(), opb, B.numpy()))
+    if Cin is not None:
+        C = C + (1 if beta is None else beta) * Cin
     if out is not None:
         out.copy_(C)
         return out
@@ -126,6 +128,34 @@ def test_world4_gloo_2d_blocks():
         assert len(res) == 24, (rank, len(res))
         for kname, err in res.items():
             assert err <= 2.0, (rank, kname, err)
+
+
+def test_summa_steps_and_c_abi_partitioning():
+    """The K-step schedule of mg.gemm_2d and the partitioning the C ABI exports (accblas_mg_row_panel,
+    accblas_mg_k_chunks): pure host logic, no GPU."""
+    import ctypes
+    sys.path.insert(0, os.path.join(ROOT, "accelerate-blas_b200", "python"))
+    from accblas_b200 import _ffi
+    from accblas_b200.mg import row_panels, summa_steps
+    assert summa_steps(2, 2) == [(0, 0, 0, 0), (1, 0, 1, 0)]
+    assert summa_steps(1, 4) == [(t, 0, 0, t) for t in range(4)]
+    assert summa_steps(2, 3) == [(0, 0, 0, 0), (0, 1, 0, 1), (1, 0, 0, 2), (1, 1, 1, 0), (2, 0, 1, 1), (2, 1, 1, 2)]
+    L = _ffi.lib()
+    s, r = ctypes.c_int64(), ctypes.c_int64()
+    for m, w in [(32768, 8), (300, 2), (5, 4), (1000, 3), (129, 8), (0, 2)]:
+        mine = []
+        for rk in range(w):
+            assert L.accblas_mg_row_panel(m, w, rk, ctypes.byref(s), ctypes.byref(r)) == 0
+            mine.append((s.value, r.value))
+        assert mine == row_panels(m, w), (m, w, mine)          # the python planner and the library agree
+    k0, dk = (ctypes.c_int64 * 64)(), (ctypes.c_int64 * 64)()
+    for k in (0, 1, 100, 4095, 4096, 5000, 8192, 32768, 33000, 100000):
+        n = L.accblas_mg_k_chunks(k, k0, dk, 64)
+        ch = [(k0[i], dk[i]) for i in range(n)]
+        assert sum(d for _, d in ch) == k and all(ch[i][0] + ch[i][1] == ch[i + 1][0] for i in range(n - 1)), (k, ch)
+        assert all(c0 % 512 == 0 for c0, _ in ch) and (k < 4096 or ch[0][1] == 512), (k, ch)
+    assert L.accblas_mg_k_chunks(1 << 20, k0, dk, 4) == 4 and k0[3] + dk[3] == 1 << 20   # cap: the last chunk takes the rest
+    assert L.accblas_mg_row_panel(10, 0, 0, ctypes.byref(s), ctypes.byref(r)) != 0
 
 
 def test_row_panels():

@@ -332,3 +332,72 @@ def test_baseline_ddot_2p28(cuda):
     assert abs(float(d) - ref) <= n * O.EPS[O.F64] * nx * ny
     # a blocked double-precision sum sits far inside the worst-case bound: 1e-3 of it is still generous
     assert abs(float(d) - ref) <= 1e-3 * n * O.EPS[O.F64] * nx * ny
+
+
+# ------------------------------------------------------------------------------------------ multi-GPU C ABI, one rank
+def test_mg_c_abi_single_rank(cuda):
+    """accblas_mg_* with world = 1 (what a one-GPU box can run): communicator bootstrap through NCCL, gemm through
+    the plan / run entry points (root path == accblas_gemm bit for bit), the peers' pull / K-chunk / beta = 1 pipeline
+    driven on the root's own arrays (ACCBLAS_TUNE_MG_SELF_PEER) against the oracle, gemv / dot through the exchange
+    buffer (== the single-GPU kernels bit for bit)."""
+    import ctypes
+    import torch
+    import accblas_b200 as ab
+    L = ab.lib()
+    vp = ctypes.c_void_p
+    ident = ctypes.create_string_buffer(128)
+    assert L.accblas_mg_unique_id(ident) == 0, L.accblas_last_cuda_error()
+    comm = vp()
+    with torch.cuda.device(cuda):
+        st = L.accblas_mg_init(ctypes.byref(comm), 0, 1, ident.raw)
+    assert st == 0, L.accblas_last_cuda_error()
+    assert L.accblas_mg_rank(comm) == 0 and L.accblas_mg_world(comm) == 1
+    stream = lambda: vp(torch.cuda.current_stream(cuda).cuda_stream)  # noqa: E731
+    p = lambda t: vp(t.data_ptr())  # noqa: E731
+    rng = np.random.default_rng(11500)
+    try:
+        for self_peer in (0, 1):
+            ab.set_tuning(ab.TUNE_MG_SELF_PEER, self_peer)
+            for dt, tdt in ((O.F64, torch.float64), (O.C32, torch.complex64)):
+                for (oa, ob, m, n, k) in [("N", "N", 384, 256, 8704), ("T", "N", 256, 384, 5000), ("N", "H", 130, 200, 4608),
+                                          ("H", "T", 200, 130, 700)]:
+                    al, A, B = gemm_inputs(rng, dt, oa, ob, m, n, k)
+                    dA, dB = dev(A, cuda), dev(B, cuda)
+                    C = torch.full((m, n), float("nan"), dtype=tdt, device=cuda)
+                    alb = np.array([al], dtype=A.dtype)
+                    plan = vp()
+                    code = {"N": 0, "T": 1, "H": 2}
+                    st = L.accblas_mg_gemm_plan(comm, dt, code[oa], code[ob], A.shape[0], A.shape[1], B.shape[0], B.shape[1],
+                                                p(dA), p(dB), p(C), 0, ctypes.byref(plan))
+                    assert st == 0, (st, L.accblas_last_cuda_error())
+                    for rep in range(2):
+                        assert L.accblas_mg_gemm_run(plan, stream(), alb.ctypes.data_as(vp)) == 0, L.accblas_last_cuda_error()
+                        torch.cuda.synchronize()
+                        if self_peer == 0:
+                            assert torch.equal(C, ab.gemm(al, oa, dA, ob, dB)), (oa, ob, m, n, k)
+                        else:
+                            err = O.gemm_error_units(host(C), O.gemm(al, oa, A, ob, B, wide=True), A, B, k, al)
+                            assert err <= TOL_UNITS_TF32X3, (O.NAMES[dt], oa, ob, m, n, k, err)
+                    assert L.accblas_mg_gemm_plan_destroy(plan) == 0
+        ab.set_tuning(ab.TUNE_MG_SELF_PEER, -1)
+        # gemv N / T / H and dot: with one rank the exchange must reproduce the local kernels exactly
+        for dt, tdt in ((O.F64, torch.float64), (O.C64, torch.complex128), (O.F32, torch.float32)):
+            A = dev(O.uniform(rng, (700, 520), dt), cuda)
+            one = np.array([1], dtype=O.NP_DTYPE[dt])
+            for op, nx, ny in (("N", 520, 700), ("T", 700, 520), ("H", 700, 520)):
+                x = dev(O.uniform(rng, (nx,), dt), cuda)
+                y = torch.empty((ny,), dtype=tdt, device=cuda)
+                for rep in range(3):
+                    st = L.accblas_mg_gemv(comm, stream(), dt, {"N": 0, "T": 1, "H": 2}[op], 700, 520, one.ctypes.data_as(vp),
+                                           p(A), p(x), nx, p(y))
+                    assert st == 0, L.accblas_last_cuda_error()
+                assert torch.equal(y, ab.gemv(1, op, A, x)), (O.NAMES[dt], op)
+            u, v = dev(O.uniform(rng, (100003,), dt), cuda), dev(O.uniform(rng, (100003,), dt), cuda)
+            out = torch.empty((), dtype=tdt, device=cuda)
+            for conj in (0, 1):
+                assert L.accblas_mg_dot(comm, stream(), dt, conj, 100003, p(u), p(v), p(out)) == 0
+                assert torch.equal(out, (ab.dotc if conj else ab.dotu)(u, v))
+    finally:
+        ab.set_tuning(ab.TUNE_MG_SELF_PEER, -1)
+        torch.cuda.synchronize()
+        L.accblas_mg_finalize(comm)

@@ -1,6 +1,7 @@
 """tools/mg_check.py -- run under torch.distributed.run on >= 2 GPUs: checks the sharded products of
-accblas_b200.mg (both transports, all op flags, real and complex) against the single-GPU library on
-rank 0 and against the oracle.  Prints one line `mg_check ok ...` on rank 0; any failure raises.
+the C ABI's accblas_mg_* entry points (driven through accblas_b200.mg, a ctypes caller) -- all op flags, real and
+complex, one-shot and plan / run -- plus the p2p transport, SUMMA and the gemv / dot exchanges, against the oracle.
+bench.py --gpus N runs check(quick=True) before timing and fails on a mismatch.  Prints one line `mg_check ok ...` on rank 0; any failure raises.
 
     python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 tools/mg_check.py
 """
@@ -15,20 +16,25 @@ import torch  # noqa: E402
 import torch.distributed as dist  # noqa: E402
 
 
-def main():
-    import accblas_b200 as ab
+def check(dev, rank, world, quick=False):
+    """The sharded products against the oracle: accblas_mg_gemm through the C ABI (one-shot and plan / run, every op
+    class, three dtypes, K long enough for several pull chunks), the p2p transport, SUMMA (mg.gemm_2d) on the grids
+    this world size allows, and the gemv / dot exchanges over peer memory.  Returns (cases, worst error units);
+    raises on the first mismatch.  `quick` = the subset bench.py runs before timing."""
+    import accblas_b200 as ab  # noqa: F401
     from accblas_b200 import mg
     from oracle import oracle as O
-    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
-    dev = torch.device(f"cuda:{int(os.environ.get('LOCAL_RANK', rank))}")
-    torch.cuda.set_device(dev)
-    dist.init_process_group("nccl", device_id=dev)
     rng = np.random.default_rng(7)
     worst, cases = 0.0, 0
-    for transport in ("peer", "p2p"):
-        for (oa, ob, m, n, k) in [("N", "N", 1024, 512, 768), ("T", "N", 900, 256, 512), ("N", "T", 130, 64, 64),
-                                  ("H", "H", 640, 384, 256), ("N", "N", 100, 40, 30)]:
+    shapes = [("N", "N", 1024, 512, 768), ("T", "N", 900, 256, 512), ("N", "T", 130, 64, 64), ("H", "H", 640, 384, 256),
+              ("N", "N", 100, 40, 30), ("N", "N", 640, 256, 8704), ("T", "H", 512, 200, 6000)]
+    if quick:
+        shapes = [("N", "N", 1024, 512, 768), ("H", "H", 640, 384, 4608), ("N", "N", 100, 40, 30)]
+    for transport in ("peer",) if quick else ("peer", "p2p"):
+        for (oa, ob, m, n, k) in shapes:
             for dt, tdt in ((O.F64, torch.float64), (O.C64, torch.complex128), (O.F32, torch.float32)):
+                if quick and dt == O.F32:
+                    continue
                 A = O.uniform(rng, (m, k) if oa == "N" else (k, m), dt)
                 B = O.uniform(rng, (k, n) if ob == "N" else (n, k), dt)
                 tA = torch.from_numpy(A).to(dev) if rank == 0 else None
@@ -44,8 +50,28 @@ def main():
                         cases += 1
                     else:
                         assert C is None
-    # 2-D block sharding (mg.gemm_2d) on the grids this world size allows
-    for (pr, pc) in [(1, world), (world, 1)] + ([(2, world // 2)] if world >= 4 and world % 2 == 0 else []):
+    # plan / run: one plan, three products into the same C (the root rewrites A between them)
+    comm = mg.get_comm(dev)
+    m, n, k = 768, 640, 5120
+    A = O.uniform(rng, (m, k), O.F64)
+    B = O.uniform(rng, (k, n), O.F64)
+    tA = torch.from_numpy(A).to(dev) if rank == 0 else None
+    tB = torch.from_numpy(B).to(dev) if rank == 0 else None
+    plan = comm.gemm_plan("N", tA, "N", tB, shapeA=A.shape, shapeB=B.shape, dtype=torch.float64)
+    for rep in range(3):
+        if rank == 0:
+            tA.mul_(-1.0)
+        C = plan.run(2.0)
+        torch.cuda.synchronize()
+        if rank == 0:
+            sign = -1.0 if rep % 2 == 0 else 1.0
+            err = O.gemm_error_units(C.cpu().numpy(), O.gemm(2.0 * sign, "N", A, "N", B), A, B, k, 2.0)
+            assert err <= 1.0, ("plan/run", rep, err)
+            cases += 1
+    plan.destroy()
+    # 2-D block sharding (mg.gemm_2d, SUMMA K-loop) on the grids this world size allows
+    grids = [(1, world), (world, 1)] + ([(2, world // 2)] if world >= 4 and world % 2 == 0 else [])
+    for (pr, pc) in grids[:1] if quick else grids:
         gi, gj = divmod(rank, pc)
         for (oa, ob, mb, nb, kb) in [("N", "N", 256, 192, 128), ("T", "N", 130, 64, 96), ("H", "H", 64, 72, 200)]:
             for dt, tdt in ((O.F64, torch.float64), (O.C32, torch.complex64)):
@@ -64,22 +90,43 @@ def main():
                 err = float(np.linalg.norm(C.cpu().numpy() - ref)) / ((k + 2) * eps * 0.5 * np.linalg.norm(A) * np.linalg.norm(B))
                 assert err <= 2.0, ("gemm_2d", pr, pc, oa, ob, dt, err)
                 cases += 1
-    # gemv / dot on pre-sharded operands
-    m, n = 512 * world, 384
-    A = O.uniform(rng, (m, n), O.F64)
-    x, x2 = O.uniform(rng, (n,), O.F64), O.uniform(rng, (m,), O.F64)
-    sl = slice(rank * 512, (rank + 1) * 512)
-    y = mg.gemv_sharded(1.0, "N", torch.from_numpy(A[sl]).to(dev), torch.from_numpy(x).to(dev))
-    assert O.gemm_error_units(y.cpu().numpy(), O.gemv(1.0, "N", A, x), A, x, n) <= 1.0
-    y = mg.gemv_sharded(1.0, "T", torch.from_numpy(A[sl]).to(dev), torch.from_numpy(x2[sl]).to(dev))
-    assert O.gemm_error_units(y.cpu().numpy(), O.gemv(1.0, "T", A, x2), A, x2, m) <= 1.0
-    d = mg.dot_sharded(torch.from_numpy(x2[sl]).to(dev), torch.from_numpy(x2[sl]).to(dev))
-    assert abs(d.item() - O.dot(x2, x2)) <= m * 2.0 ** -53 * np.linalg.norm(x2) ** 2
+    # gemv / dot on pre-sharded operands: exchange over peer memory; every rank must hold the same bits
+    for dt, tdt in ((O.F64, torch.float64), (O.C32, torch.complex64)):
+        m, n = 512 * world, 384
+        A = O.uniform(rng, (m, n), dt)
+        x, x2 = O.uniform(rng, (n,), dt), O.uniform(rng, (m,), dt)
+        sl = slice(rank * 512, (rank + 1) * 512)
+        for rep in range(3):      # back-to-back collectives alternate the two halves of the exchange buffer
+            y = mg.gemv_sharded(1.0, "N", torch.from_numpy(A[sl]).to(dev), torch.from_numpy(x).to(dev))
+            assert O.gemm_error_units(y.cpu().numpy(), O.gemv(1.0, "N", A, x), A, x, n) <= 2.0
+            for op in ("T", "H"):
+                y = mg.gemv_sharded(1.0, op, torch.from_numpy(A[sl]).to(dev), torch.from_numpy(x2[sl]).to(dev))
+                assert O.gemm_error_units(y.cpu().numpy(), O.gemv(1.0, op, A, x2), A, x2, m) <= 2.0
+            for conj in (False, True):
+                d = mg.dot_sharded(torch.from_numpy(x2[sl]).to(dev), torch.from_numpy(x2[sl]).to(dev), conj=conj)
+                ref = O.dot(x2, x2, conj=conj)
+                assert abs(complex(d.item()) - complex(ref)) <= m * O.EPS[dt] * np.linalg.norm(x2) ** 2
+        same = torch.view_as_real(y).clone() if y.is_complex() else y.clone()
+        lo, hi = same.clone(), same.clone()
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+        dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+        assert torch.equal(lo, hi), "ranks hold different bits of the all-reduced y"
+        cases += 1
     torch.cuda.synchronize()
     dist.barrier()
+    return cases, worst
+
+
+def main():
+    import accblas_b200 as ab
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    dev = torch.device(f"cuda:{int(os.environ.get('LOCAL_RANK', rank))}")
+    torch.cuda.set_device(dev)
+    dist.init_process_group("nccl", device_id=dev)
+    cases, worst = check(dev, rank, world)
     if rank == 0:
-        print(f"mg_check ok: world {world}, {cases} sharded gemm cases (peer + p2p), worst {worst:.4f} units; "
-              f"gemv N/T and dot sharded ok", flush=True)
+        print(f"mg_check ok: world {world}, {cases} sharded cases (C-ABI peer pipeline + p2p + SUMMA + gemv / dot exchange), "
+              f"worst gemm error {worst:.4f} units", flush=True)
     dist.destroy_process_group()
     ab.lib().accblas_peer_close_all()
 
