@@ -394,7 +394,7 @@ def test_mg_c_abi_single_rank(cuda):
                 assert torch.equal(y, ab.gemv(1, op, A, x)), (O.NAMES[dt], op)
             u, v = dev(O.uniform(rng, (100003,), dt), cuda), dev(O.uniform(rng, (100003,), dt), cuda)
             out = torch.empty((), dtype=tdt, device=cuda)
-            for conj in (0, 1):
+            for conj in ((0, 1) if dt == O.C64 else (0,)):
                 assert L.accblas_mg_dot(comm, stream(), dt, conj, 100003, p(u), p(v), p(out)) == 0
                 assert torch.equal(out, (ab.dotc if conj else ab.dotu)(u, v))
     finally:
