@@ -124,14 +124,18 @@ __device__ __forceinline__ void tile_coords(const DgemmParams &p, int tile, int 
 }
 
 // C = alpha * acc (+ beta * Cin) from the DMMA fragment layout, 16-byte stores where the pitch allows
-template <typename TL>
+// BETA is a TEMPLATE parameter of the data-parallel kernels: with the beta term behind a run-time test in the one
+// epilogue, ptxas gave the small tiles (56-register cap at 7 CTAs / SM) a K loop that recomputes its shared-memory
+// addresses every K-block -- 141 instead of 82 instructions per 16 DMMAs in the 32 x 32 tile, 11 % on every strip of the
+// host wavefront and on 1024^3 (round 2, profiles/r02_strip_ab.jsonl).
+template <typename TL, bool BETA = true>
 __device__ __forceinline__ void dgemm_epilogue(const DgemmParams &p, const double (&acc)[TL::MI][TL::NJ][2],
                                                int m0, int n0, int wm, int wn, int g, int t)
 {
     constexpr int MI = TL::MI, NJ = TL::NJ;
     const bool vec = ((p.n | p.ldc) & 1) == 0;
     const double alpha = p.alpha.get();
-    const bool acc_in = p.beta.on();
+    const bool acc_in = BETA && p.beta.on();
 #pragma unroll
     for (int i = 0; i < MI; ++i) {
         const int64_t r = m0 + wm * MI * 8 + i * 8 + g;
@@ -156,7 +160,7 @@ __device__ __forceinline__ void dgemm_epilogue(const DgemmParams &p, const doubl
 }
 
 // AK: op(A) is K-major in memory (opA == N).  BKM: op(B) is K-major in memory (opB == T).
-template <bool AK, bool BKM, typename TL, int REL>
+template <bool AK, bool BKM, typename TL, int REL, bool BETA>
 __global__ void __launch_bounds__(TL::THREADS, TL::MIN_CTAS)
 dgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
                   const DgemmParams p)
@@ -265,7 +269,7 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
     }
 
     // ---- epilogue: C = alpha * acc (+ beta * Cin); C itself is never read unless it is Cin ----
-    dgemm_epilogue<TL>(p, acc, m0, n0, wm, wn, g, t);
+    dgemm_epilogue<TL, BETA>(p, acc, m0, n0, wm, wn, g, t);
 }
 
 
@@ -548,7 +552,7 @@ struct ZgemmParams {
     int tiles_m, tiles_n;
 };
 
-template <bool AK, bool BKM, bool CONJA, bool CONJB, typename TL, int REL>
+template <bool AK, bool BKM, bool CONJA, bool CONJB, typename TL, int REL, bool BETA>
 __global__ void __launch_bounds__(TL::THREADS, TL::MIN_CTAS)
 zgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
                   const ZgemmParams p)
@@ -678,7 +682,7 @@ zgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
     }
 
     const double2 al = p.alpha.get();
-    const bool acc_in = p.beta.on();
+    const bool acc_in = BETA && p.beta.on();              // BETA is a template parameter: see dgemm_epilogue
 #pragma unroll
     for (int i = 0; i < MI; ++i) {
         const int64_t r = m0 + wm * MI * 8 + i * 8 + g;
@@ -779,7 +783,7 @@ void fill_params(DgemmParams &p, const GemmArgs &g, int BM, int BN)
     p.group = g_tuning[ACCBLAS_TUNE_RASTER_GROUP] > 0 ? g_tuning[ACCBLAS_TUNE_RASTER_GROUP] : 16;
 }
 
-template <bool AK, bool BKM, typename TL, int REL>
+template <bool AK, bool BKM, typename TL, int REL, bool BETA>
 int launch_dgemm_tile(const GemmArgs &g)
 {
     constexpr int BM = TL::BM, BN = TL::BN, SMEM_BYTES = TL::SMEM_BYTES;
@@ -790,13 +794,13 @@ int launch_dgemm_tile(const GemmArgs &g)
         return cuda_fail(cudaErrorInvalidValue, "cuTensorMapEncodeTiled");
     static thread_local AttrOnce attr_once;
     if (attr_once.need()) {
-        ACC_CUDA(cudaFuncSetAttribute(dgemm_dmma_kernel<AK, BKM, TL, REL>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+        ACC_CUDA(cudaFuncSetAttribute(dgemm_dmma_kernel<AK, BKM, TL, REL, BETA>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
     }
     fill_params(p, g, BM, BN);
     p.snake_waves = g_tuning[ACCBLAS_TUNE_SNAKE_K] == 0 ? 0 : sm_count() * TL::MIN_CTAS;
     const int64_t tiles = (int64_t)p.tiles_m * p.tiles_n;
     if (tiles > 0x7fffffff) return ACCBLAS_ERR_SHAPE;
-    dgemm_dmma_kernel<AK, BKM, TL, REL><<<(unsigned)tiles, TL::THREADS, SMEM_BYTES, g.stream>>>(mapA, mapB, p);
+    dgemm_dmma_kernel<AK, BKM, TL, REL, BETA><<<(unsigned)tiles, TL::THREADS, SMEM_BYTES, g.stream>>>(mapA, mapB, p);
     return check_launch("dgemm_dmma_kernel");
 }
 
@@ -875,7 +879,9 @@ int launch_dgemm_streamk(const GemmArgs &g, const StreamKPlan &pl)
 template <bool AK, bool BKM, typename TL>
 int launch_dgemm_tile_rel(const GemmArgs &g, int rel)
 {
-    return rel == REL_DELAYED ? launch_dgemm_tile<AK, BKM, TL, REL_DELAYED>(g) : launch_dgemm_tile<AK, BKM, TL, REL_FENCED>(g);
+    if (has_beta(g))
+        return rel == REL_DELAYED ? launch_dgemm_tile<AK, BKM, TL, REL_DELAYED, true>(g) : launch_dgemm_tile<AK, BKM, TL, REL_FENCED, true>(g);
+    return rel == REL_DELAYED ? launch_dgemm_tile<AK, BKM, TL, REL_DELAYED, false>(g) : launch_dgemm_tile<AK, BKM, TL, REL_FENCED, false>(g);
 }
 
 template <bool AK, bool BKM>
@@ -895,7 +901,7 @@ int launch_dgemm(const GemmArgs &g)
     }
 }
 
-template <bool AK, bool BKM, bool CA, bool CB, typename TL, int REL>
+template <bool AK, bool BKM, bool CA, bool CB, typename TL, int REL, bool BETA>
 int launch_zgemm_tile(const GemmArgs &g)
 {
     constexpr int ZBM = TL::BM, ZBN = TL::BN;
@@ -908,7 +914,7 @@ int launch_zgemm_tile(const GemmArgs &g)
         return cuda_fail(cudaErrorInvalidValue, "cuTensorMapEncodeTiled");
     static thread_local AttrOnce attr_once;
     if (attr_once.need()) {
-        ACC_CUDA(cudaFuncSetAttribute(zgemm_dmma_kernel<AK, BKM, CA, CB, TL, REL>, cudaFuncAttributeMaxDynamicSharedMemorySize, TL::SMEM_BYTES));
+        ACC_CUDA(cudaFuncSetAttribute(zgemm_dmma_kernel<AK, BKM, CA, CB, TL, REL, BETA>, cudaFuncAttributeMaxDynamicSharedMemorySize, TL::SMEM_BYTES));
     }
     ZgemmParams p;
     p.m = g.m; p.n = g.n; p.k = g.k; p.ldc = g.ldc;
@@ -919,7 +925,7 @@ int launch_zgemm_tile(const GemmArgs &g)
     p.tiles_n = (int)((g.n + ZBN - 1) / ZBN);
     const int64_t tiles = (int64_t)p.tiles_m * p.tiles_n;
     if (tiles > 0x7fffffff) return ACCBLAS_ERR_SHAPE;
-    zgemm_dmma_kernel<AK, BKM, CA, CB, TL, REL><<<(unsigned)tiles, TL::THREADS, TL::SMEM_BYTES, g.stream>>>(mapA, mapB, p);
+    zgemm_dmma_kernel<AK, BKM, CA, CB, TL, REL, BETA><<<(unsigned)tiles, TL::THREADS, TL::SMEM_BYTES, g.stream>>>(mapA, mapB, p);
     return check_launch("zgemm_dmma_kernel");
 }
 
@@ -951,11 +957,14 @@ int launch_zgemm(const GemmArgs &g)
 {
     const int tile = pick_ztile(g.m, g.n, g.k);
     // complex kernels: fenced or delayed only (the light release is known to race on the 32 x 32 tile)
-    const bool delayed = g_tuning[ACCBLAS_TUNE_RELEASE] == 2;
+    const bool delayed = g_tuning[ACCBLAS_TUNE_RELEASE] == 2, beta = has_beta(g);
     switch (tile) {
-    case 1:  return delayed ? launch_zgemm_tile<AK, BKM, CA, CB, ZTile64x64, REL_DELAYED>(g) : launch_zgemm_tile<AK, BKM, CA, CB, ZTile64x64, REL_FENCED>(g);
-    case 2:  return delayed ? launch_zgemm_tile<AK, BKM, CA, CB, ZTile32x32, REL_DELAYED>(g) : launch_zgemm_tile<AK, BKM, CA, CB, ZTile32x32, REL_FENCED>(g);
-    default: return delayed ? launch_zgemm_tile<AK, BKM, CA, CB, ZTile128x64, REL_DELAYED>(g) : launch_zgemm_tile<AK, BKM, CA, CB, ZTile128x64, REL_FENCED>(g);
+    case 1:  return delayed ? launch_zgemm_tile<AK, BKM, CA, CB, ZTile64x64, REL_DELAYED, true>(g)
+                     : beta ? launch_zgemm_tile<AK, BKM, CA, CB, ZTile64x64, REL_FENCED, true>(g) : launch_zgemm_tile<AK, BKM, CA, CB, ZTile64x64, REL_FENCED, false>(g);
+    case 2:  return delayed ? launch_zgemm_tile<AK, BKM, CA, CB, ZTile32x32, REL_DELAYED, true>(g)
+                     : beta ? launch_zgemm_tile<AK, BKM, CA, CB, ZTile32x32, REL_FENCED, true>(g) : launch_zgemm_tile<AK, BKM, CA, CB, ZTile32x32, REL_FENCED, false>(g);
+    default: return delayed ? launch_zgemm_tile<AK, BKM, CA, CB, ZTile128x64, REL_DELAYED, true>(g)
+                     : beta ? launch_zgemm_tile<AK, BKM, CA, CB, ZTile128x64, REL_FENCED, true>(g) : launch_zgemm_tile<AK, BKM, CA, CB, ZTile128x64, REL_FENCED, false>(g);
     }
 }
 

@@ -25,6 +25,7 @@
 //     results leave as interleaved float2 stores.  2 MMAs x 3 splits per 16 x 8 x 4 complex tile
 //     product: exactly the 3x of the real case, nothing wasted ("4M" arithmetic).
 #include "common.cuh"
+#include "refit.cuh"
 #include "tma.cuh"
 
 namespace accblas {
@@ -86,6 +87,7 @@ struct SgemmMmaParams {
     BetaC<float2> cbeta;
     float *C;
     int tiles_m, tiles_n;
+    Refit32 refit;             // non-finite sums are recomputed in plain FP32 from the caller's operands (refit.cuh)
 };
 
 __device__ __forceinline__ void raster(int tiles_m, int tiles_n, int &tile_m, int &tile_n)
@@ -229,6 +231,32 @@ sgemm_mma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
         }
     }
 
+    // ---- non-finite sums (Inf / NaN / overflowing inputs cannot go through the split): refit.cuh, warp-uniform ----
+    {
+        bool any = false;
+#pragma unroll
+        for (int i = 0; i < MI; ++i)
+#pragma unroll
+            for (int j = 0; j < NJ; ++j)
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    tot[i][j][e] += acc[i][j][e];
+                    acc[i][j][e] = 0.f;
+                    any |= nonfinite32(tot[i][j][e]);
+                }
+        if (__any_sync(0xffffffffu, any)) {
+#pragma unroll
+            for (int i = 0; i < MI; ++i)
+#pragma unroll
+                for (int j = 0; j < NJ; ++j)
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        const int64_t r = m0 + wm * MI * 16 + i * 16 + (e >> 1) * 8 + g;
+                        const int64_t c = n0 + wn * NJ * 8 + j * 8 + 2 * t + (e & 1);
+                        tot[i][j][e] = refit_real(p.refit, tot[i][j][e], r, c, r < p.m && c < p.n);
+                    }
+        }
+    }
     // ---- epilogue: C = alpha * (tot + acc), never read C ----
     const bool vec = ((p.n | p.ldc) & 1) == 0;
     const float alr = p.alpha.get();
@@ -395,6 +423,33 @@ cgemm_mma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
         }
     }
 
+    // ---- non-finite sums: refit.cuh, warp-uniform ----
+    {
+        bool any = false;
+#pragma unroll
+        for (int i = 0; i < MI; ++i)
+#pragma unroll
+            for (int j = 0; j < NJ; ++j)
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    tre[i][j][e] += are[i][j][e]; are[i][j][e] = 0.f;
+                    tim[i][j][e] += aim[i][j][e]; aim[i][j][e] = 0.f;
+                    any |= nonfinite32(tre[i][j][e]) || nonfinite32(tim[i][j][e]);
+                }
+        if (__any_sync(0xffffffffu, any)) {
+#pragma unroll
+            for (int i = 0; i < MI; ++i)
+#pragma unroll
+                for (int j = 0; j < NJ; ++j)
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        const int64_t r = m0 + wm * MI * 16 + i * 16 + (e >> 1) * 8 + g;
+                        const int64_t c = n0 + wn * NJ * 8 + j * 8 + 2 * t + (e & 1);
+                        const float2 v = refit_cplx(p.refit, make_float2(tre[i][j][e], tim[i][j][e]), r, c, r < p.m && c < p.n);
+                        tre[i][j][e] = v.x; tim[i][j][e] = v.y;
+                    }
+        }
+    }
     float2 *C = reinterpret_cast<float2 *>(p.C);
     const float2 al = p.calpha.get();
 #pragma unroll
@@ -444,6 +499,7 @@ int launch_sgemm_mma(const GemmArgs &g)
     p.alpha = make_alpha<float>(g.alpha, g.alpha_dev); p.calpha = Alpha<float2>{make_float2(0.f, 0.f), nullptr};
     p.beta = make_beta<float>(g); p.cbeta = BetaC<float2>{nullptr, 0, make_float2(0.f, 0.f)};
     p.C = static_cast<float *>(g.C);
+    p.refit = make_refit32(g);
     p.tiles_m = (int)((g.m + BM - 1) / BM);
     p.tiles_n = (int)((g.n + BN - 1) / BN);
     const int64_t tiles = (int64_t)p.tiles_m * p.tiles_n;
@@ -471,6 +527,7 @@ int launch_cgemm_mma(const GemmArgs &g)
     p.calpha = make_alpha<float2>(g.alpha, g.alpha_dev); p.alpha = Alpha<float>{0.f, nullptr};
     p.cbeta = make_beta<float2>(g); p.beta = BetaC<float>{nullptr, 0, 0.f};
     p.C = static_cast<float *>(g.C);
+    p.refit = make_refit32(g);
     p.tiles_m = (int)((g.m + BM - 1) / BM);
     p.tiles_n = (int)((g.n + BN - 1) / BN);
     const int64_t tiles = (int64_t)p.tiles_m * p.tiles_n;

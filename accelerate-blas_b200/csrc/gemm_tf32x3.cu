@@ -23,6 +23,7 @@
 //
 // Workspace (stream-ordered, cudaMallocAsync on the caller's stream): 2 * 4 * (R_A + R_B) * Kp bytes.
 #include "common.cuh"
+#include "refit.cuh"
 #include "tma.cuh"
 #include <cstdlib>
 #include <algorithm>
@@ -211,6 +212,7 @@ struct Combine3Args {
     int64_t m, n, ldt, ldc;
     Alpha<float2> alpha;
     BetaC<float2> beta;
+    Refit32 refit;         // non-finite results are recomputed from the caller's operands (refit.cuh)
 };
 
 // one thread = four consecutive columns: three 16-byte loads, two 16-byte stores (when C allows)
@@ -219,18 +221,34 @@ __global__ void __launch_bounds__(256) combine3_kernel(const Combine3Args a)
     const float2 al = a.alpha.get();
     const int64_t quads = a.ldt / 4, total = a.m * quads;
     const bool vec = (a.ldc & 1) == 0 && (reinterpret_cast<uintptr_t>(a.C) & 15u) == 0;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-        const int64_t r = i / quads, c = (i - r * quads) * 4;
-        if (c >= a.n) continue;
+    // the loop bound is uniform per warp (the refit votes need converged warps): `live` marks the threads with work
+    for (int64_t base = (int64_t)blockIdx.x * blockDim.x; base < total; base += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t i = base + threadIdx.x;
+        const int64_t r = i < total ? i / quads : 0, c = i < total ? (i - r * quads) * 4 : 0;
+        const bool live = i < total && c < a.n;
         const int64_t o = r * a.ldt + c;
-        const float4 t1 = *reinterpret_cast<const float4 *>(a.t[0] + o);
-        const float4 t2 = *reinterpret_cast<const float4 *>(a.t[1] + o);
-        const float4 t3 = *reinterpret_cast<const float4 *>(a.t[2] + o);
+        float4 t1 = make_float4(0.f, 0.f, 0.f, 0.f), t2 = t1, t3 = t1;
+        if (live) {
+            t1 = *reinterpret_cast<const float4 *>(a.t[0] + o);
+            t2 = *reinterpret_cast<const float4 *>(a.t[1] + o);
+            t3 = *reinterpret_cast<const float4 *>(a.t[2] + o);
+        }
         const float x1[4] = {t1.x, t1.y, t1.z, t1.w}, x2[4] = {t2.x, t2.y, t2.z, t2.w}, x3[4] = {t3.x, t3.y, t3.z, t3.w};
         float2 out[4];
+        bool any = false;
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
-            const float xr = x1[e] - x2[e], xi = (x3[e] - x1[e]) - x2[e];
+            out[e] = make_float2(x1[e] - x2[e], (x3[e] - x1[e]) - x2[e]);
+            any |= nonfinite32(out[e].x) || nonfinite32(out[e].y);
+        }
+        if (__any_sync(0xffffffffu, any && live)) {
+#pragma unroll
+            for (int e = 0; e < 4; ++e) out[e] = refit_cplx(a.refit, out[e], r, c + e, live && c + e < a.n);
+        }
+        if (!live) continue;
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            const float xr = out[e].x, xi = out[e].y;
             out[e] = make_float2(al.x * xr - al.y * xi, al.x * xi + al.y * xr);
             if (a.beta.on() && c + e < a.n) out[e] = a.beta.add(out[e], r, c + e);
         }
@@ -325,6 +343,7 @@ struct SgemmParams {
     int tiles_per_plane;
     int plane_rows_a, plane_rows_b;      // row offset of plane p in the A / B maps: p * plane_rows_*
     int64_t plane_stride_c;              // floats between the C planes
+    Refit32 refit;                       // non-finite accumulators are recomputed in plain FP32 (refit.cuh); A == nullptr: off
 };
 
 template <int TBN, int STAGES>
@@ -335,6 +354,74 @@ struct TcCfg {
     static constexpr int BAR_OFF = STAGES * STAGE;
     static constexpr int SMEM = STAGES * STAGE + 1024 + 256;
 };
+
+// ---- C = alpha * acc (+ beta * Cin): one thread owns HALF consecutive columns of one row ----
+// (called by whole warps: the non-finite refit votes)
+template <int HALF>
+__device__ __forceinline__ void tc_store(const SgemmParams &p, float (&acc)[HALF], int64_t row, int64_t col0, int plane)
+{
+    if (p.refit.A) {                                           // non-finite sums: see refit.cuh (warp-uniform)
+        bool any = false;
+#pragma unroll
+        for (int i = 0; i < HALF; ++i) any |= nonfinite32(acc[i]);
+        if (__any_sync(0xffffffffu, any && row < p.M)) {
+            if (p.cplx) {
+#pragma unroll
+                for (int i = 0; i < HALF; i += 2) {
+                    const float2 v = refit_cplx(p.refit, make_float2(acc[i], acc[i + 1]), row, (col0 + i) >> 1,
+                                                row < p.M && col0 + i < p.N);
+                    acc[i] = v.x; acc[i + 1] = v.y;
+                }
+            } else {
+#pragma unroll
+                for (int i = 0; i < HALF; ++i)
+                    acc[i] = refit_real(p.refit, acc[i], row, col0 + i, row < p.M && col0 + i < p.N);
+            }
+        }
+    }
+    const float2 al = p.alpha.dev ? (p.cplx ? *p.alpha.dev : make_float2(*reinterpret_cast<const float *>(p.alpha.dev), 0.f))
+                                  : p.alpha.v;
+    if (row < p.M) {
+        float *crow = p.C + plane * p.plane_stride_c + row * p.ldc;
+        const bool vec4 = (p.ldc & 3) == 0 && ((reinterpret_cast<uintptr_t>(p.C) & 15u) == 0) && col0 + HALF <= p.N;
+        if (p.cplx) {
+#pragma unroll
+            for (int i = 0; i < HALF; i += 2) {
+                const float xr = acc[i], xi = acc[i + 1];
+                acc[i] = al.x * xr - al.y * xi;
+                acc[i + 1] = al.x * xi + al.y * xr;
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < HALF; ++i) acc[i] *= al.x;
+        }
+        if (p.beta.on()) {                                     // + beta * Cin (accblas_gemm_ex): one row of Cin per thread
+            const float *cin = p.beta.cin + row * p.beta.ld + col0;
+            if (p.cplx) {
+#pragma unroll
+                for (int i = 0; i < HALF; i += 2)
+                    if (col0 + i < p.N) {                      // N is even for complex: a started pair is whole
+                        const float cr = cin[i], ci = cin[i + 1];
+                        acc[i] += p.cbeta.x * cr - p.cbeta.y * ci;
+                        acc[i + 1] += p.cbeta.x * ci + p.cbeta.y * cr;
+                    }
+            } else {
+#pragma unroll
+                for (int i = 0; i < HALF; ++i)
+                    if (col0 + i < p.N) acc[i] = fmaf(p.beta.beta, cin[i], acc[i]);
+            }
+        }
+        if (vec4) {
+#pragma unroll
+            for (int i = 0; i < HALF; i += 4)
+                *reinterpret_cast<float4 *>(crow + col0 + i) = make_float4(acc[i], acc[i + 1], acc[i + 2], acc[i + 3]);
+        } else {
+#pragma unroll
+            for (int i = 0; i < HALF; ++i)
+                if (col0 + i < p.N) crow[col0 + i] = acc[i];
+        }
+    }
+}
 
 template <int TBN, int STAGES, int KCB>
 __global__ void __launch_bounds__(TTHREADS, 1)
@@ -485,57 +572,245 @@ sgemm_tf32x3_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_con
             __syncwarp();
             if (lane == 0) tma::mbar_arrive(bar_acce + 8 * b);
         }
-        // ---- C = alpha * acc ----
-        const int64_t row = m0 + q * 32 + lane;
-        const float2 al = p.alpha.dev ? (p.cplx ? *p.alpha.dev : make_float2(*reinterpret_cast<const float *>(p.alpha.dev), 0.f))
-                                      : p.alpha.v;
-        if (row < p.M) {
-            float *crow = p.C + plane * p.plane_stride_c + row * p.ldc;
-            const int64_t col0 = n0 + h * HALF;
-            const bool vec4 = (p.ldc & 3) == 0 && ((reinterpret_cast<uintptr_t>(p.C) & 15u) == 0) && col0 + HALF <= p.N;
-            if (p.cplx) {
-#pragma unroll
-                for (int i = 0; i < HALF; i += 2) {
-                    const float xr = acc[i], xi = acc[i + 1];
-                    acc[i] = al.x * xr - al.y * xi;
-                    acc[i + 1] = al.x * xi + al.y * xr;
-                }
-            } else {
-#pragma unroll
-                for (int i = 0; i < HALF; ++i) acc[i] *= al.x;
-            }
-            if (p.beta.on()) {                                     // + beta * Cin (accblas_gemm_ex): one row of Cin per thread
-                const float *cin = p.beta.cin + row * p.beta.ld + col0;
-                if (p.cplx) {
-#pragma unroll
-                    for (int i = 0; i < HALF; i += 2)
-                        if (col0 + i < p.N) {                      // N is even for complex: a started pair is whole
-                            const float cr = cin[i], ci = cin[i + 1];
-                            acc[i] += p.cbeta.x * cr - p.cbeta.y * ci;
-                            acc[i + 1] += p.cbeta.x * ci + p.cbeta.y * cr;
-                        }
-                } else {
-#pragma unroll
-                    for (int i = 0; i < HALF; ++i)
-                        if (col0 + i < p.N) acc[i] = fmaf(p.beta.beta, cin[i], acc[i]);
-                }
-            }
-            if (vec4) {
-#pragma unroll
-                for (int i = 0; i < HALF; i += 4)
-                    *reinterpret_cast<float4 *>(crow + col0 + i) = make_float4(acc[i], acc[i + 1], acc[i + 2], acc[i + 3]);
-            } else {
-#pragma unroll
-                for (int i = 0; i < HALF; ++i)
-                    if (col0 + i < p.N) crow[col0 + i] = acc[i];
-            }
-        }
+        tc_store<HALF>(p, acc, m0 + q * 32 + lane, n0 + h * HALF, plane);
     }
     tc_fence_before();
     __syncthreads();
     if (warp == 2) {
         tc_fence_after();
         tmem_dealloc(tmem_base, 2 * TBN);
+    }
+}
+
+// ------------------------------------------------------------------------------------
+// sgemm_tf32x3_pair_kernel: the same product on CTA PAIRS (tcgen05.mma.cta_group::2, UMMA M = 256).
+//
+// Why: per K-block the one-CTA 128 x 256 tile moves (128 + 256) x 32 floats x {hi, lo} = 96 KiB through the SM's
+// shared memory once as TMA writes and 1.5 times as tensor-core operand reads (three MMAs per K-step) -- 240 KiB per
+// 1536 tensor clocks = 156 B/clk against the 128 B/clk the SM's shared memory delivers: the pipe cannot be more than
+// ~82 % busy (measured round 1: 80 %).  A pair of CTAs on the two SMs of a TPC computes a 256 x 256 tile: each CTA
+// stages its own 128 rows of A and only HALF of B (128 of the 256 columns), the hardware feeds both tensor cores
+// with both halves, so per CTA a K-block is 64 KiB of TMA writes + 96 KiB of operand reads = 104 B/clk, and the
+// L2 -> SM traffic per flop drops by a third as well.  Three stages of 64 KiB replace two of 96 KiB.
+//
+// Protocol (rank = %cluster_ctarank; rank 0 = leader):
+//   full[s]   lives in the LEADER: one arrive.expect_tx by the leader's producer for the bytes of BOTH CTAs; each CTA's
+//             producer issues its own TMA loads (.cta_group::2) that complete_tx on the leader's barrier;
+//   empty[s]  one per CTA, released by the leader's tcgen05.commit multicast to both CTAs;
+//   acc_full  one per CTA (commit multicast); acc_empty in the leader, 2 x 8 epilogue-warp arrivals (the peer's are
+//             remote arrives with cluster-scope release);
+//   TMEM      allocated / freed by warp 2 of BOTH CTAs (cta_group::2), cluster barrier before and after.
+// The promotion scheme (two accumulators, chunks of KCB K-blocks drained into FP32 registers) is unchanged.
+// ------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t map_to_rank(uint32_t saddr, uint32_t rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(saddr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void mbar_arrive_remote(uint32_t cluster_addr) {
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+__device__ __forceinline__ void tmem_alloc2(uint32_t slot_smem, uint32_t ncols) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(slot_smem), "r"(ncols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc2(uint32_t taddr, uint32_t ncols) {
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void umma_tf32_pair(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+// arrive on the barrier at this shared-memory offset in BOTH CTAs of the pair once all MMAs issued so far retire
+__device__ __forceinline__ void umma_commit_pair(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(bar), "h"((uint16_t)3) : "memory");
+}
+// 2-D tiled load into THIS CTA's shared memory, completing on a barrier of the pair's leader
+__device__ __forceinline__ void tma_load_2d_pair(uint32_t dst, const void *tmap, uint32_t leader_bar, int c0, int c1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(dst), "l"(tmap), "r"(leader_bar), "r"(c0), "r"(c1) : "memory");
+}
+
+constexpr int PBN = 256;                     // pair tile: 256 x 256, each CTA 128 rows x 256 columns of C
+template <int STAGES>
+struct PairCfg {
+    static constexpr int A_TILE = TBM * TBK * 4;               // 16 KiB: this CTA's 128 rows of A
+    static constexpr int B_TILE = (PBN / 2) * TBK * 4;         // 16 KiB: this CTA's half of the 256 columns of B
+    static constexpr int STAGE = 2 * A_TILE + 2 * B_TILE;      // 64 KiB
+    static constexpr int BAR_OFF = STAGES * STAGE;
+    static constexpr int SMEM = STAGES * STAGE + 1024 + 256;
+};
+
+template <int STAGES, int KCB>
+__global__ void __launch_bounds__(TTHREADS, 1)
+sgemm_tf32x3_pair_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_constant__ CUtensorMap mapAlo,
+                         const __grid_constant__ CUtensorMap mapBhi, const __grid_constant__ CUtensorMap mapBlo,
+                         const SgemmParams p)
+{
+    using Cfg = PairCfg<STAGES>;
+    constexpr int HALF = PBN / 2;                                  // columns per epilogue warp
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t smem_base = (tma::smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t bar_full = smem_base + Cfg::BAR_OFF;            // full[STAGES]   (used in the leader only)
+    const uint32_t bar_empty = bar_full + 8 * STAGES;              // empty[STAGES]  (one set per CTA)
+    const uint32_t bar_accf = bar_empty + 8 * STAGES;              // acc_full[2]    (one set per CTA)
+    const uint32_t bar_acce = bar_accf + 16;                       // acc_empty[2]   (used in the leader only)
+    const uint32_t tmem_slot = bar_acce + 16;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();
+    const bool leader = rank == 0;
+
+    constexpr int GROUP = 8;
+    int tile_m, tile_n, plane = 0;
+    {
+        int bid = blockIdx.x >> 1;                                 // pair index (cluster = 2 consecutive CTAs)
+        if (p.tiles_per_plane > 0) {
+            plane = bid / p.tiles_per_plane;
+            bid -= plane * p.tiles_per_plane;
+        }
+        const int per_group = GROUP * p.tiles_n;
+        const int grp = bid / per_group;
+        const int first_m = grp * GROUP;
+        const int gsz = min(p.tiles_m - first_m, GROUP);
+        const int in_grp = bid - grp * per_group;
+        tile_m = first_m + in_grp % gsz;
+        tile_n = in_grp / gsz;
+    }
+    const int m0 = tile_m * (2 * TBM) + (int)rank * TBM, n0 = tile_n * PBN;
+    const int ma = m0 + plane * p.plane_rows_a;                    // this CTA's 128 rows of A in the stacked map
+    const int nb = n0 + (int)rank * (PBN / 2) + plane * p.plane_rows_b;   // this CTA's half of the B rows
+    const int kblocks = (int)((p.Kp + TBK - 1) / TBK);
+    const int chunks = (kblocks + KCB - 1) / KCB;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < STAGES; ++s) {
+            tma::mbar_init(bar_full + 8 * s, 1);
+            tma::mbar_init(bar_empty + 8 * s, 1);
+        }
+        for (int b = 0; b < 2; ++b) {
+            tma::mbar_init(bar_accf + 8 * b, 1);
+            tma::mbar_init(bar_acce + 8 * b, 2 * EPI_WARPS);
+        }
+        tma::fence_barrier_init();
+    }
+    if (warp == 2) tmem_alloc2(tmem_slot, 2 * PBN);                // both CTAs, same warp: two accumulators of 256 columns
+    tc_fence_before();
+    cluster_sync_all();                                            // the peer's barriers exist before anything signals them
+    tc_fence_after();
+    uint32_t tmem_base;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+
+    if (warp < 4) {
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+        if (warp == 0 && lane == 0) {
+            // ================================ TMA producer (both CTAs) ================================
+            tma::prefetch_tmap(&mapAhi); tma::prefetch_tmap(&mapAlo);
+            tma::prefetch_tmap(&mapBhi); tma::prefetch_tmap(&mapBlo);
+            const uint32_t leader_full = map_to_rank(bar_full, 0);
+            for (int kb = 0; kb < kblocks; ++kb) {
+                const int s = kb % STAGES;
+                if (kb >= STAGES) tma::mbar_wait(bar_empty + 8 * s, ((kb / STAGES) - 1) & 1);
+                if (leader) tma::mbar_expect_tx(bar_full + 8 * s, 2 * Cfg::STAGE);     // both CTAs' bytes
+                const uint32_t full = leader_full + 8 * s;
+                const uint32_t st = smem_base + s * Cfg::STAGE;
+                const int k0 = kb * TBK;
+                tma_load_2d_pair(st, &mapAhi, full, k0, ma);
+                tma_load_2d_pair(st + Cfg::A_TILE, &mapAlo, full, k0, ma);
+                tma_load_2d_pair(st + 2 * Cfg::A_TILE, &mapBhi, full, k0, nb);
+                tma_load_2d_pair(st + 2 * Cfg::A_TILE + Cfg::B_TILE, &mapBlo, full, k0, nb);
+            }
+        } else if (warp == 1 && leader) {
+            // ================================ MMA issuer (leader only) ================================
+            constexpr uint32_t idesc = idesc_tf32(2 * TBM, PBN);
+            int kb = 0;
+            for (int c = 0; c < chunks; ++c) {
+                const int b = c & 1;
+                if (c >= 2) {                                       // accumulator b drained by BOTH CTAs' epilogues?
+                    tma::mbar_wait(bar_acce + 8 * b, ((c >> 1) - 1) & 1);
+                    tc_fence_after();
+                }
+                const uint32_t tacc = tmem_base + (uint32_t)(b * PBN);
+                const int kend = min(kb + KCB, kblocks);
+                for (int first = 1; kb < kend; ++kb) {
+                    const int s = kb % STAGES;
+                    tma::mbar_wait(bar_full + 8 * s, (kb / STAGES) & 1);
+                    tc_fence_after();
+                    if (lane == 0) {
+                        const uint32_t st = smem_base + s * Cfg::STAGE;
+                        const uint64_t ahi = smem_desc_sw128(st), alo = smem_desc_sw128(st + Cfg::A_TILE);
+                        const uint64_t bhi = smem_desc_sw128(st + 2 * Cfg::A_TILE);
+                        const uint64_t blo = smem_desc_sw128(st + 2 * Cfg::A_TILE + Cfg::B_TILE);
+#pragma unroll
+                        for (int k = 0; k < TBK / 8; ++k) {
+                            const uint64_t adv = (uint64_t)(2 * k);
+                            umma_tf32_pair(tacc, alo + adv, bhi + adv, idesc, (first && k == 0) ? 0u : 1u);
+                            umma_tf32_pair(tacc, ahi + adv, blo + adv, idesc, 1);
+                            umma_tf32_pair(tacc, ahi + adv, bhi + adv, idesc, 1);
+                        }
+                        umma_commit_pair(bar_empty + 8 * s);       // the stage is reusable in both CTAs once these retire
+                    }
+                    first = 0;
+                    __syncwarp();
+                }
+                if (lane == 0) umma_commit_pair(bar_accf + 8 * b); // chunk accumulator complete (both CTAs' epilogues)
+                __syncwarp();
+            }
+        }
+    } else {
+        // ================================ promotion + epilogue (both CTAs) ================================
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
+        const int e = warp - 4;
+        const int q = e & 3;                                       // TMEM lane quadrant (warp id % 4)
+        const int h = e >> 2;                                      // column half
+        const uint32_t leader_acce = map_to_rank(bar_acce, 0);
+        float acc[HALF];
+#pragma unroll
+        for (int i = 0; i < HALF; ++i) acc[i] = 0.f;
+        for (int c = 0; c < chunks; ++c) {
+            const int b = c & 1;
+            tma::mbar_wait(bar_accf + 8 * b, (c >> 1) & 1);
+            tc_fence_after();
+            const uint32_t t0 = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(b * PBN + h * HALF);
+#pragma unroll
+            for (int c0 = 0; c0 < HALF; c0 += 64) {
+                uint32_t v0[32], v1[32];
+                tmem_ld32(t0 + c0, v0);
+                tmem_ld32(t0 + c0 + 32, v1);
+                tmem_ld_wait();
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                    acc[c0 + i] += __uint_as_float(v0[i]);
+                    acc[c0 + 32 + i] += __uint_as_float(v1[i]);
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) {
+                if (leader) tma::mbar_arrive(bar_acce + 8 * b);
+                else mbar_arrive_remote(leader_acce + 8 * b);
+            }
+        }
+        tc_store<HALF>(p, acc, (int64_t)m0 + q * 32 + lane, (int64_t)n0 + h * HALF, plane);
+    }
+    tc_fence_before();
+    cluster_sync_all();                                            // the leader's MMAs have read the peer's shared memory
+    if (warp == 2) {
+        tc_fence_after();
+        tmem_dealloc2(tmem_base, 2 * PBN);
     }
 }
 
@@ -574,6 +849,7 @@ int pick_tc_tile(const TcPlan &t, int planes = 1)
 {
     const int forced = g_tuning[ACCBLAS_TUNE_TC_TILE];
     if (forced >= 0 && forced <= 2) return forced;
+    if (forced == 3) return t.M > TBM ? 3 : 0;                     // the pair tile needs two row blocks
     static const int tbn[3] = {256, 128, 64};
     static const double step_cost[3] = {134.0, 87.0, 68.0};
     const int sms = sm_count();
@@ -586,7 +862,38 @@ int pick_tc_tile(const TcPlan &t, int planes = 1)
         const double cost = (double)((tiles + sms - 1) / sms) * (step_cost[c] * (double)(t.pitch / 8) + 40.0 * 134.0);
         if (c == 0 || cost < best_cost * 0.97) { best = c; best_cost = cost; }
     }
+    // 3 = the 256 x 256 CTA-pair tile (cta_group::2): whenever the wide tile wins and pairing the row blocks does not
+    // add a round (an odd count of 128-row blocks wastes half a pair in the last tile row)
+    if (best == 0 && t.M > TBM) {
+        const int64_t tn = (t.N + PBN - 1) / PBN;
+        const int64_t rounds1 = (tm * tn * planes + sms - 1) / sms;
+        const int64_t pairs = std::max(1, sms / 2), rounds2 = (((tm + 1) / 2) * tn * planes + pairs - 1) / pairs;
+        if (rounds2 <= rounds1) best = 3;
+    }
     return best;
+}
+
+// the part of SgemmParams that does not depend on the tile shape
+void fill_tc_params(SgemmParams &p, const GemmArgs &g, const TcPlan &t, int planes, int plane_rows_a, int plane_rows_b,
+                    int64_t plane_stride_c)
+{
+    p.M = t.M; p.N = t.N; p.Kp = t.pitch;      // padding columns are zero-filled by pack_split
+    p.ldc = (g.dtype == ACCBLAS_C32 ? 2 : 1) * g.ldc;
+    p.C = static_cast<float *>(g.C);
+    p.cplx = g.dtype == ACCBLAS_C32;
+    if (g.alpha_dev) p.alpha = Alpha<float2>{make_float2(0.f, 0.f), static_cast<const float2 *>(g.alpha)};
+    else p.alpha = Alpha<float2>{make_float2(static_cast<const float *>(g.alpha)[0],
+                                            p.cplx ? static_cast<const float *>(g.alpha)[1] : 0.f), nullptr};
+    p.beta = BetaC<float>{nullptr, 0, 0.f};
+    p.cbeta = make_float2(0.f, 0.f);
+    if (planes == 1 && has_beta(g)) {                              // (the 3M planes take beta in combine3)
+        p.beta.cin = static_cast<const float *>(g.Cin);
+        p.beta.ld = (p.cplx ? 2 : 1) * (g.ldcin ? g.ldcin : g.ldc);
+        p.beta.beta = static_cast<const float *>(g.beta)[0];
+        if (p.cplx) p.cbeta = make_float2(static_cast<const float *>(g.beta)[0], static_cast<const float *>(g.beta)[1]);
+    }
+    p.plane_rows_a = plane_rows_a; p.plane_rows_b = plane_rows_b; p.plane_stride_c = plane_stride_c;
+    p.refit = planes == 1 ? make_refit32(g) : no_refit32();      // the 3M planes are intermediates: combine3 refits
 }
 
 template <int TBN, int STAGES, int KCB>
@@ -610,29 +917,57 @@ int launch_tc(const GemmArgs &g, const TcPlan &t, float *ahi, float *alo, float 
         ACC_CUDA(cudaFuncSetAttribute(sgemm_tf32x3_kernel<TBN, STAGES, KCB>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM));
     }
     SgemmParams p;
-    p.M = t.M; p.N = t.N; p.Kp = t.pitch;      // padding columns are zero-filled by pack_split
-    p.ldc = (g.dtype == ACCBLAS_C32 ? 2 : 1) * g.ldc;
-    p.C = static_cast<float *>(g.C);
-    p.cplx = g.dtype == ACCBLAS_C32;
-    if (g.alpha_dev) p.alpha = Alpha<float2>{make_float2(0.f, 0.f), static_cast<const float2 *>(g.alpha)};
-    else p.alpha = Alpha<float2>{make_float2(static_cast<const float *>(g.alpha)[0],
-                                            p.cplx ? static_cast<const float *>(g.alpha)[1] : 0.f), nullptr};
-    p.beta = BetaC<float>{nullptr, 0, 0.f};
-    p.cbeta = make_float2(0.f, 0.f);
-    if (planes == 1 && has_beta(g)) {                              // (the 3M planes take beta in combine3)
-        p.beta.cin = static_cast<const float *>(g.Cin);
-        p.beta.ld = (p.cplx ? 2 : 1) * (g.ldcin ? g.ldcin : g.ldc);
-        p.beta.beta = static_cast<const float *>(g.beta)[0];
-        if (p.cplx) p.cbeta = make_float2(static_cast<const float *>(g.beta)[0], static_cast<const float *>(g.beta)[1]);
-    }
+    fill_tc_params(p, g, t, planes, plane_rows_a, plane_rows_b, plane_stride_c);
     p.tiles_m = (int)((t.M + TBM - 1) / TBM);
     p.tiles_n = (int)((t.N + TBN - 1) / TBN);
     const int64_t tiles = (int64_t)p.tiles_m * p.tiles_n * planes;
     if (tiles > 0x7fffffff) return ACCBLAS_ERR_SHAPE;
     p.tiles_per_plane = planes > 1 ? p.tiles_m * p.tiles_n : 0;
-    p.plane_rows_a = plane_rows_a; p.plane_rows_b = plane_rows_b; p.plane_stride_c = plane_stride_c;
     sgemm_tf32x3_kernel<TBN, STAGES, KCB><<<(unsigned)tiles, TTHREADS, Cfg::SMEM, g.stream>>>(mAhi, mAlo, mBhi, mBlo, p);
     return check_launch("sgemm_tf32x3_kernel");
+}
+
+// pair kernel (cta_group::2): pair tiles of 256 x 256, grid = 2 CTAs per tile launched as clusters of 2
+template <int STAGES, int KCB>
+int launch_tc_pair(const GemmArgs &g, const TcPlan &t, float *ahi, float *alo, float *bhi, float *blo,
+                   int planes = 1, int plane_rows_a = 0, int plane_rows_b = 0, int64_t plane_stride_c = 0)
+{
+    using Cfg = PairCfg<STAGES>;
+    CUtensorMap mAhi, mAlo, mBhi, mBlo;
+    const uint64_t pitch_b = (uint64_t)t.pitch * 4;
+    const CUtensorMapDataType F = CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
+    const uint64_t rows_a = planes > 1 ? (uint64_t)planes * (uint64_t)plane_rows_a : (uint64_t)t.RA;
+    const uint64_t rows_b = planes > 1 ? (uint64_t)planes * (uint64_t)plane_rows_b : (uint64_t)t.RB;
+    // every box is 128 rows: a CTA's rows of A, a CTA's HALF of the tile's B rows
+    if (!tma::make_2d(&mAhi, F, 4, ahi, rows_a, (uint64_t)t.pitch, TBM, TBK, pitch_b) ||
+        !tma::make_2d(&mAlo, F, 4, alo, rows_a, (uint64_t)t.pitch, TBM, TBK, pitch_b) ||
+        !tma::make_2d(&mBhi, F, 4, bhi, rows_b, (uint64_t)t.pitch, PBN / 2, TBK, pitch_b) ||
+        !tma::make_2d(&mBlo, F, 4, blo, rows_b, (uint64_t)t.pitch, PBN / 2, TBK, pitch_b))
+        return cuda_fail(cudaErrorInvalidValue, "cuTensorMapEncodeTiled");
+    static thread_local AttrOnce attr_once;
+    if (attr_once.need()) {
+        ACC_CUDA(cudaFuncSetAttribute(sgemm_tf32x3_pair_kernel<STAGES, KCB>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM));
+    }
+    SgemmParams p;
+    fill_tc_params(p, g, t, planes, plane_rows_a, plane_rows_b, plane_stride_c);
+    p.tiles_m = (int)((t.M + 2 * TBM - 1) / (2 * TBM));
+    p.tiles_n = (int)((t.N + PBN - 1) / PBN);
+    const int64_t tiles = (int64_t)p.tiles_m * p.tiles_n * planes;
+    if (2 * tiles > 0x7fffffff) return ACCBLAS_ERR_SHAPE;
+    p.tiles_per_plane = planes > 1 ? p.tiles_m * p.tiles_n : 0;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)(2 * tiles));
+    cfg.blockDim = dim3(TTHREADS);
+    cfg.dynamicSmemBytes = Cfg::SMEM;
+    cfg.stream = g.stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, sgemm_tf32x3_pair_kernel<STAGES, KCB>, mAhi, mAlo, mBhi, mBlo, p);
+    if (e != cudaSuccess) return cuda_fail(e, "sgemm_tf32x3_pair_kernel launch");
+    return check_launch("sgemm_tf32x3_pair_kernel");
 }
 
 // ---- 3M for c32 (see pack_split3_kernel) ----
@@ -703,7 +1038,8 @@ int cgemm_3m_run(const GemmArgs &g)
         h.C = wt; h.ldc = q.ldt;
         const int ra = (int)q.rows_a, rb = (int)q.rows_b;
         const int64_t sc = (int64_t)(pt / 4);
-        s = tile == 1 ? launch_tc<128, 3, 2>(h, q.t, a.hi[0], a.lo[0], b.hi[0], b.lo[0], 3, ra, rb, sc)
+        s = tile == 3 ? launch_tc_pair<3, 2>(h, q.t, a.hi[0], a.lo[0], b.hi[0], b.lo[0], 3, ra, rb, sc)
+          : tile == 1 ? launch_tc<128, 3, 2>(h, q.t, a.hi[0], a.lo[0], b.hi[0], b.lo[0], 3, ra, rb, sc)
           : tile == 2 ? launch_tc<64, 4, 2>(h, q.t, a.hi[0], a.lo[0], b.hi[0], b.lo[0], 3, ra, rb, sc)
                       : launch_tc<256, 2, 2>(h, q.t, a.hi[0], a.lo[0], b.hi[0], b.lo[0], 3, ra, rb, sc);
     }
@@ -714,6 +1050,7 @@ int cgemm_3m_run(const GemmArgs &g)
         c.m = g.m; c.n = g.n; c.ldt = q.ldt; c.ldc = g.ldc;
         c.alpha = make_alpha<float2>(g.alpha, g.alpha_dev);
         c.beta = make_beta<float2>(g);
+        c.refit = make_refit32(g);
         const int64_t total = c.m * (c.ldt / 4);
         const int64_t want = (total + 255) / 256, cap = (int64_t)sm_count() * 32;
         combine3_kernel<<<(unsigned)std::max<int64_t>(1, std::min(want, cap)), 256, 0, g.stream>>>(c);
@@ -768,7 +1105,8 @@ int sgemm_tc(const GemmArgs &g)
     if (s == ACCBLAS_OK) {
         static const int kcb = [] { const char *e = getenv("ACCBLAS_TC_KCB"); return e ? atoi(e) : 2; }();
         const int tile = pick_tc_tile(t);
-        s = tile == 1 ? launch_tc<128, 3, 2>(g, t, ahi, alo, bhi, blo)
+        s = tile == 3 ? (kcb == 4 ? launch_tc_pair<3, 4>(g, t, ahi, alo, bhi, blo) : launch_tc_pair<3, 2>(g, t, ahi, alo, bhi, blo))
+          : tile == 1 ? launch_tc<128, 3, 2>(g, t, ahi, alo, bhi, blo)
           : tile == 2 ? launch_tc<64, 4, 2>(g, t, ahi, alo, bhi, blo)
           : kcb == 1 ? launch_tc<256, 2, 1>(g, t, ahi, alo, bhi, blo)
           : kcb == 4 ? launch_tc<256, 2, 4>(g, t, ahi, alo, bhi, blo)

@@ -20,6 +20,9 @@
 // the 16-byte alignment the TMA kernels want.
 #include "common.cuh"
 #include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <string>
 #include <vector>
 
 namespace accblas {
@@ -56,6 +59,34 @@ struct Streams {
             events.push_back(e);
         }
         return events[used++];
+    }
+};
+
+// ACCBLAS_HOST_TRACE=1: timed events at every stage boundary of the wavefront, printed (ms since the call's start) to
+// stderr when the call ends -- a debugging aid for the pipeline's schedule, never on by default.
+struct Trace {
+    bool on;
+    cudaEvent_t t0 = nullptr;
+    std::vector<std::pair<std::string, cudaEvent_t>> marks;
+    Trace() : on([] { const char *e = getenv("ACCBLAS_HOST_TRACE"); return e && *e == '1'; }()) {}
+    void start(cudaStream_t s) { if (on) { cudaEventCreate(&t0); cudaEventRecord(t0, s); } }
+    void mark(const char *what, int t, cudaStream_t s) {
+        if (!on) return;
+        cudaEvent_t e = nullptr;
+        cudaEventCreate(&e);
+        cudaEventRecord(e, s);
+        marks.emplace_back(std::string(what) + std::to_string(t), e);
+    }
+    void dump() {
+        if (!on) return;
+        for (auto &m : marks) {
+            float ms = 0.f;
+            cudaEventElapsedTime(&ms, t0, m.second);
+            fprintf(stderr, "%s=%.3f ", m.first.c_str(), ms);
+            cudaEventDestroy(m.second);
+        }
+        fprintf(stderr, "\n");
+        cudaEventDestroy(t0);
     }
 };
 
@@ -126,6 +157,8 @@ int gemm_host_pipeline(const GemmArgs &g0, const void *A_host, const void *B_hos
     ACC_CUDA(st.create());
     Streams &evs = st;
     cudaEvent_t ev_start = evs.make();
+    Trace trace;
+    trace.start(s);
     ACC_CUDA(cudaEventRecord(ev_start, s));      // the allocations are ordered on s
     for (cudaStream_t x : {st.up, st.down, st.row, st.col}) ACC_CUDA(cudaStreamWaitEvent(x, ev_start, 0));
 
@@ -157,12 +190,14 @@ int gemm_host_pipeline(const GemmArgs &g0, const void *A_host, const void *B_hos
                   : copy_window(dA.p, A_host, es, g.colsA, 0, r0, g.rowsA, h, cudaMemcpyHostToDevice, st.up));
             ev_a = evs.make();
             ck(cudaEventRecord(ev_a, st.up));
+            trace.mark("upA", t, st.up);
         }
         if (w > 0) {                              // column panel t of op(B)
             ck(bn ? copy_window(dB.p, B_host, es, g.colsB, 0, c0, g.rowsB, w, cudaMemcpyHostToDevice, st.up)
                   : copy_window(dB.p, B_host, es, g.colsB, c0, 0, w, g.colsB, cudaMemcpyHostToDevice, st.up));
             ev_b = evs.make();
             ck(cudaEventRecord(ev_b, st.up));
+            trace.mark("upB", t, st.up);
         }
         // row strip C[t, 0 .. min(t,Q)-1]: needs A_t (B_0..B_{t-1} precede it on the upload stream)
         const int64_t wn = std::min<int64_t>((int64_t)std::min(t, Q) * pn, g.n);
@@ -171,6 +206,7 @@ int gemm_host_pipeline(const GemmArgs &g0, const void *A_host, const void *B_hos
             status = product(r0, h, 0, wn, st.row);
             cudaEvent_t done = evs.make();
             ck(cudaEventRecord(done, st.row));
+            trace.mark("row", t, st.row);
             ck(cudaStreamWaitEvent(st.down, done, 0));
             ck(copy_window(C_host, dC.p, es, g.n, r0, 0, h, wn, cudaMemcpyDeviceToHost, st.down));
         }
@@ -181,10 +217,12 @@ int gemm_host_pipeline(const GemmArgs &g0, const void *A_host, const void *B_hos
             status = product(0, hm, c0, w, st.col);
             cudaEvent_t done = evs.make();
             ck(cudaEventRecord(done, st.col));
+            trace.mark("col", t, st.col);
             ck(cudaStreamWaitEvent(st.down, done, 0));
             ck(copy_window(C_host, dC.p, es, g.n, 0, c0, hm, w, cudaMemcpyDeviceToHost, st.down));
         }
     }
+    trace.mark("down", steps, st.down);
     // join everything back into the caller's stream (the scratch is freed on it), then wait
     for (cudaStream_t x : {st.up, st.row, st.col, st.down}) {
         cudaEvent_t e = evs.make();
@@ -193,6 +231,7 @@ int gemm_host_pipeline(const GemmArgs &g0, const void *A_host, const void *B_hos
     }
     ck(cudaStreamSynchronize(s));
     for (cudaStream_t x : {st.up, st.row, st.col, st.down}) cudaStreamSynchronize(x);
+    trace.dump();
     if (status != ACCBLAS_OK) return status;
     if (ce != cudaSuccess) return cuda_fail(ce, "accblas_gemm_host pipeline");
     return ACCBLAS_OK;

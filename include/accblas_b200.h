@@ -334,7 +334,7 @@ typedef enum {
     ACCBLAS_TUNE_RASTER_GROUP = 5,  /* f64 gemm: tile rows per rasterisation group (default 16)              */
     ACCBLAS_TUNE_HOST_PANELS = 6,   /* accblas_gemm_host: maximum panels per dimension of the wavefront     */
     ACCBLAS_TUNE_ZGEMM_3M = 7,      /* c64 gemm: 0 = always 4M in registers, 1 = 3M (three real products) whenever possible */
-    ACCBLAS_TUNE_TC_TILE = 8,       /* tcgen05 f32/c32 gemm CTA tile: 0 = 128x256, 1 = 128x128, 2 = 128x64                  */
+    ACCBLAS_TUNE_TC_TILE = 8,       /* tcgen05 f32/c32 gemm tile: 0 = 128x256, 1 = 128x128, 2 = 128x64, 3 = 256x256 on a CTA pair (cta_group::2) */
     ACCBLAS_TUNE_CGEMM_3M = 9,      /* c32 gemm on tcgen05: 0 = always the 4M real embedding, 1 = 3M whenever possible     */
     ACCBLAS_TUNE_SNAKE_K = 10,      /* f64 gemm: 0 = every tile walks K forwards (default: alternate per wave of CTAs)       */
     ACCBLAS_TUNE_STREAMK = 11,      /* f64 gemm: 0 = never the persistent kernel, 1 = whole-tile rounds + stream-K tail whenever

@@ -401,3 +401,80 @@ def test_mg_c_abi_single_rank(cuda):
         ab.set_tuning(ab.TUNE_MG_SELF_PEER, -1)
         torch.cuda.synchronize()
         L.accblas_mg_finalize(comm)
+
+
+# ------------------------------------------------------------------------------------------ non-finite inputs
+def _wide_product(oa, A, ob, B):
+    """op(A) op(B) in float64 from explicit real products (no complex BLAS: its Inf handling is not IEEE-by-parts)."""
+    def op(o, X):
+        X = X.T if o in ("T", "H") else X
+        return np.conj(X) if o == "H" else X
+    X, Y = op(oa, A), op(ob, B)
+    with np.errstate(all="ignore"):
+        if np.iscomplexobj(X):
+            xr, xi, yr, yi = (np.asarray(v, dtype=np.float64) for v in (X.real, X.imag, Y.real, Y.imag))
+            out = np.empty(xr.shape[:1] + yr.shape[1:], dtype=np.complex128)
+            out.real = xr @ yr - xi @ yi
+            out.imag = xr @ yi + xi @ yr
+            return out
+        return np.asarray(X, dtype=np.float64) @ np.asarray(Y, dtype=np.float64)
+
+
+@pytest.mark.parametrize("dt", [O.F32, O.C32], ids=ids)
+def test_gemm_nonfinite_inputs_f32_families(dt, cuda):
+    """+-Inf, NaN, Inf * 0 and overflowing entries through the split-precision (3xTF32) families must come out as a plain
+    FP32 gemm (cublasSgemm / cublasCgemm, LLVM/PTX/Level3.hs:91,101) returns them: Inf where the terms agree in sign, NaN
+    for Inf - Inf, Inf * 0 and NaN inputs, everything else finite and within tolerance (round-1 advisor finding:
+    the split turned every output of an Inf row into NaN).  csrc/refit.cuh."""
+    import accblas_b200 as ab
+    rng = np.random.default_rng(4242 + dt)
+    cx = dt == O.C32
+    seen = set()
+    # c32: mma.sync tiles, tcgen05 4M embedding, tcgen05 3M planes; f32: mma.sync tiles, tcgen05
+    cases = ([(96, 80, 64, -1), (300, 260, 200, -1), (1100, 1000, 520, 0), (1100, 1000, 520, 1)] if cx else
+             [(96, 80, 64, -1), (300, 260, 200, -1), (1100, 1000, 520, -1), (1536, 1280, 520, -1)])
+    for (m, n, k, c3m) in cases:
+        for oa, ob in [("N", "N"), ("T", "N"), ("N", "H"), ("H", "T")]:
+            al, A, B = gemm_inputs(rng, dt, oa, ob, m, n, k)
+            al = 1.0
+            # work on op-index views so the planted entries land at known (i, l) / (l, j)
+            Aop = A.T if oa != "N" else A
+            Bop = B.T if ob != "N" else B
+            Aop[3, :] = np.abs(Aop[3, :].real) + 0.5 if not cx else (np.abs(Aop[3, :].real) + 0.5) + 0j
+            Aop[3, 5] = np.inf                      # row 3: +Inf times positive / negative / zero entries of B
+            Aop[10, 7] = -np.inf
+            Aop[17, 2] = np.inf; Aop[17, 9] = -np.inf       # Inf - Inf in every output of row 17 with non-zero B
+            Bop[5, 11] = 0.0                        # C[3, 11] = Inf * 0 = NaN
+            Bop[2, 21] = np.nan                     # column 21 is NaN
+            if not cx:
+                Aop[20, 1] = np.finfo(np.float32).max
+                Bop[1, 30] = 2.0                    # overflow of one product
+                Aop[21, 4] = np.float32(3.4028234e38)       # |a| whose TF32 rounding would be Inf
+            ref = _wide_product(oa, A, ob, B)
+            with np.errstate(all="ignore"):
+                if cx:
+                    # alpha = 1 + 0i is applied the way every complex BLAS epilogue applies it, by parts:
+                    # re = 1 * re - 0 * im  (so an infinite imaginary part makes the real part NaN, and vice versa)
+                    by_parts = np.empty_like(ref)
+                    by_parts.real = 1.0 * ref.real - 0.0 * ref.imag
+                    by_parts.imag = 1.0 * ref.imag + 0.0 * ref.real
+                    ref = by_parts
+                ref32 = ref.astype(np.complex64 if cx else np.float32)
+            if c3m >= 0 and cx:
+                ab.set_tuning(ab.TUNE_CGEMM_3M, c3m)
+            try:
+                seen.add(ab.kernel_name(dt, oa, ob, A.shape, B.shape))
+                C = host(ab.gemm(al, oa, dev(A, cuda), ob, dev(B, cuda)))
+            finally:
+                ab.set_tuning(ab.TUNE_CGEMM_3M, -1)
+            parts = [(C.real, ref32.real), (C.imag, ref32.imag)] if cx else [(C, ref32)]
+            for got, want in parts:
+                what = (O.NAMES[dt], oa, ob, m, n, k, c3m)
+                assert np.array_equal(np.isnan(got), np.isnan(want)), ("NaN pattern", what, int(np.isnan(got).sum()), int(np.isnan(want).sum()))
+                inf = np.isinf(want)
+                assert np.array_equal(np.isinf(got), inf), ("Inf pattern", what)
+                assert np.array_equal(np.sign(got[inf]), np.sign(want[inf])), ("Inf sign", what)
+                fin = np.isfinite(want)
+                scale = np.abs(want[fin]).max() if fin.any() else 1.0
+                assert np.abs(got[fin] - want[fin]).max() <= 1e-4 * max(scale, 1.0) * np.sqrt(k), ("finite part", what)
+    assert any("tcgen05" in s for s in seen) and any("mma" in s for s in seen), seen
