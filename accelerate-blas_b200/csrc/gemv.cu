@@ -168,26 +168,42 @@ gemv_t_kernel(int64_t m, int64_t n, int64_t rows_per_split, Alpha<T> alpha_, con
 // a warp load touches 4 rows x 128 bytes = four whole lines.  The row groups are summed through
 // shared memory in a fixed order (deterministic).  Parallelism is columns / SLAB_CV CTAs, which is
 // enough to fill the GPU exactly where the two-pass kernel above is launch-bound.
-constexpr int SLAB_CV = 8, SLAB_RG = 32, SLAB_UNROLL = 8;
+//
+// Row split over a thread-block CLUSTER (round 2).  columns / SLAB_CV CTAs is a poor count at the top of the range:
+// 2000 x 3000 doubles are 188 slabs on 148 SMs -- 40 SMs stream two slabs while 108 stream one, 63 % of the
+// bandwidth at best (measured 0.85x cuBLAS, zgemv 0.75x).  A cluster of R = 2 / 4 / 8 CTAs now shares a slab, CTA r
+// taking rows [r m / R, (r + 1) m / R); the R partial slabs are handed to the cluster's rank 0 through distributed
+// shared memory and summed there in rank order -- still one launch, no scratch, no atomics, bit-reproducible --
+// and the grid is R times finer (1504 CTAs for the example: 92 % balanced).  R is chosen per shape by slab_cluster().
+constexpr int SLAB_CV = 8, SLAB_RG = 32, SLAB_UNROLL = 8, SLAB_MAXR = 8;
+
+__device__ __forceinline__ uint32_t slab_cluster_rank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ uint32_t slab_cluster_size() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(r)); return r; }
 
 template <typename T, bool CONJ, bool ALIGNED>
 __global__ void __launch_bounds__(SLAB_CV * SLAB_RG)
-gemv_t_slab_kernel(int64_t m, int64_t n, Alpha<T> alpha_, const T *__restrict__ A, const T *__restrict__ x,
+gemv_t_slab_kernel(int64_t m_all, int64_t n, Alpha<T> alpha_, const T *__restrict__ A, const T *__restrict__ x_all,
                    T *__restrict__ y)
 {
     const T alpha = alpha_.get();
     constexpr int VEC = ALIGNED ? 16 / sizeof(T) : 1;
     __shared__ T red[SLAB_RG][SLAB_CV * VEC + 1];
+    __shared__ T part[SLAB_MAXR][SLAB_CV * VEC];                  // rank 0: the other ranks' partial slabs
+    const uint32_t R = slab_cluster_size(), rank = slab_cluster_rank();
+    const int64_t slab = blockIdx.x / R;
+    // this CTA's rows [row0, row0 + m)
+    const int64_t row0 = m_all * rank / R, m = m_all * (rank + 1) / R - row0;
+    const T *__restrict__ x = x_all + row0;
     const int cv = threadIdx.x % SLAB_CV, rg = threadIdx.x / SLAB_CV;
     const int64_t nv = (n + VEC - 1) / VEC;
-    const int64_t v = (int64_t)blockIdx.x * SLAB_CV + cv;
+    const int64_t v = slab * SLAB_CV + cv;
     const bool active = v < nv;
     T acc[VEC];
 #pragma unroll
     for (int e = 0; e < VEC; ++e) acc[e] = Scalar<T>::zero();
     if (active) {
-        const char *p = reinterpret_cast<const char *>(A) + v * (int64_t)(VEC * sizeof(T));
         const int64_t pitch = n * (int64_t)sizeof(T);
+        const char *p = reinterpret_cast<const char *>(A) + row0 * pitch + v * (int64_t)(VEC * sizeof(T));
         int64_t r = rg;
         for (; r + (int64_t)(SLAB_UNROLL - 1) * SLAB_RG < m; r += (int64_t)SLAB_UNROLL * SLAB_RG) {
             Vec16<T> av[SLAB_UNROLL];
@@ -216,15 +232,51 @@ gemv_t_slab_kernel(int64_t m, int64_t n, Alpha<T> alpha_, const T *__restrict__ 
 #pragma unroll
     for (int e = 0; e < VEC; ++e) red[rg][cv * VEC + e] = acc[e];
     __syncthreads();
+    T s = Scalar<T>::zero();
     if (threadIdx.x < SLAB_CV * VEC) {
-        const int64_t j = (int64_t)blockIdx.x * SLAB_CV * VEC + threadIdx.x;
-        if (j < n) {
-            T s = Scalar<T>::zero();
 #pragma unroll 8
-            for (int g = 0; g < SLAB_RG; ++g) s = add_s(s, red[g][threadIdx.x]);
-            y[j] = mul_s(alpha, s);
-        }
+        for (int g = 0; g < SLAB_RG; ++g) s = add_s(s, red[g][threadIdx.x]);
     }
+    if (R > 1) {
+        // hand the partial slab to rank 0 (distributed shared memory), which adds them in rank order
+        if (rank != 0 && threadIdx.x < SLAB_CV * VEC) {
+            const uint32_t local = (uint32_t)__cvta_generic_to_shared(&part[rank][threadIdx.x]);
+            uint32_t remote;
+            asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local), "r"(0));
+            if constexpr (sizeof(T) == 4) asm volatile("st.shared::cluster.b32 [%0], %1;" ::"r"(remote), "r"(*reinterpret_cast<const uint32_t *>(&s)) : "memory");
+            else if constexpr (sizeof(T) == 8) asm volatile("st.shared::cluster.b64 [%0], %1;" ::"r"(remote), "l"(*reinterpret_cast<const uint64_t *>(&s)) : "memory");
+            else asm volatile("st.shared::cluster.v2.b64 [%0], {%1, %2};" ::"r"(remote), "l"(reinterpret_cast<const uint64_t *>(&s)[0]),
+                              "l"(reinterpret_cast<const uint64_t *>(&s)[1]) : "memory");
+        }
+        asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+        asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+        if (rank != 0) return;
+        if (threadIdx.x < SLAB_CV * VEC)
+            for (uint32_t q = 1; q < R; ++q) s = add_s(s, part[q][threadIdx.x]);
+    }
+    if (threadIdx.x < SLAB_CV * VEC) {
+        const int64_t j = slab * SLAB_CV * VEC + threadIdx.x;
+        if (j < n) y[j] = mul_s(alpha, s);
+    }
+}
+
+// cluster size of the slab kernel: the R in {1, 2, 4, 8} whose grid of slabs * R CTAs loads the SMs most evenly
+// (CTAs are small: several are resident per SM, so the balance is total / (ceil(total / SMs) * SMs)), the smaller
+// R on near-ties; every CTA keeps at least two full unrolled passes of rows.  ACCBLAS_GEMV_T_CLUSTER=R forces it.
+inline int slab_cluster(int64_t slabs, int64_t rows)
+{
+    static const int forced = [] { const char *e = getenv("ACCBLAS_GEMV_T_CLUSTER"); return e ? atoi(e) : 0; }();
+    if (forced == 1 || forced == 2 || forced == 4 || forced == 8) return forced;
+    const int64_t sms = sm_count();
+    int best = 1;
+    double best_eff = 0.0;
+    for (int R = 1; R <= SLAB_MAXR; R *= 2) {
+        if (R > 1 && rows / R < 2 * SLAB_RG * SLAB_UNROLL / 4) break;
+        const int64_t total = slabs * R;
+        const double eff = (double)total / (double)(((total + sms - 1) / sms) * sms);
+        if (eff > best_eff * 1.04) { best = R; best_eff = eff; }
+    }
+    return best;
 }
 
 template <typename T>
@@ -288,11 +340,23 @@ int gemv_typed(cudaStream_t st, int opA, int64_t rowsA, int64_t colsA, const voi
     const int64_t nv = aligned ? colsA / VEC : colsA;
     static const int64_t slab_max = [] { const char *e = getenv("ACCBLAS_GEMV_T_SLAB_MAX"); return e ? atoll(e) : (int64_t)64 << 20; }();
     if ((int64_t)sizeof(T) * rowsA * colsA <= slab_max) {       // one launch, no scratch
-        const unsigned grid = (unsigned)((nv + SLAB_CV - 1) / SLAB_CV);
-#define GO(CJ, AL) gemv_t_slab_kernel<T, CJ, AL><<<grid, SLAB_CV * SLAB_RG, 0, st>>>(rowsA, colsA, alpha, A, x, y)
+        const int64_t slabs = (nv + SLAB_CV - 1) / SLAB_CV;
+        const int R = slab_cluster(slabs, rowsA);
+        cudaLaunchConfig_t cfg{};
+        cfg.gridDim = dim3((unsigned)(slabs * R));
+        cfg.blockDim = dim3(SLAB_CV * SLAB_RG);
+        cfg.stream = st;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = (unsigned)R; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        cudaError_t le;
+#define GO(CJ, AL) le = cudaLaunchKernelEx(&cfg, gemv_t_slab_kernel<T, CJ, AL>, rowsA, colsA, alpha, A, x, y)
         if (aligned) { if (conj) GO(true, true); else GO(false, true); }
         else         { if (conj) GO(true, false); else GO(false, false); }
 #undef GO
+        if (le != cudaSuccess) return cuda_fail(le, "gemv_t_slab_kernel launch");
         return check_launch("gemv_t_slab_kernel");
     }
     const int64_t gx = (nv + GT_THREADS - 1) / GT_THREADS;
