@@ -54,6 +54,10 @@ using Tile128x128 = Tile<8, 4, 2, 4, 6, 1>;
 using Tile64x128  = Tile<4, 4, 2, 4, 4, 2>;
 using Tile64x64   = Tile<4, 2, 2, 4, 4, 3>;
 using Tile32x32   = Tile<2, 2, 2, 2, 3, 7>;   // 7 CTAs per SM: 1024 tiles (dgemm 1024^3) are ONE resident wave
+// The same tile with an 8-deep ring for grids of at most three CTAs per SM (500^3: 256 tiles).  There a CTA's progress is
+// bound by the LATENCY of its TMA ring, not by the pipe: three 8 KiB stages in flight per CTA are ~3 K-blocks per L2
+// round trip (r01_dgemm_nn_500_ncu.txt: DMMA 60 % active while 256 CTAs sit on 148 SMs, 16.3 us for 6.7 us of math).
+using Tile32x32Deep = Tile<2, 2, 2, 2, 8, 3>;
 
 __device__ __forceinline__ void dmma(double &d0, double &d1, double a, double b) {
     asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
@@ -893,10 +897,14 @@ int launch_dgemm(const GemmArgs &g)
         return release_mode(false) == REL_DELAYED ? launch_dgemm_streamk<AK, BKM, REL_DELAYED>(g, pl)
                                                   : launch_dgemm_streamk<AK, BKM, REL_FENCED>(g, pl);
     const int rel = release_mode(tile == 0);
+    static const int deep = [] { const char *e = getenv("ACCBLAS_DMMA_DEEP"); return e ? atoi(e) : 1; }();
     switch (tile) {
     case 1:  return launch_dgemm_tile_rel<AK, BKM, Tile64x128>(g, rel);
     case 2:  return launch_dgemm_tile_rel<AK, BKM, Tile64x64>(g, rel);
-    case 3:  return launch_dgemm_tile_rel<AK, BKM, Tile32x32>(g, rel);
+    case 3:
+        if (deep && ((g.m + 31) / 32) * ((g.n + 31) / 32) <= 3 * (int64_t)sm_count())
+            return launch_dgemm_tile_rel<AK, BKM, Tile32x32Deep>(g, rel);
+        return launch_dgemm_tile_rel<AK, BKM, Tile32x32>(g, rel);
     default: return launch_dgemm_tile_rel<AK, BKM, Tile128x128>(g, rel);
     }
 }

@@ -1103,9 +1103,14 @@ int sgemm_tc(const GemmArgs &g)
 
     int s = launch_pack(cx, pa, pb, g.stream);
     if (s == ACCBLAS_OK) {
+        // K-blocks per accumulation chunk (ACCBLAS_TC_KCB).  Measured on the pair tile at 8192^3 (profiles/r02_error_table.jsonl,
+        // r02_pair_kcb.jsonl): chunks of 2 / 4 / 8 give a componentwise error of 1.1 / 1.7 / 2.8 u (u = 2^-24; cublasSgemm on
+        // the same inputs: 6.1 u) at the same speed within the power-cap noise (243 / 241 TFLOP/s) -- so the default stays 2.
         static const int kcb = [] { const char *e = getenv("ACCBLAS_TC_KCB"); return e ? atoi(e) : 2; }();
         const int tile = pick_tc_tile(t);
-        s = tile == 3 ? (kcb == 4 ? launch_tc_pair<3, 4>(g, t, ahi, alo, bhi, blo) : launch_tc_pair<3, 2>(g, t, ahi, alo, bhi, blo))
+        s = tile == 3 ? (kcb == 4 ? launch_tc_pair<3, 4>(g, t, ahi, alo, bhi, blo)
+                       : kcb == 8 ? launch_tc_pair<3, 8>(g, t, ahi, alo, bhi, blo)
+                                  : launch_tc_pair<3, 2>(g, t, ahi, alo, bhi, blo))
           : tile == 1 ? launch_tc<128, 3, 2>(g, t, ahi, alo, bhi, blo)
           : tile == 2 ? launch_tc<64, 4, 2>(g, t, ahi, alo, bhi, blo)
           : kcb == 1 ? launch_tc<256, 2, 1>(g, t, ahi, alo, bhi, blo)

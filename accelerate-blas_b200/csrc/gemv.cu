@@ -266,11 +266,13 @@ gemv_t_slab_kernel(int64_t m_all, int64_t n, Alpha<T> alpha_, const T *__restric
 inline int slab_cluster(int64_t slabs, int64_t rows)
 {
     static const int forced = [] { const char *e = getenv("ACCBLAS_GEMV_T_CLUSTER"); return e ? atoi(e) : 0; }();
-    if (forced == 1 || forced == 2 || forced == 4 || forced == 8) return forced;
+    if (forced == 1 || forced == 2 || forced == 4 || forced == 8) return forced;      // (8: measurement only)
     const int64_t sms = sm_count();
     int best = 1;
     double best_eff = 0.0;
-    for (int R = 1; R <= SLAB_MAXR; R *= 2) {
+    // clusters of 8 measured SLOWER than no split (2000 x 3000 doubles: 14.3 us against 10.3 us for R = 2 or 4 and 12.3 us
+    // for R = 1, profiles/r02_gemv_t_cluster.txt): placement of an 8-CTA cluster needs 8 free slots in one GPC
+    for (int R = 1; R <= 4; R *= 2) {
         if (R > 1 && rows / R < 2 * SLAB_RG * SLAB_UNROLL / 4) break;
         const int64_t total = slabs * R;
         const double eff = (double)total / (double)(((total + sms - 1) / sms) * sms);
@@ -351,8 +353,10 @@ int gemv_typed(cudaStream_t st, int opA, int64_t rowsA, int64_t colsA, const voi
         attr[0].val.clusterDim.x = (unsigned)R; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
         cfg.attrs = attr;
         cfg.numAttrs = 1;
-        cudaError_t le;
-#define GO(CJ, AL) le = cudaLaunchKernelEx(&cfg, gemv_t_slab_kernel<T, CJ, AL>, rowsA, colsA, alpha, A, x, y)
+        cudaError_t le = cudaSuccess;
+        // R == 1 keeps the plain launch: a cluster launch costs ~2 us more even for clusters of one CTA (measured)
+#define GO(CJ, AL) do { if (R == 1) gemv_t_slab_kernel<T, CJ, AL><<<cfg.gridDim, cfg.blockDim, 0, st>>>(rowsA, colsA, alpha, A, x, y); \
+                        else le = cudaLaunchKernelEx(&cfg, gemv_t_slab_kernel<T, CJ, AL>, rowsA, colsA, alpha, A, x, y); } while (0)
         if (aligned) { if (conj) GO(true, true); else GO(false, true); }
         else         { if (conj) GO(true, false); else GO(false, false); }
 #undef GO
