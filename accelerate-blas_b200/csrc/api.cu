@@ -476,6 +476,25 @@ int accblas_gemm_strided_batched(accblas_stream_t stream, int dtype, int opA, in
         }
         return ACCBLAS_OK;
     }
+    // products of the warp-level tensor families (DMMA: f64 / c64, mma.sync: f32 / c32 -- everything below the sizes that
+    // fill the GPU on their own): ONE launch, the batch folded into the grid (blockIdx -> (product, tile)) and into a third
+    // dimension of the TMA tensor maps, so the tiles of all products share the waves.  Needs 16-byte multiples for the
+    // strides (TMA plane stride, vector stores); anything else falls through to the loop of launches below.
+    if (batch > 1 && g.k > 0 && g.A && g.B && g.C && g.alpha && g_gemm_path == 0) {
+        const Family f = pick_family(g);
+        const auto ok16 = [&](int64_t stride) { return (es * (size_t)stride) % 16 == 0; };
+        if ((f == FAM_DMMA || f == FAM_MMA) && ok16(strideA) && ok16(strideB) && ok16(strideC) && batch <= 0x7fffffff) {
+            ACC_TRY(device_check());
+            const size_t spanC = es * ((size_t)strideC * (size_t)(batch - 1) + (size_t)g.m * (size_t)g.n);
+            if (overlaps(g.C, spanC, g.A, es * ((size_t)strideA * (size_t)(batch - 1) + span(g.rowsA, g.colsA, g.lda))) ||
+                overlaps(g.C, spanC, g.B, es * ((size_t)strideB * (size_t)(batch - 1) + span(g.rowsB, g.colsB, g.ldb))))
+                return ACCBLAS_ERR_ALIAS;
+            GemmArgs h = g;
+            h.batch = batch; h.strideA = strideA; h.strideB = strideB; h.strideC = strideC;
+            h.no_persistent = true;
+            return run_family(f, h);
+        }
+    }
     for (int64_t b = 0; b < batch; ++b) {
         GemmArgs h{};
         h.dtype = dtype; h.opA = opA; h.opB = opB;

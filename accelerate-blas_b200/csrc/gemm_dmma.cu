@@ -108,6 +108,10 @@ template <int REL> __device__ __forceinline__ void release_after(uint32_t empty_
 struct DgemmParams {
     int64_t m, n, k, ldc;
     int a_one_box, b_one_box;   // MN-major operand fetched as ONE 3-D TMA box per stage (tma::make_mn3d)
+    // strided batch (accblas_gemm_strided_batched): gridDim.x = batch * tiles_per_batch, the tensor maps are 3-D
+    // (tma::make_2d_batched) and product b writes C + b * stride_c.  tiles_per_batch == 0: one product, 2-D maps.
+    int tiles_per_batch, plane_a, plane_b;   // plane_x = 1: operand x advances with the batch index (0: shared)
+    int64_t stride_c;
     Alpha<double> alpha;
     BetaC<double> beta;  // + beta * Cin (accblas_gemm_ex); cin == nullptr: C is write-only
     double *C;
@@ -134,17 +138,18 @@ __device__ __forceinline__ void tile_coords(const DgemmParams &p, int tile, int 
 // host wavefront and on 1024^3 (round 2, profiles/r02_strip_ab.jsonl).
 template <typename TL, bool BETA = true>
 __device__ __forceinline__ void dgemm_epilogue(const DgemmParams &p, const double (&acc)[TL::MI][TL::NJ][2],
-                                               int m0, int n0, int wm, int wn, int g, int t)
+                                               int m0, int n0, int wm, int wn, int g, int t, int64_t c_off = 0)
 {
     constexpr int MI = TL::MI, NJ = TL::NJ;
     const bool vec = ((p.n | p.ldc) & 1) == 0;
     const double alpha = p.alpha.get();
     const bool acc_in = BETA && p.beta.on();
+    double *const Cb = p.C + c_off;
 #pragma unroll
     for (int i = 0; i < MI; ++i) {
         const int64_t r = m0 + wm * MI * 8 + i * 8 + g;
         if (r >= p.m) continue;
-        double *crow = p.C + r * p.ldc;
+        double *crow = Cb + r * p.ldc;
 #pragma unroll
         for (int j = 0; j < NJ; ++j) {
             const int64_t c = n0 + wn * NJ * 8 + j * 8 + 2 * t;
@@ -176,8 +181,13 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
     const uint32_t bar_base = smem_base + STAGES * STAGE_BYTES;      // full[STAGES], empty[STAGES]
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
-    int tile_m, tile_n;
-    tile_coords(p, blockIdx.x, tile_m, tile_n);
+    int tile_m, tile_n, tile = blockIdx.x, pa = -1, pb = -1;        // pa / pb: batch plane of A / B (-1: 2-D maps)
+    if (p.tiles_per_batch > 0) {
+        const int b = tile / p.tiles_per_batch;
+        tile -= b * p.tiles_per_batch;
+        pa = b * p.plane_a; pb = b * p.plane_b;
+    }
+    tile_coords(p, tile, tile_m, tile_n);
     const int m0 = tile_m * BM, n0 = tile_n * BN;
     const int kblocks = (int)((p.k + BK - 1) / BK);
 
@@ -209,16 +219,16 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
                 const uint32_t sa = smem_base + s * STAGE_BYTES, sb = sa + A_BYTES;
                 tma::mbar_expect_tx(full, STAGE_BYTES);
                 const int k0 = (rev ? kblocks - 1 - kb : kb) * BK;
-                if (AK) tma::load_2d(sa, &mapA, full, k0, m0);
+                if (AK) tma::load_box(sa, &mapA, full, k0, m0, pa);
                 else if (p.a_one_box) tma::load_3d(sa, &mapA, full, 0, k0, m0 >> 4);
                 else
 #pragma unroll
-                    for (int j = 0; j < BM / 16; ++j) tma::load_2d(sa + j * 2048, &mapA, full, m0 + 16 * j, k0);
-                if (BKM) tma::load_2d(sb, &mapB, full, k0, n0);
+                    for (int j = 0; j < BM / 16; ++j) tma::load_box(sa + j * 2048, &mapA, full, m0 + 16 * j, k0, pa);
+                if (BKM) tma::load_box(sb, &mapB, full, k0, n0, pb);
                 else if (p.b_one_box) tma::load_3d(sb, &mapB, full, 0, k0, n0 >> 4);
                 else
 #pragma unroll
-                    for (int j = 0; j < BN / 16; ++j) tma::load_2d(sb + j * 2048, &mapB, full, n0 + 16 * j, k0);
+                    for (int j = 0; j < BN / 16; ++j) tma::load_box(sb + j * 2048, &mapB, full, n0 + 16 * j, k0, pb);
             }
         }
         return;
@@ -273,7 +283,9 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
     }
 
     // ---- epilogue: C = alpha * acc (+ beta * Cin); C itself is never read unless it is Cin ----
-    dgemm_epilogue<TL, BETA>(p, acc, m0, n0, wm, wn, g, t);
+    // (the batch's C offset is recomputed here rather than carried through the K loop)
+    dgemm_epilogue<TL, BETA>(p, acc, m0, n0, wm, wn, g, t,
+                             p.tiles_per_batch > 0 ? (int64_t)(blockIdx.x / p.tiles_per_batch) * p.stride_c : 0);
 }
 
 
@@ -554,6 +566,8 @@ struct ZgemmParams {
     BetaC<double2> beta;
     double2 *C;
     int tiles_m, tiles_n;
+    int tiles_per_batch, plane_a, plane_b;   // strided batch, as in DgemmParams (0: one product, 2-D maps)
+    int64_t stride_c;
 };
 
 template <bool AK, bool BKM, bool CONJA, bool CONJB, typename TL, int REL, bool BETA>
@@ -569,13 +583,19 @@ zgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
     constexpr int GROUP = 16;
-    int tile_m, tile_n;
+    int tile_m, tile_n, pa = -1, pb = -1;                          // pa / pb: batch plane of A / B (-1: 2-D maps)
     {
+        int tile = blockIdx.x;
+        if (p.tiles_per_batch > 0) {
+            const int b = tile / p.tiles_per_batch;
+            tile -= b * p.tiles_per_batch;
+            pa = b * p.plane_a; pb = b * p.plane_b;
+        }
         const int per_group = GROUP * p.tiles_n;
-        const int grp = blockIdx.x / per_group;
+        const int grp = tile / per_group;
         const int first_m = grp * GROUP;
         const int gsz = min(p.tiles_m - first_m, GROUP);
-        const int in_grp = blockIdx.x - grp * per_group;
+        const int in_grp = tile - grp * per_group;
         tile_m = first_m + in_grp % gsz;
         tile_n = in_grp / gsz;
     }
@@ -606,14 +626,14 @@ zgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
                 tma::mbar_expect_tx(full, ZSTAGE_BYTES);
                 const int k0 = kb * ZBK;
                 // tensor maps are over doubles: inner coordinates are 2 x the complex index
-                if (AK) tma::load_2d(sa, &mapA, full, 2 * k0, m0);
+                if (AK) tma::load_box(sa, &mapA, full, 2 * k0, m0, pa);
                 else
 #pragma unroll
-                    for (int j = 0; j < ZBM / 8; ++j) tma::load_2d(sa + j * 1024, &mapA, full, 2 * (m0 + 8 * j), k0);
-                if (BKM) tma::load_2d(sb, &mapB, full, 2 * k0, n0);
+                    for (int j = 0; j < ZBM / 8; ++j) tma::load_box(sa + j * 1024, &mapA, full, 2 * (m0 + 8 * j), k0, pa);
+                if (BKM) tma::load_box(sb, &mapB, full, 2 * k0, n0, pb);
                 else
 #pragma unroll
-                    for (int j = 0; j < ZBN / 8; ++j) tma::load_2d(sb + j * 1024, &mapB, full, 2 * (n0 + 8 * j), k0);
+                    for (int j = 0; j < ZBN / 8; ++j) tma::load_box(sb + j * 1024, &mapB, full, 2 * (n0 + 8 * j), k0, pb);
             }
         }
         return;
@@ -687,11 +707,12 @@ zgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
 
     const double2 al = p.alpha.get();
     const bool acc_in = BETA && p.beta.on();              // BETA is a template parameter: see dgemm_epilogue
+    double2 *const Cb = p.C + (p.tiles_per_batch > 0 ? (int64_t)(blockIdx.x / p.tiles_per_batch) * p.stride_c : 0);
 #pragma unroll
     for (int i = 0; i < MI; ++i) {
         const int64_t r = m0 + wm * MI * 8 + i * 8 + g;
         if (r >= p.m) continue;
-        double2 *crow = p.C + r * p.ldc;
+        double2 *crow = Cb + r * p.ldc;
 #pragma unroll
         for (int j = 0; j < NJ; ++j) {
             const int64_t c = n0 + wn * NJ * 8 + j * 8 + 2 * t;
@@ -728,7 +749,7 @@ constexpr TileModel kTileModel[4] = {
     {32, 32, 0.975, 32.0, 0.50},
 };
 
-int pick_tile(int64_t m, int64_t n, int64_t k, double *cost_out = nullptr)
+int pick_tile(int64_t m, int64_t n, int64_t k, double *cost_out = nullptr, int64_t batch = 1)
 {
     if (g_tuning[ACCBLAS_TUNE_DMMA_TILE] >= 0 && g_tuning[ACCBLAS_TUNE_DMMA_TILE] < 4) return g_tuning[ACCBLAS_TUNE_DMMA_TILE];
     const int sms = sm_count();
@@ -736,7 +757,7 @@ int pick_tile(int64_t m, int64_t n, int64_t k, double *cost_out = nullptr)
     double best_cost = 0.0;
     for (int c = 0; c < 4; ++c) {
         const TileModel &t = kTileModel[c];
-        const int64_t tiles = ((m + t.bm - 1) / t.bm) * ((n + t.bn - 1) / t.bn);
+        const int64_t tiles = ((m + t.bm - 1) / t.bm) * ((n + t.bn - 1) / t.bn) * batch;     // a batch shares the waves
         const double per_sm = (double)((tiles + sms - 1) / sms);
         const double cost = per_sm * (double)t.bm * (double)t.bn * ((double)k + t.fixed_k) / (per_sm > 1.0 ? t.eff : t.eff_alone);
         if (c == 0 || cost < best_cost * 0.999) { best = c; best_cost = cost; }
@@ -763,9 +784,12 @@ int release_mode(bool dp_big_tile)
 // tensor maps of one operand: K-major -> one 2-D box of BK x rows; MN-major -> one 3-D box when the extent allows
 // (tma::make_mn3d), else BM/16 (BN/16) 2-D boxes of 16 x 16
 bool make_operand_map(CUtensorMap *map, bool kmajor, const void *base, int64_t rows, int64_t cols, int64_t ld, int tile_extent,
-                      int *one_box)
+                      int *one_box, int64_t planes = 0, int64_t plane_stride = 0)
 {
     *one_box = 0;
+    if (planes > 0)                              // strided batch: 3-D maps, boxes as in the 2-D case (no one-box panels)
+        return tma::make_2d_batched(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 8, base, (uint64_t)rows, (uint64_t)cols,
+                                    kmajor ? tile_extent : BK, 16, (uint64_t)ld * 8, (uint64_t)planes, (uint64_t)plane_stride * 8);
     if (kmajor)
         return tma::make_2d(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 8, base, (uint64_t)rows, (uint64_t)cols, tile_extent, 16, (uint64_t)ld * 8);
     if (g_tuning[ACCBLAS_TUNE_MN_ONEBOX] != 0 && cols % 16 == 0 &&
@@ -785,6 +809,7 @@ void fill_params(DgemmParams &p, const GemmArgs &g, int BM, int BN)
     p.tiles_m = (int)((g.m + BM - 1) / BM);
     p.tiles_n = (int)((g.n + BN - 1) / BN);
     p.group = g_tuning[ACCBLAS_TUNE_RASTER_GROUP] > 0 ? g_tuning[ACCBLAS_TUNE_RASTER_GROUP] : 16;
+    p.tiles_per_batch = 0; p.plane_a = p.plane_b = 0; p.stride_c = 0;
 }
 
 template <bool AK, bool BKM, typename TL, int REL, bool BETA>
@@ -793,8 +818,12 @@ int launch_dgemm_tile(const GemmArgs &g)
     constexpr int BM = TL::BM, BN = TL::BN, SMEM_BYTES = TL::SMEM_BYTES;
     CUtensorMap mapA, mapB;
     DgemmParams p;
-    if (!make_operand_map(&mapA, AK, g.A, g.rowsA, g.colsA, g.lda, BM, &p.a_one_box) ||
-        !make_operand_map(&mapB, BKM, g.B, g.rowsB, g.colsB, g.ldb, BN, &p.b_one_box))
+    const bool batched = g.batch > 1;
+    // a batch that re-uses one operand (stride 0) maps it as a single plane and always loads plane 0
+    if (!make_operand_map(&mapA, AK, g.A, g.rowsA, g.colsA, g.lda, BM, &p.a_one_box, batched ? (g.strideA ? g.batch : 1) : 0,
+                          g.strideA ? g.strideA : g.rowsA * g.lda) ||
+        !make_operand_map(&mapB, BKM, g.B, g.rowsB, g.colsB, g.ldb, BN, &p.b_one_box, batched ? (g.strideB ? g.batch : 1) : 0,
+                          g.strideB ? g.strideB : g.rowsB * g.ldb))
         return cuda_fail(cudaErrorInvalidValue, "cuTensorMapEncodeTiled");
     static thread_local AttrOnce attr_once;
     if (attr_once.need()) {
@@ -802,7 +831,14 @@ int launch_dgemm_tile(const GemmArgs &g)
     }
     fill_params(p, g, BM, BN);
     p.snake_waves = g_tuning[ACCBLAS_TUNE_SNAKE_K] == 0 ? 0 : sm_count() * TL::MIN_CTAS;
-    const int64_t tiles = (int64_t)p.tiles_m * p.tiles_n;
+    int64_t tiles = (int64_t)p.tiles_m * p.tiles_n;
+    if (batched) {
+        p.tiles_per_batch = (int)tiles;
+        p.plane_a = g.strideA ? 1 : 0; p.plane_b = g.strideB ? 1 : 0;
+        p.stride_c = g.strideC;
+        p.snake_waves = 0;
+        tiles *= g.batch;
+    }
     if (tiles > 0x7fffffff) return ACCBLAS_ERR_SHAPE;
     dgemm_dmma_kernel<AK, BKM, TL, REL, BETA><<<(unsigned)tiles, TL::THREADS, SMEM_BYTES, g.stream>>>(mapA, mapB, p);
     return check_launch("dgemm_dmma_kernel");
@@ -891,8 +927,9 @@ int launch_dgemm_tile_rel(const GemmArgs &g, int rel)
 template <bool AK, bool BKM>
 int launch_dgemm(const GemmArgs &g)
 {
-    const int tile = pick_tile(g.m, g.n, g.k);
-    const StreamKPlan pl = g.no_persistent ? StreamKPlan{false, 0, 0} : plan_streamk(g.m, g.n, g.k);
+    const bool batched = g.batch > 1;
+    const int tile = pick_tile(g.m, g.n, g.k, nullptr, batched ? g.batch : 1);
+    const StreamKPlan pl = (g.no_persistent || batched) ? StreamKPlan{false, 0, 0} : plan_streamk(g.m, g.n, g.k);
     if (pl.use)
         return release_mode(false) == REL_DELAYED ? launch_dgemm_streamk<AK, BKM, REL_DELAYED>(g, pl)
                                                   : launch_dgemm_streamk<AK, BKM, REL_FENCED>(g, pl);
@@ -902,7 +939,7 @@ int launch_dgemm(const GemmArgs &g)
     case 1:  return launch_dgemm_tile_rel<AK, BKM, Tile64x128>(g, rel);
     case 2:  return launch_dgemm_tile_rel<AK, BKM, Tile64x64>(g, rel);
     case 3:
-        if (deep && ((g.m + 31) / 32) * ((g.n + 31) / 32) <= 3 * (int64_t)sm_count())
+        if (deep && ((g.m + 31) / 32) * ((g.n + 31) / 32) * (batched ? g.batch : 1) <= 3 * (int64_t)sm_count())
             return launch_dgemm_tile_rel<AK, BKM, Tile32x32Deep>(g, rel);
         return launch_dgemm_tile_rel<AK, BKM, Tile32x32>(g, rel);
     default: return launch_dgemm_tile_rel<AK, BKM, Tile128x128>(g, rel);
@@ -915,11 +952,18 @@ int launch_zgemm_tile(const GemmArgs &g)
     constexpr int ZBM = TL::BM, ZBN = TL::BN;
     CUtensorMap mapA, mapB;
     // maps are over doubles (no complex TMA type): a complex row of c columns is 2c doubles
-    if (!tma::make_2d(&mapA, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 8, g.A, (uint64_t)g.rowsA, 2 * (uint64_t)g.colsA,
-                      AK ? ZBM : ZBK, 16, (uint64_t)g.lda * 16) ||
-        !tma::make_2d(&mapB, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 8, g.B, (uint64_t)g.rowsB, 2 * (uint64_t)g.colsB,
-                      BKM ? ZBN : ZBK, 16, (uint64_t)g.ldb * 16))
-        return cuda_fail(cudaErrorInvalidValue, "cuTensorMapEncodeTiled");
+    const bool batched = g.batch > 1;
+    const CUtensorMapDataType F64 = CU_TENSOR_MAP_DATA_TYPE_FLOAT64;
+    bool ok;
+    if (batched)
+        ok = tma::make_2d_batched(&mapA, F64, 8, g.A, (uint64_t)g.rowsA, 2 * (uint64_t)g.colsA, AK ? ZBM : ZBK, 16, (uint64_t)g.lda * 16,
+                                  g.strideA ? (uint64_t)g.batch : 1, (uint64_t)(g.strideA ? g.strideA : g.rowsA * g.lda) * 16) &&
+             tma::make_2d_batched(&mapB, F64, 8, g.B, (uint64_t)g.rowsB, 2 * (uint64_t)g.colsB, BKM ? ZBN : ZBK, 16, (uint64_t)g.ldb * 16,
+                                  g.strideB ? (uint64_t)g.batch : 1, (uint64_t)(g.strideB ? g.strideB : g.rowsB * g.ldb) * 16);
+    else
+        ok = tma::make_2d(&mapA, F64, 8, g.A, (uint64_t)g.rowsA, 2 * (uint64_t)g.colsA, AK ? ZBM : ZBK, 16, (uint64_t)g.lda * 16) &&
+             tma::make_2d(&mapB, F64, 8, g.B, (uint64_t)g.rowsB, 2 * (uint64_t)g.colsB, BKM ? ZBN : ZBK, 16, (uint64_t)g.ldb * 16);
+    if (!ok) return cuda_fail(cudaErrorInvalidValue, "cuTensorMapEncodeTiled");
     static thread_local AttrOnce attr_once;
     if (attr_once.need()) {
         ACC_CUDA(cudaFuncSetAttribute(zgemm_dmma_kernel<AK, BKM, CA, CB, TL, REL, BETA>, cudaFuncAttributeMaxDynamicSharedMemorySize, TL::SMEM_BYTES));
@@ -931,7 +975,14 @@ int launch_zgemm_tile(const GemmArgs &g)
     p.C = static_cast<double2 *>(g.C);
     p.tiles_m = (int)((g.m + ZBM - 1) / ZBM);
     p.tiles_n = (int)((g.n + ZBN - 1) / ZBN);
-    const int64_t tiles = (int64_t)p.tiles_m * p.tiles_n;
+    int64_t tiles = (int64_t)p.tiles_m * p.tiles_n;
+    p.tiles_per_batch = 0; p.plane_a = p.plane_b = 0; p.stride_c = 0;
+    if (batched) {
+        p.tiles_per_batch = (int)tiles;
+        p.plane_a = g.strideA ? 1 : 0; p.plane_b = g.strideB ? 1 : 0;
+        p.stride_c = g.strideC;
+        tiles *= g.batch;
+    }
     if (tiles > 0x7fffffff) return ACCBLAS_ERR_SHAPE;
     zgemm_dmma_kernel<AK, BKM, CA, CB, TL, REL, BETA><<<(unsigned)tiles, TL::THREADS, TL::SMEM_BYTES, g.stream>>>(mapA, mapB, p);
     return check_launch("zgemm_dmma_kernel");
@@ -944,7 +995,7 @@ constexpr TileModel kZTileModel[3] = {
     {32, 32, 0.975, 16.0, 0.60},
 };
 
-int pick_ztile(int64_t m, int64_t n, int64_t k)
+int pick_ztile(int64_t m, int64_t n, int64_t k, int64_t batch = 1)
 {
     if (g_tuning[ACCBLAS_TUNE_ZMMA_TILE] >= 0 && g_tuning[ACCBLAS_TUNE_ZMMA_TILE] < 3) return g_tuning[ACCBLAS_TUNE_ZMMA_TILE];
     const int sms = sm_count();
@@ -952,7 +1003,7 @@ int pick_ztile(int64_t m, int64_t n, int64_t k)
     double best_cost = 0.0;
     for (int c = 0; c < 3; ++c) {
         const TileModel &t = kZTileModel[c];
-        const int64_t tiles = ((m + t.bm - 1) / t.bm) * ((n + t.bn - 1) / t.bn);
+        const int64_t tiles = ((m + t.bm - 1) / t.bm) * ((n + t.bn - 1) / t.bn) * batch;
         const double per_sm = (double)((tiles + sms - 1) / sms);
         const double cost = per_sm * (double)t.bm * (double)t.bn * ((double)k + t.fixed_k) / (per_sm > 1.0 ? t.eff : t.eff_alone);
         if (c == 0 || cost < best_cost * 0.999) { best = c; best_cost = cost; }
@@ -963,7 +1014,7 @@ int pick_ztile(int64_t m, int64_t n, int64_t k)
 template <bool AK, bool BKM, bool CA, bool CB>
 int launch_zgemm(const GemmArgs &g)
 {
-    const int tile = pick_ztile(g.m, g.n, g.k);
+    const int tile = pick_ztile(g.m, g.n, g.k, g.batch > 1 ? g.batch : 1);
     // complex kernels: fenced or delayed only (the light release is known to race on the 32 x 32 tile)
     const bool delayed = g_tuning[ACCBLAS_TUNE_RELEASE] == 2, beta = has_beta(g);
     switch (tile) {

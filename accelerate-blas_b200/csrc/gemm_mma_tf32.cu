@@ -87,17 +87,27 @@ struct SgemmMmaParams {
     BetaC<float2> cbeta;
     float *C;
     int tiles_m, tiles_n;
+    int tiles_per_batch, plane_a, plane_b;   // strided batch as in gemm_dmma.cu's DgemmParams (0: one product, 2-D maps)
+    int64_t stride_c;                        // ELEMENTS (complex elements for c32) between the outputs of the batch
     Refit32 refit;             // non-finite sums are recomputed in plain FP32 from the caller's operands (refit.cuh)
 };
 
-__device__ __forceinline__ void raster(int tiles_m, int tiles_n, int &tile_m, int &tile_n)
+__device__ __forceinline__ void raster(const SgemmMmaParams &p, int &tile_m, int &tile_n, int &pa, int &pb)
 {
     constexpr int GROUP = 16;
+    const int tiles_m = p.tiles_m, tiles_n = p.tiles_n;
+    int tile = blockIdx.x;
+    pa = pb = -1;                                                 // batch plane of A / B (-1: 2-D maps)
+    if (p.tiles_per_batch > 0) {
+        const int b = tile / p.tiles_per_batch;
+        tile -= b * p.tiles_per_batch;
+        pa = b * p.plane_a; pb = b * p.plane_b;
+    }
     const int per_group = GROUP * tiles_n;
-    const int grp = blockIdx.x / per_group;
+    const int grp = tile / per_group;
     const int first_m = grp * GROUP;
     const int gsz = min(tiles_m - first_m, GROUP);
-    const int in_grp = blockIdx.x - grp * per_group;
+    const int in_grp = tile - grp * per_group;
     tile_m = first_m + in_grp % gsz;
     tile_n = in_grp / gsz;
 }
@@ -118,8 +128,8 @@ sgemm_mma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
     const uint32_t smem_base = (tma::smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t bar_base = smem_base + STAGES * STAGE_BYTES;      // full[STAGES], empty[STAGES]
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    int tile_m, tile_n;
-    raster(p.tiles_m, p.tiles_n, tile_m, tile_n);
+    int tile_m, tile_n, pa, pb;
+    raster(p, tile_m, tile_n, pa, pb);
     const int m0 = tile_m * BM, n0 = tile_n * BN;
     const int kblocks = (int)((p.k + BK - 1) / BK);
 
@@ -144,14 +154,14 @@ sgemm_mma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                 const uint32_t sa = smem_base + s * STAGE_BYTES, sb = sa + A_BYTES;
                 tma::mbar_expect_tx(full, STAGE_BYTES);
                 const int k0 = kb * BK;
-                if (AK) tma::load_2d(sa, &mapA, full, k0, m0);
+                if (AK) tma::load_box(sa, &mapA, full, k0, m0, pa);
                 else
 #pragma unroll
-                    for (int j = 0; j < BM / 32; ++j) tma::load_2d(sa + j * 4096, &mapA, full, m0 + 32 * j, k0);
-                if (BKM) tma::load_2d(sb, &mapB, full, k0, n0);
+                    for (int j = 0; j < BM / 32; ++j) tma::load_box(sa + j * 4096, &mapA, full, m0 + 32 * j, k0, pa);
+                if (BKM) tma::load_box(sb, &mapB, full, k0, n0, pb);
                 else
 #pragma unroll
-                    for (int j = 0; j < BN / 32; ++j) tma::load_2d(sb + j * 4096, &mapB, full, n0 + 32 * j, k0);
+                    for (int j = 0; j < BN / 32; ++j) tma::load_box(sb + j * 4096, &mapB, full, n0 + 32 * j, k0, pb);
             }
         }
         return;
@@ -231,6 +241,7 @@ sgemm_mma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
         }
     }
 
+    const int64_t batch = p.tiles_per_batch > 0 ? blockIdx.x / p.tiles_per_batch : 0;   // recomputed: not carried through the K loop
     // ---- non-finite sums (Inf / NaN / overflowing inputs cannot go through the split): refit.cuh, warp-uniform ----
     {
         bool any = false;
@@ -253,7 +264,7 @@ sgemm_mma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                     for (int e = 0; e < 4; ++e) {
                         const int64_t r = m0 + wm * MI * 16 + i * 16 + (e >> 1) * 8 + g;
                         const int64_t c = n0 + wn * NJ * 8 + j * 8 + 2 * t + (e & 1);
-                        tot[i][j][e] = refit_real(p.refit, tot[i][j][e], r, c, r < p.m && c < p.n);
+                        tot[i][j][e] = refit_real(p.refit, tot[i][j][e], r, c, r < p.m && c < p.n, batch);
                     }
         }
     }
@@ -266,7 +277,7 @@ sgemm_mma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
         for (int hr = 0; hr < 2; ++hr) {
             const int64_t r = m0 + wm * MI * 16 + i * 16 + hr * 8 + g;
             if (r >= p.m) continue;
-            float *crow = p.C + r * p.ldc;
+            float *crow = p.C + batch * p.stride_c + r * p.ldc;
 #pragma unroll
             for (int j = 0; j < NJ; ++j) {
                 const int64_t c = n0 + wn * NJ * 8 + j * 8 + 2 * t;
@@ -310,8 +321,8 @@ cgemm_mma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
     const uint32_t smem_base = (tma::smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t bar_base = smem_base + STAGES * STAGE_BYTES;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    int tile_m, tile_n;
-    raster(p.tiles_m, p.tiles_n, tile_m, tile_n);
+    int tile_m, tile_n, pa, pb;
+    raster(p, tile_m, tile_n, pa, pb);
     const int m0 = tile_m * BM, n0 = tile_n * BN;
     const int kblocks = (int)((p.k + BK - 1) / BK);
 
@@ -336,14 +347,14 @@ cgemm_mma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                 tma::mbar_expect_tx(full, STAGE_BYTES);
                 const int k0 = kb * BK;
                 // tensor maps are over floats: inner coordinates are 2 x the complex index
-                if (AK) tma::load_2d(sa, &mapA, full, 2 * k0, m0);
+                if (AK) tma::load_box(sa, &mapA, full, 2 * k0, m0, pa);
                 else
 #pragma unroll
-                    for (int j = 0; j < BM / 16; ++j) tma::load_2d(sa + j * 2048, &mapA, full, 2 * (m0 + 16 * j), k0);
-                if (BKM) tma::load_2d(sb, &mapB, full, 2 * k0, n0);
+                    for (int j = 0; j < BM / 16; ++j) tma::load_box(sa + j * 2048, &mapA, full, 2 * (m0 + 16 * j), k0, pa);
+                if (BKM) tma::load_box(sb, &mapB, full, 2 * k0, n0, pb);
                 else
 #pragma unroll
-                    for (int j = 0; j < BN / 16; ++j) tma::load_2d(sb + j * 2048, &mapB, full, 2 * (n0 + 16 * j), k0);
+                    for (int j = 0; j < BN / 16; ++j) tma::load_box(sb + j * 2048, &mapB, full, 2 * (n0 + 16 * j), k0, pb);
             }
         }
         return;
@@ -423,6 +434,7 @@ cgemm_mma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
         }
     }
 
+    const int64_t batch = p.tiles_per_batch > 0 ? blockIdx.x / p.tiles_per_batch : 0;
     // ---- non-finite sums: refit.cuh, warp-uniform ----
     {
         bool any = false;
@@ -445,12 +457,12 @@ cgemm_mma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                     for (int e = 0; e < 4; ++e) {
                         const int64_t r = m0 + wm * MI * 16 + i * 16 + (e >> 1) * 8 + g;
                         const int64_t c = n0 + wn * NJ * 8 + j * 8 + 2 * t + (e & 1);
-                        const float2 v = refit_cplx(p.refit, make_float2(tre[i][j][e], tim[i][j][e]), r, c, r < p.m && c < p.n);
+                        const float2 v = refit_cplx(p.refit, make_float2(tre[i][j][e], tim[i][j][e]), r, c, r < p.m && c < p.n, batch);
                         tre[i][j][e] = v.x; tim[i][j][e] = v.y;
                     }
         }
     }
-    float2 *C = reinterpret_cast<float2 *>(p.C);
+    float2 *C = reinterpret_cast<float2 *>(p.C) + batch * p.stride_c;
     const float2 al = p.calpha.get();
 #pragma unroll
     for (int i = 0; i < MI; ++i)
@@ -480,16 +492,40 @@ cgemm_mma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
 // ---------------------------------------------------------------------------------
 bool aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
+// tensor maps of one product (2-D) or of a strided batch (3-D, tma::make_2d_batched); `fpe` = floats per element
+bool mma_maps(CUtensorMap *mapA, CUtensorMap *mapB, const GemmArgs &g, int fpe, uint32_t box_rows_a, uint32_t box_rows_b)
+{
+    const CUtensorMapDataType F = CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
+    const uint64_t eb = 4 * (uint64_t)fpe;
+    if (g.batch > 1)
+        return tma::make_2d_batched(mapA, F, 4, g.A, (uint64_t)g.rowsA, fpe * (uint64_t)g.colsA, box_rows_a, 32, (uint64_t)g.lda * eb,
+                                    g.strideA ? (uint64_t)g.batch : 1, (uint64_t)(g.strideA ? g.strideA : g.rowsA * g.lda) * eb) &&
+               tma::make_2d_batched(mapB, F, 4, g.B, (uint64_t)g.rowsB, fpe * (uint64_t)g.colsB, box_rows_b, 32, (uint64_t)g.ldb * eb,
+                                    g.strideB ? (uint64_t)g.batch : 1, (uint64_t)(g.strideB ? g.strideB : g.rowsB * g.ldb) * eb);
+    return tma::make_2d(mapA, F, 4, g.A, (uint64_t)g.rowsA, fpe * (uint64_t)g.colsA, box_rows_a, 32, (uint64_t)g.lda * eb) &&
+           tma::make_2d(mapB, F, 4, g.B, (uint64_t)g.rowsB, fpe * (uint64_t)g.colsB, box_rows_b, 32, (uint64_t)g.ldb * eb);
+}
+// grid size: tiles of one product, times the batch
+int64_t mma_batch_grid(SgemmMmaParams &p, const GemmArgs &g)
+{
+    int64_t tiles = (int64_t)p.tiles_m * p.tiles_n;
+    p.tiles_per_batch = 0; p.plane_a = p.plane_b = 0; p.stride_c = 0;
+    if (g.batch > 1) {
+        p.tiles_per_batch = (int)tiles;
+        p.plane_a = g.strideA ? 1 : 0; p.plane_b = g.strideB ? 1 : 0;
+        p.stride_c = g.strideC;
+        tiles *= g.batch;
+    }
+    return tiles;
+}
+
 template <bool AK, bool BKM, typename TL>
 int launch_sgemm_mma(const GemmArgs &g)
 {
     constexpr int BM = TL::BM, BN = TL::BN;
     CUtensorMap mapA, mapB;
-    const CUtensorMapDataType F = CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
     // K-major operand: box = 32 (k) x BM|BN rows; MN-major operand: box = 32 (m|n) x 32 (k)
-    if (!tma::make_2d(&mapA, F, 4, g.A, (uint64_t)g.rowsA, (uint64_t)g.colsA, AK ? BM : 32, 32, (uint64_t)g.lda * 4) ||
-        !tma::make_2d(&mapB, F, 4, g.B, (uint64_t)g.rowsB, (uint64_t)g.colsB, BKM ? BN : 32, 32, (uint64_t)g.ldb * 4))
-        return cuda_fail(cudaErrorInvalidValue, "cuTensorMapEncodeTiled");
+    if (!mma_maps(&mapA, &mapB, g, 1, AK ? BM : 32, BKM ? BN : 32)) return cuda_fail(cudaErrorInvalidValue, "cuTensorMapEncodeTiled");
     static thread_local AttrOnce attr_once;
     if (attr_once.need()) {
         ACC_CUDA(cudaFuncSetAttribute(sgemm_mma_kernel<AK, BKM, TL>, cudaFuncAttributeMaxDynamicSharedMemorySize, TL::SMEM_BYTES));
@@ -502,7 +538,7 @@ int launch_sgemm_mma(const GemmArgs &g)
     p.refit = make_refit32(g);
     p.tiles_m = (int)((g.m + BM - 1) / BM);
     p.tiles_n = (int)((g.n + BN - 1) / BN);
-    const int64_t tiles = (int64_t)p.tiles_m * p.tiles_n;
+    const int64_t tiles = mma_batch_grid(p, g);
     if (tiles > 0x7fffffff) return ACCBLAS_ERR_SHAPE;
     sgemm_mma_kernel<AK, BKM, TL><<<(unsigned)tiles, TL::THREADS, TL::SMEM_BYTES, g.stream>>>(mapA, mapB, p);
     return check_launch("sgemm_mma_kernel");
@@ -513,11 +549,8 @@ int launch_cgemm_mma(const GemmArgs &g)
 {
     constexpr int BM = TL::BM, BN = TL::BN;
     CUtensorMap mapA, mapB;
-    const CUtensorMapDataType F = CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
     // maps are over floats (a complex row of c columns is 2c floats); boxes are 32 floats = 16 complex wide
-    if (!tma::make_2d(&mapA, F, 4, g.A, (uint64_t)g.rowsA, 2 * (uint64_t)g.colsA, AK ? BM : 16, 32, (uint64_t)g.lda * 8) ||
-        !tma::make_2d(&mapB, F, 4, g.B, (uint64_t)g.rowsB, 2 * (uint64_t)g.colsB, BKM ? BN : 16, 32, (uint64_t)g.ldb * 8))
-        return cuda_fail(cudaErrorInvalidValue, "cuTensorMapEncodeTiled");
+    if (!mma_maps(&mapA, &mapB, g, 2, AK ? BM : 16, BKM ? BN : 16)) return cuda_fail(cudaErrorInvalidValue, "cuTensorMapEncodeTiled");
     static thread_local AttrOnce attr_once;
     if (attr_once.need()) {
         ACC_CUDA(cudaFuncSetAttribute(cgemm_mma_kernel<AK, BKM, CA, CB, TL>, cudaFuncAttributeMaxDynamicSharedMemorySize, TL::SMEM_BYTES));
@@ -530,7 +563,7 @@ int launch_cgemm_mma(const GemmArgs &g)
     p.refit = make_refit32(g);
     p.tiles_m = (int)((g.m + BM - 1) / BM);
     p.tiles_n = (int)((g.n + BN - 1) / BN);
-    const int64_t tiles = (int64_t)p.tiles_m * p.tiles_n;
+    const int64_t tiles = mma_batch_grid(p, g);
     if (tiles > 0x7fffffff) return ACCBLAS_ERR_SHAPE;
     cgemm_mma_kernel<AK, BKM, CA, CB, TL><<<(unsigned)tiles, TL::THREADS, TL::SMEM_BYTES, g.stream>>>(mapA, mapB, p);
     return check_launch("cgemm_mma_kernel");
@@ -542,14 +575,14 @@ struct TileModel { int bm, bn; double eff, eff_alone; };
 constexpr TileModel kSTiles[3] = {{128, 64, 0.85, 0.85}, {64, 64, 1.00, 1.00}, {32, 32, 0.66, 0.48}};
 constexpr TileModel kCTiles[2] = {{64, 64, 1.00, 1.00}, {32, 32, 0.80, 0.50}};
 
-int pick(const TileModel *tm, int count, int forced, int64_t m, int64_t n)
+int pick(const TileModel *tm, int count, int forced, int64_t m, int64_t n, int64_t batch = 1)
 {
     if (forced >= 0 && forced < count) return forced;
     const int sms = sm_count();
     int best = 0;
     double best_cost = 0.0;
     for (int c = 0; c < count; ++c) {
-        const int64_t tiles = ((m + tm[c].bm - 1) / tm[c].bm) * ((n + tm[c].bn - 1) / tm[c].bn);
+        const int64_t tiles = ((m + tm[c].bm - 1) / tm[c].bm) * ((n + tm[c].bn - 1) / tm[c].bn) * batch;
         const double per_sm = (double)((tiles + sms - 1) / sms);
         const double cost = per_sm * tm[c].bm * tm[c].bn / (per_sm > 1.0 ? tm[c].eff : tm[c].eff_alone);
         if (c == 0 || cost < best_cost * 0.999) { best = c; best_cost = cost; }
@@ -560,7 +593,7 @@ int pick(const TileModel *tm, int count, int forced, int64_t m, int64_t n)
 template <bool AK, bool BKM>
 int sgemm_mma_tiles(const GemmArgs &g)
 {
-    switch (pick(kSTiles, 3, g_tuning[ACCBLAS_TUNE_SMMA_TILE], g.m, g.n)) {
+    switch (pick(kSTiles, 3, g_tuning[ACCBLAS_TUNE_SMMA_TILE], g.m, g.n, g.batch > 1 ? g.batch : 1)) {
     case 1:  return launch_sgemm_mma<AK, BKM, STile64>(g);
     case 2:  return launch_sgemm_mma<AK, BKM, STile32>(g);
     default: return launch_sgemm_mma<AK, BKM, STile128>(g);
@@ -571,7 +604,7 @@ template <bool AK, bool BKM, bool CA, bool CB>
 int cgemm_mma_tiles(const GemmArgs &g)
 {
     const int forced = g_tuning[ACCBLAS_TUNE_SMMA_TILE] < 0 ? -1 : (g_tuning[ACCBLAS_TUNE_SMMA_TILE] >= 2 ? 1 : 0);
-    return pick(kCTiles, 2, forced, g.m, g.n) == 1 ? launch_cgemm_mma<AK, BKM, CA, CB, CTile32>(g)
+    return pick(kCTiles, 2, forced, g.m, g.n, g.batch > 1 ? g.batch : 1) == 1 ? launch_cgemm_mma<AK, BKM, CA, CB, CTile32>(g)
                                                    : launch_cgemm_mma<AK, BKM, CA, CB, CTile64>(g);
 }
 

@@ -23,6 +23,7 @@ struct Refit32 {
     int64_t k;
     int ta, tb;              // 1: the operand is stored transposed w.r.t. op(.) (op != N)
     float sa, sb;            // -1: conjugate the operand (op == H on a complex type), else +1
+    int64_t batch_a, batch_b;  // FLOATS between the operands of consecutive products of a strided batch (0: none / shared)
 };
 
 inline Refit32 make_refit32(const GemmArgs &g)
@@ -35,6 +36,8 @@ inline Refit32 make_refit32(const GemmArgs &g)
     const bool cx = g.dtype == ACCBLAS_C32;
     f.sa = (cx && g.opA == ACCBLAS_OP_H) ? -1.f : 1.f;
     f.sb = (cx && g.opB == ACCBLAS_OP_H) ? -1.f : 1.f;
+    f.batch_a = g.batch > 1 ? g.strideA * (cx ? 2 : 1) : 0;
+    f.batch_b = g.batch > 1 ? g.strideB * (cx ? 2 : 1) : 0;
     return f;
 }
 inline Refit32 no_refit32() { Refit32 f{}; f.A = nullptr; return f; }
@@ -64,28 +67,28 @@ static __device__ __noinline__ float2 refit_dot_cplx(const float2 *a, const floa
 
 // Called by ALL 32 lanes of a converged warp, each with its own accumulator value and the (row, column) it belongs to
 // (`mine` = the lane holds a real output there).  Returns the value to use.
-__device__ __forceinline__ float refit_real(const Refit32 &f, float v, int64_t r, int64_t c, bool mine)
+__device__ __forceinline__ float refit_real(const Refit32 &f, float v, int64_t r, int64_t c, bool mine, int64_t batch = 0)
 {
     unsigned bad = __ballot_sync(0xffffffffu, mine && nonfinite32(v));
     while (bad) {
         const int src = __ffs(bad) - 1;
         bad &= bad - 1;
         const int64_t i = __shfl_sync(0xffffffffu, r, src), j = __shfl_sync(0xffffffffu, c, src);
-        const float s = refit_dot_real(f.A + (f.ta ? i : i * f.lda), f.B + (f.tb ? j * f.ldb : j),
+        const float s = refit_dot_real(f.A + batch * f.batch_a + (f.ta ? i : i * f.lda), f.B + batch * f.batch_b + (f.tb ? j * f.ldb : j),
                                        f.ta ? f.lda : 1, f.tb ? 1 : f.ldb, f.k);
         if ((int)(threadIdx.x & 31) == src) v = s;
     }
     return v;
 }
-__device__ __forceinline__ float2 refit_cplx(const Refit32 &f, float2 v, int64_t r, int64_t c, bool mine)
+__device__ __forceinline__ float2 refit_cplx(const Refit32 &f, float2 v, int64_t r, int64_t c, bool mine, int64_t batch = 0)
 {
     unsigned bad = __ballot_sync(0xffffffffu, mine && (nonfinite32(v.x) || nonfinite32(v.y)));
     while (bad) {
         const int src = __ffs(bad) - 1;
         bad &= bad - 1;
         const int64_t i = __shfl_sync(0xffffffffu, r, src), j = __shfl_sync(0xffffffffu, c, src);
-        const float2 s = refit_dot_cplx(reinterpret_cast<const float2 *>(f.A) + (f.ta ? i : i * f.lda),
-                                        reinterpret_cast<const float2 *>(f.B) + (f.tb ? j * f.ldb : j),
+        const float2 s = refit_dot_cplx(reinterpret_cast<const float2 *>(f.A + batch * f.batch_a) + (f.ta ? i : i * f.lda),
+                                        reinterpret_cast<const float2 *>(f.B + batch * f.batch_b) + (f.tb ? j * f.ldb : j),
                                         f.ta ? f.lda : 1, f.tb ? 1 : f.ldb, f.k, f.sa, f.sb);
         if ((int)(threadIdx.x & 31) == src) v = s;
     }

@@ -70,6 +70,12 @@ __device__ __forceinline__ void load_3d(uint32_t dst, const void *tmap, uint32_t
         "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
         ::"r"(dst), "l"(tmap), "r"(bar), "r"(c0), "r"(c1), "r"(c2) : "memory");
 }
+// box (c0, c1) of plane `plane` of a strided batch of matrices (make_2d_batched), or of a single matrix (plane < 0,
+// make_2d): what the batched launches of the gemm families use for every operand box
+__device__ __forceinline__ void load_box(uint32_t dst, const void *tmap, uint32_t bar, int c0, int c1, int plane) {
+    if (plane < 0) load_2d(dst, tmap, bar, c0, c1);
+    else load_3d(dst, tmap, bar, c0, c1, plane);
+}
 
 // L2 eviction policies for TMA loads.  In a grouped rasterisation the row panels of A are re-read by
 // every wave of the group while a panel of B is used by one wave and is then dead: keeping A
@@ -125,6 +131,25 @@ inline bool make_2d(CUtensorMap *map, CUtensorMapDataType dt, size_t esize, cons
     cuuint32_t box[2] = {box_cols, box_rows};
     cuuint32_t estr[2] = {1, 1};
     return fn(map, dt, 2, const_cast<void *>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+              CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+// `planes` row-major rows x cols matrices, plane b starting plane_stride_bytes * b after `base` (a strided batch), as
+// a 3-D tensor (dim2 = plane).  Box = box_cols x box_rows x 1: lands exactly like the 2-D box of make_2d, zero fill
+// outside EACH matrix.  plane_stride_bytes must be a non-zero multiple of 16 (a batch that re-uses one operand for every
+// product passes planes = 1 and always loads plane 0).
+inline bool make_2d_batched(CUtensorMap *map, CUtensorMapDataType dt, size_t esize, const void *base, uint64_t rows,
+                            uint64_t cols, uint32_t box_rows, uint32_t box_cols, uint64_t pitch_bytes, uint64_t planes,
+                            uint64_t plane_stride_bytes)
+{
+    EncodeTiledFn fn = encode_fn();
+    if (!fn || planes == 0 || plane_stride_bytes == 0 || (plane_stride_bytes & 15u)) return false;
+    cuuint64_t dims[3] = {cols, rows, planes};
+    cuuint64_t strides[2] = {pitch_bytes ? pitch_bytes : cols * esize, plane_stride_bytes};
+    cuuint32_t box[3] = {box_cols, box_rows, 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    return fn(map, dt, 3, const_cast<void *>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
               CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }

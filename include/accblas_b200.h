@@ -111,8 +111,14 @@ int accblas_gemm_ex(accblas_stream_t stream, int dtype, int opA, int opB,
 /* `batch` independent products with identical shapes and flags: operand b of the batch lives at
  * base + b * stride (strides in ELEMENTS; strideA / strideB = 0 re-uses one operand for every product;
  * strideC >= m * n).  The reference has no batched operator (Accelerate would express it as a fold over a
- * rank-3 array and lose the foreign hook); this is SURVEY.md section 8(f) rank 3.  Tiny products run as one
- * launch with the batch on the grid, larger ones are enqueued back to back on `stream`. */
+ * rank-3 array and lose the foreign hook); this is SURVEY.md section 8(f) rank 3.
+ *   - tiny products (< 48^3): one SIMT launch, the batch on gridDim.z;
+ *   - products of the warp-level tensor families (f64 / c64 on DMMA, f32 / c32 on mma.sync: everything that does not fill
+ *     the GPU by itself): ONE launch -- the batch is folded into the grid (blockIdx -> product, tile) and into a third
+ *     dimension of the TMA tensor maps, so the tiles of all products share the waves and the tile choice sees
+ *     tiles x batch.  Needs es * stride % 16 == 0 for the three strides (TMA plane stride, vector stores);
+ *   - anything else (products large enough for the tcgen05 / 3M / persistent kernels, odd strides): enqueued back to
+ *     back on `stream`. */
 int accblas_gemm_strided_batched(accblas_stream_t stream, int dtype, int opA, int opB,
                                  int64_t rowsA, int64_t colsA, int64_t rowsB, int64_t colsB,
                                  const void *alpha_host, const void *A, int64_t strideA,
