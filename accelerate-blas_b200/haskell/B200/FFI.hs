@@ -17,6 +17,11 @@ module Data.Array.Accelerate.Numeric.LinearAlgebra.LLVM.PTX.B200.FFI (
   c_accblas_gemm_alpha_dev, c_accblas_gemv_alpha_dev,
   c_accblas_sdot, c_accblas_asum, c_accblas_amax, c_accblas_amin,
   c_accblas_gemm_strided_batched, c_accblas_set_tuning,
+  c_accblas_gemm_ex, c_accblas_trim_workspace, c_accblas_last_cuda_error_r,
+  -- multi-GPU (one process per device)
+  Comm, Plan, c_accblas_mg_unique_id, c_accblas_mg_init, c_accblas_mg_finalize, c_accblas_mg_row_panel,
+  c_accblas_mg_gemm, c_accblas_mg_gemm_plan, c_accblas_mg_gemm_run, c_accblas_mg_gemm_plan_destroy,
+  c_accblas_mg_gemv, c_accblas_mg_dot,
 
 ) where
 
@@ -26,7 +31,7 @@ import Control.Exception                                            ( throwIO, E
 import Control.Monad                                                ( when )
 import Data.Int                                                     ( Int64 )
 import Foreign.C.String                                             ( CString, peekCString )
-import Foreign.C.Types                                              ( CInt(..) )
+import Foreign.C.Types                                              ( CInt(..), CSize(..) )
 import Foreign.Ptr                                                  ( Ptr )
 
 -- | accblas_dtype_t; one constructor per NumericR constructor (Type.hs:32-36)
@@ -99,6 +104,70 @@ foreign import ccall unsafe "accblas_gemm_strided_batched"
                                  -> Int64 -> Int64 -> Int64 -> Int64
                                  -> Ptr () -> Ptr () -> Int64 -> Ptr () -> Int64    -- alpha(host) A strideA B strideB
                                  -> Ptr () -> Int64 -> Int64 -> IO Status           -- C strideC batch
+
+-- the extended product D = alpha * op(A) * op(B) + beta * Cin on windows (row pitches in elements); not used by the
+-- reference's hooks (beta = 0, LLVM/PTX/Level3.hs:90) but by a fused `zipWith (+) c (a <> b)` and by the multi-GPU path
+foreign import ccall unsafe "accblas_gemm_ex"
+  c_accblas_gemm_ex :: Ptr () -> CInt -> CInt -> CInt
+                    -> Int64 -> Int64 -> Int64 -> Int64
+                    -> Ptr () -> Ptr () -> Int64 -> Ptr () -> Int64       -- alpha(host) A lda B ldb
+                    -> Ptr () -> Ptr () -> Int64 -> Ptr () -> Int64       -- beta(host) Cin ldcin C ldc
+                    -> IO Status
+
+-- multi-GPU: one OS process (one PTX context) per device of an NVLink box.  The 128 bootstrap bytes of rank 0 travel
+-- to the other ranks by whatever transport the host runtime has (a file, a socket, MPI).
+type Comm = Ptr ()
+type Plan = Ptr ()
+
+foreign import ccall unsafe "accblas_mg_unique_id"
+  c_accblas_mg_unique_id :: Ptr () -> IO Status                           -- 128 bytes out (rank 0)
+
+foreign import ccall safe "accblas_mg_init"                               -- collective, blocks: `safe`
+  c_accblas_mg_init :: Ptr Comm -> CInt -> CInt -> Ptr () -> IO Status    -- comm(out) rank world id
+
+foreign import ccall safe "accblas_mg_finalize"
+  c_accblas_mg_finalize :: Comm -> IO Status
+
+foreign import ccall unsafe "accblas_mg_row_panel"
+  c_accblas_mg_row_panel :: Int64 -> CInt -> CInt -> Ptr Int64 -> Ptr Int64 -> IO Status   -- m world rank start(out) rows(out)
+
+-- C = alpha * op(A) * op(B): operands and result on `root`, rows of op(A) / C split over the ranks
+foreign import ccall safe "accblas_mg_gemm"
+  c_accblas_mg_gemm :: Comm -> Ptr () -> CInt -> CInt -> CInt
+                    -> Int64 -> Int64 -> Int64 -> Int64
+                    -> Ptr () -> Ptr () -> Ptr () -> Ptr () -> CInt       -- alpha(host) A B C root
+                    -> IO Status
+
+foreign import ccall safe "accblas_mg_gemm_plan"
+  c_accblas_mg_gemm_plan :: Comm -> CInt -> CInt -> CInt
+                         -> Int64 -> Int64 -> Int64 -> Int64
+                         -> Ptr () -> Ptr () -> Ptr () -> CInt -> Ptr Plan   -- A B C root plan(out)
+                         -> IO Status
+
+foreign import ccall unsafe "accblas_mg_gemm_run"
+  c_accblas_mg_gemm_run :: Plan -> Ptr () -> Ptr () -> IO Status          -- plan stream alpha(host)
+
+foreign import ccall safe "accblas_mg_gemm_plan_destroy"
+  c_accblas_mg_gemm_plan_destroy :: Plan -> IO Status
+
+-- y = alpha * op(A) * x on row-sharded A; every rank receives the whole y
+foreign import ccall unsafe "accblas_mg_gemv"
+  c_accblas_mg_gemv :: Comm -> Ptr () -> CInt -> CInt
+                    -> Int64 -> Int64 -> Ptr ()                           -- rows_local colsA alpha(host)
+                    -> Ptr () -> Ptr () -> Int64 -> Ptr ()                -- A_local x |x| y_full
+                    -> IO Status
+
+foreign import ccall unsafe "accblas_mg_dot"
+  c_accblas_mg_dot :: Comm -> Ptr () -> CInt -> CInt -> Int64             -- comm stream dtype conj_x n_local
+                   -> Ptr () -> Ptr () -> Ptr () -> IO Status             -- x_local y_local out(device)
+
+-- the library's private scratch pool (INTEGRATION.md section 4)
+foreign import ccall unsafe "accblas_trim_workspace"
+  c_accblas_trim_workspace :: IO Status
+
+-- most recent CUDA failure of ANY thread, copied into the caller's buffer (FFI calls may migrate between OS threads)
+foreign import ccall unsafe "accblas_last_cuda_error_r"
+  c_accblas_last_cuda_error_r :: CString -> CSize -> IO CSize
 
 -- per-thread kernel-choice knobs (accblas_tune_t); e.g. `c_accblas_set_tuning 7 0 >> c_accblas_set_tuning 9 0`
 -- pins complex products to 4M.  Haskell FFI calls may hop between OS threads: prefer ACCBLAS_TUNE in the
