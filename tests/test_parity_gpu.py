@@ -177,17 +177,19 @@ def test_gemm_mma_tf32_family(dt, cuda):
 
 @pytest.mark.parametrize("dt", [O.F32, O.C32], ids=ids)
 def test_gemm_every_tc_tile(dt, cuda):
-    """The tcgen05 3xTF32 family forced onto each CTA tile (128 x 256 / 128 x 128 / 128 x 64), every op pair,
-    ragged extents in m, n and k (tile edges, odd pitches), a k long enough for many promotion chunks."""
+    """The tcgen05 3xTF32 family forced onto each tile (128 x 256 / 128 x 128 / 128 x 64 on one CTA, 256 x 256 on a CTA
+    pair), every op pair, ragged extents in m, n and k (tile edges, odd pitches, an odd count of 128-row blocks for the
+    pair), a k long enough for many promotion chunks.  Complex types cover the 4M embedding here; the 3M planes on the pair
+    tile are covered by test_round2_gpu.py (BASELINE-size cgemm) and test_gemm_c3m_pair below."""
     import accblas_b200 as ab
     rng = np.random.default_rng(2900 + dt)
     try:
         ab.set_tuning(2, 2)                       # ACCBLAS_TUNE_SGEMM_FAMILY = tcgen05
-        for tile in range(3):
+        for tile in range(4):                     # 3 = the 256 x 256 CTA-pair tile (cta_group::2, round 2)
             ab.set_tuning(8, tile)                # ACCBLAS_TUNE_TC_TILE
             for oa in OPN:
                 for ob in OPN:
-                    for (m, n, k) in [(300, 260, 330), (129, 193, 1500)]:
+                    for (m, n, k) in [(300, 260, 330), (129, 193, 1500)] + ([(257, 520, 200), (640, 300, 96)] if tile == 3 else []):
                         al, A, B = gemm_inputs(rng, dt, oa, ob, m, n, k)
                         assert "tcgen05" in ab.kernel_name(dt, oa, ob, A.shape, B.shape)
                         C = host(ab.gemm(al, oa, dev(A, cuda), ob, dev(B, cuda)))
@@ -196,6 +198,26 @@ def test_gemm_every_tc_tile(dt, cuda):
     finally:
         ab.set_tuning(2, -1)
         ab.set_tuning(8, -1)
+
+
+def test_gemm_c3m_pair(cuda):
+    """cgemm 3M (three real products as stacked planes of ONE launch) on the CTA-pair tile: plane row offsets that are
+    not multiples of 256, ragged extents; against the oracle."""
+    import accblas_b200 as ab
+    rng = np.random.default_rng(3131)
+    try:
+        ab.set_tuning(2, 2)
+        ab.set_tuning(8, 3)
+        ab.set_tuning(9, 1)                       # ACCBLAS_TUNE_CGEMM_3M
+        for (m, n, k) in [(384, 260, 330), (1100, 1000, 520), (257, 300, 1000)]:
+            for oa, ob in [("N", "N"), ("H", "N"), ("T", "H")]:
+                al, A, B = gemm_inputs(rng, O.C32, oa, ob, m, n, k)
+                assert "3m" in ab.kernel_name(O.C32, oa, ob, A.shape, B.shape)
+                C = host(ab.gemm(al, oa, dev(A, cuda), ob, dev(B, cuda)))
+                err = O.gemm_error_units(C, O.gemm(al, oa, A, ob, B, wide=True), A, B, k, al)
+                assert err <= TOL_UNITS_TF32X3, (oa, ob, m, n, k, err)
+    finally:
+        ab.set_tuning(2, -1); ab.set_tuning(8, -1); ab.set_tuning(9, -1)
 
 
 @pytest.mark.parametrize("dt", DTYPES, ids=ids)
