@@ -600,6 +600,17 @@ int accblas_dot(accblas_stream_t stream, int dtype, int conj_x, int64_t n, const
     return dot_dispatch(static_cast<cudaStream_t>(stream), dtype, conj_x, n, x, y, out_dev);
 }
 
+int accblas_dot_compensated(accblas_stream_t stream, int dtype, int conj_x, int64_t n, const void *x, const void *y,
+                            void *out_dev)
+{
+    if (bad_dtype(dtype)) return ACCBLAS_ERR_DTYPE;
+    if (n < 0) return ACCBLAS_ERR_SHAPE;
+    if (!out_dev) return ACCBLAS_ERR_NULL;
+    if (n > 0 && (!x || !y)) return ACCBLAS_ERR_NULL;
+    ACC_TRY(device_check());
+    return dot_dispatch(static_cast<cudaStream_t>(stream), dtype, conj_x, n, x, y, out_dev, true);
+}
+
 int accblas_sdot(accblas_stream_t stream, int dtype, int64_t n, const void *z_host, const void *x,
                  const void *y, void *out_dev)
 {

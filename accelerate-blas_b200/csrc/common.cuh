@@ -242,7 +242,7 @@ int  sgemm_mma(const GemmArgs &g);
 int gemv_dispatch(cudaStream_t s, int dtype, int opA, int64_t rowsA, int64_t colsA,
                   const void *alpha, bool alpha_dev, const void *A, const void *x, void *y);   // gemv.cu
 int dot_dispatch(cudaStream_t s, int dtype, int conj_x, int64_t n,
-                 const void *x, const void *y, void *out);                            // dot.cu
+                 const void *x, const void *y, void *out, bool compensated = false);  // dot.cu
 
 int sdot_dispatch(cudaStream_t s, int dtype, int64_t n, const void *z_host,
                   const void *x, const void *y, void *out);                           // level1.cu

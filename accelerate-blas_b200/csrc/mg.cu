@@ -25,6 +25,7 @@
 // cudart-only link line, and single-GPU users never touch NCCL.  The bootstrap id is plain bytes the caller ships
 // with any transport (torch.distributed, MPI, a pipe), like the peer handle of accblas_peer_*.
 #include "common.cuh"
+#include "mg_exchange.cuh"
 #include <dlfcn.h>
 #include <algorithm>
 #include <cstdio>
@@ -80,10 +81,6 @@ int nccl_fail(int rc, const char *where)
 // ------------------------------------------------------------------------------------------------------------
 // communicator
 // ------------------------------------------------------------------------------------------------------------
-constexpr int MG_MAX_RANKS = 16;
-constexpr size_t XSLOT = 1u << 20;                 // bytes one rank can deposit per collective (gemv T/H partial y)
-constexpr size_t XFLAGS = 4096;                    // flag block per parity: one 64-byte line per source rank
-
 struct Comm {
     int rank = 0, world = 1, dev = 0;
     NcclComm nccl = nullptr;
@@ -94,29 +91,14 @@ struct Comm {
     char *peer_x[MG_MAX_RANKS] = {nullptr};        // peer_x[r]: rank r's buffer as mapped here (own buffer for r == rank)
     size_t xparity = 0;                            // bytes per parity
     uint32_t seq = 0;                              // exchange collectives issued so far
+    // sharded dot (one launch, dot.cu): [arrival counter | per-CTA partials]; the counter returns to zero by itself
+    char *dot_scratch = nullptr;
 };
-
-struct PeerPtrs { char *p[MG_MAX_RANKS]; };
+constexpr int MG_DOT_GRID = 1024;                  // CTAs the fused dot may launch (partials: 32 bytes each)
 
 // ------------------------------------------------------------------------------------------------------------
-// exchange kernels
+// exchange kernels (protocol and flag helpers: mg_exchange.cuh)
 // ------------------------------------------------------------------------------------------------------------
-__device__ __forceinline__ void st_release_sys(uint32_t *p, uint32_t v) {
-    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t *p) {
-    uint32_t v;
-    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ void wait_flag(const uint32_t *p, uint32_t seq) {
-    unsigned ns = 20;
-    while (ld_acquire_sys(p) != seq) {             // a collective: waits for the peer like any other would
-        __nanosleep(ns);
-        if (ns < 1000) ns *= 2;
-    }
-}
-
 // All-reduce of ONE element (dot): thread r deposits this rank's value in rank r's buffer and raises the flag;
 // then waits for rank r's deposit here; thread 0 adds the deposits in rank order.
 template <typename T>
@@ -258,6 +240,8 @@ int accblas_mg_init(accblas_mg_comm_t *comm_out, int rank, int world, const void
     ACC_CUDA(cudaStreamCreateWithPriority(&c->pull, cudaStreamNonBlocking, hi));
     ACC_CUDA(cudaMalloc(reinterpret_cast<void **>(&c->token), 64));
     ACC_CUDA(cudaMemset(c->token, 0, 64));
+    ACC_CUDA(cudaMalloc(reinterpret_cast<void **>(&c->dot_scratch), 64 + 32 * (size_t)MG_DOT_GRID));
+    ACC_CUDA(cudaMemset(c->dot_scratch, 0, 64 + 32 * (size_t)MG_DOT_GRID));
     // exchange buffer: cudaMalloc (IPC needs a plain allocation), zeroed, handle all-gathered, peers mapped
     c->xparity = XFLAGS + (size_t)world * XSLOT;
     ACC_CUDA(cudaMalloc(reinterpret_cast<void **>(&c->xbuf), 2 * c->xparity));
@@ -297,6 +281,7 @@ int accblas_mg_finalize(accblas_mg_comm_t comm)
     if (c->nccl) g_nccl.CommDestroy(c->nccl);
     if (c->xbuf) cudaFree(c->xbuf);
     if (c->token) cudaFree(c->token);
+    if (c->dot_scratch) cudaFree(c->dot_scratch);
     if (c->pull) cudaStreamDestroy(c->pull);
     delete c;
     return ACCBLAS_OK;
@@ -569,7 +554,21 @@ int accblas_mg_dot(accblas_mg_comm_t comm, accblas_stream_t stream, int dtype, i
     Comm *c = reinterpret_cast<Comm *>(comm);
     if (!c || !out_dev) return ACCBLAS_ERR_NULL;
     if (dtype < ACCBLAS_F32 || dtype > ACCBLAS_C64) return ACCBLAS_ERR_DTYPE;
+    if (n_local < 0) return ACCBLAS_ERR_SHAPE;
+    if (n_local > 0 && (!x_local || !y_local)) return ACCBLAS_ERR_NULL;
     cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if (g_tuning[ACCBLAS_TUNE_MG_DOT_FUSED] != 0) {
+        // ONE launch: the dot kernel's last CTA sums the partials and performs the exchange (dot.cu: dot_mg_kernel)
+        DotExchange ex;
+        ex.peers = peer_ptrs(c);
+        ex.rank = c->rank; ex.world = c->world;
+        ex.seq = ++c->seq;
+        ex.parity_off = (ex.seq & 1u) * c->xparity;
+        ex.counter = reinterpret_cast<unsigned *>(c->dot_scratch);
+        ex.partials = c->dot_scratch + 64;
+        return dot_mg_dispatch(s, dtype, conj_x, n_local, x_local, y_local, out_dev, ex, MG_DOT_GRID);
+    }
+    // round-2a path, kept for the A/B measurement: local dot (two launches) + one exchange kernel
     char *mine = nullptr;
     ACC_CUDA(scratch_alloc(reinterpret_cast<void **>(&mine), 16, s));
     int st = accblas_dot(stream, dtype, conj_x, n_local, x_local, y_local, mine);

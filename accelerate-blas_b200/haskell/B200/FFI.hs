@@ -13,7 +13,7 @@
 module Data.Array.Accelerate.Numeric.LinearAlgebra.LLVM.PTX.B200.FFI (
 
   DType(..), dtypeCode, opCode, Status, checkStatus,
-  c_accblas_gemm, c_accblas_gemv, c_accblas_dot,
+  c_accblas_gemm, c_accblas_gemv, c_accblas_dot, c_accblas_dot_compensated,
   c_accblas_gemm_alpha_dev, c_accblas_gemv_alpha_dev,
   c_accblas_sdot, c_accblas_asum, c_accblas_amax, c_accblas_amin,
   c_accblas_gemm_strided_batched, c_accblas_set_tuning,
@@ -69,6 +69,12 @@ foreign import ccall unsafe "accblas_dot"
   c_accblas_dot  :: Ptr () -> CInt -> CInt -> Int64         -- stream, dtype, conj_x, n
                  -> Ptr () -> Ptr () -> Ptr ()              -- x y out(device)
                  -> IO Status
+
+-- the same product with compensated arithmetic (Dot2 + the KBN combine of Numeric/Sum.hs:119-125)
+foreign import ccall unsafe "accblas_dot_compensated"
+  c_accblas_dot_compensated :: Ptr () -> CInt -> CInt -> Int64
+                            -> Ptr () -> Ptr () -> Ptr ()
+                            -> IO Status
 
 -- alpha as the device Scalar it already is (BLAS/Level3.hs:64): no indexRemote, no stream sync
 foreign import ccall unsafe "accblas_gemm_alpha_dev"

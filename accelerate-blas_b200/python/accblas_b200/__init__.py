@@ -34,7 +34,7 @@ import numpy as np
 from . import _ffi
 from ._ffi import AccblasError, lib  # noqa: F401
 
-__all__ = ["N", "T", "H", "gemm", "gemm_batched", "gemv", "dotu", "dotc", "sdot", "asum", "amax", "amin", "mXm", "mXv", "vXm", "dot", "outer",
+__all__ = ["N", "T", "H", "gemm", "gemm_batched", "gemv", "dotu", "dotc", "dot_compensated", "sdot", "asum", "amax", "amin", "mXm", "mXv", "vXm", "dot", "outer",
            "AccblasError", "kernel_name", "launch_count", "set_gemm_path", "set_tuning", "version"]
 
 # Transpose -- Type.hs:78-90
@@ -307,6 +307,26 @@ def dotc(x, y):
     return _dot(x, y, True)
 
 
+def dot_compensated(x, y, conj: bool = False):
+    """dotu / dotc (``conj``) with compensated arithmetic: exact product splitting, TwoSum accumulation and the
+    reference's Kahan-Babuska-Neumaier combine (Numeric/Sum.hs:119-125) between partial sums -- as accurate as a dot
+    evaluated in twice double precision and rounded once.  Device tensors only (result: 0-d device tensor)."""
+    code = _code(x)
+    if conj and code not in (C32, C64):
+        raise TypeError("dot_compensated: conj needs Numeric (Complex e) (BLAS/Level1.hs:85)")
+    if not _is_torch(x):
+        raise TypeError("dot_compensated: device tensors only")
+    torch = _torch()
+    x = _dev_operand(x, code, 1, "dot_compensated: x")
+    y = _dev_operand(y, code, 1, "dot_compensated: y")
+    n = min(x.shape[0], y.shape[0])
+    with torch.cuda.device(x.device):
+        out = torch.empty((), dtype=x.dtype, device=x.device)
+        st = lib().accblas_dot_compensated(_stream(x), code, int(conj), n, _ptr(x), _ptr(y), _ptr(out))
+    _ffi.check(st, "accblas_dot_compensated")
+    return out
+
+
 def sdot(z, x, y):
     """``z + sum_i x_i * y_i`` with double-precision products and accumulation, rounded once to
     the element type -- sdot, BLAS/Level1.hs:44-62."""
@@ -437,6 +457,8 @@ TUNE_SNAKE_K = 10       # f64 gemm: 0 = every tile walks K forwards
 TUNE_STREAMK = 11       # f64 gemm: 0 = never the persistent kernel, 1 = whole-tile rounds + stream-K tail, 2 = pure stream-K
 TUNE_RELEASE = 12       # f64/c64 gemm stage release: 0 = fenced everywhere, 2 = delayed by one K-block everywhere
 TUNE_MG_SELF_PEER = 14  # accblas_mg_gemm_plan: 1 = the root runs the peers' pull / K-chunk pipeline itself (test hook)
+TUNE_DOT_SHAPE = 15      # dot streaming pass CTA shape (see include/accblas_b200.h)
+TUNE_MG_DOT_FUSED = 16   # accblas_mg_dot: 0 = three launches (local dot + exchange kernel), default one fused launch
 TUNE_MN_ONEBOX = 13     # f64 gemm: 0 = MN-major operand panels as 16 x 16 boxes, default one 3-D box per stage
 TUNE_ZGEMM_3M = 7       # 0: complex-double gemm always 4M in registers, 1: 3M whenever possible, -1: cost model
 

@@ -164,6 +164,14 @@ int accblas_gemv(accblas_stream_t stream, int dtype, int opA,
  * ---------------------------------------------------------------------------------- */
 int accblas_dot(accblas_stream_t stream, int dtype, int conj_x, int64_t n,
                 const void *x, const void *y, void *out_dev);
+/* The same product with COMPENSATED arithmetic (the reference's Numeric/Sum.hs): every product is
+ * split exactly into (p, e) with one FMA, running sums are TwoSums whose rounding errors are kept beside them, and
+ * partial sums of threads, warps and CTAs are merged with the reference's Kahan-Babuska-Neumaier combine (`kbnAdd`,
+ * Numeric/Sum.hs:119-125); out = s + c rounded once.  As accurate as a dot evaluated in twice the working precision:
+ * |out - exact| <= eps |exact| + O(n^2 eps^2) sum_i |x_i y_i| with eps of DOUBLE for every dtype (float operands are
+ * multiplied exactly and summed in double).  Same HBM traffic as accblas_dot, same fixed summation tree. */
+int accblas_dot_compensated(accblas_stream_t stream, int dtype, int conj_x, int64_t n,
+                            const void *x, const void *y, void *out_dev);
 
 /* ------------------------------------------------------------------------------------
  * The other Level-1 reductions of the reference (BLAS/Level1.hs).  Like dot they are plain
@@ -352,7 +360,12 @@ typedef enum {
                                        3-D box per stage when the extent is a multiple of 16                                       */
     ACCBLAS_TUNE_MG_SELF_PEER = 14, /* accblas_mg_gemm_plan: 1 = the root also runs the peers' pull / K-chunk pipeline on its own
                                        arrays (test hook: exercises that path on a one-GPU box)                                    */
-    ACCBLAS_TUNE_COUNT = 15
+    ACCBLAS_TUNE_DOT_SHAPE = 15,    /* dot: CTA shape of the streaming pass, threads x 16-byte loads per operand per thread x CTAs
+                                       per SM: 0 = 512x4x2 (default), 1 = 256x4x4, 2 = 256x8x2, 4 = 512x8x1,
+                                       5 = 1024x4x1 (profiles/r02_dot_shapes.jsonl)                                                */
+    ACCBLAS_TUNE_MG_DOT_FUSED = 16, /* accblas_mg_dot: 0 = local dot (two launches) + one exchange kernel, default: ONE launch whose
+                                       last CTA sums the partials and runs the scalar all-reduce over the peers' buffers           */
+    ACCBLAS_TUNE_COUNT = 17
 } accblas_tune_t;
 /* Process-wide defaults for threads that never call this: environment variable
  * ACCBLAS_TUNE="knob=value,knob=value" (read once). */

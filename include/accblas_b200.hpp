@@ -182,6 +182,14 @@ template <class T> Scalar<T> dotc(const Vector<T> &x, const Vector<T> &y, cudaSt
     check(accblas_dot(s, numeric_traits<T>::dtype, 1, x.size() < y.size() ? x.size() : y.size(), x.data(), y.data(), d.data()), "dotc");
     return d;
 }
+// compensated dotu / dotc: exact product splitting + the reference's KBN combine (Numeric/Sum.hs:119-125)
+template <class T> Scalar<T> dot_compensated(const Vector<T> &x, const Vector<T> &y, bool conj = false, cudaStream_t s = nullptr)
+{
+    Scalar<T> d(s);
+    check(accblas_dot_compensated(s, numeric_traits<T>::dtype, conj ? 1 : 0, x.size() < y.size() ? x.size() : y.size(), x.data(),
+                                  y.data(), d.data()), "dot_compensated");
+    return d;
+}
 // sdot z x y = z + sum x_i y_i accumulated in double precision                      (BLAS/Level1.hs:44-62)
 template <class T> Scalar<T> sdot(T z, const Vector<T> &x, const Vector<T> &y, cudaStream_t s = nullptr)
 {

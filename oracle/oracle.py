@@ -115,6 +115,44 @@ def dot(x: np.ndarray, y: np.ndarray, conj: bool = False, wide: bool = True):
     return out[0]
 
 
+def kbn_sum(xs):
+    """`sum kbn xs` -- Numeric/Sum.hs:81-84: `map from . fold add zero . map into` with the Kahan-Babuska-Neumaier
+    state `KBN s c`, `into x = KBN x 0`, `from (KBN s c) = s + c` (:128-132) and `add = kbnAdd` (:119-125):
+        s' = s1 + s2;  c' = c1 + c2 + (if |s1| >= |s2| then (s1 - s') + s2 else (s2 - s') + s1)
+    Restated as the sequential left fold in the element type (pure Python loop: small cases only)."""
+    xs = np.asarray(xs)
+    ty = xs.dtype.type
+    s, c = ty(0), ty(0)
+    for v in xs:
+        s2, c2 = ty(v), ty(0)
+        sn = ty(s + s2)
+        lost = ty(ty(s - sn) + s2) if abs(s) >= abs(s2) else ty(ty(s2 - sn) + s)
+        c = ty(ty(c + c2) + lost)
+        s = sn
+    return ty(s + c)
+
+
+def dot_exact(x: np.ndarray, y: np.ndarray, conj: bool = False):
+    """The dot product in exact rational arithmetic (fractions.Fraction), rounded once to double / complex double:
+    the truth the compensated dot (accblas_dot_compensated) is measured against.  O(n) big-integer work: n <~ 10^5."""
+    from fractions import Fraction as Fr
+    x = np.asarray(x)
+    y = np.asarray(y)
+    n = min(x.shape[0], y.shape[0])
+    if np.iscomplexobj(x):
+        sg = -1 if conj else 1
+        re, im = Fr(0), Fr(0)
+        for a, b in zip(x[:n], y[:n]):
+            ar, ai, br, bi = Fr(float(a.real)), sg * Fr(float(a.imag)), Fr(float(b.real)), Fr(float(b.imag))
+            re += ar * br - ai * bi
+            im += ar * bi + ai * br
+        return complex(float(re), float(im))
+    acc = Fr(0)
+    for a, b in zip(x[:n], y[:n]):
+        acc += Fr(float(a)) * Fr(float(b))
+    return float(acc)
+
+
 def sdot(z, x: np.ndarray, y: np.ndarray, wide: bool = True):
     """sdot z xs ys -- BLAS/Level1.hs:44-62: z + sum x_i y_i in double precision, rounded once."""
     x = np.ascontiguousarray(x)

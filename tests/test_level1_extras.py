@@ -168,3 +168,83 @@ def test_gpu_outer_product_rank1(dt, cuda):
             got = ab.gemm(al, oa, dev(A, cuda), ob, dev(B, cuda)).cpu().numpy()
             ref = O.gemm(al, oa, A, ob, B, wide=True)
             assert O.gemm_error_units(got, ref, A, B, 1, al) <= 1.0, (oa, ob, m, n)
+
+
+# ------------------------------------------------------------------------------- compensated dot
+# The reference's only known-answer vector for its compensated sums (Numeric/Sum.hs:72-80):
+#   sum kbn [1.0, 1.0e100, 1.0, -1.0e100] == 2.0      (Prelude.sum gives 0.0)
+KBN_HADDOCK = ([1.0, 1.0e100, 1.0, -1.0e100], 2.0)
+
+
+def illcond(rng, n, dt, spread):
+    """x . y with heavy cancellation: the second half undoes the first up to a small perturbation, exponents spread
+    over 2^+-spread.  Returns operands whose exact dot is ~1e-10 .. 1e-6 of sum |x_i y_i|."""
+    h = n // 2
+    base = np.float32 if dt in (O.F32, O.C32) else np.float64
+
+    def part(shape):
+        return (rng.uniform(-1, 1, shape) * 2.0 ** rng.integers(-spread, spread, shape)).astype(base)
+    if dt in (O.C32, O.C64):
+        a = part(h) + 1j * part(h)
+        b = part(h) + 1j * part(h)
+    else:
+        a, b = part(h), part(h)
+    a = a.astype(O.NP_DTYPE[dt])
+    b = b.astype(O.NP_DTYPE[dt])
+    x = np.concatenate([a, a])
+    y = np.concatenate([b, -b])
+    y[h:] += (np.abs(b) * 1e-6).astype(y.dtype) * (rng.uniform(-1, 1, h)).astype(base)
+    p = rng.permutation(2 * h)
+    return np.ascontiguousarray(x[p]), np.ascontiguousarray(y[p])
+
+
+def test_oracle_kbn_restatement_and_exact_dot():
+    xs, want = KBN_HADDOCK
+    assert O.kbn_sum(np.array(xs, dtype=np.float64)) == want          # the reference's own example
+    assert float(np.sum(np.array(xs))) != want                        # ... which a plain sum misses
+    rng = np.random.default_rng(8300)
+    x, y = illcond(rng, 2000, O.F64, 30)
+    import math
+    assert abs(O.dot_exact(x, y)) <= 1e-3 * float(np.sum(np.abs(x) * np.abs(y)))      # the generator does cancel
+    # products of floats are exact in double, so fsum of them is the exact dot rounded once: a second route to dot_exact
+    xf, yf = illcond(rng, 2000, O.F32, 10)
+    assert O.dot_exact(xf, yf) == math.fsum(float(a) * float(b) for a, b in zip(xf, yf))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dt", DTYPES, ids=ids)
+def test_gpu_dot_compensated(dt, cuda):
+    import accblas_b200 as ab
+    cplx = dt in (O.C32, O.C64)
+    # the reference's haddock vector, as a dot with ones (element types that can hold 1e100)
+    if dt in (O.F64, O.C64):
+        xs, want = KBN_HADDOCK
+        x = np.array(xs, dtype=O.NP_DTYPE[dt])
+        one = np.ones(4, dtype=O.NP_DTYPE[dt])
+        assert complex(ab.dot_compensated(dev(x, cuda), dev(one, cuda)).item()) == complex(want)
+        assert complex(ab.dotu(dev(x, cuda), dev(one, cuda)).item()) != complex(want)
+    rng = np.random.default_rng(8400 + dt)
+    assert complex(ab.dot_compensated(dev(np.zeros(0, O.NP_DTYPE[dt]), cuda), dev(np.zeros(0, O.NP_DTYPE[dt]), cuda)).item()) == 0
+    for n in (2, 3, 33, 1000, 4097, 65538, 200_001):
+        for conj in ((False, True) if cplx else (False,)):
+            x, y = illcond(rng, n, dt, 8 if dt in (O.F32, O.C32) else 30)
+            x, y = x[: n], y[: max(1, n - 1)]                          # unequal extents: zipWith intersects
+            exact = complex(O.dot_exact(x, y, conj))
+            got = complex(ab.dot_compensated(dev(x, cuda), dev(y, cuda), conj).item())
+            plain = complex((ab.dotc if conj else ab.dotu)(dev(x, cuda), dev(y, cuda)).item())
+            mag = float(np.sum(np.abs(x[: len(y)]).astype(np.float64) * np.abs(y).astype(np.float64)))
+            # twice-double-precision evaluation + one rounding to the element type
+            bound = 2 * O.EPS[dt] * abs(exact) + (2 if cplx else 1) * (len(y) * 2.0 ** -52) ** 2 * mag + 1e-300
+            assert abs(got - exact) <= bound, (O.NAMES[dt], n, conj, got, exact, bound)
+            # the plain fold is allowed its usual n * eps * sum|x_i y_i| -- and on these inputs it needs it
+            assert abs(plain - exact) <= (len(y) + 2) * O.EPS[dt] * mag
+    # unaligned operands take the scalar path
+    x, y = illcond(rng, 10_001, dt, 8 if dt in (O.F32, O.C32) else 30)
+    dx, dy = dev(x, cuda), dev(y, cuda)
+    got = complex(ab.dot_compensated(dx[1:], dy[1:]).item())
+    exact = complex(O.dot_exact(x[1:], y[1:]))
+    mag = float(np.sum(np.abs(x[1:]).astype(np.float64) * np.abs(y[1:]).astype(np.float64)))
+    assert abs(got - exact) <= 2 * O.EPS[dt] * abs(exact) + 2 * (10_000 * 2.0 ** -52) ** 2 * mag + 1e-300
+    # run-to-run bit equality (fixed tree)
+    a = ab.dot_compensated(dx, dy).cpu().numpy().tobytes()
+    assert all(ab.dot_compensated(dx, dy).cpu().numpy().tobytes() == a for _ in range(5))
