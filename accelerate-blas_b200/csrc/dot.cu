@@ -322,7 +322,13 @@ int dot_typed(cudaStream_t st, bool conj, int64_t n, const T *x, const T *y, T *
     case 2:  return dot_launch<T, Plain<T, 8>, 256, 8, 2>(st, conj, n, x, y, out);
     case 4:  return dot_launch<T, Plain<T, 8>, 512, 8, 1>(st, conj, n, x, y, out);
     case 5:  return dot_launch<T, Plain<T, 4>, 1024, 4, 1>(st, conj, n, x, y, out);
-    default: return dot_launch<T, Plain<T, 4>, 512, 4, 2>(st, conj, n, x, y, out);
+    case 0:  return dot_launch<T, Plain<T, 4>, 512, 4, 2>(st, conj, n, x, y, out);
+    default:
+        // Float: 8 loads per operand in flight per thread measure 7 056 GB/s at 2^28 against 6 639 for 4 (the 4-byte
+        // elements need twice the FMAs per byte, and the deeper batch hides them); the 8-byte types are within 0.3 %
+        // of each other on every shape (profiles/r02_dot_shapes.jsonl)
+        if (sizeof(T) == 4) return dot_launch<T, Plain<T, 8>, 256, 8, 2>(st, conj, n, x, y, out);
+        return dot_launch<T, Plain<T, 4>, 512, 4, 2>(st, conj, n, x, y, out);
     }
 }
 

@@ -222,7 +222,8 @@ def test_gpu_dot_compensated(dt, cuda):
         x = np.array(xs, dtype=O.NP_DTYPE[dt])
         one = np.ones(4, dtype=O.NP_DTYPE[dt])
         assert complex(ab.dot_compensated(dev(x, cuda), dev(one, cuda)).item()) == complex(want)
-        assert complex(ab.dotu(dev(x, cuda), dev(one, cuda)).item()) != complex(want)
+        if dt == O.F64:      # the plain fold loses the ones (for c64 its tree happens to pair the big terms first)
+            assert complex(ab.dotu(dev(x, cuda), dev(one, cuda)).item()) != complex(want)
     rng = np.random.default_rng(8400 + dt)
     assert complex(ab.dot_compensated(dev(np.zeros(0, O.NP_DTYPE[dt]), cuda), dev(np.zeros(0, O.NP_DTYPE[dt]), cuda)).item()) == 0
     for n in (2, 3, 33, 1000, 4097, 65538, 200_001):
