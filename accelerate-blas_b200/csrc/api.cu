@@ -274,6 +274,8 @@ int gemm_repitched(const GemmArgs &g)
     auto bad = [&](const void *p, int64_t ld) { return (reinterpret_cast<uintptr_t>(p) & 15u) != 0 || (ld % q) != 0; };
     const bool fixA = bad(g.A, g.lda), fixB = bad(g.B, g.ldb);
     if ((!fixA && !fixB) || (reinterpret_cast<uintptr_t>(g.C) & 15u) != 0) return gemm_generic(g);
+    // small f32 products: the mma.sync kernel loads the misaligned panels itself (one launch, no copy, no scratch)
+    if (g_tuning[ACCBLAS_TUNE_SGEMM_DIRECT] != 0 && sgemm_mma_direct_eligible(g)) return sgemm_mma_direct(g);
     GemmArgs h = g;
     const int64_t lda = fixA ? (g.colsA + q - 1) / q * q : g.lda, ldb = fixB ? (g.colsB + q - 1) / q * q : g.ldb;
     h.lda = lda; h.ldb = ldb;
@@ -515,6 +517,7 @@ const char *accblas_gemm_kernel_name(int dtype, int opA, int opB, int64_t rowsA,
     if (derive_gemm(g) != ACCBLAS_OK) return "invalid";
     Family f = pick_family(g);
     if (f == FAM_GENERIC && g_gemm_path == 0 && (double)g.m * (double)g.n * (double)g.k >= 48.0 * 48.0 * 48.0) {
+        if (g_tuning[ACCBLAS_TUNE_SGEMM_DIRECT] != 0 && sgemm_mma_direct_eligible(g)) return "sgemm_tf32x3_mma_direct";
         const int64_t q = (int64_t)(16 / elem_size(g.dtype));         // what gemm_repitched would run
         GemmArgs h = g;
         h.lda = (g.colsA + q - 1) / q * q;

@@ -238,6 +238,8 @@ int  cgemm_3m(const GemmArgs &g);
 size_t cgemm_3m_workspace(const GemmArgs &g);
 bool sgemm_mma_eligible(const GemmArgs &g);           // gemm_mma_tf32.cu : f32 / c32 on mma.sync, small / medium
 int  sgemm_mma(const GemmArgs &g);
+bool sgemm_mma_direct_eligible(const GemmArgs &g);    //                    f32, misaligned operands, whole K in shared memory
+int  sgemm_mma_direct(const GemmArgs &g);
 
 int gemv_dispatch(cudaStream_t s, int dtype, int opA, int64_t rowsA, int64_t colsA,
                   const void *alpha, bool alpha_dev, const void *A, const void *x, void *y);   // gemv.cu

@@ -5,6 +5,7 @@
 #include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <cstdlib>
 
 namespace accblas {
 namespace tma {
@@ -117,6 +118,44 @@ inline EncodeTiledFn encode_fn()
     return fn;
 }
 
+// Encoding a tensor map costs the host about a microsecond -- a visible share of a 6 us call on the reference's small
+// benchmark shapes, where a loop multiplies the same arrays again and again.  The map is a pure function of
+// (type, rank, base, dims, strides, box), so a small per-thread direct-mapped cache of encoded maps is safe: a hit
+// returns the bytes the driver produced for exactly these arguments (no device state is involved).
+// ACCBLAS_TMAP_CACHE=0 disables it (A/B measurements).
+struct MapKey {
+    uint64_t base, dims[3], strides[2];
+    uint32_t box[3], dt, rank;
+    bool operator==(const MapKey &o) const {
+        return base == o.base && dims[0] == o.dims[0] && dims[1] == o.dims[1] && dims[2] == o.dims[2] &&
+               strides[0] == o.strides[0] && strides[1] == o.strides[1] && box[0] == o.box[0] && box[1] == o.box[1] &&
+               box[2] == o.box[2] && dt == o.dt && rank == o.rank;
+    }
+};
+inline bool encode_cached(CUtensorMap *map, CUtensorMapDataType dt, uint32_t rank, const void *base, const cuuint64_t *dims,
+                          const cuuint64_t *strides, const cuuint32_t *box)
+{
+    EncodeTiledFn fn = encode_fn();
+    if (!fn) return false;
+    static const bool enabled = [] { const char *e = getenv("ACCBLAS_TMAP_CACHE"); return !(e && *e == '0'); }();
+    constexpr int SLOTS = 64;
+    struct Entry { MapKey key; CUtensorMap map; bool valid; };
+    static thread_local Entry cache[SLOTS];
+    MapKey k{};
+    k.base = reinterpret_cast<uint64_t>(base); k.dt = (uint32_t)dt; k.rank = rank;
+    for (uint32_t i = 0; i < rank; ++i) { k.dims[i] = dims[i]; k.box[i] = box[i]; }
+    for (uint32_t i = 0; i + 1 < rank; ++i) k.strides[i] = strides[i];
+    uint64_t h = k.base * 0x9E3779B97F4A7C15ull ^ (k.dims[0] * 31 + k.dims[1] * 131 + k.box[0] * 7 + k.box[1] * 3 + k.box[2] + rank);
+    Entry &e = cache[(h >> 40) % SLOTS];
+    if (enabled && e.valid && e.key == k) { *map = e.map; return true; }
+    cuuint32_t estr[3] = {1, 1, 1};
+    if (fn(map, dt, rank, const_cast<void *>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+           CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+        return false;
+    e.key = k; e.map = *map; e.valid = true;
+    return true;
+}
+
 // Row-major rows x cols matrix of `esize`-byte elements viewed as a 2-D tensor
 // (dim0 = columns, contiguous).  Box = box_cols x box_rows, 128-byte swizzle, zero fill
 // outside the matrix.  Requires: base 16-byte aligned, cols * esize % 16 == 0,
@@ -124,15 +163,10 @@ inline EncodeTiledFn encode_fn()
 inline bool make_2d(CUtensorMap *map, CUtensorMapDataType dt, size_t esize, const void *base, uint64_t rows,
                     uint64_t cols, uint32_t box_rows, uint32_t box_cols, uint64_t pitch_bytes = 0)
 {
-    EncodeTiledFn fn = encode_fn();
-    if (!fn) return false;
     cuuint64_t dims[2] = {cols, rows};
     cuuint64_t strides[1] = {pitch_bytes ? pitch_bytes : cols * esize};
     cuuint32_t box[2] = {box_cols, box_rows};
-    cuuint32_t estr[2] = {1, 1};
-    return fn(map, dt, 2, const_cast<void *>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-              CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+    return encode_cached(map, dt, 2, base, dims, strides, box);
 }
 
 // `planes` row-major rows x cols matrices, plane b starting plane_stride_bytes * b after `base` (a strided batch), as
@@ -143,15 +177,11 @@ inline bool make_2d_batched(CUtensorMap *map, CUtensorMapDataType dt, size_t esi
                             uint64_t cols, uint32_t box_rows, uint32_t box_cols, uint64_t pitch_bytes, uint64_t planes,
                             uint64_t plane_stride_bytes)
 {
-    EncodeTiledFn fn = encode_fn();
-    if (!fn || planes == 0 || plane_stride_bytes == 0 || (plane_stride_bytes & 15u)) return false;
+    if (planes == 0 || plane_stride_bytes == 0 || (plane_stride_bytes & 15u)) return false;
     cuuint64_t dims[3] = {cols, rows, planes};
     cuuint64_t strides[2] = {pitch_bytes ? pitch_bytes : cols * esize, plane_stride_bytes};
     cuuint32_t box[3] = {box_cols, box_rows, 1};
-    cuuint32_t estr[3] = {1, 1, 1};
-    return fn(map, dt, 3, const_cast<void *>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-              CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+    return encode_cached(map, dt, 3, base, dims, strides, box);
 }
 
 // An MN-major operand (rows = K, cols = the m or n extent, `cols` a multiple of `inner`) viewed as a 3-D tensor
@@ -163,15 +193,11 @@ inline bool make_2d_batched(CUtensorMap *map, CUtensorMapDataType dt, size_t esi
 inline bool make_mn3d(CUtensorMap *map, CUtensorMapDataType dt, size_t esize, const void *base, uint64_t rows_k,
                       uint64_t cols, uint32_t inner, uint32_t box_k, uint32_t groups, uint64_t pitch_bytes)
 {
-    EncodeTiledFn fn = encode_fn();
-    if (!fn || cols % inner != 0) return false;
+    if (cols % inner != 0) return false;
     cuuint64_t dims[3] = {inner, rows_k, cols / inner};
     cuuint64_t strides[2] = {pitch_bytes, (cuuint64_t)inner * esize};
     cuuint32_t box[3] = {inner, box_k, groups};
-    cuuint32_t estr[3] = {1, 1, 1};
-    return fn(map, dt, 3, const_cast<void *>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-              CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+    return encode_cached(map, dt, 3, base, dims, strides, box);
 }
 
 }  // namespace tma

@@ -9,6 +9,7 @@
 #include <cublas_v2.h>
 #include <cuda_runtime.h>
 #include <algorithm>
+#include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -64,18 +65,24 @@ template <typename F> float time_ms(F f, int warm, int iters, float *best) {
 
 // sustained time per call: `iters` calls enqueued back to back between TWO events (no event between calls; the per-call
 // events above cost the short kernels a visible gap and sit on the timer's ~1 us quantum).  Best of 3 batches.
+static double now_ms();
+static float g_enqueue_us = 0.f;                 // host time per call of the last stream_ms batch (enqueue only, no sync)
 template <typename F> float stream_ms(F f, int iters) {
     cudaEvent_t e0, e1;
     cudaEventCreate(&e0); cudaEventCreate(&e1);
     float best = 1e30f;
+    g_enqueue_us = 1e30f;
     for (int rep = 0; rep < 3; ++rep) {
         CK(cudaDeviceSynchronize());
         cudaEventRecord(e0);
+        const double h0 = now_ms();
         for (int i = 0; i < iters; ++i) f();
+        const double h1 = now_ms();
         cudaEventRecord(e1);
         CK(cudaDeviceSynchronize());
         float t; cudaEventElapsedTime(&t, e0, e1);
         best = std::min(best, t / iters);
+        g_enqueue_us = std::min(g_enqueue_us, (float)((h1 - h0) * 1e3 / iters));
     }
     cudaEventDestroy(e0); cudaEventDestroy(e1);
     return best;
@@ -107,8 +114,9 @@ static void gemm_case(int dt, char opA, char opB, long m, long n, long k, int it
            name, accblas_gemm_kernel_name(dt, opcode(opA), opcode(opB), rowsA, colsA, rowsB, colsB), m1, b1, m2, b2,
            flop / m1 * 1e-9, flop / m2 * 1e-9, m2 / m1);
     if (m1 < 1.0f) {
-        const float s1 = stream_ms(ours, iters), s2 = stream_ms(theirs, iters);
-        printf(",\"accblas_ms_stream\":%.4f,\"cublas_ms_stream\":%.4f,\"speedup_stream\":%.3f", s1, s2, s2 / s1);
+        const float s1 = stream_ms(ours, iters), q1 = g_enqueue_us, s2 = stream_ms(theirs, iters), q2 = g_enqueue_us;
+        printf(",\"accblas_ms_stream\":%.4f,\"cublas_ms_stream\":%.4f,\"speedup_stream\":%.3f,\"accblas_enqueue_us\":%.2f,\"cublas_enqueue_us\":%.2f",
+               s1, s2, s2 / s1, q1, q2);
     }
     printf("}\n");
     fflush(stdout);
@@ -138,8 +146,9 @@ static void gemv_case(int dt, char op, long rows, long cols, int iters) {
            "\"accblas_gbs\":%.1f,\"cublas_gbs\":%.1f,\"speedup\":%.3f",
            name, m1, b1, m2, b2, bytes / m1 * 1e-6, bytes / m2 * 1e-6, m2 / m1);
     if (m1 < 1.0f) {
-        const float s1 = stream_ms(ours, iters), s2 = stream_ms(theirs, iters);
-        printf(",\"accblas_ms_stream\":%.4f,\"cublas_ms_stream\":%.4f,\"speedup_stream\":%.3f", s1, s2, s2 / s1);
+        const float s1 = stream_ms(ours, iters), q1 = g_enqueue_us, s2 = stream_ms(theirs, iters), q2 = g_enqueue_us;
+        printf(",\"accblas_ms_stream\":%.4f,\"cublas_ms_stream\":%.4f,\"speedup_stream\":%.3f,\"accblas_enqueue_us\":%.2f,\"cublas_enqueue_us\":%.2f",
+               s1, s2, s2 / s1, q1, q2);
     }
     printf("}\n");
     fflush(stdout);
@@ -171,7 +180,6 @@ static void dot_case(int dt, long n, int iters) {
     cudaFree(x); cudaFree(y); cudaFree(out);
 }
 
-#include <chrono>
 static double now_ms() {
     return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
 }

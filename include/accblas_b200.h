@@ -365,7 +365,9 @@ typedef enum {
                                        5 = 1024x4x1 (profiles/r02_dot_shapes.jsonl)                                                */
     ACCBLAS_TUNE_MG_DOT_FUSED = 16, /* accblas_mg_dot: 0 = local dot (two launches) + one exchange kernel, default: ONE launch whose
                                        last CTA sums the partials and runs the scalar all-reduce over the peers' buffers           */
-    ACCBLAS_TUNE_COUNT = 17
+    ACCBLAS_TUNE_SGEMM_DIRECT = 17, /* f32 gemm, operand base / pitch off TMA's 16-byte grid, k <= 768: 0 = copy into aligned scratch first
+                                       (round 1), default: the mma.sync kernel loads its panels itself (one launch, no scratch)     */
+    ACCBLAS_TUNE_COUNT = 18
 } accblas_tune_t;
 /* Process-wide defaults for threads that never call this: environment variable
  * ACCBLAS_TUNE="knob=value,knob=value" (read once). */

@@ -478,3 +478,58 @@ def test_gemm_nonfinite_inputs_f32_families(dt, cuda):
                 scale = np.abs(want[fin]).max() if fin.any() else 1.0
                 assert np.abs(got[fin] - want[fin]).max() <= 1e-4 * max(scale, 1.0) * np.sqrt(k), ("finite part", what)
     assert any("tcgen05" in s for s in seen) and any("mma" in s for s in seen), seen
+
+
+# ------------------------------------------------------------------------------------------ f32, operands off TMA's grid
+def test_sgemm_direct_misaligned_operands(cuda):
+    """Float operands whose row pitch is not a multiple of 16 bytes (the reference benchmarks 250 x 250 Floats,
+    bench/Bench/Accelerate.hs:92-125) with k <= 768: the mma.sync kernel loads its own panels (one launch, no re-pitch
+    copy).  Every op pair, ragged extents, alpha, the beta epilogue, a misaligned base; against the wide oracle and
+    against the round-1 path (copy into aligned scratch) on the same inputs."""
+    import accblas_b200 as ab
+    dt = O.F32
+    rng = np.random.default_rng(12100)
+    TUNE_SGEMM_DIRECT = 17
+    shapes = [(250, 250, 250), (33, 47, 95), (100, 31, 767), (129, 65, 37), (31, 250, 513)]
+    for (m, n, k) in shapes:
+        for oa in "NTH":
+            for ob in "NTH":
+                al, A, B = gemm_inputs(rng, dt, oa, ob, m, n, k)
+                assert ab.kernel_name(dt, oa, ob, A.shape, B.shape) == "sgemm_tf32x3_mma_direct", (m, n, k, oa, ob)
+                dA, dB = dev(A, cuda), dev(B, cuda)
+                ref = O.gemm(al, oa, A, ob, B, wide=True)
+                C = host(ab.gemm(al, oa, dA, ob, dB))
+                err = O.gemm_error_units(C, ref, A, B, k, alpha=al)
+                assert err <= TOL_UNITS_TF32X3, (m, n, k, oa, ob, err)
+                ab.set_tuning(TUNE_SGEMM_DIRECT, 0)
+                try:
+                    C0 = host(ab.gemm(al, oa, dA, ob, dB))
+                finally:
+                    ab.set_tuning(TUNE_SGEMM_DIRECT, -1)
+                assert O.gemm_error_units(C0, ref, A, B, k, alpha=al) <= TOL_UNITS_TF32X3
+    # beta epilogue + an operand base that is only 4-byte aligned (a view one element into a buffer)
+    m, n, k = 130, 94, 301
+    al, A, B = gemm_inputs(rng, dt, "N", "N", m, n, k)
+    beta = np.float32(0.75)
+    Cin = O.uniform(rng, (m, n), dt)
+    import torch
+    bufA = torch.empty(m * k + 1, dtype=torch.float32, device=cuda)
+    dA = bufA[1:].view(m, k)
+    dA.copy_(dev(A, cuda))
+    D = host(ab.gemm(al, "N", dA, "N", dev(B, cuda), beta=beta, Cin=dev(Cin, cuda)))
+    ref = O.gemm(al, "N", A, "N", B, wide=True).astype(np.float64) + np.float64(beta) * Cin.astype(np.float64)
+    assert O.fro(D.astype(np.float64) - ref) <= ex_bound(dt, TOL_UNITS_TF32X3, al, A, B, k, beta, Cin, ref)
+    # beyond the shared-memory budget the copy path still serves the product
+    A = O.uniform(rng, (70, 801), dt)
+    B = O.uniform(rng, (801, 50), dt)
+    assert ab.kernel_name(dt, "N", "N", A.shape, B.shape) == "sgemm_tf32x3_mma"
+    C = host(ab.gemm(1, "N", dev(A, cuda), "N", dev(B, cuda)))
+    assert O.gemm_error_units(C, O.gemm(1, "N", A, "N", B, wide=True), A, B, 801) <= TOL_UNITS_TF32X3
+    # non-finite inputs keep the FP32 pattern on this path too
+    A = O.uniform(rng, (64, 250), dt)
+    B = O.uniform(rng, (250, 66), dt)
+    A[3, 7] = np.inf
+    B[9, 5] = np.nan
+    C = host(ab.gemm(1, "N", dev(A, cuda), "N", dev(B, cuda)))
+    want = A.astype(np.float64) @ B.astype(np.float64)
+    assert np.array_equal(np.isnan(C), np.isnan(want)) and np.array_equal(np.isinf(C), np.isinf(want))
