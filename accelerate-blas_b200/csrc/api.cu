@@ -276,6 +276,7 @@ int gemm_repitched(const GemmArgs &g)
     if ((!fixA && !fixB) || (reinterpret_cast<uintptr_t>(g.C) & 15u) != 0) return gemm_generic(g);
     // small f32 products: the mma.sync kernel loads the misaligned panels itself (one launch, no copy, no scratch)
     if (g_tuning[ACCBLAS_TUNE_SGEMM_DIRECT] != 0 && sgemm_mma_direct_eligible(g)) return sgemm_mma_direct(g);
+    if (g.dtype == ACCBLAS_F64 && dgemm_direct_eligible(g)) return dgemm_direct(g);
     GemmArgs h = g;
     const int64_t lda = fixA ? (g.colsA + q - 1) / q * q : g.lda, ldb = fixB ? (g.colsB + q - 1) / q * q : g.ldb;
     h.lda = lda; h.ldb = ldb;
@@ -518,6 +519,7 @@ const char *accblas_gemm_kernel_name(int dtype, int opA, int opB, int64_t rowsA,
     Family f = pick_family(g);
     if (f == FAM_GENERIC && g_gemm_path == 0 && (double)g.m * (double)g.n * (double)g.k >= 48.0 * 48.0 * 48.0) {
         if (g_tuning[ACCBLAS_TUNE_SGEMM_DIRECT] != 0 && sgemm_mma_direct_eligible(g)) return "sgemm_tf32x3_mma_direct";
+        if (g.dtype == ACCBLAS_F64 && dgemm_direct_eligible(g)) return "dgemm_dmma_direct";
         const int64_t q = (int64_t)(16 / elem_size(g.dtype));         // what gemm_repitched would run
         GemmArgs h = g;
         h.lda = (g.colsA + q - 1) / q * q;

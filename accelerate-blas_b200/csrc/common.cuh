@@ -225,6 +225,8 @@ int gemm_generic(const GemmArgs &g);                  // gemm_generic.cu : any s
 int gemm_rank1(const GemmArgs &g);                    // gemm_generic.cu : k == 1 (outer product `><`)
 bool dgemm_dmma_eligible(const GemmArgs &g);          // gemm_dmma.cu    : f64 / c64 on DMMA
 int  dgemm_dmma(const GemmArgs &g);
+bool dgemm_direct_eligible(const GemmArgs &g);        //                   f64, misaligned operands, one wave of 32 x 32 tiles, whole K in smem
+int  dgemm_direct(const GemmArgs &g);
 size_t dgemm_dmma_workspace(const GemmArgs &g);        //                   stream-K scratch (0 for the data-parallel tiles)
 bool zgemm_3m_eligible(const GemmArgs &g);            // gemm_3m.cu      : c64 as three real DMMA products
 bool zgemm_3m_wanted(const GemmArgs &g);              //                   (knob + cost model)

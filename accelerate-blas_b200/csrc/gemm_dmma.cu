@@ -58,6 +58,9 @@ using Tile32x32   = Tile<2, 2, 2, 2, 3, 7>;   // 7 CTAs per SM: 1024 tiles (dgem
 // bound by the LATENCY of its TMA ring, not by the pipe: three 8 KiB stages in flight per CTA are ~3 K-blocks per L2
 // round trip (r01_dgemm_nn_500_ncu.txt: DMMA 60 % active while 256 CTAs sit on 148 SMs, 16.3 us for 6.7 us of math).
 using Tile32x32Deep = Tile<2, 2, 2, 2, 8, 3>;
+// (Round 2, measured and NOT kept: dealing the K-blocks to two groups of consumer warps inside the CTA -- 250^3: 7.10 -> 6.91 us
+//  of kernel time, 250 x 250 x 1024: 18.9 -> 18.8; splitting the accumulators by k-step -- 1000^3: 70 -> 82 us; loading the
+//  panels with plain loads instead of the ring -- no change.  profiles/r02_small_shapes.md.)
 
 __device__ __forceinline__ void dmma(double &d0, double &d1, double a, double b) {
     asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
@@ -117,7 +120,11 @@ struct DgemmParams {
     double *C;
     int tiles_m, tiles_n, group;
     int snake_waves;     // CTAs per resident wave (0: every tile walks K forwards)
+    const double *Ag, *Bg;   // DIRECT kernels only: the stored operands and their row pitches (elements)
+    int64_t lda, ldb;
 };
+constexpr int kDirectThreads = 512;      // DIRECT kernels: 16 loader warps, the first CONSUMER_WARPS of them go on to multiply
+constexpr int kDirectMaxKBlocks = 24;    // 24 stages of 8 KiB + slack fit a CTA's 227 KiB (k <= 384 doubles)
 
 // tile index -> (tile_m, tile_n) under the grouped rasterisation: p.group tile-rows per group, so that one resident
 // wave re-uses its A and B panels out of L2
@@ -169,8 +176,15 @@ __device__ __forceinline__ void dgemm_epilogue(const DgemmParams &p, const doubl
 }
 
 // AK: op(A) is K-major in memory (opA == N).  BKM: op(B) is K-major in memory (opB == T).
-template <bool AK, bool BKM, typename TL, int REL, bool BETA>
-__global__ void __launch_bounds__(TL::THREADS, TL::MIN_CTAS)
+// DIRECT (round 2): operands that miss TMA's 16-byte rule (odd column counts: 8-byte aligned rows) in a product of at most
+// one 32 x 32 tile per SM with k <= 384 -- no TMA ring, no re-pitch copy in front (api.cu: gemm_repitched).  All 16 warps
+// of the CTA load its two panels for the WHOLE K extent with plain 8-byte loads (16 in flight per lane, zero fill outside
+// the matrix) straight into the swizzled stage layout a TMA box would have produced, one stage per K-block; after one
+// __syncthreads the consumer warps run the K loop with no barrier at all.  Same tile, same K order, same DMMA sequence
+// as the ring kernel: bit-identical results.  (Measured on ALIGNED operands the direct load is no faster than the ring
+// -- 250^3: 8.2 us either way -- so aligned products keep the ring; profiles/r02_small_shapes.md.)
+template <bool AK, bool BKM, typename TL, int REL, bool BETA, bool DIRECT = false>
+__global__ void __launch_bounds__(DIRECT ? kDirectThreads : TL::THREADS, DIRECT ? 1 : TL::MIN_CTAS)
 dgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
                   const DgemmParams p)
 {
@@ -191,47 +205,103 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
     const int m0 = tile_m * BM, n0 = tile_n * BN;
     const int kblocks = (int)((p.k + BK - 1) / BK);
 
-    if (threadIdx.x == 0) {
-        for (int s = 0; s < STAGES; ++s) {
-            tma::mbar_init(bar_base + 8 * s, 1);                       // full: producer's expect_tx arrive
-            tma::mbar_init(bar_base + 8 * (STAGES + s), CONSUMER_WARPS); // empty: one arrive per consumer warp
-        }
-        tma::fence_barrier_init();
-    }
-    __syncthreads();
-
-    if (warp == CONSUMER_WARPS) {
-        // ================================ producer ================================
-        if (lane == 0) {
-            tma::prefetch_tmap(&mapA);
-            tma::prefetch_tmap(&mapB);
-            // (L2 eviction hints -- evict_last on A, evict_first on B, tma::load_2d_hint -- were measured:
-            //  DRAM traffic 6.9 GB per 8192^3 launch with or without them, time unchanged; left out.)
-            // Successive waves of CTAs (one CTA per SM: blockIdx / gridDim-independent SM count) walk K in
-            // opposite directions: a wave ends with the K-tail of its panels in L2, and the next wave -- which
-            // shares its A panels under the grouped rasterisation -- starts on exactly that tail.
-            const bool rev = p.snake_waves > 0 && ((blockIdx.x / p.snake_waves) & 1);
-            for (int kb = 0; kb < kblocks; ++kb) {
-                const int s = kb % STAGES;
-                const uint32_t round = kb / STAGES;
-                if (kb >= STAGES) tma::mbar_wait(bar_base + 8 * (STAGES + s), (round - 1) & 1);
-                const uint32_t full = bar_base + 8 * s;
-                const uint32_t sa = smem_base + s * STAGE_BYTES, sb = sa + A_BYTES;
-                tma::mbar_expect_tx(full, STAGE_BYTES);
-                const int k0 = (rev ? kblocks - 1 - kb : kb) * BK;
-                if (AK) tma::load_box(sa, &mapA, full, k0, m0, pa);
-                else if (p.a_one_box) tma::load_3d(sa, &mapA, full, 0, k0, m0 >> 4);
-                else
+    if constexpr (DIRECT) {
+        constexpr int NW = kDirectThreads / 32, U = 16;
+        const int kpad = kblocks * BK;
+        // (no "memory" clobber: the next batch's loads may be scheduled above these stores; the __syncthreads below orders
+        //  them against the consumers' ld.shared)
+        auto sts = [](uint32_t addr, double v) { asm volatile("st.shared.f64 [%0], %1;" ::"r"(addr), "d"(v)); };
+        // K-major panel (rows = the m | n index, k contiguous): (r, k) -> stage k / 16, row r, chunk ((k % 16) / 2) ^ (r % 8)
+        auto load_kmajor = [&](const double *__restrict__ G, int64_t ld, int r0, int64_t rmax, int rows, uint32_t off) {
+            for (int r = warp; r < rows; r += NW) {
+                const bool rin = r0 + r < rmax;
+                const double *row = G + (int64_t)(r0 + r) * ld;
+                for (int kq = lane; kq < kpad; kq += 32 * U) {
+                    double v[U];
 #pragma unroll
-                    for (int j = 0; j < BM / 16; ++j) tma::load_box(sa + j * 2048, &mapA, full, m0 + 16 * j, k0, pa);
-                if (BKM) tma::load_box(sb, &mapB, full, k0, n0, pb);
-                else if (p.b_one_box) tma::load_3d(sb, &mapB, full, 0, k0, n0 >> 4);
-                else
+                    for (int u = 0; u < U; ++u) {
+                        const int k = kq + 32 * u;
+                        v[u] = (rin && k < p.k) ? __ldg(row + k) : 0.0;
+                    }
 #pragma unroll
-                    for (int j = 0; j < BN / 16; ++j) tma::load_box(sb + j * 2048, &mapB, full, n0 + 16 * j, k0, pb);
+                    for (int u = 0; u < U; ++u) {
+                        const int k = kq + 32 * u, kk = k & 15;
+                        if (k < kpad)
+                            sts(smem_base + (k >> 4) * STAGE_BYTES + off + r * 128 + ((((kk >> 1) ^ r) & 7) << 4) + (kk & 1) * 8, v[u]);
+                    }
+                }
             }
+        };
+        // MN-major panel (rows = k, the m | n index contiguous): (k, c) -> stage k / 16, box c / 16, row k % 16,
+        // chunk ((c % 16) / 2) ^ (k % 8)
+        auto load_mnmajor = [&](const double *__restrict__ G, int64_t ld, int c0, int64_t cmax, int cols, uint32_t off) {
+            for (int c = lane; c < cols; c += 32) {
+                const bool cin = c0 + c < cmax;
+                const double *col = G + c0 + c;
+                for (int kq = warp; kq < kpad; kq += NW * U) {
+                    double v[U];
+#pragma unroll
+                    for (int u = 0; u < U; ++u) {
+                        const int k = kq + NW * u;
+                        v[u] = (cin && k < p.k) ? __ldg(col + (int64_t)k * ld) : 0.0;
+                    }
+#pragma unroll
+                    for (int u = 0; u < U; ++u) {
+                        const int k = kq + NW * u, kk = k & 15;
+                        if (k < kpad)
+                            sts(smem_base + (k >> 4) * STAGE_BYTES + off + (c >> 4) * 2048 + kk * 128 +
+                                    (((((c & 15) >> 1) ^ kk) & 7) << 4) + (c & 1) * 8, v[u]);
+                    }
+                }
+            }
+        };
+        if (AK) load_kmajor(p.Ag, p.lda, m0, p.m, BM, 0); else load_mnmajor(p.Ag, p.lda, m0, p.m, BM, 0);
+        if (BKM) load_kmajor(p.Bg, p.ldb, n0, p.n, BN, A_BYTES); else load_mnmajor(p.Bg, p.ldb, n0, p.n, BN, A_BYTES);
+        __syncthreads();
+        if (warp >= CONSUMER_WARPS) return;
+    } else {
+        if (threadIdx.x == 0) {
+            for (int s = 0; s < STAGES; ++s) {
+                tma::mbar_init(bar_base + 8 * s, 1);                       // full: producer's expect_tx arrive
+                tma::mbar_init(bar_base + 8 * (STAGES + s), CONSUMER_WARPS); // empty: one arrive per consumer warp
+            }
+            tma::fence_barrier_init();
         }
-        return;
+        __syncthreads();
+
+        if (warp == CONSUMER_WARPS) {
+            // ================================ producer ================================
+            if (lane == 0) {
+                tma::prefetch_tmap(&mapA);
+                tma::prefetch_tmap(&mapB);
+                // (L2 eviction hints -- evict_last on A, evict_first on B, tma::load_2d_hint -- were measured:
+                //  DRAM traffic 6.9 GB per 8192^3 launch with or without them, time unchanged; left out.)
+                // Successive waves of CTAs (one CTA per SM: blockIdx / gridDim-independent SM count) walk K in
+                // opposite directions: a wave ends with the K-tail of its panels in L2, and the next wave -- which
+                // shares its A panels under the grouped rasterisation -- starts on exactly that tail.
+                const bool rev = p.snake_waves > 0 && ((blockIdx.x / p.snake_waves) & 1);
+                for (int kb = 0; kb < kblocks; ++kb) {
+                    const int s = kb % STAGES;
+                    const uint32_t round = kb / STAGES;
+                    if (kb >= STAGES) tma::mbar_wait(bar_base + 8 * (STAGES + s), (round - 1) & 1);
+                    const uint32_t full = bar_base + 8 * s;
+                    const uint32_t sa = smem_base + s * STAGE_BYTES, sb = sa + A_BYTES;
+                    tma::mbar_expect_tx(full, STAGE_BYTES);
+                    const int k0 = (rev ? kblocks - 1 - kb : kb) * BK;
+                    if (AK) tma::load_box(sa, &mapA, full, k0, m0, pa);
+                    else if (p.a_one_box) tma::load_3d(sa, &mapA, full, 0, k0, m0 >> 4);
+                    else
+    #pragma unroll
+                        for (int j = 0; j < BM / 16; ++j) tma::load_box(sa + j * 2048, &mapA, full, m0 + 16 * j, k0, pa);
+                    if (BKM) tma::load_box(sb, &mapB, full, k0, n0, pb);
+                    else if (p.b_one_box) tma::load_3d(sb, &mapB, full, 0, k0, n0 >> 4);
+                    else
+    #pragma unroll
+                        for (int j = 0; j < BN / 16; ++j) tma::load_box(sb + j * 2048, &mapB, full, n0 + 16 * j, k0, pb);
+                }
+            }
+            return;
+        }
     }
 
     // ================================ consumers ================================
@@ -265,10 +335,12 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
     };
 
     for (int kb = 0; kb < kblocks; ++kb) {
-        const int s = kb % STAGES;
+        const int s = DIRECT ? kb : kb % STAGES;
         const uint32_t stage = smem_base + s * STAGE_BYTES;
-        tma::mbar_wait(bar_base + 8 * s, (kb / STAGES) & 1);
-        release_before<REL, STAGES>(bar_base + 8 * STAGES, s, kb == 0, lane);
+        if constexpr (!DIRECT) {
+            tma::mbar_wait(bar_base + 8 * s, (kb / STAGES) & 1);
+            release_before<REL, STAGES>(bar_base + 8 * STAGES, s, kb == 0, lane);
+        }
         double a[2][MI], b[2][NJ];
         load_frags(stage, 0, a[0], b[0]);
 #pragma unroll
@@ -279,7 +351,7 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
 #pragma unroll
                 for (int j = 0; j < NJ; ++j) dmma(acc[i][j][0], acc[i][j][1], a[st & 1][i], b[st & 1][j]);
         }
-        release_after<REL>(bar_base + 8 * (STAGES + s), lane);          // stage consumed by this warp
+        if constexpr (!DIRECT) release_after<REL>(bar_base + 8 * (STAGES + s), lane);   // stage consumed by this warp
     }
 
     // ---- epilogue: C = alpha * acc (+ beta * Cin); C itself is never read unless it is Cin ----
@@ -916,6 +988,34 @@ int launch_dgemm_streamk(const GemmArgs &g, const StreamKPlan &pl)
     return st;
 }
 
+// DIRECT launch: 32 x 32 tiles, whole K resident (one 8 KiB stage per K-block), 16 loader warps; the tensor maps are unused.
+template <bool AK, bool BKM, bool BETA>
+int launch_dgemm_direct_beta(const GemmArgs &g)
+{
+    using TL = Tile32x32Deep;                         // (only BM / BN / STAGE_BYTES matter: there is no ring)
+    constexpr int MAX_SMEM = kDirectMaxKBlocks * TL::STAGE_BYTES + 1024;
+    static thread_local AttrOnce attr_once;
+    if (attr_once.need()) {
+        ACC_CUDA(cudaFuncSetAttribute(dgemm_dmma_kernel<AK, BKM, TL, REL_FENCED, BETA, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_SMEM));
+    }
+    DgemmParams p;
+    fill_params(p, g, TL::BM, TL::BN);
+    p.a_one_box = p.b_one_box = 0; p.snake_waves = 0;
+    p.Ag = static_cast<const double *>(g.A); p.Bg = static_cast<const double *>(g.B);
+    p.lda = g.lda; p.ldb = g.ldb;
+    const int64_t tiles = (int64_t)p.tiles_m * p.tiles_n;
+    const int kblocks = (int)((g.k + BK - 1) / BK);
+    static const CUtensorMap unused{};
+    dgemm_dmma_kernel<AK, BKM, TL, REL_FENCED, BETA, true><<<(unsigned)tiles, kDirectThreads, (size_t)kblocks * TL::STAGE_BYTES + 1024, g.stream>>>(
+        unused, unused, p);
+    return check_launch("dgemm_dmma_kernel<direct>");
+}
+template <bool AK, bool BKM>
+int launch_dgemm_direct(const GemmArgs &g)
+{
+    return has_beta(g) ? launch_dgemm_direct_beta<AK, BKM, true>(g) : launch_dgemm_direct_beta<AK, BKM, false>(g);
+}
+
 template <bool AK, bool BKM, typename TL>
 int launch_dgemm_tile_rel(const GemmArgs &g, int rel)
 {
@@ -1068,6 +1168,24 @@ size_t dgemm_dmma_workspace(const GemmArgs &g)
     if (g.dtype != ACCBLAS_F64) return 0;
     const StreamKPlan pl = plan_streamk(g.m, g.n, g.k);
     return pl.use ? (size_t)pl.grid * 128 * 128 * 8 + 4096 : 0;                        // accumulator slots + flags
+}
+
+// f64 products with an operand off TMA's 16-byte grid (odd column count, 8-byte aligned rows) that fit the direct kernel:
+// one wave of 32 x 32 tiles at one CTA per SM, whole K in shared memory, one product
+bool dgemm_direct_eligible(const GemmArgs &g)
+{
+    if (g_tuning[ACCBLAS_TUNE_DGEMM_DIRECT] == 0 || g.dtype != ACCBLAS_F64 || g.batch > 1) return false;
+    if (g.k > (int64_t)BK * kDirectMaxKBlocks || ((g.m + 31) / 32) * ((g.n + 31) / 32) > (int64_t)sm_count()) return false;
+    if (!aligned16(g.C) || g.m * g.n < 24 * 24 || g.k < 4) return false;
+    return g.rowsA <= 0x7fffffff && g.colsA <= 0x7fffffff && g.rowsB <= 0x7fffffff && g.colsB <= 0x7fffffff;
+}
+int dgemm_direct(const GemmArgs &g)
+{
+    const bool ak = g.opA == ACCBLAS_OP_N, bk = g.opB != ACCBLAS_OP_N;
+    if (ak && bk) return launch_dgemm_direct<true, true>(g);
+    if (ak && !bk) return launch_dgemm_direct<true, false>(g);
+    if (!ak && bk) return launch_dgemm_direct<false, true>(g);
+    return launch_dgemm_direct<false, false>(g);
 }
 
 int dgemm_dmma(const GemmArgs &g)

@@ -93,7 +93,7 @@ static int opcode(char c) { return c == 'N' ? 0 : c == 'T' ? 1 : 2; }
 
 static void gemm_case(int dt, char opA, char opB, long m, long n, long k, int iters) {
     char name[80]; snprintf(name, sizeof name, "%cgemm_%c%c_%ldx%ldx%ld", DT[dt], opA, opB, m, n, k);
-    if (!strstr(name, filter)) return;
+    if (!strstr(name, filter) && strcmp(filter, "ksweep")) return;
     if (iters_override) iters = iters_override;
     void *A = dev_random(dt, (size_t)m * k, 1), *B = dev_random(dt, (size_t)k * n, 2), *C = dev_random(dt, (size_t)m * n, 3);
     long rowsA = opA == 'N' ? m : k, colsA = opA == 'N' ? k : m, rowsB = opB == 'N' ? k : n, colsB = opB == 'N' ? n : k;
@@ -301,6 +301,13 @@ int main(int argc, char **argv) {
     if (argc > 2) iters_override = atoi(argv[2]);
     CK(cublasCreate(&H));
     CK(cublasSetAtomicsMode(H, CUBLAS_ATOMICS_ALLOWED));              // LLVM/PTX/Context.hs:59
+    if (!strcmp(filter, "ksweep")) {                                  // fixed m = n, growing k: fixed cost vs per-K cost of the small kernels
+        for (int dt = 0; dt < 4; ++dt)
+            for (long mn : {96L, 250L})
+                for (long k : {16L, 64L, 128L, 256L, 512L, 1024L}) gemm_case(dt, 'N', 'N', mn, mn, k, 300);
+        return 0;
+    }
+    if (!strcmp(filter, "k1024")) { filter = ""; gemm_case(1, 'N', 'N', 250, 250, 1024, 20); gemm_case(1, 'N', 'N', 250, 250, 250, 20); gemm_case(1, 'N', 'N', 100, 100, 100, 20); return 0; }
     if (!strcmp(filter, "tiles")) { tile_sweep(); return 0; }
     if (!strcmp(filter, "families")) { family_sweep(); return 0; }
     // --- the reference's own benchmark shapes (bench/Bench/Accelerate.hs) ---

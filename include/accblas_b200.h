@@ -367,7 +367,9 @@ typedef enum {
                                        last CTA sums the partials and runs the scalar all-reduce over the peers' buffers           */
     ACCBLAS_TUNE_SGEMM_DIRECT = 17, /* f32 gemm, operand base / pitch off TMA's 16-byte grid, k <= 768: 0 = copy into aligned scratch first
                                        (round 1), default: the mma.sync kernel loads its panels itself (one launch, no scratch)     */
-    ACCBLAS_TUNE_COUNT = 18
+    ACCBLAS_TUNE_DGEMM_DIRECT = 18, /* f64 gemm, operand off TMA's 16-byte grid (odd column count), at most one 32 x 32 tile per SM, k <= 384:
+                                       0 = copy into aligned scratch first (round 1), default: the DMMA kernel loads its panels itself   */
+    ACCBLAS_TUNE_COUNT = 19
 } accblas_tune_t;
 /* Process-wide defaults for threads that never call this: environment variable
  * ACCBLAS_TUNE="knob=value,knob=value" (read once). */

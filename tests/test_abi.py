@@ -71,7 +71,9 @@ def test_kernel_selection_names():
     assert ab.kernel_name(0, "N", "N", *sq(8192)) == "sgemm_tf32x3_tcgen05"
     assert ab.kernel_name(0, "N", "N", *sq(1000)) == "sgemm_tf32x3_tcgen05"      # 128 x 64 tcgen05 tile
     assert ab.kernel_name(0, "N", "N", *sq(500)) == "sgemm_tf32x3_mma"
-    assert ab.kernel_name(0, "N", "N", *sq(250)) == "sgemm_tf32x3_mma"           # via the re-pitch copy
+    assert ab.kernel_name(0, "N", "N", *sq(250)) == "sgemm_tf32x3_mma_direct"    # 1000-byte rows: the kernel loads its panels itself
+    assert ab.kernel_name(0, "N", "N", (250, 802), (802, 250)) in ("sgemm_tf32x3_mma", "sgemm_tf32x3_tcgen05")   # k > 768: via the re-pitch copy
+    assert ab.kernel_name(1, "N", "N", *sq(251)) in ("dgemm_dmma_direct", "dgemm_dmma_tma")  # (direct needs the SM count: GPU box)
     assert ab.kernel_name(3, "H", "N", *sq(4096)) == "zgemm_3m_dmma"
     assert ab.kernel_name(3, "H", "N", *sq(1000)) == "zgemm_dmma_tma"
     assert ab.kernel_name(2, "H", "N", *sq(4096)) == "cgemm_3m_tf32x3_tcgen05"

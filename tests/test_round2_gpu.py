@@ -533,3 +533,40 @@ def test_sgemm_direct_misaligned_operands(cuda):
     C = host(ab.gemm(1, "N", dev(A, cuda), "N", dev(B, cuda)))
     want = A.astype(np.float64) @ B.astype(np.float64)
     assert np.array_equal(np.isnan(C), np.isnan(want)) and np.array_equal(np.isinf(C), np.isinf(want))
+
+
+def test_dgemm_direct_misaligned_operands(cuda):
+    """Double operands with an odd column count (rows 8- but not 16-byte aligned) in a product of at most one 32 x 32 tile
+    per SM with k <= 384: the DMMA kernel loads its panels for the whole K extent itself instead of running behind a
+    re-pitch copy.  Every op pair, alpha, beta; against the wide oracle and against the round-1 path (copy + TMA ring)."""
+    import accblas_b200 as ab
+    dt = O.F64
+    rng = np.random.default_rng(12200)
+    TUNE_DGEMM_DIRECT = 18
+    for (m, n, k) in [(251, 249, 251), (33, 47, 95), (129, 65, 383), (99, 101, 13)]:
+        for oa in "NTH":
+            for ob in "NTH":
+                al, A, B = gemm_inputs(rng, dt, oa, ob, m, n, k)
+                assert ab.kernel_name(dt, oa, ob, A.shape, B.shape) == "dgemm_dmma_direct", (m, n, k, oa, ob)
+                dA, dB = dev(A, cuda), dev(B, cuda)
+                ref = O.gemm(al, oa, A, ob, B, wide=True)
+                C = ab.gemm(al, oa, dA, ob, dB)
+                assert O.gemm_error_units(host(C), ref, A, B, k, alpha=al) <= TOL_UNITS[dt], (m, n, k, oa, ob)
+                ab.set_tuning(TUNE_DGEMM_DIRECT, 0)
+                try:
+                    assert ab.kernel_name(dt, oa, ob, A.shape, B.shape) in ("dgemm_dmma_tma", "gemm_simt_generic")
+                    C0 = ab.gemm(al, oa, dA, ob, dB)
+                finally:
+                    ab.set_tuning(TUNE_DGEMM_DIRECT, -1)
+                assert O.gemm_error_units(host(C0), ref, A, B, k, alpha=al) <= TOL_UNITS[dt]
+    m, n, k = 131, 95, 301
+    al, A, B = gemm_inputs(rng, dt, "T", "N", m, n, k)
+    beta = np.float64(-0.5)
+    Cin = O.uniform(rng, (m, n), dt)
+    assert ab.kernel_name(dt, "T", "N", A.shape, B.shape) == "dgemm_dmma_direct"
+    D = host(ab.gemm(al, "T", dev(A, cuda), "N", dev(B, cuda), beta=beta, Cin=dev(Cin, cuda)))
+    ref = O.gemm(al, "T", A, "N", B, wide=True).astype(np.float64) + beta * Cin
+    assert O.fro(D - ref) <= ex_bound(dt, TOL_UNITS[dt], al, A, B, k, beta, Cin, ref)
+    # one wave only: a product with more 32 x 32 tiles than SMs keeps the copy + ring path
+    A, B = O.uniform(rng, (501, 101), dt), O.uniform(rng, (101, 499), dt)
+    assert ab.kernel_name(dt, "N", "N", A.shape, B.shape) == "dgemm_dmma_tma"
