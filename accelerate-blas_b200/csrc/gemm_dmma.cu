@@ -143,7 +143,7 @@ __device__ __forceinline__ void tile_coords(const DgemmParams &p, int tile, int 
 // epilogue, ptxas gave the small tiles (56-register cap at 7 CTAs / SM) a K loop that recomputes its shared-memory
 // addresses every K-block -- 141 instead of 82 instructions per 16 DMMAs in the 32 x 32 tile, 11 % on every strip of the
 // host wavefront and on 1024^3 (round 2, profiles/r02_strip_ab.jsonl).
-template <typename TL, bool BETA = true>
+template <typename TL, bool BETA = true, int IB = 2>
 __device__ __forceinline__ void dgemm_epilogue(const DgemmParams &p, const double (&acc)[TL::MI][TL::NJ][2],
                                                int m0, int n0, int wm, int wn, int g, int t, int64_t c_off = 0)
 {
@@ -152,6 +152,60 @@ __device__ __forceinline__ void dgemm_epilogue(const DgemmParams &p, const doubl
     const double alpha = p.alpha.get();
     const bool acc_in = BETA && p.beta.on();
     double *const Cb = p.C + c_off;
+    if constexpr (IB > 0) if (acc_in) {
+        // beta * Cin: Cin may be C itself, so the compiler must keep every load behind the preceding store -- one
+        // HBM / L2 round trip per 16 bytes, 32 of them in a row for a 128 x 128 tile (measured: ~20 us per tile, 0.55 ms per
+        // in-place pass over an 8192^2 C; the K-panel host schedule and the multi-GPU chunk pipeline make many such
+        // passes).  A thread only ever reads the elements it writes itself, so the loads of IB rows are issued by hand
+        // before the first store of the batch: IB * NJ round trips overlap.  (IB = 1 in the persistent kernel, whose main loop
+        // sits at the 168-register limit of a 9-warp CTA: a deeper batch there spilt in the fenced variants too.)
+        static_assert(IB == 0 || MI % (IB > 0 ? IB : 1) == 0, "row batches divide the warp tile");
+        const bool cvec = vec && ((p.beta.ld & 1) == 0) && ((reinterpret_cast<uintptr_t>(p.beta.cin) & 15u) == 0);
+        const double *const Cin = p.beta.cin;          // (no batch offset: the strided batch has no beta term)
+        const double beta = p.beta.beta;
+#pragma unroll
+        for (int i0 = 0; i0 < MI; i0 += IB) {
+            double cin[IB][NJ][2];
+#pragma unroll
+            for (int ii = 0; ii < IB; ++ii) {
+                const int64_t r = m0 + wm * MI * 8 + (i0 + ii) * 8 + g;
+#pragma unroll
+                for (int j = 0; j < NJ; ++j) {
+                    const int64_t c = n0 + wn * NJ * 8 + j * 8 + 2 * t;
+                    cin[ii][j][0] = cin[ii][j][1] = 0.0;
+                    if (r < p.m) {
+                        const double *src = Cin + r * p.beta.ld + c;
+                        if (cvec) {
+                            if (c < p.n) { const double2 v = *reinterpret_cast<const double2 *>(src); cin[ii][j][0] = v.x; cin[ii][j][1] = v.y; }
+                        } else {
+                            if (c < p.n) cin[ii][j][0] = src[0];
+                            if (c + 1 < p.n) cin[ii][j][1] = src[1];
+                        }
+                    }
+                }
+            }
+#pragma unroll
+            for (int ii = 0; ii < IB; ++ii) {
+                const int i = i0 + ii;
+                const int64_t r = m0 + wm * MI * 8 + i * 8 + g;
+                if (r >= p.m) continue;
+                double *crow = Cb + r * p.ldc;
+#pragma unroll
+                for (int j = 0; j < NJ; ++j) {
+                    const int64_t c = n0 + wn * NJ * 8 + j * 8 + 2 * t;
+                    const double v0 = fma(beta, cin[ii][j][0], alpha * acc[i][j][0]);
+                    const double v1 = fma(beta, cin[ii][j][1], alpha * acc[i][j][1]);
+                    if (vec) {
+                        if (c < p.n) *reinterpret_cast<double2 *>(crow + c) = make_double2(v0, v1);
+                    } else {
+                        if (c < p.n) crow[c] = v0;
+                        if (c + 1 < p.n) crow[c + 1] = v1;
+                    }
+                }
+            }
+        }
+        return;
+    }
 #pragma unroll
     for (int i = 0; i < MI; ++i) {
         const int64_t r = m0 + wm * MI * 8 + i * 8 + g;
@@ -161,7 +215,7 @@ __device__ __forceinline__ void dgemm_epilogue(const DgemmParams &p, const doubl
         for (int j = 0; j < NJ; ++j) {
             const int64_t c = n0 + wn * NJ * 8 + j * 8 + 2 * t;
             double v0 = alpha * acc[i][j][0], v1 = alpha * acc[i][j][1];
-            if (acc_in) {
+            if (IB == 0 && acc_in) {              // one element at a time (the persistent kernel)
                 if (c < p.n) v0 = p.beta.add(v0, r, c);
                 if (c + 1 < p.n) v1 = p.beta.add(v1, r, c + 1);
             }
@@ -584,7 +638,7 @@ dgemm_dmma_streamk_kernel(const __grid_constant__ CUtensorMap mapA, const __grid
             }
             int tile_m, tile_n;
             tile_coords(p, tile, tile_m, tile_n);
-            dgemm_epilogue<TL>(p, acc, tile_m * BM, tile_n * BN, wm, wn, gq, t);
+            dgemm_epilogue<TL, true, 0>(p, acc, tile_m * BM, tile_n * BN, wm, wn, gq, t);
         }
     }
 }
@@ -1029,7 +1083,10 @@ int launch_dgemm(const GemmArgs &g)
 {
     const bool batched = g.batch > 1;
     const int tile = pick_tile(g.m, g.n, g.k, nullptr, batched ? g.batch : 1);
-    const StreamKPlan pl = (g.no_persistent || batched) ? StreamKPlan{false, 0, 0} : plan_streamk(g.m, g.n, g.k);
+    // beta products take the data-parallel tile unless the persistent schedule is forced: its epilogue batches the Cin loads
+    // (dgemm_epilogue), which the persistent kernel has no registers for
+    const bool beta_dp = has_beta(g) && g_tuning[ACCBLAS_TUNE_STREAMK] < 1;
+    const StreamKPlan pl = (g.no_persistent || batched || beta_dp) ? StreamKPlan{false, 0, 0} : plan_streamk(g.m, g.n, g.k);
     if (pl.use)
         return release_mode(false) == REL_DELAYED ? launch_dgemm_streamk<AK, BKM, REL_DELAYED>(g, pl)
                                                   : launch_dgemm_streamk<AK, BKM, REL_FENCED>(g, pl);

@@ -369,7 +369,9 @@ typedef enum {
                                        (round 1), default: the mma.sync kernel loads its panels itself (one launch, no scratch)     */
     ACCBLAS_TUNE_DGEMM_DIRECT = 18, /* f64 gemm, operand off TMA's 16-byte grid (odd column count), at most one 32 x 32 tile per SM, k <= 384:
                                        0 = copy into aligned scratch first (round 1), default: the DMMA kernel loads its panels itself   */
-    ACCBLAS_TUNE_COUNT = 19
+    ACCBLAS_TUNE_HOST_SCHEDULE = 19, /* accblas_gemm_host: 0 = always the block wavefront, 1 = always K-panel rank updates + row-panel finish,
+                                        default: K-panels when the product is compute-bound against the PCIe link (csrc/host_pipeline.cu) */
+    ACCBLAS_TUNE_COUNT = 20
 } accblas_tune_t;
 /* Process-wide defaults for threads that never call this: environment variable
  * ACCBLAS_TUNE="knob=value,knob=value" (read once). */

@@ -570,3 +570,38 @@ def test_dgemm_direct_misaligned_operands(cuda):
     # one wave only: a product with more 32 x 32 tiles than SMs keeps the copy + ring path
     A, B = O.uniform(rng, (501, 101), dt), O.uniform(rng, (101, 499), dt)
     assert ab.kernel_name(dt, "N", "N", A.shape, B.shape) == "dgemm_dmma_tma"
+
+
+# ------------------------------------------------------------------------------------------ host pipeline, K-panel schedule
+@pytest.mark.parametrize("dt", DTYPES, ids=ids)
+def test_host_pipeline_kpanels(dt, cuda):
+    """accblas_gemm_host with the compute-bound schedule forced (csrc/host_pipeline.cu: K-panel rank updates of the whole C,
+    then the remaining K range row panel by row panel with the downloads underneath): every op pair, ragged extents (last
+    K panel, last row panel), complex alpha; sampled rows against the wide oracle and the whole result against the block
+    wavefront on the same host arrays."""
+    import accblas_b200 as ab
+    TUNE_HOST_SCHEDULE = 19
+    rng = np.random.default_rng(12300 + dt)
+    m, n, k = 1200, 1090, 2700
+    for oa in "NTH":
+        for ob in "NTH":
+            al, A, B = gemm_inputs(rng, dt, oa, ob, m, n, k)
+            ab.set_tuning(TUNE_HOST_SCHEDULE, 1)
+            try:
+                C = ab.gemm(al, oa, A, ob, B)
+            finally:
+                ab.set_tuning(TUNE_HOST_SCHEDULE, -1)
+            rows = np.arange(0, m, 97)
+            Asub = A[rows] if oa == "N" else np.ascontiguousarray(A[:, rows])
+            ref = O.gemm(al, oa, Asub, ob, B, wide=True)
+            tol = TOL_UNITS_TF32X3 if dt in (O.F32, O.C32) else TOL_UNITS[dt]
+            err = O.gemm_error_units(np.ascontiguousarray(C[rows]), ref, Asub, B, k, al)
+            assert err <= tol, (O.NAMES[dt], oa, ob, err)
+            ab.set_tuning(TUNE_HOST_SCHEDULE, 0)
+            ab.set_tuning(4, 1)
+            try:
+                W = ab.gemm(al, oa, A, ob, B)
+            finally:
+                ab.set_tuning(TUNE_HOST_SCHEDULE, -1)
+                ab.set_tuning(4, -1)
+            assert O.gemm_error_units(C, W, A, B, k, al) <= 2 * tol, (O.NAMES[dt], oa, ob, "K-panels vs wavefront")
