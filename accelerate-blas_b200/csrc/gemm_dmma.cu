@@ -60,7 +60,9 @@ using Tile32x32   = Tile<2, 2, 2, 2, 3, 7>;   // 7 CTAs per SM: 1024 tiles (dgem
 using Tile32x32Deep = Tile<2, 2, 2, 2, 8, 3>;
 // (Round 2, measured and NOT kept: dealing the K-blocks to two groups of consumer warps inside the CTA -- 250^3: 7.10 -> 6.91 us
 //  of kernel time, 250 x 250 x 1024: 18.9 -> 18.8; splitting the accumulators by k-step -- 1000^3: 70 -> 82 us; loading the
-//  panels with plain loads instead of the ring -- no change.  profiles/r02_small_shapes.md.)
+//  panels with plain loads instead of the ring -- no change; a 32 x 16 tile (twice the CTAs, half the work each) -- 7.04 us;
+//  polling the barriers with test_wait instead of try_wait -- 7.17; three TMA boxes per K-block instead of two -- 7.10.
+//  The one-wave kernel costs ~295 ns per K-block whatever is changed.  profiles/r02_small_shapes.md.)
 
 __device__ __forceinline__ void dmma(double &d0, double &d1, double a, double b) {
     asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
@@ -1083,10 +1085,7 @@ int launch_dgemm(const GemmArgs &g)
 {
     const bool batched = g.batch > 1;
     const int tile = pick_tile(g.m, g.n, g.k, nullptr, batched ? g.batch : 1);
-    // beta products take the data-parallel tile unless the persistent schedule is forced: its epilogue batches the Cin loads
-    // (dgemm_epilogue), which the persistent kernel has no registers for
-    const bool beta_dp = has_beta(g) && g_tuning[ACCBLAS_TUNE_STREAMK] < 1;
-    const StreamKPlan pl = (g.no_persistent || batched || beta_dp) ? StreamKPlan{false, 0, 0} : plan_streamk(g.m, g.n, g.k);
+    const StreamKPlan pl = (g.no_persistent || batched) ? StreamKPlan{false, 0, 0} : plan_streamk(g.m, g.n, g.k);
     if (pl.use)
         return release_mode(false) == REL_DELAYED ? launch_dgemm_streamk<AK, BKM, REL_DELAYED>(g, pl)
                                                   : launch_dgemm_streamk<AK, BKM, REL_FENCED>(g, pl);
