@@ -91,7 +91,7 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def ncu_traffic(name="r02_dgemm_nn_8192_ncu.txt"):
+def ncu_traffic(name="r02b_dgemm_nn_8192_ncu.txt"):
     """dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the committed
     `ncu --set full` summary of the same kernel and shape (profiles/; tools/ncu_capture.sh)."""
     unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
@@ -297,7 +297,7 @@ def run_single(args):
         "config": workload_config(1),
         "roofline": {"bound": "tensor", "achieved": round(flops / kernel_ms * 1e-9, 3), "peak": round(peak, 2),
                      "unit": "TFLOP/s", "frac": round(flops / kernel_ms * 1e-9 / peak, 4), "traffic": ncu_traffic(),
-                     "traffic_unit": "bytes per launch (dram read + write, profiles/r02_dgemm_nn_8192_ncu.txt); "
+                     "traffic_unit": "bytes per launch (dram read + write, profiles/r02b_dgemm_nn_8192_ncu.txt); "
                                      "algorithmic bytes 1 610 612 736",
                      "kernel": kernel_desc, "flops_per_launch": flops,
                      "peak_source": peak_src + "; MEASURED_PEAKS.json carries no FP64 figure "
