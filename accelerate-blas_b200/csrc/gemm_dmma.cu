@@ -1086,9 +1086,14 @@ int launch_dgemm(const GemmArgs &g)
     const bool batched = g.batch > 1;
     const int tile = pick_tile(g.m, g.n, g.k, nullptr, batched ? g.batch : 1);
     const StreamKPlan pl = (g.no_persistent || batched) ? StreamKPlan{false, 0, 0} : plan_streamk(g.m, g.n, g.k);
-    if (pl.use)
-        return release_mode(false) == REL_DELAYED ? launch_dgemm_streamk<AK, BKM, REL_DELAYED>(g, pl)
-                                                  : launch_dgemm_streamk<AK, BKM, REL_FENCED>(g, pl);
+    if (pl.use) {
+        // Products of at most two whole-tile rounds (2048^3: 256 tiles) spend most of their time in the stream-K region and
+        // its short segments, where the fence of every release weighs more than the delayed variant's spills: 2048^3
+        // 513 -> 503 us (cuBLAS 496); 4096^3 3852 us either way; 8192^3 30.54 fenced against 30.60 delayed.
+        const int knob = g_tuning[ACCBLAS_TUNE_RELEASE];
+        const bool delayed = knob == 2 || (knob < 0 && pl.dp_rounds <= 2);
+        return delayed ? launch_dgemm_streamk<AK, BKM, REL_DELAYED>(g, pl) : launch_dgemm_streamk<AK, BKM, REL_FENCED>(g, pl);
+    }
     const int rel = release_mode(tile == 0);
     static const int deep = [] { const char *e = getenv("ACCBLAS_DMMA_DEEP"); return e ? atoi(e) : 1; }();
     switch (tile) {

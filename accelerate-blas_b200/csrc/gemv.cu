@@ -272,8 +272,17 @@ inline int slab_cluster(int64_t slabs, int64_t rows)
     double best_eff = 0.0;
     // clusters of 8 measured SLOWER than no split (2000 x 3000 doubles: 14.3 us against 10.3 us for R = 2 or 4 and 12.3 us
     // for R = 1, profiles/r02_gemv_t_cluster.txt): placement of an 8-CTA cluster needs 8 free slots in one GPC
+    // Fewer than two CTAs per SM: the kernel is bound by the bytes in flight per SM, not by balance -- split the rows once
+    // (twice when even that leaves SMs empty).  Kernel times at 1000 x 2000 (ncu, us; R = 1 / 2 / 4): Float 5.6 / 5.0 / 5.1,
+    // Double 5.9 / 5.2 / 5.4, Complex Float 7.2 / 5.9 / 6.1, Complex Double 6.7 / 6.2 / 9.6 (cuBLAS 5.7 / 6.3 / 6.4 / 7.9);
+    // the balance rule below had picked 1, 1, 1 and 4 for them.
+    const int64_t min_rows = 2 * SLAB_RG * SLAB_UNROLL / 4;
+    if (slabs < 2 * sms) {
+        if (rows / 2 < min_rows) return 1;
+        return (2 * slabs < sms && rows / 4 >= min_rows) ? 4 : 2;
+    }
     for (int R = 1; R <= 4; R *= 2) {
-        if (R > 1 && rows / R < 2 * SLAB_RG * SLAB_UNROLL / 4) break;
+        if (R > 1 && rows / R < min_rows) break;
         const int64_t total = slabs * R;
         const double eff = (double)total / (double)(((total + sms - 1) / sms) * sms);
         if (eff > best_eff * 1.04) { best = R; best_eff = eff; }
@@ -340,10 +349,12 @@ int gemv_typed(cudaStream_t st, int opA, int64_t rowsA, int64_t colsA, const voi
 
     const bool conj = Scalar<T>::cplx && opA == ACCBLAS_OP_H;
     const int64_t nv = aligned ? colsA / VEC : colsA;
-    static const int64_t slab_max = [] { const char *e = getenv("ACCBLAS_GEMV_T_SLAB_MAX"); return e ? atoll(e) : (int64_t)64 << 20; }();
+    static const int64_t slab_max = [] { const char *e = getenv("ACCBLAS_GEMV_T_SLAB_MAX"); return e ? atoll(e) : (int64_t)128 << 20; }();
     if ((int64_t)sizeof(T) * rowsA * colsA <= slab_max) {       // one launch, no scratch
         const int64_t slabs = (nv + SLAB_CV - 1) / SLAB_CV;
-        const int R = slab_cluster(slabs, rowsA);
+        // 64 .. 128 MiB (Complex Double 2000 x 3000 = 96 MB): one plain launch.  Kernel times there: slab R = 1 18.0 us, R = 2
+        // 22.5, R = 4 21.1, the two-pass kernels 17.3 + 8.1 (cuBLAS 14.2).
+        const int R = (int64_t)sizeof(T) * rowsA * colsA > ((int64_t)64 << 20) ? 1 : slab_cluster(slabs, rowsA);
         cudaLaunchConfig_t cfg{};
         cfg.gridDim = dim3((unsigned)(slabs * R));
         cfg.blockDim = dim3(SLAB_CV * SLAB_RG);
