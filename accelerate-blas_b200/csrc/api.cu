@@ -186,6 +186,16 @@ Family pick_family(const GemmArgs &g)
         if (want == 1 && mma) return FAM_MMA;
         if (want == 2 && tc) return cgemm_3m_wanted(g) ? FAM_C3M : FAM_TC;
         const double work = (g.dtype == ACCBLAS_C32 ? 4.0 : 1.0) * (double)g.m * (double)g.n * (double)g.k;
+        if (tc && !mma && work < kTcMinWork && want != 2 && g_gemm_path == 0) {
+            // Small product whose operands only miss TMA's alignment (250 x 250 x 512 Floats): the pack pass + tcgen05 tiles
+            // measured 24.6 us there against cuBLAS 10.3; the mma.sync family serves it -- through its direct variant or behind
+            // the re-pitch copy (gemm_repitched) -- if it would take the aligned product.
+            GemmArgs h = g;
+            const int64_t q = g.dtype == ACCBLAS_C32 ? 2 : 4;
+            h.A = h.B = nullptr;
+            h.lda = (g.lda + q - 1) / q * q; h.ldb = (g.ldb + q - 1) / q * q;
+            if (sgemm_mma_eligible(h)) return FAM_GENERIC;
+        }
         if (tc && (work >= kTcMinWork || !mma)) return cgemm_3m_wanted(g) ? FAM_C3M : FAM_TC;
         if (mma) return FAM_MMA;
     }

@@ -192,6 +192,10 @@ struct GemmArgs {
     // strided batch (accblas_gemm_strided_batched): `batch` independent products, operand b of the batch at
     // base + b * stride (elements; stride 0 = the same operand for every product).  batch <= 1: one product.
     int64_t batch, strideA, strideB, strideC;
+    // internal (gemm_dmma.cu): split-K over idle SMs -- ksplit slices of the K-blocks, slice s writes its alpha-scaled partial
+    // product to ksplit_ws + s * m * n (row pitch n); a reduce kernel sums the slices into C.  0 / 1: no split.
+    int ksplit;
+    void *ksplit_ws;
 };
 
 template <typename T> inline bool scalar_is_zero(const T &v);
@@ -222,7 +226,8 @@ int gemm_device(GemmArgs &g);                         // api.cu : validate + dis
 int gemm_host_pipeline(const GemmArgs &g, const void *A_host, const void *B_host,
                        void *C_host);                 // host_pipeline.cu : upload / multiply / download wavefront
 int gemm_generic(const GemmArgs &g);                  // gemm_generic.cu : any shape
-int gemm_rank1(const GemmArgs &g);                    // gemm_generic.cu : k == 1 (outer product `><`)
+int gemm_rank1(const GemmArgs &g);
+int splitk_reduce(const GemmArgs &g);                //                   sum of the split-K slices (ksplit_ws -> C)                    // gemm_generic.cu : k == 1 (outer product `><`)
 bool dgemm_dmma_eligible(const GemmArgs &g);          // gemm_dmma.cu    : f64 / c64 on DMMA
 int  dgemm_dmma(const GemmArgs &g);
 bool dgemm_direct_eligible(const GemmArgs &g);        //                   f64, misaligned operands, one wave of 32 x 32 tiles, whole K in smem

@@ -117,6 +117,9 @@ struct DgemmParams {
     // (tma::make_2d_batched) and product b writes C + b * stride_c.  tiles_per_batch == 0: one product, 2-D maps.
     int tiles_per_batch, plane_a, plane_b;   // plane_x = 1: operand x advances with the batch index (0: shared)
     int64_t stride_c;
+    // split-K (one product, 2-D maps): gridDim.x = slices * tiles_per_batch, slice s multiplies K-blocks
+    // [s * kb_per_slice, (s + 1) * kb_per_slice) and writes plane s of the scratch (C + s * stride_c).  0: whole K.
+    int kb_per_slice;
     Alpha<double> alpha;
     BetaC<double> beta;  // + beta * Cin (accblas_gemm_ex); cin == nullptr: C is write-only
     double *C;
@@ -252,14 +255,19 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
     int tile_m, tile_n, tile = blockIdx.x, pa = -1, pb = -1;        // pa / pb: batch plane of A / B (-1: 2-D maps)
+    int kb_begin = 0, kblocks = (int)((p.k + BK - 1) / BK);
     if (p.tiles_per_batch > 0) {
         const int b = tile / p.tiles_per_batch;
         tile -= b * p.tiles_per_batch;
-        pa = b * p.plane_a; pb = b * p.plane_b;
+        if (p.kb_per_slice > 0) {            // split-K: b is the K slice, the operands are the same 2-D arrays
+            kb_begin = b * p.kb_per_slice;
+            kblocks = max(0, min(p.kb_per_slice, kblocks - kb_begin));
+        } else {
+            pa = b * p.plane_a; pb = b * p.plane_b;
+        }
     }
     tile_coords(p, tile, tile_m, tile_n);
     const int m0 = tile_m * BM, n0 = tile_n * BN;
-    const int kblocks = (int)((p.k + BK - 1) / BK);
 
     if constexpr (DIRECT) {
         constexpr int NW = kDirectThreads / 32, U = 16;
@@ -343,7 +351,7 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
                     const uint32_t full = bar_base + 8 * s;
                     const uint32_t sa = smem_base + s * STAGE_BYTES, sb = sa + A_BYTES;
                     tma::mbar_expect_tx(full, STAGE_BYTES);
-                    const int k0 = (rev ? kblocks - 1 - kb : kb) * BK;
+                    const int k0 = (kb_begin + (rev ? kblocks - 1 - kb : kb)) * BK;
                     if (AK) tma::load_box(sa, &mapA, full, k0, m0, pa);
                     else if (p.a_one_box) tma::load_3d(sa, &mapA, full, 0, k0, m0 >> 4);
                     else
@@ -696,6 +704,7 @@ struct ZgemmParams {
     int tiles_m, tiles_n;
     int tiles_per_batch, plane_a, plane_b;   // strided batch, as in DgemmParams (0: one product, 2-D maps)
     int64_t stride_c;
+    int kb_per_slice;                        // split-K, as in DgemmParams (0: whole K)
 };
 
 template <bool AK, bool BKM, bool CONJA, bool CONJB, typename TL, int REL, bool BETA>
@@ -712,12 +721,18 @@ zgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
 
     constexpr int GROUP = 16;
     int tile_m, tile_n, pa = -1, pb = -1;                          // pa / pb: batch plane of A / B (-1: 2-D maps)
+    int kb_begin = 0, kblocks = (int)((p.k + ZBK - 1) / ZBK);
     {
         int tile = blockIdx.x;
         if (p.tiles_per_batch > 0) {
             const int b = tile / p.tiles_per_batch;
             tile -= b * p.tiles_per_batch;
-            pa = b * p.plane_a; pb = b * p.plane_b;
+            if (p.kb_per_slice > 0) {        // split-K: b is the K slice
+                kb_begin = b * p.kb_per_slice;
+                kblocks = max(0, min(p.kb_per_slice, kblocks - kb_begin));
+            } else {
+                pa = b * p.plane_a; pb = b * p.plane_b;
+            }
         }
         const int per_group = GROUP * p.tiles_n;
         const int grp = tile / per_group;
@@ -728,7 +743,6 @@ zgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
         tile_n = in_grp / gsz;
     }
     const int m0 = tile_m * ZBM, n0 = tile_n * ZBN;
-    const int kblocks = (int)((p.k + ZBK - 1) / ZBK);
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < ZSTAGES; ++s) {
@@ -752,7 +766,7 @@ zgemm_dmma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
                 const uint32_t full = bar_base + 8 * s;
                 const uint32_t sa = smem_base + s * ZSTAGE_BYTES, sb = sa + ZA_BYTES;
                 tma::mbar_expect_tx(full, ZSTAGE_BYTES);
-                const int k0 = kb * ZBK;
+                const int k0 = (kb_begin + kb) * ZBK;
                 // tensor maps are over doubles: inner coordinates are 2 x the complex index
                 if (AK) tma::load_box(sa, &mapA, full, 2 * k0, m0, pa);
                 else
@@ -938,6 +952,8 @@ void fill_params(DgemmParams &p, const GemmArgs &g, int BM, int BN)
     p.tiles_n = (int)((g.n + BN - 1) / BN);
     p.group = g_tuning[ACCBLAS_TUNE_RASTER_GROUP] > 0 ? g_tuning[ACCBLAS_TUNE_RASTER_GROUP] : 16;
     p.tiles_per_batch = 0; p.plane_a = p.plane_b = 0; p.stride_c = 0;
+    p.kb_per_slice = 0;
+    p.Ag = p.Bg = nullptr; p.lda = p.ldb = 0;
 }
 
 template <bool AK, bool BKM, typename TL, int REL, bool BETA>
@@ -966,6 +982,13 @@ int launch_dgemm_tile(const GemmArgs &g)
         p.stride_c = g.strideC;
         p.snake_waves = 0;
         tiles *= g.batch;
+    } else if (g.ksplit > 1) {
+        const int kblocks = (int)((g.k + BK - 1) / BK);
+        p.tiles_per_batch = (int)tiles;
+        p.kb_per_slice = (kblocks + g.ksplit - 1) / g.ksplit;
+        p.C = static_cast<double *>(g.ksplit_ws); p.ldc = g.n; p.stride_c = g.m * g.n;
+        p.snake_waves = 0;
+        tiles *= g.ksplit;
     }
     if (tiles > 0x7fffffff) return ACCBLAS_ERR_SHAPE;
     dgemm_dmma_kernel<AK, BKM, TL, REL, BETA><<<(unsigned)tiles, TL::THREADS, SMEM_BYTES, g.stream>>>(mapA, mapB, p);
@@ -1099,10 +1122,31 @@ int launch_dgemm(const GemmArgs &g)
     switch (tile) {
     case 1:  return launch_dgemm_tile_rel<AK, BKM, Tile64x128>(g, rel);
     case 2:  return launch_dgemm_tile_rel<AK, BKM, Tile64x64>(g, rel);
-    case 3:
+    case 3: {
+        // Split-K over idle SMs: a grid of at most half a wave of 32 x 32 tiles with a long K (250 x 250 x 1024: 64 CTAs
+        // walking 64 K-blocks each, 19.4 us against cuBLAS's split-K 13.1) is cut into up to 16 K slices of at least 8
+        // K-blocks -- one launch, slice = the batch index of the strided-batch grid -- whose alpha-scaled partials a second
+        // small kernel sums in slice order (deterministic).  The reference's cubes (k <= 1000 at >= 1000 tiles, 250^3:
+        // 16 K-blocks) are untouched.
+        const int64_t tiles32 = ((g.m + 31) / 32) * ((g.n + 31) / 32), kblocks = (g.k + BK - 1) / BK;
+        if (!batched && !has_beta(g) && g.ksplit == 0 && g_tuning[ACCBLAS_TUNE_SPLITK] != 0 && 2 * tiles32 <= sm_count() && kblocks >= 32) {
+            // two small CTAs per SM overlap their latency-bound K loops; a split must save more than the reduce launch costs
+            const int S = (int)std::min<int64_t>(std::min<int64_t>(2 * sm_count() / tiles32, kblocks / 8), 16);
+            if (S >= 2 && kblocks * (S - 1) >= 32 * (int64_t)S) {
+                GemmArgs h = g;
+                h.ksplit = S;
+                ACC_CUDA(scratch_alloc(&h.ksplit_ws, sizeof(double) * (size_t)S * (size_t)g.m * (size_t)g.n, g.stream));
+                int st = launch_dgemm_tile_rel<AK, BKM, Tile32x32Deep>(h, rel);
+                if (st == ACCBLAS_OK) st = splitk_reduce(h);
+                const cudaError_t e = cudaFreeAsync(h.ksplit_ws, g.stream);
+                if (st == ACCBLAS_OK && e != cudaSuccess) return cuda_fail(e, "cudaFreeAsync");
+                return st;
+            }
+        }
         if (deep && ((g.m + 31) / 32) * ((g.n + 31) / 32) * (batched ? g.batch : 1) <= 3 * (int64_t)sm_count())
             return launch_dgemm_tile_rel<AK, BKM, Tile32x32Deep>(g, rel);
         return launch_dgemm_tile_rel<AK, BKM, Tile32x32>(g, rel);
+    }
     default: return launch_dgemm_tile_rel<AK, BKM, Tile128x128>(g, rel);
     }
 }
@@ -1138,11 +1182,18 @@ int launch_zgemm_tile(const GemmArgs &g)
     p.tiles_n = (int)((g.n + ZBN - 1) / ZBN);
     int64_t tiles = (int64_t)p.tiles_m * p.tiles_n;
     p.tiles_per_batch = 0; p.plane_a = p.plane_b = 0; p.stride_c = 0;
+    p.kb_per_slice = 0;
     if (batched) {
         p.tiles_per_batch = (int)tiles;
         p.plane_a = g.strideA ? 1 : 0; p.plane_b = g.strideB ? 1 : 0;
         p.stride_c = g.strideC;
         tiles *= g.batch;
+    } else if (g.ksplit > 1) {
+        const int kblocks = (int)((g.k + ZBK - 1) / ZBK);
+        p.tiles_per_batch = (int)tiles;
+        p.kb_per_slice = (kblocks + g.ksplit - 1) / g.ksplit;
+        p.C = static_cast<double2 *>(g.ksplit_ws); p.ldc = g.n; p.stride_c = g.m * g.n;
+        tiles *= g.ksplit;
     }
     if (tiles > 0x7fffffff) return ACCBLAS_ERR_SHAPE;
     zgemm_dmma_kernel<AK, BKM, CA, CB, TL, REL, BETA><<<(unsigned)tiles, TL::THREADS, TL::SMEM_BYTES, g.stream>>>(mapA, mapB, p);
@@ -1181,8 +1232,26 @@ int launch_zgemm(const GemmArgs &g)
     switch (tile) {
     case 1:  return delayed ? launch_zgemm_tile<AK, BKM, CA, CB, ZTile64x64, REL_DELAYED, true>(g)
                      : beta ? launch_zgemm_tile<AK, BKM, CA, CB, ZTile64x64, REL_FENCED, true>(g) : launch_zgemm_tile<AK, BKM, CA, CB, ZTile64x64, REL_FENCED, false>(g);
-    case 2:  return delayed ? launch_zgemm_tile<AK, BKM, CA, CB, ZTile32x32, REL_DELAYED, true>(g)
+    case 2: {
+        // split-K over idle SMs, as for the real 32 x 32 tile (launch_dgemm); a complex K-block is 8 wide
+        const int64_t tiles32 = ((g.m + 31) / 32) * ((g.n + 31) / 32), kblocks = (g.k + ZBK - 1) / ZBK;
+        if (g.batch <= 1 && !beta && !delayed && g.ksplit == 0 && g_tuning[ACCBLAS_TUNE_SPLITK] != 0 && 2 * tiles32 <= sm_count() && kblocks >= 32) {
+            // two small CTAs per SM overlap their latency-bound K loops; a split must save more than the reduce launch costs
+            const int S = (int)std::min<int64_t>(std::min<int64_t>(2 * sm_count() / tiles32, kblocks / 8), 16);
+            if (S >= 2 && kblocks * (S - 1) >= 24 * (int64_t)S) {
+                GemmArgs h = g;
+                h.ksplit = S;
+                ACC_CUDA(scratch_alloc(&h.ksplit_ws, sizeof(double2) * (size_t)S * (size_t)g.m * (size_t)g.n, g.stream));
+                int st = launch_zgemm_tile<AK, BKM, CA, CB, ZTile32x32, REL_FENCED, false>(h);
+                if (st == ACCBLAS_OK) st = splitk_reduce(h);
+                const cudaError_t e = cudaFreeAsync(h.ksplit_ws, g.stream);
+                if (st == ACCBLAS_OK && e != cudaSuccess) return cuda_fail(e, "cudaFreeAsync");
+                return st;
+            }
+        }
+        return delayed ? launch_zgemm_tile<AK, BKM, CA, CB, ZTile32x32, REL_DELAYED, true>(g)
                      : beta ? launch_zgemm_tile<AK, BKM, CA, CB, ZTile32x32, REL_FENCED, true>(g) : launch_zgemm_tile<AK, BKM, CA, CB, ZTile32x32, REL_FENCED, false>(g);
+    }
     default: return delayed ? launch_zgemm_tile<AK, BKM, CA, CB, ZTile128x64, REL_DELAYED, true>(g)
                      : beta ? launch_zgemm_tile<AK, BKM, CA, CB, ZTile128x64, REL_FENCED, true>(g) : launch_zgemm_tile<AK, BKM, CA, CB, ZTile128x64, REL_FENCED, false>(g);
     }

@@ -10,6 +10,7 @@
 // operands staged k-major in shared memory; global reads are coalesced along the
 // stored row whichever op is requested.
 #include "common.cuh"
+#include <algorithm>
 
 namespace accblas {
 namespace {
@@ -219,6 +220,42 @@ int gemm_generic(const GemmArgs &g)
     case ACCBLAS_F64: return launch_typed<double>(g);
     case ACCBLAS_C32: return launch_typed<float2>(g);
     default:          return launch_typed<double2>(g);
+    }
+}
+
+
+// ---------------------------------------------------------------------------------------------------------------
+// split-K (gemm_dmma.cu, gemm_mma_tf32.cu): the sum of the K slices' alpha-scaled partial products, in slice order
+//     C[r][c] = sum_s P[s][r][c],   P = g.ksplit_ws (g.ksplit planes of m x n, row pitch n),  C with row pitch g.ldc
+// ---------------------------------------------------------------------------------------------------------------
+namespace {
+template <typename T>
+__global__ void __launch_bounds__(256) splitk_reduce_kernel(const T *__restrict__ P, int slices, int64_t m, int64_t n, T *__restrict__ C, int64_t ldc)
+{
+    const int64_t total = m * n;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        T acc = P[i];
+        for (int sl = 1; sl < slices; ++sl) acc = add_s(acc, P[(int64_t)sl * total + i]);
+        const int64_t r = i / n;
+        C[r * ldc + (i - r * n)] = acc;
+    }
+}
+template <typename T> int launch_splitk_reduce(const GemmArgs &g)
+{
+    const int64_t total = g.m * g.n;
+    const unsigned blocks = (unsigned)std::min<int64_t>((total + 255) / 256, 4 * (int64_t)sm_count());
+    splitk_reduce_kernel<T><<<blocks, 256, 0, g.stream>>>(static_cast<const T *>(g.ksplit_ws), g.ksplit, g.m, g.n, static_cast<T *>(g.C), g.ldc);
+    return check_launch("splitk_reduce_kernel");
+}
+}  // namespace
+
+int splitk_reduce(const GemmArgs &g)
+{
+    switch (g.dtype) {
+    case ACCBLAS_F32: return launch_splitk_reduce<float>(g);
+    case ACCBLAS_F64: return launch_splitk_reduce<double>(g);
+    case ACCBLAS_C32: return launch_splitk_reduce<float2>(g);
+    default:          return launch_splitk_reduce<double2>(g);
     }
 }
 

@@ -90,8 +90,20 @@ struct SgemmMmaParams {
     int tiles_m, tiles_n;
     int tiles_per_batch, plane_a, plane_b;   // strided batch as in gemm_dmma.cu's DgemmParams (0: one product, 2-D maps)
     int64_t stride_c;                        // ELEMENTS (complex elements for c32) between the outputs of the batch
+    int kb_per_slice;                        // split-K as in gemm_dmma.cu: the batch index is a K slice of this many K-blocks (0: whole K)
     Refit32 refit;             // non-finite sums are recomputed in plain FP32 from the caller's operands (refit.cuh)
 };
+
+// the K range [k0, k0 + len) of a product as its own refit problem (split-K: a slice recomputes ITS inner product);
+// fpe = floats per element
+__device__ __forceinline__ Refit32 slice_refit(Refit32 f, int k0, int len, int fpe)
+{
+    if (k0 == 0 && len >= f.k) return f;
+    f.A += (int64_t)fpe * (f.ta ? (int64_t)k0 * f.lda : k0);
+    f.B += (int64_t)fpe * (f.tb ? k0 : (int64_t)k0 * f.ldb);
+    f.k = min((int64_t)len, f.k - k0);
+    return f;
+}
 
 __device__ __forceinline__ void raster(const SgemmMmaParams &p, int &tile_m, int &tile_n, int &pa, int &pb)
 {
@@ -139,7 +151,12 @@ sgemm_mma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
     int tile_m, tile_n, pa, pb;
     raster(p, tile_m, tile_n, pa, pb);
     const int m0 = tile_m * BM, n0 = tile_n * BN;
-    const int kblocks = (int)((p.k + BK - 1) / BK);
+    int kb_begin = 0, kblocks = (int)((p.k + BK - 1) / BK);
+    if (p.kb_per_slice > 0) {                 // split-K: the batch index is the K slice; operands are the same 2-D arrays
+        kb_begin = (int)(blockIdx.x / p.tiles_per_batch) * p.kb_per_slice;
+        kblocks = max(0, min(p.kb_per_slice, kblocks - kb_begin));
+        pa = pb = -1;
+    }
 
     if constexpr (DIRECT) {
         // ---- every warp: this CTA's panels, all K-blocks, into stage kb = smem_base + kb * STAGE_BYTES ----
@@ -221,7 +238,7 @@ sgemm_mma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                     const uint32_t full = bar_base + 8 * s;
                     const uint32_t sa = smem_base + s * STAGE_BYTES, sb = sa + A_BYTES;
                     tma::mbar_expect_tx(full, STAGE_BYTES);
-                    const int k0 = kb * BK;
+                    const int k0 = (kb_begin + kb) * BK;
                     if (AK) tma::load_box(sa, &mapA, full, k0, m0, pa);
                     else
     #pragma unroll
@@ -335,7 +352,7 @@ sgemm_mma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                     for (int e = 0; e < 4; ++e) {
                         const int64_t r = m0 + wm * MI * 16 + i * 16 + (e >> 1) * 8 + g;
                         const int64_t c = n0 + wn * NJ * 8 + j * 8 + 2 * t + (e & 1);
-                        tot[i][j][e] = refit_real(p.refit, tot[i][j][e], r, c, r < p.m && c < p.n, batch);
+                        tot[i][j][e] = refit_real(slice_refit(p.refit, kb_begin * BK, kblocks * BK, 1), tot[i][j][e], r, c, r < p.m && c < p.n, batch);
                     }
         }
     }
@@ -395,7 +412,12 @@ cgemm_mma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
     int tile_m, tile_n, pa, pb;
     raster(p, tile_m, tile_n, pa, pb);
     const int m0 = tile_m * BM, n0 = tile_n * BN;
-    const int kblocks = (int)((p.k + BK - 1) / BK);
+    int kb_begin = 0, kblocks = (int)((p.k + BK - 1) / BK);
+    if (p.kb_per_slice > 0) {                 // split-K: the batch index is the K slice; operands are the same 2-D arrays
+        kb_begin = (int)(blockIdx.x / p.tiles_per_batch) * p.kb_per_slice;
+        kblocks = max(0, min(p.kb_per_slice, kblocks - kb_begin));
+        pa = pb = -1;
+    }
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < STAGES; ++s) {
@@ -416,7 +438,7 @@ cgemm_mma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                 const uint32_t full = bar_base + 8 * s;
                 const uint32_t sa = smem_base + s * STAGE_BYTES, sb = sa + A_BYTES;
                 tma::mbar_expect_tx(full, STAGE_BYTES);
-                const int k0 = kb * BK;
+                const int k0 = (kb_begin + kb) * BK;
                 // tensor maps are over floats: inner coordinates are 2 x the complex index
                 if (AK) tma::load_box(sa, &mapA, full, 2 * k0, m0, pa);
                 else
@@ -528,7 +550,7 @@ cgemm_mma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                     for (int e = 0; e < 4; ++e) {
                         const int64_t r = m0 + wm * MI * 16 + i * 16 + (e >> 1) * 8 + g;
                         const int64_t c = n0 + wn * NJ * 8 + j * 8 + 2 * t + (e & 1);
-                        const float2 v = refit_cplx(p.refit, make_float2(tre[i][j][e], tim[i][j][e]), r, c, r < p.m && c < p.n, batch);
+                        const float2 v = refit_cplx(slice_refit(p.refit, kb_begin * BK, kblocks * BK, 2), make_float2(tre[i][j][e], tim[i][j][e]), r, c, r < p.m && c < p.n, batch);
                         tre[i][j][e] = v.x; tim[i][j][e] = v.y;
                     }
         }
@@ -580,7 +602,15 @@ bool mma_maps(CUtensorMap *mapA, CUtensorMap *mapB, const GemmArgs &g, int fpe, 
 int64_t mma_batch_grid(SgemmMmaParams &p, const GemmArgs &g)
 {
     int64_t tiles = (int64_t)p.tiles_m * p.tiles_n;
-    p.tiles_per_batch = 0; p.plane_a = p.plane_b = 0; p.stride_c = 0;
+    p.tiles_per_batch = 0; p.plane_a = p.plane_b = 0; p.stride_c = 0; p.kb_per_slice = 0;
+    if (g.ksplit > 1 && g.batch <= 1) {              // split-K: slices as the batch index, partials into the scratch planes
+        const int bk = g.dtype == ACCBLAS_C32 ? 16 : 32;
+        const int kblocks = (int)((g.k + bk - 1) / bk);
+        p.tiles_per_batch = (int)tiles;
+        p.kb_per_slice = (kblocks + g.ksplit - 1) / g.ksplit;
+        p.C = static_cast<float *>(g.ksplit_ws); p.ldc = g.n; p.stride_c = g.m * g.n;
+        return tiles * g.ksplit;
+    }
     if (g.batch > 1) {
         p.tiles_per_batch = (int)tiles;
         p.plane_a = g.strideA ? 1 : 0; p.plane_b = g.strideB ? 1 : 0;
@@ -635,7 +665,7 @@ int launch_sgemm_mma_direct(const GemmArgs &g)
     p.refit = make_refit32(g);                    // also carries the operand pointers and pitches the loader reads
     p.tiles_m = (int)((g.m + TL::BM - 1) / TL::BM);
     p.tiles_n = (int)((g.n + TL::BN - 1) / TL::BN);
-    p.tiles_per_batch = 0; p.plane_a = p.plane_b = 0; p.stride_c = 0;
+    p.tiles_per_batch = 0; p.plane_a = p.plane_b = 0; p.stride_c = 0; p.kb_per_slice = 0;
     const int64_t tiles = (int64_t)p.tiles_m * p.tiles_n;
     if (tiles > 0x7fffffff) return ACCBLAS_ERR_SHAPE;
     const int kblocks = (int)((g.k + 31) / 32);
@@ -690,12 +720,39 @@ int pick(const TileModel *tm, int count, int forced, int64_t m, int64_t n, int64
     return best;
 }
 
+// Split-K over idle SMs for the 32 x 32 tiles (as in gemm_dmma.cu): at most half a wave of tiles, a long K -> up to 16 K
+// slices as the batch index of ONE launch, alpha-scaled partials into scratch, summed in slice order by splitk_reduce.
+int splitk_slices(const GemmArgs &g, int bk)
+{
+    if (g.batch > 1 || has_beta(g) || g.ksplit != 0 || g_tuning[ACCBLAS_TUNE_SPLITK] == 0) return 0;
+    const int64_t tiles32 = ((g.m + 31) / 32) * ((g.n + 31) / 32), kblocks = (g.k + bk - 1) / bk;
+    if (2 * tiles32 > sm_count() || kblocks < 32) return 0;
+    const int S = (int)std::min<int64_t>(std::min<int64_t>(2 * sm_count() / tiles32, kblocks / 8), 16);
+    return (S >= 2 && kblocks * (S - 1) >= 24 * (int64_t)S) ? S : 0;
+}
+template <typename Launch>
+int with_splitk(const GemmArgs &g, int S, Launch launch)
+{
+    GemmArgs h = g;
+    h.ksplit = S;
+    ACC_CUDA(scratch_alloc(&h.ksplit_ws, elem_size(g.dtype) * (size_t)S * (size_t)g.m * (size_t)g.n, g.stream));
+    int st = launch(h);
+    if (st == ACCBLAS_OK) st = splitk_reduce(h);
+    const cudaError_t e = cudaFreeAsync(h.ksplit_ws, g.stream);
+    if (st == ACCBLAS_OK && e != cudaSuccess) return cuda_fail(e, "cudaFreeAsync");
+    return st;
+}
+
 template <bool AK, bool BKM>
 int sgemm_mma_tiles(const GemmArgs &g)
 {
     switch (pick(kSTiles, 3, g_tuning[ACCBLAS_TUNE_SMMA_TILE], g.m, g.n, g.batch > 1 ? g.batch : 1)) {
     case 1:  return launch_sgemm_mma<AK, BKM, STile64>(g);
-    case 2:  return launch_sgemm_mma<AK, BKM, STile32>(g);
+    case 2:  {
+        const int S = splitk_slices(g, 32);
+        if (S >= 2) return with_splitk(g, S, [](const GemmArgs &h) { return launch_sgemm_mma<AK, BKM, STile32>(h); });
+        return launch_sgemm_mma<AK, BKM, STile32>(g);
+    }
     default: return launch_sgemm_mma<AK, BKM, STile128>(g);
     }
 }
@@ -704,8 +761,12 @@ template <bool AK, bool BKM, bool CA, bool CB>
 int cgemm_mma_tiles(const GemmArgs &g)
 {
     const int forced = g_tuning[ACCBLAS_TUNE_SMMA_TILE] < 0 ? -1 : (g_tuning[ACCBLAS_TUNE_SMMA_TILE] >= 2 ? 1 : 0);
-    return pick(kCTiles, 2, forced, g.m, g.n, g.batch > 1 ? g.batch : 1) == 1 ? launch_cgemm_mma<AK, BKM, CA, CB, CTile32>(g)
-                                                   : launch_cgemm_mma<AK, BKM, CA, CB, CTile64>(g);
+    if (pick(kCTiles, 2, forced, g.m, g.n, g.batch > 1 ? g.batch : 1) == 1) {
+        const int S = splitk_slices(g, 16);
+        if (S >= 2) return with_splitk(g, S, [](const GemmArgs &h) { return launch_cgemm_mma<AK, BKM, CA, CB, CTile32>(h); });
+        return launch_cgemm_mma<AK, BKM, CA, CB, CTile32>(g);
+    }
+    return launch_cgemm_mma<AK, BKM, CA, CB, CTile64>(g);
 }
 
 template <bool AK, bool BKM>

@@ -371,7 +371,9 @@ typedef enum {
                                        0 = copy into aligned scratch first (round 1), default: the DMMA kernel loads its panels itself   */
     ACCBLAS_TUNE_HOST_SCHEDULE = 19, /* accblas_gemm_host: 0 = always the block wavefront, 1 = always K-panel rank updates + row-panel finish,
                                         default: K-panels when the product is compute-bound against the PCIe link (csrc/host_pipeline.cu) */
-    ACCBLAS_TUNE_COUNT = 20
+    ACCBLAS_TUNE_SPLITK = 20,       /* f64 / c64 gemm: 0 = never split K over idle SMs (round 1), default: products of at most half a wave of
+                                       32 x 32 tiles with k >= 512 (c64: 256) run up to 16 K slices + a reduce kernel                 */
+    ACCBLAS_TUNE_COUNT = 21
 } accblas_tune_t;
 /* Process-wide defaults for threads that never call this: environment variable
  * ACCBLAS_TUNE="knob=value,knob=value" (read once). */

@@ -605,3 +605,54 @@ def test_host_pipeline_kpanels(dt, cuda):
                 ab.set_tuning(TUNE_HOST_SCHEDULE, -1)
                 ab.set_tuning(4, -1)
             assert O.gemm_error_units(C, W, A, B, k, al) <= 2 * tol, (O.NAMES[dt], oa, ob, "K-panels vs wavefront")
+
+
+# ------------------------------------------------------------------------------------------ split-K over idle SMs
+@pytest.mark.parametrize("dt", DTYPES, ids=ids)
+def test_gemm_splitk_small_grids_long_k(dt, cuda):
+    """Products of at most half a wave of 32 x 32 tiles with a long K (csrc/gemm_dmma.cu, csrc/gemm_mma_tf32.cu: K slices as the
+    batch index of one launch + a reduce kernel): every op pair, ragged K (last slice shorter, K not a multiple of the K-block), alpha; against
+    the wide oracle, against the unsplit kernel, and bit-reproducible run to run."""
+    import torch
+    import accblas_b200 as ab
+    TUNE_SPLITK = 20
+    rng = np.random.default_rng(12400 + dt)
+    for (m, n, k) in [(250, 250, 1024), (96, 96, 1031), (64, 200, 777), (33, 65, 4099)]:
+        for oa in "NTH":
+            for ob in "NTH":
+                al, A, B = gemm_inputs(rng, dt, oa, ob, m, n, k)
+                dA, dB = dev(A, cuda), dev(B, cuda)
+                ref = O.gemm(al, oa, A, ob, B, wide=True)
+                tol = TOL_UNITS_TF32X3 if dt in (O.F32, O.C32) else TOL_UNITS[dt]
+                C = ab.gemm(al, oa, dA, ob, dB)
+                assert O.gemm_error_units(host(C), ref, A, B, k, alpha=al) <= tol, (O.NAMES[dt], m, n, k, oa, ob)
+                assert torch.equal(C, ab.gemm(al, oa, dA, ob, dB)), "split-K sums its slices in a fixed order"
+                ab.set_tuning(TUNE_SPLITK, 0)
+                try:
+                    C0 = ab.gemm(al, oa, dA, ob, dB)
+                finally:
+                    ab.set_tuning(TUNE_SPLITK, -1)
+                assert O.gemm_error_units(host(C0), ref, A, B, k, alpha=al) <= tol
+                assert O.gemm_error_units(host(C), host(C0), A, B, k, alpha=al) <= 2 * tol
+    # an output window with its own pitch (accblas_gemm_ld): the reduce kernel writes rows at the caller's ldc
+    m, n, k = 100, 60, 2048
+    al, A, B = gemm_inputs(rng, dt, "N", "N", m, n, k)
+    big = torch.full((m, n + 12), 7.0, dtype=dev(A, cuda).dtype, device=cuda)
+    out = big[:, 4:4 + n]
+    ab.gemm(al, "N", dev(A, cuda), "N", dev(B, cuda), out=out)
+    assert O.gemm_error_units(host(out.contiguous()), O.gemm(al, "N", A, "N", B, wide=True), A, B, k, alpha=al) <= (
+        TOL_UNITS_TF32X3 if dt in (O.F32, O.C32) else TOL_UNITS[dt])
+    assert bool((big[:, :4] == 7.0).all()) and bool((big[:, 4 + n:] == 7.0).all()), "wrote outside the window"
+    if dt in (O.F32, O.C32):
+        # non-finite inputs: every slice refits ITS OWN K range, the sum has the FP32 pattern of the whole product
+        A = O.uniform(rng, (64, 2048), dt)
+        B = O.uniform(rng, (2048, 66), dt)
+        A[3, 7] = np.inf
+        B[1900, 5] = np.nan
+        A[9, 1500] = np.float32(3.4e38)             # TF32 rounding overflows; the product stays finite in FP32
+        B[1500, :] *= np.float32(1e-3)
+        C = host(ab.gemm(1, "N", dev(A, cuda), "N", dev(B, cuda)))
+        want = A.astype(np.complex128 if dt == O.C32 else np.float64) @ B.astype(np.complex128 if dt == O.C32 else np.float64)
+        fin = np.isfinite(want)
+        assert np.array_equal(np.isfinite(C), fin)
+        assert np.allclose(C[fin], want[fin].astype(C.dtype), rtol=2e-3, atol=1e-2 * np.abs(want[fin]).max())
