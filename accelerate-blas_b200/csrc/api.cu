@@ -3,6 +3,7 @@
 // There is NO CPU fallback anywhere in this file: every path ends in a kernel launch on
 // the caller's stream or in an error status.
 #include "common.cuh"
+#include <vector>
 #include <cstdio>
 #include <cstring>
 #include <cstdlib>
@@ -666,6 +667,33 @@ int accblas_amin(accblas_stream_t stream, int dtype, int64_t n, const void *x, i
 // -------------------------------------------------------------------------------------
 // host-buffer entry points (upload -> kernels -> download, all on `stream`)
 // -------------------------------------------------------------------------------------
+namespace {
+// the copy stream and events of the chunked gemv upload: per thread and device, created on first use and kept (like the side
+// streams of host_pipeline.cu); they carry no state between calls -- the entry points are synchronous
+struct HostPipe {
+    cudaStream_t copy = nullptr;
+    std::vector<cudaEvent_t> events;
+    size_t used = 0;
+    cudaError_t create() { return copy ? cudaSuccess : cudaStreamCreateWithFlags(&copy, cudaStreamNonBlocking); }
+    cudaEvent_t event() {
+        if (used == events.size()) {
+            cudaEvent_t e = nullptr;
+            cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
+            events.push_back(e);
+        }
+        return events[used++];
+    }
+};
+HostPipe &host_pipe()
+{
+    static thread_local HostPipe per_device[64];
+    int dev = 0;
+    cudaGetDevice(&dev);
+    HostPipe &h = per_device[(dev >= 0 && dev < 64) ? dev : 0];
+    h.used = 0;
+    return h;
+}
+}  // namespace
 int accblas_gemm_host(accblas_stream_t stream, int dtype, int opA, int opB, int64_t rowsA, int64_t colsA,
                       int64_t rowsB, int64_t colsB, const void *alpha_host, const void *A_host,
                       const void *B_host, void *C_host)
@@ -701,6 +729,34 @@ int accblas_gemv_host(accblas_stream_t stream, int dtype, int opA, int64_t rowsA
     ACC_CUDA(dA.alloc(es * (size_t)rowsA * (size_t)colsA));
     ACC_CUDA(dx.alloc(es * (size_t)lenx));
     ACC_CUDA(dy.alloc(es * (size_t)leny));
+    // op N on a large matrix: row chunks of A go up on a second stream and chunk i multiplies (y[chunk] = alpha * A[chunk, :] x)
+    // while chunk i + 1 is on the link -- the product is < 1 % of the transfer (1.2 ms against 155 ms for 32768^2 doubles),
+    // so all this hides is the product.  op T / H needs every row of A for every output and stays upload -> product -> download.
+    const size_t row_bytes = es * (size_t)colsA;
+    const int64_t chunk_rows = row_bytes ? std::max<int64_t>(1, (int64_t)(((size_t)16 << 20) / row_bytes)) : rowsA;
+    if (need > 0 && opA == ACCBLAS_OP_N && rowsA >= 4 * chunk_rows) {
+        HostPipe &hp = host_pipe();
+        ACC_CUDA(hp.create());
+        ACC_CUDA(cudaMemcpyAsync(dx.p, x_host, es * (size_t)lenx, cudaMemcpyHostToDevice, s));
+        cudaEvent_t start = hp.event();
+        ACC_CUDA(cudaEventRecord(start, s));
+        ACC_CUDA(cudaStreamWaitEvent(hp.copy, start, 0));
+        int st = ACCBLAS_OK;
+        for (int64_t r0 = 0; r0 < rowsA && st == ACCBLAS_OK; r0 += chunk_rows) {
+            const int64_t h = std::min(chunk_rows, rowsA - r0);
+            char *dchunk = static_cast<char *>(dA.p) + row_bytes * (size_t)r0;
+            ACC_CUDA(cudaMemcpyAsync(dchunk, static_cast<const char *>(A_host) + row_bytes * (size_t)r0, row_bytes * (size_t)h,
+                                     cudaMemcpyHostToDevice, hp.copy));
+            cudaEvent_t landed = hp.event();
+            ACC_CUDA(cudaEventRecord(landed, hp.copy));
+            ACC_CUDA(cudaStreamWaitEvent(s, landed, 0));
+            st = accblas_gemv(stream, dtype, opA, h, colsA, alpha_host, dchunk, dx.p, lenx, static_cast<char *>(dy.p) + es * (size_t)r0);
+        }
+        if (st == ACCBLAS_OK) ACC_CUDA(cudaMemcpyAsync(y_host, dy.p, es * (size_t)leny, cudaMemcpyDeviceToHost, s));
+        ACC_CUDA(cudaStreamSynchronize(s));
+        cudaStreamSynchronize(hp.copy);
+        return st;
+    }
     if (need > 0) {
         ACC_CUDA(cudaMemcpyAsync(dA.p, A_host, es * (size_t)rowsA * (size_t)colsA, cudaMemcpyHostToDevice, s));
         ACC_CUDA(cudaMemcpyAsync(dx.p, x_host, es * (size_t)lenx, cudaMemcpyHostToDevice, s));

@@ -201,7 +201,10 @@ int accblas_amin(accblas_stream_t stream, int dtype, int64_t n, const void *x, i
  * out are HOST pointers (pinned memory gives full PCIe rate, pageable works);
  * gemm overlaps upload, multiply and download as a wavefront over a block grid of C: step t
  * uploads row panel t of op(A) and column panel t of op(B), which releases the L-shaped strip
- * C[t, 0..t-1] + C[0..t, t] for multiplication (csrc/host_pipeline.cu).  Synchronous: returns
+ * C[t, 0..t-1] + C[0..t, t] for multiplication -- or, when the product is compute-bound against the PCIe link, as K-panel
+ * rank updates of the whole C followed by a row-panel finish with the downloads underneath (csrc/host_pipeline.cu).
+ * gemv op N uploads A in row chunks and multiplies chunk i under the upload of chunk i + 1; gemv op T / H and the Level-1
+ * routines are upload -> kernel -> download (their kernels are < 1 % of the transfer).  Synchronous: returns
  * when the result is in host memory.  `stream` orders the work like above.
  * ---------------------------------------------------------------------------------- */
 int accblas_gemm_host(accblas_stream_t stream, int dtype, int opA, int opB,

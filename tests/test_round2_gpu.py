@@ -656,3 +656,22 @@ def test_gemm_splitk_small_grids_long_k(dt, cuda):
         fin = np.isfinite(want)
         assert np.array_equal(np.isfinite(C), fin)
         assert np.allclose(C[fin], want[fin].astype(C.dtype), rtol=2e-3, atol=1e-2 * np.abs(want[fin]).max())
+
+
+# ------------------------------------------------------------------------------------------ gemv from host buffers, chunked upload
+@pytest.mark.parametrize("dt", [O.F64, O.C32], ids=ids)
+def test_gemv_host_chunked_upload(dt, cuda):
+    """accblas_gemv_host on a matrix large enough for the chunked upload (op N: row chunks of 16 MiB multiply under the next
+    chunk's transfer; ragged last chunk); T / H keep the serial flow.  Against the wide oracle and the device-resident call."""
+    import accblas_b200 as ab
+    rng = np.random.default_rng(12500 + dt)
+    m, n = 9001, 3000                                       # 216 MB (f64) / 216 MB (c32): 13 chunks, the last one short
+    A = O.uniform(rng, (m, n), dt)
+    for oa in "NTH":
+        x = O.uniform(rng, (n if oa == "N" else m,), dt)
+        al = O.uniform(rng, (1,), dt)[0]
+        y = ab.gemv(al, oa, A, x)                           # numpy operands: the host-buffer entry point
+        ref = O.gemv(al, oa, A, x, wide=True)
+        assert O.gemm_error_units(y, ref, A, x, x.shape[0], al) <= TOL_UNITS[dt], (O.NAMES[dt], oa)
+        yd = host(ab.gemv(al, oa, dev(A, cuda), dev(x, cuda)))
+        assert np.array_equal(y, yd) or O.gemm_error_units(y, yd, A, x, x.shape[0], al) <= TOL_UNITS[dt]
