@@ -376,7 +376,9 @@ typedef enum {
                                         default: K-panels when the product is compute-bound against the PCIe link (csrc/host_pipeline.cu) */
     ACCBLAS_TUNE_SPLITK = 20,       /* f64 / c64 gemm: 0 = never split K over idle SMs (round 1), default: products of at most half a wave of
                                        32 x 32 tiles with k >= 512 (c64: 256) run up to 16 K slices + a reduce kernel                 */
-    ACCBLAS_TUNE_COUNT = 21
+    ACCBLAS_TUNE_DOT_FUSED = 21,    /* dot: 0 = partial kernel + final kernel (round 1), default: one launch whose last CTA sums the partials
+                                       (needs 33 KiB of device memory kept per thread and stream)                                  */
+    ACCBLAS_TUNE_COUNT = 22
 } accblas_tune_t;
 /* Process-wide defaults for threads that never call this: environment variable
  * ACCBLAS_TUNE="knob=value,knob=value" (read once). */
