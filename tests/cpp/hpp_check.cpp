@@ -85,6 +85,9 @@ template <class T> void gemv_dot_case(std::mt19937_64 &g, Transpose oa, int64_t 
     const long double db = (lenx + 2) * eps_of<T>() * nx;
     EXPECT(std::abs(widen(dotu(dx, dz).value()) - su) <= db, "dotu dtype %d n %ld", numeric_traits<T>::dtype, (long)lenx);
     EXPECT(std::abs(widen(dotc(dx, dz).value()) - sc) <= db, "dotc dtype %d n %ld", numeric_traits<T>::dtype, (long)lenx);
+    // the compensated dot is at least as close (twice-double evaluation, one rounding to the element type)
+    EXPECT(std::abs(widen(dot_compensated(dx, dz, false).value()) - su) <= 4 * eps_of<T>() * std::abs(su) + 1e-30L,
+           "dot_compensated dtype %d n %ld", numeric_traits<T>::dtype, (long)lenx);
 }
 
 static void haddock() {
@@ -92,6 +95,8 @@ static void haddock() {
     // LinearAlgebra.hs:48-56  (<.>)
     EXPECT(dot(Vector<double>({1, 2, 3, 4}), Vector<double>({-2, 0, 1, 1})).value() == 5.0, "haddock dotu real");
     EXPECT(dot(Vector<cd>({cd(1, 1), cd(1, 0)}), Vector<cd>({cd(1, 0), cd(1, -1)})).value() == cd(2, 0), "haddock dotu complex");
+    // Numeric/Sum.hs:72-80  sum kbn [1.0, 1.0e100, 1.0, -1.0e100] == 2.0  (as a dot with ones)
+    EXPECT(dot_compensated(Vector<double>({1.0, 1.0e100, 1.0, -1.0e100}), Vector<double>({1, 1, 1, 1})).value() == 2.0, "haddock sum kbn");
     // LinearAlgebra.hs:65-71  (><)
     EXPECT(outer(Vector<double>({1, 2, 3}), Vector<double>({5, 2, 3})).to_host() == std::vector<double>({5, 2, 3, 10, 4, 6, 15, 6, 9}), "haddock outer");
     // LinearAlgebra.hs:86-95  (#>)   and :106-115  (<#)
