@@ -1235,10 +1235,11 @@ int launch_zgemm(const GemmArgs &g)
     case 2: {
         // split-K over idle SMs, as for the real 32 x 32 tile (launch_dgemm); a complex K-block is 8 wide
         const int64_t tiles32 = ((g.m + 31) / 32) * ((g.n + 31) / 32), kblocks = (g.k + ZBK - 1) / ZBK;
-        if (g.batch <= 1 && !beta && !delayed && g.ksplit == 0 && g_tuning[ACCBLAS_TUNE_SPLITK] != 0 && 2 * tiles32 <= sm_count() && kblocks >= 32) {
-            // two small CTAs per SM overlap their latency-bound K loops; a split must save more than the reduce launch costs
-            const int S = (int)std::min<int64_t>(std::min<int64_t>(2 * sm_count() / tiles32, kblocks / 8), 16);
-            if (S >= 2 && kblocks * (S - 1) >= 24 * (int64_t)S) {
+        if (g.batch <= 1 && !beta && !delayed && g.ksplit == 0 && g_tuning[ACCBLAS_TUNE_SPLITK] != 0 && 2 * tiles32 <= sm_count() && kblocks >= 12) {
+            // a complex K-block (8 wide, four DMMAs per tile product) costs ~0.5 us of a one-wave CTA's loop against ~0.3 us for
+            // a real one: the split pays from 16 K-blocks of saving, in slices of at least 4
+            const int S = (int)std::min<int64_t>(std::min<int64_t>(2 * sm_count() / tiles32, kblocks / 4), 16);
+            if (S >= 2 && kblocks * (S - 1) >= 16 * (int64_t)S) {
                 GemmArgs h = g;
                 h.ksplit = S;
                 ACC_CUDA(scratch_alloc(&h.ksplit_ws, sizeof(double2) * (size_t)S * (size_t)g.m * (size_t)g.n, g.stream));
