@@ -742,20 +742,25 @@ int accblas_gemv_host(accblas_stream_t stream, int dtype, int opA, int64_t rowsA
         ACC_CUDA(cudaEventRecord(start, s));
         ACC_CUDA(cudaStreamWaitEvent(hp.copy, start, 0));
         int st = ACCBLAS_OK;
-        for (int64_t r0 = 0; r0 < rowsA && st == ACCBLAS_OK; r0 += chunk_rows) {
+        cudaError_t ce = cudaSuccess;                 // no early return inside the loop: both streams are joined before the scratch goes
+        for (int64_t r0 = 0; r0 < rowsA && st == ACCBLAS_OK && ce == cudaSuccess; r0 += chunk_rows) {
             const int64_t h = std::min(chunk_rows, rowsA - r0);
             char *dchunk = static_cast<char *>(dA.p) + row_bytes * (size_t)r0;
-            ACC_CUDA(cudaMemcpyAsync(dchunk, static_cast<const char *>(A_host) + row_bytes * (size_t)r0, row_bytes * (size_t)h,
-                                     cudaMemcpyHostToDevice, hp.copy));
+            ce = cudaMemcpyAsync(dchunk, static_cast<const char *>(A_host) + row_bytes * (size_t)r0, row_bytes * (size_t)h,
+                                 cudaMemcpyHostToDevice, hp.copy);
             cudaEvent_t landed = hp.event();
-            ACC_CUDA(cudaEventRecord(landed, hp.copy));
-            ACC_CUDA(cudaStreamWaitEvent(s, landed, 0));
-            st = accblas_gemv(stream, dtype, opA, h, colsA, alpha_host, dchunk, dx.p, lenx, static_cast<char *>(dy.p) + es * (size_t)r0);
+            if (ce == cudaSuccess) ce = cudaEventRecord(landed, hp.copy);
+            if (ce == cudaSuccess) ce = cudaStreamWaitEvent(s, landed, 0);
+            if (ce == cudaSuccess)
+                st = accblas_gemv(stream, dtype, opA, h, colsA, alpha_host, dchunk, dx.p, lenx, static_cast<char *>(dy.p) + es * (size_t)r0);
         }
-        if (st == ACCBLAS_OK) ACC_CUDA(cudaMemcpyAsync(y_host, dy.p, es * (size_t)leny, cudaMemcpyDeviceToHost, s));
-        ACC_CUDA(cudaStreamSynchronize(s));
+        if (st == ACCBLAS_OK && ce == cudaSuccess) ce = cudaMemcpyAsync(y_host, dy.p, es * (size_t)leny, cudaMemcpyDeviceToHost, s);
         cudaStreamSynchronize(hp.copy);
-        return st;
+        const cudaError_t se = cudaStreamSynchronize(s);
+        if (st != ACCBLAS_OK) return st;
+        if (ce != cudaSuccess) return cuda_fail(ce, "accblas_gemv_host (chunked upload)");
+        if (se != cudaSuccess) return cuda_fail(se, "cudaStreamSynchronize");
+        return ACCBLAS_OK;
     }
     if (need > 0) {
         ACC_CUDA(cudaMemcpyAsync(dA.p, A_host, es * (size_t)rowsA * (size_t)colsA, cudaMemcpyHostToDevice, s));
