@@ -59,6 +59,18 @@ int cuda_fail(cudaError_t e, const char *where)
     return ACCBLAS_ERR_CUDA;
 }
 
+// A failure that is not a CUDA error but still deserves a sentence (a built-in limit exceeded): the text goes where
+// accblas_last_cuda_error / accblas_last_cuda_error_r find it, the status is returned unchanged.
+int fail_text(int status, const char *text)
+{
+    snprintf(g_cuda_err, sizeof(g_cuda_err), "%s", text);
+    {
+        std::lock_guard<std::mutex> lock(g_err_mu);
+        memcpy(g_cuda_err_any, g_cuda_err, sizeof(g_cuda_err_any));
+    }
+    return status;
+}
+
 namespace {
 struct DevInfo { int sms = 0; int cc_major = 0; };
 DevInfo &dev_info()

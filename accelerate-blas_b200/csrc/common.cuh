@@ -26,6 +26,7 @@ struct Tuning {
 extern thread_local Tuning g_tuning;
 
 int cuda_fail(cudaError_t e, const char *where);   // records text, returns ACCBLAS_ERR_CUDA
+int fail_text(int status, const char *text);       // records text for a non-CUDA failure, returns status
 inline int check_launch(const char *where) {
     ++g_launches;
     g_launches_total.fetch_add(1, std::memory_order_relaxed);

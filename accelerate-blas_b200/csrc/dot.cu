@@ -394,7 +394,86 @@ int dot_mg_typed(cudaStream_t st, bool conj, int64_t n, const T *x, const T *y, 
     return check_launch("dot_mg_kernel");
 }
 
+// ----------------------------------------------------------------------------------------------------------------
+// accblas_dot_static: the dot for callers that must not allocate
+// ----------------------------------------------------------------------------------------------------------------
+// The per-CTA partial sums of the two-kernel dot live in an array that is part of the library image instead of in
+// memory from a pool: loading libaccblas_b200.so on a GPU reserves it (ACCBLAS_DOT_STATIC_SLOTS x 32 bytes = 32 KiB)
+// and it stays until the process exits.  g_dot_static_scratch is a device symbol: device code may name it, host
+// code may NOT use the name as a pointer -- the host sees a stand-in object, and a kernel handed that would read
+// host memory or fault.  dot_static_scratch() asks the runtime for the real address, once per device.
+constexpr int DOT_STATIC_SLOT_BYTES = 32;
+static __device__ __align__(256) unsigned char g_dot_static_scratch[ACCBLAS_DOT_STATIC_SLOTS * DOT_STATIC_SLOT_BYTES];
+
+// Device address of the array on the CURRENT device (each device that loads the module has its own copy).  The look-up
+// is the one piece of set-up this entry point has; it makes the runtime load the module on that device if it has not
+// yet, which is why a first call per device belongs before any stream capture.  Process-wide table, not per thread:
+// the address belongs to the device, whichever host thread asks.
+int dot_static_scratch(void **out)
+{
+    static std::atomic<void *> addr[64];
+    int dev = 0;
+    ACC_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return cuda_fail(cudaErrorInvalidDevice, "accblas_dot_static: device ordinal beyond 63");
+    void *p = addr[dev].load(std::memory_order_acquire);
+    if (!p) {
+        ACC_CUDA(cudaGetSymbolAddress(&p, g_dot_static_scratch));
+        if (!p) return cuda_fail(cudaErrorInvalidSymbol, "cudaGetSymbolAddress(g_dot_static_scratch)");
+        addr[dev].store(p, std::memory_order_release);      // two threads racing here store the same value
+    }
+    *out = p;
+    return ACCBLAS_OK;
+}
+
+// Same CTA shape, grid and summation tree as accblas_dot's default path (the last CTA of dot_mg_kernel and
+// dot_final_kernel<.., THREADS> add the partials in the same order), so the two entry points return the same bits.
+template <typename T, typename P, int THREADS, int UNROLL, int MINB>
+int dot_static_launch(cudaStream_t st, bool conj, int64_t n, const T *x, const T *y, T *out)
+{
+    using Part = typename P::Part;
+    static_assert(sizeof(Part) <= DOT_STATIC_SLOT_BYTES, "a partial fits its slot");
+    const bool aligned = both_aligned(x, y);
+    const int grid = grid_for<T>(n, aligned, THREADS, MINB);
+    if (grid > ACCBLAS_DOT_STATIC_SLOTS)
+        return fail_text(ACCBLAS_ERR_WORKSPACE,
+                         "accblas_dot_static: this device wants more CTAs than the built-in scratch has slots "
+                         "(ACCBLAS_DOT_STATIC_SLOTS); use accblas_dot");
+    void *scratch = nullptr;
+    ACC_TRY(dot_static_scratch(&scratch));
+    Part *partial = static_cast<Part *>(scratch);
+    const bool cj = conj && Scalar<T>::cplx;
+    // every slot the second kernel reads is written by the first: nothing in the array has to start at zero
+#define GO(CJ, AL) dot_partial_kernel<T, P, CJ, AL, THREADS, UNROLL, MINB><<<grid, THREADS, 0, st>>>(n, x, y, partial)
+    if (aligned) { if (cj) GO(true, true); else GO(false, true); }
+    else         { if (cj) GO(true, false); else GO(false, false); }
+#undef GO
+    ACC_TRY(check_launch("dot_partial_kernel (static scratch)"));
+    dot_final_kernel<T, P, THREADS><<<1, THREADS, 0, st>>>(grid, partial, out);
+    return check_launch("dot_final_kernel (static scratch)");
+}
+
+template <typename T>
+int dot_static_typed(cudaStream_t st, bool conj, int64_t n, const T *x, const T *y, T *out)
+{
+    if (n == 0) {   // fold (+) 0 over nothing
+        ACC_CUDA(cudaMemsetAsync(out, 0, sizeof(T), st));
+        return ACCBLAS_OK;
+    }
+    if (sizeof(T) == 4) return dot_static_launch<T, Plain<T, 8>, 256, 8, 2>(st, conj, n, x, y, out);
+    return dot_static_launch<T, Plain<T, 4>, 512, 4, 2>(st, conj, n, x, y, out);
+}
+
 }  // namespace
+
+int dot_static_dispatch(cudaStream_t s, int dtype, int conj_x, int64_t n, const void *x, const void *y, void *out)
+{
+    switch (dtype) {
+    case ACCBLAS_F32: return dot_static_typed<float>(s, false, n, (const float *)x, (const float *)y, (float *)out);
+    case ACCBLAS_F64: return dot_static_typed<double>(s, false, n, (const double *)x, (const double *)y, (double *)out);
+    case ACCBLAS_C32: return dot_static_typed<float2>(s, conj_x != 0, n, (const float2 *)x, (const float2 *)y, (float2 *)out);
+    default:          return dot_static_typed<double2>(s, conj_x != 0, n, (const double2 *)x, (const double2 *)y, (double2 *)out);
+    }
+}
 
 int dot_dispatch(cudaStream_t s, int dtype, int conj_x, int64_t n, const void *x, const void *y, void *out, bool compensated)
 {
@@ -418,3 +497,20 @@ int dot_mg_dispatch(cudaStream_t s, int dtype, int conj_x, int64_t n, const void
 }
 
 }  // namespace accblas
+
+// See include/accblas_b200.h.  Argument checks come first and touch no CUDA state, so the limits can be probed on a
+// machine without a GPU.
+extern "C" int accblas_dot_static(accblas_stream_t stream, int dtype, int conj_x, int64_t n, const void *x, const void *y,
+                                  void *out_dev)
+{
+    using namespace accblas;
+    if (dtype != ACCBLAS_F32 && dtype != ACCBLAS_F64 && dtype != ACCBLAS_C32 && dtype != ACCBLAS_C64) return ACCBLAS_ERR_DTYPE;
+    if (n < 0) return ACCBLAS_ERR_SHAPE;
+    if (n > ACCBLAS_DOT_STATIC_MAX_N)
+        return fail_text(ACCBLAS_ERR_WORKSPACE,
+                         "accblas_dot_static: n is beyond ACCBLAS_DOT_STATIC_MAX_N (2^32 elements); use accblas_dot");
+    if (!out_dev) return ACCBLAS_ERR_NULL;
+    if (n > 0 && (!x || !y)) return ACCBLAS_ERR_NULL;
+    ACC_TRY(device_check());
+    return dot_static_dispatch(static_cast<cudaStream_t>(stream), dtype, conj_x, n, x, y, out_dev);
+}

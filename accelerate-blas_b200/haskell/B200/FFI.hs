@@ -13,7 +13,7 @@
 module Data.Array.Accelerate.Numeric.LinearAlgebra.LLVM.PTX.B200.FFI (
 
   DType(..), dtypeCode, opCode, Status, checkStatus,
-  c_accblas_gemm, c_accblas_gemv, c_accblas_dot, c_accblas_dot_compensated,
+  c_accblas_gemm, c_accblas_gemv, c_accblas_dot, c_accblas_dot_compensated, c_accblas_dot_static,
   c_accblas_gemm_alpha_dev, c_accblas_gemv_alpha_dev,
   c_accblas_sdot, c_accblas_asum, c_accblas_amax, c_accblas_amin,
   c_accblas_gemm_strided_batched, c_accblas_set_tuning,
@@ -75,6 +75,13 @@ foreign import ccall unsafe "accblas_dot_compensated"
   c_accblas_dot_compensated :: Ptr () -> CInt -> CInt -> Int64
                             -> Ptr () -> Ptr () -> Ptr ()
                             -> IO Status
+
+-- accblas_dot with its partial sums in a fixed array inside the library: allocates nothing, so it cannot disturb
+-- the backend's memory table (Data.Array.Accelerate.LLVM.PTX.Array.Remote).  One call at a time per device.
+foreign import ccall unsafe "accblas_dot_static"
+  c_accblas_dot_static :: Ptr () -> CInt -> CInt -> Int64
+                       -> Ptr () -> Ptr () -> Ptr ()
+                       -> IO Status
 
 -- alpha as the device Scalar it already is (BLAS/Level3.hs:64): no indexRemote, no stream sync
 foreign import ccall unsafe "accblas_gemm_alpha_dev"

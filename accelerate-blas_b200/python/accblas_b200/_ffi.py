@@ -15,7 +15,7 @@ LIB_PATH = os.environ.get("ACCBLAS_B200_LIB", os.path.join(PKG_ROOT, "lib", "lib
 # every symbol include/accblas_b200.h declares (tests/test_abi.py checks this list against the header)
 SYMBOLS = (
     "accblas_gemm", "accblas_gemm_ld", "accblas_gemm_ex", "accblas_last_cuda_error_r", "accblas_launch_count_total",
-    "accblas_trim_workspace", "accblas_workspace_cached_bytes", "accblas_gemm_strided_batched", "accblas_gemm_alpha_dev", "accblas_gemv_alpha_dev", "accblas_gemm_workspace_bytes", "accblas_gemv", "accblas_dot", "accblas_dot_compensated",
+    "accblas_trim_workspace", "accblas_workspace_cached_bytes", "accblas_gemm_strided_batched", "accblas_gemm_alpha_dev", "accblas_gemv_alpha_dev", "accblas_gemm_workspace_bytes", "accblas_gemv", "accblas_dot", "accblas_dot_compensated", "accblas_dot_static",
     "accblas_gemm_host", "accblas_gemv_host", "accblas_dot_host",
     "accblas_sdot", "accblas_asum", "accblas_amax", "accblas_amin",
     "accblas_sdot_host", "accblas_asum_host", "accblas_amax_host", "accblas_amin_host",
@@ -80,6 +80,8 @@ def lib() -> ctypes.CDLL:
     L.accblas_dot_host.argtypes = L.accblas_dot.argtypes
     L.accblas_dot_compensated.argtypes = L.accblas_dot.argtypes
     L.accblas_dot_compensated.restype = ci
+    L.accblas_dot_static.argtypes = L.accblas_dot.argtypes
+    L.accblas_dot_static.restype = ci
     L.accblas_sdot.argtypes = [vp, ci, i64, vp, vp, vp, vp]
     L.accblas_sdot_host.argtypes = L.accblas_sdot.argtypes
     for f in (L.accblas_asum, L.accblas_asum_host, L.accblas_amax, L.accblas_amax_host, L.accblas_amin,

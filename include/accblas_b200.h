@@ -172,6 +172,35 @@ int accblas_dot(accblas_stream_t stream, int dtype, int conj_x, int64_t n,
  * multiplied exactly and summed in double).  Same HBM traffic as accblas_dot, same fixed summation tree. */
 int accblas_dot_compensated(accblas_stream_t stream, int dtype, int conj_x, int64_t n,
                             const void *x, const void *y, void *out_dev);
+/* accblas_dot for callers that cannot let the library allocate device memory.  No counterpart in the reference
+ * (which has no foreign dot at all); it exists for hosts like these:
+ *   - a runtime that budgets the whole of HBM through its own memory manager (Accelerate's llvm-ptx backend keeps a
+ *     table of every device array and evicts by it): memory a foreign function takes behind its back is memory the
+ *     manager still believes free, and the next allocation of either side can fail;
+ *   - a process whose device memory has all been handed to an arena or caching allocator, where cudaMalloc simply
+ *     returns out-of-memory;
+ *   - latency-sensitive callers with several streams in flight: cudaMalloc / cudaFree synchronise the device.
+ * accblas_dot keeps 33 KiB from cudaMalloc per (host thread, device, stream) or takes its partial sums from the
+ * library's memory pool.  This variant does neither: the per-CTA partial sums go to a fixed array inside the library
+ * image (ACCBLAS_DOT_STATIC_SLOTS slots of 32 bytes = 32 KiB; every GPU that loads the library holds it until the
+ * process exits).  It calls no cudaMalloc, cudaFree, pool or other allocating routine; x, y and out_dev are still the
+ * caller's.  Same arguments, same result BITS as accblas_dot with default tuning (same grid, same summation tree);
+ * two launches instead of one.
+ *
+ * Limits (ACCBLAS_ERR_WORKSPACE, with a sentence in accblas_last_cuda_error): n <= ACCBLAS_DOT_STATIC_MAX_N, and the
+ * launch must need at most ACCBLAS_DOT_STATIC_SLOTS CTAs (it uses two per SM: 296 on a B200).  Use accblas_dot beyond.
+ *
+ * First call on each device: looks the array's device address up (cudaGetSymbolAddress, which may load the module on
+ * that device) with that device current -- make that first call outside any stream capture.  Later calls do no set-up.
+ *
+ * Every call on a device shares the one array, whatever the stream or host thread.  Calls on the same stream are
+ * ordered and safe.  Calls that can run on the GPU at the same time (different streams, no event between them)
+ * overwrite each other's partial sums and return garbage: serialise them, or use accblas_dot for all but one stream.
+ * Nothing in the array has to be zero between calls: each call writes every slot it later reads. */
+#define ACCBLAS_DOT_STATIC_SLOTS 1024
+#define ACCBLAS_DOT_STATIC_MAX_N ((int64_t)1 << 32)
+int accblas_dot_static(accblas_stream_t stream, int dtype, int conj_x, int64_t n,
+                       const void *x, const void *y, void *out_dev);
 
 /* ------------------------------------------------------------------------------------
  * The other Level-1 reductions of the reference (BLAS/Level1.hs).  Like dot they are plain
