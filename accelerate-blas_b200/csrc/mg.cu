@@ -93,7 +93,11 @@ struct Comm {
     uint32_t seq = 0;                              // exchange collectives issued so far
     // sharded dot (one launch, dot.cu): [arrival counter | per-CTA partials]; the counter returns to zero by itself
     char *dot_scratch = nullptr;
+    // staging for the plan's handle broadcast: owned by the communicator so that a plan never has to allocate
+    // (and possibly fail) between deciding to enter a collective and entering it
+    char *wire = nullptr;
 };
+constexpr size_t MG_WIRE_BYTES = 512;
 constexpr int MG_DOT_GRID = 1024;                  // CTAs the fused dot may launch (partials: 32 bytes each)
 
 // ------------------------------------------------------------------------------------------------------------
@@ -135,16 +139,26 @@ __global__ void __launch_bounds__(256) mg_push_kernel(PeerPtrs peers, int rank, 
 // flag in every peer; every CTA waits for all peers' flags here, then
 //   GATHER : copies slice r (slice_bytes each) of the result from rank r's deposit            (gemv N)
 //   REDUCE : sums the deposits elementwise in rank order                                       (gemv T/H)
+// The deposits of a GATHER need not have the same length (accblas_mg_row_panel hands out whole 128-row tiles: m = 1000
+// on 8 ranks is 7 x 128 + 104, m = 256 leaves ranks 2..7 empty): every rank writes its element count into the spare
+// bytes of its 64-byte flag line (offset 8) before it raises the flag, and the gather places deposit r behind the
+// deposits of ranks 0..r-1.
 template <typename T, bool REDUCE>
 __global__ void __launch_bounds__(256) mg_collect_kernel(PeerPtrs peers, int rank, int world, size_t parity_off, uint32_t seq,
-                                                         T *out, size_t elems /*per deposit*/)
+                                                         T *out, size_t elems /*this rank's deposit*/)
 {
     if (blockIdx.x == 0 && threadIdx.x < world) {
+        char *line = peers.p[threadIdx.x] + parity_off + 64 * rank;
+        *reinterpret_cast<unsigned long long *>(line + 8) = (unsigned long long)elems;
         __threadfence_system();
-        st_release_sys(reinterpret_cast<uint32_t *>(peers.p[threadIdx.x] + parity_off + 64 * rank), seq);
+        st_release_sys(reinterpret_cast<uint32_t *>(line), seq);
     }
     const char *own = peers.p[rank] + parity_off;
-    if (threadIdx.x < world) wait_flag(reinterpret_cast<const uint32_t *>(own + 64 * threadIdx.x), seq);
+    __shared__ unsigned long long count[MG_MAX_RANKS];
+    if (threadIdx.x < world) {
+        wait_flag(reinterpret_cast<const uint32_t *>(own + 64 * threadIdx.x), seq);
+        count[threadIdx.x] = __ldcv(reinterpret_cast<const unsigned long long *>(own + 64 * threadIdx.x + 8));
+    }
     __syncthreads();
     const size_t stride = (size_t)gridDim.x * blockDim.x, i0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (REDUCE) {
@@ -154,9 +168,13 @@ __global__ void __launch_bounds__(256) mg_collect_kernel(PeerPtrs peers, int ran
             out[i] = acc;
         }
     } else {
-        for (int r = 0; r < world; ++r)
-            for (size_t i = i0; i < elems; i += stride)
-                out[(size_t)r * elems + i] = __ldcv(reinterpret_cast<const T *>(own + XFLAGS + (size_t)r * XSLOT) + i);
+        size_t at = 0;
+        for (int r = 0; r < world; ++r) {
+            const size_t len = (size_t)count[r];
+            for (size_t i = i0; i < len; i += stride)
+                out[at + i] = __ldcv(reinterpret_cast<const T *>(own + XFLAGS + (size_t)r * XSLOT) + i);
+            at += len;
+        }
     }
 }
 
@@ -178,7 +196,7 @@ int exchange(Comm *c, cudaStream_t s, const void *mine, size_t elems, T *out)
     dim3 grid((unsigned)std::max<size_t>(1, std::min<size_t>((vecs + 255) / 256, 16)), (unsigned)c->world);
     mg_push_kernel<<<grid, 256, 0, s>>>(pp, c->rank, off, static_cast<const int4 *>(mine), vecs);
     ACC_TRY(check_launch("mg_push_kernel"));
-    const size_t total = REDUCE ? elems : elems * (size_t)c->world;
+    const size_t total = REDUCE ? elems : std::max<size_t>(elems, 256) * (size_t)c->world;   // gather: the peers' lengths are not known here
     const unsigned blocks = (unsigned)std::max<size_t>(1, std::min<size_t>((total + 255) / 256, 2 * (size_t)sm_count()));
     mg_collect_kernel<T, REDUCE><<<blocks, 256, 0, s>>>(pp, c->rank, c->world, off, seq, out, elems);
     return check_launch("mg_collect_kernel");
@@ -242,6 +260,7 @@ int accblas_mg_init(accblas_mg_comm_t *comm_out, int rank, int world, const void
     ACC_CUDA(cudaMemset(c->token, 0, 64));
     ACC_CUDA(cudaMalloc(reinterpret_cast<void **>(&c->dot_scratch), 64 + 32 * (size_t)MG_DOT_GRID));
     ACC_CUDA(cudaMemset(c->dot_scratch, 0, 64 + 32 * (size_t)MG_DOT_GRID));
+    ACC_CUDA(cudaMalloc(reinterpret_cast<void **>(&c->wire), MG_WIRE_BYTES));
     // exchange buffer: cudaMalloc (IPC needs a plain allocation), zeroed, handle all-gathered, peers mapped
     c->xparity = XFLAGS + (size_t)world * XSLOT;
     ACC_CUDA(cudaMalloc(reinterpret_cast<void **>(&c->xbuf), 2 * c->xparity));
@@ -282,6 +301,7 @@ int accblas_mg_finalize(accblas_mg_comm_t comm)
     if (c->xbuf) cudaFree(c->xbuf);
     if (c->token) cudaFree(c->token);
     if (c->dot_scratch) cudaFree(c->dot_scratch);
+    if (c->wire) cudaFree(c->wire);
     if (c->pull) cudaStreamDestroy(c->pull);
     delete c;
     return ACCBLAS_OK;
@@ -343,55 +363,85 @@ int accblas_mg_gemm_plan(accblas_mg_comm_t comm, int dtype, int opA, int opB, in
     const int nc = accblas_mg_k_chunks(p->k, k0, dk, 64);
     for (int i = 0; i < nc; ++i) p->chunks.push_back(Chunk{k0[i], dk[i]});
     const size_t es = elem_size(dtype);
-    // the root describes the allocations behind A, B, C; everyone else maps them (accblas_peer_*)
-    accblas_peer_handle_t hs[3];
-    memset(hs, 0, sizeof hs);
+    // The root describes the allocations behind A, B, C; everyone else maps them (accblas_peer_*).  From here on the
+    // call is COLLECTIVE: no rank may leave between the broadcast and the closing agreement, whatever failed locally,
+    // or the others would wait in a collective forever.  Failures are recorded in `st` and travel with the data.
+    struct Wire { accblas_peer_handle_t hs[3]; int32_t status; int32_t pad[3]; };
+    static_assert(sizeof(Wire) <= MG_WIRE_BYTES, "the plan's broadcast fits the communicator's staging buffer");
+    Wire w;
+    memset(&w, 0, sizeof w);
+    int st = ACCBLAS_OK;
     if (c->rank == root) {
-        if ((p->m > 0 && p->n > 0 && !C) || (p->k > 0 && p->m > 0 && p->n > 0 && (!A || !B))) { delete p; return ACCBLAS_ERR_NULL; }
+        if ((p->m > 0 && p->n > 0 && !C) || (p->k > 0 && p->m > 0 && p->n > 0 && (!A || !B))) st = ACCBLAS_ERR_NULL;
         const void *ptrs[3] = {A, B, C};
-        for (int i = 0; i < 3; ++i)
-            if (ptrs[i] && c->world > 1) {
-                const int st = accblas_peer_export(ptrs[i], &hs[i]);
-                if (st != ACCBLAS_OK) { delete p; return st; }
-            }
+        for (int i = 0; i < 3 && st == ACCBLAS_OK; ++i)
+            if (ptrs[i] && c->world > 1) st = accblas_peer_export(ptrs[i], &w.hs[i]);
         p->A = static_cast<const char *>(A); p->B = static_cast<const char *>(B); p->C = static_cast<char *>(C);
+        w.status = st;
     }
     if (c->world > 1) {
-        unsigned char *hd = nullptr;
-        ACC_CUDA(cudaMalloc(reinterpret_cast<void **>(&hd), sizeof hs));
-        if (c->rank == root) ACC_CUDA(cudaMemcpy(hd, hs, sizeof hs, cudaMemcpyHostToDevice));
-        ACC_NCCL(g_nccl.Broadcast(hd, hd, sizeof hs, NCCL_UINT8, root, c->nccl, nullptr));
-        ACC_CUDA(cudaStreamSynchronize(nullptr));
-        ACC_CUDA(cudaMemcpy(hs, hd, sizeof hs, cudaMemcpyDeviceToHost));
-        cudaFree(hd);
+        // the root's verdict rides with the handles: a root that could not export gives EVERY rank the same error
+        if (c->rank == root) {
+            const cudaError_t e = cudaMemcpy(c->wire, &w, sizeof w, cudaMemcpyHostToDevice);
+            if (e != cudaSuccess && st == ACCBLAS_OK) st = cuda_fail(e, "accblas_mg_gemm_plan: staging the handles");
+        }
+        const int rc = g_nccl.Broadcast(c->wire, c->wire, sizeof w, NCCL_UINT8, root, c->nccl, nullptr);
+        if (rc != 0) { delete p; return nccl_fail(rc, "accblas_mg_gemm_plan: ncclBroadcast"); }   // the communicator itself is gone
+        cudaError_t e = cudaStreamSynchronize(nullptr);
+        if (e == cudaSuccess) e = cudaMemcpy(&w, c->wire, sizeof w, cudaMemcpyDeviceToHost);
+        if (e != cudaSuccess && st == ACCBLAS_OK) st = cuda_fail(e, "accblas_mg_gemm_plan: reading the handles");
+        if (st == ACCBLAS_OK && w.status != ACCBLAS_OK) {
+            st = w.status;
+            fail_text(st, "accblas_mg_gemm_plan: the root rank could not describe its operands (see its own error text)");
+        }
     }
     const bool self_peer = c->rank == root && g_tuning[ACCBLAS_TUNE_MG_SELF_PEER] == 1;
     p->as_peer = c->rank != root || self_peer;
-    if (p->as_peer && p->rows > 0 && p->n > 0) {
-        if (!self_peer) {
-            void *mapped[3] = {nullptr, nullptr, nullptr};
-            for (int i = 0; i < 3; ++i)
-                if (hs[i].size) {
-                    const int st = accblas_peer_open(&hs[i], &mapped[i]);
-                    if (st != ACCBLAS_OK) { delete p; return st; }
-                }
-            p->A = static_cast<const char *>(mapped[0]); p->B = static_cast<const char *>(mapped[1]); p->C = static_cast<char *>(mapped[2]);
+    auto local_setup = [&]() -> int {
+        if (p->as_peer && p->rows > 0 && p->n > 0) {
+            if (!self_peer) {
+                void *mapped[3] = {nullptr, nullptr, nullptr};
+                for (int i = 0; i < 3; ++i)
+                    if (w.hs[i].size) ACC_TRY(accblas_peer_open(&w.hs[i], &mapped[i]));
+                p->A = static_cast<const char *>(mapped[0]); p->B = static_cast<const char *>(mapped[1]); p->C = static_cast<char *>(mapped[2]);
+            }
+            // local replicas: this rank's panel of A (stored layout), all of B, and -- when the product is chunked --
+            // the accumulator panel (the last chunk writes to the root instead)
+            const size_t bytesA = es * (size_t)p->rows * (size_t)p->k, bytesB = es * (size_t)p->k * (size_t)p->n;
+            if (p->k > 0) {
+                ACC_CUDA(cudaMalloc(reinterpret_cast<void **>(&p->A_loc), std::max<size_t>(bytesA, 16)));
+                ACC_CUDA(cudaMalloc(reinterpret_cast<void **>(&p->B_loc), std::max<size_t>(bytesB, 16)));
+            }
+            if (p->chunks.size() > 1) ACC_CUDA(cudaMalloc(reinterpret_cast<void **>(&p->C_acc), es * (size_t)p->rows * (size_t)p->n));
+            for (size_t i = 0; i < p->chunks.size(); ++i) {
+                cudaEvent_t e;
+                ACC_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+                p->landed.push_back(e);
+            }
         }
-        // local replicas: this rank's panel of A (stored layout), all of B, and -- when the product is chunked --
-        // the accumulator panel (the last chunk writes to the root instead)
-        const size_t bytesA = es * (size_t)p->rows * (size_t)p->k, bytesB = es * (size_t)p->k * (size_t)p->n;
-        if (p->k > 0) {
-            ACC_CUDA(cudaMalloc(reinterpret_cast<void **>(&p->A_loc), std::max<size_t>(bytesA, 16)));
-            ACC_CUDA(cudaMalloc(reinterpret_cast<void **>(&p->B_loc), std::max<size_t>(bytesB, 16)));
-        }
-        if (p->chunks.size() > 1) ACC_CUDA(cudaMalloc(reinterpret_cast<void **>(&p->C_acc), es * (size_t)p->rows * (size_t)p->n));
-        for (size_t i = 0; i < p->chunks.size(); ++i) {
-            cudaEvent_t e;
-            ACC_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-            p->landed.push_back(e);
-        }
+        ACC_CUDA(cudaEventCreateWithFlags(&p->go, cudaEventDisableTiming));
+        return ACCBLAS_OK;
+    };
+    if (st == ACCBLAS_OK) st = local_setup();
+    if (c->world > 1) {
+        // closing agreement: a plan exists on every rank or on none (a rank that could not map or allocate must not
+        // leave the others with a plan whose run would wait for it).  The token carries the count of failed ranks.
+        const double mine = st == ACCBLAS_OK ? 0.0 : 1.0;
+        double failed = 1.0;
+        cudaError_t e = cudaMemcpy(c->token, &mine, sizeof mine, cudaMemcpyHostToDevice);
+        const int rc = g_nccl.AllReduce(c->token, c->token, 1, NCCL_FLOAT64, NCCL_SUM, c->nccl, nullptr);
+        if (rc != 0) { accblas_mg_gemm_plan_destroy(reinterpret_cast<accblas_mg_plan_t>(p)); return nccl_fail(rc, "accblas_mg_gemm_plan: ncclAllReduce"); }
+        if (e == cudaSuccess) e = cudaStreamSynchronize(nullptr);
+        if (e == cudaSuccess) e = cudaMemcpy(&failed, c->token, sizeof failed, cudaMemcpyDeviceToHost);
+        cudaMemset(c->token, 0, sizeof(double));                                  // the run tokens add zeros
+        if (e != cudaSuccess && st == ACCBLAS_OK) st = cuda_fail(e, "accblas_mg_gemm_plan: closing agreement");
+        if (st == ACCBLAS_OK && failed != 0.0)
+            st = cuda_fail(cudaErrorUnknown, "accblas_mg_gemm_plan: another rank could not set its plan up (see that rank's error text)");
     }
-    ACC_CUDA(cudaEventCreateWithFlags(&p->go, cudaEventDisableTiming));
+    if (st != ACCBLAS_OK) {
+        accblas_mg_gemm_plan_destroy(reinterpret_cast<accblas_mg_plan_t>(p));     // frees whatever was set up
+        return st;
+    }
     *plan_out = reinterpret_cast<accblas_mg_plan_t>(p);
     return ACCBLAS_OK;
 }
@@ -426,6 +476,10 @@ int accblas_mg_gemm_run(accblas_mg_plan_t plan, accblas_stream_t stream, const v
     static const float one_f[2] = {1.f, 0.f};
     const void *one = (p->dtype == ACCBLAS_F32 || p->dtype == ACCBLAS_C32) ? static_cast<const void *>(one_f) : one_d;
 
+    // Everything between the two tokens is LOCAL work.  Its first failure ends the local work only: the "done" token
+    // below is still enqueued, because the other ranks enter it whatever happened here (a rank that returned early
+    // would leave them waiting in the all-reduce).
+    auto local_work = [&]() -> int {
     int st = ACCBLAS_OK;
     if (!p->as_peer) {
         // the root multiplies its own panel in place: nothing to move
@@ -490,6 +544,9 @@ int accblas_mg_gemm_run(accblas_mg_plan_t plan, accblas_stream_t stream, const v
             }
         }
     }
+    return st;
+    };
+    const int st = local_work();
     // "done": when this has run on the root's stream, every peer's last kernel -- and its stores into C -- has finished
     if (c->world > 1) ACC_NCCL(g_nccl.AllReduce(c->token, c->token, 1, NCCL_FLOAT64, NCCL_SUM, c->nccl, s));
     return st;
@@ -522,16 +579,18 @@ int accblas_mg_gemv(accblas_mg_comm_t comm, accblas_stream_t stream, int dtype, 
     const size_t es = elem_size(dtype);
     const bool n_op = opA == ACCBLAS_OP_N;
     const int64_t leny_local = n_op ? rows_local : colsA;
-    if (leny_local == 0) return ACCBLAS_OK;
-    if (!y_full) return ACCBLAS_ERR_NULL;
+    // T / H: colsA is the same on every rank, so this return is taken by all of them or by none.  N with an empty
+    // local panel still has to take part in the exchange below (the other ranks wait for this rank's flag).
+    if (!n_op && leny_local == 0) return ACCBLAS_OK;
+    if (!y_full && (leny_local > 0 || c->world == 1)) return ACCBLAS_ERR_NULL;
     if (es * (size_t)leny_local > XSLOT) return ACCBLAS_ERR_WORKSPACE;          // beyond the exchange slot: shard coarser
     // local product into scratch (16-byte aligned, whole vectors: the deposit is copied in 16-byte units)
     char *mine = nullptr;
     ACC_CUDA(scratch_alloc(reinterpret_cast<void **>(&mine), es * (size_t)leny_local + 16, s));
-    int st = accblas_gemv(stream, dtype, opA, rows_local, colsA, alpha_host, A_local, x, lenx, mine);
+    int st = leny_local > 0 ? accblas_gemv(stream, dtype, opA, rows_local, colsA, alpha_host, A_local, x, lenx, mine) : ACCBLAS_OK;
     if (st == ACCBLAS_OK) {
         const size_t elems = (size_t)leny_local;
-        if (n_op) {          // all-gather of the row slices (equal panels)
+        if (n_op) {          // all-gather of the row slices, each rank's length travelling with its deposit
             st = dtype == ACCBLAS_F32 ? exchange<float, false>(c, s, mine, elems, static_cast<float *>(y_full))
                : dtype == ACCBLAS_F64 ? exchange<double, false>(c, s, mine, elems, static_cast<double *>(y_full))
                : dtype == ACCBLAS_C32 ? exchange<float2, false>(c, s, mine, elems, static_cast<float2 *>(y_full))

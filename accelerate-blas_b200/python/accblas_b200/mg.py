@@ -207,12 +207,15 @@ class Comm:
         return GemmPlan(self, opA, A, opB, B, shapeA, shapeB, dtype, out, root)
 
     # ---- gemv / dot over the exchange buffer ----
-    def gemv(self, alpha, opA, A_local: torch.Tensor, x: torch.Tensor, out: Optional[torch.Tensor] = None):
+    def gemv(self, alpha, opA, A_local: torch.Tensor, x: torch.Tensor, out: Optional[torch.Tensor] = None,
+             m_total: Optional[int] = None):
+        """op N: the row panels may differ in height, down to empty (each rank's length travels with its deposit);
+        ``m_total`` = rows of the whole matrix = length of y.  Without it the panels are taken to be equal."""
         ct = self._ct
         opa = {"N": 0, "T": 1, "H": 2}.get(opA, opA)
         A_local, x = A_local.contiguous(), x.contiguous()
         rows, cols = A_local.shape
-        leny = self.world * rows if opa == 0 else cols
+        leny = (self.world * rows if m_total is None else int(m_total)) if opa == 0 else cols
         y = out if out is not None else torch.empty((leny,), dtype=A_local.dtype, device=A_local.device)
         al = np.array([alpha], dtype=_NP[A_local.dtype])
         with torch.cuda.device(self.device):
@@ -300,20 +303,35 @@ def _gemm_rowsharded_peer(alpha, opa, A, opb, B, shapeA, shapeB, mnk, dtype, dev
 
 
 def gemv_sharded(alpha, opA, A_local: torch.Tensor, x: torch.Tensor, *, group=None,
-                 local_gemv: Optional[Callable] = None):
+                 local_gemv: Optional[Callable] = None, m_total: Optional[int] = None):
     """y = alpha * op(A) * x with the ROWS of the stored A pre-sharded (A_local = this rank's row panel).
 
     op N: x is the full vector on every rank (broadcast by the caller or replicated); returns the
-          full y on every rank (all-gather of the row slices; panels must be equal-sized).
+          full y on every rank (all-gather of the row slices).  Panels cut by ``row_panels(m_total, world)``
+          (= accblas_mg_row_panel: whole 128-row tiles, so the last ones can be short or empty) need ``m_total``;
+          without it the panels must be equal-sized.
     op T/H: x is this rank's slice of the vector; returns the full y on every rank (all-reduce).
     """
     if local_gemv is None and A_local.is_cuda:
-        return get_comm(A_local.device, group).gemv(alpha, opA, A_local, x)      # exchange over peer memory (C ABI)
+        return get_comm(A_local.device, group).gemv(alpha, opA, A_local, x, m_total=m_total)   # exchange over peer memory (C ABI)
     if local_gemv is None:
         import accblas_b200 as ab
         local_gemv = ab.gemv
     opa = {"N": 0, "T": 1, "H": 2}.get(opA, opA)
     world = dist.get_world_size(group)
+    if opa == 0 and m_total is not None:
+        # ragged panels on a backend without a variable-length gather: pad every slice to the tallest panel
+        panels = row_panels(int(m_total), world)
+        rows = panels[dist.get_rank(group)][1]
+        if rows != A_local.shape[0]:
+            raise ValueError(f"gemv_sharded: this rank's panel has {A_local.shape[0]} rows, row_panels gives {rows}")
+        tall = max(r for _, r in panels)
+        padded = torch.zeros((tall,), dtype=A_local.dtype, device=A_local.device)
+        if rows > 0:
+            padded[:rows] = local_gemv(alpha, opa, A_local, x)
+        full = torch.empty((world * tall,), dtype=padded.dtype, device=padded.device)
+        dist.all_gather_into_tensor(full, padded, group=group)
+        return torch.cat([full[r * tall:r * tall + n] for r, (_, n) in enumerate(panels)])
     y = local_gemv(alpha, opa, A_local, x)
     if opa == 0:
         full = torch.empty((world * y.shape[0],), dtype=y.dtype, device=y.device)

@@ -64,6 +64,13 @@ def _worker(rank, world, port, q):
         half = slice(rank * 128, (rank + 1) * 128)
         y = mg.gemv_sharded(1.0, "N", torch.from_numpy(A[half]), torch.from_numpy(x), local_gemv=_local_gemv)
         res["gemv_N"] = O.gemm_error_units(y.numpy(), O.gemv(1.0, "N", A, x), A, x, 100)
+        # ragged panels, as accblas_mg_row_panel cuts them: 200 rows on 2 ranks = 128 + 72, 100 rows = 100 + 0
+        for mt in (200, 100):
+            s0, r0 = mg.row_panels(mt, 2)[rank]
+            y = mg.gemv_sharded(1.0, "N", torch.from_numpy(A[s0:s0 + r0]), torch.from_numpy(x), local_gemv=_local_gemv,
+                                m_total=mt)
+            assert y.shape == (mt,)
+            res[f"gemv_N_ragged_{mt}"] = O.gemm_error_units(y.numpy(), O.gemv(1.0, "N", A[:mt], x), A[:mt], x, 100)
         x2 = O.uniform(rng, (256,), O.F64)
         y = mg.gemv_sharded(1.0, "T", torch.from_numpy(A[half]), torch.from_numpy(x2[half]), local_gemv=_local_gemv)
         res["gemv_T"] = O.gemm_error_units(y.numpy(), O.gemv(1.0, "T", A, x2), A, x2, 256)

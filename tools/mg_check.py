@@ -69,6 +69,19 @@ def check(dev, rank, world, quick=False):
             assert err <= 1.0, ("plan/run", rep, err)
             cases += 1
     plan.destroy()
+    # a plan the ROOT cannot make (its C is host memory: no CUDA IPC handle exists for it) fails on EVERY rank -- before
+    # round 3 the root returned early and the peers waited in the handle broadcast forever -- and leaves the communicator
+    # usable (the exchanges further down run on it)
+    if world > 1 and not quick:
+        import ctypes as ct
+        bogus = np.zeros(m * n)
+        hnd = ct.c_void_p()
+        root_ptr = lambda t: ct.c_void_p(t.data_ptr()) if rank == 0 else ct.c_void_p(0)   # noqa: E731
+        with torch.cuda.device(dev):
+            st = comm.L.accblas_mg_gemm_plan(comm.handle, 1, 0, 0, m, k, k, n, root_ptr(tA), root_ptr(tB),
+                                             ct.c_void_p(bogus.ctypes.data if rank == 0 else 0), 0, ct.byref(hnd))
+        assert st != 0 and not hnd.value, ("plan with a host C must fail on every rank", rank, st)
+        cases += 1
     # 2-D block sharding (mg.gemm_2d, SUMMA K-loop) on the grids this world size allows
     grids = [(1, world), (world, 1)] + ([(2, world // 2)] if world >= 4 and world % 2 == 0 else [])
     for (pr, pc) in grids[:1] if quick else grids:
@@ -99,6 +112,12 @@ def check(dev, rank, world, quick=False):
         for rep in range(3):      # back-to-back collectives alternate the two halves of the exchange buffer
             y = mg.gemv_sharded(1.0, "N", torch.from_numpy(A[sl]).to(dev), torch.from_numpy(x).to(dev))
             assert O.gemm_error_units(y.cpu().numpy(), O.gemv(1.0, "N", A, x), A, x, n) <= 2.0
+            # panels as accblas_mg_row_panel cuts them: unequal (the last one short) and, for m = 256, EMPTY on ranks >= 2
+            for mt in (m - 24, 256):
+                s0, r0 = mg.row_panels(mt, world)[rank]
+                y = mg.gemv_sharded(1.0, "N", torch.from_numpy(A[s0:s0 + r0]).to(dev), torch.from_numpy(x).to(dev), m_total=mt)
+                assert y.shape == (mt,)
+                assert O.gemm_error_units(y.cpu().numpy(), O.gemv(1.0, "N", A[:mt], x), A[:mt], x, n) <= 2.0
             for op in ("T", "H"):
                 y = mg.gemv_sharded(1.0, op, torch.from_numpy(A[sl]).to(dev), torch.from_numpy(x2[sl]).to(dev))
                 assert O.gemm_error_units(y.cpu().numpy(), O.gemv(1.0, op, A, x2), A, x2, m) <= 2.0
