@@ -225,6 +225,16 @@ int gemm_device(GemmArgs &g)
     if (g.m == 0 || g.n == 0) return ACCBLAS_OK;                       // nothing to write
     if (!g.C || !g.alpha) return ACCBLAS_ERR_NULL;
     const size_t es = elem_size(g.dtype);
+    const size_t bytesC = es * span(g.m, g.n, g.ldc);
+    if (has_beta(g)) {                                                 // checked first: the k == 0 product reads Cin too
+        // Cin is either the output itself (same base AND pitch: in place) or an array that does not touch it
+        if (g.ldcin == 0) g.ldcin = g.ldc;
+        if (g.ldcin < g.n) return ACCBLAS_ERR_SHAPE;
+        const bool in_place = g.Cin == g.C && g.ldcin == g.ldc;
+        if (!in_place && overlaps(g.C, bytesC, g.Cin, es * span(g.m, g.n, g.ldcin))) return ACCBLAS_ERR_ALIAS;
+    } else {
+        g.beta = nullptr; g.Cin = nullptr;
+    }
     if (g.k == 0 && !has_beta(g)) {                                    // alpha * (empty sum) = 0
         ACC_CUDA(cudaMemset2DAsync(g.C, es * (size_t)g.ldc, 0, es * (size_t)g.n, (size_t)g.m, g.stream));
         return ACCBLAS_OK;
@@ -234,16 +244,6 @@ int gemm_device(GemmArgs &g)
         return gemm_generic(g);
     }
     if (!g.A || !g.B) return ACCBLAS_ERR_NULL;
-    const size_t bytesC = es * span(g.m, g.n, g.ldc);
-    if (has_beta(g)) {
-        // Cin is either the output itself (same base AND pitch: in place) or an array that does not touch it
-        if (g.ldcin == 0) g.ldcin = g.ldc;
-        if (g.ldcin < g.n) return ACCBLAS_ERR_SHAPE;
-        const bool in_place = g.Cin == g.C && g.ldcin == g.ldc;
-        if (!in_place && overlaps(g.C, bytesC, g.Cin, es * span(g.m, g.n, g.ldcin))) return ACCBLAS_ERR_ALIAS;
-    } else {
-        g.beta = nullptr; g.Cin = nullptr;
-    }
     if (overlaps(g.C, bytesC, g.A, es * span(g.rowsA, g.colsA, g.lda)) ||
         overlaps(g.C, bytesC, g.B, es * span(g.rowsB, g.colsB, g.ldb)))
         return ACCBLAS_ERR_ALIAS;

@@ -299,16 +299,27 @@ constexpr int DOT_SLOT_GRID = 1024;
 char *dot_slot(cudaStream_t st)
 {
     struct Entry { int dev; cudaStream_t st; char *mem; };
-    static thread_local Entry entries[32];
-    static thread_local int count = 0;
+    // the slots die with the host thread that made them (cudaFree waits for the launches still using one; at process
+    // exit the runtime may already be gone and the call fails harmlessly)
+    struct Slots {
+        Entry e[32];
+        int count = 0;
+        ~Slots() { for (int i = 0; i < count; ++i) cudaFree(e[i].mem); }
+    };
+    static thread_local Slots slots;
+    Entry *entries = slots.e;
+    int &count = slots.count;
     if (g_tuning[ACCBLAS_TUNE_DOT_FUSED] == 0) return nullptr;
+    // A capture must not bake a slot into a graph: the graph could be replayed on another stream, twice at once, or
+    // beside eager dots of this stream, and all of those would share the arrival counter.  Checked BEFORE the cache
+    // look-up -- a stream that already owns a slot can start capturing later.  Captured dots take the two-kernel path.
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(st, &cap) != cudaSuccess || cap != cudaStreamCaptureStatusNone) { cudaGetLastError(); return nullptr; }
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess) return nullptr;
     for (int i = 0; i < count; ++i)
         if (entries[i].dev == dev && entries[i].st == st) return entries[i].mem;
     if (count == 32) return nullptr;
-    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
-    if (cudaStreamIsCapturing(st, &cap) != cudaSuccess || cap != cudaStreamCaptureStatusNone) { cudaGetLastError(); return nullptr; }
     char *mem = nullptr;
     const size_t bytes = 64 + 32 * (size_t)DOT_SLOT_GRID;
     if (cudaMalloc(reinterpret_cast<void **>(&mem), bytes) != cudaSuccess || cudaMemset(mem, 0, bytes) != cudaSuccess) {

@@ -191,6 +191,9 @@ gemv_t_slab_kernel(int64_t m_all, int64_t n, Alpha<T> alpha_, const T *__restric
     __shared__ T part[SLAB_MAXR][SLAB_CV * VEC];                  // rank 0: the other ranks' partial slabs
     const uint32_t R = slab_cluster_size(), rank = slab_cluster_rank();
     const int64_t slab = blockIdx.x / R;
+    // "I am running": distributed shared memory of a CTA may only be touched once that CTA has started.  Arrive here,
+    // wait just before the remote stores below -- the streaming loop in between hides the barrier's latency.
+    if (R > 1) asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
     // this CTA's rows [row0, row0 + m)
     const int64_t row0 = m_all * rank / R, m = m_all * (rank + 1) / R - row0;
     const T *__restrict__ x = x_all + row0;
@@ -239,6 +242,7 @@ gemv_t_slab_kernel(int64_t m_all, int64_t n, Alpha<T> alpha_, const T *__restric
     }
     if (R > 1) {
         // hand the partial slab to rank 0 (distributed shared memory), which adds them in rank order
+        asm volatile("barrier.cluster.wait.aligned;" ::: "memory");      // every CTA of the cluster has started (see entry)
         if (rank != 0 && threadIdx.x < SLAB_CV * VEC) {
             const uint32_t local = (uint32_t)__cvta_generic_to_shared(&part[rank][threadIdx.x]);
             uint32_t remote;

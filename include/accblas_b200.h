@@ -134,8 +134,12 @@ int accblas_gemm_alpha_dev(accblas_stream_t stream, int dtype, int opA, int opB,
 int accblas_gemv_alpha_dev(accblas_stream_t stream, int dtype, int opA, int64_t rowsA, int64_t colsA,
                            const void *alpha_dev, const void *A, const void *x, int64_t lenx, void *y);
 
-/* Bytes of stream-ordered scratch accblas_gemm will take from the library's memory pool for this
- * problem (0 for the direct kernels).  Informational. */
+/* Bytes of stream-ordered scratch the MAIN kernel family of accblas_gemm takes from the library's memory pool for
+ * this problem: the hi / lo planes of the 3xTF32 path, the 3M planes, the stream-K accumulator slots (0 for the direct
+ * kernels).  Informational, and a lower bound: it leaves out the two small extras a call may add -- the split-K
+ * partial planes of a small product spread over idle SMs (S * m * n elements, S <= 16, products of at most a few
+ * hundred rows and columns) and the re-pitched copy of an operand off the 16-byte grid (that operand's size with
+ * its pitch rounded up).  accblas_workspace_cached_bytes() after a call shows what was really taken. */
 size_t accblas_gemm_workspace_bytes(int dtype, int opA, int opB,
                                     int64_t rowsA, int64_t colsA, int64_t rowsB, int64_t colsB);
 
@@ -293,16 +297,25 @@ int accblas_peer_copy2d(accblas_stream_t stream, void *dst, size_t dst_pitch, co
  *                          from the root's HBM with the copy engines in K-chunks (accblas_mg_k_chunks), multiply
  *                          each chunk as it lands (beta = 1 accumulation, accblas_gemm_ex) and store the last chunk's
  *                          result straight into the root's C over NVLink (gather fused into the epilogue).  The
- *                          root's A, B, C must come from cudaMalloc (CUDA IPC).  Collective, stream-ordered: when
- *                          the call's work has completed on the root's stream, C is complete.
+ *                          root's A, B, C must come from cudaMalloc (CUDA IPC).  Collective.  This one-shot form
+ *                          plans, runs, WAITS for the stream and frees the peers' replicas on every call (it is
+ *                          synchronous); loops should use the plan / run split below, whose run is stream-ordered:
+ *                          when its work has completed on the root's stream, C is complete.
+ *                          A failure on any rank while planning (an operand that is not a cudaMalloc allocation, a
+ *                          mapping or replica that cannot be made) is reported on EVERY rank and no rank keeps a
+ *                          plan; a failure of one rank's local work in run still passes the closing token, so the
+ *                          other ranks return instead of waiting.
  *   accblas_mg_gemm_plan / _run / _plan_destroy
  *                          the same, split: the plan exchanges the IPC handles and allocates the peers' replicas
  *                          once, so that a loop over the same arrays pays no handle exchange or host
  *                          synchronisation per product.
- *   accblas_mg_gemv        y = alpha * op(A) * x with the ROWS of the stored A pre-sharded (A_local = rows_local x colsA;
- *                          equal panels).  op N: x (colsA) replicated, every rank receives the full y
- *                          (world * rows_local).  op T / H: x = this rank's slice (rows_local); every rank receives the
- *                          full y (colsA), partials summed in rank order.
+ *   accblas_mg_gemv        y = alpha * op(A) * x with the ROWS of the stored A pre-sharded (A_local = rows_local x colsA).
+ *                          op N: x (colsA) replicated, every rank receives the full y = the ranks' slices in rank
+ *                          order.  The panels may differ in height and may be empty (accblas_mg_row_panel cuts whole
+ *                          128-row tiles: m = 1000 on 8 ranks is 7 x 128 + 104, m = 256 leaves ranks 2..7 empty):
+ *                          each rank's length travels with its deposit; y_full holds the SUM of all rows_local, and a
+ *                          rank with no rows still makes the call.  op T / H: x = this rank's slice (rows_local);
+ *                          every rank receives the full y (colsA), partials summed in rank order.
  *   accblas_mg_dot         dotu / dotc over pre-sharded slices; every rank receives the scalar in out_dev.
  *                          gemv / dot exchange through IPC-mapped buffers with flags (no collective kernel);
  *                          at most 1 MiB of y per rank (ACCBLAS_ERR_WORKSPACE beyond).  Calls on one communicator

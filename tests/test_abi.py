@@ -50,6 +50,15 @@ def test_argument_validation_needs_no_gpu():
     assert L.accblas_gemv(None, 1, 1, 2, 3, p, p, p, 3, p) == 3
     assert L.accblas_dot(None, 1, 0, -1, p, p, p) == 3
     assert L.accblas_dot(None, 1, 0, 4, p, p, None) == 4
+    # D = beta * Cin with an empty inner extent (k == 0) reads Cin like any other product: its pitch and its
+    # overlap with C are checked before the dispatch (m = 2, n = 4, k = 0)
+    buf = np.zeros(64)
+    q = lambda off: ctypes.c_void_p(buf.ctypes.data + 8 * off)                                     # noqa: E731
+    ex = L.accblas_gemm_ex
+    assert ex(None, 1, 0, 0, 2, 0, 0, 4, p, None, 0, None, 0, p, q(32), 3, q(0), 4) == 3            # ldcin < n
+    assert ex(None, 1, 0, 0, 2, 0, 0, 4, p, None, 0, None, 0, p, q(2), 4, q(0), 4) == 8             # Cin overlaps C
+    assert ex(None, 1, 0, 0, 2, 0, 0, 4, p, None, 0, None, 0, p, q(0), 5, q(0), 4) == 8             # same base, other pitch
+    assert ex(None, 1, 0, 0, 2, 0, 0, 4, p, None, 0, None, 0, p, None, 4, q(0), 4) == 4             # beta without Cin
     # strided batch: negative stride / batch, outputs that would overlap, operand stride inside one operand
     sb = L.accblas_gemm_strided_batched
     assert sb(None, 1, 0, 0, 2, 3, 3, 2, p, p, -1, p, 6, p, 4, 2) == 3
