@@ -311,7 +311,23 @@ def run_single(args):
     }
     if args.extras:
         line["extras"] = extras(peak, peak_src, mp, total_ms / args.steps)
+        line["summary"] = summary_of(line["extras"])
     print(json.dumps(line), flush=True)
+
+
+def summary_of(ex):
+    """Every BASELINE.json config of the extras in a few hundred bytes, as the LAST key of the line (a record that keeps
+    only the tail of stdout still holds it): case -> [ms, rate (TFLOP/s or GB/s), roofline fraction, time of cuBLAS /
+    own time (> 1: ahead), parity error in tolerance units, median SM MHz during the case]."""
+    out = {"columns": ["ms", "tflops_or_gbs", "roofline_frac", "vs_cublas", "error_units", "sm_mhz"]}
+    for e in ex:
+        if "ms" not in e:
+            continue
+        name = e["case"].replace("gemm_", "").replace("32768x32768x32768_1gpu", "32768^3_T1")
+        name = name.replace("8192x8192x8192", "8192^3").replace("4096x4096x4096", "4096^3").replace("1024x1024x1024", "1024^3")
+        out[name] = [e["ms"], e.get("tflops", e.get("gbs")), (e.get("roofline") or {}).get("frac"), e.get("vs_cublas"),
+                     (e.get("parity") or {}).get("error_units"), (e.get("clocks") or {}).get("sm_mhz")]
+    return out
 
 
 def run_multi(args):
@@ -411,7 +427,26 @@ def run_multi(args):
         assert err <= 1.0, f"parity lost in multi-GPU bench: {err}"
         peak, peak_src = DMMA_PEAK_FALLBACK, "baseline/ubench dmma_m8n8k4 issue rate on this pool (profiles/)"
         value = flops * args.steps / total_ms * 1e-9
-        comm_bytes = 8.0 * n * n * (1 + 2.0 * (world - 1) / world)     # bcast B + scatter A + gather C (per root link)
+        # what really crosses the root's links in the pull design: every peer reads ALL of B and its own panel of A out
+        # of the root's HBM, and stores its panel of C into it
+        egress = 8.0 * n * n * ((world - 1) + (world - 1) / world)
+        ingress = 8.0 * n * n * (world - 1) / world
+        # T1 of THIS product on rank 0 alone, same run, same box (after the parity rows above were read: it rewrites C)
+        t1_ms = None
+        if args.t1:
+            try:
+                ab.gemm(1.0, "N", A, "N", B, out=C)
+                torch.cuda.synchronize()
+                c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                reps = 3 if n >= 16384 else 10
+                c0.record()
+                for _ in range(reps):
+                    ab.gemm(1.0, "N", A, "N", B, out=C)
+                c1.record()
+                torch.cuda.synchronize()
+                t1_ms = c0.elapsed_time(c1) / reps
+            except torch.cuda.OutOfMemoryError:
+                t1_ms = None
         line = {
             "metric": METRIC, "value": round(value, 3), "unit": "TFLOP/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": round(total_ms / args.steps, 3), "higher_is_better": True,
@@ -421,7 +456,8 @@ def run_multi(args):
                          "frac": round(value / world / peak, 4), "traffic": None,
                          "kernel": "dgemm_dmma (persistent schedule) per rank, K-chunked; achieved = whole-job rate / ranks "
                                    "(includes every inter-GPU transfer)", "peak_source": peak_src,
-                         "nvlink_bytes_through_root": comm_bytes},
+                         "root_egress_bytes": egress, "root_ingress_bytes": ingress,
+                         "link_note": "pull design: (N-1) |B| + (N-1)/N |A| leave the root, (N-1)/N |C| arrives"},
             "cpu_baseline": None,
             "e2e": {"value": round(value, 3), "unit": "TFLOP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0,
                     "note": "operands and result are device-resident on rank 0 by definition of configs[4]; the "
@@ -435,6 +471,13 @@ def run_multi(args):
         line["overhead_vs_panel_product_ms"] = round(total_ms / args.steps - bms.item(), 3)
         line["mg_check"] = {"cases": mg_cases, "worst_gemm_error_units": round(mg_worst, 5), "when": "before timing, every rank"}
         line["extras"] = l12
+        # last keys: survive a record that keeps only the tail of stdout
+        line["summary"] = {"ms_per_step": round(total_ms / args.steps, 3), "t1_ms": round(t1_ms, 3) if t1_ms else None,
+                           "speedup_vs_t1": round(t1_ms / (total_ms / args.steps), 4) if t1_ms else None,
+                           "t1_note": "the same n^3 product on rank 0 alone (accblas_gemm, operands resident), same run",
+                           "panel_product_ms": round(bms.item(), 3), "tflops_per_gpu": round(value / world, 3),
+                           "mg_check_cases": mg_cases, "error_units": round(err, 5), "sm_mhz": clocks.get("sm_mhz")}
+    dist.barrier()                                # the other ranks wait here while rank 0 measures T1
     dist.destroy_process_group()
     sys.stdout.flush()
     os.dup2(saved_stdout, 1)
@@ -701,6 +744,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--extras", dest="extras", action="store_true", default=True)
     ap.add_argument("--no-extras", dest="extras", action="store_false")
+    ap.add_argument("--no-t1", dest="t1", action="store_false", default=True,
+                    help="N > 1: skip the single-GPU time of the same product (rank 0 alone, after the timed region)")
     ap.add_argument("--n-mg", type=int, default=NMG, dest="n_mg")
     ap.add_argument("--subpanels", type=int, default=4)
     ap.add_argument("--transport", default="peer", choices=["peer", "p2p"],
