@@ -5,7 +5,7 @@
 // cuBLAS is called the way the reference calls it (operand swap, beta = 0, LLVM/PTX/Level3.hs:91-106,
 // LLVM/PTX/Level2.hs:105-124).  REPORTED BASELINE TOOL: nothing here is part of the product.
 //
-// usage: sidebyside [filter-substring] [iters]      modes: "ref" shapes, "big" configs, "host" e2e
+// usage: sidebyside [filter-substring | refshapes | ksweep | tiles | families] [iters]
 #include <cublas_v2.h>
 #include <cuda_runtime.h>
 #include <algorithm>
@@ -310,6 +310,9 @@ int main(int argc, char **argv) {
     if (!strcmp(filter, "k1024")) { filter = ""; gemm_case(1, 'N', 'N', 250, 250, 1024, 20); gemm_case(1, 'N', 'N', 250, 250, 250, 20); gemm_case(1, 'N', 'N', 100, 100, 100, 20); return 0; }
     if (!strcmp(filter, "tiles")) { tile_sweep(); return 0; }
     if (!strcmp(filter, "families")) { family_sweep(); return 0; }
+    // "refshapes": only the 16 gemm + 32 gemv / gevm cases the reference itself benchmarks (bench.py's extras run this)
+    const bool ref_only = !strcmp(filter, "refshapes");
+    if (ref_only) filter = "";
     // --- the reference's own benchmark shapes (bench/Bench/Accelerate.hs) ---
     for (int dt = 0; dt < 4; ++dt)
         for (long n : {100L, 250L, 500L, 1000L}) gemm_case(dt, 'N', 'N', n, n, n, 200);
@@ -318,6 +321,7 @@ int main(int argc, char **argv) {
             gemv_case(dt, 'N', sh.first, sh.second, 200);
             gemv_case(dt, 'T', sh.first, sh.second, 200);
         }
+    if (ref_only) return 0;
     // --- BASELINE.json configs and the sizes in between ---
     for (long n : {512L, 1024L, 2048L, 4096L}) gemm_case(1, 'N', 'N', n, n, n, 50);
     for (long n : {2048L, 4096L}) gemm_case(0, 'N', 'N', n, n, n, 50);

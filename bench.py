@@ -321,6 +321,9 @@ def summary_of(ex):
     own time (> 1: ahead), parity error in tolerance units, median SM MHz during the case]."""
     out = {"columns": ["ms", "tflops_or_gbs", "roofline_frac", "vs_cublas", "error_units", "sm_mhz"]}
     for e in ex:
+        if e.get("case") == "reference_benchmark_shapes":
+            out["ref_shapes_vs_cublas_sustained"] = e.get("summary")
+            continue
         if "ms" not in e:
             continue
         name = e["case"].replace("gemm_", "").replace("32768x32768x32768_1gpu", "32768^3_T1")
@@ -565,6 +568,41 @@ def cublas_arm(cases, iters=8):
     return out
 
 
+def ref_shapes_arm():
+    """The reference's OWN benchmark workload (bench/Bench/Accelerate.hs:44-58,92-125: gemm 100 / 250 / 500 / 1000 cubed and
+    gemv / gevm 200x400 .. 2000x3000, four element types = 48 cases), this library and cuBLAS timed by the same C driver
+    (baseline/sidebyside, a subprocess) on the same buffers: per-call events and the sustained time of 400 calls back to
+    back.  Returns (cases, clocks over the whole arm)."""
+    exe = os.path.join(ROOT, "baseline", "sidebyside")
+    if not os.path.exists(exe):
+        return [], None
+    sampler = ClockSampler(0).start()
+    t0 = time.time()
+    rows = []
+    try:
+        res = subprocess.run([exe, "refshapes"], capture_output=True, text=True, timeout=300)
+        for l in res.stdout.splitlines():
+            if l.startswith("{"):
+                rows.append(json.loads(l))
+    except Exception as e:
+        rows.append({"case": "ref_shapes_arm", "error": repr(e)})
+    return rows, sampler.stop(t0, time.time())
+
+
+def ref_shapes_summary(rows):
+    """sustained time of cuBLAS / sustained time of this library per case (> 1: ahead), condensed."""
+    r = {d["case"]: d["speedup_stream"] for d in rows if "speedup_stream" in d}
+    if not r:
+        return None
+    import math
+    behind = sorted((v, k) for k, v in r.items() if v < 1.0)
+    return {"cases": len(r), "at_or_ahead_of_cublas": sum(1 for v in r.values() if v >= 1.0),
+            "within_2pct": sum(1 for v in r.values() if v >= 0.98),
+            "geomean": round(math.exp(sum(math.log(v) for v in r.values()) / len(r)), 4),
+            "min": round(min(r.values()), 3), "max": round(max(r.values()), 3),
+            "behind": {k: round(v, 3) for v, k in behind[:8]}}
+
+
 def extras(dmma_peak, dmma_src, mp, headline_ms):
     """Every other BASELINE.json config at N = 1 (configs[0..3] and the T1 of configs[4]); see the module docstring."""
     import numpy as np
@@ -733,6 +771,14 @@ def extras(dmma_peak, dmma_src, mp, headline_ms):
             e["vs_cublas"] = round(c["ms_median"] / e["ms"], 4)      # > 1: this library is faster
     if "error" in cb:
         out.append({"case": "cublas_arm", "error": cb["error"]})
+    # ---- the reference's own benchmark shapes, both libraries in one C driver
+    rs, rs_clocks = ref_shapes_arm()
+    if rs:
+        out.append({"case": "reference_benchmark_shapes", "source": "bench/Bench/Accelerate.hs:44-58,92-125 via baseline/sidebyside refshapes",
+                    "clocks": rs_clocks, "summary": ref_shapes_summary(rs),
+                    "columns": ["case", "kernel", "accblas_us_sustained", "cublas_us_sustained", "cublas/accblas"],
+                    "rows": [[d.get("case"), d.get("kernel"), round(1e3 * d.get("accblas_ms_stream", 0), 2),
+                              round(1e3 * d.get("cublas_ms_stream", 0), 2), d.get("speedup_stream")] for d in rs]})
     return out
 
 
