@@ -448,8 +448,9 @@ def run_multi(args):
                 c1.record()
                 torch.cuda.synchronize()
                 t1_ms = c0.elapsed_time(c1) / reps
-            except torch.cuda.OutOfMemoryError:
+            except Exception:                     # an optional extra must not cost the line (e.g. out of memory)
                 t1_ms = None
+                torch.cuda.empty_cache()
         line = {
             "metric": METRIC, "value": round(value, 3), "unit": "TFLOP/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": round(total_ms / args.steps, 3), "higher_is_better": True,
@@ -475,11 +476,15 @@ def run_multi(args):
         line["mg_check"] = {"cases": mg_cases, "worst_gemm_error_units": round(mg_worst, 5), "when": "before timing, every rank"}
         line["extras"] = l12
         # last keys: survive a record that keeps only the tail of stdout
-        line["summary"] = {"ms_per_step": round(total_ms / args.steps, 3), "t1_ms": round(t1_ms, 3) if t1_ms else None,
-                           "speedup_vs_t1": round(t1_ms / (total_ms / args.steps), 4) if t1_ms else None,
-                           "t1_note": "the same n^3 product on rank 0 alone (accblas_gemm, operands resident), same run",
-                           "panel_product_ms": round(bms.item(), 3), "tflops_per_gpu": round(value / world, 3),
-                           "mg_check_cases": mg_cases, "error_units": round(err, 5), "sm_mhz": clocks.get("sm_mhz")}
+        try:
+            line["summary"] = {"ms_per_step": round(total_ms / args.steps, 3), "t1_ms": round(t1_ms, 3) if t1_ms else None,
+                               "speedup_vs_t1": round(t1_ms / (total_ms / args.steps), 4) if t1_ms else None,
+                               "t1_note": "the same n^3 product on rank 0 alone (accblas_gemm, operands resident), same run",
+                               "panel_product_ms": round(bms.item(), 3), "tflops_per_gpu": round(value / world, 3),
+                               "mg_check_cases": mg_cases, "error_units": round(err, 5),
+                               "sm_mhz": (clocks or {}).get("sm_mhz")}
+        except Exception as e:                    # a convenience key must never cost the line
+            line["summary"] = {"error": repr(e)}
     dist.barrier()                                # the other ranks wait here while rank 0 measures T1
     dist.destroy_process_group()
     sys.stdout.flush()
